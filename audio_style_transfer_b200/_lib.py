@@ -1,0 +1,118 @@
+"""ctypes binding of libast_b200.so (include/ast_b200.h) and its in-tree nvcc build.
+
+The product path has NO CPU fallback: if the shared library is missing or no sm_100 GPU is present,
+`load()` / `Context()` raise.  PyTorch is used by callers only to own device memory and streams;
+nothing torch-typed crosses this boundary (plain pointers and sizes).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+PKG = Path(__file__).resolve().parent
+ROOT = PKG.parent
+SO = PKG / "libast_b200.so"
+SOURCES = ["csrc/api.cu", "csrc/kernels_f32.cu", "csrc/kernels_tc.cu"]
+HEADERS = ["csrc/common.cuh", "csrc/tc.cuh", "../include/ast_b200.h"]
+
+AST_PREC_FP32 = 0
+AST_PREC_BF16 = 1
+AST_MAX_IDS = 32
+ERRORS = {-1: "AST_EINVAL", -2: "AST_ECUDA", -3: "AST_EUNSUPPORTED", -4: "AST_ESTATE"}
+
+SYMBOLS = [
+    "ast_create", "ast_destroy", "ast_last_error", "ast_version", "ast_workspace_bytes",
+    "ast_set_weights", "ast_set_targets", "ast_embeds", "ast_step", "ast_step_host",
+    "ast_step_forward", "ast_partials", "ast_step_backward", "ast_get_extract",
+    "ast_launches_per_step", "ast_step_timed",
+]
+
+
+class AstConfig(C.Structure):
+    _fields_ = [
+        ("T", C.c_int32), ("B", C.c_int32), ("n_layers", C.c_int32),
+        ("n_cont", C.c_int32), ("cont_ids", C.c_int32 * AST_MAX_IDS),
+        ("n_style", C.c_int32), ("style_ids", C.c_int32 * AST_MAX_IDS),
+        ("gatys", C.c_int32), ("nb_channels", C.c_int32), ("cnt_channels", C.c_int32),
+        ("precision", C.c_int32),
+        ("total_T", C.c_int64), ("win_begin", C.c_int64), ("own_begin", C.c_int64), ("own_end", C.c_int64),
+        ("device", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+class AstError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"{ERRORS.get(code, code)}: {msg}")
+        self.code = code
+
+
+def nvcc_command(out: Path = SO):
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    return [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+            "-shared", "-Xcompiler", "-fPIC", "-o", str(out)] + [str(PKG / s) for s in SOURCES]
+
+
+def needs_build() -> bool:
+    if not SO.exists():
+        return True
+    t = SO.stat().st_mtime
+    return any((PKG / p).resolve().stat().st_mtime > t for p in SOURCES + HEADERS)
+
+
+def build(force: bool = False, verbose: bool = False) -> Path:
+    """Compile every CUDA source for sm_100a into the in-tree libast_b200.so (nvcc cross-compiles
+    without a GPU)."""
+    if force or needs_build():
+        cmd = nvcc_command()
+        if verbose:
+            print(" ".join(cmd), file=sys.stderr)
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
+    return SO
+
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """dlopen the in-tree library and declare every prototype of include/ast_b200.h."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not SO.exists():
+        raise ImportError(f"{SO} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(there is no CPU fallback for the step)")
+    lib = C.CDLL(str(SO))
+    vp, i32, i64, dbl = C.c_void_p, C.c_int32, C.c_int64, C.c_double
+    lib.ast_create.argtypes = [C.POINTER(AstConfig), C.POINTER(vp)]
+    lib.ast_destroy.argtypes = [vp]
+    lib.ast_last_error.restype = C.c_char_p
+    lib.ast_version.restype = C.c_char_p
+    lib.ast_workspace_bytes.argtypes = [vp]
+    lib.ast_workspace_bytes.restype = i64
+    lib.ast_set_weights.argtypes = [vp] + [vp] * 6 + [vp]
+    lib.ast_set_targets.argtypes = [vp, vp, vp, dbl, dbl, vp]
+    lib.ast_embeds.argtypes = [vp, vp, vp, vp, vp]
+    lib.ast_step.argtypes = [vp, vp, vp, vp, vp]
+    lib.ast_step_host.argtypes = [vp, vp, vp, vp]
+    lib.ast_step_forward.argtypes = [vp, vp, vp]
+    lib.ast_partials.argtypes = [vp, C.POINTER(vp), C.POINTER(i64)]
+    lib.ast_step_backward.argtypes = [vp, vp, vp, vp]
+    lib.ast_get_extract.argtypes = [vp, i32, vp, vp]
+    lib.ast_launches_per_step.argtypes = [vp]
+    lib.ast_step_timed.argtypes = [vp, vp, vp, vp, vp, vp]
+    for name in SYMBOLS:
+        f = getattr(lib, name)
+        if f.restype is C.c_int:      # default restype; the int-returning entry points
+            f.restype = C.c_int
+    _lib = lib
+    return lib
+
+
+def check(code: int):
+    if code != 0:
+        raise AstError(code, load().ast_last_error().decode())

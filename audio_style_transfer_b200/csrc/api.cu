@@ -1,0 +1,480 @@
+// api.cu -- the C ABI (include/ast_b200.h): context, workspaces, step orchestration, CUDA graph.
+#include "../../include/ast_b200.h"
+#include "common.cuh"
+#include "tc.cuh"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+thread_local int ast_launch_counter = 0;
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(AST_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+struct ast_ctx {
+    ast_config cfg;
+    int T, B, R, NL, L, n_cont, prec;
+    int own_lo, own_hi;           // window-local owned rows
+    int64_t total_T;
+    int style_layer[AST_MAX_IDS]; // encoder layer (0..29) behind each style slot
+    int cont_layer[AST_MAX_IDS];
+    int head_buf[30];             // layer -> dF buffer index or -1
+    int n_head;
+    int nmat, nmat_used, msize, n_side;
+    int gram_chunk_rows, gram_nchunk, sse_nblk;
+    int64_t bytes;
+    std::vector<void*> allocs;
+    // weights (fp32 masters + transposes for the backward)
+    float *W0, *b0, *Wd, *bd, *Wr, *br, *WdT, *WrT;
+    // activations / masks
+    float* H;          // [NL+1][R][128]
+    uint32_t* hmask;   // [NL+1][R][4]
+    uint32_t* zmask;   // [NL][R][4]
+    float* g;          // [R][128]
+    float* dz[2];      // fp32 mode: [R][128] fp32 each
+    float* dF;         // [n_head][R][128]
+    float* scratch3R;
+    // heads
+    float* gram_part;
+    float* partials;   // [B*nmat*msize raw Gram | B content sse]
+    int64_t n_partials;
+    float *Gn, *Ssym, *ls_part, *sse_part;
+    float *Pc, *Ps;
+    const float** d_Fptr;
+    float** d_dFptr;
+    const float** d_Hcptr;
+    float lambd;
+    bool have_w, have_t;
+    TcState* tc;       // tensor-core path state (AST_PREC_BF16), else NULL
+    // host-buffer step (ast_step_host)
+    cudaStream_t hstream;
+    cudaGraphExec_t gexec;
+    float *d_x, *d_losses, *d_grad;
+    float *p_x, *p_out;            // pinned
+    int launches_per_step;
+    cudaEvent_t ev[5];
+};
+
+template <typename Tp>
+static int dalloc(ast_ctx* c, Tp** p, size_t n) {
+    void* q = nullptr;
+    const size_t bytes = std::max<size_t>(n * sizeof(Tp), 256);
+    cudaError_t e = cudaMalloc(&q, bytes);
+    if (e != cudaSuccess) return fail(AST_ECUDA, "cudaMalloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+    c->allocs.push_back(q);
+    c->bytes += (int64_t)bytes;
+    *p = reinterpret_cast<Tp*>(q);
+    return AST_OK;
+}
+#define DA(ptr, n)                                   \
+    do {                                             \
+        int r_ = dalloc(c, &(ptr), (size_t)(n));     \
+        if (r_ != AST_OK) { ast_destroy(c); return r_; } \
+    } while (0)
+
+static inline int dil(int l) { return 1 << (l % 10); }   // model.py:98
+static inline float* Hl(const ast_ctx* c, int l) { return c->H + (size_t)l * c->R * AST_C; }
+static inline uint32_t* hm(const ast_ctx* c, int l) { return c->hmask + (size_t)l * c->R * AST_MW; }
+static inline uint32_t* zm(const ast_ctx* c, int l) { return c->zmask + (size_t)l * c->R * AST_MW; }
+static inline float* dFb(const ast_ctx* c, int i) { return c->dF + (size_t)i * c->R * AST_C; }
+
+extern "C" const char* ast_last_error(void) { return g_err; }
+extern "C" const char* ast_version(void) { return "ast_b200 0.1 sm_100a"; }
+extern "C" int64_t ast_workspace_bytes(const ast_ctx* c) { return c ? c->bytes : 0; }
+extern "C" int ast_launches_per_step(const ast_ctx* c) { return c ? c->launches_per_step : 0; }
+
+extern "C" int ast_destroy(ast_ctx* c) {
+    if (!c) return AST_OK;
+    cudaSetDevice(c->cfg.device);
+    if (c->tc) tc_destroy(c->tc);
+    if (c->gexec) cudaGraphExecDestroy(c->gexec);
+    if (c->hstream) cudaStreamDestroy(c->hstream);
+    for (auto& e : c->ev) if (e) cudaEventDestroy(e);
+    if (c->p_x) cudaFreeHost(c->p_x);
+    if (c->p_out) cudaFreeHost(c->p_out);
+    for (void* p : c->allocs) cudaFree(p);
+    delete c;
+    return AST_OK;
+}
+
+extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
+    if (!cfg || !out) return fail(AST_EINVAL, "null argument");
+    *out = nullptr;
+    if (cfg->T <= 0 || cfg->T % 128 != 0) return fail(AST_EINVAL, "T=%d must be a positive multiple of 128", cfg->T);
+    if (cfg->B <= 0) return fail(AST_EINVAL, "B=%d must be positive", cfg->B);
+    if ((int64_t)cfg->B * cfg->T > (int64_t)1 << 30) return fail(AST_EINVAL, "B*T too large");
+    if (cfg->n_layers < 1 || cfg->n_layers > 30) return fail(AST_EINVAL, "n_layers=%d outside 1..30", cfg->n_layers);
+    if (cfg->n_cont < 1 || cfg->n_cont > AST_MAX_IDS) return fail(AST_EINVAL, "n_cont=%d outside 1..%d", cfg->n_cont, AST_MAX_IDS);
+    if (cfg->n_style < 1 || cfg->n_style > AST_MAX_IDS) return fail(AST_EINVAL, "n_style=%d outside 1..%d", cfg->n_style, AST_MAX_IDS);
+    if (cfg->nb_channels < 1 || cfg->nb_channels > 128) return fail(AST_EINVAL, "nb_channels outside 1..128");
+    if (cfg->cnt_channels < 1 || cfg->cnt_channels > 128) return fail(AST_EINVAL, "cnt_channels outside 1..128");
+    if (cfg->precision != AST_PREC_FP32 && cfg->precision != AST_PREC_BF16) return fail(AST_EINVAL, "unknown precision %d", cfg->precision);
+
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(AST_ECUDA, "no CUDA device: this library has no CPU fallback");
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(AST_EINVAL, "device %d outside 0..%d", cfg->device, ndev - 1);
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, cfg->device));
+    if (prop.major != 10) return fail(AST_ECUDA, "device %d is sm_%d%d; this library is built for sm_100a only", cfg->device, prop.major, prop.minor);
+    CK(cudaSetDevice(cfg->device));
+
+    ast_ctx* c = new ast_ctx();
+    memset(static_cast<void*>(&c->cfg), 0, sizeof(ast_config));
+    c->cfg = *cfg;
+    c->T = cfg->T; c->B = cfg->B; c->R = cfg->B * cfg->T; c->NL = cfg->n_layers; c->L = cfg->n_style;
+    c->n_cont = cfg->n_cont; c->prec = cfg->precision; c->bytes = 0;
+    c->tc = nullptr; c->hstream = nullptr; c->gexec = nullptr; c->p_x = c->p_out = nullptr;
+    for (auto& e : c->ev) e = nullptr;
+    c->have_w = c->have_t = false; c->launches_per_step = 0; c->lambd = 0.f;
+
+    // time-sharding window (all zero = unsharded)
+    c->total_T = cfg->total_T > 0 ? cfg->total_T : cfg->T;
+    int64_t ob = cfg->own_begin, oe = cfg->own_end;
+    if (cfg->total_T <= 0) { ob = 0; oe = cfg->T; }
+    c->own_lo = (int)(ob - cfg->win_begin); c->own_hi = (int)(oe - cfg->win_begin);
+    if (c->own_lo < 0 || c->own_hi > c->T || c->own_lo >= c->own_hi) { delete c; return fail(AST_EINVAL, "owned rows outside the window"); }
+
+    // resolve heads.  extracts[30] aliases extracts[29] (model.py:118-119); [31] (bottleneck) is out of scope.
+    for (int i = 0; i < 30; ++i) c->head_buf[i] = -1;
+    c->n_head = 0;
+    bool seen[30] = {false};
+    for (int i = 0; i < c->L; ++i) {
+        int id = cfg->style_ids[i];
+        if (id < 0 || id > 30) { delete c; return fail(AST_EINVAL, "style id %d outside 0..30", id); }
+        id = std::min(id, 29);
+        if (id >= c->NL) { delete c; return fail(AST_EINVAL, "style id %d needs more than n_layers=%d layers", id, c->NL); }
+        if (seen[id]) { delete c; return fail(AST_EUNSUPPORTED, "encoder layer %d appears twice in the style set", id); }
+        seen[id] = true;
+        c->style_layer[i] = id;
+        if (c->head_buf[id] < 0) c->head_buf[id] = c->n_head++;
+    }
+    for (int i = 0; i < c->n_cont; ++i) {
+        int id = cfg->cont_ids[i];
+        if (id < 0 || id > 30) { delete c; return fail(AST_EINVAL, "content id %d outside 0..30", id); }
+        id = std::min(id, 29);
+        if (id >= c->NL) { delete c; return fail(AST_EINVAL, "content id %d needs more than n_layers=%d layers", id, c->NL); }
+        c->cont_layer[i] = id;
+        if (c->head_buf[id] < 0) c->head_buf[id] = c->n_head++;
+    }
+    if (c->head_buf[c->NL - 1] < 0) { delete c; return fail(AST_EINVAL, "n_layers=%d but no head reads extracts[%d]", c->NL, c->NL - 1); }
+
+    if (cfg->gatys) { c->nmat = c->L; c->nmat_used = c->L; c->n_side = AST_C; }
+    else { c->nmat = AST_C; c->nmat_used = cfg->nb_channels; c->n_side = c->L; }
+    c->msize = c->n_side * c->n_side;
+
+    {   // Gram split-K geometry: few enough chunks to keep the partial buffer small, enough to fill the SMs
+        int target = cfg->gatys ? 16 : 64;
+        target = std::max(2, (target + c->B - 1) / c->B);
+        int rows = (c->T + target - 1) / target;
+        rows = std::max(128, ((rows + 127) / 128) * 128);
+        c->gram_chunk_rows = rows;
+        c->gram_nchunk = (c->T + rows - 1) / rows;
+        c->sse_nblk = 64;
+    }
+
+    const size_t RC = (size_t)c->R * AST_C;
+    DA(c->W0, 3 * AST_C); DA(c->b0, AST_C);
+    DA(c->Wd, (size_t)c->NL * 3 * AST_C * AST_C); DA(c->bd, (size_t)c->NL * AST_C);
+    DA(c->Wr, (size_t)c->NL * AST_C * AST_C);     DA(c->br, (size_t)c->NL * AST_C);
+    DA(c->WdT, (size_t)c->NL * 3 * AST_C * AST_C); DA(c->WrT, (size_t)c->NL * AST_C * AST_C);
+    DA(c->H, (size_t)(c->NL + 1) * RC);
+    DA(c->hmask, (size_t)(c->NL + 1) * c->R * AST_MW);
+    DA(c->zmask, (size_t)c->NL * c->R * AST_MW);
+    DA(c->g, RC);
+    if (c->prec == AST_PREC_FP32) { DA(c->dz[0], RC); DA(c->dz[1], RC); } else { c->dz[0] = c->dz[1] = nullptr; }
+    DA(c->dF, (size_t)c->n_head * RC);
+    DA(c->scratch3R, (size_t)3 * c->R);
+    const size_t gsz = (size_t)c->B * c->nmat * c->msize;
+    DA(c->gram_part, gsz * c->gram_nchunk);
+    c->n_partials = (int64_t)gsz + c->B;
+    DA(c->partials, (size_t)c->n_partials);
+    DA(c->Gn, gsz); DA(c->Ssym, gsz); DA(c->ls_part, (size_t)c->B * c->nmat);
+    DA(c->sse_part, (size_t)2 * c->B * c->sse_nblk);   // doubles
+    DA(c->Pc, (size_t)c->R * c->n_cont * cfg->cnt_channels);
+    DA(c->Ps, (size_t)c->B * c->nmat_used * c->msize);
+    DA(c->d_Fptr, AST_MAX_IDS); DA(c->d_dFptr, AST_MAX_IDS); DA(c->d_Hcptr, AST_MAX_IDS);
+    DA(c->d_x, (size_t)c->R); DA(c->d_losses, (size_t)c->B * 4); DA(c->d_grad, (size_t)c->R);
+    {
+        const float* fp[AST_MAX_IDS] = {nullptr}; float* dfp[AST_MAX_IDS] = {nullptr}; const float* hc[AST_MAX_IDS] = {nullptr};
+        for (int i = 0; i < c->L; ++i) { fp[i] = Hl(c, c->style_layer[i] + 1); dfp[i] = dFb(c, c->head_buf[c->style_layer[i]]); }
+        for (int i = 0; i < c->n_cont; ++i) hc[i] = Hl(c, c->cont_layer[i] + 1);
+        cudaMemcpy(c->d_Fptr, fp, sizeof(fp), cudaMemcpyHostToDevice);
+        cudaMemcpy(c->d_dFptr, dfp, sizeof(dfp), cudaMemcpyHostToDevice);
+        cudaMemcpy(c->d_Hcptr, hc, sizeof(hc), cudaMemcpyHostToDevice);
+    }
+    if (cudaMallocHost(&c->p_x, (size_t)c->R * sizeof(float)) != cudaSuccess ||
+        cudaMallocHost(&c->p_out, ((size_t)c->R + 4 * c->B) * sizeof(float)) != cudaSuccess) {
+        ast_destroy(c); return fail(AST_ECUDA, "cudaMallocHost failed");
+    }
+    if (cudaStreamCreateWithFlags(&c->hstream, cudaStreamNonBlocking) != cudaSuccess) { ast_destroy(c); return fail(AST_ECUDA, "stream create failed"); }
+    for (auto& e : c->ev) if (cudaEventCreate(&e) != cudaSuccess) { ast_destroy(c); return fail(AST_ECUDA, "event create failed"); }
+    if (setup_f32_kernels() != 0) { ast_destroy(c); return fail(AST_ECUDA, "cudaFuncSetAttribute failed (is the GPU sm_100?)"); }
+    if (c->prec == AST_PREC_BF16) {
+        const char* why = nullptr;
+        c->tc = tc_create(c->T, c->B, c->NL, &c->bytes, &why);
+        if (!c->tc) { ast_destroy(c); return fail(AST_ECUDA, "tensor-core path setup failed: %s", why ? why : "?"); }
+    }
+    if (cudaDeviceSynchronize() != cudaSuccess || cudaGetLastError() != cudaSuccess) { ast_destroy(c); return fail(AST_ECUDA, "context setup failed"); }
+    *out = c;
+    return AST_OK;
+}
+
+// ---- weights --------------------------------------------------------------------------------
+// out[m][j][i] = in[m][i][j] for 128x128 matrices (backward operands Wd[k]^T, Wr^T)
+__global__ void transpose128_kernel(const float* __restrict__ in, float* __restrict__ out) {
+    __shared__ float tile[32][33];
+    const size_t base = (size_t)blockIdx.z * AST_C * AST_C;
+    const int x = blockIdx.x * 32 + threadIdx.x, y0 = blockIdx.y * 32;
+    for (int j = threadIdx.y; j < 32; j += 8) tile[j][threadIdx.x] = in[base + (size_t)(y0 + j) * AST_C + x];
+    __syncthreads();
+    const int xo = blockIdx.y * 32 + threadIdx.x, yo0 = blockIdx.x * 32;
+    for (int j = threadIdx.y; j < 32; j += 8) out[base + (size_t)(yo0 + j) * AST_C + xo] = tile[threadIdx.x][j];
+}
+
+extern "C" int ast_set_weights(ast_ctx* c, const float* W0, const float* b0, const float* Wd, const float* bd,
+                               const float* Wr, const float* br, void* stream) {
+    if (!c || !W0 || !b0 || !Wd || !bd || !Wr || !br) return fail(AST_EINVAL, "null argument");
+    cudaStream_t s = (cudaStream_t)stream;
+    CK(cudaSetDevice(c->cfg.device));
+    const size_t f = sizeof(float);
+    CK(cudaMemcpyAsync(c->W0, W0, 3 * AST_C * f, cudaMemcpyDefault, s));
+    CK(cudaMemcpyAsync(c->b0, b0, AST_C * f, cudaMemcpyDefault, s));
+    CK(cudaMemcpyAsync(c->Wd, Wd, (size_t)c->NL * 3 * AST_C * AST_C * f, cudaMemcpyDefault, s));
+    CK(cudaMemcpyAsync(c->bd, bd, (size_t)c->NL * AST_C * f, cudaMemcpyDefault, s));
+    CK(cudaMemcpyAsync(c->Wr, Wr, (size_t)c->NL * AST_C * AST_C * f, cudaMemcpyDefault, s));
+    CK(cudaMemcpyAsync(c->br, br, (size_t)c->NL * AST_C * f, cudaMemcpyDefault, s));
+    transpose128_kernel<<<dim3(4, 4, c->NL * 3), dim3(32, 8), 0, s>>>(c->Wd, c->WdT);
+    transpose128_kernel<<<dim3(4, 4, c->NL), dim3(32, 8), 0, s>>>(c->Wr, c->WrT);
+    if (c->tc && tc_set_weights(c->tc, c->Wd, c->Wr, s) != 0) return fail(AST_ECUDA, "tc_set_weights failed");
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(s));     // the caller's host buffers may be reused after return
+    c->have_w = true;
+    return AST_OK;
+}
+
+extern "C" int ast_set_targets(ast_ctx* c, const float* Pc, const float* Ps, double lambd, double gamma, void* stream) {
+    if (!c || !Pc || !Ps) return fail(AST_EINVAL, "null argument");
+    if (gamma != 0.0) return fail(AST_EUNSUPPORTED, "gamma != 0: the STFT regulariser (methods.py:121-123) is not built yet");
+    cudaStream_t s = (cudaStream_t)stream;
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaMemcpyAsync(c->Pc, Pc, (size_t)c->R * c->n_cont * c->cfg.cnt_channels * sizeof(float), cudaMemcpyDefault, s));
+    CK(cudaMemcpyAsync(c->Ps, Ps, (size_t)c->B * c->nmat_used * c->msize * sizeof(float), cudaMemcpyDefault, s));
+    CK(cudaStreamSynchronize(s));
+    c->lambd = (float)lambd;
+    c->have_t = true;
+    if (c->gexec) { cudaGraphExecDestroy(c->gexec); c->gexec = nullptr; }   // loss weights are baked in the graph
+    return AST_OK;
+}
+
+// ---- forward --------------------------------------------------------------------------------
+static void run_encoder(ast_ctx* c, const float* d_x, cudaStream_t s) {
+    launch_startconv_fwd(d_x, c->W0, c->b0, Hl(c, 0), hm(c, 0), c->T, c->R, s);
+    if (c->tc) tc_prepare_input(c->tc, Hl(c, 0), s);
+    for (int l = 0; l < c->NL; ++l) {
+        if (c->tc) {
+            tc_layer_fwd(c->tc, l, c->bd + (size_t)l * AST_C, c->br + (size_t)l * AST_C, Hl(c, l), Hl(c, l + 1),
+                         zm(c, l), hm(c, l + 1), s);
+            continue;
+        }
+        LayerArgsF32 a;
+        memset(&a, 0, sizeof(a));
+        a.A1 = Hl(c, l); a.W1 = c->Wd + (size_t)l * 3 * AST_C * AST_C; a.bias1 = c->bd + (size_t)l * AST_C;
+        a.W2 = c->Wr + (size_t)l * AST_C * AST_C; a.bias2 = c->br + (size_t)l * AST_C;
+        a.Hin = Hl(c, l); a.Hout = Hl(c, l + 1); a.zmask_out = zm(c, l); a.hmask_out = hm(c, l + 1);
+        a.T = c->T; a.R = c->R; a.shift = dil(l);
+        launch_layer_f32(a, false, s);
+    }
+}
+static void run_gram(ast_ctx* c, cudaStream_t s) {
+    if (c->cfg.gatys)
+        launch_gram_gatys(c->d_Fptr, c->L, c->T, c->B, c->own_lo, c->own_hi, c->gram_part, c->gram_nchunk, c->gram_chunk_rows, s);
+    else
+        launch_gram_ours(c->d_Fptr, c->L, c->T, c->B, c->own_lo, c->own_hi, c->gram_part, c->gram_nchunk, c->gram_chunk_rows, s);
+    launch_gram_reduce(c->gram_part, c->partials, c->cfg.gatys, c->L, c->B, c->gram_nchunk, s);
+}
+
+extern "C" int ast_step_forward(ast_ctx* c, const float* d_x, void* stream) {
+    if (!c || !d_x) return fail(AST_EINVAL, "null argument");
+    if (!c->have_w || !c->have_t) return fail(AST_ESTATE, "ast_set_weights and ast_set_targets must precede a step");
+    cudaStream_t s = (cudaStream_t)stream;
+    run_encoder(c, d_x, s);
+    run_gram(c, s);
+    launch_content_sse(c->d_Hcptr, c->n_cont, c->cfg.cnt_channels, c->Pc, c->T, c->B, c->own_lo, c->own_hi,
+                       c->sse_part, c->sse_nblk, c->partials + (size_t)c->B * c->nmat * c->msize, s);
+    CK(cudaGetLastError());
+    return AST_OK;
+}
+
+extern "C" int ast_partials(ast_ctx* c, float** d_buf, int64_t* count) {
+    if (!c || !d_buf || !count) return fail(AST_EINVAL, "null argument");
+    *d_buf = c->partials;
+    *count = c->n_partials;
+    return AST_OK;
+}
+
+static HeadArgs head_args(ast_ctx* c, bool with_targets, float* losses) {
+    HeadArgs h;
+    memset(&h, 0, sizeof(h));
+    const double Ns = (double)c->nmat_used * c->msize;
+    const double Nc = (double)c->total_T * c->n_cont * c->cfg.cnt_channels;
+    h.G = c->partials; h.Ps = c->Ps; h.Gn = c->Gn; h.Ssym = with_targets ? c->Ssym : nullptr;
+    h.ls_part = c->ls_part; h.sse = c->partials + (size_t)c->B * c->nmat * c->msize; h.losses = losses;
+    h.nmat = c->nmat; h.nmat_used = with_targets ? c->nmat_used : 0; h.n = c->n_side; h.B = c->B;
+    h.coef_dGn = (float)((double)c->lambd * 1e3 * 2.0 / Ns);
+    h.ls_scale = (float)(1e3 / Ns); h.lc_scale = (float)(10.0 / Nc); h.lambd = c->lambd;
+    return h;
+}
+
+// ---- backward -------------------------------------------------------------------------------
+extern "C" int ast_step_backward(ast_ctx* c, float* d_losses, float* d_grad, void* stream) {
+    if (!c || !d_losses || !d_grad) return fail(AST_EINVAL, "null argument");
+    if (!c->have_w || !c->have_t) return fail(AST_ESTATE, "ast_set_weights and ast_set_targets must precede a step");
+    cudaStream_t s = (cudaStream_t)stream;
+    launch_heads(head_args(c, true, d_losses), s);
+    if (c->cfg.gatys) launch_style_grad_gatys(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
+    else              launch_style_grad_ours(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
+    {
+        bool init[30];
+        for (int l = 0; l < 30; ++l) init[l] = false;
+        for (int i = 0; i < c->L; ++i) init[c->style_layer[i]] = true;
+        const double Nc = (double)c->total_T * c->n_cont * c->cfg.cnt_channels;
+        for (int i = 0; i < c->n_cont; ++i) {
+            const int l = c->cont_layer[i];
+            launch_content_grad(Hl(c, l + 1), c->Pc, dFb(c, c->head_buf[l]), i, c->n_cont, c->cfg.cnt_channels,
+                                (float)(20.0 / Nc), init[l] ? 1 : 0, c->R, s);
+            init[l] = true;
+        }
+    }
+    int cur = 0;
+    for (int l = c->NL; l >= 0; --l) {
+        const float* dF = (l >= 1 && c->head_buf[l - 1] >= 0) ? dFb(c, c->head_buf[l - 1]) : nullptr;
+        if (c->tc) {
+            tc_layer_bwd(c->tc, l, c->g, l < c->NL ? hm(c, l) : nullptr, dF, l >= 1 ? zm(c, l - 1) : nullptr, s);
+            continue;
+        }
+        LayerArgsF32 a;
+        memset(&a, 0, sizeof(a));
+        a.T = c->T; a.R = c->R; a.g = c->g; a.dF = dF;
+        if (l < c->NL) {
+            a.A1 = c->dz[cur]; a.W1 = c->WdT + (size_t)l * 3 * AST_C * AST_C; a.shift = -dil(l); a.hmask_in = hm(c, l);
+        } else {
+            a.g_init = 1;
+        }
+        if (l >= 1) {
+            a.W2 = c->WrT + (size_t)(l - 1) * AST_C * AST_C; a.zmask_in = zm(c, l - 1); a.dz_out = c->dz[cur ^ 1];
+        }
+        launch_layer_f32(a, true, s);
+        cur ^= 1;
+    }
+    launch_startconv_bwd(c->g, c->W0, c->scratch3R, d_grad, c->T, c->R, s);
+    CK(cudaGetLastError());
+    return AST_OK;
+}
+
+extern "C" int ast_step(ast_ctx* c, const float* d_x, float* d_losses, float* d_grad, void* stream) {
+    const int before = ast_launch_counter;
+    int r = ast_step_forward(c, d_x, stream);
+    if (r != AST_OK) return r;
+    r = ast_step_backward(c, d_losses, d_grad, stream);
+    if (r == AST_OK) c->launches_per_step = ast_launch_counter - before;
+    return r;
+}
+
+// ---- get_embeds (methods.py:86-95) -------------------------------------------------------------
+extern "C" int ast_embeds(ast_ctx* c, const float* d_x, float* d_Ec, float* d_Gn, void* stream) {
+    if (!c || !d_x) return fail(AST_EINVAL, "null argument");
+    if (!c->have_w) return fail(AST_ESTATE, "ast_set_weights must precede ast_embeds");
+    cudaStream_t s = (cudaStream_t)stream;
+    run_encoder(c, d_x, s);
+    if (d_Ec) launch_content_gather(c->d_Hcptr, c->n_cont, c->cfg.cnt_channels, d_Ec, c->R, s);
+    if (d_Gn) {
+        run_gram(c, s);
+        launch_heads(head_args(c, false, nullptr), s);
+        const size_t used = (size_t)c->nmat_used * c->msize * sizeof(float), full = (size_t)c->nmat * c->msize * sizeof(float);
+        CK(cudaMemcpy2DAsync(d_Gn, used, c->Gn, full, used, c->B, cudaMemcpyDeviceToDevice, s));
+    }
+    CK(cudaGetLastError());
+    return AST_OK;
+}
+
+extern "C" int ast_get_extract(ast_ctx* c, int32_t layer, float* d_out, void* stream) {
+    if (!c || !d_out) return fail(AST_EINVAL, "null argument");
+    if (layer < -1 || layer > 30) return fail(AST_EINVAL, "layer %d outside -1..30", layer);
+    const int l = std::min(layer, 29);        // -1 = start-conv output
+    if (l >= c->NL) return fail(AST_EINVAL, "layer %d was not evaluated (n_layers=%d)", layer, c->NL);
+    CK(cudaMemcpyAsync(d_out, Hl(c, l + 1), (size_t)c->R * AST_C * sizeof(float), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return AST_OK;
+}
+
+// ---- the evaluation as SciPy sees it: host float64 in, host float64 out -------------------------
+static int capture_host_graph(ast_ctx* c) {
+    cudaGraph_t graph = nullptr;
+    CK(cudaStreamBeginCapture(c->hstream, cudaStreamCaptureModeThreadLocal));
+    cudaMemcpyAsync(c->d_x, c->p_x, (size_t)c->R * sizeof(float), cudaMemcpyHostToDevice, c->hstream);
+    int r = ast_step(c, c->d_x, c->d_losses, c->d_grad, c->hstream);
+    cudaMemcpyAsync(c->p_out, c->d_losses, (size_t)c->B * 4 * sizeof(float), cudaMemcpyDeviceToHost, c->hstream);
+    cudaMemcpyAsync(c->p_out + 4 * c->B, c->d_grad, (size_t)c->R * sizeof(float), cudaMemcpyDeviceToHost, c->hstream);
+    cudaError_t e = cudaStreamEndCapture(c->hstream, &graph);
+    if (r != AST_OK) { if (graph) cudaGraphDestroy(graph); return r; }
+    if (e != cudaSuccess) return fail(AST_ECUDA, "graph capture failed: %s", cudaGetErrorString(e));
+    e = cudaGraphInstantiate(&c->gexec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) { c->gexec = nullptr; return fail(AST_ECUDA, "graph instantiate failed: %s", cudaGetErrorString(e)); }
+    return AST_OK;
+}
+
+extern "C" int ast_step_host(ast_ctx* c, const double* h_x, double* h_losses, double* h_grad) {
+    if (!c || !h_x || !h_losses || !h_grad) return fail(AST_EINVAL, "null argument");
+    if (!c->have_w || !c->have_t) return fail(AST_ESTATE, "ast_set_weights and ast_set_targets must precede a step");
+    CK(cudaSetDevice(c->cfg.device));
+    if (!c->gexec) { int r = capture_host_graph(c); if (r != AST_OK) return r; }
+    for (int i = 0; i < c->R; ++i) c->p_x[i] = (float)h_x[i];
+    CK(cudaGraphLaunch(c->gexec, c->hstream));
+    CK(cudaStreamSynchronize(c->hstream));
+    for (int i = 0; i < 4 * c->B; ++i) h_losses[i] = (double)c->p_out[i];
+    const float* g = c->p_out + 4 * c->B;
+    for (int i = 0; i < c->R; ++i) h_grad[i] = (double)g[i];
+    return AST_OK;
+}
+
+// ---- phase timing with CUDA events on the launching stream (bench.py roofline) ------------------
+extern "C" int ast_step_timed(ast_ctx* c, const float* d_x, float* d_losses, float* d_grad, void* stream, float* ms_out) {
+    if (!c || !d_x || !d_losses || !d_grad || !ms_out) return fail(AST_EINVAL, "null argument");
+    if (!c->have_w || !c->have_t) return fail(AST_ESTATE, "ast_set_weights and ast_set_targets must precede a step");
+    cudaStream_t s = (cudaStream_t)stream;
+    // same launches as ast_step, with events between the phases
+    CK(cudaEventRecord(c->ev[0], s));
+    run_encoder(c, d_x, s);
+    CK(cudaEventRecord(c->ev[1], s));
+    run_gram(c, s);
+    launch_content_sse(c->d_Hcptr, c->n_cont, c->cfg.cnt_channels, c->Pc, c->T, c->B, c->own_lo, c->own_hi,
+                       c->sse_part, c->sse_nblk, c->partials + (size_t)c->B * c->nmat * c->msize, s);
+    CK(cudaEventRecord(c->ev[2], s));
+    int r = ast_step_backward(c, d_losses, d_grad, s);
+    if (r != AST_OK) return r;
+    CK(cudaEventRecord(c->ev[3], s));
+    CK(cudaEventSynchronize(c->ev[3]));
+    float enc = 0, gram = 0, bwd = 0, tot = 0;
+    CK(cudaEventElapsedTime(&enc, c->ev[0], c->ev[1]));
+    CK(cudaEventElapsedTime(&gram, c->ev[1], c->ev[2]));
+    CK(cudaEventElapsedTime(&bwd, c->ev[2], c->ev[3]));
+    CK(cudaEventElapsedTime(&tot, c->ev[0], c->ev[3]));
+    ms_out[0] = enc; ms_out[1] = bwd; ms_out[2] = gram; ms_out[3] = tot;
+    return AST_OK;
+}

@@ -1,0 +1,85 @@
+// common.cuh -- shared declarations of the B200-native style-transfer step (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+#define AST_C 128           // ae_width (model.py:73 of the reference)
+#define AST_MW 4            // 32-bit words of one row's 128-bit sign mask
+
+// kernels launched since the counter was last reset (bench.py gpu_launches); bumped by every launcher
+extern thread_local int ast_launch_counter;
+
+// ---- kernel argument blocks ---------------------------------------------------------------
+// One "layer" launch = two chained GEMMs over a tile of rows (see DESIGN.md "kernels"):
+//   forward  (model.py:99-114):  z = conv3_d(relu(h)) + bd ; h' = h + relu(z) Wr + br
+//   backward :  g += conv3_d^T(dz_l) * [h_l > 0] (+ head terms) ; dz_{l-1} = (g Wr_{l-1}^T) * [z_{l-1} > 0]
+struct LayerArgsF32 {
+    const float* A1;        // fwd: H[l] (ReLU applied on load); bwd: dz_l.  [R,128].  NULL: skip GEMM1
+    const float* W1;        // [3][128 k][128 n] fp32 (fwd: Wd[l]; bwd: Wd[l]^T per tap)
+    const float* bias1;     // fwd: bd[l]; bwd: NULL
+    const float* W2;        // [128 k][128 n] (fwd: Wr[l]; bwd: Wr[l-1]^T).  NULL: skip GEMM2
+    const float* bias2;     // fwd: br[l]
+    const float* Hin;       // fwd: H[l] (residual)
+    float*       Hout;      // fwd: H[l+1]
+    uint32_t*    zmask_out; // fwd: [R,4]
+    uint32_t*    hmask_out; // fwd: [R,4]  sign mask of H[l+1]
+    float*       g;         // bwd: running d h, in place [R,128]
+    const uint32_t* hmask_in;  // bwd: [h_l > 0]
+    const float* dF;        // bwd: head gradient for extracts[l-1] = H[l], or NULL
+    const uint32_t* zmask_in;  // bwd: [z_{l-1} > 0]
+    float*       dz_out;    // bwd: dz_{l-1}
+    int T;                  // rows per pair (shifts never cross a pair boundary)
+    int R;                  // total rows = B*T
+    int shift;              // tap k reads row t + (k-1)*shift  (fwd: +d, bwd: -d)
+    int g_init;             // bwd: 1 = treat incoming g as zero (top of the stack)
+};
+
+// ---- launchers implemented in kernels_f32.cu ------------------------------------------------
+void launch_startconv_fwd(const float* x, const float* W0, const float* b0, float* H0, uint32_t* hmask0,
+                          int T, int R, cudaStream_t s);
+void launch_startconv_bwd(const float* g, const float* W0, float* scratch3R, float* dx, int T, int R, cudaStream_t s);
+void launch_layer_f32(const LayerArgsF32& a, bool bwd, cudaStream_t s);
+int  setup_f32_kernels();
+
+// Gram partials.  ours: part[b][chunk][c][l][m]; gatys: part[b][l][chunk][128][128].  Rows outside
+// [own_lo, own_hi) (row index within the pair) do not contribute (time sharding).
+void launch_gram_ours(const float* const* d_F, int L, int T, int B, int own_lo, int own_hi,
+                      float* part, int nchunk, int chunk_rows, cudaStream_t s);
+void launch_gram_gatys(const float* const* d_F, int L, int T, int B, int own_lo, int own_hi,
+                       float* part, int nchunk, int chunk_rows, cudaStream_t s);
+// deterministic fixed-order reduction of partials -> G (fp32).  nmat matrices of msize elements;
+// partial p of matrix m is at part[m_outer(m) ... ] -- see kernels_f32.cu for the two layouts.
+void launch_gram_reduce(const float* part, float* G, int gatys, int L, int B, int nchunk, cudaStream_t s);
+
+// content squared error over owned rows -> sse[b] (double accumulate, fp32 out)
+void launch_content_sse(const float* const* d_Hc, int n_cont, int cnt_ch, const float* Pc,
+                        int T, int B, int own_lo, int own_hi, float* part, int nblk, float* sse, cudaStream_t s);
+
+// heads: normalise (methods.py:74), style MSE (methods.py:118-119), dG, Ssym = dG + dG^T, losses.
+struct HeadArgs {
+    const float* G;       // raw Gram [B][nmat][msize]
+    const float* Ps;      // targets  [B][nmat_used][msize]
+    float* Gn;            // out, may be NULL: normalised Gram [B][nmat][msize]
+    float* Ssym;          // out, may be NULL: [B][nmat][msize]
+    float* ls_part;       // [B][nmat] per-matrix sum of squared differences
+    const float* sse;     // [B] content squared error (already all-reduced when sharded)
+    float* losses;        // out [B][4]
+    int nmat, nmat_used, n;   // n = matrix side (L for ours, 128 for gatys)
+    int B;
+    float coef_dGn;       // lambd * 1e3 * 2 / N_s
+    float ls_scale;       // 1e3 / N_s
+    float lc_scale;       // 10 / N_c
+    float lambd;
+};
+void launch_heads(const HeadArgs& a, cudaStream_t s);
+
+// head gradients -> dF buffers
+void launch_style_grad_ours(const float* const* d_F, float* const* d_dF, const float* Ssym, int L, int T, int B,
+                            cudaStream_t s);
+void launch_style_grad_gatys(const float* const* d_F, float* const* d_dF, const float* Ssym, int L, int T, int B,
+                             cudaStream_t s);
+// dF[t, j] (+)= coef * (H[t, j] - Pc[t, slot*cnt + j]) for j < cnt ; accumulate=0 also zero-fills j >= cnt
+void launch_content_grad(const float* H, const float* Pc, float* dF, int slot, int n_cont, int cnt_ch, float coef,
+                         int accumulate, int R, cudaStream_t s);
+void launch_content_gather(const float* const* d_Hc, int n_cont, int cnt_ch, float* Ec, int R, cudaStream_t s);

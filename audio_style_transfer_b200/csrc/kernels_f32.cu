@@ -1,0 +1,662 @@
+// kernels_f32.cu -- CUDA-core fp32 kernels: the <=1e-4 accuracy tier and every non-GEMM stage.
+// sm_100a only.  Reference lines are cited per kernel (paths relative to the upstream repo).
+#include "common.cuh"
+
+// =============================================================================================
+// helpers
+// =============================================================================================
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+// OR-reduce across each aligned group of 8 lanes
+__device__ __forceinline__ uint32_t or8(uint32_t v) {
+    v |= __shfl_xor_sync(0xffffffffu, v, 1);
+    v |= __shfl_xor_sync(0xffffffffu, v, 2);
+    v |= __shfl_xor_sync(0xffffffffu, v, 4);
+    return v;
+}
+
+// =============================================================================================
+// start conv (model.py:80-93): h0[t,c] = b0[c] + sum_k W0[k,0,c] * x[t+k-1] / 128, zero padded.
+// one warp per row, lane owns channels 4*lane..4*lane+3.  Also emits the sign mask of h0.
+// =============================================================================================
+__global__ void __launch_bounds__(256) startconv_fwd_kernel(const float* __restrict__ x, const float* __restrict__ W0,
+                                                            const float* __restrict__ b0, float* __restrict__ H0,
+                                                            uint32_t* __restrict__ hmask, int T, int R) {
+    const int lane = threadIdx.x & 31;
+    const int warps_per_blk = blockDim.x >> 5;
+    const float4 w0 = reinterpret_cast<const float4*>(W0)[lane];
+    const float4 w1 = reinterpret_cast<const float4*>(W0 + AST_C)[lane];
+    const float4 w2 = reinterpret_cast<const float4*>(W0 + 2 * AST_C)[lane];
+    const float4 bb = reinterpret_cast<const float4*>(b0)[lane];
+    for (int row = blockIdx.x * warps_per_blk + (threadIdx.x >> 5); row < R; row += gridDim.x * warps_per_blk) {
+        const int t = row % T;
+        const float xm = (t > 0) ? x[row - 1] * (1.0f / 128.0f) : 0.f;
+        const float x0 = x[row] * (1.0f / 128.0f);
+        const float xp = (t + 1 < T) ? x[row + 1] * (1.0f / 128.0f) : 0.f;
+        float4 h;
+        h.x = fmaf(w2.x, xp, fmaf(w1.x, x0, fmaf(w0.x, xm, bb.x)));
+        h.y = fmaf(w2.y, xp, fmaf(w1.y, x0, fmaf(w0.y, xm, bb.y)));
+        h.z = fmaf(w2.z, xp, fmaf(w1.z, x0, fmaf(w0.z, xm, bb.z)));
+        h.w = fmaf(w2.w, xp, fmaf(w1.w, x0, fmaf(w0.w, xm, bb.w)));
+        reinterpret_cast<float4*>(H0 + (size_t)row * AST_C)[lane] = h;
+        uint32_t nib = (h.x > 0.f ? 1u : 0u) | (h.y > 0.f ? 2u : 0u) | (h.z > 0.f ? 4u : 0u) | (h.w > 0.f ? 8u : 0u);
+        uint32_t wv = or8(nib << (4 * (lane & 7)));
+        if ((lane & 7) == 0) hmask[(size_t)row * AST_MW + (lane >> 3)] = wv;
+    }
+}
+
+void launch_startconv_fwd(const float* x, const float* W0, const float* b0, float* H0, uint32_t* hmask0, int T, int R,
+                          cudaStream_t s) {
+    int blocks = (R + 7) / 8;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    startconv_fwd_kernel<<<blocks, 256, 0, s>>>(x, W0, b0, H0, hmask0, T, R);
+    ast_launch_counter += 1;
+}
+
+// adjoint of the start conv (SURVEY.md 8(a) last line):
+//   p_k[t] = sum_c W0[k,0,c] g[t,c] ;  dx[t] = (p_0[t+1] + p_1[t] + p_2[t-1]) / 128
+__global__ void __launch_bounds__(256) startconv_bwd_dots(const float* __restrict__ g, const float* __restrict__ W0,
+                                                          float* __restrict__ p, int R) {
+    const int lane = threadIdx.x & 31;
+    const int wpb = blockDim.x >> 5;
+    const float4 w0 = reinterpret_cast<const float4*>(W0)[lane];
+    const float4 w1 = reinterpret_cast<const float4*>(W0 + AST_C)[lane];
+    const float4 w2 = reinterpret_cast<const float4*>(W0 + 2 * AST_C)[lane];
+    for (int row = blockIdx.x * wpb + (threadIdx.x >> 5); row < R; row += gridDim.x * wpb) {
+        const float4 v = reinterpret_cast<const float4*>(g + (size_t)row * AST_C)[lane];
+        float a0 = v.x * w0.x + v.y * w0.y + v.z * w0.z + v.w * w0.w;
+        float a1 = v.x * w1.x + v.y * w1.y + v.z * w1.z + v.w * w1.w;
+        float a2 = v.x * w2.x + v.y * w2.y + v.z * w2.z + v.w * w2.w;
+        a0 = warp_sum(a0); a1 = warp_sum(a1); a2 = warp_sum(a2);
+        if (lane == 0) { p[row] = a0; p[R + row] = a1; p[2 * (size_t)R + row] = a2; }
+    }
+}
+__global__ void startconv_bwd_combine(const float* __restrict__ p, float* __restrict__ dx, int T, int R) {
+    int row = blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= R) return;
+    int t = row % T;
+    float v = p[R + row];
+    if (t + 1 < T) v += p[row + 1];
+    if (t > 0) v += p[2 * (size_t)R + row - 1];
+    dx[row] = v * (1.0f / 128.0f);
+}
+void launch_startconv_bwd(const float* g, const float* W0, float* scratch3R, float* dx, int T, int R, cudaStream_t s) {
+    int blocks = (R + 7) / 8;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    startconv_bwd_dots<<<blocks, 256, 0, s>>>(g, W0, scratch3R, R);
+    ast_launch_counter += 1;
+    startconv_bwd_combine<<<(R + 255) / 256, 256, 0, s>>>(scratch3R, dx, T, R);
+    ast_launch_counter += 1;
+}
+
+// =============================================================================================
+// layer kernel (fp32, CUDA cores): two chained GEMMs over a 64-row tile, 256 threads, 4x8 per thread.
+//   forward  (model.py:99-114, masked.py:110-160 closed form):
+//       z = b + sum_k relu(h)[t+(k-1)d] Wd[k] ; r = relu(z) ; h' = h + r Wr + br
+//   backward:
+//       g += (sum_k dz[t-(k-1)d] Wd[k]^T) * [h>0] + dF ; dz' = (g Wr'^T) * [z'>0]
+// Rows outside [0,T) of the pair contribute zero: the reference's per-layer 'SAME' zero padding.
+// =============================================================================================
+#define LF_BM 64
+#define LF_KC 32
+#define LF_AS_LD 36
+#define LF_RT_LD 132
+#define LF_SMEM ((LF_BM * LF_AS_LD + LF_KC * AST_C + LF_BM * LF_RT_LD) * 4)
+
+__device__ __forceinline__ void lf_load_w(float* Ws, const float* __restrict__ W, int tid) {
+    // W points at a [32][128] fp32 chunk
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        int idx = tid + i * 256;
+        reinterpret_cast<float4*>(Ws)[idx] = reinterpret_cast<const float4*>(W)[idx];
+    }
+}
+__device__ __forceinline__ void lf_mma(float (&acc)[4][8], const float* As, int lda, const float* Ws, int ty, int tx) {
+#pragma unroll 8
+    for (int kk = 0; kk < LF_KC; ++kk) {
+        float a[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) a[i] = As[(ty * 4 + i) * lda + kk];
+        const float4 b0 = *reinterpret_cast<const float4*>(Ws + kk * AST_C + tx * 4);
+        const float4 b1 = *reinterpret_cast<const float4*>(Ws + kk * AST_C + 64 + tx * 4);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            acc[i][0] = fmaf(a[i], b0.x, acc[i][0]); acc[i][1] = fmaf(a[i], b0.y, acc[i][1]);
+            acc[i][2] = fmaf(a[i], b0.z, acc[i][2]); acc[i][3] = fmaf(a[i], b0.w, acc[i][3]);
+            acc[i][4] = fmaf(a[i], b1.x, acc[i][4]); acc[i][5] = fmaf(a[i], b1.y, acc[i][5]);
+            acc[i][6] = fmaf(a[i], b1.z, acc[i][6]); acc[i][7] = fmaf(a[i], b1.w, acc[i][7]);
+        }
+    }
+}
+// sign mask of a thread tile row -> 4 words of the row; lanes tx&7==0 write
+__device__ __forceinline__ void lf_store_mask(const float (&v)[8], uint32_t* __restrict__ mrow, int tx) {
+    uint32_t lo = (v[0] > 0.f ? 1u : 0u) | (v[1] > 0.f ? 2u : 0u) | (v[2] > 0.f ? 4u : 0u) | (v[3] > 0.f ? 8u : 0u);
+    uint32_t hi = (v[4] > 0.f ? 1u : 0u) | (v[5] > 0.f ? 2u : 0u) | (v[6] > 0.f ? 4u : 0u) | (v[7] > 0.f ? 8u : 0u);
+    lo = or8(lo << (4 * (tx & 7)));
+    hi = or8(hi << (4 * (tx & 7)));
+    if ((tx & 7) == 0) { mrow[tx >> 3] = lo; mrow[2 + (tx >> 3)] = hi; }
+}
+__device__ __forceinline__ void lf_apply_mask(float (&v)[8], const uint32_t* __restrict__ mrow, int tx) {
+    const uint32_t lo = mrow[tx >> 3] >> (4 * (tx & 7));
+    const uint32_t hi = mrow[2 + (tx >> 3)] >> (4 * (tx & 7));
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        if (!((lo >> j) & 1u)) v[j] = 0.f;
+        if (!((hi >> j) & 1u)) v[4 + j] = 0.f;
+    }
+}
+
+template <bool BWD>
+__global__ void __launch_bounds__(256) layer_f32_kernel(const LayerArgsF32 a) {
+    extern __shared__ __align__(16) float lf_smem[];
+    float* As = lf_smem;
+    float* Ws = As + LF_BM * LF_AS_LD;
+    float* Rt = Ws + LF_KC * AST_C;
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int row0 = blockIdx.x * LF_BM;
+    const int t0 = row0 % a.T;
+    const int pbase = row0 - t0;
+
+    float acc[4][8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+
+    if (a.A1 != nullptr) {
+        for (int k = 0; k < 3; ++k) {
+            const int sh = (k - 1) * a.shift;
+            if (t0 + sh + LF_BM <= 0 || t0 + sh >= a.T) continue;      // whole tap tile is padding (block-uniform)
+            for (int kc = 0; kc < AST_C / LF_KC; ++kc) {
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const int idx = tid + i * 256, r = idx >> 3, q = idx & 7;
+                    const int t = t0 + r + sh;
+                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (t >= 0 && t < a.T)
+                        v = *reinterpret_cast<const float4*>(a.A1 + (size_t)(pbase + t) * AST_C + kc * LF_KC + q * 4);
+                    if (!BWD) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+                    *reinterpret_cast<float4*>(As + r * LF_AS_LD + q * 4) = v;
+                }
+                lf_load_w(Ws, a.W1 + ((size_t)k * AST_C + kc * LF_KC) * AST_C, tid);
+                __syncthreads();
+                lf_mma(acc, As, LF_AS_LD, Ws, ty, tx);
+                __syncthreads();
+            }
+        }
+    }
+
+    // ---- epilogue 1 -> Rt (A operand of GEMM2) ------------------------------------------------
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int row = row0 + ty * 4 + i;
+        float v[8];
+        if (!BWD) {
+            const float4 b0 = *reinterpret_cast<const float4*>(a.bias1 + tx * 4);
+            const float4 b1 = *reinterpret_cast<const float4*>(a.bias1 + 64 + tx * 4);
+            v[0] = acc[i][0] + b0.x; v[1] = acc[i][1] + b0.y; v[2] = acc[i][2] + b0.z; v[3] = acc[i][3] + b0.w;
+            v[4] = acc[i][4] + b1.x; v[5] = acc[i][5] + b1.y; v[6] = acc[i][6] + b1.z; v[7] = acc[i][7] + b1.w;
+            lf_store_mask(v, a.zmask_out + (size_t)row * AST_MW, tx);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = acc[i][j];
+            if (a.A1 != nullptr) lf_apply_mask(v, a.hmask_in + (size_t)row * AST_MW, tx);
+            float* grow = a.g + (size_t)row * AST_C;
+            if (!a.g_init) {
+                const float4 g0 = *reinterpret_cast<const float4*>(grow + tx * 4);
+                const float4 g1 = *reinterpret_cast<const float4*>(grow + 64 + tx * 4);
+                v[0] += g0.x; v[1] += g0.y; v[2] += g0.z; v[3] += g0.w;
+                v[4] += g1.x; v[5] += g1.y; v[6] += g1.z; v[7] += g1.w;
+            }
+            if (a.dF != nullptr) {
+                const float4 f0 = *reinterpret_cast<const float4*>(a.dF + (size_t)row * AST_C + tx * 4);
+                const float4 f1 = *reinterpret_cast<const float4*>(a.dF + (size_t)row * AST_C + 64 + tx * 4);
+                v[0] += f0.x; v[1] += f0.y; v[2] += f0.z; v[3] += f0.w;
+                v[4] += f1.x; v[5] += f1.y; v[6] += f1.z; v[7] += f1.w;
+            }
+            *reinterpret_cast<float4*>(grow + tx * 4) = make_float4(v[0], v[1], v[2], v[3]);
+            *reinterpret_cast<float4*>(grow + 64 + tx * 4) = make_float4(v[4], v[5], v[6], v[7]);
+        }
+        *reinterpret_cast<float4*>(Rt + (ty * 4 + i) * LF_RT_LD + tx * 4) = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4*>(Rt + (ty * 4 + i) * LF_RT_LD + 64 + tx * 4) = make_float4(v[4], v[5], v[6], v[7]);
+    }
+    if (a.W2 == nullptr) return;
+    __syncthreads();
+
+    // ---- GEMM2: [64 x 128] . W2[128 x 128] ----------------------------------------------------
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+    for (int kc = 0; kc < AST_C / LF_KC; ++kc) {
+        lf_load_w(Ws, a.W2 + (size_t)kc * LF_KC * AST_C, tid);
+        __syncthreads();
+        lf_mma(acc, Rt + kc * LF_KC, LF_RT_LD, Ws, ty, tx);
+        __syncthreads();
+    }
+
+    // ---- epilogue 2 ---------------------------------------------------------------------------
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int row = row0 + ty * 4 + i;
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = acc[i][j];
+        if (!BWD) {
+            const float4 b0 = *reinterpret_cast<const float4*>(a.bias2 + tx * 4);
+            const float4 b1 = *reinterpret_cast<const float4*>(a.bias2 + 64 + tx * 4);
+            const float4 h0 = *reinterpret_cast<const float4*>(a.Hin + (size_t)row * AST_C + tx * 4);
+            const float4 h1 = *reinterpret_cast<const float4*>(a.Hin + (size_t)row * AST_C + 64 + tx * 4);
+            // h' = h + (r Wr + br): same association as the reference (model.py:109-114)
+            v[0] = h0.x + (v[0] + b0.x); v[1] = h0.y + (v[1] + b0.y); v[2] = h0.z + (v[2] + b0.z); v[3] = h0.w + (v[3] + b0.w);
+            v[4] = h1.x + (v[4] + b1.x); v[5] = h1.y + (v[5] + b1.y); v[6] = h1.z + (v[6] + b1.z); v[7] = h1.w + (v[7] + b1.w);
+            *reinterpret_cast<float4*>(a.Hout + (size_t)row * AST_C + tx * 4) = make_float4(v[0], v[1], v[2], v[3]);
+            *reinterpret_cast<float4*>(a.Hout + (size_t)row * AST_C + 64 + tx * 4) = make_float4(v[4], v[5], v[6], v[7]);
+            lf_store_mask(v, a.hmask_out + (size_t)row * AST_MW, tx);
+        } else {
+            lf_apply_mask(v, a.zmask_in + (size_t)row * AST_MW, tx);
+            *reinterpret_cast<float4*>(a.dz_out + (size_t)row * AST_C + tx * 4) = make_float4(v[0], v[1], v[2], v[3]);
+            *reinterpret_cast<float4*>(a.dz_out + (size_t)row * AST_C + 64 + tx * 4) = make_float4(v[4], v[5], v[6], v[7]);
+        }
+    }
+}
+
+int setup_f32_kernels() {
+    cudaError_t e = cudaFuncSetAttribute(layer_f32_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, LF_SMEM);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(layer_f32_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, LF_SMEM);
+    return (int)e;
+}
+void launch_layer_f32(const LayerArgsF32& a, bool bwd, cudaStream_t s) {
+    const int blocks = a.R / LF_BM;
+    if (bwd) layer_f32_kernel<true><<<blocks, 256, LF_SMEM, s>>>(a);
+    else     layer_f32_kernel<false><<<blocks, 256, LF_SMEM, s>>>(a);
+    ast_launch_counter += 1;
+}
+
+// =============================================================================================
+// Gram partials (methods.py:62-73).  Deterministic: every CTA writes its own partial, a second
+// kernel sums the partials in a fixed order (no float atomics).
+// =============================================================================================
+// "ours": G[c,l,m] = sum_t F_l[t,c] F_m[t,c].  block = 32 channels x (ng x ng) groups, each thread an
+// 8x8 (l,m) block for one channel.  grid = (nchunk, 4 channel quads, B).  part[b][chunk][c][l][m].
+__global__ void __launch_bounds__(512) gram_ours_kernel(const float* const* __restrict__ F, int L, int T, int own_lo,
+                                                        int own_hi, float* __restrict__ part, int nchunk,
+                                                        int chunk_rows, int ng) {
+    const int cl = threadIdx.x;                 // 0..31
+    const int grp = threadIdx.y;                // 0..ng*ng-1
+    const int lg = grp / ng, mg = grp % ng;
+    const int c = blockIdx.y * 32 + cl;
+    const int b = blockIdx.z;
+    const int tb = blockIdx.x * chunk_rows;
+    int t_lo = max(tb, own_lo), t_hi = min(min(tb + chunk_rows, T), own_hi);
+    float acc[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+    const float* pl[8];
+    const float* pm[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int l = lg * 8 + i, m = mg * 8 + i;
+        pl[i] = (l < L) ? F[l] + (size_t)b * T * AST_C + c : nullptr;
+        pm[i] = (m < L) ? F[m] + (size_t)b * T * AST_C + c : nullptr;
+    }
+    for (int t = t_lo; t < t_hi; ++t) {
+        float vl[8], vm[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            vl[i] = pl[i] ? pl[i][(size_t)t * AST_C] : 0.f;
+            vm[i] = pm[i] ? pm[i][(size_t)t * AST_C] : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(vl[i], vm[j], acc[i][j]);
+    }
+    float* out = part + (((size_t)b * nchunk + blockIdx.x) * AST_C + c) * L * L;
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int l = lg * 8 + i, m = mg * 8 + j;
+            if (l < L && m < L) out[l * L + m] = acc[i][j];
+        }
+}
+void launch_gram_ours(const float* const* d_F, int L, int T, int B, int own_lo, int own_hi, float* part, int nchunk,
+                      int chunk_rows, cudaStream_t s) {
+    const int ng = (L + 7) / 8;
+    dim3 grid(nchunk, AST_C / 32, B), block(32, ng * ng);
+    gram_ours_kernel<<<grid, block, 0, s>>>(d_F, L, T, own_lo, own_hi, part, nchunk, chunk_rows, ng);
+    ast_launch_counter += 1;
+}
+
+// gatys: G_l = F_l^T F_l (128x128).  256 threads, 8x8 per thread (rows ty*4.., 64+ty*4.. ; cols likewise).
+// grid = (nchunk, L, B).  part[(b*L+l)][chunk][128][128].
+__global__ void __launch_bounds__(256) gram_gatys_kernel(const float* const* __restrict__ F, int L, int T, int own_lo,
+                                                         int own_hi, float* __restrict__ part, int nchunk,
+                                                         int chunk_rows) {
+    __shared__ __align__(16) float Fs[32][AST_C];
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int l = blockIdx.y, b = blockIdx.z;
+    const float* Fl = F[l] + (size_t)b * T * AST_C;
+    const int tb = blockIdx.x * chunk_rows;
+    float acc[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+    for (int ts = tb; ts < min(tb + chunk_rows, T); ts += 32) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int idx = tid + i * 256, r = idx >> 5, q = idx & 31;
+            const int t = ts + r;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (t < T && t >= own_lo && t < own_hi) v = *reinterpret_cast<const float4*>(Fl + (size_t)t * AST_C + q * 4);
+            *reinterpret_cast<float4*>(&Fs[r][q * 4]) = v;
+        }
+        __syncthreads();
+#pragma unroll 4
+        for (int r = 0; r < 32; ++r) {
+            const float4 a0 = *reinterpret_cast<const float4*>(&Fs[r][ty * 4]);
+            const float4 a1 = *reinterpret_cast<const float4*>(&Fs[r][64 + ty * 4]);
+            const float4 b0 = *reinterpret_cast<const float4*>(&Fs[r][tx * 4]);
+            const float4 b1 = *reinterpret_cast<const float4*>(&Fs[r][64 + tx * 4]);
+            const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            const float bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+    float* out = part + (((size_t)b * L + l) * nchunk + blockIdx.x) * AST_C * AST_C;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int row = (i < 4) ? ty * 4 + i : 64 + ty * 4 + (i - 4);
+        *reinterpret_cast<float4*>(out + row * AST_C + tx * 4) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+        *reinterpret_cast<float4*>(out + row * AST_C + 64 + tx * 4) = make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]);
+    }
+}
+void launch_gram_gatys(const float* const* d_F, int L, int T, int B, int own_lo, int own_hi, float* part, int nchunk,
+                       int chunk_rows, cudaStream_t s) {
+    dim3 grid(nchunk, L, B);
+    gram_gatys_kernel<<<grid, 256, 0, s>>>(d_F, L, T, own_lo, own_hi, part, nchunk, chunk_rows);
+    ast_launch_counter += 1;
+}
+
+// G[o][e] = sum_{ch} part[o][ch][e], ch ascending (fixed order), double accumulate.
+__global__ void gram_reduce_kernel(const float* __restrict__ part, float* __restrict__ G, int nchunk, int E) {
+    const int o = blockIdx.y;
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < E; e += gridDim.x * blockDim.x) {
+        const float* p = part + (size_t)o * nchunk * E + e;
+        double s = 0.0;
+        for (int ch = 0; ch < nchunk; ++ch) s += (double)p[(size_t)ch * E];
+        G[(size_t)o * E + e] = (float)s;
+    }
+}
+void launch_gram_reduce(const float* part, float* G, int gatys, int L, int B, int nchunk, cudaStream_t s) {
+    const int nouter = gatys ? B * L : B;
+    const int E = gatys ? AST_C * AST_C : AST_C * L * L;
+    dim3 grid((E + 255) / 256, nouter);
+    gram_reduce_kernel<<<grid, 256, 0, s>>>(part, G, nchunk, E);
+    ast_launch_counter += 1;
+}
+
+// =============================================================================================
+// content head (methods.py:58,116-117): squared error of Ec - Pc over the owned rows.
+// grid = (nblk, B); part[b][blk] (double), then a fixed-order final sum -> sse[b].
+// =============================================================================================
+__global__ void __launch_bounds__(256) content_sse_kernel(const float* const* __restrict__ Hc, int n_cont, int cnt_ch,
+                                                          const float* __restrict__ Pc, int T, int own_lo, int own_hi,
+                                                          double* __restrict__ part) {
+    __shared__ double red[8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int b = blockIdx.y;
+    const int ncols = n_cont * cnt_ch;
+    double s = 0.0;
+    for (int t = own_lo + blockIdx.x * 8 + warp; t < own_hi; t += gridDim.x * 8) {
+        const size_t row = (size_t)b * T + t;
+        for (int slot = 0; slot < n_cont; ++slot) {
+            const float* h = Hc[slot] + row * AST_C;
+            const float* p = Pc + row * ncols + (size_t)slot * cnt_ch;
+            for (int j = lane; j < cnt_ch; j += 32) {
+                const float d = h[j] - p[j];
+                s += (double)d * (double)d;
+            }
+        }
+    }
+    s = warp_sum_d(s);
+    if (lane == 0) red[warp] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double tot = 0.0;
+        for (int i = 0; i < 8; ++i) tot += red[i];
+        part[(size_t)b * gridDim.x + blockIdx.x] = tot;
+    }
+}
+__global__ void content_sse_final(const double* __restrict__ part, int nblk, float* __restrict__ sse) {
+    if (threadIdx.x == 0) {
+        double tot = 0.0;
+        for (int i = 0; i < nblk; ++i) tot += part[(size_t)blockIdx.x * nblk + i];
+        sse[blockIdx.x] = (float)tot;
+    }
+}
+void launch_content_sse(const float* const* d_Hc, int n_cont, int cnt_ch, const float* Pc, int T, int B, int own_lo,
+                        int own_hi, float* part, int nblk, float* sse, cudaStream_t s) {
+    dim3 grid(nblk, B);
+    content_sse_kernel<<<grid, 256, 0, s>>>(d_Hc, n_cont, cnt_ch, Pc, T, own_lo, own_hi, reinterpret_cast<double*>(part));
+    ast_launch_counter += 1;
+    content_sse_final<<<B, 32, 0, s>>>(reinterpret_cast<const double*>(part), nblk, sse);
+    ast_launch_counter += 1;
+}
+
+// =============================================================================================
+// heads: Frobenius normalise (methods.py:74), style MSE (methods.py:118-119) and its gradient
+// through the normalisation:  dG = (dGn - Gn <dGn,Gn>) * rsqrt(max(|G|^2, 1e-12)).
+// grid = (nmat, B), one CTA per matrix.
+// =============================================================================================
+__device__ __forceinline__ double block_sum_d(double v, double* red) {
+    v = warp_sum_d(v);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __syncthreads();
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    double t = 0.0;
+    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) t += red[i];
+    return t;
+}
+__global__ void __launch_bounds__(256) heads_kernel(const HeadArgs a) {
+    __shared__ double red[8];
+    const int mat = blockIdx.x, b = blockIdx.y;
+    const int n = a.n, msize = n * n;
+    const float* G = a.G + ((size_t)b * a.nmat + mat) * msize;
+    const bool used = mat < a.nmat_used;
+    const float* Ps = used ? a.Ps + ((size_t)b * a.nmat_used + mat) * msize : nullptr;
+    double ss = 0.0;
+    for (int e = threadIdx.x; e < msize; e += blockDim.x) { const double g = G[e]; ss += g * g; }
+    ss = block_sum_d(ss, red);
+    const double inv = 1.0 / sqrt(fmax(ss, 1e-12));
+    double ls = 0.0, dot = 0.0;
+    if (used) {
+        for (int e = threadIdx.x; e < msize; e += blockDim.x) {
+            const double gn = (double)G[e] * inv;
+            const double d = gn - (double)Ps[e];
+            ls += d * d;
+            dot += (double)a.coef_dGn * d * gn;
+        }
+    }
+    ls = block_sum_d(ls, red);
+    dot = block_sum_d(dot, red);
+    if (threadIdx.x == 0) a.ls_part[(size_t)b * a.nmat + mat] = (float)ls;
+    const bool clamped = ss < 1e-12;
+    float* Gn = a.Gn ? a.Gn + ((size_t)b * a.nmat + mat) * msize : nullptr;
+    float* Ss = a.Ssym ? a.Ssym + ((size_t)b * a.nmat + mat) * msize : nullptr;
+    for (int e = threadIdx.x; e < msize; e += blockDim.x) {
+        const int i = e / n, j = e - i * n;
+        const int et = j * n + i;
+        const double gn = (double)G[e] * inv, gnt = (double)G[et] * inv;
+        if (Gn) Gn[e] = (float)gn;
+        if (Ss) {
+            double v = 0.0;
+            if (used) {
+                const double dgn = (double)a.coef_dGn * (gn - (double)Ps[e]);
+                const double dgnt = (double)a.coef_dGn * (gnt - (double)Ps[et]);
+                const double dg = clamped ? dgn * inv : (dgn - gn * dot) * inv;
+                const double dgt = clamped ? dgnt * inv : (dgnt - gnt * dot) * inv;
+                v = dg + dgt;
+            }
+            Ss[e] = (float)v;
+        }
+    }
+}
+// losses[b] = {Lc + lambd Ls, Lc, Ls, 0}  (methods.py:116-125, gamma = 0)
+__global__ void losses_final_kernel(const HeadArgs a) {
+    if (threadIdx.x != 0) return;
+    const int b = blockIdx.x;
+    double s = 0.0;
+    for (int m = 0; m < a.nmat_used; ++m) s += (double)a.ls_part[(size_t)b * a.nmat + m];
+    const double Ls = (double)a.ls_scale * s;
+    const double Lc = (double)a.lc_scale * (double)a.sse[b];
+    a.losses[b * 4 + 0] = (float)(Lc + (double)a.lambd * Ls);
+    a.losses[b * 4 + 1] = (float)Lc;
+    a.losses[b * 4 + 2] = (float)Ls;
+    a.losses[b * 4 + 3] = 0.f;
+}
+void launch_heads(const HeadArgs& a, cudaStream_t s) {
+    dim3 grid(a.nmat, a.B);
+    heads_kernel<<<grid, 256, 0, s>>>(a);
+    ast_launch_counter += 1;
+    if (a.losses) { losses_final_kernel<<<a.B, 32, 0, s>>>(a); ast_launch_counter += 1; }
+}
+
+// =============================================================================================
+// head gradients
+// =============================================================================================
+// ours: dF_l[t,c] = sum_m Ssym[c,l,m] F_m[t,c].  block = (32 channels, L layers); each thread keeps its
+// row Ssym[c,l,:] in registers and walks 64 rows staged 8 at a time through shared memory.
+// grid = (T/64, 4 channel quads, B).
+#define SG_ROWS 8
+__global__ void __launch_bounds__(1024) style_grad_ours_kernel(const float* const* __restrict__ F,
+                                                               float* const* __restrict__ dF,
+                                                               const float* __restrict__ Ssym, int L, int T) {
+    __shared__ float Fs[32][SG_ROWS][32];   // [m][r][cl]
+    const int cl = threadIdx.x, l = threadIdx.y;
+    const int c = blockIdx.y * 32 + cl, b = blockIdx.z;
+    float S[32];
+#pragma unroll
+    for (int m = 0; m < 32; ++m) S[m] = (m < L) ? Ssym[(((size_t)b * AST_C + c) * L + l) * L + m] : 0.f;
+    const float* Fl = F[l] + (size_t)b * T * AST_C + c;
+    float* dFl = dF[l] + (size_t)b * T * AST_C + c;
+    const int tb = blockIdx.x * 64;
+    for (int ts = tb; ts < tb + 64; ts += SG_ROWS) {
+#pragma unroll
+        for (int r = 0; r < SG_ROWS; ++r) Fs[l][r][cl] = Fl[(size_t)(ts + r) * AST_C];
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < SG_ROWS; ++r) {
+            float acc = 0.f;
+#pragma unroll
+            for (int m = 0; m < 32; ++m)
+                if (m < L) acc = fmaf(S[m], Fs[m][r][cl], acc);
+            dFl[(size_t)(ts + r) * AST_C] = acc;
+        }
+        __syncthreads();
+    }
+}
+void launch_style_grad_ours(const float* const* d_F, float* const* d_dF, const float* Ssym, int L, int T, int B,
+                            cudaStream_t s) {
+    dim3 grid(T / 64, AST_C / 32, B), block(32, L);
+    style_grad_ours_kernel<<<grid, block, 0, s>>>(d_F, d_dF, Ssym, L, T);
+    ast_launch_counter += 1;
+}
+
+// gatys: dF_l = F_l (dG_l + dG_l^T): a [rows x 128].[128 x 128] GEMM per style layer.  grid = (B*T/64, L).
+__global__ void __launch_bounds__(256) style_grad_gatys_kernel(const float* const* __restrict__ F,
+                                                               float* const* __restrict__ dF,
+                                                               const float* __restrict__ Ssym, int L, int T) {
+    __shared__ __align__(16) float As[LF_BM * LF_AS_LD];
+    __shared__ __align__(16) float Ws[LF_KC * AST_C];
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int l = blockIdx.y;
+    const int row0 = blockIdx.x * LF_BM;
+    const int b = row0 / T;
+    const float* A = F[l];
+    const float* W = Ssym + ((size_t)b * L + l) * AST_C * AST_C;
+    float acc[4][8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+    for (int kc = 0; kc < AST_C / LF_KC; ++kc) {
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int idx = tid + i * 256, r = idx >> 3, q = idx & 7;
+            *reinterpret_cast<float4*>(As + r * LF_AS_LD + q * 4) =
+                *reinterpret_cast<const float4*>(A + (size_t)(row0 + r) * AST_C + kc * LF_KC + q * 4);
+        }
+        lf_load_w(Ws, W + (size_t)kc * LF_KC * AST_C, tid);
+        __syncthreads();
+        lf_mma(acc, As, LF_AS_LD, Ws, ty, tx);
+        __syncthreads();
+    }
+    float* out = dF[l];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const size_t row = (size_t)row0 + ty * 4 + i;
+        *reinterpret_cast<float4*>(out + row * AST_C + tx * 4) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+        *reinterpret_cast<float4*>(out + row * AST_C + 64 + tx * 4) = make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]);
+    }
+}
+void launch_style_grad_gatys(const float* const* d_F, float* const* d_dF, const float* Ssym, int L, int T, int B,
+                             cudaStream_t s) {
+    dim3 grid(B * T / LF_BM, L);
+    style_grad_gatys_kernel<<<grid, 256, 0, s>>>(d_F, d_dF, Ssym, L, T);
+    ast_launch_counter += 1;
+}
+
+// content: dF[t,j] (+)= coef (H[t,j] - Pc[t, slot*cnt + j]) for j < cnt (methods.py:58,116-117)
+__global__ void content_grad_kernel(const float* __restrict__ H, const float* __restrict__ Pc, float* __restrict__ dF,
+                                    int slot, int n_cont, int cnt_ch, float coef, int accumulate, int R) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)R * AST_C) return;
+    const size_t row = i / AST_C;
+    const int j = (int)(i % AST_C);
+    float v = 0.f;
+    if (j < cnt_ch) v = coef * (H[i] - Pc[row * (size_t)(n_cont * cnt_ch) + (size_t)slot * cnt_ch + j]);
+    dF[i] = accumulate ? dF[i] + v : v;
+}
+void launch_content_grad(const float* H, const float* Pc, float* dF, int slot, int n_cont, int cnt_ch, float coef,
+                         int accumulate, int R, cudaStream_t s) {
+    const size_t n = (size_t)R * AST_C;
+    content_grad_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(H, Pc, dF, slot, n_cont, cnt_ch, coef, accumulate, R);
+    ast_launch_counter += 1;
+}
+// Ec[t, slot*cnt + j] = extracts[id_slot][t, j]  (methods.py:58)
+__global__ void content_gather_kernel(const float* const* __restrict__ Hc, int n_cont, int cnt_ch,
+                                      float* __restrict__ Ec, int R) {
+    const int ncols = n_cont * cnt_ch;
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)R * ncols) return;
+    const size_t row = i / ncols;
+    const int col = (int)(i % ncols);
+    const int slot = col / cnt_ch, j = col % cnt_ch;
+    Ec[i] = Hc[slot][row * AST_C + j];
+}
+void launch_content_gather(const float* const* d_Hc, int n_cont, int cnt_ch, float* Ec, int R, cudaStream_t s) {
+    const size_t n = (size_t)R * n_cont * cnt_ch;
+    content_gather_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(d_Hc, n_cont, cnt_ch, Ec, R);
+    ast_launch_counter += 1;
+}

@@ -1,0 +1,200 @@
+"""StyleStep -- Python owner of one ast_ctx: the fwd + bwd + Gram-loss evaluation on one B200.
+
+torch is used for device-memory ownership and streams only; all arithmetic happens in
+libast_b200.so (hand-written sm_100a CUDA).  No CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from .synth import EncoderWeights, layers_needed
+
+PRECISIONS = {"fp32": _lib.AST_PREC_FP32, "bf16": _lib.AST_PREC_BF16}
+
+
+class _DevMem:
+    """__cuda_array_interface__ shim so torch can view library-owned device memory without a copy."""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (ptr, False), "version": 2}
+
+
+def _ptr(t):
+    if t is None:
+        return None
+    if isinstance(t, torch.Tensor):
+        assert t.is_contiguous()
+        return C.c_void_p(t.data_ptr())
+    if isinstance(t, np.ndarray):
+        assert t.flags["C_CONTIGUOUS"]
+        return C.c_void_p(t.ctypes.data)
+    raise TypeError(type(t))
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class StyleStep:
+    """One context = fixed (T, B, layer set, head, precision) -- the static shapes of GatysNet.build
+    (methods.py:44-77).  `window=(total_T, win_begin, own_begin, own_end)` makes this context one
+    time shard of a longer clip (multi-GPU)."""
+
+    def __init__(self, T, cont_ids, style_ids, gatys=False, nb_channels=128, cnt_channels=128, B=1,
+                 precision="bf16", device=None, window=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("no CUDA device: the B200 step has no CPU fallback")
+        self.lib = _lib.load()
+        self.device = torch.cuda.current_device() if device is None else int(device)
+        self.dev = torch.device("cuda", self.device)
+        self.T, self.B = int(T), int(B)
+        self.cont_ids, self.style_ids = [int(i) for i in cont_ids], [int(i) for i in style_ids]
+        self.gatys = bool(gatys)
+        self.nb_channels, self.cnt_channels = int(nb_channels), int(cnt_channels)
+        self.n_layers = layers_needed(self.cont_ids, self.style_ids)
+        self.L = len(self.style_ids)
+        self.precision = precision
+        cfg = _lib.AstConfig()
+        cfg.T, cfg.B, cfg.n_layers = self.T, self.B, self.n_layers
+        cfg.n_cont, cfg.n_style = len(self.cont_ids), self.L
+        if cfg.n_cont > _lib.AST_MAX_IDS or cfg.n_style > _lib.AST_MAX_IDS:
+            raise ValueError("too many layer ids")
+        for i, v in enumerate(self.cont_ids):
+            cfg.cont_ids[i] = v
+        for i, v in enumerate(self.style_ids):
+            cfg.style_ids[i] = v
+        cfg.gatys, cfg.nb_channels, cfg.cnt_channels = int(self.gatys), self.nb_channels, self.cnt_channels
+        cfg.precision = PRECISIONS[precision]
+        if window is not None:
+            cfg.total_T, cfg.win_begin, cfg.own_begin, cfg.own_end = [int(v) for v in window]
+        cfg.device = self.device
+        self._h = C.c_void_p()
+        _lib.check(self.lib.ast_create(C.byref(cfg), C.byref(self._h)))
+        self.ec_cols = len(self.cont_ids) * self.cnt_channels
+        if self.gatys:
+            self.gn_shape = (self.B, self.L, 128, 128)
+        else:
+            self.gn_shape = (self.B, self.nb_channels, self.L, self.L)
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self.lib.ast_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- setup ------------------------------------------------------------------------------
+    def set_weights(self, w: EncoderWeights):
+        """GatysNet.load_model (methods.py:79-84)."""
+        if w.n_layers < self.n_layers:
+            raise ValueError(f"need {self.n_layers} layers of weights, got {w.n_layers}")
+        f = lambda a: np.ascontiguousarray(a, dtype=np.float32)
+        arrs = [f(w.W0), f(w.b0), f(w.Wd[:self.n_layers]), f(w.bd[:self.n_layers]),
+                f(w.Wr[:self.n_layers]), f(w.br[:self.n_layers])]
+        with torch.cuda.device(self.dev):
+            _lib.check(self.lib.ast_set_weights(self._h, *[_ptr(a) for a in arrs], _stream()))
+
+    def set_targets(self, Pc, Ps, lambd, gamma=0.0):
+        """define_loss (methods.py:113-125): bake targets and loss weights."""
+        Pc = self._as_f32(Pc, (self.B, self.T, self.ec_cols))
+        Ps = self._as_f32(Ps, self.gn_shape)
+        with torch.cuda.device(self.dev):
+            _lib.check(self.lib.ast_set_targets(self._h, _ptr(Pc), _ptr(Ps), float(lambd), float(gamma), _stream()))
+
+    def _as_f32(self, a, shape):
+        if isinstance(a, torch.Tensor):
+            a = a.to(torch.float32).contiguous()
+            assert a.numel() == int(np.prod(shape)), (tuple(a.shape), shape)
+            return a
+        a = np.ascontiguousarray(a, dtype=np.float32)
+        assert a.size == int(np.prod(shape)), (a.shape, shape)
+        return a
+
+    def _x(self, x):
+        if not isinstance(x, torch.Tensor):
+            x = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32), device=self.dev)
+        x = x.to(device=self.dev, dtype=torch.float32).contiguous()
+        assert x.numel() == self.B * self.T, (tuple(x.shape), self.B, self.T)
+        return x
+
+    # -- get_embeds (methods.py:86-95) --------------------------------------------------------
+    def embeds(self, x, content=True, style=True):
+        x = self._x(x)
+        with torch.cuda.device(self.dev):
+            Ec = torch.empty((self.B, self.T, self.ec_cols), dtype=torch.float32, device=self.dev) if content else None
+            Gn = torch.empty(self.gn_shape, dtype=torch.float32, device=self.dev) if style else None
+            _lib.check(self.lib.ast_embeds(self._h, _ptr(x), _ptr(Ec), _ptr(Gn), _stream()))
+        return Ec, Gn
+
+    # -- the step -------------------------------------------------------------------------------
+    def step(self, x, losses=None, grad=None):
+        """Device in, device out, asynchronous on the current stream.  Returns (losses [B,4], grad [B,T])."""
+        x = self._x(x)
+        with torch.cuda.device(self.dev):
+            if losses is None:
+                losses = torch.empty((self.B, 4), dtype=torch.float32, device=self.dev)
+            if grad is None:
+                grad = torch.empty((self.B, self.T), dtype=torch.float32, device=self.dev)
+            _lib.check(self.lib.ast_step(self._h, _ptr(x), _ptr(losses), _ptr(grad), _stream()))
+        return losses, grad
+
+    def step_timed(self, x, losses, grad):
+        """One step with CUDA events between phases; returns ms (encoder fwd, bwd, gram+heads, total)."""
+        ms = (C.c_float * 4)()
+        with torch.cuda.device(self.dev):
+            _lib.check(self.lib.ast_step_timed(self._h, _ptr(x), _ptr(losses), _ptr(grad), _stream(), ms))
+        return list(ms)
+
+    def step_host(self, x64: np.ndarray):
+        """SciPy-facing evaluation: float64 host in, (losses [B,4] float64, grad [B,T] float64) out;
+        H2D + captured CUDA graph + D2H inside (ast_step_host)."""
+        x64 = np.ascontiguousarray(x64, dtype=np.float64)
+        assert x64.size == self.B * self.T
+        losses = np.empty((self.B, 4), np.float64)
+        grad = np.empty((self.B, self.T), np.float64)
+        _lib.check(self.lib.ast_step_host(self._h, _ptr(x64), _ptr(losses), _ptr(grad)))
+        return losses, grad
+
+    # -- two-phase step for time sharding -------------------------------------------------------
+    def forward_partial(self, x):
+        x = self._x(x)
+        with torch.cuda.device(self.dev):
+            _lib.check(self.lib.ast_step_forward(self._h, _ptr(x), _stream()))
+
+    def partials(self) -> torch.Tensor:
+        """Zero-copy torch view of the raw Gram + content-SSE partial sums (all-reduce this)."""
+        p, n = C.c_void_p(), C.c_int64()
+        _lib.check(self.lib.ast_partials(self._h, C.byref(p), C.byref(n)))
+        return torch.as_tensor(_DevMem(p.value, n.value), device=self.dev)
+
+    def backward(self, losses=None, grad=None):
+        with torch.cuda.device(self.dev):
+            if losses is None:
+                losses = torch.empty((self.B, 4), dtype=torch.float32, device=self.dev)
+            if grad is None:
+                grad = torch.empty((self.B, self.T), dtype=torch.float32, device=self.dev)
+            _lib.check(self.lib.ast_step_backward(self._h, _ptr(losses), _ptr(grad), _stream()))
+        return losses, grad
+
+    def extract(self, layer: int) -> torch.Tensor:
+        """cfg.extracts[layer] of the last forward (model.py:116); layer -1 = start-conv output."""
+        out = torch.empty((self.B, self.T, 128), dtype=torch.float32, device=self.dev)
+        with torch.cuda.device(self.dev):
+            _lib.check(self.lib.ast_get_extract(self._h, int(layer), _ptr(out), _stream()))
+        return out
+
+    @property
+    def launches_per_step(self) -> int:
+        return int(self.lib.ast_launches_per_step(self._h))
+
+    @property
+    def workspace_bytes(self) -> int:
+        return int(self.lib.ast_workspace_bytes(self._h))

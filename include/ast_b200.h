@@ -1,0 +1,132 @@
+/* ast_b200.h -- C ABI of the B200-native audio-style-transfer step.
+ *
+ * The reference (winlp4ever/audio_style_transfer) has no FFI: its step is an anonymous TensorFlow
+ * sub-graph driven from Python.  The boundary this library honours is therefore the Python-level
+ * contract of `GatysNet` (methods.py:19-216); each entry point below names the reference lines it
+ * replaces.  The ctypes binding a maintainer would add is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes, no C++ / torch types.
+ *   - every function returns 0 on success or a negative AST_E* code; ast_last_error() gives a
+ *     thread-local message.  No exception crosses the ABI.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).
+ *   - pointers named d_* are DEVICE pointers owned by the caller; pointers named h_* are HOST
+ *     pointers; pointers named p_* may be either (copied with cudaMemcpyDefault).
+ *   - an ast_ctx is bound to one device and is not thread-safe; distinct contexts are independent.
+ *   - there is NO CPU fallback: if no sm_100 device is present ast_create fails with AST_ECUDA.
+ *
+ * Layouts (row-major, innermost last)
+ *   x, grad      [B, T]            float32, mu-law units (methods.py:49-54)
+ *   extracts     [B, T, 128]       float32 (model.py:116, TF's [1, T, 128])
+ *   Pc           [B, T, n_cont*cnt_channels]                         (methods.py:58)
+ *   Ps / Gn      [B, nb_channels, L, L]  channel-wise ("ours", methods.py:69,73-76)
+ *                [B, L, 128, 128]        --gatys                     (methods.py:71,73)
+ *   weights      W0 [3,1,128]  b0 [128]  Wd [NL,3,128,128] (k,cin,cout)  bd [NL,128]
+ *                Wr [NL,128,128] (cin,cout)  br [NL,128]   -- TF's [1,K,Cin,Cout] order
+ *                (nsynth/wavenet/masked.py:136), so a checkpoint reader is a plain copy.
+ */
+#ifndef AST_B200_H
+#define AST_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AST_OK            0
+#define AST_EINVAL       -1   /* bad argument / unsupported shape                       */
+#define AST_ECUDA        -2   /* CUDA runtime/driver error, or no sm_100 device          */
+#define AST_EUNSUPPORTED -3   /* valid in the reference but outside this path (gamma!=0) */
+#define AST_ESTATE       -4   /* call order violated (weights/targets not set)          */
+
+#define AST_PREC_FP32     0   /* CUDA-core fp32 everywhere: the <=1e-4 tier                           */
+#define AST_PREC_BF16     1   /* tcgen05 bf16 tensor cores, fp32 accumulate in TMEM: the <=1e-2 tier.  */
+                              /* forward operands are 2-term bf16 splits (hi+lo), backward plain bf16 */
+
+#define AST_MAX_IDS      32
+#define AST_CHANNELS    128   /* ae_width, model.py:73 */
+
+typedef struct ast_ctx ast_ctx;
+
+typedef struct ast_config {
+    int32_t T;                       /* samples per pair = --batch_size (methods.py:250); T % 128 == 0    */
+    int32_t B;                       /* independent content/style pairs (reference: 1, methods.py:50)    */
+    int32_t n_layers;                /* NL = 1 + highest extract used (TF prunes the rest)              */
+    int32_t n_cont;                  /* --cont_lyrs (methods.py:254)                                     */
+    int32_t cont_ids[AST_MAX_IDS];
+    int32_t n_style;                 /* resolved style ids (methods.py:60-66)                            */
+    int32_t style_ids[AST_MAX_IDS];
+    int32_t gatys;                   /* --gatys (methods.py:261)                                         */
+    int32_t nb_channels;             /* --channels (methods.py:258), ours only                           */
+    int32_t cnt_channels;            /* --cnt_channels (methods.py:259)                                  */
+    int32_t precision;               /* AST_PREC_*                                                       */
+    /* Time sharding (new capability, DESIGN.md "multi-GPU"): this context holds the window
+     * [win_begin, win_begin + T) of a clip of total_T samples and OWNS rows
+     * [own_begin, own_end) of it (global sample indices).  Gram / content sums run over owned rows
+     * only; loss means are normalised with total_T.  Unsharded: win_begin = 0, own = [0, T),
+     * total_T = T (or all zero, which means the same). */
+    int64_t total_T;
+    int64_t win_begin;
+    int64_t own_begin;
+    int64_t own_end;
+    int32_t device;                  /* CUDA device ordinal                                              */
+    int32_t reserved;
+} ast_config;
+
+/* GatysNet.__init__/build (methods.py:20-77): allocate workspaces for a fixed (T, B, layer set). */
+int  ast_create(const ast_config* cfg, ast_ctx** out);
+int  ast_destroy(ast_ctx* ctx);
+const char* ast_last_error(void);
+/* Library identification: "ast_b200 <version> sm_100a". */
+const char* ast_version(void);
+/* Bytes of device memory the context holds. */
+int64_t ast_workspace_bytes(const ast_ctx* ctx);
+
+/* GatysNet.load_model (methods.py:79-84).  Copies; host or device pointers. */
+int  ast_set_weights(ast_ctx* ctx, const float* p_W0, const float* p_b0,
+                     const float* p_Wd, const float* p_bd,
+                     const float* p_Wr, const float* p_br, void* stream);
+
+/* define_loss (methods.py:113-125): targets and loss weights baked for the following steps.
+ * gamma != 0 -> AST_EUNSUPPORTED (STFT regulariser). */
+int  ast_set_targets(ast_ctx* ctx, const float* p_Pc, const float* p_Ps,
+                     double lambd, double gamma, void* stream);
+
+/* get_embeds (methods.py:86-95), forward only.  Either output may be NULL. */
+int  ast_embeds(ast_ctx* ctx, const float* d_x, float* d_Ec, float* d_Gn, void* stream);
+
+/* One function evaluation of the L-BFGS-B loop (methods.py:133-137,167):
+ * d_losses [B,4] = {total, content, style, regulariser(=0)}, d_grad [B,T] = d total / d x.
+ * Asynchronous on `stream`, no host sync, CUDA-graph capturable. */
+int  ast_step(ast_ctx* ctx, const float* d_x, float* d_losses, float* d_grad, void* stream);
+
+/* The same evaluation through HOST buffers, as SciPy's fun(x)->(f,g) sees it (float64 each way,
+ * methods.py:167 / ScipyOptimizerInterface): H2D of x, a replay of the captured CUDA graph of
+ * ast_step, D2H of losses and gradient, stream synchronised before return. */
+int  ast_step_host(ast_ctx* ctx, const double* h_x, double* h_losses, double* h_grad);
+
+/* Two-phase step for time-sharded clips.  Phase 1 runs the forward and leaves the raw (un-normalised)
+ * Gram partials and content squared-error partials of the owned rows in one contiguous fp32 device
+ * buffer (ast_partials) that the caller all-reduces (sum) across ranks; phase 2 normalises, forms
+ * the losses and runs the backward.  ast_step == forward + backward with no reduction between. */
+int  ast_step_forward(ast_ctx* ctx, const float* d_x, void* stream);
+int  ast_partials(ast_ctx* ctx, float** d_buf, int64_t* count);
+int  ast_step_backward(ast_ctx* ctx, float* d_losses, float* d_grad, void* stream);
+
+/* cfg.extracts[layer] of the last forward (model.py:116), [B,T,128] fp32 -> d_out.  Debug/parity. */
+int  ast_get_extract(ast_ctx* ctx, int32_t layer, float* d_out, void* stream);
+
+/* Number of kernels one ast_step launches (for bench.py's gpu_launches). */
+int  ast_launches_per_step(const ast_ctx* ctx);
+
+/* Times the dominant kernels of the last ast_step_timed call with CUDA events on `stream`.
+ * ms_out[0] = forward layer kernels, [1] = backward layer kernels, [2] = Gram+heads, [3] = total. */
+int  ast_step_timed(ast_ctx* ctx, const float* d_x, float* d_losses, float* d_grad, void* stream,
+                    float* ms_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AST_B200_H */

@@ -1,0 +1,198 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI, against the fp64 oracle on the
+same seeded inputs.  Tolerances are BASELINE.json's: rel-L2 <= 1e-4 on loss and gradient in the fp32
+tier, <= 1e-2 in the bf16 tensor-core tier; integer indexing bit-exact."""
+import numpy as np
+import pytest
+import torch
+
+from audio_style_transfer_b200 import synth
+from oracle import cases, step_np
+
+pytestmark = pytest.mark.gpu
+
+TOL = {"fp32": dict(loss=1e-4, grad=1e-4, feat=2e-5), "bf16": dict(loss=1e-2, grad=1e-2, feat=2e-3)}
+PRECS = ["fp32", "bf16"]
+
+
+def rel(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300)
+
+
+def make_step(case, prec, B=1, window=None, T=None):
+    from audio_style_transfer_b200.step import StyleStep
+    st = StyleStep(T or case["T"], case["cont"], case["style"], case["gatys"], case["nb"], case["cnt"], B=B,
+                   precision=prec, window=window)
+    st.set_weights(case["w"])
+    return st
+
+
+SMALL = ["t1024_ours_s0", "t1024_ours_sub", "t1024_ours_ids", "t2048_gatys_s1", "t4096_cfg0", "t4096_cfg1",
+         "t4096_alias30"]
+
+
+@pytest.mark.parametrize("prec", PRECS)
+@pytest.mark.parametrize("name", SMALL)
+def test_step_matches_oracle(name, prec):
+    case = cases.build_inputs(name)
+    Pc, Ps = cases.oracle_targets(case)
+    losses, dx, aux = cases.oracle_step(case, Pc, Ps, return_aux=True)
+    st = make_step(case, prec)
+    # forward features first (get_embeds, methods.py:86-95)
+    Ec, Gn = st.embeds(case["x"][None])
+    tol = TOL[prec]
+    assert rel(Ec[0].cpu().numpy(), aux["Ec"]) <= tol["feat"]
+    assert rel(Gn[0].cpu().numpy(), aux["Gn"][:Gn.shape[1]]) <= tol["feat"]
+    for l in (-1, 0, case["NL"] - 1):
+        assert rel(st.extract(l)[0].cpu().numpy(), aux["H"][l + 1]) <= tol["feat"], l
+    st.set_targets(Pc[None], Ps[None], case["lambd"])
+    lo, g = st.step(case["x"][None])
+    lo, g = lo.cpu().numpy()[0], g.cpu().numpy()[0]
+    assert abs(lo[0] - losses[0]) <= tol["loss"] * abs(losses[0])
+    assert abs(lo[2] - losses[2]) <= tol["loss"] * abs(losses[2])
+    # content loss is a difference of nearly equal features (x = content + noise): the absolute error
+    # of the features shows up relative to a small number, so it is bounded relative to the total
+    assert abs(lo[1] - losses[1]) <= tol["loss"] * max(abs(losses[1]), abs(losses[0]))
+    assert lo[3] == 0.0
+    assert rel(g, dx) <= tol["grad"], rel(g, dx)
+    st.close()
+
+
+@pytest.mark.parametrize("prec", PRECS)
+@pytest.mark.parametrize("name", ["t16384_cfg0", "t16384_cfg1"])
+def test_baseline_size_matches_oracle_and_golden(name, prec, golden_dir):
+    """BASELINE.json configs[0]/[1] sizes: oracle computed here (tens of seconds) and cross-checked
+    with the committed golden vectors, then the CUDA step against both."""
+    case = cases.build_inputs(name)
+    Pc, Ps = cases.oracle_targets(case)
+    losses, dx = cases.oracle_step(case, Pc, Ps)
+    gold = np.load(golden_dir / f"{name}.npz")
+    assert np.allclose(losses[:3], gold["losses"], rtol=1e-9)
+    assert rel(dx[::int(gold["dx_stride"])], gold["dx"]) <= 1e-8
+    st = make_step(case, prec)
+    st.set_targets(Pc[None], Ps[None], case["lambd"])
+    lo, g = st.step(case["x"][None])
+    lo, g = lo.cpu().numpy()[0], g.cpu().numpy()[0]
+    tol = TOL[prec]
+    assert abs(lo[0] - losses[0]) <= tol["loss"] * abs(losses[0])
+    assert rel(g, dx) <= tol["grad"], rel(g, dx)
+    # the SciPy-facing host entry point returns the same numbers (float64 each way, CUDA graph inside)
+    lh, gh = st.step_host(case["x"])
+    assert np.allclose(lh[0], lo, rtol=1e-6, atol=1e-7)
+    assert rel(gh[0], g) <= 1e-6
+    lh2, gh2 = st.step_host(case["x"])      # graph replay is deterministic
+    assert np.array_equal(gh, gh2) and np.array_equal(lh, lh2)
+    st.close()
+
+
+@pytest.mark.parametrize("prec", PRECS)
+def test_index_probe_bit_exact(prec):
+    """Integer weights and inputs: every product and sum is exact in fp32 (and in the bf16 hi/lo split),
+    so tap offsets t+-d, zero padding at both clip ends and tile seams must reproduce the oracle
+    EXACTLY at every layer."""
+    NL, T = 12, 2048
+    w = synth.make_int_weights(NL, 5)
+    x = np.random.default_rng(7).integers(-3, 4, T).astype(np.float64)
+    H, _ = step_np.encoder_forward(x, w, NL)
+    from audio_style_transfer_b200.step import StyleStep
+    st = StyleStep(T, [NL - 1], list(range(NL)), precision=prec)
+    st.set_weights(w)
+    st.embeds(x[None], style=False)
+    nl_exact = NL if prec == "fp32" else 0
+    for l in range(-1, NL):
+        got = st.extract(l)[0].cpu().numpy().astype(np.float64)
+        if np.abs(H[l + 1]).max() < 2 ** (24 if prec == "fp32" else 16):
+            assert np.array_equal(got, H[l + 1]), f"layer {l}"
+            nl_exact = max(nl_exact, l + 1)
+    assert nl_exact >= 4
+    st.close()
+
+
+@pytest.mark.parametrize("prec", PRECS)
+def test_one_hot_impulse_response_positions(prec):
+    """A single non-zero sample: the support of every layer's response must sit at exactly the
+    oracle's rows (dilation offsets and both clip edges), here with the impulse near the end."""
+    NL, T = 10, 1024
+    w = synth.make_weights(NL, 3, bias_scale=0.0)
+    for pos in (0, 517, T - 1):
+        x = np.zeros(T); x[pos] = 64.0
+        H, _ = step_np.encoder_forward(x, w, NL)
+        from audio_style_transfer_b200.step import StyleStep
+        st = StyleStep(T, [NL - 1], list(range(NL)), precision=prec)
+        st.set_weights(w)
+        st.embeds(x[None], style=False)
+        for l in (0, 4, 9):
+            got = st.extract(l)[0].cpu().numpy()
+            assert np.array_equal(np.abs(got).sum(1) > 0, np.abs(H[l + 1]).sum(1) > 0), (pos, l)
+        st.close()
+
+
+@pytest.mark.parametrize("prec", PRECS)
+def test_batch_of_pairs_equals_loop(prec):
+    """B independent pairs (BASELINE configs[3], new capability): each row of the batch must equal the
+    B=1 result for that pair bit for bit (no cross-pair leakage through the dilated taps)."""
+    case = cases.build_inputs("t1024_ours_s0")
+    Pc, Ps = cases.oracle_targets(case)
+    rng = np.random.default_rng(5)
+    B = 3
+    xs = np.stack([case["x"] + rng.standard_normal(case["T"]) * (i > 0) for i in range(B)])
+    stB = make_step(case, prec, B=B)
+    stB.set_targets(np.repeat(Pc[None], B, 0), np.repeat(Ps[None], B, 0), case["lambd"])
+    loB, gB = stB.step(xs)
+    st1 = make_step(case, prec)
+    st1.set_targets(Pc[None], Ps[None], case["lambd"])
+    for i in range(B):
+        lo, g = st1.step(xs[i:i + 1])
+        assert torch.equal(g[0], gB[i]) and torch.equal(lo[0], loB[i]), i
+    stB.close(); st1.close()
+
+
+@pytest.mark.parametrize("prec", PRECS)
+def test_time_sharded_windows_equal_unsharded(prec):
+    """Time sharding emulated on one GPU: P window contexts, partial sums added (= the all-reduce),
+    owned gradient slices concatenated.  Must agree with the single-context step; on integer data the
+    forward at the seams is bit-exact."""
+    from audio_style_transfer_b200.sharding import plan_windows
+    case = cases.build_inputs("t4096_cfg0")
+    case = dict(case, cont=[5], style=[0, 1, 2, 3, 4, 5], NL=6)
+    case["w"] = synth.make_weights(6, 0, 0.1)
+    Pc, Ps = cases.oracle_targets(case)
+    full = make_step(case, prec)
+    full.set_targets(Pc[None], Ps[None], case["lambd"])
+    lo_f, g_f = full.step(case["x"][None])
+    P = 3
+    plan = plan_windows(case["T"], P, case["NL"])
+    steps, parts = [], []
+    for (wb, we, ob, oe) in plan:
+        st = make_step(case, prec, window=(case["T"], wb, ob, oe), T=we - wb)
+        st.set_targets(Pc[None, wb:we], Ps[None], case["lambd"])
+        st.forward_partial(case["x"][None, wb:we])
+        steps.append(st); parts.append(st.partials())
+    total = torch.stack([p.clone() for p in parts]).sum(0)
+    g = torch.empty(case["T"], device="cuda")
+    for st, p, (wb, we, ob, oe) in zip(steps, parts, plan):
+        p.copy_(total)
+        lo, gw = st.backward()
+        g[ob:oe] = gw[0, ob - wb:oe - wb]
+        assert torch.allclose(lo, lo_f, rtol=2e-5 if prec == "fp32" else 2e-3)
+    tol = 2e-5 if prec == "fp32" else 5e-3
+    assert rel(g.cpu().numpy(), g_f[0].cpu().numpy()) <= tol
+    for st in steps:
+        st.close()
+    full.close()
+
+
+def test_errors_are_loud():
+    from audio_style_transfer_b200._lib import AstError
+    from audio_style_transfer_b200.step import StyleStep
+    with pytest.raises(AstError):
+        StyleStep(1000, [9], list(range(10)), precision="fp32")          # T % 128
+    st = StyleStep(1024, [9], list(range(10)), precision="fp32")
+    with pytest.raises(AstError):                                         # AST_ESTATE: no weights/targets
+        st.step(np.zeros((1, 1024), np.float32))
+    st.set_weights(synth.make_weights(10))
+    with pytest.raises(AstError):                                         # gamma != 0 -> AST_EUNSUPPORTED
+        st.set_targets(np.zeros((1, 1024, 128), np.float32), np.zeros((1, 128, 10, 10), np.float32), 100.0, 0.1)
+    with pytest.raises(AstError):
+        StyleStep(1024, [9], [3, 3], precision="fp32")                    # duplicate style layer
+    st.close()
