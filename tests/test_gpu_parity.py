@@ -19,6 +19,20 @@ def rel(a, b):
     return np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300)
 
 
+def fp32_floor(case, Pc, Ps, dx64):
+    """rel-L2 distance between an fp32 CPU run of the same step (what the reference's fp32 TensorFlow
+    graph computes) and fp64 truth.  The 30-layer ReLU stack amplifies rounding (sign-mask flips), so
+    for deep cases two correct fp32 implementations differ by more than 1e-4; the tolerance is then
+    a small multiple of this measured floor instead ("accuracy tiers")."""
+    _, dx32 = step_np.step(case["x"].astype(np.float32), case["w"], Pc.astype(np.float32), Ps.astype(np.float32),
+                           case["cont"], case["style"], case["gatys"], case["lambd"], 0.0, case["nb"], case["cnt"])
+    return rel(dx32, dx64)
+
+
+def grad_tol(prec, floor):
+    return max(TOL[prec]["grad"], (10.0 if prec == "fp32" else 100.0) * floor)
+
+
 def make_step(case, prec, B=1, window=None, T=None):
     from audio_style_transfer_b200.step import StyleStep
     st = StyleStep(T or case["T"], case["cont"], case["style"], case["gatys"], case["nb"], case["cnt"], B=B,
@@ -54,7 +68,8 @@ def test_step_matches_oracle(name, prec):
     # of the features shows up relative to a small number, so it is bounded relative to the total
     assert abs(lo[1] - losses[1]) <= tol["loss"] * max(abs(losses[1]), abs(losses[0]))
     assert lo[3] == 0.0
-    assert rel(g, dx) <= tol["grad"], rel(g, dx)
+    floor = fp32_floor(case, Pc, Ps, dx)
+    assert rel(g, dx) <= grad_tol(prec, floor), (rel(g, dx), floor)
     st.close()
 
 
@@ -75,7 +90,10 @@ def test_baseline_size_matches_oracle_and_golden(name, prec, golden_dir):
     lo, g = lo.cpu().numpy()[0], g.cpu().numpy()[0]
     tol = TOL[prec]
     assert abs(lo[0] - losses[0]) <= tol["loss"] * abs(losses[0])
-    assert rel(g, dx) <= tol["grad"], rel(g, dx)
+    floor = fp32_floor(case, Pc, Ps, dx)
+    print(f"{name}[{prec}]: loss rel {abs(lo[0] - losses[0]) / abs(losses[0]):.2e} grad rel-L2 {rel(g, dx):.2e} "
+          f"(fp32 CPU floor {floor:.2e})")
+    assert rel(g, dx) <= grad_tol(prec, floor), (rel(g, dx), floor)
     # the SciPy-facing host entry point returns the same numbers (float64 each way, CUDA graph inside)
     lh, gh = st.step_host(case["x"])
     assert np.allclose(lh[0], lo, rtol=1e-6, atol=1e-7)
@@ -141,9 +159,13 @@ def test_batch_of_pairs_equals_loop(prec):
     loB, gB = stB.step(xs)
     st1 = make_step(case, prec)
     st1.set_targets(Pc[None], Ps[None], case["lambd"])
+    exB = stB.extract(case["NL"] - 1)
     for i in range(B):
         lo, g = st1.step(xs[i:i + 1])
-        assert torch.equal(g[0], gB[i]) and torch.equal(lo[0], loB[i]), i
+        assert torch.equal(st1.extract(case["NL"] - 1)[0], exB[i]), i      # encoder: bit for bit
+        # Gram split-K geometry depends on B, so sums differ in the last bits only
+        assert rel(g[0].cpu().numpy(), gB[i].cpu().numpy()) <= 1e-5, i
+        assert torch.allclose(lo[0], loB[i], rtol=1e-5), i
     stB.close(); st1.close()
 
 
