@@ -25,7 +25,7 @@ ERRORS = {-1: "AST_EINVAL", -2: "AST_ECUDA", -3: "AST_EUNSUPPORTED", -4: "AST_ES
 
 SYMBOLS = [
     "ast_create", "ast_destroy", "ast_last_error", "ast_version", "ast_workspace_bytes",
-    "ast_set_weights", "ast_set_targets", "ast_embeds", "ast_step", "ast_step_host",
+    "ast_set_weights", "ast_set_targets", "ast_embeds", "ast_step", "ast_step_graph", "ast_step_host",
     "ast_step_forward", "ast_partials", "ast_step_backward", "ast_get_extract",
     "ast_launches_per_step", "ast_step_timed",
 ]
@@ -98,6 +98,7 @@ def load() -> C.CDLL:
     lib.ast_set_targets.argtypes = [vp, vp, vp, dbl, dbl, vp]
     lib.ast_embeds.argtypes = [vp, vp, vp, vp, vp]
     lib.ast_step.argtypes = [vp, vp, vp, vp, vp]
+    lib.ast_step_graph.argtypes = [vp, vp, vp, vp, vp]
     lib.ast_step_host.argtypes = [vp, vp, vp, vp]
     lib.ast_step_forward.argtypes = [vp, vp, vp]
     lib.ast_partials.argtypes = [vp, C.POINTER(vp), C.POINTER(i64)]

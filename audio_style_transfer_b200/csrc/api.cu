@@ -64,6 +64,9 @@ struct ast_ctx {
     // host-buffer step (ast_step_host)
     cudaStream_t hstream;
     cudaGraphExec_t gexec;
+    cudaGraphExec_t gdev;                       // ast_step_graph: device-pointer step
+    const float* gdev_x; float* gdev_losses; float* gdev_grad;
+    cudaGraphExec_t gphase[3];                  // ast_step_timed: encoder fwd | gram + heads | backward
     float *d_x, *d_losses, *d_grad;
     float *p_x, *p_out;            // pinned
     int launches_per_step;
@@ -98,11 +101,19 @@ extern "C" const char* ast_version(void) { return "ast_b200 0.1 sm_100a"; }
 extern "C" int64_t ast_workspace_bytes(const ast_ctx* c) { return c ? c->bytes : 0; }
 extern "C" int ast_launches_per_step(const ast_ctx* c) { return c ? c->launches_per_step : 0; }
 
+static void drop_graphs(ast_ctx* c) {
+    if (c->gexec) { cudaGraphExecDestroy(c->gexec); c->gexec = nullptr; }
+    if (c->gdev) { cudaGraphExecDestroy(c->gdev); c->gdev = nullptr; }
+    for (auto& g : c->gphase) if (g) { cudaGraphExecDestroy(g); g = nullptr; }
+}
+
 extern "C" int ast_destroy(ast_ctx* c) {
     if (!c) return AST_OK;
     cudaSetDevice(c->cfg.device);
     if (c->tc) tc_destroy(c->tc);
     if (c->gexec) cudaGraphExecDestroy(c->gexec);
+    if (c->gdev) cudaGraphExecDestroy(c->gdev);
+    for (auto& g : c->gphase) if (g) cudaGraphExecDestroy(g);
     if (c->hstream) cudaStreamDestroy(c->hstream);
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
     if (c->p_x) cudaFreeHost(c->p_x);
@@ -140,6 +151,8 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
     c->T = cfg->T; c->B = cfg->B; c->R = cfg->B * cfg->T; c->NL = cfg->n_layers; c->L = cfg->n_style;
     c->n_cont = cfg->n_cont; c->prec = cfg->precision; c->bytes = 0;
     c->tc = nullptr; c->hstream = nullptr; c->gexec = nullptr; c->p_x = c->p_out = nullptr;
+    c->gdev = nullptr; c->gdev_x = nullptr; c->gdev_losses = c->gdev_grad = nullptr;
+    for (auto& g : c->gphase) g = nullptr;
     for (auto& e : c->ev) e = nullptr;
     c->have_w = c->have_t = false; c->launches_per_step = 0; c->lambd = 0.f;
 
@@ -278,7 +291,7 @@ extern "C" int ast_set_targets(ast_ctx* c, const float* Pc, const float* Ps, dou
     CK(cudaStreamSynchronize(s));
     c->lambd = (float)lambd;
     c->have_t = true;
-    if (c->gexec) { cudaGraphExecDestroy(c->gexec); c->gexec = nullptr; }   // loss weights are baked in the graph
+    drop_graphs(c);                                                         // loss weights are baked in the graphs
     return AST_OK;
 }
 
@@ -422,28 +435,37 @@ extern "C" int ast_get_extract(ast_ctx* c, int32_t layer, float* d_out, void* st
     return AST_OK;
 }
 
-// ---- the evaluation as SciPy sees it: host float64 in, host float64 out -------------------------
-static int capture_host_graph(ast_ctx* c) {
+// ---- CUDA graphs ---------------------------------------------------------------------------------
+// Captures whatever `body` enqueues on the context's private stream into an executable graph.
+template <typename F>
+static int capture_graph(ast_ctx* c, cudaGraphExec_t* out, F body) {
     cudaGraph_t graph = nullptr;
     CK(cudaStreamBeginCapture(c->hstream, cudaStreamCaptureModeThreadLocal));
-    cudaMemcpyAsync(c->d_x, c->p_x, (size_t)c->R * sizeof(float), cudaMemcpyHostToDevice, c->hstream);
-    int r = ast_step(c, c->d_x, c->d_losses, c->d_grad, c->hstream);
-    cudaMemcpyAsync(c->p_out, c->d_losses, (size_t)c->B * 4 * sizeof(float), cudaMemcpyDeviceToHost, c->hstream);
-    cudaMemcpyAsync(c->p_out + 4 * c->B, c->d_grad, (size_t)c->R * sizeof(float), cudaMemcpyDeviceToHost, c->hstream);
-    cudaError_t e = cudaStreamEndCapture(c->hstream, &graph);
+    const int r = body(c->hstream);
+    const cudaError_t e = cudaStreamEndCapture(c->hstream, &graph);
     if (r != AST_OK) { if (graph) cudaGraphDestroy(graph); return r; }
     if (e != cudaSuccess) return fail(AST_ECUDA, "graph capture failed: %s", cudaGetErrorString(e));
-    e = cudaGraphInstantiate(&c->gexec, graph, 0);
+    const cudaError_t e2 = cudaGraphInstantiate(out, graph, 0);
     cudaGraphDestroy(graph);
-    if (e != cudaSuccess) { c->gexec = nullptr; return fail(AST_ECUDA, "graph instantiate failed: %s", cudaGetErrorString(e)); }
+    if (e2 != cudaSuccess) { *out = nullptr; return fail(AST_ECUDA, "graph instantiate failed: %s", cudaGetErrorString(e2)); }
     return AST_OK;
 }
 
+// the evaluation as SciPy sees it: host float64 in, host float64 out
 extern "C" int ast_step_host(ast_ctx* c, const double* h_x, double* h_losses, double* h_grad) {
     if (!c || !h_x || !h_losses || !h_grad) return fail(AST_EINVAL, "null argument");
     if (!c->have_w || !c->have_t) return fail(AST_ESTATE, "ast_set_weights and ast_set_targets must precede a step");
     CK(cudaSetDevice(c->cfg.device));
-    if (!c->gexec) { int r = capture_host_graph(c); if (r != AST_OK) return r; }
+    if (!c->gexec) {
+        const int r = capture_graph(c, &c->gexec, [&](cudaStream_t s) {
+            cudaMemcpyAsync(c->d_x, c->p_x, (size_t)c->R * sizeof(float), cudaMemcpyHostToDevice, s);
+            const int rr = ast_step(c, c->d_x, c->d_losses, c->d_grad, s);
+            cudaMemcpyAsync(c->p_out, c->d_losses, (size_t)c->B * 4 * sizeof(float), cudaMemcpyDeviceToHost, s);
+            cudaMemcpyAsync(c->p_out + 4 * c->B, c->d_grad, (size_t)c->R * sizeof(float), cudaMemcpyDeviceToHost, s);
+            return rr;
+        });
+        if (r != AST_OK) return r;
+    }
     for (int i = 0; i < c->R; ++i) c->p_x[i] = (float)h_x[i];
     CK(cudaGraphLaunch(c->gexec, c->hstream));
     CK(cudaStreamSynchronize(c->hstream));
@@ -453,22 +475,53 @@ extern "C" int ast_step_host(ast_ctx* c, const double* h_x, double* h_losses, do
     return AST_OK;
 }
 
+// device pointers in, device pointers out: one cudaGraphLaunch per evaluation
+extern "C" int ast_step_graph(ast_ctx* c, const float* d_x, float* d_losses, float* d_grad, void* stream) {
+    if (!c || !d_x || !d_losses || !d_grad) return fail(AST_EINVAL, "null argument");
+    if (!c->have_w || !c->have_t) return fail(AST_ESTATE, "ast_set_weights and ast_set_targets must precede a step");
+    if (c->gdev && (c->gdev_x != d_x || c->gdev_losses != d_losses || c->gdev_grad != d_grad)) {
+        cudaGraphExecDestroy(c->gdev); c->gdev = nullptr;          // pointers are baked into the graph
+    }
+    if (!c->gdev) {
+        CK(cudaStreamSynchronize((cudaStream_t)stream));
+        const int r = capture_graph(c, &c->gdev, [&](cudaStream_t s) { return ast_step(c, d_x, d_losses, d_grad, s); });
+        if (r != AST_OK) return r;
+        c->gdev_x = d_x; c->gdev_losses = d_losses; c->gdev_grad = d_grad;
+    }
+    CK(cudaGraphLaunch(c->gdev, (cudaStream_t)stream));
+    return AST_OK;
+}
+
 // ---- phase timing with CUDA events on the launching stream (bench.py roofline) ------------------
+// Each phase is its own captured graph (same launches as ast_step), replayed with events between.
 extern "C" int ast_step_timed(ast_ctx* c, const float* d_x, float* d_losses, float* d_grad, void* stream, float* ms_out) {
     if (!c || !d_x || !d_losses || !d_grad || !ms_out) return fail(AST_EINVAL, "null argument");
     if (!c->have_w || !c->have_t) return fail(AST_ESTATE, "ast_set_weights and ast_set_targets must precede a step");
     cudaStream_t s = (cudaStream_t)stream;
-    // same launches as ast_step, with events between the phases
+    if (!c->gphase[0]) {
+        CK(cudaStreamSynchronize(s));
+        int r = capture_graph(c, &c->gphase[0], [&](cudaStream_t cs) { run_encoder(c, c->d_x, cs); return AST_OK; });
+        if (r != AST_OK) return r;
+        r = capture_graph(c, &c->gphase[1], [&](cudaStream_t cs) {
+            run_gram(c, cs);
+            launch_content_sse(c->d_Hcptr, c->n_cont, c->cfg.cnt_channels, c->Pc, c->T, c->B, c->own_lo, c->own_hi,
+                               c->sse_part, c->sse_nblk, c->partials + (size_t)c->B * c->nmat * c->msize, cs);
+            return AST_OK;
+        });
+        if (r != AST_OK) return r;
+        r = capture_graph(c, &c->gphase[2], [&](cudaStream_t cs) { return ast_step_backward(c, c->d_losses, c->d_grad, cs); });
+        if (r != AST_OK) return r;
+    }
+    CK(cudaMemcpyAsync(c->d_x, d_x, (size_t)c->R * sizeof(float), cudaMemcpyDeviceToDevice, s));
     CK(cudaEventRecord(c->ev[0], s));
-    run_encoder(c, d_x, s);
+    CK(cudaGraphLaunch(c->gphase[0], s));
     CK(cudaEventRecord(c->ev[1], s));
-    run_gram(c, s);
-    launch_content_sse(c->d_Hcptr, c->n_cont, c->cfg.cnt_channels, c->Pc, c->T, c->B, c->own_lo, c->own_hi,
-                       c->sse_part, c->sse_nblk, c->partials + (size_t)c->B * c->nmat * c->msize, s);
+    CK(cudaGraphLaunch(c->gphase[1], s));
     CK(cudaEventRecord(c->ev[2], s));
-    int r = ast_step_backward(c, d_losses, d_grad, s);
-    if (r != AST_OK) return r;
+    CK(cudaGraphLaunch(c->gphase[2], s));
     CK(cudaEventRecord(c->ev[3], s));
+    CK(cudaMemcpyAsync(d_losses, c->d_losses, (size_t)c->B * 4 * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    CK(cudaMemcpyAsync(d_grad, c->d_grad, (size_t)c->R * sizeof(float), cudaMemcpyDeviceToDevice, s));
     CK(cudaEventSynchronize(c->ev[3]));
     float enc = 0, gram = 0, bwd = 0, tot = 0;
     CK(cudaEventElapsedTime(&enc, c->ev[0], c->ev[1]));

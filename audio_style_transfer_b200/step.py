@@ -146,6 +146,13 @@ class StyleStep:
             _lib.check(self.lib.ast_step(self._h, _ptr(x), _ptr(losses), _ptr(grad), _stream()))
         return losses, grad
 
+    def step_graph(self, x, losses, grad):
+        """The same evaluation replayed from the library's captured CUDA graph (fixed device buffers)."""
+        assert x.is_cuda and x.dtype == torch.float32 and x.is_contiguous()
+        with torch.cuda.device(self.dev):
+            _lib.check(self.lib.ast_step_graph(self._h, _ptr(x), _ptr(losses), _ptr(grad), _stream()))
+        return losses, grad
+
     def step_timed(self, x, losses, grad):
         """One step with CUDA events between phases; returns ms (encoder fwd, bwd, gram+heads, total)."""
         ms = (C.c_float * 4)()

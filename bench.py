@@ -116,3 +116,256 @@ def build_workload(name, B, seed_shift=0):
     xs = np.stack([synth.step_input(c, seed=3 + 10 * (seed_shift + i)) for i, c in enumerate(cs)])
     return dict(T=T, cont=cont, style=style, gatys=gatys, NL=NL, L=len(style), w=w, content=np.stack(cs),
                 style_a=np.stack(ss), x=xs, desc=desc, lambd=100.0)
+
+
+def l2n(G, eps=1e-12):
+    import torch
+    ss = (G * G).sum(dim=(-2, -1), keepdim=True)
+    return G * torch.rsqrt(torch.clamp(ss, min=eps))
+
+
+def gpu_targets(st, content, style):
+    """GatysNet.run target construction (methods.py:192-212) through the product's own forward
+    (ast_embeds): Pc = Ec(content); Ps = l2n(Gn(content) + mean Gn(style chunks) - mean Gn(content chunks))."""
+    Pc, Gc = st.embeds(content)
+    _, Gs = st.embeds(style)
+    return Pc, l2n(Gc + Gs - Gc)
+
+
+def cpu_step_factory(wl, threads):
+    """The CPU arm: oracle/torch_step.py (torch-CPU fp32 restatement, kind='port').  The reference's own
+    TF1 CPU path cannot run on this image (no TensorFlow for Python 3.12, no network)."""
+    import torch
+    from oracle.torch_step import TorchStep
+    torch.set_num_threads(threads)
+    ts = TorchStep(wl["w"], wl["cont"], wl["style"], wl["gatys"], wl["lambd"], n_layers=wl["NL"], dtype=torch.float32)
+    x = torch.tensor(wl["x"][:1])
+    with torch.no_grad():
+        ex = ts.forward(torch.tensor(wl["content"][:1]))
+        Pc, Gc = ts.heads(ex)
+        _, Gs = ts.heads(ts.forward(torch.tensor(wl["style_a"][:1])))
+        Ps = l2n(Gc + Gs - Gc)
+    return lambda: ts.step(x, Pc, Ps)
+
+
+def time_cpu(fn, budget_s, max_steps, warmup=1):
+    for _ in range(warmup):
+        fn()
+    t0 = time.perf_counter()
+    fn()
+    t1 = time.perf_counter() - t0
+    n = int(max(1, min(max_steps, budget_s / max(t1, 1e-6))))
+    t0 = time.perf_counter()
+    for _ in range(n):
+        fn()
+    dt = (time.perf_counter() - t0) / n
+    return dt, n
+
+
+def run_reference(args):
+    """--impl reference: the CPU implementation of the same step on the host cores (rank 0 only)."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    name = args.workload or "cfg1"
+    wl = build_workload(name, 1)
+    cores = os.cpu_count() or 1
+    fn = cpu_step_factory(wl, cores)
+    dt, n = time_cpu(fn, budget_s=150.0, max_steps=max(1, args.steps), warmup=max(1, min(args.warmup, 2)))
+    sps = 1.0 / dt
+    line = {
+        "impl": "reference", "metric": "fwd+bwd+Gram-loss steps/sec @16384 samples", "value": sps, "unit": "steps/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": name, "desc": wl["desc"], "T": wl["T"], "n_layers": wl["NL"], "style_layers": wl["L"],
+                   "gatys": wl["gatys"], "pairs": 1, "weights": "random-init (seed 0)"},
+        "audio_sec_per_sec": sps * wl["T"] / SR,
+        "cpu_baseline": {"value": sps, "unit": "steps/s", "cores": cores, "kind": "port",
+                         "sample": f"{n} full evaluations of the workload timed (of --steps {args.steps}); torch-CPU fp32 "
+                                   "restatement (oracle/torch_step.py); the reference's TF1 graph cannot run on this image"},
+        "e2e": {"value": sps, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from audio_style_transfer_b200.step import StyleStep
+    from audio_style_transfer_b200.sharding import TimeShardedStep
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the B200 step has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    name = args.workload or "cfg1"
+    sharded = name == "cfg2" and world > 1
+    B = args.pairs
+    wl = build_workload(name, B, seed_shift=0 if sharded else rank * B)
+    T, NL, L = wl["T"], wl["NL"], wl["L"]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- contexts + targets (product path) -----------------------------------------------------
+    x_full = torch.as_tensor(wl["x"], device=dev)
+    if sharded:
+        full = StyleStep(T, wl["cont"], wl["style"], wl["gatys"], B=B, precision=args.precision, device=local)
+        full.set_weights(wl["w"])
+        Pc, Ps = gpu_targets(full, torch.as_tensor(wl["content"], device=dev), torch.as_tensor(wl["style_a"], device=dev))
+        full.close()
+
+        def make_ctx(Tw, window):
+            s = StyleStep(Tw, wl["cont"], wl["style"], wl["gatys"], B=B, precision=args.precision, device=local, window=window)
+            s.set_weights(wl["w"])
+            return s
+        ts = TimeShardedStep(T, NL, rank, world, make_ctx, lambda p: dist.all_reduce(p))
+        st = ts.ctx
+        st.set_targets(ts.window(Pc).contiguous(), Ps, wl["lambd"])
+        x = ts.window(x_full).contiguous()
+        own = ts.oe - ts.ob
+        losses = torch.empty((B, 4), device=dev)
+        grad = torch.empty((B, st.T), device=dev)
+
+        def one_step():
+            st.forward_partial(x)
+            dist.all_reduce(st.partials())
+            st.backward(losses, grad)
+        units_per_step = B            # whole-job: one evaluation of B clips per step, all ranks together
+    else:
+        st = StyleStep(T, wl["cont"], wl["style"], wl["gatys"], B=B, precision=args.precision, device=local)
+        st.set_weights(wl["w"])
+        Pc, Ps = gpu_targets(st, torch.as_tensor(wl["content"], device=dev), torch.as_tensor(wl["style_a"], device=dev))
+        st.set_targets(Pc, Ps, wl["lambd"])
+        x = x_full
+        losses = torch.empty((B, 4), device=dev)
+        grad = torch.empty((B, T), device=dev)
+
+        def one_step():
+            st.step_graph(x, losses, grad)
+        units_per_step = B * world    # independent pairs on every rank (weak scaling)
+
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
+
+    def flush_l2():
+        flush.zero_()
+
+    # ---- warm-up, then EXACTLY K timed steps ------------------------------------------------------
+    for _ in range(max(3, args.warmup)):
+        one_step()
+    barrier()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    with ClockSampler(local) as clk:
+        barrier()
+        for a, b in ev:
+            flush_l2()
+            a.record()
+            one_step()
+            b.record()
+        barrier()
+        dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+        # ---- e2e: the same evaluation through HOST float64 buffers (what SciPy calls) ---------------
+        e2e = None
+        if not sharded:
+            xh = wl["x"].astype(np.float64)
+            for _ in range(3):
+                st.step_host(xh)
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                lh, gh = st.step_host(xh)
+            torch.cuda.synchronize()
+            e2e_ms = (time.perf_counter() - t0) * 1e3
+            barrier()
+    tmax = torch.tensor([dev_ms, e2e_ms if not sharded else 0.0], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = float(tmax[0]), float(tmax[1])
+    ms_per_step = dev_ms / args.steps
+    value = units_per_step / (ms_per_step * 1e-3)
+
+    # ---- roofline of the dominant kernel, timed live (CUDA events on the launching stream) -------
+    roof = None
+    phases = None
+    if not sharded:
+        pk = peaks()
+        reps = [st.step_timed(x, losses, grad) for _ in range(8)][3:]
+        phases = [float(np.median([r[i] for r in reps])) for i in range(4)]
+        enc_ms, bwd_ms, gram_ms, tot_ms = phases
+        fl_launch = 2.0 * B * T * 128 * 128 * 4                      # one layer kernel: K=3 conv + 1x1, 2 FLOP/MAC
+        dur_fwd = enc_ms * 1e-3 / NL                                  # average launch duration inside the encoder phase
+        dur_bwd = bwd_ms * 1e-3 / (NL + 1)
+        ach = fl_launch / dur_fwd / 1e12
+        roof = {"bound": "tensor", "kernel": "tc_layer_kernel<fwd>" if args.precision == "bf16" else "layer_f32_kernel<fwd>",
+                "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": ach / pk["tflops"], "traffic": None,
+                "peak_source": pk["src"] + " (bf16 sustained)", "flops_per_launch": fl_launch,
+                "avg_launch_us": dur_fwd * 1e6,
+                "note": "avg = encoder-forward graph phase / n_layers (includes start conv + launch gaps)",
+                "bwd_layer": {"achieved": fl_launch / dur_bwd / 1e12, "avg_launch_us": dur_bwd * 1e6},
+                "phases_ms": {"encoder_fwd": enc_ms, "gram_partials": gram_ms, "heads_bwd": bwd_ms, "total": tot_ms}}
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    flops = algorithmic_flops(T, NL, L, wl["gatys"], B)
+    line = {
+        "metric": "fwd+bwd+Gram-loss steps/sec @16384 samples", "value": value, "unit": "steps/s",
+        "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_per_step,
+        "higher_is_better": True, "scaling": "strong" if sharded else "weak", "vs_baseline": None,
+        "dtype": "bf16 (fwd operands 2-term bf16 split, fp32 accumulate in TMEM)" if args.precision == "bf16" else "f32",
+        "data": "synthetic",
+        "config": {"workload": name, "desc": wl["desc"], "T": T, "n_layers": NL, "style_layers": L, "gatys": wl["gatys"],
+                   "pairs_per_gpu": B, "parallelism": ("time-sharded x%d" % world) if sharded else ("pairs dp%d" % world),
+                   "weights": "random-init (seed 0)", "l2": "flushed between timed steps (256 MiB memset outside the events)",
+                   "graph": "one cudaGraphLaunch per step"},
+        "audio_sec_per_sec": value * T / SR,
+        "algorithmic_gflop_per_step": flops / 1e9,
+        "model_tflops": flops * (1.0 if sharded else world) / (ms_per_step * 1e-3) / 1e12,
+        "gpu_launches": st.launches_per_step * args.steps,
+        "launches_per_step": st.launches_per_step,
+        "clocks": clk.summary(),
+    }
+    if not sharded:
+        line["e2e"] = {"value": units_per_step / (e2e_ms / args.steps * 1e-3), "unit": "steps/s",
+                       "h2d_bytes_per_step": B * T * 4, "d2h_bytes_per_step": (B * T + 4 * B) * 4,
+                       "ms_per_step": e2e_ms / args.steps,
+                       "api": "StyleStep.step_host -> ast_step_host (float64 host in/out, graph replay inside)"}
+    if roof:
+        line["roofline"] = roof
+    if world == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        dt, n = time_cpu(cpu_step_factory(wl, cores), budget_s=15.0, max_steps=20)
+        line["cpu_baseline"] = {"value": 1.0 / dt, "unit": "steps/s", "cores": cores, "kind": "port",
+                                "sample": f"{n} full evaluations of the same workload (torch-CPU fp32 restatement, "
+                                          "oracle/torch_step.py; reference TF1 path unavailable on this image)"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--pairs", type=int, default=1, help="independent pairs per GPU (B)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

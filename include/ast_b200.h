@@ -102,6 +102,11 @@ int  ast_embeds(ast_ctx* ctx, const float* d_x, float* d_Ec, float* d_Gn, void* 
  * Asynchronous on `stream`, no host sync, CUDA-graph capturable. */
 int  ast_step(ast_ctx* ctx, const float* d_x, float* d_losses, float* d_grad, void* stream);
 
+/* ast_step replayed from a captured CUDA graph (north_star (e)): captured on first use for this
+ * (d_x, d_losses, d_grad) pointer triple, re-captured when the pointers change; one
+ * cudaGraphLaunch on `stream` per call. */
+int  ast_step_graph(ast_ctx* ctx, const float* d_x, float* d_losses, float* d_grad, void* stream);
+
 /* The same evaluation through HOST buffers, as SciPy's fun(x)->(f,g) sees it (float64 each way,
  * methods.py:167 / ScipyOptimizerInterface): H2D of x, a replay of the captured CUDA graph of
  * ast_step, D2H of losses and gradient, stream synchronised before return. */
@@ -121,8 +126,9 @@ int  ast_get_extract(ast_ctx* ctx, int32_t layer, float* d_out, void* stream);
 /* Number of kernels one ast_step launches (for bench.py's gpu_launches). */
 int  ast_launches_per_step(const ast_ctx* ctx);
 
-/* Times the dominant kernels of the last ast_step_timed call with CUDA events on `stream`.
- * ms_out[0] = forward layer kernels, [1] = backward layer kernels, [2] = Gram+heads, [3] = total. */
+/* One step as three captured graphs (encoder forward | Gram partials + content SSE | heads + backward)
+ * replayed on `stream` with CUDA events between them.
+ * ms_out[0] = encoder forward, [1] = heads + backward, [2] = Gram partials, [3] = total. */
 int  ast_step_timed(ast_ctx* ctx, const float* d_x, float* d_losses, float* d_grad, void* stream,
                     float* ms_out);
 
