@@ -240,7 +240,7 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
     if (setup_f32_kernels() != 0) { ast_destroy(c); return fail(AST_ECUDA, "cudaFuncSetAttribute failed (is the GPU sm_100?)"); }
     if (c->prec == AST_PREC_BF16) {
         const char* why = nullptr;
-        c->tc = tc_create(c->T, c->B, c->NL, &c->bytes, &why);
+        c->tc = tc_create(c->T, c->B, c->NL, c->H, c->g, c->dF, c->n_head, &c->bytes, &why);
         if (!c->tc) { ast_destroy(c); return fail(AST_ECUDA, "tensor-core path setup failed: %s", why ? why : "?"); }
     }
     if (cudaDeviceSynchronize() != cudaSuccess || cudaGetLastError() != cudaSuccess) { ast_destroy(c); return fail(AST_ECUDA, "context setup failed"); }
@@ -301,8 +301,7 @@ static void run_encoder(ast_ctx* c, const float* d_x, cudaStream_t s) {
     if (c->tc) tc_prepare_input(c->tc, Hl(c, 0), s);
     for (int l = 0; l < c->NL; ++l) {
         if (c->tc) {
-            tc_layer_fwd(c->tc, l, c->bd + (size_t)l * AST_C, c->br + (size_t)l * AST_C, Hl(c, l), Hl(c, l + 1),
-                         zm(c, l), hm(c, l + 1), s);
+            tc_layer_fwd(c->tc, l, c->bd + (size_t)l * AST_C, c->br + (size_t)l * AST_C, zm(c, l), hm(c, l + 1), s);
             continue;
         }
         LayerArgsF32 a;
@@ -378,7 +377,8 @@ extern "C" int ast_step_backward(ast_ctx* c, float* d_losses, float* d_grad, voi
     for (int l = c->NL; l >= 0; --l) {
         const float* dF = (l >= 1 && c->head_buf[l - 1] >= 0) ? dFb(c, c->head_buf[l - 1]) : nullptr;
         if (c->tc) {
-            tc_layer_bwd(c->tc, l, c->g, l < c->NL ? hm(c, l) : nullptr, dF, l >= 1 ? zm(c, l - 1) : nullptr, s);
+            tc_layer_bwd(c->tc, l, l < c->NL ? hm(c, l) : nullptr, (l >= 1) ? c->head_buf[l - 1] : -1,
+                         l >= 1 ? zm(c, l - 1) : nullptr, s);
             continue;
         }
         LayerArgsF32 a;

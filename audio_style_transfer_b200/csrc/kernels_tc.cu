@@ -1,252 +1,165 @@
-// kernels_tc.cu -- the dilated-conv stack on 5th-gen tensor cores: tcgen05.mma with TMEM accumulators,
-// operands staged by TMA (128B swizzle), warp-specialised (TMA producer / MMA issuer / 4 epilogue warps).
-// sm_100a only.  One CTA = one 128-row time tile of one layer, two chained GEMMs:
+// kernels_tc.cu -- the dilated-conv stack on 5th-gen tensor cores (sm_100a only): tcgen05.mma with TMEM
+// accumulators, every operand AND every activation tile moved by TMA (128B swizzle), warp-specialised
+// (warp 0 = TMA producer, warp 1 = MMA issuer, warps 2-5 = epilogue).
+// One CTA = one 128-row time tile of one layer, two chained GEMMs:
 //   forward  (model.py:99-114):  z = conv3_d(relu(h)) + bd ; h' = h + relu(z) Wr + br
 //   backward :  g += conv3_d^T(dz_l) * [h_l>0] + dF ; dz_{l-1} = (g Wr_{l-1}^T) * [z_{l-1}>0]
 // The K=3 dilated conv is an implicit GEMM: three TMA loads of the same activation matrix at row
 // offsets t0-d, t0, t0+d; rows outside [0,T) of the pair are zero-filled by TMA, which IS the
-// reference's per-layer 'SAME' zero padding (masked.py:139).
+// reference's per-layer 'SAME' zero padding (masked.py:139).  A tap whose whole tile is padding is
+// skipped (no load, no MMA).
 // Forward operands are 2-term bf16 splits (x = hi + lo, products hi*hi + lo*hi + hi*lo): plain bf16
-// forward activations flip too many ReLU signs for the <=1e-2 gradient tier.
+// (or fp16 / tf32) forward activations flip too many ReLU signs through 30 layers for the <=1e-2
+// gradient tier (oracle/precision_study.py, DESIGN.md "accuracy tiers").
+// Epilogues never touch global memory row-per-thread: fp32 tiles (residual stream, running gradient,
+// head gradient) arrive by TMA into swizzled smem, are updated in place by the thread that owns the
+// row (= its TMEM lane), and leave by TMA store; only the 16-byte-per-row sign masks use plain
+// (fully coalesced) global accesses.
 #include "tc.cuh"
+#include "ptx.cuh"
 
 #include <cuda.h>
 #include <cudaTypedefs.h>
 
 #include <cstdio>
+#include <cstring>
+
+#define TILE16 16384                            // [128 rows][128 B]: one bf16 K-half or one fp32 32-column group
+static constexpr uint32_t IDESC = umma_idesc_bf16(128, 128);
+
+// barrier block layout (byte offsets from the barrier base)
+#define B_FULL(i)  (8u * (i))
+#define B_EMPTY(i) (16u + 8u * (i))
+#define B_ACC1  32u
+#define B_RT    40u
+#define B_ACC2  48u
+#define B_IO    56u
+#define B_TMEM  64u
+
+__device__ __forceinline__ bool tap_live(int t0, int k, int shift, int T) {
+    const int t = t0 + (k - 1) * shift;
+    return t + 128 > 0 && t < T;
+}
 
 // =============================================================================================
-// PTX wrappers
+// forward layer
 // =============================================================================================
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE_%=;\n\t"
-        "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int x, int y) {
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-                 ::"r"(dst), "l"(map), "r"(bar), "r"(x), "r"(y) : "memory");
-}
-__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int x, int y, int z) {
-    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-                 ::"r"(dst), "l"(map), "r"(bar), "r"(x), "r"(y), "r"(z) : "memory");
-}
-__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
-    asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-
-__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
-}
-// D[tmem] (+)= A[smem] * B[smem], bf16 x bf16 -> fp32, issued by one thread for the CTA
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-}
-// mbarrier arrives once every previously issued tcgen05.mma of this thread has completed
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-// 32 lanes x 32 consecutive fp32 columns: thread i of the warp gets lane (base + i), columns c..c+31
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
-    uint32_t r[32];
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
-          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
-          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-        : "r"(taddr) : "memory");
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-}
-
-// K-major, 128B-swizzled operand tile ([rows][64 bf16], 8-row groups 1024 B apart): the layout TMA
-// writes with CU_TENSOR_MAP_SWIZZLE_128B.  start>>4 | SBO=1024>>4 @32 | version 1 @46 | SWIZZLE_128B (2) @61
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
-    return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)0x40004040u << 32);
-}
-// kind::f16 instruction descriptor: D=f32 (1@4), A=B=bf16 (1@7, 1@10), K-major both, N=128 (16@17), M=128 (8@24)
-#define UMMA_IDESC_BF16_M128_N128 0x08200490u
-
-__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
-    __nv_bfloat162 t = __floats2bfloat162_rn(a, b);      // .x = a (low half), .y = b
-    return *reinterpret_cast<uint32_t*>(&t);
-}
-__device__ __forceinline__ float bf16_round(float a) { return __bfloat162float(__float2bfloat16_rn(a)); }
-
-// =============================================================================================
-// the layer kernel
-// =============================================================================================
-struct alignas(64) TcArgs {
-    CUtensorMap tmA0;          // fwd: bf16 hi of relu(h) [B][T][128];  bwd: bf16 dz_l
-    CUtensorMap tmA1;          // fwd: bf16 lo of relu(h);              bwd: unused
-    CUtensorMap tmW1;          // conv weights, rows of 128 k-contiguous bf16 (see tc_set_weights)
-    CUtensorMap tmW2;          // 1x1 weights
-    int w1_row, w2_row;        // first row of this layer's block in tmW1 / tmW2
-    int T, shift;              // rows per pair; tap k reads row t + (k-1)*shift
-    int do_gemm1, do_gemm2, g_init;
-    // forward
-    const float* bias1; const float* bias2; const float* Hin; float* Hout;
+struct alignas(64) FwdArgs {
+    CUtensorMap tmA_hi, tmA_lo;      // loads: relu(h) hi / lo, bf16 [2][B][T][128], box {64,128,1,1}
+    CUtensorMap tmAo_hi, tmAo_lo;    // stores: same buffers, box {64,32,1,1}
+    CUtensorMap tmH_ld, tmH_st;      // fp32 residual stream [NL+1][B][T][128]: box {32,128,1,1} / {32,32,1,1}
+    CUtensorMap tmW1, tmW2;          // weight operands, rows of 128 k-contiguous bf16, box {64,128}
+    int w1_row, w2_row;              // first row of this layer's block in tmW1 / tmW2
+    int T, shift, l, a_in, a_out;    // rows per pair; dilation; layer; ping-pong indices of the bf16 operand buffers
+    const float* bias1; const float* bias2;
     uint32_t* zmask_out; uint32_t* hmask_out;
-    __nv_bfloat16* a_hi_out; __nv_bfloat16* a_lo_out;
-    // backward
-    float* g; const uint32_t* hmask_in; const float* dF; const uint32_t* zmask_in; __nv_bfloat16* dz_out;
 };
+// smem: stage 0 | stage 1 (64 KB each: A_hi, A_lo, W_hi, W_lo x [128][64] bf16) | RT (64 KB: relu(z) hi/lo, 2 K-halves)
+// After GEMM1 the A half of each stage receives two 32-column groups of the fp32 H tile (the residual
+// input), updated in place to H' and stored from there; RT is reused to stage relu(H') hi/lo.
+#define FWD_STAGE 65536
+#define FWD_SMEM (2 * FWD_STAGE + 65536 + 1024 + 128)
 
-#define TC_TILE_BYTES 16384                     // [128 rows][64 bf16], 128B swizzle
-template <bool BWD> struct TcCfg {
-    static constexpr int NPART = BWD ? 1 : 2;                          // hi/lo operand parts
-    static constexpr int NS = BWD ? 4 : 2;                             // pipeline stages
-    static constexpr int STAGE = 2 * NPART * TC_TILE_BYTES;            // A parts + W parts
-    static constexpr int RT = 2 * NPART * TC_TILE_BYTES;               // GEMM2 A operand: 2 K-halves x parts
-    static constexpr int SMEM = NS * STAGE + RT + 1024 /*align*/ + 256 /*barriers*/;
-};
-
-// swizzled byte offset of the 16-byte chunk holding columns [8*chunk, 8*chunk+8) of row r in a K-half tile
-__device__ __forceinline__ uint32_t sw128_off(int r, int chunk) { return (uint32_t)(r * 128 + ((chunk ^ (r & 7)) << 4)); }
-
-template <bool BWD>
-__global__ void __launch_bounds__(192, 1) tc_layer_kernel(const __grid_constant__ TcArgs p) {
-    using Cfg = TcCfg<BWD>;
-    constexpr int NP = Cfg::NPART, NS = Cfg::NS;
+__global__ void __launch_bounds__(192, 1) tc_fwd_kernel(const __grid_constant__ FwdArgs p) {
     extern __shared__ uint8_t tc_smem_raw[];
     const uint32_t base = (smem_u32(tc_smem_raw) + 1023u) & ~1023u;
-    const uint32_t s_stage = base;
-    const uint32_t s_rt = base + NS * Cfg::STAGE;
-    const uint32_t s_bar = s_rt + Cfg::RT;
-    // barriers: full[NS], empty[NS], acc1_full, r_ready, acc2_full, then the TMEM base word
-    const uint32_t b_full = s_bar, b_empty = s_bar + 8 * NS;
-    const uint32_t b_acc1 = s_bar + 16 * NS, b_rready = b_acc1 + 8, b_acc2 = b_acc1 + 16, s_tmem = b_acc1 + 24;
-    uint8_t* gen_base = tc_smem_raw + (base - smem_u32(tc_smem_raw));      // generic pointer to `base`
-
+    uint8_t* gen = tc_smem_raw + (base - smem_u32(tc_smem_raw));          // generic pointer to `base`
+    const uint32_t s_rt = base + 2 * FWD_STAGE, bar = s_rt + 65536;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int row0 = blockIdx.x * 128;
     const int b = row0 / p.T, t0 = row0 - b * p.T;
 
     if (warp == 0 && lane == 0) {
-        tma_prefetch_desc(&p.tmA0); tma_prefetch_desc(&p.tmW1); tma_prefetch_desc(&p.tmW2);
-        if (!BWD) tma_prefetch_desc(&p.tmA1);
-        for (int i = 0; i < NS; ++i) { mbar_init(b_full + 8 * i, 1); mbar_init(b_empty + 8 * i, 1); }
-        mbar_init(b_acc1, 1); mbar_init(b_rready, 128); mbar_init(b_acc2, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        tma_prefetch_desc(&p.tmA_hi); tma_prefetch_desc(&p.tmA_lo); tma_prefetch_desc(&p.tmW1); tma_prefetch_desc(&p.tmW2);
+        tma_prefetch_desc(&p.tmH_ld); tma_prefetch_desc(&p.tmH_st); tma_prefetch_desc(&p.tmAo_hi); tma_prefetch_desc(&p.tmAo_lo);
+        for (int i = 0; i < 2; ++i) { mbar_init(bar + B_FULL(i), 1); mbar_init(bar + B_EMPTY(i), 1); }
+        mbar_init(bar + B_ACC1, 1); mbar_init(bar + B_RT, 128); mbar_init(bar + B_ACC2, 1);
+        mbar_init_fence();
     }
-    if (warp == 1) tmem_alloc(s_tmem, 256);
+    if (warp == 1) tmem_alloc<256>(bar + B_TMEM);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gen_base + (s_tmem - base));
+    const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gen + (bar + B_TMEM - base));
     const uint32_t acc1 = tmem, acc2 = tmem + 128;
 
     if (warp == 0) {
         // ================================ TMA producer ========================================
         if (lane == 0) {
             int it = 0;
-            if (p.do_gemm1) {
-                for (int k = 0; k < 3; ++k) {
-                    const int t = t0 + (k - 1) * p.shift;
-                    for (int j = 0; j < 2; ++j, ++it) {
-                        const int slot = it % NS;
-                        mbar_wait(b_empty + 8 * slot, ((it / NS) & 1) ^ 1);
-                        const uint32_t st = s_stage + slot * Cfg::STAGE, fb = b_full + 8 * slot;
-                        mbar_expect_tx(fb, Cfg::STAGE);
-                        tma_load_3d(st, &p.tmA0, fb, j * 64, t, b);
-                        if (!BWD) tma_load_3d(st + TC_TILE_BYTES, &p.tmA1, fb, j * 64, t, b);
-                        for (int part = 0; part < NP; ++part)
-                            tma_load_2d(st + (NP + part) * TC_TILE_BYTES, &p.tmW1, fb, j * 64, p.w1_row + (k * NP + part) * 128);
-                    }
+            for (int k = 0; k < 3; ++k) {
+                if (!tap_live(t0, k, p.shift, p.T)) continue;
+                const int t = t0 + (k - 1) * p.shift;
+                for (int j = 0; j < 2; ++j, ++it) {
+                    const int slot = it & 1;
+                    mbar_wait(bar + B_EMPTY(slot), ((it >> 1) & 1) ^ 1);
+                    const uint32_t st = base + slot * FWD_STAGE, fb = bar + B_FULL(slot);
+                    mbar_expect_tx(fb, 4 * TILE16);
+                    tma_load_4d(st, &p.tmA_hi, fb, j * 64, t, b, p.a_in);
+                    tma_load_4d(st + TILE16, &p.tmA_lo, fb, j * 64, t, b, p.a_in);
+                    tma_load_2d(st + 2 * TILE16, &p.tmW1, fb, j * 64, p.w1_row + (k * 2 + 0) * 128);
+                    tma_load_2d(st + 3 * TILE16, &p.tmW1, fb, j * 64, p.w1_row + (k * 2 + 1) * 128);
                 }
             }
-            if (p.do_gemm2) {
-                for (int j = 0; j < 2; ++j, ++it) {
-                    const int slot = it % NS;
-                    mbar_wait(b_empty + 8 * slot, ((it / NS) & 1) ^ 1);
-                    const uint32_t st = s_stage + slot * Cfg::STAGE, fb = b_full + 8 * slot;
-                    mbar_expect_tx(fb, NP * TC_TILE_BYTES);
-                    for (int part = 0; part < NP; ++part)
-                        tma_load_2d(st + (NP + part) * TC_TILE_BYTES, &p.tmW2, fb, j * 64, p.w2_row + part * 128);
-                }
+            // 1x1 weights (K-half j) + two column groups of the fp32 residual tile per stage
+            for (int j = 0; j < 2; ++j, ++it) {
+                const int slot = it & 1;
+                mbar_wait(bar + B_EMPTY(slot), ((it >> 1) & 1) ^ 1);
+                const uint32_t st = base + slot * FWD_STAGE, fb = bar + B_FULL(slot);
+                mbar_expect_tx(fb, 4 * TILE16);
+                tma_load_2d(st + 2 * TILE16, &p.tmW2, fb, j * 64, p.w2_row);
+                tma_load_2d(st + 3 * TILE16, &p.tmW2, fb, j * 64, p.w2_row + 128);
+                tma_load_4d(st, &p.tmH_ld, fb, (2 * slot) * 32, t0, b, p.l);
+                tma_load_4d(st + TILE16, &p.tmH_ld, fb, (2 * slot + 1) * 32, t0, b, p.l);
             }
         }
     } else if (warp == 1) {
         // ================================ MMA issuer ==========================================
         if (lane == 0) {
             int it = 0;
-            if (p.do_gemm1) {
-                for (int s = 0; s < 6; ++s, ++it) {
-                    const int slot = it % NS;
-                    mbar_wait(b_full + 8 * slot, (it / NS) & 1);
-                    tc_fence_after();
-                    const uint32_t st = s_stage + slot * Cfg::STAGE;
-#pragma unroll
-                    for (int kk = 0; kk < 4; ++kk) {
-                        const uint64_t a_hi = umma_desc_sw128(st + kk * 32);
-                        const uint64_t w_hi = umma_desc_sw128(st + NP * TC_TILE_BYTES + kk * 32);
-                        umma_bf16(acc1, a_hi, w_hi, UMMA_IDESC_BF16_M128_N128, (s > 0 || kk > 0) ? 1u : 0u);
-                        if (!BWD) {
-                            const uint64_t a_lo = umma_desc_sw128(st + TC_TILE_BYTES + kk * 32);
-                            const uint64_t w_lo = umma_desc_sw128(st + 3 * TC_TILE_BYTES + kk * 32);
-                            umma_bf16(acc1, a_lo, w_hi, UMMA_IDESC_BF16_M128_N128, 1u);
-                            umma_bf16(acc1, a_hi, w_lo, UMMA_IDESC_BF16_M128_N128, 1u);
-                        }
-                    }
-                    umma_commit(b_empty + 8 * slot);
-                }
-                umma_commit(b_acc1);
-            }
-            if (p.do_gemm2) {
-                mbar_wait(b_rready, 0);
-                tc_fence_after();
+            uint32_t accum = 0;
+            for (int k = 0; k < 3; ++k) {
+                if (!tap_live(t0, k, p.shift, p.T)) continue;
                 for (int j = 0; j < 2; ++j, ++it) {
-                    const int slot = it % NS;
-                    mbar_wait(b_full + 8 * slot, (it / NS) & 1);
+                    const int slot = it & 1;
+                    mbar_wait(bar + B_FULL(slot), (it >> 1) & 1);
                     tc_fence_after();
-                    const uint32_t st = s_stage + slot * Cfg::STAGE;
-                    const uint32_t ra = s_rt + j * NP * TC_TILE_BYTES;      // [K-half j][part]
+                    const uint32_t st = base + slot * FWD_STAGE;
 #pragma unroll
                     for (int kk = 0; kk < 4; ++kk) {
-                        const uint64_t a_hi = umma_desc_sw128(ra + kk * 32);
-                        const uint64_t w_hi = umma_desc_sw128(st + NP * TC_TILE_BYTES + kk * 32);
-                        umma_bf16(acc2, a_hi, w_hi, UMMA_IDESC_BF16_M128_N128, (j > 0 || kk > 0) ? 1u : 0u);
-                        if (!BWD) {
-                            const uint64_t a_lo = umma_desc_sw128(ra + TC_TILE_BYTES + kk * 32);
-                            const uint64_t w_lo = umma_desc_sw128(st + 3 * TC_TILE_BYTES + kk * 32);
-                            umma_bf16(acc2, a_lo, w_hi, UMMA_IDESC_BF16_M128_N128, 1u);
-                            umma_bf16(acc2, a_hi, w_lo, UMMA_IDESC_BF16_M128_N128, 1u);
-                        }
+                        const uint64_t a_hi = umma_desc_kmajor_sw128(st + kk * 32);
+                        const uint64_t a_lo = umma_desc_kmajor_sw128(st + TILE16 + kk * 32);
+                        const uint64_t w_hi = umma_desc_kmajor_sw128(st + 2 * TILE16 + kk * 32);
+                        const uint64_t w_lo = umma_desc_kmajor_sw128(st + 3 * TILE16 + kk * 32);
+                        umma_f16(acc1, a_hi, w_hi, IDESC, accum);
+                        umma_f16(acc1, a_lo, w_hi, IDESC, 1u);
+                        umma_f16(acc1, a_hi, w_lo, IDESC, 1u);
+                        accum = 1u;
                     }
-                    umma_commit(b_empty + 8 * slot);
+                    umma_commit(bar + B_EMPTY(slot));
                 }
-                umma_commit(b_acc2);
             }
+            umma_commit(bar + B_ACC1);
+            mbar_wait(bar + B_RT, 0);
+            tc_fence_after();
+            for (int j = 0; j < 2; ++j, ++it) {
+                const int slot = it & 1;
+                mbar_wait(bar + B_FULL(slot), (it >> 1) & 1);
+                tc_fence_after();
+                const uint32_t st = base + slot * FWD_STAGE;
+                const uint32_t ra = s_rt + j * 2 * TILE16;                  // [K-half j][hi, lo]
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk) {
+                    const uint64_t a_hi = umma_desc_kmajor_sw128(ra + kk * 32);
+                    const uint64_t a_lo = umma_desc_kmajor_sw128(ra + TILE16 + kk * 32);
+                    const uint64_t w_hi = umma_desc_kmajor_sw128(st + 2 * TILE16 + kk * 32);
+                    const uint64_t w_lo = umma_desc_kmajor_sw128(st + 3 * TILE16 + kk * 32);
+                    umma_f16(acc2, a_hi, w_hi, IDESC, (j > 0 || kk > 0) ? 1u : 0u);
+                    umma_f16(acc2, a_lo, w_hi, IDESC, 1u);
+                    umma_f16(acc2, a_hi, w_lo, IDESC, 1u);
+                }
+            }
+            umma_commit(bar + B_ACC2);
         }
         __syncwarp();
     } else {
@@ -255,126 +168,325 @@ __global__ void __launch_bounds__(192, 1) tc_layer_kernel(const __grid_constant_
         const int r = q * 32 + lane;                              // row within the tile = TMEM lane
         const size_t row = (size_t)row0 + r;
         const uint32_t lane_off = (uint32_t)(q * 32) << 16;
-        uint8_t* rt = gen_base + (s_rt - base);
+        uint8_t* rt = gen + (s_rt - base);
         float v[32];
-
-        // ---- epilogue 1: accumulator 1 -> A operand of GEMM2 (smem, swizzled) -----------------
-        if (p.do_gemm1) { mbar_wait(b_acc1, 0); tc_fence_after(); }
         uint32_t mw[4];
-        if (BWD && p.do_gemm1) { const uint4 m = *reinterpret_cast<const uint4*>(p.hmask_in + row * AST_MW); mw[0] = m.x; mw[1] = m.y; mw[2] = m.z; mw[3] = m.w; }
+
+        // ---- epilogue 1: z = acc1 + bd -> sign mask, relu(z) hi/lo -> A operand of the 1x1 GEMM ----
+        mbar_wait(bar + B_ACC1, 0);
+        tc_fence_after();
 #pragma unroll
         for (int cc = 0; cc < 4; ++cc) {
-            if (p.do_gemm1) tmem_ld32(acc1 + lane_off + cc * 32, v);
-            else {
+            tmem_ld32(acc1 + lane_off + cc * 32, v);
+            uint32_t word = 0;
 #pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] = 0.f;
+            for (int i = 0; i < 32; ++i) {
+                v[i] += __ldg(p.bias1 + cc * 32 + i);
+                word |= (v[i] > 0.f ? 1u : 0u) << i;
+                v[i] = fmaxf(v[i], 0.f);
             }
-            if (!BWD) {
-                uint32_t word = 0;
+            mw[cc] = word;
+            uint8_t* half = rt + (cc >> 1) * 2 * TILE16;
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    v[i] += __ldg(p.bias1 + cc * 32 + i);
-                    word |= (v[i] > 0.f ? 1u : 0u) << i;
-                    v[i] = fmaxf(v[i], 0.f);
-                }
-                mw[cc] = word;
-            } else {
-                float* grow = p.g + row * AST_C + cc * 32;
-                if (p.do_gemm1) {
+            for (int i = 0; i < 4; ++i) {
+                const uint32_t off = sw128_off(r, (cc & 1) * 4 + i);
+                float hi[8];
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) if (!((mw[cc] >> i) & 1u)) v[i] = 0.f;
-                }
-                if (!p.g_init) {
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const float4 t = reinterpret_cast<const float4*>(grow)[i];
-                        v[4 * i] += t.x; v[4 * i + 1] += t.y; v[4 * i + 2] += t.z; v[4 * i + 3] += t.w;
-                    }
-                }
-                if (p.dF != nullptr) {
-                    const float4* f = reinterpret_cast<const float4*>(p.dF + row * AST_C + cc * 32);
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const float4 t = f[i];
-                        v[4 * i] += t.x; v[4 * i + 1] += t.y; v[4 * i + 2] += t.z; v[4 * i + 3] += t.w;
-                    }
-                }
-#pragma unroll
-                for (int i = 0; i < 8; ++i)
-                    reinterpret_cast<float4*>(grow)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-            }
-            if (p.do_gemm2) {
-                uint8_t* half = rt + (cc >> 1) * NP * TC_TILE_BYTES;
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const uint32_t off = sw128_off(r, (cc & 1) * 4 + i);
-                    float hi[8];
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) hi[e] = bf16_round(v[8 * i + e]);
-                    *reinterpret_cast<uint4*>(half + off) = make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]),
-                                                                      pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
-                    if (!BWD)
-                        *reinterpret_cast<uint4*>(half + TC_TILE_BYTES + off) =
-                            make_uint4(pack_bf16(v[8 * i] - hi[0], v[8 * i + 1] - hi[1]), pack_bf16(v[8 * i + 2] - hi[2], v[8 * i + 3] - hi[3]),
-                                       pack_bf16(v[8 * i + 4] - hi[4], v[8 * i + 5] - hi[5]), pack_bf16(v[8 * i + 6] - hi[6], v[8 * i + 7] - hi[7]));
-                }
+                for (int e = 0; e < 8; ++e) hi[e] = bf16_round(v[8 * i + e]);
+                *reinterpret_cast<uint4*>(half + off) = make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]),
+                                                                  pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
+                *reinterpret_cast<uint4*>(half + TILE16 + off) =
+                    make_uint4(pack_bf16(v[8 * i] - hi[0], v[8 * i + 1] - hi[1]), pack_bf16(v[8 * i + 2] - hi[2], v[8 * i + 3] - hi[3]),
+                               pack_bf16(v[8 * i + 4] - hi[4], v[8 * i + 5] - hi[5]), pack_bf16(v[8 * i + 6] - hi[6], v[8 * i + 7] - hi[7]));
             }
         }
-        if (!BWD) *reinterpret_cast<uint4*>(p.zmask_out + row * AST_MW) = make_uint4(mw[0], mw[1], mw[2], mw[3]);
-        if (p.do_gemm2) {
-            fence_proxy_async_smem();          // generic-proxy smem writes -> visible to the tensor core (async proxy)
-            tc_fence_before();
-            mbar_arrive(b_rready);
+        fence_proxy_async_smem();
+        tc_fence_before();
+        mbar_arrive(bar + B_RT);
+        *reinterpret_cast<uint4*>(p.zmask_out + row * AST_MW) = make_uint4(mw[0], mw[1], mw[2], mw[3]);
 
-            // ---- epilogue 2 ----------------------------------------------------------------------
-            mbar_wait(b_acc2, 0);
-            tc_fence_after();
-            if (BWD) { const uint4 m = *reinterpret_cast<const uint4*>(p.zmask_in + row * AST_MW); mw[0] = m.x; mw[1] = m.y; mw[2] = m.z; mw[3] = m.w; }
-#pragma unroll
-            for (int cc = 0; cc < 4; ++cc) {
-                tmem_ld32(acc2 + lane_off + cc * 32, v);
-                if (!BWD) {
-                    const float4* hin = reinterpret_cast<const float4*>(p.Hin + row * AST_C + cc * 32);
-                    float4* hout = reinterpret_cast<float4*>(p.Hout + row * AST_C + cc * 32);
-                    uint32_t word = 0;
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const float4 h = hin[i];
-                        const float4 bb = __ldg(reinterpret_cast<const float4*>(p.bias2 + cc * 32) + i);
-                        v[4 * i] = h.x + (v[4 * i] + bb.x); v[4 * i + 1] = h.y + (v[4 * i + 1] + bb.y);
-                        v[4 * i + 2] = h.z + (v[4 * i + 2] + bb.z); v[4 * i + 3] = h.w + (v[4 * i + 3] + bb.w);
-                        hout[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-                    }
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) { word |= (v[i] > 0.f ? 1u : 0u) << i; v[i] = fmaxf(v[i], 0.f); }
-                    mw[cc] = word;
-                    uint4* oh = reinterpret_cast<uint4*>(p.a_hi_out + row * AST_C + cc * 32);
-                    uint4* ol = reinterpret_cast<uint4*>(p.a_lo_out + row * AST_C + cc * 32);
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        float hi[8];
-#pragma unroll
-                        for (int e = 0; e < 8; ++e) hi[e] = bf16_round(v[8 * i + e]);
-                        oh[i] = make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]), pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
-                        ol[i] = make_uint4(pack_bf16(v[8 * i] - hi[0], v[8 * i + 1] - hi[1]), pack_bf16(v[8 * i + 2] - hi[2], v[8 * i + 3] - hi[3]),
-                                           pack_bf16(v[8 * i + 4] - hi[4], v[8 * i + 5] - hi[5]), pack_bf16(v[8 * i + 6] - hi[6], v[8 * i + 7] - hi[7]));
-                    }
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) if (!((mw[cc] >> i) & 1u)) v[i] = 0.f;
-                    uint4* o = reinterpret_cast<uint4*>(p.dz_out + row * AST_C + cc * 32);
-#pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        o[i] = make_uint4(pack_bf16(v[8 * i], v[8 * i + 1]), pack_bf16(v[8 * i + 2], v[8 * i + 3]),
-                                          pack_bf16(v[8 * i + 4], v[8 * i + 5]), pack_bf16(v[8 * i + 6], v[8 * i + 7]));
-                }
-            }
-            if (!BWD) *reinterpret_cast<uint4*>(p.hmask_out + row * AST_MW) = make_uint4(mw[0], mw[1], mw[2], mw[3]);
+        // ---- epilogue 2: h' = h + (acc2 + br) in place in smem; relu(h') hi/lo -> RT; masks ---------
+        mbar_wait(bar + B_ACC2, 0);
+        tc_fence_after();
+        {   // residual tile landed: the last fill of each stage (fill index = number of live taps)
+            const uint32_t par = (uint32_t)(tap_live(t0, 0, p.shift, p.T) + 1 + tap_live(t0, 2, p.shift, p.T)) & 1u;
+            mbar_wait(bar + B_FULL(0), par);
+            mbar_wait(bar + B_FULL(1), par);
         }
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+            tmem_ld32(acc2 + lane_off + cc * 32, v);
+            uint8_t* hcg = gen + (cc >> 1) * FWD_STAGE + (cc & 1) * TILE16;      // fp32 column group cc
+            uint32_t word = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                float4* hp = reinterpret_cast<float4*>(hcg + sw128_off(r, i));
+                const float4 h = *hp;
+                const float4 bb = __ldg(reinterpret_cast<const float4*>(p.bias2 + cc * 32) + i);
+                // h' = h + (r Wr + br): same association as the reference (model.py:109-114)
+                v[4 * i] = h.x + (v[4 * i] + bb.x); v[4 * i + 1] = h.y + (v[4 * i + 1] + bb.y);
+                v[4 * i + 2] = h.z + (v[4 * i + 2] + bb.z); v[4 * i + 3] = h.w + (v[4 * i + 3] + bb.w);
+                *hp = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+            }
+#pragma unroll
+            for (int i = 0; i < 32; ++i) { word |= (v[i] > 0.f ? 1u : 0u) << i; v[i] = fmaxf(v[i], 0.f); }
+            mw[cc] = word;
+            uint8_t* half = rt + (cc >> 1) * 2 * TILE16;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const uint32_t off = sw128_off(r, (cc & 1) * 4 + i);
+                float hi[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) hi[e] = bf16_round(v[8 * i + e]);
+                *reinterpret_cast<uint4*>(half + off) = make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]),
+                                                                  pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
+                *reinterpret_cast<uint4*>(half + TILE16 + off) =
+                    make_uint4(pack_bf16(v[8 * i] - hi[0], v[8 * i + 1] - hi[1]), pack_bf16(v[8 * i + 2] - hi[2], v[8 * i + 3] - hi[3]),
+                               pack_bf16(v[8 * i + 4] - hi[4], v[8 * i + 5] - hi[5]), pack_bf16(v[8 * i + 6] - hi[6], v[8 * i + 7] - hi[7]));
+            }
+        }
+        *reinterpret_cast<uint4*>(p.hmask_out + row * AST_MW) = make_uint4(mw[0], mw[1], mw[2], mw[3]);
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {                                           // this warp's 32-row slab of every output tile
+            const int tr = t0 + q * 32;
+            const uint32_t slab = (uint32_t)q * 4096;
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc)
+                tma_store_4d(&p.tmH_st, base + (cc >> 1) * FWD_STAGE + (cc & 1) * TILE16 + slab, cc * 32, tr, b, p.l + 1);
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                tma_store_4d(&p.tmAo_hi, s_rt + j * 2 * TILE16 + slab, j * 64, tr, b, p.a_out);
+                tma_store_4d(&p.tmAo_lo, s_rt + j * 2 * TILE16 + TILE16 + slab, j * 64, tr, b, p.a_out);
+            }
+            tma_store_commit();
+            tma_store_wait_all();
+        }
+        __syncwarp();
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) tmem_dealloc(tmem, 256);
+    if (warp == 1) tmem_dealloc<256>(tmem);
+}
+
+// =============================================================================================
+// backward boundary l (between layer l-1 and layer l), plain bf16 operands
+// =============================================================================================
+struct alignas(64) BwdArgs {
+    CUtensorMap tmDz_ld, tmDz_st;    // bf16 dz ping-pong [2][B][T][128]: box {64,128,1,1} / {64,32,1,1}
+    CUtensorMap tmG_ld, tmG_st;      // fp32 running gradient [1][B][T][128]: box {32,128,1,1} / {32,32,1,1}
+    CUtensorMap tmDF_ld;             // fp32 head gradients [n_head][B][T][128], box {32,128,1,1}
+    CUtensorMap tmW1, tmW2;
+    int w1_row, w2_row;
+    int T, shift;                    // tap k reads dz row t + (k-1)*shift, shift = -d
+    int do_gemm1, do_gemm2, g_init, df_idx;      // df_idx < 0: no head gradient at this boundary
+    int dz_in, dz_out;
+    const uint32_t* hmask_in; const uint32_t* zmask_in;
+};
+// smem: 2 stages x (A 16 KB | W 16 KB) | RT 32 KB (bf16 g, 2 K-halves) | G 64 KB (fp32, in place) | DF 64 KB
+#define BWD_STAGE 32768
+#define BWD_RT (2 * BWD_STAGE)
+#define BWD_G (BWD_RT + 32768)
+#define BWD_DF (BWD_G + 65536)
+#define BWD_SMEM (BWD_DF + 65536 + 1024 + 128)
+
+__global__ void __launch_bounds__(192, 1) tc_bwd_kernel(const __grid_constant__ BwdArgs p) {
+    extern __shared__ uint8_t tc_smem_raw[];
+    const uint32_t base = (smem_u32(tc_smem_raw) + 1023u) & ~1023u;
+    uint8_t* gen = tc_smem_raw + (base - smem_u32(tc_smem_raw));
+    const uint32_t s_rt = base + BWD_RT, s_g = base + BWD_G, s_df = base + BWD_DF, bar = s_df + 65536;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int row0 = blockIdx.x * 128;
+    const int b = row0 / p.T, t0 = row0 - b * p.T;
+    const bool has_io = !p.g_init || p.df_idx >= 0;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&p.tmDz_ld); tma_prefetch_desc(&p.tmW1); tma_prefetch_desc(&p.tmW2); tma_prefetch_desc(&p.tmG_ld);
+        tma_prefetch_desc(&p.tmG_st); tma_prefetch_desc(&p.tmDF_ld); tma_prefetch_desc(&p.tmDz_st);
+        for (int i = 0; i < 2; ++i) { mbar_init(bar + B_FULL(i), 1); mbar_init(bar + B_EMPTY(i), 1); }
+        mbar_init(bar + B_ACC1, 1); mbar_init(bar + B_RT, 128); mbar_init(bar + B_ACC2, 1); mbar_init(bar + B_IO, 1);
+        mbar_init_fence();
+    }
+    if (warp == 1) tmem_alloc<256>(bar + B_TMEM);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gen + (bar + B_TMEM - base));
+    const uint32_t acc1 = tmem, acc2 = tmem + 128;
+
+    if (warp == 0) {
+        // ================================ TMA producer ========================================
+        if (lane == 0) {
+            int it = 0;
+            bool io_sent = !has_io;
+            auto send_io = [&]() {
+                if (io_sent) return;
+                io_sent = true;
+                mbar_expect_tx(bar + B_IO, (uint32_t)((p.g_init ? 0 : 4) + (p.df_idx >= 0 ? 4 : 0)) * TILE16);
+                if (!p.g_init)
+                    for (int cg = 0; cg < 4; ++cg) tma_load_4d(s_g + cg * TILE16, &p.tmG_ld, bar + B_IO, cg * 32, t0, b, 0);
+                if (p.df_idx >= 0)
+                    for (int cg = 0; cg < 4; ++cg) tma_load_4d(s_df + cg * TILE16, &p.tmDF_ld, bar + B_IO, cg * 32, t0, b, p.df_idx);
+            };
+            if (p.do_gemm1) {
+                for (int k = 0; k < 3; ++k) {
+                    if (!tap_live(t0, k, p.shift, p.T)) continue;
+                    const int t = t0 + (k - 1) * p.shift;
+                    for (int j = 0; j < 2; ++j, ++it) {
+                        const int slot = it & 1;
+                        if (it == 2) send_io();          // after the first two operand stages are in flight
+                        mbar_wait(bar + B_EMPTY(slot), ((it >> 1) & 1) ^ 1);
+                        const uint32_t st = base + slot * BWD_STAGE, fb = bar + B_FULL(slot);
+                        mbar_expect_tx(fb, 2 * TILE16);
+                        tma_load_4d(st, &p.tmDz_ld, fb, j * 64, t, b, p.dz_in);
+                        tma_load_2d(st + TILE16, &p.tmW1, fb, j * 64, p.w1_row + k * 128);
+                    }
+                }
+            }
+            send_io();
+            if (p.do_gemm2) {
+                for (int j = 0; j < 2; ++j, ++it) {
+                    const int slot = it & 1;
+                    mbar_wait(bar + B_EMPTY(slot), ((it >> 1) & 1) ^ 1);
+                    const uint32_t st = base + slot * BWD_STAGE, fb = bar + B_FULL(slot);
+                    mbar_expect_tx(fb, TILE16);
+                    tma_load_2d(st + TILE16, &p.tmW2, fb, j * 64, p.w2_row);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================================ MMA issuer ==========================================
+        if (lane == 0) {
+            int it = 0;
+            if (p.do_gemm1) {
+                uint32_t accum = 0;
+                for (int k = 0; k < 3; ++k) {
+                    if (!tap_live(t0, k, p.shift, p.T)) continue;
+                    for (int j = 0; j < 2; ++j, ++it) {
+                        const int slot = it & 1;
+                        mbar_wait(bar + B_FULL(slot), (it >> 1) & 1);
+                        tc_fence_after();
+                        const uint32_t st = base + slot * BWD_STAGE;
+#pragma unroll
+                        for (int kk = 0; kk < 4; ++kk) {
+                            umma_f16(acc1, umma_desc_kmajor_sw128(st + kk * 32), umma_desc_kmajor_sw128(st + TILE16 + kk * 32), IDESC, accum);
+                            accum = 1u;
+                        }
+                        umma_commit(bar + B_EMPTY(slot));
+                    }
+                }
+                umma_commit(bar + B_ACC1);
+            }
+            if (p.do_gemm2) {
+                mbar_wait(bar + B_RT, 0);
+                tc_fence_after();
+                for (int j = 0; j < 2; ++j, ++it) {
+                    const int slot = it & 1;
+                    mbar_wait(bar + B_FULL(slot), (it >> 1) & 1);
+                    tc_fence_after();
+                    const uint32_t st = base + slot * BWD_STAGE;
+#pragma unroll
+                    for (int kk = 0; kk < 4; ++kk)
+                        umma_f16(acc2, umma_desc_kmajor_sw128(s_rt + j * TILE16 + kk * 32),
+                                 umma_desc_kmajor_sw128(st + TILE16 + kk * 32), IDESC, (j > 0 || kk > 0) ? 1u : 0u);
+                }
+                umma_commit(bar + B_ACC2);
+            }
+        }
+        __syncwarp();
+    } else {
+        // ================================ epilogue warps ======================================
+        const int q = warp & 3;
+        const int r = q * 32 + lane;
+        const size_t row = (size_t)row0 + r;
+        const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+        const int tr = t0 + q * 32;
+        const uint32_t slab = (uint32_t)q * 4096;
+        float v[32];
+        uint32_t mw[4] = {0, 0, 0, 0};
+
+        // ---- epilogue 1: g' = g + acc1 * [h>0] + dF, in place in smem -> TMA store; bf16(g') -> RT ----
+        if (p.do_gemm1) {
+            const uint4 m = *reinterpret_cast<const uint4*>(p.hmask_in + row * AST_MW);
+            mw[0] = m.x; mw[1] = m.y; mw[2] = m.z; mw[3] = m.w;
+            mbar_wait(bar + B_ACC1, 0);
+            tc_fence_after();
+        }
+        if (has_io) mbar_wait(bar + B_IO, 0);
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+            if (p.do_gemm1) {
+                tmem_ld32(acc1 + lane_off + cc * 32, v);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) if (!((mw[cc] >> i) & 1u)) v[i] = 0.f;
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = 0.f;
+            }
+            uint8_t* gcg = gen + BWD_G + cc * TILE16;
+            const uint8_t* dcg = gen + BWD_DF + cc * TILE16;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const uint32_t off = sw128_off(r, i);
+                if (!p.g_init) {
+                    const float4 t = *reinterpret_cast<const float4*>(gcg + off);
+                    v[4 * i] += t.x; v[4 * i + 1] += t.y; v[4 * i + 2] += t.z; v[4 * i + 3] += t.w;
+                }
+                if (p.df_idx >= 0) {
+                    const float4 t = *reinterpret_cast<const float4*>(dcg + off);
+                    v[4 * i] += t.x; v[4 * i + 1] += t.y; v[4 * i + 2] += t.z; v[4 * i + 3] += t.w;
+                }
+                *reinterpret_cast<float4*>(gcg + off) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+            }
+            if (p.do_gemm2) {
+                uint8_t* half = gen + BWD_RT + (cc >> 1) * TILE16;
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    *reinterpret_cast<uint4*>(half + sw128_off(r, (cc & 1) * 4 + i)) =
+                        make_uint4(pack_bf16(v[8 * i], v[8 * i + 1]), pack_bf16(v[8 * i + 2], v[8 * i + 3]),
+                                   pack_bf16(v[8 * i + 4], v[8 * i + 5]), pack_bf16(v[8 * i + 6], v[8 * i + 7]));
+            }
+        }
+        fence_proxy_async_smem();
+        if (p.do_gemm2) { tc_fence_before(); mbar_arrive(bar + B_RT); }
+        __syncwarp();
+        if (lane == 0) {
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc) tma_store_4d(&p.tmG_st, s_g + cc * TILE16 + slab, cc * 32, tr, b, 0);
+            tma_store_commit();
+        }
+        if (p.do_gemm2) {
+            // ---- epilogue 2: dz = acc2 * [z>0] -> bf16, staged in the (now free) DF region -------------
+            const uint4 m = *reinterpret_cast<const uint4*>(p.zmask_in + row * AST_MW);
+            mw[0] = m.x; mw[1] = m.y; mw[2] = m.z; mw[3] = m.w;
+            mbar_wait(bar + B_ACC2, 0);
+            tc_fence_after();
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc) {
+                tmem_ld32(acc2 + lane_off + cc * 32, v);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) if (!((mw[cc] >> i) & 1u)) v[i] = 0.f;
+                uint8_t* half = gen + BWD_DF + (cc >> 1) * TILE16;
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    *reinterpret_cast<uint4*>(half + sw128_off(r, (cc & 1) * 4 + i)) =
+                        make_uint4(pack_bf16(v[8 * i], v[8 * i + 1]), pack_bf16(v[8 * i + 2], v[8 * i + 3]),
+                                   pack_bf16(v[8 * i + 4], v[8 * i + 5]), pack_bf16(v[8 * i + 6], v[8 * i + 7]));
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+#pragma unroll
+                for (int j = 0; j < 2; ++j) tma_store_4d(&p.tmDz_st, s_df + j * TILE16 + slab, j * 64, tr, b, p.dz_out);
+                tma_store_commit();
+            }
+        }
+        if (lane == 0) tma_store_wait_all();
+        __syncwarp();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<256>(tmem);
 }
 
 // =============================================================================================
@@ -413,36 +525,38 @@ __global__ void tc_weights_bwd_kernel(const float* __restrict__ W, __nv_bfloat16
 // =============================================================================================
 struct TcState {
     int T, B, R, NL;
-    __nv_bfloat16 *a_hi[2], *a_lo[2], *dz[2];
+    __nv_bfloat16 *a_hi, *a_lo, *dz;           // [2][R][128] each (ping-pong)
     __nv_bfloat16 *w1f, *w2f, *w1b, *w2b;
-    CUtensorMap tm_a_hi[2], tm_a_lo[2], tm_dz[2], tm_w1f, tm_w2f, tm_w1b, tm_w2b;
+    CUtensorMap tm_a_hi_ld, tm_a_lo_ld, tm_a_hi_st, tm_a_lo_st, tm_dz_ld, tm_dz_st;
+    CUtensorMap tm_H_ld, tm_H_st, tm_g_ld, tm_g_st, tm_dF_ld;
+    CUtensorMap tm_w1f, tm_w2f, tm_w1b, tm_w2b;
     int cur;                       // dz buffer holding the most recent backward output
 };
 
 static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
 
-static bool make_map(CUtensorMap* m, void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-                     const uint32_t* box) {
-    const uint32_t estr[3] = {1, 1, 1};
-    CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, ptr, dims, strides_bytes, box, estr,
-                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    return r == CUDA_SUCCESS;
-}
-static bool make_act_map(CUtensorMap* m, void* ptr, int T, int B) {          // [B][T][128] bf16, box [1][128][64]
-    const uint64_t dims[3] = {AST_C, (uint64_t)T, (uint64_t)B};
-    const uint64_t str[2] = {AST_C * 2, (uint64_t)T * AST_C * 2};
-    const uint32_t box[3] = {64, 128, 1};
-    return make_map(m, ptr, 3, dims, str, box);
+// [nbuf][B][T][128] activation tensor; box = {cols, rows, 1, 1}; 128B swizzle (cols * elem = 128 B)
+static bool make_act_map(CUtensorMap* m, void* ptr, bool fp32, int T, int B, int nbuf, int box_rows) {
+    const uint64_t es = fp32 ? 4 : 2;
+    const uint64_t dims[4] = {AST_C, (uint64_t)T, (uint64_t)B, (uint64_t)nbuf};
+    const uint64_t str[3] = {AST_C * es, (uint64_t)T * AST_C * es, (uint64_t)B * T * AST_C * es};
+    const uint32_t box[4] = {fp32 ? 32u : 64u, (uint32_t)box_rows, 1, 1};
+    const uint32_t estr[4] = {1, 1, 1, 1};
+    return g_encode(m, fp32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, ptr, dims, str, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 static bool make_w_map(CUtensorMap* m, void* ptr, size_t rows) {             // [rows][128] bf16, box [128][64]
     const uint64_t dims[2] = {AST_C, (uint64_t)rows};
     const uint64_t str[1] = {AST_C * 2};
     const uint32_t box[2] = {64, 128};
-    return make_map(m, ptr, 2, dims, str, box);
+    const uint32_t estr[2] = {1, 1};
+    return g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, ptr, dims, str, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-TcState* tc_create(int T, int B, int NL, int64_t* bytes, const char** why) {
+TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_head, int64_t* bytes, const char** why) {
     if (!g_encode) {
         void* fn = nullptr;
         cudaDriverEntryPointQueryResult qres;
@@ -454,27 +568,27 @@ TcState* tc_create(int T, int B, int NL, int64_t* bytes, const char** why) {
         g_encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
     }
     TcState* s = new TcState();
-    s->T = T; s->B = B; s->R = B * T; s->NL = NL; s->cur = 0;
-    const size_t act = (size_t)s->R * AST_C * sizeof(__nv_bfloat16);
+    memset(s, 0, sizeof(*s));
+    s->T = T; s->B = B; s->R = B * T; s->NL = NL;
+    const size_t act = (size_t)2 * s->R * AST_C * sizeof(__nv_bfloat16);
     const size_t mat = (size_t)AST_C * AST_C * sizeof(__nv_bfloat16);
-    void** ptrs[] = {(void**)&s->a_hi[0], (void**)&s->a_hi[1], (void**)&s->a_lo[0], (void**)&s->a_lo[1],
-                     (void**)&s->dz[0], (void**)&s->dz[1]};
-    for (void** p : ptrs) { *p = nullptr; }
-    bool ok = true;
-    for (void** p : ptrs) ok = ok && cudaMalloc(p, act) == cudaSuccess;
-    s->w1f = s->w2f = s->w1b = s->w2b = nullptr;
-    ok = ok && cudaMalloc(&s->w1f, mat * NL * 3 * 2) == cudaSuccess && cudaMalloc(&s->w2f, mat * NL * 2) == cudaSuccess &&
-         cudaMalloc(&s->w1b, mat * NL * 3) == cudaSuccess && cudaMalloc(&s->w2b, mat * NL) == cudaSuccess;
+    bool ok = cudaMalloc(&s->a_hi, act) == cudaSuccess && cudaMalloc(&s->a_lo, act) == cudaSuccess &&
+              cudaMalloc(&s->dz, act) == cudaSuccess && cudaMalloc(&s->w1f, mat * NL * 3 * 2) == cudaSuccess &&
+              cudaMalloc(&s->w2f, mat * NL * 2) == cudaSuccess && cudaMalloc(&s->w1b, mat * NL * 3) == cudaSuccess &&
+              cudaMalloc(&s->w2b, mat * NL) == cudaSuccess;
     if (!ok) { *why = "cudaMalloc failed"; tc_destroy(s); return nullptr; }
-    *bytes += (int64_t)(6 * act + mat * NL * 12);
-    for (int i = 0; i < 2; ++i)
-        ok = ok && make_act_map(&s->tm_a_hi[i], s->a_hi[i], T, B) && make_act_map(&s->tm_a_lo[i], s->a_lo[i], T, B) &&
-             make_act_map(&s->tm_dz[i], s->dz[i], T, B);
-    ok = ok && make_w_map(&s->tm_w1f, s->w1f, (size_t)NL * 3 * 2 * AST_C) && make_w_map(&s->tm_w2f, s->w2f, (size_t)NL * 2 * AST_C) &&
+    *bytes += (int64_t)(3 * act + mat * NL * 12);
+    ok = make_act_map(&s->tm_a_hi_ld, s->a_hi, false, T, B, 2, 128) && make_act_map(&s->tm_a_hi_st, s->a_hi, false, T, B, 2, 32) &&
+         make_act_map(&s->tm_a_lo_ld, s->a_lo, false, T, B, 2, 128) && make_act_map(&s->tm_a_lo_st, s->a_lo, false, T, B, 2, 32) &&
+         make_act_map(&s->tm_dz_ld, s->dz, false, T, B, 2, 128) && make_act_map(&s->tm_dz_st, s->dz, false, T, B, 2, 32) &&
+         make_act_map(&s->tm_H_ld, H, true, T, B, NL + 1, 128) && make_act_map(&s->tm_H_st, H, true, T, B, NL + 1, 32) &&
+         make_act_map(&s->tm_g_ld, g, true, T, B, 1, 128) && make_act_map(&s->tm_g_st, g, true, T, B, 1, 32) &&
+         make_act_map(&s->tm_dF_ld, dF, true, T, B, n_head > 0 ? n_head : 1, 128) &&
+         make_w_map(&s->tm_w1f, s->w1f, (size_t)NL * 3 * 2 * AST_C) && make_w_map(&s->tm_w2f, s->w2f, (size_t)NL * 2 * AST_C) &&
          make_w_map(&s->tm_w1b, s->w1b, (size_t)NL * 3 * AST_C) && make_w_map(&s->tm_w2b, s->w2b, (size_t)NL * AST_C);
     if (!ok) { *why = "cuTensorMapEncodeTiled failed"; tc_destroy(s); return nullptr; }
-    if (cudaFuncSetAttribute(tc_layer_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<false>::SMEM) != cudaSuccess ||
-        cudaFuncSetAttribute(tc_layer_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<true>::SMEM) != cudaSuccess) {
+    if (cudaFuncSetAttribute(tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM) != cudaSuccess ||
+        cudaFuncSetAttribute(tc_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM) != cudaSuccess) {
         *why = "cudaFuncSetAttribute(max dynamic smem) failed";
         tc_destroy(s);
         return nullptr;
@@ -484,7 +598,7 @@ TcState* tc_create(int T, int B, int NL, int64_t* bytes, const char** why) {
 
 void tc_destroy(TcState* s) {
     if (!s) return;
-    for (int i = 0; i < 2; ++i) { cudaFree(s->a_hi[i]); cudaFree(s->a_lo[i]); cudaFree(s->dz[i]); }
+    cudaFree(s->a_hi); cudaFree(s->a_lo); cudaFree(s->dz);
     cudaFree(s->w1f); cudaFree(s->w2f); cudaFree(s->w1b); cudaFree(s->w2b);
     delete s;
 }
@@ -500,35 +614,35 @@ int tc_set_weights(TcState* s, const float* Wd, const float* Wr, cudaStream_t st
 
 void tc_prepare_input(TcState* s, const float* H0, cudaStream_t st) {
     const size_t n4 = (size_t)s->R * AST_C / 4;
-    tc_split_relu_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, st>>>(H0, s->a_hi[0], s->a_lo[0], n4);
+    tc_split_relu_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, st>>>(H0, s->a_hi, s->a_lo, n4);
     ast_launch_counter += 1;
 }
 
-void tc_layer_fwd(TcState* s, int l, const float* bd, const float* br, const float* Hin, float* Hout,
-                  uint32_t* zmask_out, uint32_t* hmask_out, cudaStream_t st) {
-    TcArgs a;
-    memset(&a, 0, sizeof(a));
-    const int in = l & 1, out = in ^ 1;
-    a.tmA0 = s->tm_a_hi[in]; a.tmA1 = s->tm_a_lo[in]; a.tmW1 = s->tm_w1f; a.tmW2 = s->tm_w2f;
-    a.w1_row = l * 3 * 2 * AST_C; a.w2_row = l * 2 * AST_C;
-    a.T = s->T; a.shift = 1 << (l % 10); a.do_gemm1 = 1; a.do_gemm2 = 1;
-    a.bias1 = bd; a.bias2 = br; a.Hin = Hin; a.Hout = Hout; a.zmask_out = zmask_out; a.hmask_out = hmask_out;
-    a.a_hi_out = s->a_hi[out]; a.a_lo_out = s->a_lo[out];
-    tc_layer_kernel<false><<<s->R / 128, 192, TcCfg<false>::SMEM, st>>>(a);
-    ast_launch_counter += 1;
-}
-
-void tc_layer_bwd(TcState* s, int l, float* g, const uint32_t* hmask_in, const float* dF, const uint32_t* zmask_in,
+void tc_layer_fwd(TcState* s, int l, const float* bd, const float* br, uint32_t* zmask_out, uint32_t* hmask_out,
                   cudaStream_t st) {
-    TcArgs a;
+    FwdArgs a;
+    memset(&a, 0, sizeof(a));
+    a.tmA_hi = s->tm_a_hi_ld; a.tmA_lo = s->tm_a_lo_ld; a.tmAo_hi = s->tm_a_hi_st; a.tmAo_lo = s->tm_a_lo_st;
+    a.tmH_ld = s->tm_H_ld; a.tmH_st = s->tm_H_st; a.tmW1 = s->tm_w1f; a.tmW2 = s->tm_w2f;
+    a.w1_row = l * 3 * 2 * AST_C; a.w2_row = l * 2 * AST_C;
+    a.T = s->T; a.shift = 1 << (l % 10); a.l = l; a.a_in = l & 1; a.a_out = (l & 1) ^ 1;
+    a.bias1 = bd; a.bias2 = br; a.zmask_out = zmask_out; a.hmask_out = hmask_out;
+    tc_fwd_kernel<<<s->R / 128, 192, FWD_SMEM, st>>>(a);
+    ast_launch_counter += 1;
+}
+
+void tc_layer_bwd(TcState* s, int l, const uint32_t* hmask_in, int df_idx, const uint32_t* zmask_in, cudaStream_t st) {
+    BwdArgs a;
     memset(&a, 0, sizeof(a));
     if (l == s->NL) s->cur = 0;                 // top of the stack: (re)start the dz ping-pong
-    a.tmA0 = s->tm_dz[s->cur]; a.tmA1 = s->tm_dz[s->cur]; a.tmW1 = s->tm_w1b; a.tmW2 = s->tm_w2b;
-    a.T = s->T; a.g = g; a.dF = dF; a.hmask_in = hmask_in; a.zmask_in = zmask_in;
+    a.tmDz_ld = s->tm_dz_ld; a.tmDz_st = s->tm_dz_st; a.tmG_ld = s->tm_g_ld; a.tmG_st = s->tm_g_st; a.tmDF_ld = s->tm_dF_ld;
+    a.tmW1 = s->tm_w1b; a.tmW2 = s->tm_w2b;
+    a.T = s->T; a.df_idx = df_idx; a.hmask_in = hmask_in; a.zmask_in = zmask_in;
+    a.dz_in = s->cur; a.dz_out = s->cur ^ 1;
     if (l < s->NL) { a.do_gemm1 = 1; a.w1_row = l * 3 * AST_C; a.shift = -(1 << (l % 10)); }
     else a.g_init = 1;
-    if (l >= 1) { a.do_gemm2 = 1; a.w2_row = (l - 1) * AST_C; a.dz_out = s->dz[s->cur ^ 1]; }
-    tc_layer_kernel<true><<<s->R / 128, 192, TcCfg<true>::SMEM, st>>>(a);
+    if (l >= 1) { a.do_gemm2 = 1; a.w2_row = (l - 1) * AST_C; }
+    tc_bwd_kernel<<<s->R / 128, 192, BWD_SMEM, st>>>(a);
     ast_launch_counter += 1;
     s->cur ^= 1;
 }
