@@ -34,6 +34,8 @@ struct ast_ctx {
     int style_layer[AST_MAX_IDS]; // encoder layer (0..29) behind each style slot
     int cont_layer[AST_MAX_IDS];
     int head_buf[30];             // layer -> dF buffer index or -1
+    int f_slot[30];               // layer -> style slot (Gatys bf16 extract copy) or -1
+    int head_of_slot[AST_MAX_IDS];
     int n_head;
     int nmat, nmat_used, msize, n_side;
     int gram_chunk_rows, gram_nchunk, sse_nblk;
@@ -162,9 +164,10 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
     if (cfg->total_T <= 0) { ob = 0; oe = cfg->T; }
     c->own_lo = (int)(ob - cfg->win_begin); c->own_hi = (int)(oe - cfg->win_begin);
     if (c->own_lo < 0 || c->own_hi > c->T || c->own_lo >= c->own_hi) { delete c; return fail(AST_EINVAL, "owned rows outside the window"); }
+    if (c->own_lo % 128 || c->own_hi % 128) { delete c; return fail(AST_EINVAL, "owned range must be aligned to 128 samples"); }
 
     // resolve heads.  extracts[30] aliases extracts[29] (model.py:118-119); [31] (bottleneck) is out of scope.
-    for (int i = 0; i < 30; ++i) c->head_buf[i] = -1;
+    for (int i = 0; i < 30; ++i) { c->head_buf[i] = -1; c->f_slot[i] = -1; }
     c->n_head = 0;
     bool seen[30] = {false};
     for (int i = 0; i < c->L; ++i) {
@@ -175,7 +178,9 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
         if (seen[id]) { delete c; return fail(AST_EUNSUPPORTED, "encoder layer %d appears twice in the style set", id); }
         seen[id] = true;
         c->style_layer[i] = id;
+        c->f_slot[id] = i;
         if (c->head_buf[id] < 0) c->head_buf[id] = c->n_head++;
+        c->head_of_slot[i] = c->head_buf[id];
     }
     for (int i = 0; i < c->n_cont; ++i) {
         int id = cfg->cont_ids[i];
@@ -196,6 +201,13 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
         target = std::max(2, (target + c->B - 1) / c->B);
         int rows = (c->T + target - 1) / target;
         rows = std::max(128, ((rows + 127) / 128) * 128);
+        if (cfg->gatys && cfg->precision == AST_PREC_BF16) {
+            // tensor-core Gram: one wave of CTAs, each accumulating its tiles in TMEM
+            const int ntiles = c->T / 128;
+            int nch = std::max(1, std::min(ntiles, 148 / std::max(1, c->L * c->B)));
+            const int ct = (ntiles + nch - 1) / nch;
+            rows = ct * 128;
+        }
         c->gram_chunk_rows = rows;
         c->gram_nchunk = (c->T + rows - 1) / rows;
         c->sse_nblk = 64;
@@ -240,7 +252,8 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
     if (setup_f32_kernels() != 0) { ast_destroy(c); return fail(AST_ECUDA, "cudaFuncSetAttribute failed (is the GPU sm_100?)"); }
     if (c->prec == AST_PREC_BF16) {
         const char* why = nullptr;
-        c->tc = tc_create(c->T, c->B, c->NL, c->H, c->g, c->dF, c->n_head, &c->bytes, &why);
+        c->tc = tc_create(c->T, c->B, c->NL, c->H, c->g, c->dF, c->n_head, cfg->gatys ? c->L : 0, c->gram_part,
+                          (int64_t)c->B * c->nmat * c->gram_nchunk, &c->bytes, &why);
         if (!c->tc) { ast_destroy(c); return fail(AST_ECUDA, "tensor-core path setup failed: %s", why ? why : "?"); }
     }
     if (cudaDeviceSynchronize() != cudaSuccess || cudaGetLastError() != cudaSuccess) { ast_destroy(c); return fail(AST_ECUDA, "context setup failed"); }
@@ -301,7 +314,8 @@ static void run_encoder(ast_ctx* c, const float* d_x, cudaStream_t s) {
     if (c->tc) tc_prepare_input(c->tc, Hl(c, 0), s);
     for (int l = 0; l < c->NL; ++l) {
         if (c->tc) {
-            tc_layer_fwd(c->tc, l, c->bd + (size_t)l * AST_C, c->br + (size_t)l * AST_C, zm(c, l), hm(c, l + 1), s);
+            tc_layer_fwd(c->tc, l, c->bd + (size_t)l * AST_C, c->br + (size_t)l * AST_C, zm(c, l), hm(c, l + 1),
+                         c->f_slot[l], s);
             continue;
         }
         LayerArgsF32 a;
@@ -314,7 +328,9 @@ static void run_encoder(ast_ctx* c, const float* d_x, cudaStream_t s) {
     }
 }
 static void run_gram(ast_ctx* c, cudaStream_t s) {
-    if (c->cfg.gatys)
+    if (c->cfg.gatys && c->tc)
+        tc_gram(c->tc, c->L, c->gram_nchunk, c->gram_chunk_rows / 128, c->own_lo / 128, c->own_hi / 128, s);
+    else if (c->cfg.gatys)
         launch_gram_gatys(c->d_Fptr, c->L, c->T, c->B, c->own_lo, c->own_hi, c->gram_part, c->gram_nchunk, c->gram_chunk_rows, s);
     else
         launch_gram_ours(c->d_Fptr, c->L, c->T, c->B, c->own_lo, c->own_hi, c->gram_part, c->gram_nchunk, c->gram_chunk_rows, s);
@@ -346,6 +362,7 @@ static HeadArgs head_args(ast_ctx* c, bool with_targets, float* losses) {
     const double Ns = (double)c->nmat_used * c->msize;
     const double Nc = (double)c->total_T * c->n_cont * c->cfg.cnt_channels;
     h.G = c->partials; h.Ps = c->Ps; h.Gn = c->Gn; h.Ssym = with_targets ? c->Ssym : nullptr;
+    h.Ssym_bf16 = (with_targets && c->cfg.gatys && c->tc) ? tc_ssym_bf16(c->tc) : nullptr;
     h.ls_part = c->ls_part; h.sse = c->partials + (size_t)c->B * c->nmat * c->msize; h.losses = losses;
     h.nmat = c->nmat; h.nmat_used = with_targets ? c->nmat_used : 0; h.n = c->n_side; h.B = c->B;
     h.coef_dGn = (float)((double)c->lambd * 1e3 * 2.0 / Ns);
@@ -359,7 +376,8 @@ extern "C" int ast_step_backward(ast_ctx* c, float* d_losses, float* d_grad, voi
     if (!c->have_w || !c->have_t) return fail(AST_ESTATE, "ast_set_weights and ast_set_targets must precede a step");
     cudaStream_t s = (cudaStream_t)stream;
     launch_heads(head_args(c, true, d_losses), s);
-    if (c->cfg.gatys) launch_style_grad_gatys(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
+    if (c->cfg.gatys && c->tc) tc_style_grad(c->tc, c->L, c->head_of_slot, s);
+    else if (c->cfg.gatys) launch_style_grad_gatys(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
     else              launch_style_grad_ours(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
     {
         bool init[30];

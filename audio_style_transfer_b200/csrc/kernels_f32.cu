@@ -504,6 +504,7 @@ __global__ void __launch_bounds__(256) heads_kernel(const HeadArgs a) {
     const bool clamped = ss < 1e-12;
     float* Gn = a.Gn ? a.Gn + ((size_t)b * a.nmat + mat) * msize : nullptr;
     float* Ss = a.Ssym ? a.Ssym + ((size_t)b * a.nmat + mat) * msize : nullptr;
+    __nv_bfloat16* Sb = a.Ssym_bf16 ? a.Ssym_bf16 + ((size_t)b * a.nmat + mat) * msize : nullptr;
     for (int e = threadIdx.x; e < msize; e += blockDim.x) {
         const int i = e / n, j = e - i * n;
         const int et = j * n + i;
@@ -519,6 +520,7 @@ __global__ void __launch_bounds__(256) heads_kernel(const HeadArgs a) {
                 v = dg + dgt;
             }
             Ss[e] = (float)v;
+            if (Sb) Sb[e] = __float2bfloat16_rn((float)v);
         }
     }
 }

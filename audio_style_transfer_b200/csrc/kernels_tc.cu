@@ -49,7 +49,9 @@ struct alignas(64) FwdArgs {
     CUtensorMap tmAo_hi, tmAo_lo;    // stores: same buffers, box {64,32,1,1}
     CUtensorMap tmH_ld, tmH_st;      // fp32 residual stream [NL+1][B][T][128]: box {32,128,1,1} / {32,32,1,1}
     CUtensorMap tmW1, tmW2;          // weight operands, rows of 128 k-contiguous bf16, box {64,128}
+    CUtensorMap tmF_st;              // bf16 copy of the extract for the Gram head [n_style][B][T][128], box {64,32,1,1}
     int w1_row, w2_row;              // first row of this layer's block in tmW1 / tmW2
+    int f_slot;                      // style slot of extracts[l] (row of tmF_st), or -1
     int T, shift, l, a_in, a_out;    // rows per pair; dilation; layer; ping-pong indices of the bf16 operand buffers
     const float* bias1; const float* bias2;
     uint32_t* zmask_out; uint32_t* hmask_out;
@@ -72,6 +74,7 @@ __global__ void __launch_bounds__(192, 1) tc_fwd_kernel(const __grid_constant__ 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&p.tmA_hi); tma_prefetch_desc(&p.tmA_lo); tma_prefetch_desc(&p.tmW1); tma_prefetch_desc(&p.tmW2);
         tma_prefetch_desc(&p.tmH_ld); tma_prefetch_desc(&p.tmH_st); tma_prefetch_desc(&p.tmAo_hi); tma_prefetch_desc(&p.tmAo_lo);
+        if (p.f_slot >= 0) tma_prefetch_desc(&p.tmF_st);
         for (int i = 0; i < 2; ++i) { mbar_init(bar + B_FULL(i), 1); mbar_init(bar + B_EMPTY(i), 1); }
         mbar_init(bar + B_ACC1, 1); mbar_init(bar + B_RT, 128); mbar_init(bar + B_ACC2, 1);
         mbar_init_fence();
@@ -228,6 +231,14 @@ __global__ void __launch_bounds__(192, 1) tc_fwd_kernel(const __grid_constant__ 
                 v[4 * i + 2] = h.z + (v[4 * i + 2] + bb.z); v[4 * i + 3] = h.w + (v[4 * i + 3] + bb.w);
                 *hp = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
             }
+            if (p.f_slot >= 0) {                                   // bf16(h') for the Gram head, staged in the dead W2 tile
+                uint8_t* fh = gen + (cc >> 1) * FWD_STAGE + 2 * TILE16;
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    *reinterpret_cast<uint4*>(fh + sw128_off(r, (cc & 1) * 4 + i)) =
+                        make_uint4(pack_bf16(v[8 * i], v[8 * i + 1]), pack_bf16(v[8 * i + 2], v[8 * i + 3]),
+                                   pack_bf16(v[8 * i + 4], v[8 * i + 5]), pack_bf16(v[8 * i + 6], v[8 * i + 7]));
+            }
 #pragma unroll
             for (int i = 0; i < 32; ++i) { word |= (v[i] > 0.f ? 1u : 0u) << i; v[i] = fmaxf(v[i], 0.f); }
             mw[cc] = word;
@@ -258,6 +269,7 @@ __global__ void __launch_bounds__(192, 1) tc_fwd_kernel(const __grid_constant__ 
             for (int j = 0; j < 2; ++j) {
                 tma_store_4d(&p.tmAo_hi, s_rt + j * 2 * TILE16 + slab, j * 64, tr, b, p.a_out);
                 tma_store_4d(&p.tmAo_lo, s_rt + j * 2 * TILE16 + TILE16 + slab, j * 64, tr, b, p.a_out);
+                if (p.f_slot >= 0) tma_store_4d(&p.tmF_st, base + j * FWD_STAGE + 2 * TILE16 + slab, j * 64, tr, b, p.f_slot);
             }
             tma_store_commit();
             tma_store_wait_all();
@@ -527,6 +539,9 @@ struct TcState {
     int T, B, R, NL;
     __nv_bfloat16 *a_hi, *a_lo, *dz;           // [2][R][128] each (ping-pong)
     __nv_bfloat16 *w1f, *w2f, *w1b, *w2b;
+    __nv_bfloat16 *F, *ssym;                   // Gatys head: bf16 extracts [n_fslots][R][128], bf16 Ssym [B*n_fslots][128][128]
+    int n_fslots;
+    CUtensorMap tm_F_st, tm_F_ld, tm_ssym, tm_gpart, tm_dF_st;
     CUtensorMap tm_a_hi_ld, tm_a_lo_ld, tm_a_hi_st, tm_a_lo_st, tm_dz_ld, tm_dz_st;
     CUtensorMap tm_H_ld, tm_H_st, tm_g_ld, tm_g_st, tm_dF_ld;
     CUtensorMap tm_w1f, tm_w2f, tm_w1b, tm_w2b;
@@ -556,7 +571,19 @@ static bool make_w_map(CUtensorMap* m, void* ptr, size_t rows) {             // 
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_head, int64_t* bytes, const char** why) {
+static bool make_rows_map(CUtensorMap* m, void* ptr, bool fp32, size_t rows, int box_rows) {   // [rows][128]
+    const uint64_t es = fp32 ? 4 : 2;
+    const uint64_t dims[2] = {AST_C, (uint64_t)rows};
+    const uint64_t str[1] = {AST_C * es};
+    const uint32_t box[2] = {fp32 ? 32u : 64u, (uint32_t)box_rows};
+    const uint32_t estr[2] = {1, 1};
+    return g_encode(m, fp32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, ptr, dims, str, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_head, int n_fslots,
+                   float* gram_part, int64_t gram_part_mats, int64_t* bytes, const char** why) {
     if (!g_encode) {
         void* fn = nullptr;
         cudaDriverEntryPointQueryResult qres;
@@ -586,6 +613,18 @@ TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_he
          make_act_map(&s->tm_dF_ld, dF, true, T, B, n_head > 0 ? n_head : 1, 128) &&
          make_w_map(&s->tm_w1f, s->w1f, (size_t)NL * 3 * 2 * AST_C) && make_w_map(&s->tm_w2f, s->w2f, (size_t)NL * 2 * AST_C) &&
          make_w_map(&s->tm_w1b, s->w1b, (size_t)NL * 3 * AST_C) && make_w_map(&s->tm_w2b, s->w2b, (size_t)NL * AST_C);
+    s->n_fslots = n_fslots;
+    if (ok && n_fslots > 0) {
+        const size_t fb = (size_t)n_fslots * s->R * AST_C * sizeof(__nv_bfloat16), sb = (size_t)B * n_fslots * mat;
+        if (cudaMalloc(&s->F, fb) != cudaSuccess || cudaMalloc(&s->ssym, sb) != cudaSuccess) {
+            *why = "cudaMalloc failed"; tc_destroy(s); return nullptr;
+        }
+        *bytes += (int64_t)(fb + sb);
+        ok = make_act_map(&s->tm_F_st, s->F, false, T, B, n_fslots, 32) && make_act_map(&s->tm_F_ld, s->F, false, T, B, n_fslots, 128) &&
+             make_rows_map(&s->tm_ssym, s->ssym, false, (size_t)B * n_fslots * AST_C, 128) &&
+             make_rows_map(&s->tm_gpart, gram_part, true, (size_t)gram_part_mats * AST_C, 32) &&
+             make_act_map(&s->tm_dF_st, dF, true, T, B, n_head > 0 ? n_head : 1, 32) && setup_gram_tc_kernels() == 0;
+    }
     if (!ok) { *why = "cuTensorMapEncodeTiled failed"; tc_destroy(s); return nullptr; }
     if (cudaFuncSetAttribute(tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM) != cudaSuccess ||
         cudaFuncSetAttribute(tc_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM) != cudaSuccess) {
@@ -600,6 +639,7 @@ void tc_destroy(TcState* s) {
     if (!s) return;
     cudaFree(s->a_hi); cudaFree(s->a_lo); cudaFree(s->dz);
     cudaFree(s->w1f); cudaFree(s->w2f); cudaFree(s->w1b); cudaFree(s->w2b);
+    cudaFree(s->F); cudaFree(s->ssym);
     delete s;
 }
 
@@ -619,7 +659,7 @@ void tc_prepare_input(TcState* s, const float* H0, cudaStream_t st) {
 }
 
 void tc_layer_fwd(TcState* s, int l, const float* bd, const float* br, uint32_t* zmask_out, uint32_t* hmask_out,
-                  cudaStream_t st) {
+                  int f_slot, cudaStream_t st) {
     FwdArgs a;
     memset(&a, 0, sizeof(a));
     a.tmA_hi = s->tm_a_hi_ld; a.tmA_lo = s->tm_a_lo_ld; a.tmAo_hi = s->tm_a_hi_st; a.tmAo_lo = s->tm_a_lo_st;
@@ -627,6 +667,8 @@ void tc_layer_fwd(TcState* s, int l, const float* bd, const float* br, uint32_t*
     a.w1_row = l * 3 * 2 * AST_C; a.w2_row = l * 2 * AST_C;
     a.T = s->T; a.shift = 1 << (l % 10); a.l = l; a.a_in = l & 1; a.a_out = (l & 1) ^ 1;
     a.bias1 = bd; a.bias2 = br; a.zmask_out = zmask_out; a.hmask_out = hmask_out;
+    a.f_slot = (s->n_fslots > 0) ? f_slot : -1;
+    if (a.f_slot >= 0) a.tmF_st = s->tm_F_st;
     tc_fwd_kernel<<<s->R / 128, 192, FWD_SMEM, st>>>(a);
     ast_launch_counter += 1;
 }
@@ -645,4 +687,22 @@ void tc_layer_bwd(TcState* s, int l, const uint32_t* hmask_in, int df_idx, const
     tc_bwd_kernel<<<s->R / 128, 192, BWD_SMEM, st>>>(a);
     ast_launch_counter += 1;
     s->cur ^= 1;
+}
+
+// ---- Gatys head ---------------------------------------------------------------------------------
+void tc_gram(TcState* s, int L, int nchunk, int chunk_tiles, int tile_lo, int tile_hi, cudaStream_t st) {
+    GramTcArgs a;
+    memset(&a, 0, sizeof(a));
+    a.tmF = s->tm_F_ld; a.tmP = s->tm_gpart;
+    a.L = L; a.chunk_tiles = chunk_tiles; a.tile_lo = tile_lo; a.tile_hi = tile_hi;
+    launch_gram_tc(a, nchunk, L, s->B, st);
+}
+__nv_bfloat16* tc_ssym_bf16(TcState* s) { return s ? s->ssym : nullptr; }
+void tc_style_grad(TcState* s, int L, const int* head_of_slot, cudaStream_t st) {
+    SGradTcArgs a;
+    memset(&a, 0, sizeof(a));
+    a.tmF = s->tm_F_ld; a.tmS = s->tm_ssym; a.tmDF = s->tm_dF_st;
+    a.T = s->T; a.L = L;
+    for (int i = 0; i < L && i < 32; ++i) a.head_of_slot[i] = head_of_slot[i];
+    launch_sgrad_tc(a, s->R / 128, L, st);
 }

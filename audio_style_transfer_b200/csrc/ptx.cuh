@@ -109,6 +109,13 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 __device__ __forceinline__ uint64_t umma_desc_kmajor_sw128(uint32_t saddr) {
     return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)0x40004040u << 32);
 }
+// MN-major operand (the GEMM's M/N index is the contiguous one): the same [rows][64 bf16] swizzled tile
+// read "transposed" -- rows are K, the 64 contiguous elements are M (or N).  Canonical layout
+// ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16-byte units: LBO = distance between 64-element MN blocks,
+// SBO = distance between 8-row K groups (1024 B).  Advancing K by 16 rows = +2048 B on the start address.
+__device__ __forceinline__ uint64_t umma_desc_mnmajor_sw128(uint32_t saddr, uint32_t lbo_bytes) {
+    return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) | ((uint64_t)0x40004040u << 32);
+}
 // kind::f16 instruction descriptor: D = f32 (1 @4), A = B = bf16 (1 @7, 1 @10), N>>3 @17, M>>4 @24;
 // bit 15 / 16 = A / B is MN-major (transposed) instead of K-major.
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N, bool a_mn = false, bool b_mn = false) {

@@ -1,22 +1,52 @@
-// tc.cuh -- interface of the tcgen05 / TMEM / TMA layer kernels (kernels_tc.cu), AST_PREC_BF16.
+// tc.cuh -- interface of the tcgen05 / TMEM / TMA kernels (kernels_tc.cu, gram_tc.cu), AST_PREC_BF16.
 #pragma once
 #include "common.cuh"
+
+#include <cuda.h>
 
 struct TcState;
 
 // Allocates the bf16 operand buffers and encodes the TMA tensor maps over the caller's fp32 buffers:
 // H [NL+1][R][128] residual stream, g [R][128] running gradient, dF [n_head][R][128] head gradients.
-TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_head, int64_t* bytes, const char** why);
+// n_fslots > 0 (Gatys head): also a bf16 copy F [n_fslots][R][128] of the style extracts, a bf16 image
+// of Ssym [B*n_fslots][128][128], and a map over the caller's Gram partial buffer
+// gram_part [gram_part_mats][128][128] fp32.
+TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_head, int n_fslots,
+                   float* gram_part, int64_t gram_part_mats, int64_t* bytes, const char** why);
 void tc_destroy(TcState* s);
 // bf16 operand copies of the fp32 master weights (device pointers, layouts of ast_set_weights).
 int tc_set_weights(TcState* s, const float* Wd, const float* Wr, cudaStream_t st);
 // split relu(H[0]) into the hi/lo bf16 A operands of layer 0
 void tc_prepare_input(TcState* s, const float* H0, cudaStream_t st);
 // forward layer l (model.py:99-114): reads relu(H[l]) as bf16 hi/lo + H[l] fp32, writes H[l+1],
-// the bf16 hi/lo of relu(H[l+1]), zmask[l], hmask[l+1].
+// the bf16 hi/lo of relu(H[l+1]), zmask[l], hmask[l+1] and, if f_slot >= 0, bf16(H[l+1]) -> F[f_slot].
 void tc_layer_fwd(TcState* s, int l, const float* bd, const float* br, uint32_t* zmask_out, uint32_t* hmask_out,
-                  cudaStream_t st);
+                  int f_slot, cudaStream_t st);
 // backward boundary l in NL..0: g += conv^T(dz_l) * hmask + dF[df_idx] (df_idx < 0: none);
 // dz_{l-1} = (g Wr_{l-1}^T) * zmask.  bf16 dz buffers owned by the TcState.  l == NL: no conv (top);
 // l == 0: no 1x1 (bottom).
 void tc_layer_bwd(TcState* s, int l, const uint32_t* hmask_in, int df_idx, const uint32_t* zmask_in, cudaStream_t st);
+
+// Gatys Gram partials of the owned tiles [tile_lo, tile_hi) of every pair: part[(b*L+l)][chunk][128][128]
+void tc_gram(TcState* s, int L, int nchunk, int chunk_tiles, int tile_lo, int tile_hi, cudaStream_t st);
+// bf16 image of Ssym that the heads kernel fills ([B*L][128][128]), or NULL
+__nv_bfloat16* tc_ssym_bf16(TcState* s);
+// dF[head_of_slot[i]] = F[i] . Ssym[i] for every style slot i
+void tc_style_grad(TcState* s, int L, const int* head_of_slot, cudaStream_t st);
+
+// ---- gram_tc.cu ------------------------------------------------------------------------------------
+struct alignas(64) GramTcArgs {
+    CUtensorMap tmF;                 // bf16 [L][B][T][128], box {64,128,1,1}
+    CUtensorMap tmP;                 // fp32 partials as rows [mats*128][128], box {32,32}
+    int L, chunk_tiles, tile_lo, tile_hi;
+};
+struct alignas(64) SGradTcArgs {
+    CUtensorMap tmF;                 // bf16 [L][B][T][128], box {64,128,1,1}
+    CUtensorMap tmS;                 // bf16 Ssym rows [B*L*128][128], box {64,128}
+    CUtensorMap tmDF;                // fp32 [n_head][B][T][128], store box {32,32,1,1}
+    int T, L;
+    int head_of_slot[32];
+};
+void launch_gram_tc(const GramTcArgs& a, int nchunk, int L, int B, cudaStream_t s);
+void launch_sgrad_tc(const SGradTcArgs& a, int ntiles, int L, cudaStream_t s);
+int setup_gram_tc_kernels();
