@@ -549,3 +549,7 @@ extern "C" int ast_step_timed(ast_ctx* c, const float* d_x, float* d_losses, flo
     ms_out[0] = enc; ms_out[1] = bwd; ms_out[2] = gram; ms_out[3] = tot;
     return AST_OK;
 }
+
+// profiling aid (scripts/timeline.py): per-CTA clock64() stamps of the forward layer kernel's phases
+void tc_set_timeline(unsigned long long* d_buf);
+extern "C" int ast_debug_timeline(void* d_buf) { tc_set_timeline((unsigned long long*)d_buf); return AST_OK; }

@@ -84,3 +84,16 @@ void launch_style_grad_gatys(const float* const* d_F, float* const* d_dF, const 
 void launch_content_grad(const float* H, const float* Pc, float* dF, int slot, int n_cont, int cnt_ch, float coef,
                          int accumulate, int R, cudaStream_t s);
 void launch_content_gather(const float* const* d_Hc, int n_cont, int cnt_ch, float* Ec, int R, cudaStream_t s);
+
+// Launch with programmatic stream serialization (PDL): the kernel MUST call pdl_wait() (ptx.cuh) before it
+// touches anything an earlier kernel in the stream wrote or reads.
+template <typename Kern, typename Args>
+static inline cudaError_t launch_pdl(Kern kernel, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const Args& args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, args);
+}

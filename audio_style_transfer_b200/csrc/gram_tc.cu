@@ -45,6 +45,8 @@ __global__ void __launch_bounds__(192, 1) gram_tc_kernel(const __grid_constant__
     __syncthreads();
     tc_fence_after();
     const uint32_t acc = *reinterpret_cast<volatile uint32_t*>(gen + (bar + GB_TMEM - base));
+    pdl_launch_dependents();
+    pdl_wait();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -110,7 +112,7 @@ __global__ void __launch_bounds__(192, 1) gram_tc_kernel(const __grid_constant__
 }
 
 void launch_gram_tc(const GramTcArgs& a, int nchunk, int L, int B, cudaStream_t s) {
-    gram_tc_kernel<<<dim3(nchunk, L, B), 192, GRAM_SMEM, s>>>(a);
+    launch_pdl(gram_tc_kernel, dim3(nchunk, L, B), dim3(192), GRAM_SMEM, s, a);
     ast_launch_counter += 1;
 }
 
@@ -138,6 +140,8 @@ __global__ void __launch_bounds__(192, 3) sgrad_tc_kernel(const __grid_constant_
     __syncthreads();
     tc_fence_after();
     const uint32_t acc = *reinterpret_cast<volatile uint32_t*>(gen + (bar + GB_TMEM - base));
+    pdl_launch_dependents();
+    pdl_wait();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -193,7 +197,7 @@ __global__ void __launch_bounds__(192, 3) sgrad_tc_kernel(const __grid_constant_
 }
 
 void launch_sgrad_tc(const SGradTcArgs& a, int ntiles, int L, cudaStream_t s) {
-    sgrad_tc_kernel<<<dim3(ntiles, L), 192, SG_SMEM, s>>>(a);
+    launch_pdl(sgrad_tc_kernel, dim3(ntiles, L), dim3(192), SG_SMEM, s, a);
     ast_launch_counter += 1;
 }
 

@@ -27,14 +27,10 @@
 #define TILE16 16384                            // [128 rows][128 B]: one bf16 K-half or one fp32 32-column group
 static constexpr uint32_t IDESC = umma_idesc_bf16(128, 128);
 
-// barrier block layout (byte offsets from the barrier base)
-#define B_FULL(i)  (8u * (i))
-#define B_EMPTY(i) (16u + 8u * (i))
-#define B_ACC1  32u
-#define B_RT    40u
-#define B_ACC2  48u
-#define B_IO    56u
-#define B_TMEM  64u
+// optional per-CTA timeline (debug / profiling aid, scripts/timeline.py): slot i of CTA c <- clock64()
+__device__ unsigned long long* g_timeline = nullptr;
+#define TL(i) do { if (g_timeline) g_timeline[(size_t)blockIdx.x * 64 + (i)] = clock64(); } while (0)
+void tc_set_timeline(unsigned long long* d_buf) { cudaMemcpyToSymbol(g_timeline, &d_buf, sizeof(d_buf)); }
 
 __device__ __forceinline__ bool tap_live(int t0, int k, int shift, int T) {
     const int t = t0 + (k - 1) * shift;
@@ -45,111 +41,154 @@ __device__ __forceinline__ bool tap_live(int t0, int k, int shift, int T) {
 // forward layer
 // =============================================================================================
 struct alignas(64) FwdArgs {
-    CUtensorMap tmA_hi, tmA_lo;      // loads: relu(h) hi / lo, bf16 [2][B][T][128], box {64,128,1,1}
-    CUtensorMap tmAo_hi, tmAo_lo;    // stores: same buffers, box {64,32,1,1}
-    CUtensorMap tmH_ld, tmH_st;      // fp32 residual stream [NL+1][B][T][128]: box {32,128,1,1} / {32,32,1,1}
+    CUtensorMap tmA_hi, tmA_lo;      // relu(h) hi / lo, bf16 [2][B][T][128], box {64,128,1,1} (loads and stores)
+    CUtensorMap tmH;                 // fp32 residual stream [NL+1][B][T][128], box {32,128,1,1} (loads and stores)
     CUtensorMap tmW1, tmW2;          // weight operands, rows of 128 k-contiguous bf16, box {64,128}
-    CUtensorMap tmF_st;              // bf16 copy of the extract for the Gram head [n_style][B][T][128], box {64,32,1,1}
+    CUtensorMap tmF;                 // bf16 copy of the extract for the Gram head [n_style][B][T][128], box {64,128,1,1}
     int w1_row, w2_row;              // first row of this layer's block in tmW1 / tmW2
-    int f_slot;                      // style slot of extracts[l] (row of tmF_st), or -1
+    int f_slot;                      // style slot of extracts[l] (row of tmF), or -1
     int T, shift, l, a_in, a_out;    // rows per pair; dilation; layer; ping-pong indices of the bf16 operand buffers
     const float* bias1; const float* bias2;
     uint32_t* zmask_out; uint32_t* hmask_out;
 };
-// smem: stage 0 | stage 1 (64 KB each: A_hi, A_lo, W_hi, W_lo x [128][64] bf16) | RT (64 KB: relu(z) hi/lo, 2 K-halves)
-// After GEMM1 the A half of each stage receives two 32-column groups of the fp32 H tile (the residual
-// input), updated in place to H' and stored from there; RT is reused to stage relu(H') hi/lo.
+// smem: slot 0 | slot 1 | slot 2 (64 KB each: A_hi, A_lo, W_hi, W_lo x [128][64] bf16).  Slot 2 is a pipeline
+// stage only during GEMM1; afterwards it is RT: relu(z) hi/lo (A operand of the 1x1 GEMM), then the staging
+// area of relu(h') hi/lo.  After GEMM1 the A half of slots 0/1 receives the fp32 H tile (two 32-column groups
+// each), updated in place to H' and stored from there; their W_hi quarter, dead after GEMM2, stages bf16(h').
 #define FWD_STAGE 65536
-#define FWD_SMEM (2 * FWD_STAGE + 65536 + 1024 + 128)
+#define FWD_SMEM (3 * FWD_STAGE + 1024 + 128)
+#define FWD_THREADS 576                          // warp 0 TMA, warp 1 MMA, 16 epilogue warps (quadrant x column group)
+// barrier block
+#define FB_FULL(i)  (8u * (i))
+#define FB_EMPTY(i) (24u + 8u * (i))
+#define FB_ACC1 48u
+#define FB_RT(j) (56u + 8u * (j))
+#define FB_ACC2 72u
+#define FB_TMEM 80u
 
-__global__ void __launch_bounds__(192, 1) tc_fwd_kernel(const __grid_constant__ FwdArgs p) {
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+// relu'd (or raw) 32 floats -> 4 x 16-byte chunks of bf16 hi (and lo = v - hi) in a swizzled [128][64] tile pair
+__device__ __forceinline__ void stage_hi_lo(uint8_t* tile_hi, uint8_t* tile_lo, int r, int chunk0, const float (&v)[32]) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const uint32_t off = sw128_off(r, chunk0 + i);
+        float hi[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) hi[e] = bf16_round(v[8 * i + e]);
+        *reinterpret_cast<uint4*>(tile_hi + off) = make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]),
+                                                             pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
+        *reinterpret_cast<uint4*>(tile_lo + off) =
+            make_uint4(pack_bf16(v[8 * i] - hi[0], v[8 * i + 1] - hi[1]), pack_bf16(v[8 * i + 2] - hi[2], v[8 * i + 3] - hi[3]),
+                       pack_bf16(v[8 * i + 4] - hi[4], v[8 * i + 5] - hi[5]), pack_bf16(v[8 * i + 6] - hi[6], v[8 * i + 7] - hi[7]));
+    }
+}
+__device__ __forceinline__ void stage_bf16(uint8_t* tile, int r, int chunk0, const float (&v)[32]) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<uint4*>(tile + sw128_off(r, chunk0 + i)) =
+            make_uint4(pack_bf16(v[8 * i], v[8 * i + 1]), pack_bf16(v[8 * i + 2], v[8 * i + 3]),
+                       pack_bf16(v[8 * i + 4], v[8 * i + 5]), pack_bf16(v[8 * i + 6], v[8 * i + 7]));
+}
+
+__global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_kernel(const __grid_constant__ FwdArgs p) {
     extern __shared__ uint8_t tc_smem_raw[];
     const uint32_t base = (smem_u32(tc_smem_raw) + 1023u) & ~1023u;
     uint8_t* gen = tc_smem_raw + (base - smem_u32(tc_smem_raw));          // generic pointer to `base`
-    const uint32_t s_rt = base + 2 * FWD_STAGE, bar = s_rt + 65536;
+    const uint32_t s_rt = base + 2 * FWD_STAGE, bar = base + 3 * FWD_STAGE;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int row0 = blockIdx.x * 128;
     const int b = row0 / p.T, t0 = row0 - b * p.T;
+    const int nlive = (int)tap_live(t0, 0, p.shift, p.T) + 1 + (int)tap_live(t0, 2, p.shift, p.T);
+    const int n1 = 2 * nlive;                                              // GEMM1 K-slices of 64
+    if (threadIdx.x == 0) TL(0);
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&p.tmA_hi); tma_prefetch_desc(&p.tmA_lo); tma_prefetch_desc(&p.tmW1); tma_prefetch_desc(&p.tmW2);
-        tma_prefetch_desc(&p.tmH_ld); tma_prefetch_desc(&p.tmH_st); tma_prefetch_desc(&p.tmAo_hi); tma_prefetch_desc(&p.tmAo_lo);
-        if (p.f_slot >= 0) tma_prefetch_desc(&p.tmF_st);
-        for (int i = 0; i < 2; ++i) { mbar_init(bar + B_FULL(i), 1); mbar_init(bar + B_EMPTY(i), 1); }
-        mbar_init(bar + B_ACC1, 1); mbar_init(bar + B_RT, 128); mbar_init(bar + B_ACC2, 1);
+        tma_prefetch_desc(&p.tmH);
+        if (p.f_slot >= 0) tma_prefetch_desc(&p.tmF);
+        for (int i = 0; i < 3; ++i) { mbar_init(bar + FB_FULL(i), 1); mbar_init(bar + FB_EMPTY(i), 1); }
+        mbar_init(bar + FB_ACC1, 1); mbar_init(bar + FB_RT(0), 8); mbar_init(bar + FB_RT(1), 8); mbar_init(bar + FB_ACC2, 1);
         mbar_init_fence();
     }
-    if (warp == 1) tmem_alloc<256>(bar + B_TMEM);
+    if (warp == 1) tmem_alloc<256>(bar + FB_TMEM);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gen + (bar + B_TMEM - base));
+    const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gen + (bar + FB_TMEM - base));
     const uint32_t acc1 = tmem, acc2 = tmem + 128;
+    pdl_launch_dependents();
+    pdl_wait();                        // everything above overlapped the previous kernel's tail
+    if (threadIdx.x == 0) TL(1);
 
     if (warp == 0) {
         // ================================ TMA producer ========================================
         if (lane == 0) {
+            int fills[3] = {0, 0, 0};
             int it = 0;
             for (int k = 0; k < 3; ++k) {
                 if (!tap_live(t0, k, p.shift, p.T)) continue;
                 const int t = t0 + (k - 1) * p.shift;
                 for (int j = 0; j < 2; ++j, ++it) {
-                    const int slot = it & 1;
-                    mbar_wait(bar + B_EMPTY(slot), ((it >> 1) & 1) ^ 1);
-                    const uint32_t st = base + slot * FWD_STAGE, fb = bar + B_FULL(slot);
+                    const int slot = it % 3;
+                    mbar_wait(bar + FB_EMPTY(slot), (fills[slot] & 1) ^ 1);
+                    ++fills[slot];
+                    const uint32_t st = base + slot * FWD_STAGE, fb = bar + FB_FULL(slot);
                     mbar_expect_tx(fb, 4 * TILE16);
                     tma_load_4d(st, &p.tmA_hi, fb, j * 64, t, b, p.a_in);
                     tma_load_4d(st + TILE16, &p.tmA_lo, fb, j * 64, t, b, p.a_in);
                     tma_load_2d(st + 2 * TILE16, &p.tmW1, fb, j * 64, p.w1_row + (k * 2 + 0) * 128);
                     tma_load_2d(st + 3 * TILE16, &p.tmW1, fb, j * 64, p.w1_row + (k * 2 + 1) * 128);
+                    TL(2 + it);
                 }
             }
-            // 1x1 weights (K-half j) + two column groups of the fp32 residual tile per stage
-            for (int j = 0; j < 2; ++j, ++it) {
-                const int slot = it & 1;
-                mbar_wait(bar + B_EMPTY(slot), ((it >> 1) & 1) ^ 1);
-                const uint32_t st = base + slot * FWD_STAGE, fb = bar + B_FULL(slot);
+            // 1x1 weights (K-half j) + two column groups of the fp32 residual tile, into slots 0 and 1
+            for (int j = 0; j < 2; ++j) {
+                mbar_wait(bar + FB_EMPTY(j), (fills[j] & 1) ^ 1);
+                ++fills[j];
+                const uint32_t st = base + j * FWD_STAGE, fb = bar + FB_FULL(j);
                 mbar_expect_tx(fb, 4 * TILE16);
                 tma_load_2d(st + 2 * TILE16, &p.tmW2, fb, j * 64, p.w2_row);
                 tma_load_2d(st + 3 * TILE16, &p.tmW2, fb, j * 64, p.w2_row + 128);
-                tma_load_4d(st, &p.tmH_ld, fb, (2 * slot) * 32, t0, b, p.l);
-                tma_load_4d(st + TILE16, &p.tmH_ld, fb, (2 * slot + 1) * 32, t0, b, p.l);
+                tma_load_4d(st, &p.tmH, fb, (2 * j) * 32, t0, b, p.l);
+                tma_load_4d(st + TILE16, &p.tmH, fb, (2 * j + 1) * 32, t0, b, p.l);
+                TL(8 + j);
             }
         }
     } else if (warp == 1) {
         // ================================ MMA issuer ==========================================
         if (lane == 0) {
-            int it = 0;
+            int uses[3] = {0, 0, 0};
             uint32_t accum = 0;
-            for (int k = 0; k < 3; ++k) {
-                if (!tap_live(t0, k, p.shift, p.T)) continue;
-                for (int j = 0; j < 2; ++j, ++it) {
-                    const int slot = it & 1;
-                    mbar_wait(bar + B_FULL(slot), (it >> 1) & 1);
-                    tc_fence_after();
-                    const uint32_t st = base + slot * FWD_STAGE;
-#pragma unroll
-                    for (int kk = 0; kk < 4; ++kk) {
-                        const uint64_t a_hi = umma_desc_kmajor_sw128(st + kk * 32);
-                        const uint64_t a_lo = umma_desc_kmajor_sw128(st + TILE16 + kk * 32);
-                        const uint64_t w_hi = umma_desc_kmajor_sw128(st + 2 * TILE16 + kk * 32);
-                        const uint64_t w_lo = umma_desc_kmajor_sw128(st + 3 * TILE16 + kk * 32);
-                        umma_f16(acc1, a_hi, w_hi, IDESC, accum);
-                        umma_f16(acc1, a_lo, w_hi, IDESC, 1u);
-                        umma_f16(acc1, a_hi, w_lo, IDESC, 1u);
-                        accum = 1u;
-                    }
-                    umma_commit(bar + B_EMPTY(slot));
-                }
-            }
-            umma_commit(bar + B_ACC1);
-            mbar_wait(bar + B_RT, 0);
-            tc_fence_after();
-            for (int j = 0; j < 2; ++j, ++it) {
-                const int slot = it & 1;
-                mbar_wait(bar + B_FULL(slot), (it >> 1) & 1);
+            for (int it = 0; it < n1; ++it) {
+                const int slot = it % 3;
+                mbar_wait(bar + FB_FULL(slot), uses[slot] & 1);
+                ++uses[slot];
                 tc_fence_after();
+                TL(10 + it);
                 const uint32_t st = base + slot * FWD_STAGE;
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk) {
+                    const uint64_t a_hi = umma_desc_kmajor_sw128(st + kk * 32);
+                    const uint64_t a_lo = umma_desc_kmajor_sw128(st + TILE16 + kk * 32);
+                    const uint64_t w_hi = umma_desc_kmajor_sw128(st + 2 * TILE16 + kk * 32);
+                    const uint64_t w_lo = umma_desc_kmajor_sw128(st + 3 * TILE16 + kk * 32);
+                    umma_f16(acc1, a_hi, w_hi, IDESC, accum);
+                    umma_f16(acc1, a_lo, w_hi, IDESC, 1u);
+                    umma_f16(acc1, a_hi, w_lo, IDESC, 1u);
+                    accum = 1u;
+                }
+                umma_commit(bar + FB_EMPTY(slot));
+            }
+            umma_commit(bar + FB_ACC1);
+            TL(18);
+            for (int j = 0; j < 2; ++j) {
+                mbar_wait(bar + FB_RT(j), 0);
+                mbar_wait(bar + FB_FULL(j), uses[j] & 1);
+                tc_fence_after();
+                TL(16 + j * 3);
+                const uint32_t st = base + j * FWD_STAGE;
                 const uint32_t ra = s_rt + j * 2 * TILE16;                  // [K-half j][hi, lo]
 #pragma unroll
                 for (int kk = 0; kk < 4; ++kk) {
@@ -162,65 +201,54 @@ __global__ void __launch_bounds__(192, 1) tc_fwd_kernel(const __grid_constant__ 
                     umma_f16(acc2, a_hi, w_lo, IDESC, 1u);
                 }
             }
-            umma_commit(bar + B_ACC2);
+            umma_commit(bar + FB_ACC2);
+            TL(20);
         }
         __syncwarp();
     } else {
         // ================================ epilogue warps ======================================
-        const int q = warp & 3;                                   // TMEM lane quadrant this warp may read
+        // warp -> (TMEM lane quadrant q = warp % 4, 32-column group cc): 4 warps per scheduler hide each other's latency
+        const int q = warp & 3, cc = (warp - 2) >> 2, half = cc >> 1;
         const int r = q * 32 + lane;                              // row within the tile = TMEM lane
         const size_t row = (size_t)row0 + r;
         const uint32_t lane_off = (uint32_t)(q * 32) << 16;
-        uint8_t* rt = gen + (s_rt - base);
+        uint8_t* rt = gen + 2 * FWD_STAGE + half * 2 * TILE16;    // [K-half][hi, lo]
         float v[32];
-        uint32_t mw[4];
 
         // ---- epilogue 1: z = acc1 + bd -> sign mask, relu(z) hi/lo -> A operand of the 1x1 GEMM ----
-        mbar_wait(bar + B_ACC1, 0);
+        mbar_wait(bar + FB_ACC1, 0);
         tc_fence_after();
-#pragma unroll
-        for (int cc = 0; cc < 4; ++cc) {
-            tmem_ld32(acc1 + lane_off + cc * 32, v);
+        if (threadIdx.x == 64) TL(24);
+        tmem_ld32(acc1 + lane_off + cc * 32, v);
+        {
             uint32_t word = 0;
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                v[i] += __ldg(p.bias1 + cc * 32 + i);
-                word |= (v[i] > 0.f ? 1u : 0u) << i;
-                v[i] = fmaxf(v[i], 0.f);
+            for (int i = 0; i < 8; ++i) {
+                const float4 bb = __ldg(reinterpret_cast<const float4*>(p.bias1 + cc * 32) + i);
+                v[4 * i] += bb.x; v[4 * i + 1] += bb.y; v[4 * i + 2] += bb.z; v[4 * i + 3] += bb.w;
             }
-            mw[cc] = word;
-            uint8_t* half = rt + (cc >> 1) * 2 * TILE16;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const uint32_t off = sw128_off(r, (cc & 1) * 4 + i);
-                float hi[8];
-#pragma unroll
-                for (int e = 0; e < 8; ++e) hi[e] = bf16_round(v[8 * i + e]);
-                *reinterpret_cast<uint4*>(half + off) = make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]),
-                                                                  pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
-                *reinterpret_cast<uint4*>(half + TILE16 + off) =
-                    make_uint4(pack_bf16(v[8 * i] - hi[0], v[8 * i + 1] - hi[1]), pack_bf16(v[8 * i + 2] - hi[2], v[8 * i + 3] - hi[3]),
-                               pack_bf16(v[8 * i + 4] - hi[4], v[8 * i + 5] - hi[5]), pack_bf16(v[8 * i + 6] - hi[6], v[8 * i + 7] - hi[7]));
-            }
+            for (int i = 0; i < 32; ++i) { word |= (v[i] > 0.f ? 1u : 0u) << i; v[i] = fmaxf(v[i], 0.f); }
+            stage_hi_lo(rt, rt + TILE16, r, (cc & 1) * 4, v);
+            fence_proxy_async_smem();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar + FB_RT(half));
+            p.zmask_out[row * AST_MW + cc] = word;
         }
-        fence_proxy_async_smem();
-        tc_fence_before();
-        mbar_arrive(bar + B_RT);
-        *reinterpret_cast<uint4*>(p.zmask_out + row * AST_MW) = make_uint4(mw[0], mw[1], mw[2], mw[3]);
+        if (threadIdx.x == 64) TL(25);
 
-        // ---- epilogue 2: h' = h + (acc2 + br) in place in smem; relu(h') hi/lo -> RT; masks ---------
-        mbar_wait(bar + B_ACC2, 0);
+        // ---- epilogue 2: h' = h + (acc2 + br) in place in smem; bf16(h'); relu(h') hi/lo -> RT; mask ----
+        mbar_wait(bar + FB_ACC2, 0);
         tc_fence_after();
-        {   // residual tile landed: the last fill of each stage (fill index = number of live taps)
-            const uint32_t par = (uint32_t)(tap_live(t0, 0, p.shift, p.T) + 1 + tap_live(t0, 2, p.shift, p.T)) & 1u;
-            mbar_wait(bar + B_FULL(0), par);
-            mbar_wait(bar + B_FULL(1), par);
-        }
-#pragma unroll
-        for (int cc = 0; cc < 4; ++cc) {
-            tmem_ld32(acc2 + lane_off + cc * 32, v);
-            uint8_t* hcg = gen + (cc >> 1) * FWD_STAGE + (cc & 1) * TILE16;      // fp32 column group cc
-            uint32_t word = 0;
+        if (threadIdx.x == 64) TL(26);
+        // residual tile landed: last fill of slot `half` (fill index = its number of GEMM1 slices)
+        mbar_wait(bar + FB_FULL(half), (uint32_t)((n1 - half + 2) / 3) & 1u);
+        if (threadIdx.x == 64) TL(27);
+        tmem_ld32(acc2 + lane_off + cc * 32, v);
+        if (threadIdx.x == 64) TL(40);
+        {
+            uint8_t* hcg = gen + half * FWD_STAGE + (cc & 1) * TILE16;           // fp32 column group cc
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 float4* hp = reinterpret_cast<float4*>(hcg + sw128_off(r, i));
@@ -231,53 +259,37 @@ __global__ void __launch_bounds__(192, 1) tc_fwd_kernel(const __grid_constant__ 
                 v[4 * i + 2] = h.z + (v[4 * i + 2] + bb.z); v[4 * i + 3] = h.w + (v[4 * i + 3] + bb.w);
                 *hp = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
             }
-            if (p.f_slot >= 0) {                                   // bf16(h') for the Gram head, staged in the dead W2 tile
-                uint8_t* fh = gen + (cc >> 1) * FWD_STAGE + 2 * TILE16;
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    *reinterpret_cast<uint4*>(fh + sw128_off(r, (cc & 1) * 4 + i)) =
-                        make_uint4(pack_bf16(v[8 * i], v[8 * i + 1]), pack_bf16(v[8 * i + 2], v[8 * i + 3]),
-                                   pack_bf16(v[8 * i + 4], v[8 * i + 5]), pack_bf16(v[8 * i + 6], v[8 * i + 7]));
-            }
+            if (threadIdx.x == 64) TL(41);
+            if (p.f_slot >= 0) stage_bf16(gen + half * FWD_STAGE + 2 * TILE16, r, (cc & 1) * 4, v);
+            uint32_t word = 0;
 #pragma unroll
             for (int i = 0; i < 32; ++i) { word |= (v[i] > 0.f ? 1u : 0u) << i; v[i] = fmaxf(v[i], 0.f); }
-            mw[cc] = word;
-            uint8_t* half = rt + (cc >> 1) * 2 * TILE16;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const uint32_t off = sw128_off(r, (cc & 1) * 4 + i);
-                float hi[8];
-#pragma unroll
-                for (int e = 0; e < 8; ++e) hi[e] = bf16_round(v[8 * i + e]);
-                *reinterpret_cast<uint4*>(half + off) = make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]),
-                                                                  pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
-                *reinterpret_cast<uint4*>(half + TILE16 + off) =
-                    make_uint4(pack_bf16(v[8 * i] - hi[0], v[8 * i + 1] - hi[1]), pack_bf16(v[8 * i + 2] - hi[2], v[8 * i + 3] - hi[3]),
-                               pack_bf16(v[8 * i + 4] - hi[4], v[8 * i + 5] - hi[5]), pack_bf16(v[8 * i + 6] - hi[6], v[8 * i + 7] - hi[7]));
-            }
+            if (threadIdx.x == 64) TL(42);
+            stage_hi_lo(rt, rt + TILE16, r, (cc & 1) * 4, v);
+            if (threadIdx.x == 64) TL(43);
+            p.hmask_out[row * AST_MW + cc] = word;
         }
-        *reinterpret_cast<uint4*>(p.hmask_out + row * AST_MW) = make_uint4(mw[0], mw[1], mw[2], mw[3]);
+        if (threadIdx.x == 64) TL(44);
         fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0) {                                           // this warp's 32-row slab of every output tile
-            const int tr = t0 + q * 32;
-            const uint32_t slab = (uint32_t)q * 4096;
-#pragma unroll
-            for (int cc = 0; cc < 4; ++cc)
-                tma_store_4d(&p.tmH_st, base + (cc >> 1) * FWD_STAGE + (cc & 1) * TILE16 + slab, cc * 32, tr, b, p.l + 1);
-#pragma unroll
-            for (int j = 0; j < 2; ++j) {
-                tma_store_4d(&p.tmAo_hi, s_rt + j * 2 * TILE16 + slab, j * 64, tr, b, p.a_out);
-                tma_store_4d(&p.tmAo_lo, s_rt + j * 2 * TILE16 + TILE16 + slab, j * 64, tr, b, p.a_out);
-                if (p.f_slot >= 0) tma_store_4d(&p.tmF_st, base + j * FWD_STAGE + 2 * TILE16 + slab, j * 64, tr, b, p.f_slot);
-            }
+        if (threadIdx.x == 64) TL(28);
+        // the 8 warps of this 64-column half are done: one thread stores the half's tiles
+        named_bar_sync(1 + half, 256);
+        if (q == 0 && (cc & 1) == 0 && lane == 0) {
+            const uint32_t st = base + half * FWD_STAGE;
+            tma_store_4d(&p.tmH, st, (2 * half) * 32, t0, b, p.l + 1);
+            tma_store_4d(&p.tmH, st + TILE16, (2 * half + 1) * 32, t0, b, p.l + 1);
+            tma_store_4d(&p.tmA_hi, s_rt + half * 2 * TILE16, half * 64, t0, b, p.a_out);
+            tma_store_4d(&p.tmA_lo, s_rt + half * 2 * TILE16 + TILE16, half * 64, t0, b, p.a_out);
+            if (p.f_slot >= 0) tma_store_4d(&p.tmF, st + 2 * TILE16, half * 64, t0, b, p.f_slot);
             tma_store_commit();
-            tma_store_wait_all();
+            if (half == 0) TL(29);
+            tma_store_wait_read();
+            if (half == 0) TL(30);
         }
-        __syncwarp();
     }
     tc_fence_before();
     __syncthreads();
+    if (threadIdx.x == 0) TL(31);
     if (warp == 1) tmem_dealloc<256>(tmem);
 }
 
@@ -285,9 +297,9 @@ __global__ void __launch_bounds__(192, 1) tc_fwd_kernel(const __grid_constant__ 
 // backward boundary l (between layer l-1 and layer l), plain bf16 operands
 // =============================================================================================
 struct alignas(64) BwdArgs {
-    CUtensorMap tmDz_ld, tmDz_st;    // bf16 dz ping-pong [2][B][T][128]: box {64,128,1,1} / {64,32,1,1}
-    CUtensorMap tmG_ld, tmG_st;      // fp32 running gradient [1][B][T][128]: box {32,128,1,1} / {32,32,1,1}
-    CUtensorMap tmDF_ld;             // fp32 head gradients [n_head][B][T][128], box {32,128,1,1}
+    CUtensorMap tmDz;                // bf16 dz ping-pong [2][B][T][128], box {64,128,1,1} (loads and stores)
+    CUtensorMap tmG;                 // fp32 running gradient [1][B][T][128], box {32,128,1,1} (loads and stores)
+    CUtensorMap tmDF;                // fp32 head gradients [n_head][B][T][128], box {32,128,1,1}
     CUtensorMap tmW1, tmW2;
     int w1_row, w2_row;
     int T, shift;                    // tap k reads dz row t + (k-1)*shift, shift = -d
@@ -295,146 +307,143 @@ struct alignas(64) BwdArgs {
     int dz_in, dz_out;
     const uint32_t* hmask_in; const uint32_t* zmask_in;
 };
-// smem: 2 stages x (A 16 KB | W 16 KB) | RT 32 KB (bf16 g, 2 K-halves) | G 64 KB (fp32, in place) | DF 64 KB
+// smem: slots 0,1,2 x (A 16 KB | W 16 KB) | G 64 KB (fp32, updated in place) | DF 64 KB (head gradient, then dz staging)
+// Slot 2 is a pipeline stage during GEMM1, then RT = bf16(g') (A operand of the 1x1 GEMM, 2 K-halves).
 #define BWD_STAGE 32768
-#define BWD_RT (2 * BWD_STAGE)
-#define BWD_G (BWD_RT + 32768)
+#define BWD_G (3 * BWD_STAGE)
 #define BWD_DF (BWD_G + 65536)
 #define BWD_SMEM (BWD_DF + 65536 + 1024 + 128)
+#define BWD_THREADS 576
+#define BB_IO 88u
 
-__global__ void __launch_bounds__(192, 1) tc_bwd_kernel(const __grid_constant__ BwdArgs p) {
+__global__ void __launch_bounds__(BWD_THREADS, 1) tc_bwd_kernel(const __grid_constant__ BwdArgs p) {
     extern __shared__ uint8_t tc_smem_raw[];
     const uint32_t base = (smem_u32(tc_smem_raw) + 1023u) & ~1023u;
     uint8_t* gen = tc_smem_raw + (base - smem_u32(tc_smem_raw));
-    const uint32_t s_rt = base + BWD_RT, s_g = base + BWD_G, s_df = base + BWD_DF, bar = s_df + 65536;
+    const uint32_t s_rt = base + 2 * BWD_STAGE, s_g = base + BWD_G, s_df = base + BWD_DF, bar = s_df + 65536;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int row0 = blockIdx.x * 128;
     const int b = row0 / p.T, t0 = row0 - b * p.T;
     const bool has_io = !p.g_init || p.df_idx >= 0;
+    const int n1 = p.do_gemm1 ? 2 * ((int)tap_live(t0, 0, p.shift, p.T) + 1 + (int)tap_live(t0, 2, p.shift, p.T)) : 0;
 
     if (warp == 0 && lane == 0) {
-        tma_prefetch_desc(&p.tmDz_ld); tma_prefetch_desc(&p.tmW1); tma_prefetch_desc(&p.tmW2); tma_prefetch_desc(&p.tmG_ld);
-        tma_prefetch_desc(&p.tmG_st); tma_prefetch_desc(&p.tmDF_ld); tma_prefetch_desc(&p.tmDz_st);
-        for (int i = 0; i < 2; ++i) { mbar_init(bar + B_FULL(i), 1); mbar_init(bar + B_EMPTY(i), 1); }
-        mbar_init(bar + B_ACC1, 1); mbar_init(bar + B_RT, 128); mbar_init(bar + B_ACC2, 1); mbar_init(bar + B_IO, 1);
+        tma_prefetch_desc(&p.tmDz); tma_prefetch_desc(&p.tmW1); tma_prefetch_desc(&p.tmW2); tma_prefetch_desc(&p.tmG);
+        tma_prefetch_desc(&p.tmDF);
+        for (int i = 0; i < 3; ++i) { mbar_init(bar + FB_FULL(i), 1); mbar_init(bar + FB_EMPTY(i), 1); }
+        mbar_init(bar + FB_ACC1, 1); mbar_init(bar + FB_RT(0), 8); mbar_init(bar + FB_RT(1), 8); mbar_init(bar + FB_ACC2, 1);
+        mbar_init(bar + BB_IO, 1);
         mbar_init_fence();
     }
-    if (warp == 1) tmem_alloc<256>(bar + B_TMEM);
+    if (warp == 1) tmem_alloc<256>(bar + FB_TMEM);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gen + (bar + B_TMEM - base));
+    const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gen + (bar + FB_TMEM - base));
     const uint32_t acc1 = tmem, acc2 = tmem + 128;
+    pdl_launch_dependents();
+    pdl_wait();
 
     if (warp == 0) {
         // ================================ TMA producer ========================================
         if (lane == 0) {
+            int fills[3] = {0, 0, 0};
             int it = 0;
             bool io_sent = !has_io;
             auto send_io = [&]() {
                 if (io_sent) return;
                 io_sent = true;
-                mbar_expect_tx(bar + B_IO, (uint32_t)((p.g_init ? 0 : 4) + (p.df_idx >= 0 ? 4 : 0)) * TILE16);
+                mbar_expect_tx(bar + BB_IO, (uint32_t)((p.g_init ? 0 : 4) + (p.df_idx >= 0 ? 4 : 0)) * TILE16);
                 if (!p.g_init)
-                    for (int cg = 0; cg < 4; ++cg) tma_load_4d(s_g + cg * TILE16, &p.tmG_ld, bar + B_IO, cg * 32, t0, b, 0);
+                    for (int cg = 0; cg < 4; ++cg) tma_load_4d(s_g + cg * TILE16, &p.tmG, bar + BB_IO, cg * 32, t0, b, 0);
                 if (p.df_idx >= 0)
-                    for (int cg = 0; cg < 4; ++cg) tma_load_4d(s_df + cg * TILE16, &p.tmDF_ld, bar + B_IO, cg * 32, t0, b, p.df_idx);
+                    for (int cg = 0; cg < 4; ++cg) tma_load_4d(s_df + cg * TILE16, &p.tmDF, bar + BB_IO, cg * 32, t0, b, p.df_idx);
             };
             if (p.do_gemm1) {
                 for (int k = 0; k < 3; ++k) {
                     if (!tap_live(t0, k, p.shift, p.T)) continue;
                     const int t = t0 + (k - 1) * p.shift;
                     for (int j = 0; j < 2; ++j, ++it) {
-                        const int slot = it & 1;
-                        if (it == 2) send_io();          // after the first two operand stages are in flight
-                        mbar_wait(bar + B_EMPTY(slot), ((it >> 1) & 1) ^ 1);
-                        const uint32_t st = base + slot * BWD_STAGE, fb = bar + B_FULL(slot);
+                        const int slot = it % 3;
+                        if (it == 3) send_io();          // after the first three operand stages are in flight
+                        mbar_wait(bar + FB_EMPTY(slot), (fills[slot] & 1) ^ 1);
+                        ++fills[slot];
+                        const uint32_t st = base + slot * BWD_STAGE, fb = bar + FB_FULL(slot);
                         mbar_expect_tx(fb, 2 * TILE16);
-                        tma_load_4d(st, &p.tmDz_ld, fb, j * 64, t, b, p.dz_in);
+                        tma_load_4d(st, &p.tmDz, fb, j * 64, t, b, p.dz_in);
                         tma_load_2d(st + TILE16, &p.tmW1, fb, j * 64, p.w1_row + k * 128);
                     }
                 }
             }
             send_io();
-            if (p.do_gemm2) {
-                for (int j = 0; j < 2; ++j, ++it) {
-                    const int slot = it & 1;
-                    mbar_wait(bar + B_EMPTY(slot), ((it >> 1) & 1) ^ 1);
-                    const uint32_t st = base + slot * BWD_STAGE, fb = bar + B_FULL(slot);
+            if (p.do_gemm2) {                            // Wr^T K-halves into the W part of slots 0 and 1
+                for (int j = 0; j < 2; ++j) {
+                    mbar_wait(bar + FB_EMPTY(j), (fills[j] & 1) ^ 1);
+                    ++fills[j];
+                    const uint32_t fb = bar + FB_FULL(j);
                     mbar_expect_tx(fb, TILE16);
-                    tma_load_2d(st + TILE16, &p.tmW2, fb, j * 64, p.w2_row);
+                    tma_load_2d(base + j * BWD_STAGE + TILE16, &p.tmW2, fb, j * 64, p.w2_row);
                 }
             }
         }
     } else if (warp == 1) {
         // ================================ MMA issuer ==========================================
         if (lane == 0) {
-            int it = 0;
+            int uses[3] = {0, 0, 0};
             if (p.do_gemm1) {
                 uint32_t accum = 0;
-                for (int k = 0; k < 3; ++k) {
-                    if (!tap_live(t0, k, p.shift, p.T)) continue;
-                    for (int j = 0; j < 2; ++j, ++it) {
-                        const int slot = it & 1;
-                        mbar_wait(bar + B_FULL(slot), (it >> 1) & 1);
-                        tc_fence_after();
-                        const uint32_t st = base + slot * BWD_STAGE;
-#pragma unroll
-                        for (int kk = 0; kk < 4; ++kk) {
-                            umma_f16(acc1, umma_desc_kmajor_sw128(st + kk * 32), umma_desc_kmajor_sw128(st + TILE16 + kk * 32), IDESC, accum);
-                            accum = 1u;
-                        }
-                        umma_commit(bar + B_EMPTY(slot));
-                    }
-                }
-                umma_commit(bar + B_ACC1);
-            }
-            if (p.do_gemm2) {
-                mbar_wait(bar + B_RT, 0);
-                tc_fence_after();
-                for (int j = 0; j < 2; ++j, ++it) {
-                    const int slot = it & 1;
-                    mbar_wait(bar + B_FULL(slot), (it >> 1) & 1);
+                for (int it = 0; it < n1; ++it) {
+                    const int slot = it % 3;
+                    mbar_wait(bar + FB_FULL(slot), uses[slot] & 1);
+                    ++uses[slot];
                     tc_fence_after();
                     const uint32_t st = base + slot * BWD_STAGE;
 #pragma unroll
+                    for (int kk = 0; kk < 4; ++kk) {
+                        umma_f16(acc1, umma_desc_kmajor_sw128(st + kk * 32), umma_desc_kmajor_sw128(st + TILE16 + kk * 32), IDESC, accum);
+                        accum = 1u;
+                    }
+                    umma_commit(bar + FB_EMPTY(slot));
+                }
+                umma_commit(bar + FB_ACC1);
+            }
+            if (p.do_gemm2) {
+                for (int j = 0; j < 2; ++j) {
+                    mbar_wait(bar + FB_RT(j), 0);
+                    mbar_wait(bar + FB_FULL(j), uses[j] & 1);
+                    tc_fence_after();
+#pragma unroll
                     for (int kk = 0; kk < 4; ++kk)
                         umma_f16(acc2, umma_desc_kmajor_sw128(s_rt + j * TILE16 + kk * 32),
-                                 umma_desc_kmajor_sw128(st + TILE16 + kk * 32), IDESC, (j > 0 || kk > 0) ? 1u : 0u);
+                                 umma_desc_kmajor_sw128(base + j * BWD_STAGE + TILE16 + kk * 32), IDESC, (j > 0 || kk > 0) ? 1u : 0u);
                 }
-                umma_commit(bar + B_ACC2);
+                umma_commit(bar + FB_ACC2);
             }
         }
         __syncwarp();
     } else {
         // ================================ epilogue warps ======================================
-        const int q = warp & 3;
+        const int q = warp & 3, cc = (warp - 2) >> 2, half = cc >> 1;
         const int r = q * 32 + lane;
         const size_t row = (size_t)row0 + r;
         const uint32_t lane_off = (uint32_t)(q * 32) << 16;
-        const int tr = t0 + q * 32;
-        const uint32_t slab = (uint32_t)q * 4096;
         float v[32];
-        uint32_t mw[4] = {0, 0, 0, 0};
 
         // ---- epilogue 1: g' = g + acc1 * [h>0] + dF, in place in smem -> TMA store; bf16(g') -> RT ----
+        uint32_t mask = 0;
         if (p.do_gemm1) {
-            const uint4 m = *reinterpret_cast<const uint4*>(p.hmask_in + row * AST_MW);
-            mw[0] = m.x; mw[1] = m.y; mw[2] = m.z; mw[3] = m.w;
-            mbar_wait(bar + B_ACC1, 0);
+            mask = p.hmask_in[row * AST_MW + cc];
+            mbar_wait(bar + FB_ACC1, 0);
             tc_fence_after();
+            tmem_ld32(acc1 + lane_off + cc * 32, v);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) if (!((mask >> i) & 1u)) v[i] = 0.f;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = 0.f;
         }
-        if (has_io) mbar_wait(bar + B_IO, 0);
-#pragma unroll
-        for (int cc = 0; cc < 4; ++cc) {
-            if (p.do_gemm1) {
-                tmem_ld32(acc1 + lane_off + cc * 32, v);
-#pragma unroll
-                for (int i = 0; i < 32; ++i) if (!((mw[cc] >> i) & 1u)) v[i] = 0.f;
-            } else {
-#pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] = 0.f;
-            }
+        if (has_io) mbar_wait(bar + BB_IO, 0);
+        {
             uint8_t* gcg = gen + BWD_G + cc * TILE16;
             const uint8_t* dcg = gen + BWD_DF + cc * TILE16;
 #pragma unroll
@@ -450,51 +459,38 @@ __global__ void __launch_bounds__(192, 1) tc_bwd_kernel(const __grid_constant__ 
                 }
                 *reinterpret_cast<float4*>(gcg + off) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
             }
-            if (p.do_gemm2) {
-                uint8_t* half = gen + BWD_RT + (cc >> 1) * TILE16;
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    *reinterpret_cast<uint4*>(half + sw128_off(r, (cc & 1) * 4 + i)) =
-                        make_uint4(pack_bf16(v[8 * i], v[8 * i + 1]), pack_bf16(v[8 * i + 2], v[8 * i + 3]),
-                                   pack_bf16(v[8 * i + 4], v[8 * i + 5]), pack_bf16(v[8 * i + 6], v[8 * i + 7]));
-            }
+            if (p.do_gemm2) stage_bf16(gen + 2 * BWD_STAGE + half * TILE16, r, (cc & 1) * 4, v);
         }
         fence_proxy_async_smem();
-        if (p.do_gemm2) { tc_fence_before(); mbar_arrive(bar + B_RT); }
-        __syncwarp();
-        if (lane == 0) {
-#pragma unroll
-            for (int cc = 0; cc < 4; ++cc) tma_store_4d(&p.tmG_st, s_g + cc * TILE16 + slab, cc * 32, tr, b, 0);
+        if (p.do_gemm2) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar + FB_RT(half));
+        }
+        named_bar_sync(1 + cc, 128);                       // the 4 quadrant warps of this column group
+        if (q == 0 && lane == 0) {
+            tma_store_4d(&p.tmG, s_g + cc * TILE16, cc * 32, t0, b, 0);
             tma_store_commit();
         }
         if (p.do_gemm2) {
             // ---- epilogue 2: dz = acc2 * [z>0] -> bf16, staged in the (now free) DF region -------------
-            const uint4 m = *reinterpret_cast<const uint4*>(p.zmask_in + row * AST_MW);
-            mw[0] = m.x; mw[1] = m.y; mw[2] = m.z; mw[3] = m.w;
-            mbar_wait(bar + B_ACC2, 0);
+            mask = p.zmask_in[row * AST_MW + cc];
+            mbar_wait(bar + FB_ACC2, 0);
             tc_fence_after();
+            tmem_ld32(acc2 + lane_off + cc * 32, v);
 #pragma unroll
-            for (int cc = 0; cc < 4; ++cc) {
-                tmem_ld32(acc2 + lane_off + cc * 32, v);
-#pragma unroll
-                for (int i = 0; i < 32; ++i) if (!((mw[cc] >> i) & 1u)) v[i] = 0.f;
-                uint8_t* half = gen + BWD_DF + (cc >> 1) * TILE16;
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    *reinterpret_cast<uint4*>(half + sw128_off(r, (cc & 1) * 4 + i)) =
-                        make_uint4(pack_bf16(v[8 * i], v[8 * i + 1]), pack_bf16(v[8 * i + 2], v[8 * i + 3]),
-                                   pack_bf16(v[8 * i + 4], v[8 * i + 5]), pack_bf16(v[8 * i + 6], v[8 * i + 7]));
-            }
+            for (int i = 0; i < 32; ++i) if (!((mask >> i) & 1u)) v[i] = 0.f;
+            // every warp of this half must have finished READING the DF tile before it is overwritten:
+            // acc2 is complete only after all 16 warps arrived on RT, i.e. after their epilogue-1 reads
+            stage_bf16(gen + BWD_DF + half * TILE16, r, (cc & 1) * 4, v);
             fence_proxy_async_smem();
-            __syncwarp();
-            if (lane == 0) {
-#pragma unroll
-                for (int j = 0; j < 2; ++j) tma_store_4d(&p.tmDz_st, s_df + j * TILE16 + slab, j * 64, tr, b, p.dz_out);
+            named_bar_sync(5 + half, 256);
+            if (q == 0 && (cc & 1) == 0 && lane == 0) {
+                tma_store_4d(&p.tmDz, s_df + half * TILE16, half * 64, t0, b, p.dz_out);
                 tma_store_commit();
             }
         }
-        if (lane == 0) tma_store_wait_all();
-        __syncwarp();
+        if (q == 0 && lane == 0) tma_store_wait_read();
     }
     tc_fence_before();
     __syncthreads();
@@ -541,9 +537,8 @@ struct TcState {
     __nv_bfloat16 *w1f, *w2f, *w1b, *w2b;
     __nv_bfloat16 *F, *ssym;                   // Gatys head: bf16 extracts [n_fslots][R][128], bf16 Ssym [B*n_fslots][128][128]
     int n_fslots;
-    CUtensorMap tm_F_st, tm_F_ld, tm_ssym, tm_gpart, tm_dF_st;
-    CUtensorMap tm_a_hi_ld, tm_a_lo_ld, tm_a_hi_st, tm_a_lo_st, tm_dz_ld, tm_dz_st;
-    CUtensorMap tm_H_ld, tm_H_st, tm_g_ld, tm_g_st, tm_dF_ld;
+    CUtensorMap tm_F, tm_ssym, tm_gpart, tm_dF_st;
+    CUtensorMap tm_a_hi, tm_a_lo, tm_dz, tm_H, tm_g, tm_dF;      // box = 128 rows x 128 bytes, loads and stores
     CUtensorMap tm_w1f, tm_w2f, tm_w1b, tm_w2b;
     int cur;                       // dz buffer holding the most recent backward output
 };
@@ -605,12 +600,9 @@ TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_he
               cudaMalloc(&s->w2b, mat * NL) == cudaSuccess;
     if (!ok) { *why = "cudaMalloc failed"; tc_destroy(s); return nullptr; }
     *bytes += (int64_t)(3 * act + mat * NL * 12);
-    ok = make_act_map(&s->tm_a_hi_ld, s->a_hi, false, T, B, 2, 128) && make_act_map(&s->tm_a_hi_st, s->a_hi, false, T, B, 2, 32) &&
-         make_act_map(&s->tm_a_lo_ld, s->a_lo, false, T, B, 2, 128) && make_act_map(&s->tm_a_lo_st, s->a_lo, false, T, B, 2, 32) &&
-         make_act_map(&s->tm_dz_ld, s->dz, false, T, B, 2, 128) && make_act_map(&s->tm_dz_st, s->dz, false, T, B, 2, 32) &&
-         make_act_map(&s->tm_H_ld, H, true, T, B, NL + 1, 128) && make_act_map(&s->tm_H_st, H, true, T, B, NL + 1, 32) &&
-         make_act_map(&s->tm_g_ld, g, true, T, B, 1, 128) && make_act_map(&s->tm_g_st, g, true, T, B, 1, 32) &&
-         make_act_map(&s->tm_dF_ld, dF, true, T, B, n_head > 0 ? n_head : 1, 128) &&
+    ok = make_act_map(&s->tm_a_hi, s->a_hi, false, T, B, 2, 128) && make_act_map(&s->tm_a_lo, s->a_lo, false, T, B, 2, 128) &&
+         make_act_map(&s->tm_dz, s->dz, false, T, B, 2, 128) && make_act_map(&s->tm_H, H, true, T, B, NL + 1, 128) &&
+         make_act_map(&s->tm_g, g, true, T, B, 1, 128) && make_act_map(&s->tm_dF, dF, true, T, B, n_head > 0 ? n_head : 1, 128) &&
          make_w_map(&s->tm_w1f, s->w1f, (size_t)NL * 3 * 2 * AST_C) && make_w_map(&s->tm_w2f, s->w2f, (size_t)NL * 2 * AST_C) &&
          make_w_map(&s->tm_w1b, s->w1b, (size_t)NL * 3 * AST_C) && make_w_map(&s->tm_w2b, s->w2b, (size_t)NL * AST_C);
     s->n_fslots = n_fslots;
@@ -620,7 +612,7 @@ TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_he
             *why = "cudaMalloc failed"; tc_destroy(s); return nullptr;
         }
         *bytes += (int64_t)(fb + sb);
-        ok = make_act_map(&s->tm_F_st, s->F, false, T, B, n_fslots, 32) && make_act_map(&s->tm_F_ld, s->F, false, T, B, n_fslots, 128) &&
+        ok = make_act_map(&s->tm_F, s->F, false, T, B, n_fslots, 128) &&
              make_rows_map(&s->tm_ssym, s->ssym, false, (size_t)B * n_fslots * AST_C, 128) &&
              make_rows_map(&s->tm_gpart, gram_part, true, (size_t)gram_part_mats * AST_C, 32) &&
              make_act_map(&s->tm_dF_st, dF, true, T, B, n_head > 0 ? n_head : 1, 32) && setup_gram_tc_kernels() == 0;
@@ -662,14 +654,13 @@ void tc_layer_fwd(TcState* s, int l, const float* bd, const float* br, uint32_t*
                   int f_slot, cudaStream_t st) {
     FwdArgs a;
     memset(&a, 0, sizeof(a));
-    a.tmA_hi = s->tm_a_hi_ld; a.tmA_lo = s->tm_a_lo_ld; a.tmAo_hi = s->tm_a_hi_st; a.tmAo_lo = s->tm_a_lo_st;
-    a.tmH_ld = s->tm_H_ld; a.tmH_st = s->tm_H_st; a.tmW1 = s->tm_w1f; a.tmW2 = s->tm_w2f;
+    a.tmA_hi = s->tm_a_hi; a.tmA_lo = s->tm_a_lo; a.tmH = s->tm_H; a.tmW1 = s->tm_w1f; a.tmW2 = s->tm_w2f;
     a.w1_row = l * 3 * 2 * AST_C; a.w2_row = l * 2 * AST_C;
     a.T = s->T; a.shift = 1 << (l % 10); a.l = l; a.a_in = l & 1; a.a_out = (l & 1) ^ 1;
     a.bias1 = bd; a.bias2 = br; a.zmask_out = zmask_out; a.hmask_out = hmask_out;
     a.f_slot = (s->n_fslots > 0) ? f_slot : -1;
-    if (a.f_slot >= 0) a.tmF_st = s->tm_F_st;
-    tc_fwd_kernel<<<s->R / 128, 192, FWD_SMEM, st>>>(a);
+    if (a.f_slot >= 0) a.tmF = s->tm_F;
+    launch_pdl(tc_fwd_kernel, dim3(s->R / 128), dim3(FWD_THREADS), FWD_SMEM, st, a);
     ast_launch_counter += 1;
 }
 
@@ -677,14 +668,14 @@ void tc_layer_bwd(TcState* s, int l, const uint32_t* hmask_in, int df_idx, const
     BwdArgs a;
     memset(&a, 0, sizeof(a));
     if (l == s->NL) s->cur = 0;                 // top of the stack: (re)start the dz ping-pong
-    a.tmDz_ld = s->tm_dz_ld; a.tmDz_st = s->tm_dz_st; a.tmG_ld = s->tm_g_ld; a.tmG_st = s->tm_g_st; a.tmDF_ld = s->tm_dF_ld;
+    a.tmDz = s->tm_dz; a.tmG = s->tm_g; a.tmDF = s->tm_dF;
     a.tmW1 = s->tm_w1b; a.tmW2 = s->tm_w2b;
     a.T = s->T; a.df_idx = df_idx; a.hmask_in = hmask_in; a.zmask_in = zmask_in;
     a.dz_in = s->cur; a.dz_out = s->cur ^ 1;
     if (l < s->NL) { a.do_gemm1 = 1; a.w1_row = l * 3 * AST_C; a.shift = -(1 << (l % 10)); }
     else a.g_init = 1;
     if (l >= 1) { a.do_gemm2 = 1; a.w2_row = (l - 1) * AST_C; }
-    tc_bwd_kernel<<<s->R / 128, 192, BWD_SMEM, st>>>(a);
+    launch_pdl(tc_bwd_kernel, dim3(s->R / 128), dim3(BWD_THREADS), BWD_SMEM, st, a);
     ast_launch_counter += 1;
     s->cur ^= 1;
 }
@@ -693,7 +684,7 @@ void tc_layer_bwd(TcState* s, int l, const uint32_t* hmask_in, int df_idx, const
 void tc_gram(TcState* s, int L, int nchunk, int chunk_tiles, int tile_lo, int tile_hi, cudaStream_t st) {
     GramTcArgs a;
     memset(&a, 0, sizeof(a));
-    a.tmF = s->tm_F_ld; a.tmP = s->tm_gpart;
+    a.tmF = s->tm_F; a.tmP = s->tm_gpart;
     a.L = L; a.chunk_tiles = chunk_tiles; a.tile_lo = tile_lo; a.tile_hi = tile_hi;
     launch_gram_tc(a, nchunk, L, s->B, st);
 }
@@ -701,7 +692,7 @@ __nv_bfloat16* tc_ssym_bf16(TcState* s) { return s ? s->ssym : nullptr; }
 void tc_style_grad(TcState* s, int L, const int* head_of_slot, cudaStream_t st) {
     SGradTcArgs a;
     memset(&a, 0, sizeof(a));
-    a.tmF = s->tm_F_ld; a.tmS = s->tm_ssym; a.tmDF = s->tm_dF_st;
+    a.tmF = s->tm_F; a.tmS = s->tm_ssym; a.tmDF = s->tm_dF_st;
     a.T = s->T; a.L = L;
     for (int i = 0; i < L && i < 32; ++i) a.head_of_slot[i] = head_of_slot[i];
     launch_sgrad_tc(a, s->R / 128, L, st);
