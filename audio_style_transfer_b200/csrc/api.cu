@@ -210,7 +210,7 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
         }
         c->gram_chunk_rows = rows;
         c->gram_nchunk = (c->T + rows - 1) / rows;
-        c->sse_nblk = 64;
+        c->sse_nblk = 296;                     // 2 CTAs per SM
     }
 
     const size_t RC = (size_t)c->R * AST_C;
@@ -376,7 +376,17 @@ extern "C" int ast_step_backward(ast_ctx* c, float* d_losses, float* d_grad, voi
     if (!c->have_w || !c->have_t) return fail(AST_ESTATE, "ast_set_weights and ast_set_targets must precede a step");
     cudaStream_t s = (cudaStream_t)stream;
     launch_heads(head_args(c, true, d_losses), s);
-    if (c->cfg.gatys && c->tc) tc_style_grad(c->tc, c->L, c->head_of_slot, s);
+    // Gatys + tensor cores: the style gradient of an extract is fused into the backward layer kernel unless the
+    // same extract also carries a content term (then the standalone kernel fills its dF buffer first)
+    bool is_cont[30];
+    for (int l = 0; l < 30; ++l) is_cont[l] = false;
+    for (int i = 0; i < c->n_cont; ++i) is_cont[c->cont_layer[i]] = true;
+    const bool fuse_sg = c->cfg.gatys && c->tc;
+    if (fuse_sg) {
+        int hos[AST_MAX_IDS];
+        for (int i = 0; i < c->L; ++i) hos[i] = is_cont[c->style_layer[i]] ? c->head_of_slot[i] : -1;
+        tc_style_grad(c->tc, c->L, hos, s);
+    }
     else if (c->cfg.gatys) launch_style_grad_gatys(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
     else              launch_style_grad_ours(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
     {
@@ -395,8 +405,9 @@ extern "C" int ast_step_backward(ast_ctx* c, float* d_losses, float* d_grad, voi
     for (int l = c->NL; l >= 0; --l) {
         const float* dF = (l >= 1 && c->head_buf[l - 1] >= 0) ? dFb(c, c->head_buf[l - 1]) : nullptr;
         if (c->tc) {
-            tc_layer_bwd(c->tc, l, l < c->NL ? hm(c, l) : nullptr, (l >= 1) ? c->head_buf[l - 1] : -1,
-                         l >= 1 ? zm(c, l - 1) : nullptr, s);
+            int df_idx = (l >= 1) ? c->head_buf[l - 1] : -1, sg_slot = -1;
+            if (fuse_sg && l >= 1 && c->f_slot[l - 1] >= 0 && !is_cont[l - 1]) { sg_slot = c->f_slot[l - 1]; df_idx = -1; }
+            tc_layer_bwd(c->tc, l, l < c->NL ? hm(c, l) : nullptr, df_idx, sg_slot, c->L, l >= 1 ? zm(c, l - 1) : nullptr, s);
             continue;
         }
         LayerArgsF32 a;

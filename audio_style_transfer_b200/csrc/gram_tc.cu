@@ -129,6 +129,7 @@ __global__ void __launch_bounds__(192, 3) sgrad_tc_kernel(const __grid_constant_
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int row0 = blockIdx.x * 128, l = blockIdx.y;
     const int b = row0 / p.T, t0 = row0 - b * p.T;
+    if (p.head_of_slot[l] < 0) return;             // this slot's gradient is fused into the backward layer kernel
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&p.tmF); tma_prefetch_desc(&p.tmS); tma_prefetch_desc(&p.tmDF);

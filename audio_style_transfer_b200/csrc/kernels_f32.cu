@@ -478,8 +478,8 @@ __device__ __forceinline__ double block_sum_d(double v, double* red) {
     for (int i = 0; i < (int)(blockDim.x >> 5); ++i) t += red[i];
     return t;
 }
-__global__ void __launch_bounds__(256) heads_kernel(const HeadArgs a) {
-    __shared__ double red[8];
+__global__ void __launch_bounds__(1024) heads_kernel(const HeadArgs a) {
+    __shared__ double red[32];
     const int mat = blockIdx.x, b = blockIdx.y;
     const int n = a.n, msize = n * n;
     const float* G = a.G + ((size_t)b * a.nmat + mat) * msize;
@@ -539,7 +539,7 @@ __global__ void losses_final_kernel(const HeadArgs a) {
 }
 void launch_heads(const HeadArgs& a, cudaStream_t s) {
     dim3 grid(a.nmat, a.B);
-    heads_kernel<<<grid, 256, 0, s>>>(a);
+    heads_kernel<<<grid, a.n * a.n >= 4096 ? 1024 : 256, 0, s>>>(a);
     ast_launch_counter += 1;
     if (a.losses) { losses_final_kernel<<<a.B, 32, 0, s>>>(a); ast_launch_counter += 1; }
 }

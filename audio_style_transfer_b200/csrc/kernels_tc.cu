@@ -1,6 +1,6 @@
 // kernels_tc.cu -- the dilated-conv stack on 5th-gen tensor cores (sm_100a only): tcgen05.mma with TMEM
 // accumulators, every operand AND every activation tile moved by TMA (128B swizzle), warp-specialised
-// (warp 0 = TMA producer, warp 1 = MMA issuer, warps 2-5 = epilogue).
+// (warp 0 = TMA producer, warp 1 = MMA issuer, warps 2-17 = epilogue: TMEM lane quadrant x 32-column group).
 // One CTA = one 128-row time tile of one layer, two chained GEMMs:
 //   forward  (model.py:99-114):  z = conv3_d(relu(h)) + bd ; h' = h + relu(z) Wr + br
 //   backward :  g += conv3_d^T(dz_l) * [h_l>0] + dF ; dz_{l-1} = (g Wr_{l-1}^T) * [z_{l-1}>0]
@@ -301,13 +301,16 @@ struct alignas(64) BwdArgs {
     CUtensorMap tmG;                 // fp32 running gradient [1][B][T][128], box {32,128,1,1} (loads and stores)
     CUtensorMap tmDF;                // fp32 head gradients [n_head][B][T][128], box {32,128,1,1}
     CUtensorMap tmW1, tmW2;
+    CUtensorMap tmF, tmS;            // fused Gatys style gradient: bf16 extract F [L][B][T][128] and bf16 Ssym rows [B*L*128][128]
+    int sg_slot, sg_L;               // style slot whose gradient F.Ssym is added at this boundary (-1: none; excludes df_idx >= 0)
     int w1_row, w2_row;
     int T, shift;                    // tap k reads dz row t + (k-1)*shift, shift = -d
     int do_gemm1, do_gemm2, g_init, df_idx;      // df_idx < 0: no head gradient at this boundary
     int dz_in, dz_out;
     const uint32_t* hmask_in; const uint32_t* zmask_in;
 };
-// smem: slots 0,1,2 x (A 16 KB | W 16 KB) | G 64 KB (fp32, updated in place) | DF 64 KB (head gradient, then dz staging)
+// smem: slots 0,1,2 x (A 16 KB | W 16 KB) | G 64 KB (fp32, updated in place) | DF 64 KB (fp32 head gradient, OR the
+// operands F (2 K-halves) and Ssym (2 K-halves) of the fused style-gradient GEMM; then dz staging)
 // Slot 2 is a pipeline stage during GEMM1, then RT = bf16(g') (A operand of the 1x1 GEMM, 2 K-halves).
 #define BWD_STAGE 32768
 #define BWD_G (3 * BWD_STAGE)
@@ -324,23 +327,25 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) tc_bwd_kernel(const __grid_con
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int row0 = blockIdx.x * 128;
     const int b = row0 / p.T, t0 = row0 - b * p.T;
-    const bool has_io = !p.g_init || p.df_idx >= 0;
+    const bool has_io = !p.g_init || p.df_idx >= 0 || p.sg_slot >= 0;
     const int n1 = p.do_gemm1 ? 2 * ((int)tap_live(t0, 0, p.shift, p.T) + 1 + (int)tap_live(t0, 2, p.shift, p.T)) : 0;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&p.tmDz); tma_prefetch_desc(&p.tmW1); tma_prefetch_desc(&p.tmW2); tma_prefetch_desc(&p.tmG);
         tma_prefetch_desc(&p.tmDF);
+        if (p.sg_slot >= 0) { tma_prefetch_desc(&p.tmF); tma_prefetch_desc(&p.tmS); }
         for (int i = 0; i < 3; ++i) { mbar_init(bar + FB_FULL(i), 1); mbar_init(bar + FB_EMPTY(i), 1); }
         mbar_init(bar + FB_ACC1, 1); mbar_init(bar + FB_RT(0), 8); mbar_init(bar + FB_RT(1), 8); mbar_init(bar + FB_ACC2, 1);
         mbar_init(bar + BB_IO, 1);
         mbar_init_fence();
     }
-    if (warp == 1) tmem_alloc<256>(bar + FB_TMEM);
+    if (warp == 1) tmem_alloc<512>(bar + FB_TMEM);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gen + (bar + FB_TMEM - base));
-    const uint32_t acc1 = tmem, acc2 = tmem + 128;
+    const uint32_t acc1 = tmem, acc2 = tmem + 128, acc3 = tmem + 256;
+    const bool sg = p.sg_slot >= 0;
     pdl_launch_dependents();
     pdl_wait();
 
@@ -353,7 +358,12 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) tc_bwd_kernel(const __grid_con
             auto send_io = [&]() {
                 if (io_sent) return;
                 io_sent = true;
-                mbar_expect_tx(bar + BB_IO, (uint32_t)((p.g_init ? 0 : 4) + (p.df_idx >= 0 ? 4 : 0)) * TILE16);
+                mbar_expect_tx(bar + BB_IO, (uint32_t)((p.g_init ? 0 : 4) + (p.df_idx >= 0 ? 4 : 0) + (sg ? 4 : 0)) * TILE16);
+                if (sg)
+                    for (int j = 0; j < 2; ++j) {
+                        tma_load_4d(s_df + j * TILE16, &p.tmF, bar + BB_IO, j * 64, t0, b, p.sg_slot);
+                        tma_load_2d(s_df + (2 + j) * TILE16, &p.tmS, bar + BB_IO, j * 64, (b * p.sg_L + p.sg_slot) * 128);
+                    }
                 if (!p.g_init)
                     for (int cg = 0; cg < 4; ++cg) tma_load_4d(s_g + cg * TILE16, &p.tmG, bar + BB_IO, cg * 32, t0, b, 0);
                 if (p.df_idx >= 0)
@@ -405,8 +415,18 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) tc_bwd_kernel(const __grid_con
                     }
                     umma_commit(bar + FB_EMPTY(slot));
                 }
-                umma_commit(bar + FB_ACC1);
             }
+            if (sg) {                                    // acc3 = F_tile . Ssym  (the Gatys style gradient of this extract)
+                mbar_wait(bar + BB_IO, 0);
+                tc_fence_after();
+#pragma unroll
+                for (int j = 0; j < 2; ++j)
+#pragma unroll
+                    for (int kk = 0; kk < 4; ++kk)
+                        umma_f16(acc3, umma_desc_kmajor_sw128(s_df + j * TILE16 + kk * 32),
+                                 umma_desc_kmajor_sw128(s_df + (2 + j) * TILE16 + kk * 32), IDESC, (j > 0 || kk > 0) ? 1u : 0u);
+            }
+            if (p.do_gemm1 || sg) umma_commit(bar + FB_ACC1);
             if (p.do_gemm2) {
                 for (int j = 0; j < 2; ++j) {
                     mbar_wait(bar + FB_RT(j), 0);
@@ -431,16 +451,24 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) tc_bwd_kernel(const __grid_con
 
         // ---- epilogue 1: g' = g + acc1 * [h>0] + dF, in place in smem -> TMA store; bf16(g') -> RT ----
         uint32_t mask = 0;
-        if (p.do_gemm1) {
-            mask = p.hmask_in[row * AST_MW + cc];
+        if (p.do_gemm1) mask = p.hmask_in[row * AST_MW + cc];
+        if (p.do_gemm1 || sg) {
             mbar_wait(bar + FB_ACC1, 0);
             tc_fence_after();
+        }
+        if (p.do_gemm1) {
             tmem_ld32(acc1 + lane_off + cc * 32, v);
 #pragma unroll
             for (int i = 0; i < 32; ++i) if (!((mask >> i) & 1u)) v[i] = 0.f;
         } else {
 #pragma unroll
             for (int i = 0; i < 32; ++i) v[i] = 0.f;
+        }
+        if (sg) {
+            float w[32];
+            tmem_ld32(acc3 + lane_off + cc * 32, w);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] += w[i];
         }
         if (has_io) mbar_wait(bar + BB_IO, 0);
         {
@@ -494,7 +522,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) tc_bwd_kernel(const __grid_con
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) tmem_dealloc<256>(tmem);
+    if (warp == 1) tmem_dealloc<512>(tmem);
 }
 
 // =============================================================================================
@@ -664,13 +692,16 @@ void tc_layer_fwd(TcState* s, int l, const float* bd, const float* br, uint32_t*
     ast_launch_counter += 1;
 }
 
-void tc_layer_bwd(TcState* s, int l, const uint32_t* hmask_in, int df_idx, const uint32_t* zmask_in, cudaStream_t st) {
+void tc_layer_bwd(TcState* s, int l, const uint32_t* hmask_in, int df_idx, int sg_slot, int sg_L, const uint32_t* zmask_in,
+                  cudaStream_t st) {
     BwdArgs a;
     memset(&a, 0, sizeof(a));
     if (l == s->NL) s->cur = 0;                 // top of the stack: (re)start the dz ping-pong
     a.tmDz = s->tm_dz; a.tmG = s->tm_g; a.tmDF = s->tm_dF;
     a.tmW1 = s->tm_w1b; a.tmW2 = s->tm_w2b;
     a.T = s->T; a.df_idx = df_idx; a.hmask_in = hmask_in; a.zmask_in = zmask_in;
+    a.sg_slot = (s->n_fslots > 0 && df_idx < 0) ? sg_slot : -1; a.sg_L = sg_L;
+    if (a.sg_slot >= 0) { a.tmF = s->tm_F; a.tmS = s->tm_ssym; }
     a.dz_in = s->cur; a.dz_out = s->cur ^ 1;
     if (l < s->NL) { a.do_gemm1 = 1; a.w1_row = l * 3 * AST_C; a.shift = -(1 << (l % 10)); }
     else a.g_init = 1;
@@ -694,6 +725,7 @@ void tc_style_grad(TcState* s, int L, const int* head_of_slot, cudaStream_t st) 
     memset(&a, 0, sizeof(a));
     a.tmF = s->tm_F; a.tmS = s->tm_ssym; a.tmDF = s->tm_dF_st;
     a.T = s->T; a.L = L;
-    for (int i = 0; i < L && i < 32; ++i) a.head_of_slot[i] = head_of_slot[i];
-    launch_sgrad_tc(a, s->R / 128, L, st);
+    bool any = false;
+    for (int i = 0; i < L && i < 32; ++i) { a.head_of_slot[i] = head_of_slot[i]; any = any || head_of_slot[i] >= 0; }
+    if (any) launch_sgrad_tc(a, s->R / 128, L, st);
 }

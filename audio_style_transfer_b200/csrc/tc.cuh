@@ -25,13 +25,15 @@ void tc_layer_fwd(TcState* s, int l, const float* bd, const float* br, uint32_t*
 // backward boundary l in NL..0: g += conv^T(dz_l) * hmask + dF[df_idx] (df_idx < 0: none);
 // dz_{l-1} = (g Wr_{l-1}^T) * zmask.  bf16 dz buffers owned by the TcState.  l == NL: no conv (top);
 // l == 0: no 1x1 (bottom).
-void tc_layer_bwd(TcState* s, int l, const uint32_t* hmask_in, int df_idx, const uint32_t* zmask_in, cudaStream_t st);
+// sg_slot >= 0 (and df_idx < 0): the Gatys style gradient F[sg_slot] . Ssym[sg_slot] is computed in the same kernel.
+void tc_layer_bwd(TcState* s, int l, const uint32_t* hmask_in, int df_idx, int sg_slot, int sg_L, const uint32_t* zmask_in,
+                  cudaStream_t st);
 
 // Gatys Gram partials of the owned tiles [tile_lo, tile_hi) of every pair: part[(b*L+l)][chunk][128][128]
 void tc_gram(TcState* s, int L, int nchunk, int chunk_tiles, int tile_lo, int tile_hi, cudaStream_t st);
 // bf16 image of Ssym that the heads kernel fills ([B*L][128][128]), or NULL
 __nv_bfloat16* tc_ssym_bf16(TcState* s);
-// dF[head_of_slot[i]] = F[i] . Ssym[i] for every style slot i
+// dF[head_of_slot[i]] = F[i] . Ssym[i] for every style slot i with head_of_slot[i] >= 0
 void tc_style_grad(TcState* s, int L, const int* head_of_slot, cudaStream_t st);
 
 // ---- gram_tc.cu ------------------------------------------------------------------------------------
