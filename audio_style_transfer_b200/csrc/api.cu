@@ -71,7 +71,8 @@ struct ast_ctx {
     cudaGraphExec_t gphase[3];                  // ast_step_timed: encoder fwd | gram + heads | backward
     float *d_x, *d_losses, *d_grad;
     float *p_x, *p_out;            // pinned
-    int launches_per_step;
+    int launches_per_step;         // kernels of the last forward + the last backward
+    int launches_fwd, launches_bwd;
     cudaEvent_t ev[5];
 };
 
@@ -156,7 +157,7 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
     c->gdev = nullptr; c->gdev_x = nullptr; c->gdev_losses = c->gdev_grad = nullptr;
     for (auto& g : c->gphase) g = nullptr;
     for (auto& e : c->ev) e = nullptr;
-    c->have_w = c->have_t = false; c->launches_per_step = 0; c->lambd = 0.f;
+    c->have_w = c->have_t = false; c->launches_per_step = c->launches_fwd = c->launches_bwd = 0; c->lambd = 0.f;
 
     // time-sharding window (all zero = unsharded)
     c->total_T = cfg->total_T > 0 ? cfg->total_T : cfg->T;
@@ -341,10 +342,13 @@ extern "C" int ast_step_forward(ast_ctx* c, const float* d_x, void* stream) {
     if (!c || !d_x) return fail(AST_EINVAL, "null argument");
     if (!c->have_w || !c->have_t) return fail(AST_ESTATE, "ast_set_weights and ast_set_targets must precede a step");
     cudaStream_t s = (cudaStream_t)stream;
+    const int before = ast_launch_counter;
     run_encoder(c, d_x, s);
     run_gram(c, s);
     launch_content_sse(c->d_Hcptr, c->n_cont, c->cfg.cnt_channels, c->Pc, c->T, c->B, c->own_lo, c->own_hi,
                        c->sse_part, c->sse_nblk, c->partials + (size_t)c->B * c->nmat * c->msize, s);
+    c->launches_fwd = ast_launch_counter - before;
+    c->launches_per_step = c->launches_fwd + c->launches_bwd;
     CK(cudaGetLastError());
     return AST_OK;
 }
@@ -375,6 +379,7 @@ extern "C" int ast_step_backward(ast_ctx* c, float* d_losses, float* d_grad, voi
     if (!c || !d_losses || !d_grad) return fail(AST_EINVAL, "null argument");
     if (!c->have_w || !c->have_t) return fail(AST_ESTATE, "ast_set_weights and ast_set_targets must precede a step");
     cudaStream_t s = (cudaStream_t)stream;
+    const int bwd_before = ast_launch_counter;
     launch_heads(head_args(c, true, d_losses), s);
     // Gatys + tensor cores: the style gradient of an extract is fused into the backward layer kernel unless the
     // same extract also carries a content term (then the standalone kernel fills its dF buffer first)
@@ -425,17 +430,16 @@ extern "C" int ast_step_backward(ast_ctx* c, float* d_losses, float* d_grad, voi
         cur ^= 1;
     }
     launch_startconv_bwd(c->g, c->W0, c->scratch3R, d_grad, c->T, c->R, s);
+    c->launches_bwd = ast_launch_counter - bwd_before;
+    c->launches_per_step = c->launches_fwd + c->launches_bwd;
     CK(cudaGetLastError());
     return AST_OK;
 }
 
 extern "C" int ast_step(ast_ctx* c, const float* d_x, float* d_losses, float* d_grad, void* stream) {
-    const int before = ast_launch_counter;
     int r = ast_step_forward(c, d_x, stream);
     if (r != AST_OK) return r;
-    r = ast_step_backward(c, d_losses, d_grad, stream);
-    if (r == AST_OK) c->launches_per_step = ast_launch_counter - before;
-    return r;
+    return ast_step_backward(c, d_losses, d_grad, stream);
 }
 
 // ---- get_embeds (methods.py:86-95) -------------------------------------------------------------

@@ -303,8 +303,13 @@ def run_ours(args):
         dur_fwd = enc_ms * 1e-3 / NL                                  # average launch duration inside the encoder phase
         dur_bwd = bwd_ms * 1e-3 / (NL + 1)
         ach = fl_launch / dur_fwd / 1e12
-        roof = {"bound": "tensor", "kernel": "tc_layer_kernel<fwd>" if args.precision == "bf16" else "layer_f32_kernel<fwd>",
-                "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": ach / pk["tflops"], "traffic": None,
+        traffic = None
+        tj = ROOT / "profiles" / "r1_traffic.json"
+        if tj.exists() and name == "cfg1" and B == 1 and args.precision == "bf16":     # captured on exactly this workload
+            traffic = json.loads(tj.read_text())["tc_fwd_kernel"]["traffic"]
+        roof = {"bound": "tensor", "kernel": "tc_fwd_kernel" if args.precision == "bf16" else "layer_f32_kernel<fwd>",
+                "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": ach / pk["tflops"], "traffic": traffic,
+                "traffic_source": "profiles/r1_traffic.json (ncu --set full, dram read+write per launch)" if traffic else None,
                 "peak_source": pk["src"] + " (bf16 sustained)", "flops_per_launch": fl_launch,
                 "avg_launch_us": dur_fwd * 1e6,
                 "note": "avg = encoder-forward graph phase / n_layers (includes start conv + launch gaps)",

@@ -195,6 +195,7 @@ def test_time_sharded_windows_equal_unsharded(prec):
     for st, p, (wb, we, ob, oe) in zip(steps, parts, plan):
         p.copy_(total)
         lo, gw = st.backward()
+        assert st.launches_per_step > 0          # the two-phase path must account for its kernels (bench gpu_launches)
         g[ob:oe] = gw[0, ob - wb:oe - wb]
         assert torch.allclose(lo, lo_f, rtol=2e-5 if prec == "fp32" else 2e-3)
     tol = 2e-5 if prec == "fp32" else 5e-3
