@@ -568,3 +568,5 @@ extern "C" int ast_step_timed(ast_ctx* c, const float* d_x, float* d_losses, flo
 // profiling aid (scripts/timeline.py): per-CTA clock64() stamps of the forward layer kernel's phases
 void tc_set_timeline(unsigned long long* d_buf);
 extern "C" int ast_debug_timeline(void* d_buf) { tc_set_timeline((unsigned long long*)d_buf); return AST_OK; }
+void tc_set_dbg_skipw(int v);
+extern "C" int ast_debug_skipw(int v) { tc_set_dbg_skipw(v); return AST_OK; }

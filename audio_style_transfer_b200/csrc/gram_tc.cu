@@ -127,9 +127,8 @@ __global__ void __launch_bounds__(192, 3) sgrad_tc_kernel(const __grid_constant_
     uint8_t* gen = tc_smem_raw + (base - smem_u32(tc_smem_raw));
     const uint32_t bar = base + 4 * TILE16;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int row0 = blockIdx.x * 128, l = blockIdx.y;
+    const int row0 = blockIdx.x * 128, l = p.slot_of[blockIdx.y];      // slots fused into the backward kernel are not launched
     const int b = row0 / p.T, t0 = row0 - b * p.T;
-    if (p.head_of_slot[l] < 0) return;             // this slot's gradient is fused into the backward layer kernel
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&p.tmF); tma_prefetch_desc(&p.tmS); tma_prefetch_desc(&p.tmDF);
@@ -197,8 +196,8 @@ __global__ void __launch_bounds__(192, 3) sgrad_tc_kernel(const __grid_constant_
     if (warp == 1) tmem_dealloc<128>(acc);
 }
 
-void launch_sgrad_tc(const SGradTcArgs& a, int ntiles, int L, cudaStream_t s) {
-    launch_pdl(sgrad_tc_kernel, dim3(ntiles, L), dim3(192), SG_SMEM, s, a);
+void launch_sgrad_tc(const SGradTcArgs& a, int ntiles, cudaStream_t s) {
+    launch_pdl(sgrad_tc_kernel, dim3(ntiles, a.n_active), dim3(192), SG_SMEM, s, a);
     ast_launch_counter += 1;
 }
 

@@ -31,6 +31,10 @@ static constexpr uint32_t IDESC = umma_idesc_bf16(128, 128);
 __device__ unsigned long long* g_timeline = nullptr;
 #define TL(i) do { if (g_timeline) g_timeline[(size_t)blockIdx.x * 64 + (i)] = clock64(); } while (0)
 void tc_set_timeline(unsigned long long* d_buf) { cudaMemcpyToSymbol(g_timeline, &d_buf, sizeof(d_buf)); }
+// TIMING EXPERIMENT ONLY (scripts/timeline.py --skipw): the forward producer does not load the conv weight tiles,
+// so results are garbage; tells whether the K=3 GEMM phase is bound by operand bytes or by TMA latency.
+__device__ int g_dbg_skipw = 0;
+void tc_set_dbg_skipw(int v) { cudaMemcpyToSymbol(g_dbg_skipw, &v, sizeof(v)); }
 
 __device__ __forceinline__ bool tap_live(int t0, int k, int shift, int T) {
     const int t = t0 + (k - 1) * shift;
@@ -119,29 +123,46 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_kernel(const __grid_con
     const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gen + (bar + FB_TMEM - base));
     const uint32_t acc1 = tmem, acc2 = tmem + 128;
     pdl_launch_dependents();
-    pdl_wait();                        // everything above overlapped the previous kernel's tail
-    if (threadIdx.x == 0) TL(1);
+    // Everything above overlapped the previous kernel's tail.  The producer thread goes further before it waits:
+    // weight tiles are constants, so the W half of the first three stages is requested ahead of griddepcontrol.wait.
+    if (threadIdx.x != 0) pdl_wait();
 
     if (warp == 0) {
         // ================================ TMA producer ========================================
         if (lane == 0) {
             int fills[3] = {0, 0, 0};
-            int it = 0;
-            for (int k = 0; k < 3; ++k) {
-                if (!tap_live(t0, k, p.shift, p.T)) continue;
-                const int t = t0 + (k - 1) * p.shift;
-                for (int j = 0; j < 2; ++j, ++it) {
-                    const int slot = it % 3;
-                    mbar_wait(bar + FB_EMPTY(slot), (fills[slot] & 1) ^ 1);
-                    ++fills[slot];
-                    const uint32_t st = base + slot * FWD_STAGE, fb = bar + FB_FULL(slot);
-                    mbar_expect_tx(fb, 4 * TILE16);
-                    tma_load_4d(st, &p.tmA_hi, fb, j * 64, t, b, p.a_in);
-                    tma_load_4d(st + TILE16, &p.tmA_lo, fb, j * 64, t, b, p.a_in);
+            const bool skipw = g_dbg_skipw != 0;
+            int tap_of[6];
+            {
+                int n = 0;
+                for (int k = 0; k < 3; ++k)
+                    if (tap_live(t0, k, p.shift, p.T)) { tap_of[n++] = k; tap_of[n++] = k; }
+            }
+            auto load_w = [&](int it) {                      // arms the stage and requests its two weight tiles
+                const int slot = it % 3, k = tap_of[it], j = it & 1;
+                const uint32_t st = base + slot * FWD_STAGE, fb = bar + FB_FULL(slot);
+                mbar_expect_tx(fb, (skipw ? 2 : 4) * TILE16);
+                if (!skipw) {
                     tma_load_2d(st + 2 * TILE16, &p.tmW1, fb, j * 64, p.w1_row + (k * 2 + 0) * 128);
                     tma_load_2d(st + 3 * TILE16, &p.tmW1, fb, j * 64, p.w1_row + (k * 2 + 1) * 128);
-                    TL(2 + it);
                 }
+            };
+            const int npre = n1 < 3 ? n1 : 3;
+            for (int it = 0; it < npre; ++it) load_w(it);
+            pdl_wait();                                      // activations of the previous layer are now complete and visible
+            TL(1);
+            for (int it = 0; it < n1; ++it) {
+                const int slot = it % 3, k = tap_of[it], j = it & 1;
+                const int t = t0 + (k - 1) * p.shift;
+                if (it >= npre) {
+                    mbar_wait(bar + FB_EMPTY(slot), (fills[slot] & 1) ^ 1);
+                    load_w(it);
+                }
+                ++fills[slot];
+                const uint32_t st = base + slot * FWD_STAGE, fb = bar + FB_FULL(slot);
+                tma_load_4d(st, &p.tmA_hi, fb, j * 64, t, b, p.a_in);
+                tma_load_4d(st + TILE16, &p.tmA_lo, fb, j * 64, t, b, p.a_in);
+                TL(2 + it);
             }
             // 1x1 weights (K-half j) + two column groups of the fp32 residual tile, into slots 0 and 1
             for (int j = 0; j < 2; ++j) {
@@ -347,13 +368,27 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) tc_bwd_kernel(const __grid_con
     const uint32_t acc1 = tmem, acc2 = tmem + 128, acc3 = tmem + 256;
     const bool sg = p.sg_slot >= 0;
     pdl_launch_dependents();
-    pdl_wait();
+    if (threadIdx.x != 0) pdl_wait();      // the producer thread first requests constant weight tiles (see forward kernel)
 
     if (warp == 0) {
         // ================================ TMA producer ========================================
         if (lane == 0) {
             int fills[3] = {0, 0, 0};
-            int it = 0;
+            int tap_of[6];
+            {
+                int n = 0;
+                for (int k = 0; k < 3; ++k)
+                    if (p.do_gemm1 && tap_live(t0, k, p.shift, p.T)) { tap_of[n++] = k; tap_of[n++] = k; }
+            }
+            auto load_w = [&](int it) {
+                const int slot = it % 3;
+                const uint32_t fb = bar + FB_FULL(slot);
+                mbar_expect_tx(fb, 2 * TILE16);
+                tma_load_2d(base + slot * BWD_STAGE + TILE16, &p.tmW1, fb, (it & 1) * 64, p.w1_row + tap_of[it] * 128);
+            };
+            const int npre = n1 < 3 ? n1 : 3;
+            for (int it = 0; it < npre; ++it) load_w(it);
+            pdl_wait();
             bool io_sent = !has_io;
             auto send_io = [&]() {
                 if (io_sent) return;
@@ -369,21 +404,16 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) tc_bwd_kernel(const __grid_con
                 if (p.df_idx >= 0)
                     for (int cg = 0; cg < 4; ++cg) tma_load_4d(s_df + cg * TILE16, &p.tmDF, bar + BB_IO, cg * 32, t0, b, p.df_idx);
             };
-            if (p.do_gemm1) {
-                for (int k = 0; k < 3; ++k) {
-                    if (!tap_live(t0, k, p.shift, p.T)) continue;
-                    const int t = t0 + (k - 1) * p.shift;
-                    for (int j = 0; j < 2; ++j, ++it) {
-                        const int slot = it % 3;
-                        if (it == 3) send_io();          // after the first three operand stages are in flight
-                        mbar_wait(bar + FB_EMPTY(slot), (fills[slot] & 1) ^ 1);
-                        ++fills[slot];
-                        const uint32_t st = base + slot * BWD_STAGE, fb = bar + FB_FULL(slot);
-                        mbar_expect_tx(fb, 2 * TILE16);
-                        tma_load_4d(st, &p.tmDz, fb, j * 64, t, b, p.dz_in);
-                        tma_load_2d(st + TILE16, &p.tmW1, fb, j * 64, p.w1_row + k * 128);
-                    }
+            for (int it = 0; it < n1; ++it) {
+                const int slot = it % 3;
+                if (it == 3) send_io();                  // after the first three operand stages are in flight
+                if (it >= npre) {
+                    mbar_wait(bar + FB_EMPTY(slot), (fills[slot] & 1) ^ 1);
+                    load_w(it);
                 }
+                ++fills[slot];
+                tma_load_4d(base + slot * BWD_STAGE, &p.tmDz, bar + FB_FULL(slot), (it & 1) * 64,
+                            t0 + (tap_of[it] - 1) * p.shift, b, p.dz_in);
             }
             send_io();
             if (p.do_gemm2) {                            // Wr^T K-halves into the W part of slots 0 and 1
@@ -725,7 +755,9 @@ void tc_style_grad(TcState* s, int L, const int* head_of_slot, cudaStream_t st) 
     memset(&a, 0, sizeof(a));
     a.tmF = s->tm_F; a.tmS = s->tm_ssym; a.tmDF = s->tm_dF_st;
     a.T = s->T; a.L = L;
-    bool any = false;
-    for (int i = 0; i < L && i < 32; ++i) { a.head_of_slot[i] = head_of_slot[i]; any = any || head_of_slot[i] >= 0; }
-    if (any) launch_sgrad_tc(a, s->R / 128, L, st);
+    for (int i = 0; i < L && i < 32; ++i) {
+        a.head_of_slot[i] = head_of_slot[i];
+        if (head_of_slot[i] >= 0) a.slot_of[a.n_active++] = i;
+    }
+    if (a.n_active > 0) launch_sgrad_tc(a, s->R / 128, st);
 }

@@ -47,8 +47,10 @@ struct alignas(64) SGradTcArgs {
     CUtensorMap tmS;                 // bf16 Ssym rows [B*L*128][128], box {64,128}
     CUtensorMap tmDF;                // fp32 [n_head][B][T][128], store box {32,32,1,1}
     int T, L;
-    int head_of_slot[32];
+    int n_active;                    // grid.y: only slots that need the standalone kernel are launched
+    int slot_of[32];                 // blockIdx.y -> style slot
+    int head_of_slot[32];            // style slot -> dF buffer
 };
 void launch_gram_tc(const GramTcArgs& a, int nchunk, int L, int B, cudaStream_t s);
-void launch_sgrad_tc(const SGradTcArgs& a, int ntiles, int L, cudaStream_t s);
+void launch_sgrad_tc(const SGradTcArgs& a, int ntiles, cudaStream_t s);
 int setup_gram_tc_kernels();

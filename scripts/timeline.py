@@ -16,9 +16,12 @@ for _ in range(3):
     st.embeds(x, style=False)
 torch.cuda.synchronize()
 lib.ast_debug_timeline(C.c_void_p(buf.data_ptr()))
+if '--skipw' in sys.argv:          # timing experiment: forward producer skips the conv weight tiles (results garbage)
+    lib.ast_debug_skipw(1)
 st.embeds(x, style=False)          # the LAST layer's stamps survive
 torch.cuda.synchronize()
 lib.ast_debug_timeline(C.c_void_p(0))
+lib.ast_debug_skipw(0)
 tl = buf.cpu().numpy().reshape(128, 64)
 names = {0: 'entry', 1: 'setup done', **{2 + i: f'tma issued it{i}' for i in range(6)}, 8: 'tma issued W2/H 0', 9: 'tma issued W2/H 1',
          **{10 + i: f'mma full it{i}' for i in range(6)}, 16: 'gemm2 half0 start', 19: 'gemm2 half1 start',
