@@ -198,7 +198,7 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
     c->msize = c->n_side * c->n_side;
 
     {   // Gram split-K geometry: few enough chunks to keep the partial buffer small, enough to fill the SMs
-        int target = cfg->gatys ? 16 : 64;
+        int target = cfg->gatys ? 16 : 128;      // ours: 128 chunks x 4 channel quads = 512 CTAs of the latency-bound kernel
         target = std::max(2, (target + c->B - 1) / c->B);
         int rows = (c->T + target - 1) / target;
         rows = std::max(128, ((rows + 127) / 128) * 128);

@@ -1,6 +1,7 @@
 // kernels_f32.cu -- CUDA-core fp32 kernels: the <=1e-4 accuracy tier and every non-GEMM stage.
 // sm_100a only.  Reference lines are cited per kernel (paths relative to the upstream repo).
 #include "common.cuh"
+#include "ptx.cuh"
 
 // =============================================================================================
 // helpers
@@ -288,57 +289,100 @@ void launch_layer_f32(const LayerArgsF32& a, bool bwd, cudaStream_t s) {
 // Gram partials (methods.py:62-73).  Deterministic: every CTA writes its own partial, a second
 // kernel sums the partials in a fixed order (no float atomics).
 // =============================================================================================
-// "ours": G[c,l,m] = sum_t F_l[t,c] F_m[t,c].  block = 32 channels x (ng x ng) groups, each thread an
-// 8x8 (l,m) block for one channel.  grid = (nchunk, 4 channel quads, B).  part[b][chunk][c][l][m].
-__global__ void __launch_bounds__(512) gram_ours_kernel(const float* const* __restrict__ F, int L, int T, int own_lo,
+// "ours": G[c,l,m] = sum_t F_l[t,c] F_m[t,c].  grid = (nchunk, 4 channel quads, B); part[b][chunk][c][l][m].
+// A CTA owns 32 channels of one row chunk.  R rows of all L extracts are staged per round into shared memory
+// with cp.async (3 stages, one barrier per round), so every element of F is requested from L2/HBM exactly once;
+// block = 32 channels x ng(ng+1)/2 groups, each thread an 8x8 (l,m) register block of the UPPER triangle of
+// 8-layer groups (the Gram is symmetric; the mirror is written at the end).  Layers L..8ng-1 are zero rows in
+// shared memory, rows past the chunk end are zero-filled by cp.async (src-size 0).  Rows are accumulated in
+// ascending order -> run-to-run reproducible.
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool valid) {
+    const int sz = valid ? 16 : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+#define GO_STAGES 3
+template <int R>
+__global__ void __launch_bounds__(320) gram_ours_kernel(const float* const* __restrict__ F, int L, int T, int own_lo,
                                                         int own_hi, float* __restrict__ part, int nchunk,
                                                         int chunk_rows, int ng) {
-    const int cl = threadIdx.x;                 // 0..31
-    const int grp = threadIdx.y;                // 0..ng*ng-1
-    const int lg = grp / ng, mg = grp % ng;
-    const int c = blockIdx.y * 32 + cl;
-    const int b = blockIdx.z;
+    extern __shared__ __align__(16) float go_s[];          // [stage][8 ng][R][32]
+    const int stage_f = ng * 8 * R * 32;
+    const int cl = threadIdx.x, grp = threadIdx.y;
+    const int nthr = blockDim.x * blockDim.y, tid = grp * 32 + cl;
+    int lg = 0, mg = grp;                                   // triangular index -> (lg <= mg)
+    for (int w = ng; mg >= w; --w) { mg -= w; ++lg; }
+    mg += lg;
+    const int c0 = blockIdx.y * 32, b = blockIdx.z;
     const int tb = blockIdx.x * chunk_rows;
-    int t_lo = max(tb, own_lo), t_hi = min(min(tb + chunk_rows, T), own_hi);
+    const int t_lo = max(tb, own_lo), t_hi = min(min(tb + chunk_rows, T), own_hi);
+    for (int i = tid; i < GO_STAGES * stage_f; i += nthr)
+        if ((i % stage_f) / (R * 32) >= L) go_s[i] = 0.f;
+    const int nround = t_hi > t_lo ? (t_hi - t_lo + R - 1) / R : 0;
+    auto issue = [&](int round) {
+        if (round < nround) {
+            float* dst = go_s + (round % GO_STAGES) * stage_f;
+            const int t0 = t_lo + round * R;
+            for (int i = tid; i < L * R * 8; i += nthr) {
+                const int q = i & 7, r = (i >> 3) % R, l = i / (8 * R);
+                const bool ok = t0 + r < t_hi;
+                const float* src = F[l] + ((size_t)b * T + (ok ? t0 + r : t_lo)) * AST_C + c0 + q * 4;
+                cp_async16(smem_u32(dst + (l * R + r) * 32 + q * 4), src, ok);
+            }
+        }
+        cp_async_commit();
+    };
     float acc[8][8];
 #pragma unroll
     for (int i = 0; i < 8; ++i)
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
-    const float* pl[8];
-    const float* pm[8];
+    issue(0);
+    issue(1);
+    for (int round = 0; round < nround; ++round) {
+        cp_async_wait<1>();                 // this thread's copies of `round` have landed
+        __syncthreads();                    // everyone's have; and everyone is done reading stage (round+2)%3
+        issue(round + 2);
+        const float* sl = go_s + (round % GO_STAGES) * stage_f + (lg * 8 * R) * 32 + cl;
+        const float* sm = go_s + (round % GO_STAGES) * stage_f + (mg * 8 * R) * 32 + cl;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const int l = lg * 8 + i, m = mg * 8 + i;
-        pl[i] = (l < L) ? F[l] + (size_t)b * T * AST_C + c : nullptr;
-        pm[i] = (m < L) ? F[m] + (size_t)b * T * AST_C + c : nullptr;
-    }
-    for (int t = t_lo; t < t_hi; ++t) {
-        float vl[8], vm[8];
+        for (int r = 0; r < R; ++r) {
+            float vl[8], vm[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            vl[i] = pl[i] ? pl[i][(size_t)t * AST_C] : 0.f;
-            vm[i] = pm[i] ? pm[i][(size_t)t * AST_C] : 0.f;
+            for (int i = 0; i < 8; ++i) { vl[i] = sl[(i * R + r) * 32]; vm[i] = sm[(i * R + r) * 32]; }
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(vl[i], vm[j], acc[i][j]);
         }
-#pragma unroll
-        for (int i = 0; i < 8; ++i)
-#pragma unroll
-            for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(vl[i], vm[j], acc[i][j]);
     }
-    float* out = part + (((size_t)b * nchunk + blockIdx.x) * AST_C + c) * L * L;
+    cp_async_wait<0>();
+    float* out = part + (((size_t)b * nchunk + blockIdx.x) * AST_C + c0 + cl) * L * L;
 #pragma unroll
     for (int i = 0; i < 8; ++i)
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const int l = lg * 8 + i, m = mg * 8 + j;
-            if (l < L && m < L) out[l * L + m] = acc[i][j];
+            if (l < L && m < L) {
+                out[l * L + m] = acc[i][j];
+                if (lg != mg) out[m * L + l] = acc[i][j];
+            }
         }
 }
 void launch_gram_ours(const float* const* d_F, int L, int T, int B, int own_lo, int own_hi, float* part, int nchunk,
                       int chunk_rows, cudaStream_t s) {
     const int ng = (L + 7) / 8;
-    dim3 grid(nchunk, AST_C / 32, B), block(32, ng * ng);
-    gram_ours_kernel<<<grid, block, 0, s>>>(d_F, L, T, own_lo, own_hi, part, nchunk, chunk_rows, ng);
+    dim3 grid(nchunk, AST_C / 32, B), block(32, ng * (ng + 1) / 2);
+    if (ng <= 2) {
+        const size_t smem = (size_t)GO_STAGES * ng * 8 * 8 * 32 * sizeof(float);      // <= 48 KB
+        gram_ours_kernel<8><<<grid, block, smem, s>>>(d_F, L, T, own_lo, own_hi, part, nchunk, chunk_rows, ng);
+    } else {
+        const size_t smem = (size_t)GO_STAGES * ng * 8 * 4 * 32 * sizeof(float);      // <= 48 KB at ng = 4
+        gram_ours_kernel<4><<<grid, block, smem, s>>>(d_F, L, T, own_lo, own_hi, part, nchunk, chunk_rows, ng);
+    }
     ast_launch_counter += 1;
 }
 
@@ -402,16 +446,49 @@ __global__ void gram_reduce_kernel(const float* __restrict__ part, float* __rest
     const int o = blockIdx.y;
     for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < E; e += gridDim.x * blockDim.x) {
         const float* p = part + (size_t)o * nchunk * E + e;
-        double s = 0.0;
-        for (int ch = 0; ch < nchunk; ++ch) s += (double)p[(size_t)ch * E];
-        G[(size_t)o * E + e] = (float)s;
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;          // fixed association: run-to-run reproducible
+        int ch = 0;
+        for (; ch + 4 <= nchunk; ch += 4) {
+            s0 += (double)p[(size_t)ch * E]; s1 += (double)p[(size_t)(ch + 1) * E];
+            s2 += (double)p[(size_t)(ch + 2) * E]; s3 += (double)p[(size_t)(ch + 3) * E];
+        }
+        for (; ch < nchunk; ++ch) s0 += (double)p[(size_t)ch * E];
+        G[(size_t)o * E + e] = (float)((s0 + s1) + (s2 + s3));
+    }
+}
+// many chunks (channel-wise Gram, 128 of them): block = 32 elements x 8 chunk slices; slice k sums chunks
+// k, k+8, ... in two interleaved chains, then the 8 slice sums are combined in fixed order through smem.
+__global__ void __launch_bounds__(256) gram_reduce_sliced_kernel(const float* __restrict__ part, float* __restrict__ G,
+                                                                 int nchunk, int E) {
+    __shared__ double red[8][32];
+    const int o = blockIdx.y, k = threadIdx.y;
+    const int e = blockIdx.x * 32 + threadIdx.x;
+    double s0 = 0.0, s1 = 0.0;
+    if (e < E) {
+        const float* p = part + (size_t)o * nchunk * E + e;
+        int ch = k;
+        for (; ch + 8 < nchunk; ch += 16) { s0 += (double)p[(size_t)ch * E]; s1 += (double)p[(size_t)(ch + 8) * E]; }
+        if (ch < nchunk) s0 += (double)p[(size_t)ch * E];
+    }
+    red[k][threadIdx.x] = s0 + s1;
+    __syncthreads();
+    if (k == 0 && e < E) {
+        double t = 0.0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t += red[i][threadIdx.x];
+        G[(size_t)o * E + e] = (float)t;
     }
 }
 void launch_gram_reduce(const float* part, float* G, int gatys, int L, int B, int nchunk, cudaStream_t s) {
     const int nouter = gatys ? B * L : B;
     const int E = gatys ? AST_C * AST_C : AST_C * L * L;
-    dim3 grid((E + 255) / 256, nouter);
-    gram_reduce_kernel<<<grid, 256, 0, s>>>(part, G, nchunk, E);
+    if (nchunk >= 32) {
+        dim3 grid((E + 31) / 32, nouter), block(32, 8);
+        gram_reduce_sliced_kernel<<<grid, block, 0, s>>>(part, G, nchunk, E);
+    } else {
+        dim3 grid((E + 255) / 256, nouter);
+        gram_reduce_kernel<<<grid, 256, 0, s>>>(part, G, nchunk, E);
+    }
     ast_launch_counter += 1;
 }
 
@@ -448,11 +525,10 @@ __global__ void __launch_bounds__(256) content_sse_kernel(const float* const* __
     }
 }
 __global__ void content_sse_final(const double* __restrict__ part, int nblk, float* __restrict__ sse) {
-    if (threadIdx.x == 0) {
-        double tot = 0.0;
-        for (int i = 0; i < nblk; ++i) tot += part[(size_t)blockIdx.x * nblk + i];
-        sse[blockIdx.x] = (float)tot;
-    }
+    double tot = 0.0;                           // one warp; lane-strided then a fixed shuffle tree: deterministic
+    for (int i = threadIdx.x; i < nblk; i += 32) tot += part[(size_t)blockIdx.x * nblk + i];
+    tot = warp_sum_d(tot);
+    if (threadIdx.x == 0) sse[blockIdx.x] = (float)tot;
 }
 void launch_content_sse(const float* const* d_Hc, int n_cont, int cnt_ch, const float* Pc, int T, int B, int own_lo,
                         int own_hi, float* part, int nblk, float* sse, cudaStream_t s) {
@@ -526,10 +602,11 @@ __global__ void __launch_bounds__(1024) heads_kernel(const HeadArgs a) {
 }
 // losses[b] = {Lc + lambd Ls, Lc, Ls, 0}  (methods.py:116-125, gamma = 0)
 __global__ void losses_final_kernel(const HeadArgs a) {
-    if (threadIdx.x != 0) return;
     const int b = blockIdx.x;
-    double s = 0.0;
-    for (int m = 0; m < a.nmat_used; ++m) s += (double)a.ls_part[(size_t)b * a.nmat + m];
+    double s = 0.0;                             // one warp, fixed order
+    for (int m = threadIdx.x; m < a.nmat_used; m += 32) s += (double)a.ls_part[(size_t)b * a.nmat + m];
+    s = warp_sum_d(s);
+    if (threadIdx.x != 0) return;
     const double Ls = (double)a.ls_scale * s;
     const double Lc = (double)a.lc_scale * (double)a.sse[b];
     a.losses[b * 4 + 0] = (float)(Lc + (double)a.lambd * Ls);
@@ -547,41 +624,72 @@ void launch_heads(const HeadArgs& a, cudaStream_t s) {
 // =============================================================================================
 // head gradients
 // =============================================================================================
-// ours: dF_l[t,c] = sum_m Ssym[c,l,m] F_m[t,c].  block = (32 channels, L layers); each thread keeps its
-// row Ssym[c,l,:] in registers and walks 64 rows staged 8 at a time through shared memory.
-// grid = (T/64, 4 channel quads, B).
-#define SG_ROWS 8
-__global__ void __launch_bounds__(1024) style_grad_ours_kernel(const float* const* __restrict__ F,
-                                                               float* const* __restrict__ dF,
-                                                               const float* __restrict__ Ssym, int L, int T) {
-    __shared__ float Fs[32][SG_ROWS][32];   // [m][r][cl]
+// ours: dF_l[t,c] = sum_m Ssym[c,l,m] F_m[t,c].  block = (32 channels, L layers), grid = (T/64, 4 channel
+// quads, B).  Each thread keeps its row Ssym[c,l,:] in registers and walks 64 rows, ROWS at a time: the rows of
+// all L extracts are shared through a double-buffered smem tile, and the next round's global loads are issued
+// into registers BEFORE the current round's FMAs, so memory latency overlaps the arithmetic (one barrier per
+// round).  L is a template parameter: the inner product is exactly L LDS + L FMA per output (a runtime-L loop
+// with an `m < L` guard issued 32 predicated pairs and was issue-bound at 3x the work for L = 10).
+// Measured dead ends on B200: no staging at all (every thread reads F_m through L1) 2.4x slower; 32-row rounds
+// without the register prefetch 1.8x slower than 8-row rounds (all resident CTAs sit in their load phase at once).
+template <int L, int ROWS>
+__global__ void __launch_bounds__(32 * L) style_grad_ours_kernel(const float* const* __restrict__ F,
+                                                                 float* const* __restrict__ dF,
+                                                                 const float* __restrict__ Ssym, int T) {
+    __shared__ float Fs[2][L][ROWS][32];
     const int cl = threadIdx.x, l = threadIdx.y;
     const int c = blockIdx.y * 32 + cl, b = blockIdx.z;
-    float S[32];
+    float S[L];
 #pragma unroll
-    for (int m = 0; m < 32; ++m) S[m] = (m < L) ? Ssym[(((size_t)b * AST_C + c) * L + l) * L + m] : 0.f;
-    const float* Fl = F[l] + (size_t)b * T * AST_C + c;
-    float* dFl = dF[l] + (size_t)b * T * AST_C + c;
+    for (int m = 0; m < L; ++m) S[m] = Ssym[(((size_t)b * AST_C + c) * L + l) * L + m];
     const int tb = blockIdx.x * 64;
-    for (int ts = tb; ts < tb + 64; ts += SG_ROWS) {
+    const float* Fl = F[l] + ((size_t)b * T + tb) * AST_C + c;
+    float* dFl = dF[l] + ((size_t)b * T + tb) * AST_C + c;
+    float nxt[ROWS];
 #pragma unroll
-        for (int r = 0; r < SG_ROWS; ++r) Fs[l][r][cl] = Fl[(size_t)(ts + r) * AST_C];
-        __syncthreads();
+    for (int r = 0; r < ROWS; ++r) nxt[r] = __ldg(Fl + (size_t)r * AST_C);
 #pragma unroll
-        for (int r = 0; r < SG_ROWS; ++r) {
+    for (int r = 0; r < ROWS; ++r) Fs[0][l][r][cl] = nxt[r];
+    __syncthreads();
+    constexpr int NIT = 64 / ROWS;
+#pragma unroll 1
+    for (int it = 0; it < NIT; ++it) {
+        const int cur = it & 1;
+        if (it + 1 < NIT) {
+#pragma unroll
+            for (int r = 0; r < ROWS; ++r) nxt[r] = __ldg(Fl + (size_t)((it + 1) * ROWS + r) * AST_C);
+        }
+#pragma unroll
+        for (int r = 0; r < ROWS; ++r) {
             float acc = 0.f;
 #pragma unroll
-            for (int m = 0; m < 32; ++m)
-                if (m < L) acc = fmaf(S[m], Fs[m][r][cl], acc);
-            dFl[(size_t)(ts + r) * AST_C] = acc;
+            for (int m = 0; m < L; ++m) acc = fmaf(S[m], Fs[cur][m][r][cl], acc);
+            dFl[(size_t)(it * ROWS + r) * AST_C] = acc;
+        }
+        if (it + 1 < NIT) {
+#pragma unroll
+            for (int r = 0; r < ROWS; ++r) Fs[cur ^ 1][l][r][cl] = nxt[r];
         }
         __syncthreads();
     }
 }
+template <int L>
+static void launch_sgo(const float* const* d_F, float* const* d_dF, const float* Ssym, int T, int B, cudaStream_t s) {
+    constexpr int ROWS = L <= 24 ? 8 : 4;                      // 2 * L * ROWS * 128 B <= 48 KB of static smem
+    dim3 grid(T / 64, AST_C / 32, B), block(32, L);
+    style_grad_ours_kernel<L, ROWS><<<grid, block, 0, s>>>(d_F, d_dF, Ssym, T);
+}
 void launch_style_grad_ours(const float* const* d_F, float* const* d_dF, const float* Ssym, int L, int T, int B,
                             cudaStream_t s) {
-    dim3 grid(T / 64, AST_C / 32, B), block(32, L);
-    style_grad_ours_kernel<<<grid, block, 0, s>>>(d_F, d_dF, Ssym, L, T);
+#define SGO_CASE(n) case n: launch_sgo<n>(d_F, d_dF, Ssym, T, B, s); break;
+    switch (L) {
+        SGO_CASE(1) SGO_CASE(2) SGO_CASE(3) SGO_CASE(4) SGO_CASE(5) SGO_CASE(6) SGO_CASE(7) SGO_CASE(8)
+        SGO_CASE(9) SGO_CASE(10) SGO_CASE(11) SGO_CASE(12) SGO_CASE(13) SGO_CASE(14) SGO_CASE(15) SGO_CASE(16)
+        SGO_CASE(17) SGO_CASE(18) SGO_CASE(19) SGO_CASE(20) SGO_CASE(21) SGO_CASE(22) SGO_CASE(23) SGO_CASE(24)
+        SGO_CASE(25) SGO_CASE(26) SGO_CASE(27) SGO_CASE(28) SGO_CASE(29) SGO_CASE(30) SGO_CASE(31) SGO_CASE(32)
+        default: break;                                        // ast_create rejects L outside 1..32
+    }
+#undef SGO_CASE
     ast_launch_counter += 1;
 }
 
