@@ -7,6 +7,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <vector>
 
 thread_local int ast_launch_counter = 0;
@@ -73,6 +74,8 @@ struct ast_ctx {
     float *p_x, *p_out;            // pinned
     int launches_per_step;         // kernels of the last forward + the last backward
     int launches_fwd, launches_bwd;
+    bool use_stack;                // whole-stack forward kernel (one launch) instead of one kernel per layer
+    unsigned char h_kept[33];      // H[i] of the last forward is valid in global memory
     cudaEvent_t ev[5];
 };
 
@@ -256,6 +259,8 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
         c->tc = tc_create(c->T, c->B, c->NL, c->H, c->g, c->dF, c->n_head, cfg->gatys ? c->L : 0, c->gram_part,
                           (int64_t)c->B * c->nmat * c->gram_nchunk, &c->bytes, &why);
         if (!c->tc) { ast_destroy(c); return fail(AST_ECUDA, "tensor-core path setup failed: %s", why ? why : "?"); }
+        const char* no = getenv("AST_B200_NO_STACK");           // A/B switch for profiling: one kernel per layer instead
+        c->use_stack = tc_stack_ok(c->tc) && !(no && no[0] == '1');
     }
     if (cudaDeviceSynchronize() != cudaSuccess || cudaGetLastError() != cudaSuccess) { ast_destroy(c); return fail(AST_ECUDA, "context setup failed"); }
     *out = c;
@@ -310,7 +315,20 @@ extern "C" int ast_set_targets(ast_ctx* c, const float* Pc, const float* Ps, dou
 }
 
 // ---- forward --------------------------------------------------------------------------------
-static void run_encoder(ast_ctx* c, const float* d_x, cudaStream_t s) {
+// keep_all: every H[i] is written to global memory (ast_embeds / ast_get_extract); the optimisation step keeps only
+// what its heads read -- the whole-stack kernel holds the residual stream in TMEM.
+static void run_encoder(ast_ctx* c, const float* d_x, cudaStream_t s, bool keep_all) {
+    if (c->tc && c->use_stack) {
+        unsigned char keep[33];
+        for (int i = 0; i <= c->NL; ++i) keep[i] = keep_all ? 1 : 0;
+        for (int i = 0; i < c->n_cont; ++i) keep[c->cont_layer[i] + 1] = 1;
+        if (!c->cfg.gatys)                      // channel-wise Gram and its gradient read the fp32 extracts
+            for (int i = 0; i < c->L; ++i) keep[c->style_layer[i] + 1] = 1;
+        memcpy(c->h_kept, keep, sizeof(keep));
+        tc_forward_stack(c->tc, d_x, c->W0, c->b0, c->bd, c->br, c->H, c->zmask, c->hmask, c->f_slot, keep, s);
+        return;
+    }
+    memset(c->h_kept, 1, sizeof(c->h_kept));
     launch_startconv_fwd(d_x, c->W0, c->b0, Hl(c, 0), hm(c, 0), c->T, c->R, s);
     if (c->tc) tc_prepare_input(c->tc, Hl(c, 0), s);
     for (int l = 0; l < c->NL; ++l) {
@@ -343,7 +361,7 @@ extern "C" int ast_step_forward(ast_ctx* c, const float* d_x, void* stream) {
     if (!c->have_w || !c->have_t) return fail(AST_ESTATE, "ast_set_weights and ast_set_targets must precede a step");
     cudaStream_t s = (cudaStream_t)stream;
     const int before = ast_launch_counter;
-    run_encoder(c, d_x, s);
+    run_encoder(c, d_x, s, false);
     run_gram(c, s);
     launch_content_sse(c->d_Hcptr, c->n_cont, c->cfg.cnt_channels, c->Pc, c->T, c->B, c->own_lo, c->own_hi,
                        c->sse_part, c->sse_nblk, c->partials + (size_t)c->B * c->nmat * c->msize, s);
@@ -447,7 +465,7 @@ extern "C" int ast_embeds(ast_ctx* c, const float* d_x, float* d_Ec, float* d_Gn
     if (!c || !d_x) return fail(AST_EINVAL, "null argument");
     if (!c->have_w) return fail(AST_ESTATE, "ast_set_weights must precede ast_embeds");
     cudaStream_t s = (cudaStream_t)stream;
-    run_encoder(c, d_x, s);
+    run_encoder(c, d_x, s, true);
     if (d_Ec) launch_content_gather(c->d_Hcptr, c->n_cont, c->cfg.cnt_channels, d_Ec, c->R, s);
     if (d_Gn) {
         run_gram(c, s);
@@ -464,6 +482,9 @@ extern "C" int ast_get_extract(ast_ctx* c, int32_t layer, float* d_out, void* st
     if (layer < -1 || layer > 30) return fail(AST_EINVAL, "layer %d outside -1..30", layer);
     const int l = std::min(layer, 29);        // -1 = start-conv output
     if (l >= c->NL) return fail(AST_EINVAL, "layer %d was not evaluated (n_layers=%d)", layer, c->NL);
+    if (!c->h_kept[l + 1])
+        return fail(AST_ESTATE, "layer %d was not retained by the last step (only the configured content/style extracts "
+                    "are; ast_embeds retains every layer)", layer);
     CK(cudaMemcpyAsync(d_out, Hl(c, l + 1), (size_t)c->R * AST_C * sizeof(float), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
     return AST_OK;
 }
@@ -533,7 +554,7 @@ extern "C" int ast_step_timed(ast_ctx* c, const float* d_x, float* d_losses, flo
     cudaStream_t s = (cudaStream_t)stream;
     if (!c->gphase[0]) {
         CK(cudaStreamSynchronize(s));
-        int r = capture_graph(c, &c->gphase[0], [&](cudaStream_t cs) { run_encoder(c, c->d_x, cs); return AST_OK; });
+        int r = capture_graph(c, &c->gphase[0], [&](cudaStream_t cs) { run_encoder(c, c->d_x, cs, false); return AST_OK; });
         if (r != AST_OK) return r;
         r = capture_graph(c, &c->gphase[1], [&](cudaStream_t cs) {
             run_gram(c, cs);
@@ -569,4 +590,15 @@ extern "C" int ast_step_timed(ast_ctx* c, const float* d_x, float* d_losses, flo
 void tc_set_timeline(unsigned long long* d_buf);
 extern "C" int ast_debug_timeline(void* d_buf) { tc_set_timeline((unsigned long long*)d_buf); return AST_OK; }
 void tc_set_dbg_skipw(int v);
+// 1 if a bounded spin of the whole-stack kernels expired since the context was created (results are then invalid)
+extern "C" int ast_debug_stack_err(ast_ctx* c) {
+    if (!c || !c->tc) return 0;
+    unsigned e[2] = {0, 0};
+    cudaDeviceSynchronize();
+    cudaMemcpy(e, tc_stack_err(c->tc), sizeof(e), cudaMemcpyDeviceToHost);
+    return (int)(e[0] | e[1]);
+}
+extern "C" int ast_debug_uses_stack(ast_ctx* c) { return c && c->use_stack ? 1 : 0; }
+void tc_set_tl_layer(int l);
+extern "C" int ast_debug_tl_layer(int l) { tc_set_tl_layer(l); return AST_OK; }
 extern "C" int ast_debug_skipw(int v) { tc_set_dbg_skipw(v); return AST_OK; }

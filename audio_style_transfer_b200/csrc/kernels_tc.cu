@@ -35,6 +35,7 @@ void tc_set_timeline(unsigned long long* d_buf) { cudaMemcpyToSymbol(g_timeline,
 // so results are garbage; tells whether the K=3 GEMM phase is bound by operand bytes or by TMA latency.
 __device__ int g_dbg_skipw = 0;
 void tc_set_dbg_skipw(int v) { cudaMemcpyToSymbol(g_dbg_skipw, &v, sizeof(v)); }
+void tc_set_tl_layer(int l);
 
 __device__ __forceinline__ bool tap_live(int t0, int k, int shift, int T) {
     const int t = t0 + (k - 1) * shift;
@@ -313,6 +314,9 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_kernel(const __grid_con
     if (threadIdx.x == 0) TL(31);
     if (warp == 1) tmem_dealloc<256>(tmem);
 }
+
+#include "stack_fwd.cuh"
+void tc_set_tl_layer(int l) { cudaMemcpyToSymbol(g_tl_layer, &l, sizeof(l)); }
 
 // =============================================================================================
 // backward boundary l (between layer l-1 and layer l), plain bf16 operands
@@ -599,6 +603,8 @@ struct TcState {
     CUtensorMap tm_a_hi, tm_a_lo, tm_dz, tm_H, tm_g, tm_dF;      // box = 128 rows x 128 bytes, loads and stores
     CUtensorMap tm_w1f, tm_w2f, tm_w1b, tm_w2b;
     int cur;                       // dz buffer holding the most recent backward output
+    unsigned* flags;               // [2][R/128] publish counters of the forward / backward stack kernels, then err[2]
+    int n_sm, coop;                // SM count; cooperative launch supported
 };
 
 static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
@@ -656,7 +662,15 @@ TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_he
               cudaMalloc(&s->dz, act) == cudaSuccess && cudaMalloc(&s->w1f, mat * NL * 3 * 2) == cudaSuccess &&
               cudaMalloc(&s->w2f, mat * NL * 2) == cudaSuccess && cudaMalloc(&s->w1b, mat * NL * 3) == cudaSuccess &&
               cudaMalloc(&s->w2b, mat * NL) == cudaSuccess;
+    ok = ok && cudaMalloc(&s->flags, ((size_t)2 * (s->R / 128) + 2) * sizeof(unsigned)) == cudaSuccess;
     if (!ok) { *why = "cudaMalloc failed"; tc_destroy(s); return nullptr; }
+    cudaMemset(s->flags, 0, ((size_t)2 * (s->R / 128) + 2) * sizeof(unsigned));
+    {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&s->n_sm, cudaDevAttrMultiProcessorCount, dev);
+        cudaDeviceGetAttribute(&s->coop, cudaDevAttrCooperativeLaunch, dev);
+    }
     *bytes += (int64_t)(3 * act + mat * NL * 12);
     ok = make_act_map(&s->tm_a_hi, s->a_hi, false, T, B, 2, 128) && make_act_map(&s->tm_a_lo, s->a_lo, false, T, B, 2, 128) &&
          make_act_map(&s->tm_dz, s->dz, false, T, B, 2, 128) && make_act_map(&s->tm_H, H, true, T, B, NL + 1, 128) &&
@@ -676,7 +690,8 @@ TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_he
              make_act_map(&s->tm_dF_st, dF, true, T, B, n_head > 0 ? n_head : 1, 32) && setup_gram_tc_kernels() == 0;
     }
     if (!ok) { *why = "cuTensorMapEncodeTiled failed"; tc_destroy(s); return nullptr; }
-    if (cudaFuncSetAttribute(tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM) != cudaSuccess ||
+    if (cudaFuncSetAttribute(tc_fwd_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FS_SMEM) != cudaSuccess ||
+        cudaFuncSetAttribute(tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM) != cudaSuccess ||
         cudaFuncSetAttribute(tc_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM) != cudaSuccess) {
         *why = "cudaFuncSetAttribute(max dynamic smem) failed";
         tc_destroy(s);
@@ -689,7 +704,7 @@ void tc_destroy(TcState* s) {
     if (!s) return;
     cudaFree(s->a_hi); cudaFree(s->a_lo); cudaFree(s->dz);
     cudaFree(s->w1f); cudaFree(s->w2f); cudaFree(s->w1b); cudaFree(s->w2b);
-    cudaFree(s->F); cudaFree(s->ssym);
+    cudaFree(s->F); cudaFree(s->ssym); cudaFree(s->flags);
     delete s;
 }
 
@@ -720,6 +735,38 @@ void tc_layer_fwd(TcState* s, int l, const float* bd, const float* br, uint32_t*
     if (a.f_slot >= 0) a.tmF = s->tm_F;
     launch_pdl(tc_fwd_kernel, dim3(s->R / 128), dim3(FWD_THREADS), FWD_SMEM, st, a);
     ast_launch_counter += 1;
+}
+
+// ---- whole-stack forward (stack_fwd.cuh) ------------------------------------------------------------
+template <typename Kern, typename Args>
+static cudaError_t launch_coop(Kern kernel, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const Args& args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeCooperative;           // all CTAs co-resident, or the launch fails
+    at[0].val.cooperative = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, args);
+}
+bool tc_stack_ok(const TcState* s) { return s && s->coop && s->R / 128 <= s->n_sm && s->NL <= 32; }
+unsigned* tc_stack_err(TcState* s) { return s->flags + (size_t)2 * (s->R / 128); }
+int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b0, const float* bd, const float* br,
+                     float* H, uint32_t* zmask, uint32_t* hmask, const int* f_slot, const unsigned char* export_h,
+                     cudaStream_t st) {
+    FwdStackArgs a;
+    memset(&a, 0, sizeof(a));
+    a.tmA_hi = s->tm_a_hi; a.tmA_lo = s->tm_a_lo; a.tmW1 = s->tm_w1f; a.tmW2 = s->tm_w2f;
+    a.tmF = s->n_fslots > 0 ? s->tm_F : s->tm_a_hi;          // never dereferenced without an f_slot
+    a.x = x; a.W0 = W0; a.b0 = b0; a.bd = bd; a.br = br; a.H = H; a.zmask = zmask; a.hmask = hmask;
+    a.a_hi = s->a_hi; a.a_lo = s->a_lo;
+    a.flags = s->flags; a.err = tc_stack_err(s);
+    a.T = s->T; a.R = s->R; a.NL = s->NL; a.tiles_per_pair = s->T / 128;
+    for (int l = 0; l < 32; ++l) a.f_slot[l] = (signed char)((s->n_fslots > 0 && l < s->NL) ? f_slot[l] : -1);
+    for (int i = 0; i <= s->NL; ++i) a.export_h[i] = export_h[i];
+    cudaMemsetAsync(s->flags, 0, (size_t)(s->R / 128) * sizeof(unsigned), st);
+    const cudaError_t e = launch_coop(tc_fwd_stack_kernel, dim3(s->R / 128), dim3(FWD_THREADS), FS_SMEM, st, a);
+    ast_launch_counter += 1;
+    return e == cudaSuccess ? 0 : -1;
 }
 
 void tc_layer_bwd(TcState* s, int l, const uint32_t* hmask_in, int df_idx, int sg_slot, int sg_L, const uint32_t* zmask_in,

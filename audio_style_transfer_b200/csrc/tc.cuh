@@ -22,6 +22,14 @@ void tc_prepare_input(TcState* s, const float* H0, cudaStream_t st);
 // the bf16 hi/lo of relu(H[l+1]), zmask[l], hmask[l+1] and, if f_slot >= 0, bf16(H[l+1]) -> F[f_slot].
 void tc_layer_fwd(TcState* s, int l, const float* bd, const float* br, uint32_t* zmask_out, uint32_t* hmask_out,
                   int f_slot, cudaStream_t st);
+// Whole encoder forward (start conv + all layers) in one cooperative launch; available when the clip has at most
+// one 128-row tile per SM.  Writes zmask[l], hmask[l], the bf16 extract copies, and H[i] only where export_h[i] != 0
+// (i = 0: start-conv output, i = l+1: output of layer l).  *tc_stack_err() != 0 afterwards = a bounded spin expired.
+bool tc_stack_ok(const TcState* s);
+unsigned* tc_stack_err(TcState* s);
+int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b0, const float* bd, const float* br,
+                     float* H, uint32_t* zmask, uint32_t* hmask, const int* f_slot, const unsigned char* export_h,
+                     cudaStream_t st);
 // backward boundary l in NL..0: g += conv^T(dz_l) * hmask + dF[df_idx] (df_idx < 0: none);
 // dz_{l-1} = (g Wr_{l-1}^T) * zmask.  bf16 dz buffers owned by the TcState.  l == NL: no conv (top);
 // l == 0: no 1x1 (bottom).

@@ -1,0 +1,61 @@
+"""Timeline of the whole-stack forward kernel (TL / TLD clock64 stamps, stack_fwd.cuh).
+
+    python scripts/timeline_stack.py [layer] [gatys 0/1]
+Coarse: per layer, when the epilogue saw GEMM1 complete and when the layer's epilogue 2 + publish finished.
+Detailed: every event of ONE layer for a few CTAs.
+"""
+import ctypes as C
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, '.')
+from audio_style_transfer_b200 import _lib, synth  # noqa: E402
+from audio_style_transfer_b200.step import StyleStep  # noqa: E402
+
+layer = int(sys.argv[1]) if len(sys.argv) > 1 else 12
+gatys = bool(int(sys.argv[2])) if len(sys.argv) > 2 else True
+T, NL = 16384, 30
+NT = T // 128
+st = StyleStep(T, [NL - 1], list(range(NL)) if gatys else list(range(9, 29, 2)), gatys, precision='bf16')
+st.set_weights(synth.make_weights(NL, 0, 0.0))
+x = torch.randn(1, T, device='cuda') * 40
+Ec, Gn = st.embeds(x)
+st.set_targets(Ec * 0.9, Gn.roll(1, 1), 100.0)
+buf = torch.zeros(2 * NT * 64, dtype=torch.int64, device='cuda')
+lib = _lib.load()
+for _ in range(3):
+    st.step(x)
+torch.cuda.synchronize()
+lib.ast_debug_tl_layer(layer)
+lib.ast_debug_timeline(C.c_void_p(buf.data_ptr()))
+st.step(x)
+torch.cuda.synchronize()
+lib.ast_debug_timeline(C.c_void_p(0))
+tl = buf.cpu().numpy().reshape(2, NT, 64)
+co, de = tl[0], tl[1]
+print('kernel duration per CTA (cycles): min %d median %d max %d' % tuple(
+    f(co[:, 1] - co[:, 0]) for f in (np.min, np.median, np.max)))
+for cta in (0, 64):
+    t0 = co[cta, 0]
+    acc1 = co[cta, 2:2 + NL] - t0
+    fin = co[cta, 32:32 + NL] - t0
+    print(f'--- CTA {cta}: layer: GEMM1-complete, layer-finished, (period)')
+    prev = 0
+    for l in range(NL):
+        print(f'   l{l:2d} d={1 << (l % 10):3d}  acc1 {acc1[l]:8d}  fin {fin[l]:8d}  period {fin[l] - prev:6d}  (gemm1 wait {acc1[l] - prev:6d})')
+        prev = fin[l]
+names = {0: 'P: layer start', 1: 'P: centre W issued', 2: 'P: flags ok tap0', 3: 'P: tap0 issued', 4: 'P: flags ok tap2',
+         5: 'P: tap2 issued', 6: 'P: W2 issued', 8: 'M: ACT ready', 9: 'M: centre j0 go', 10: 'M: centre j1 go',
+         11: 'M: tap0 j0 go', 12: 'M: tap0 j1 go', 13: 'M: tap2 j0 go', 14: 'M: tap2 j1 go', 15: 'M: acc1 commit issued',
+         16: 'M: gemm2 j0 go', 17: 'M: gemm2 j1 go', 18: 'M: acc2 commit issued', 30: 'E: acc1 complete',
+         32: 'E: epi1 done', 33: 'E: acc2 complete', 35: "E: h' staged (smem+TMEM)", 36: 'E: staged+fenced',
+         37: 'E: published, flag, ACT arrive', 41: 'E: layer done'}
+for cta in (5, 64, 100):
+    ev = de[cta]
+    t0 = min(ev[k] for k in names if ev[k])
+    print(f'--- CTA {cta}, layer {layer} (d={1 << (layer % 10)})')
+    for k in sorted(names, key=lambda k: ev[k]):
+        if ev[k]:
+            print(f'  {names[k]:24s} {ev[k] - t0:8d}')
