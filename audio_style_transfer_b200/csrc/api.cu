@@ -75,6 +75,7 @@ struct ast_ctx {
     int launches_per_step;         // kernels of the last forward + the last backward
     int launches_fwd, launches_bwd;
     bool use_stack;                // whole-stack forward kernel (one launch) instead of one kernel per layer
+    bool use_stack_bwd;            // likewise for the backward sweep
     unsigned char h_kept[33];      // H[i] of the last forward is valid in global memory
     cudaEvent_t ev[5];
 };
@@ -260,7 +261,8 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
                           (int64_t)c->B * c->nmat * c->gram_nchunk, &c->bytes, &why);
         if (!c->tc) { ast_destroy(c); return fail(AST_ECUDA, "tensor-core path setup failed: %s", why ? why : "?"); }
         const char* no = getenv("AST_B200_NO_STACK");           // A/B switch for profiling: one kernel per layer instead
-        c->use_stack = tc_stack_ok(c->tc) && !(no && no[0] == '1');
+        c->use_stack = tc_stack_ok(c->tc) && !(no && no[0] == '1');                      // "1": per-layer kernels both ways
+        c->use_stack_bwd = c->use_stack && !(no && no[0] == '2');                        // "2": whole-stack forward only
     }
     if (cudaDeviceSynchronize() != cudaSuccess || cudaGetLastError() != cudaSuccess) { ast_destroy(c); return fail(AST_ECUDA, "context setup failed"); }
     *out = c;
@@ -424,8 +426,17 @@ extern "C" int ast_step_backward(ast_ctx* c, float* d_losses, float* d_grad, voi
             init[l] = true;
         }
     }
+    if (c->tc && c->use_stack_bwd) {
+        int df_idx[33], sg_slot[33];
+        for (int l = 0; l <= c->NL; ++l) {
+            df_idx[l] = (l >= 1) ? c->head_buf[l - 1] : -1;
+            sg_slot[l] = -1;
+            if (fuse_sg && l >= 1 && c->f_slot[l - 1] >= 0 && !is_cont[l - 1]) { sg_slot[l] = c->f_slot[l - 1]; df_idx[l] = -1; }
+        }
+        tc_backward_stack(c->tc, c->hmask, c->zmask, df_idx, sg_slot, c->L, c->g, s);
+    }
     int cur = 0;
-    for (int l = c->NL; l >= 0; --l) {
+    for (int l = c->NL; l >= 0 && !(c->tc && c->use_stack_bwd); --l) {
         const float* dF = (l >= 1 && c->head_buf[l - 1] >= 0) ? dFb(c, c->head_buf[l - 1]) : nullptr;
         if (c->tc) {
             int df_idx = (l >= 1) ? c->head_buf[l - 1] : -1, sg_slot = -1;

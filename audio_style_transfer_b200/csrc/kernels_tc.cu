@@ -316,6 +316,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_kernel(const __grid_con
 }
 
 #include "stack_fwd.cuh"
+#include "stack_bwd.cuh"
 void tc_set_tl_layer(int l) { cudaMemcpyToSymbol(g_tl_layer, &l, sizeof(l)); }
 
 // =============================================================================================
@@ -691,6 +692,7 @@ TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_he
     }
     if (!ok) { *why = "cuTensorMapEncodeTiled failed"; tc_destroy(s); return nullptr; }
     if (cudaFuncSetAttribute(tc_fwd_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FS_SMEM) != cudaSuccess ||
+        cudaFuncSetAttribute(tc_bwd_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BS_SMEM) != cudaSuccess ||
         cudaFuncSetAttribute(tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM) != cudaSuccess ||
         cudaFuncSetAttribute(tc_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM) != cudaSuccess) {
         *why = "cudaFuncSetAttribute(max dynamic smem) failed";
@@ -765,6 +767,27 @@ int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b
     for (int i = 0; i <= s->NL; ++i) a.export_h[i] = export_h[i];
     cudaMemsetAsync(s->flags, 0, (size_t)(s->R / 128) * sizeof(unsigned), st);
     const cudaError_t e = launch_coop(tc_fwd_stack_kernel, dim3(s->R / 128), dim3(FWD_THREADS), FS_SMEM, st, a);
+    ast_launch_counter += 1;
+    return e == cudaSuccess ? 0 : -1;
+}
+
+int tc_backward_stack(TcState* s, const uint32_t* hmask, const uint32_t* zmask, const int* df_idx, const int* sg_slot,
+                      int sg_L, float* g, cudaStream_t st) {
+    BwdStackArgs a;
+    memset(&a, 0, sizeof(a));
+    a.tmDz = s->tm_dz; a.tmW1 = s->tm_w1b; a.tmW2 = s->tm_w2b; a.tmDF = s->tm_dF;
+    a.tmF = s->n_fslots > 0 ? s->tm_F : s->tm_dz; a.tmS = s->n_fslots > 0 ? s->tm_ssym : s->tm_w2b;   // unused without slots
+    a.dz = s->dz; a.g = g; a.hmask = hmask; a.zmask = zmask;
+    const size_t nt = (size_t)(s->R / 128);
+    a.flags = s->flags + nt; a.err = tc_stack_err(s) + 1;
+    a.T = s->T; a.R = s->R; a.NL = s->NL; a.tiles_per_pair = s->T / 128; a.sg_L = sg_L;
+    for (int l = 0; l < 33; ++l) { a.df_idx[l] = -1; a.sg_slot[l] = -1; }
+    for (int l = 0; l <= s->NL; ++l) {
+        a.sg_slot[l] = (signed char)((s->n_fslots > 0 && df_idx[l] < 0) ? sg_slot[l] : -1);
+        a.df_idx[l] = (signed char)df_idx[l];
+    }
+    cudaMemsetAsync(s->flags + nt, 0, nt * sizeof(unsigned), st);
+    const cudaError_t e = launch_coop(tc_bwd_stack_kernel, dim3(s->R / 128), dim3(FWD_THREADS), BS_SMEM, st, a);
     ast_launch_counter += 1;
     return e == cudaSuccess ? 0 : -1;
 }

@@ -59,18 +59,22 @@ __device__ int g_tl_layer = 12;
 
 // Waits until every tile that holds rows [t, t+127] of pair b (clipped to the pair; one or two tiles) has published
 // `need` increments.  Both flags are polled in the same loop so that their L2 round trips overlap.
-__device__ __forceinline__ void fs_wait_rows(const FwdStackArgs& p, int b, int t, unsigned need) {
+__device__ __forceinline__ void stack_wait_rows(const unsigned* flags, int tiles_per_pair, int T, unsigned* err, int b, int t,
+                                                unsigned need) {
+    if (t + 127 < 0 || t >= T) return;                       // no such rows in this pair: nothing to wait for
     const int lo = (t < 0 ? 0 : t) >> 7;
-    const int hi = ((t + 127 >= p.T ? p.T - 1 : t + 127)) >> 7;
-    if (t + 127 < 0 || t >= p.T) return;                     // no such rows in this pair: nothing to wait for
-    const unsigned* f0 = p.flags + (size_t)b * p.tiles_per_pair + lo;
-    const unsigned* f1 = p.flags + (size_t)b * p.tiles_per_pair + hi;
+    const int hi = ((t + 127 >= T ? T - 1 : t + 127)) >> 7;
+    const unsigned* f0 = flags + (size_t)b * tiles_per_pair + lo;
+    const unsigned* f1 = flags + (size_t)b * tiles_per_pair + hi;
     unsigned spins = 0;
     for (;;) {
         const unsigned v0 = ld_acquire_gpu(f0), v1 = ld_acquire_gpu(f1);
         if (v0 >= need && v1 >= need) break;
-        if (++spins > FS_SPIN_LIMIT) { atomicExch(p.err, 1u); break; }
+        if (++spins > FS_SPIN_LIMIT) { atomicExch(err, 1u); break; }
     }
+}
+__device__ __forceinline__ void fs_wait_rows(const FwdStackArgs& p, int b, int t, unsigned need) {
+    stack_wait_rows(p.flags, p.tiles_per_pair, p.T, p.err, b, t, need);
 }
 
 __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }

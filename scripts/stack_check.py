@@ -23,6 +23,7 @@ T = int(sys.argv[1]) if len(sys.argv) > 1 else 2048
 NL = int(sys.argv[2]) if len(sys.argv) > 2 else 12
 gatys = bool(int(sys.argv[3])) if len(sys.argv) > 3 else True
 B = int(sys.argv[4]) if len(sys.argv) > 4 else 1
+REF_MODE = sys.argv[5] if len(sys.argv) > 5 else "1"      # "1": per-layer kernels; "2": stack forward + per-layer backward
 w = synth.make_weights(NL, 0, 0.1)
 torch.manual_seed(0)
 x = torch.randn(B, T, device='cuda') * 40
@@ -30,7 +31,7 @@ cont, style = [NL - 1], list(range(NL)) if gatys else list(range(min(NL, 10)))
 
 
 def make(no_stack):
-    os.environ["AST_B200_NO_STACK"] = "1" if no_stack else "0"
+    os.environ["AST_B200_NO_STACK"] = REF_MODE if no_stack else "0"
     st = StyleStep(T, cont, style, gatys, precision='bf16', B=B)
     st.set_weights(w)
     return st
