@@ -45,6 +45,10 @@ struct alignas(64) BwdStackArgs {
 #define BSB_ANTI 152u
 #define BSB_TMEM 160u
 
+// timeline (scripts/timeline_stack.py): detailed stamps of boundary g_tl_layer in block 2 of the buffer, one stamp per
+// boundary (publish done) in block 3
+#define TLB(i) do { if (g_timeline && l == g_tl_layer) g_timeline[((size_t)2 * gridDim.x + blockIdx.x) * 64 + (i)] = clock64(); } while (0)
+#define TLC() do { if (g_timeline && l < 64) g_timeline[((size_t)3 * gridDim.x + blockIdx.x) * 64 + l] = clock64(); } while (0)
 // bf16(v[0..7]) -> one 16-byte chunk at byte offset `off` of a swizzled tile
 __device__ __forceinline__ void stage8_bf16(uint8_t* tile, uint32_t off, const float* v) {
     *reinterpret_cast<uint4*>(tile + off) =
@@ -95,6 +99,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_bwd_stack_kernel(const __gr
                 const bool g1 = l < NL, g2 = l >= 1;
                 const int d = 1 << (l % 10);
                 const int df = p.df_idx[l], sg = p.sg_slot[l];
+                TLB(0);
                 if (df >= 0 || sg >= 0) {                     // head gradient operands: independent of the sweep
                     if (io_n > 0) mbar_wait(bar + BSB_IOFREE, (io_n - 1u) & 1u);
                     ++io_n;
@@ -114,18 +119,30 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_bwd_stack_kernel(const __gr
                         const uint32_t slot = acquire();
                         tma_load_2d(s_ring + slot * TILE16, &p.tmW1, bar + BSB_FULL(slot), j * 64, w1row + k * 128);
                     };
+                    // Fill order (= the MMA issuer's take order): all weight tiles of this boundary's transposed conv (centre
+                    // tap, then every live side tap: at most 6 slots = the whole ring, none of them waits for a neighbour), then
+                    // ONE poll of all the neighbour flags, then the operand tiles of the side taps.
+                    TLB(1);
                     load_w1(1, 0);                            // centre tap: the dz tile is resident
                     load_w1(1, 1);
-                    for (int k = 0; k < 3; k += 2) {
-                        if (!tap_live(t0, k, -d, p.T)) continue;
-                        const int t = t0 - (k - 1) * d;
-                        stack_wait_rows(p.flags, p.tiles_per_pair, p.T, p.err, b, t, FS_PUB * (unsigned)s);
+                    const bool live0 = tap_live(t0, 0, -d, p.T), live2 = tap_live(t0, 2, -d, p.T);
+                    if (live0) { load_w1(0, 0); load_w1(0, 1); }
+                    if (live2) { load_w1(2, 0); load_w1(2, 1); }
+                    TLB(2);
+                    if (live0 || live2) {
+                        stack_wait_rows2(p.flags, p.tiles_per_pair, p.T, p.err, b, live0 ? t0 + d : t0 - d, live2 ? t0 - d : t0 + d,
+                                         FS_PUB * (unsigned)s);
                         fence_proxy_async_all();
-                        for (int j = 0; j < 2; ++j) {
-                            const uint32_t slot = acquire();
-                            tma_load_4d(s_ring + slot * TILE16, &p.tmDz, bar + BSB_FULL(slot), j * 64, t, b, s & 1);
-                            load_w1(k, j);
+                        TLB(3);
+                        for (int k = 0; k < 3; k += 2) {
+                            if (!(k == 0 ? live0 : live2)) continue;
+                            const int t = t0 - (k - 1) * d;
+                            for (int j = 0; j < 2; ++j) {
+                                const uint32_t slot = acquire();
+                                tma_load_4d(s_ring + slot * TILE16, &p.tmDz, bar + BSB_FULL(slot), j * 64, t, b, s & 1);
+                            }
                         }
+                        TLB(4);
                     }
                 }
                 if (g2) {
@@ -138,10 +155,10 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_bwd_stack_kernel(const __gr
                     // The adjacent tiles were waited for above unless d_l >= 128; the far taps need the extra look.
                     if (l + 1 < NL && bs_anti_needed(l + 1)) {
                         const int dp = 1 << ((l + 1) % 10);
-                        stack_wait_rows(p.flags, p.tiles_per_pair, p.T, p.err, b, t0 - dp, FS_PUB * (unsigned)s);
-                        stack_wait_rows(p.flags, p.tiles_per_pair, p.T, p.err, b, t0 + dp, FS_PUB * (unsigned)s);
+                        stack_wait_rows2(p.flags, p.tiles_per_pair, p.T, p.err, b, t0 - dp, t0 + dp, FS_PUB * (unsigned)s);
                         mbar_arrive(bar + BSB_ANTI);
                     }
+                    TLB(8);
                 }
             }
         }
@@ -168,21 +185,27 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_bwd_stack_kernel(const __gr
                     mbar_wait(bar + BSB_DZ, dz_n & 1u);       // own dz_l staged
                     ++dz_n;
                     tc_fence_after();
+                    TLB(10);
                     for (int j = 0; j < 2; ++j) {
                         const uint32_t sw = take();
                         tc_fence_after();
+                        TLB(11 + j);
                         mma4(acc1, s_dz + j * TILE16, s_ring + sw * TILE16, j > 0 ? 1u : 0u);
                         umma_commit(bar + BSB_EMPTY(sw));
                     }
+                    uint32_t sw[2][2];
+                    const bool live0 = tap_live(t0, 0, -d, p.T), live2 = tap_live(t0, 2, -d, p.T);
+                    if (live0) { sw[0][0] = take(); sw[0][1] = take(); }        // weights first (producer fill order)
+                    if (live2) { sw[1][0] = take(); sw[1][1] = take(); }
                     for (int k = 0; k < 3; k += 2) {
-                        if (!tap_live(t0, k, -d, p.T)) continue;
+                        if (!(k == 0 ? live0 : live2)) continue;
                         for (int j = 0; j < 2; ++j) {
                             const uint32_t sa = take();
-                            const uint32_t sw = take();
                             tc_fence_after();
-                            mma4(acc1, s_ring + sa * TILE16, s_ring + sw * TILE16, 1u);
+                            TLB(13 + k + j);
+                            mma4(acc1, s_ring + sa * TILE16, s_ring + sw[k >> 1][j] * TILE16, 1u);
                             umma_commit(bar + BSB_EMPTY(sa));
-                            umma_commit(bar + BSB_EMPTY(sw));
+                            umma_commit(bar + BSB_EMPTY(sw[k >> 1][j]));
                         }
                     }
                 }
@@ -196,16 +219,19 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_bwd_stack_kernel(const __gr
                     ++io_n;
                 }
                 if (g1 || sg >= 0) umma_commit(bar + BSB_ACC1);
+                TLB(17);
                 if (g2) {
                     for (int j = 0; j < 2; ++j) {
                         mbar_wait(bar + BSB_RT(j), rt_n & 1u);
                         const uint32_t sw = take();
                         tc_fence_after();
+                        TLB(18 + j);
                         mma4(acc2, s_rt + j * TILE16, s_ring + sw * TILE16, j > 0 ? 1u : 0u);
                         umma_commit(bar + BSB_EMPTY(sw));
                     }
                     ++rt_n;
                     umma_commit(bar + BSB_ACC2);
+                    TLB(20);
                 }
             }
         }
@@ -229,7 +255,9 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_bwd_stack_kernel(const __gr
             const uint32_t zm = g2 ? p.zmask[((size_t)(l - 1) * p.R + row) * AST_MW + cc] : 0u;
             // ---- epilogue 1: g' = g + acc1 * [h>0] (+ acc3) + dF -> TMEM; bf16(g') -> A operand of the 1x1 GEMM ----
             if (g1 || sg >= 0) { mbar_wait(bar + BSB_ACC1, acc1_n & 1u); ++acc1_n; tc_fence_after(); }
+            if (threadIdx.x == 128) TLB(30);
             if (has_io) { mbar_wait(bar + BSB_IOFULL, io_n & 1u); ++io_n; }
+            if (threadIdx.x == 128) TLB(31);
 #pragma unroll
             for (int sb = 0; sb < 2; ++sb) {
                 const uint32_t col = lane_off + cc * 32 + sb * 16;
@@ -284,11 +312,13 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_bwd_stack_kernel(const __gr
                 if (lane == 0) mbar_arrive(bar + BSB_RT(half));
             }
             tmem_wait_st();
+            if (threadIdx.x == 128) TLB(32);
             if (!g2) break;
             // ---- epilogue 2: dz_{l-1} = acc2 * [z>0] -> bf16: own centre-tap operand (smem) + published tile ----
             mbar_wait(bar + BSB_ACC2, acc2_n & 1u);
             ++acc2_n;
             tc_fence_after();
+            if (threadIdx.x == 128) TLB(33);
 #pragma unroll
             for (int sb = 0; sb < 2; ++sb) {
                 float v[16];
@@ -302,6 +332,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_bwd_stack_kernel(const __gr
             fence_proxy_async_smem();
             tc_fence_before();
             __syncwarp();
+            if (threadIdx.x == 128) TLB(34);
             if (l - 1 >= 0 && l >= 1) {
                 if (l + 1 < NL && bs_anti_needed(l + 1)) { mbar_wait(bar + BSB_ANTI, anti_n & 1u); ++anti_n; }   // see producer
                 // each warp publishes the region it staged itself: 32 rows x 64 bytes (see stack_fwd.cuh)
@@ -315,6 +346,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_bwd_stack_kernel(const __gr
                 __syncwarp();
                 // release before the DZ arrival: cumulative flag counts then imply every warp finished this publish
                 if (lane == 0) { red_release_gpu_add(my_flag, 1u); mbar_arrive(bar + BSB_DZ); }
+                if (threadIdx.x == 128) { TLB(35); TLC(); }
             }
         }
     }

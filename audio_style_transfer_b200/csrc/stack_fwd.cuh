@@ -68,13 +68,31 @@ __device__ __forceinline__ void stack_wait_rows(const unsigned* flags, int tiles
     const unsigned* f1 = flags + (size_t)b * tiles_per_pair + hi;
     unsigned spins = 0;
     for (;;) {
-        const unsigned v0 = ld_acquire_gpu(f0), v1 = ld_acquire_gpu(f1);
+        const unsigned v0 = ld_relaxed_gpu(f0), v1 = ld_relaxed_gpu(f1);
         if (v0 >= need && v1 >= need) break;
         if (++spins > FS_SPIN_LIMIT) { atomicExch(err, 1u); break; }
     }
+    fence_acq_rel_gpu();
 }
-__device__ __forceinline__ void fs_wait_rows(const FwdStackArgs& p, int b, int t, unsigned need) {
-    stack_wait_rows(p.flags, p.tiles_per_pair, p.T, p.err, b, t, need);
+// Same for the rows of two taps (ta, tb) at once: up to four flags polled per round trip.
+__device__ __forceinline__ void stack_wait_rows2(const unsigned* flags, int tiles_per_pair, int T, unsigned* err, int b, int ta,
+                                                 int tb, unsigned need) {
+    const bool la = !(ta + 127 < 0 || ta >= T), lb = !(tb + 127 < 0 || tb >= T);
+    if (!la && !lb) return;
+    if (!la) ta = tb;
+    if (!lb) tb = ta;
+    const unsigned* base = flags + (size_t)b * tiles_per_pair;
+    const unsigned* f0 = base + ((ta < 0 ? 0 : ta) >> 7);
+    const unsigned* f1 = base + ((ta + 127 >= T ? T - 1 : ta + 127) >> 7);
+    const unsigned* f2 = base + ((tb < 0 ? 0 : tb) >> 7);
+    const unsigned* f3 = base + ((tb + 127 >= T ? T - 1 : tb + 127) >> 7);
+    unsigned spins = 0;
+    for (;;) {
+        const unsigned v0 = ld_relaxed_gpu(f0), v1 = ld_relaxed_gpu(f1), v2 = ld_relaxed_gpu(f2), v3 = ld_relaxed_gpu(f3);
+        if (v0 >= need && v1 >= need && v2 >= need && v3 >= need) break;
+        if (++spins > FS_SPIN_LIMIT) { atomicExch(err, 1u); break; }
+    }
+    fence_acq_rel_gpu();
 }
 
 __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
@@ -152,22 +170,32 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_stack_kernel(const __gr
                     tma_load_2d(st, &p.tmW1, fb, j * 64, w1row + (k * 2 + 0) * 128);
                     tma_load_2d(st + TILE16, &p.tmW1, fb, j * 64, w1row + (k * 2 + 1) * 128);
                 };
+                // Fill order (the MMA issuer takes slots in the same order): centre-tap weights; then per live side tap its two
+                // weight slots followed by its two operand slots.  Weights never wait for a neighbour, so they are requested
+                // before the flags are polled; all flags this layer needs are polled in ONE loop before the first operand tile.
                 TLD(0);
                 load_w1(1, 0);                                // centre tap: operand tile is resident, weights only
                 load_w1(1, 1);
                 TLD(1);
+                const bool live0 = tap_live(t0, 0, d, p.T), live2 = tap_live(t0, 2, d, p.T);
+                bool polled = false;
                 for (int k = 0; k < 3; k += 2) {
-                    if (!tap_live(t0, k, d, p.T)) continue;
+                    if (!(k == 0 ? live0 : live2)) continue;
                     const int t = t0 + (k - 1) * d;
-                    fs_wait_rows(p, b, t, FS_PUB * (unsigned)(l + 1));  // relu(h_l) of those rows is in global memory
-                    fence_proxy_async_all();
-                    TLD(2 + k);
+                    load_w1(k, 0);
+                    load_w1(k, 1);
+                    if (!polled) {                            // relu(h_l) of the tap rows is in global memory
+                        stack_wait_rows2(p.flags, p.tiles_per_pair, p.T, p.err, b, live0 ? t0 - d : t0 + d, live2 ? t0 + d : t0 - d,
+                                         FS_PUB * (unsigned)(l + 1));
+                        fence_proxy_async_all();
+                        polled = true;
+                        TLD(2);
+                    }
                     for (int j = 0; j < 2; ++j) {
                         const uint32_t slot = acquire();
                         const uint32_t st = s_ring + slot * FS_SLOT, fb = bar + FSB_FULL(slot);
                         tma_load_4d(st, &p.tmA_hi, fb, j * 64, t, b, l & 1);
                         tma_load_4d(st + TILE16, &p.tmA_lo, fb, j * 64, t, b, l & 1);
-                        load_w1(k, j);
                     }
                     TLD(3 + k);
                 }
@@ -184,8 +212,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_stack_kernel(const __gr
                 // far taps (d_{l-1} >= 128, incl. the 512 -> 1 wrap) need this extra look, done here off the critical path.
                 if (l >= 1 && l + 1 < p.NL && ((l - 1) % 10) >= 7) {
                     const int dp = 1 << ((l - 1) % 10);
-                    fs_wait_rows(p, b, t0 - dp, FS_PUB * (unsigned)(l + 1));
-                    fs_wait_rows(p, b, t0 + dp, FS_PUB * (unsigned)(l + 1));
+                    stack_wait_rows2(p.flags, p.tiles_per_pair, p.T, p.err, b, t0 - dp, t0 + dp, FS_PUB * (unsigned)(l + 1));
                     mbar_arrive(bar + FSB_ANTI);
                 }
             }
@@ -228,14 +255,16 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_stack_kernel(const __gr
                 }
                 for (int k = 0; k < 3; k += 2) {
                     if (!tap_live(t0, k, d, p.T)) continue;
+                    uint32_t sw[2];
+                    sw[0] = take();                           // weights of both K-halves arrive first (producer fill order)
+                    sw[1] = take();
                     for (int j = 0; j < 2; ++j) {
                         const uint32_t sa = take();
-                        const uint32_t sw = take();
                         tc_fence_after();
                         TLD(11 + k + j);
-                        mma_slice(acc1, s_ring + sa * FS_SLOT, s_ring + sw * FS_SLOT, 1u);
+                        mma_slice(acc1, s_ring + sa * FS_SLOT, s_ring + sw[j] * FS_SLOT, 1u);
                         umma_commit(bar + FSB_EMPTY(sa));
-                        umma_commit(bar + FSB_EMPTY(sw));
+                        umma_commit(bar + FSB_EMPTY(sw[j]));
                     }
                 }
                 umma_commit(bar + FSB_ACC1);

@@ -199,6 +199,20 @@ class StyleStep:
         return out
 
     @property
+    def uses_stack_kernels(self) -> bool:
+        """True when the encoder forward / backward run as ONE cooperative kernel each (clip fits one tile per SM)."""
+        f = self.lib.ast_debug_uses_stack
+        f.argtypes = [C.c_void_p]
+        return bool(f(self._h))
+
+    @property
+    def stack_error(self) -> bool:
+        """True if a bounded spin of the whole-stack kernels ever expired in this context (results invalid)."""
+        f = self.lib.ast_debug_stack_err
+        f.argtypes = [C.c_void_p]
+        return bool(f(self._h))
+
+    @property
     def launches_per_step(self) -> int:
         return int(self.lib.ast_launches_per_step(self._h))
 

@@ -299,21 +299,31 @@ def run_ours(args):
         reps = [st.step_timed(x, losses, grad) for _ in range(8)][3:]
         phases = [float(np.median([r[i] for r in reps])) for i in range(4)]
         enc_ms, bwd_ms, gram_ms, tot_ms = phases
-        fl_launch = 2.0 * B * T * 128 * 128 * 4                      # one layer kernel: K=3 conv + 1x1, 2 FLOP/MAC
-        dur_fwd = enc_ms * 1e-3 / NL                                  # average launch duration inside the encoder phase
-        dur_bwd = bwd_ms * 1e-3 / (NL + 1)
+        fl_layer = 2.0 * B * T * 128 * 128 * 4                       # one layer: K=3 conv + 1x1, 2 FLOP/MAC
+        stack = args.precision == "bf16" and st.uses_stack_kernels
+        n_sg = L if (wl["gatys"] and args.precision == "bf16") else 0  # style-gradient GEMMs fused into the backward
+        if stack:
+            # ONE launch runs the start conv and all NL layers; the graph phase = that kernel + a 512-byte memset node
+            fl_launch, dur_fwd, kname = fl_layer * NL, enc_ms * 1e-3, "tc_fwd_stack_kernel"
+            note = "launch duration = encoder-forward graph phase (one cooperative kernel covering all layers)"
+            fl_bwd, dur_bwd, kbwd = fl_layer * NL + 2.0 * B * T * 128 * 128 * n_sg, bwd_ms * 1e-3, "tc_bwd_stack_kernel"
+        else:
+            fl_launch, dur_fwd = fl_layer, enc_ms * 1e-3 / NL        # average launch duration inside the encoder phase
+            kname = "tc_fwd_kernel" if args.precision == "bf16" else "layer_f32_kernel<fwd>"
+            note = "avg = encoder-forward graph phase / n_layers (includes start conv + launch gaps)"
+            fl_bwd, dur_bwd, kbwd = fl_layer, bwd_ms * 1e-3 / (NL + 1), "tc_bwd_kernel"
         ach = fl_launch / dur_fwd / 1e12
         traffic = None
         tj = ROOT / "profiles" / "r1_traffic.json"
         if tj.exists() and name == "cfg1" and B == 1 and args.precision == "bf16":     # captured on exactly this workload
-            traffic = json.loads(tj.read_text())["tc_fwd_kernel"]["traffic"]
-        roof = {"bound": "tensor", "kernel": "tc_fwd_kernel" if args.precision == "bf16" else "layer_f32_kernel<fwd>",
+            traffic = json.loads(tj.read_text()).get(kname, {}).get("traffic")
+        roof = {"bound": "tensor", "kernel": kname,
                 "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": ach / pk["tflops"], "traffic": traffic,
                 "traffic_source": "profiles/r1_traffic.json (ncu --set full, dram read+write per launch)" if traffic else None,
                 "peak_source": pk["src"] + " (bf16 sustained)", "flops_per_launch": fl_launch,
-                "avg_launch_us": dur_fwd * 1e6,
-                "note": "avg = encoder-forward graph phase / n_layers (includes start conv + launch gaps)",
-                "bwd_layer": {"achieved": fl_launch / dur_bwd / 1e12, "avg_launch_us": dur_bwd * 1e6},
+                "avg_launch_us": dur_fwd * 1e6, "note": note,
+                "bwd": {"kernel": kbwd, "achieved": fl_bwd / dur_bwd / 1e12, "avg_launch_us": dur_bwd * 1e6,
+                        "note": "duration = heads + head gradients + backward sweep + start-conv adjoint phase"},
                 "phases_ms": {"encoder_fwd": enc_ms, "gram_partials": gram_ms, "heads_bwd": bwd_ms, "total": tot_ms}}
     if rank != 0:
         if world > 1:

@@ -23,7 +23,7 @@ st.set_weights(synth.make_weights(NL, 0, 0.0))
 x = torch.randn(1, T, device='cuda') * 40
 Ec, Gn = st.embeds(x)
 st.set_targets(Ec * 0.9, Gn.roll(1, 1), 100.0)
-buf = torch.zeros(2 * NT * 64, dtype=torch.int64, device='cuda')
+buf = torch.zeros(4 * NT * 64, dtype=torch.int64, device='cuda')
 lib = _lib.load()
 for _ in range(3):
     st.step(x)
@@ -33,8 +33,8 @@ lib.ast_debug_timeline(C.c_void_p(buf.data_ptr()))
 st.step(x)
 torch.cuda.synchronize()
 lib.ast_debug_timeline(C.c_void_p(0))
-tl = buf.cpu().numpy().reshape(2, NT, 64)
-co, de = tl[0], tl[1]
+tl = buf.cpu().numpy().reshape(4, NT, 64)
+co, de, bde, bco = tl[0], tl[1], tl[2], tl[3]
 print('kernel duration per CTA (cycles): min %d median %d max %d' % tuple(
     f(co[:, 1] - co[:, 0]) for f in (np.min, np.median, np.max)))
 for cta in (0, 64):
@@ -46,7 +46,7 @@ for cta in (0, 64):
     for l in range(NL):
         print(f'   l{l:2d} d={1 << (l % 10):3d}  acc1 {acc1[l]:8d}  fin {fin[l]:8d}  period {fin[l] - prev:6d}  (gemm1 wait {acc1[l] - prev:6d})')
         prev = fin[l]
-names = {0: 'P: layer start', 1: 'P: centre W issued', 2: 'P: flags ok tap0', 3: 'P: tap0 issued', 4: 'P: flags ok tap2',
+names = {0: 'P: layer start', 1: 'P: centre W issued', 2: 'P: all flags ok', 3: 'P: tap0 issued', 4: 'P: (unused)',
          5: 'P: tap2 issued', 6: 'P: W2 issued', 8: 'M: ACT ready', 9: 'M: centre j0 go', 10: 'M: centre j1 go',
          11: 'M: tap0 j0 go', 12: 'M: tap0 j1 go', 13: 'M: tap2 j0 go', 14: 'M: tap2 j1 go', 15: 'M: acc1 commit issued',
          16: 'M: gemm2 j0 go', 17: 'M: gemm2 j1 go', 18: 'M: acc2 commit issued', 30: 'E: acc1 complete',
@@ -59,3 +59,22 @@ for cta in (5, 64, 100):
     for k in sorted(names, key=lambda k: ev[k]):
         if ev[k]:
             print(f'  {names[k]:24s} {ev[k] - t0:8d}')
+
+print('=== backward stack kernel')
+for cta in (64,):
+    done = bco[cta, 1:NL + 1]                 # stamp at boundary l = publish of dz_{l-1} done
+    print(f'--- CTA {cta}: boundary period (cycles), boundaries {NL}..1')
+    print('   ', [int(done[l - 1] - done[l]) for l in range(NL - 1, 0, -1)])
+bnames = {0: 'P: boundary start', 1: 'P: IO issued', 2: 'P: centre W issued', 3: 'P: all flags ok', 4: 'P: dz tiles issued',
+          5: 'P: flags ok tap2', 6: 'P: tap2 issued', 8: 'P: W2 issued (+anti)', 10: 'M: DZ ready', 11: 'M: centre j0 go',
+          12: 'M: centre j1 go', 13: 'M: tap0 j0 go', 14: 'M: tap0 j1 go', 15: 'M: tap2 j0 go', 16: 'M: tap2 j1 go',
+          17: 'M: acc1 commit issued', 18: 'M: gemm2 j0 go', 19: 'M: gemm2 j1 go', 20: 'M: acc2 commit issued',
+          30: 'E: acc1 complete', 31: 'E: IO landed', 32: 'E: epi1 done', 33: 'E: acc2 complete', 34: 'E: dz staged',
+          35: 'E: published, flag, DZ arrive'}
+for cta in (64, 100):
+    ev = bde[cta]
+    t0 = min(ev[k] for k in bnames if ev[k])
+    print(f'--- CTA {cta}, boundary {layer} (d={1 << (layer % 10)})')
+    for k in sorted(bnames, key=lambda k: ev[k]):
+        if ev[k]:
+            print(f'  {bnames[k]:28s} {ev[k] - t0:8d}')
