@@ -504,14 +504,23 @@ __global__ void __launch_bounds__(256) content_sse_kernel(const float* const* __
     const int b = blockIdx.y;
     const int ncols = n_cont * cnt_ch;
     double s = 0.0;
+    const bool vec = (cnt_ch & 3) == 0;               // 16-byte loads (Pc rows stay 16-byte aligned: ncols % 4 == 0)
     for (int t = own_lo + blockIdx.x * 8 + warp; t < own_hi; t += gridDim.x * 8) {
         const size_t row = (size_t)b * T + t;
         for (int slot = 0; slot < n_cont; ++slot) {
             const float* h = Hc[slot] + row * AST_C;
             const float* p = Pc + row * ncols + (size_t)slot * cnt_ch;
-            for (int j = lane; j < cnt_ch; j += 32) {
-                const float d = h[j] - p[j];
-                s += (double)d * (double)d;
+            if (vec) {
+                for (int j = lane * 4; j < cnt_ch; j += 128) {
+                    const float4 a = *reinterpret_cast<const float4*>(h + j), c = *reinterpret_cast<const float4*>(p + j);
+                    const float d0 = a.x - c.x, d1 = a.y - c.y, d2 = a.z - c.z, d3 = a.w - c.w;
+                    s += ((double)d0 * (double)d0 + (double)d1 * (double)d1) + ((double)d2 * (double)d2 + (double)d3 * (double)d3);
+                }
+            } else {
+                for (int j = lane; j < cnt_ch; j += 32) {
+                    const float d = h[j] - p[j];
+                    s += (double)d * (double)d;
+                }
             }
         }
     }
@@ -561,35 +570,56 @@ __global__ void __launch_bounds__(1024) heads_kernel(const HeadArgs a) {
     const float* G = a.G + ((size_t)b * a.nmat + mat) * msize;
     const bool used = mat < a.nmat_used;
     const float* Ps = used ? a.Ps + ((size_t)b * a.nmat_used + mat) * msize : nullptr;
+    // The kernel is a chain of block reductions, i.e. latency: G and Ps are loaded ONCE into registers (<= 16 elements per
+    // thread: msize <= 16 blockDim for both head types), and the two sums of the second pass share one reduction.
+    // The style loss keeps the direct sum of (gn - Ps)^2: the algebraic one-pass form cancels when gn is close to Ps.
+    float gr[16], pr[16];
     double ss = 0.0;
-    for (int e = threadIdx.x; e < msize; e += blockDim.x) { const double g = G[e]; ss += g * g; }
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        const int e = threadIdx.x + k * blockDim.x;
+        gr[k] = e < msize ? G[e] : 0.f;
+        pr[k] = (used && e < msize) ? Ps[e] : 0.f;
+        ss += (double)gr[k] * (double)gr[k];
+    }
     ss = block_sum_d(ss, red);
     const double inv = 1.0 / sqrt(fmax(ss, 1e-12));
     double ls = 0.0, dot = 0.0;
     if (used) {
-        for (int e = threadIdx.x; e < msize; e += blockDim.x) {
-            const double gn = (double)G[e] * inv;
-            const double d = gn - (double)Ps[e];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            const double gn = (double)gr[k] * inv;
+            const double d = gn - (double)pr[k];
             ls += d * d;
             dot += (double)a.coef_dGn * d * gn;
         }
     }
-    ls = block_sum_d(ls, red);
-    dot = block_sum_d(dot, red);
+    {
+        ls = warp_sum_d(ls); dot = warp_sum_d(dot);
+        __shared__ double red2[2][32];
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (int)(blockDim.x >> 5);
+        if (lane == 0) { red2[0][warp] = ls; red2[1][warp] = dot; }
+        __syncthreads();
+        ls = 0.0; dot = 0.0;
+        for (int i = 0; i < nw; ++i) { ls += red2[0][i]; dot += red2[1][i]; }      // same order in every thread
+    }
     if (threadIdx.x == 0) a.ls_part[(size_t)b * a.nmat + mat] = (float)ls;
     const bool clamped = ss < 1e-12;
     float* Gn = a.Gn ? a.Gn + ((size_t)b * a.nmat + mat) * msize : nullptr;
     float* Ss = a.Ssym ? a.Ssym + ((size_t)b * a.nmat + mat) * msize : nullptr;
     __nv_bfloat16* Sb = a.Ssym_bf16 ? a.Ssym_bf16 + ((size_t)b * a.nmat + mat) * msize : nullptr;
-    for (int e = threadIdx.x; e < msize; e += blockDim.x) {
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        const int e = threadIdx.x + k * blockDim.x;
+        if (e >= msize) break;
         const int i = e / n, j = e - i * n;
         const int et = j * n + i;
-        const double gn = (double)G[e] * inv, gnt = (double)G[et] * inv;
+        const double gn = (double)gr[k] * inv, gnt = (double)G[et] * inv;
         if (Gn) Gn[e] = (float)gn;
         if (Ss) {
             double v = 0.0;
             if (used) {
-                const double dgn = (double)a.coef_dGn * (gn - (double)Ps[e]);
+                const double dgn = (double)a.coef_dGn * (gn - (double)pr[k]);
                 const double dgnt = (double)a.coef_dGn * (gnt - (double)Ps[et]);
                 const double dg = clamped ? dgn * inv : (dgn - gn * dot) * inv;
                 const double dgt = clamped ? dgnt * inv : (dgnt - gnt * dot) * inv;
@@ -740,18 +770,25 @@ void launch_style_grad_gatys(const float* const* d_F, float* const* d_dF, const 
 // content: dF[t,j] (+)= coef (H[t,j] - Pc[t, slot*cnt + j]) for j < cnt (methods.py:58,116-117)
 __global__ void content_grad_kernel(const float* __restrict__ H, const float* __restrict__ Pc, float* __restrict__ dF,
                                     int slot, int n_cont, int cnt_ch, float coef, int accumulate, int R) {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= (size_t)R * AST_C) return;
-    const size_t row = i / AST_C;
-    const int j = (int)(i % AST_C);
-    float v = 0.f;
-    if (j < cnt_ch) v = coef * (H[i] - Pc[row * (size_t)(n_cont * cnt_ch) + (size_t)slot * cnt_ch + j]);
-    dF[i] = accumulate ? dF[i] + v : v;
+    const size_t i4 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;      // one thread = 4 consecutive channels of a row
+    if (i4 >= (size_t)R * (AST_C / 4)) return;
+    const size_t row = i4 / (AST_C / 4);
+    const int j = (int)(i4 % (AST_C / 4)) * 4;
+    const float4 h = reinterpret_cast<const float4*>(H)[i4];
+    const float* p = Pc + row * (size_t)(n_cont * cnt_ch) + (size_t)slot * cnt_ch + j;
+    float4 v;
+    v.x = j + 0 < cnt_ch ? coef * (h.x - p[0]) : 0.f;
+    v.y = j + 1 < cnt_ch ? coef * (h.y - p[1]) : 0.f;
+    v.z = j + 2 < cnt_ch ? coef * (h.z - p[2]) : 0.f;
+    v.w = j + 3 < cnt_ch ? coef * (h.w - p[3]) : 0.f;
+    float4* out = reinterpret_cast<float4*>(dF) + i4;
+    if (accumulate) { const float4 o = *out; v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
+    *out = v;
 }
 void launch_content_grad(const float* H, const float* Pc, float* dF, int slot, int n_cont, int cnt_ch, float coef,
                          int accumulate, int R, cudaStream_t s) {
-    const size_t n = (size_t)R * AST_C;
-    content_grad_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(H, Pc, dF, slot, n_cont, cnt_ch, coef, accumulate, R);
+    const size_t n4 = (size_t)R * (AST_C / 4);
+    content_grad_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, s>>>(H, Pc, dF, slot, n_cont, cnt_ch, coef, accumulate, R);
     ast_launch_counter += 1;
 }
 // Ec[t, slot*cnt + j] = extracts[id_slot][t, j]  (methods.py:58)
