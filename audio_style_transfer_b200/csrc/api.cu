@@ -364,6 +364,7 @@ extern "C" int ast_step_forward(ast_ctx* c, const float* d_x, void* stream) {
     cudaStream_t s = (cudaStream_t)stream;
     const int before = ast_launch_counter;
     run_encoder(c, d_x, s, false);
+    // (Forking the content SSE onto a second stream next to the Gram kernels was measured: no gain within run-to-run noise.)
     run_gram(c, s);
     launch_content_sse(c->d_Hcptr, c->n_cont, c->cfg.cnt_channels, c->Pc, c->T, c->B, c->own_lo, c->own_hi,
                        c->sse_part, c->sse_nblk, c->partials + (size_t)c->B * c->nmat * c->msize, s);

@@ -120,7 +120,10 @@ int  ast_step_forward(ast_ctx* ctx, const float* d_x, void* stream);
 int  ast_partials(ast_ctx* ctx, float** d_buf, int64_t* count);
 int  ast_step_backward(ast_ctx* ctx, float* d_losses, float* d_grad, void* stream);
 
-/* cfg.extracts[layer] of the last forward (model.py:116), [B,T,128] fp32 -> d_out.  Debug/parity. */
+/* cfg.extracts[layer] of the last forward (model.py:116), [B,T,128] fp32 -> d_out.  Debug/parity.
+ * After ast_embeds every layer is available.  After ast_step* in the tensor-core tier only the layers a head reads
+ * are: the whole-stack kernels keep the residual stream on chip (TMEM) and write the content extracts (and, for the
+ * channel-wise Gram, the style extracts) only; any other layer returns AST_ESTATE ("not retained"). */
 int  ast_get_extract(ast_ctx* ctx, int32_t layer, float* d_out, void* stream);
 
 /* Number of kernels one ast_step launches (for bench.py's gpu_launches). */
