@@ -750,7 +750,8 @@ static cudaError_t launch_coop(Kern kernel, dim3 grid, dim3 block, size_t smem, 
     cfg.attrs = at; cfg.numAttrs = 1;
     return cudaLaunchKernelEx(&cfg, kernel, args);
 }
-bool tc_stack_ok(const TcState* s) { return s && s->coop && s->R / 128 <= s->n_sm && s->NL <= 32; }
+// one pair must fit one tile per SM; bigger batches are launched pair group by pair group
+bool tc_stack_ok(const TcState* s) { return s && s->coop && s->T / 128 <= s->n_sm && s->NL <= 32; }
 unsigned* tc_stack_err(TcState* s) { return s->flags + (size_t)2 * (s->R / 128); }
 int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b0, const float* bd, const float* br,
                      float* H, uint32_t* zmask, uint32_t* hmask, const int* f_slot, const unsigned char* export_h,
@@ -766,8 +767,14 @@ int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b
     for (int l = 0; l < 32; ++l) a.f_slot[l] = (signed char)((s->n_fslots > 0 && l < s->NL) ? f_slot[l] : -1);
     for (int i = 0; i <= s->NL; ++i) a.export_h[i] = export_h[i];
     cudaMemsetAsync(s->flags, 0, (size_t)(s->R / 128) * sizeof(unsigned), st);
-    const cudaError_t e = launch_coop(tc_fwd_stack_kernel, dim3(s->R / 128), dim3(FWD_THREADS), FS_SMEM, st, a);
-    ast_launch_counter += 1;
+    const int tpp = s->T / 128, ppl = s->n_sm / tpp;         // tiles per pair; pairs per launch (all CTAs co-resident)
+    cudaError_t e = cudaSuccess;
+    for (int p0 = 0; p0 < s->B && e == cudaSuccess; p0 += ppl) {
+        const int np = s->B - p0 < ppl ? s->B - p0 : ppl;
+        a.tile0 = p0 * tpp;
+        e = launch_coop(tc_fwd_stack_kernel, dim3(np * tpp), dim3(FWD_THREADS), FS_SMEM, st, a);
+        ast_launch_counter += 1;
+    }
     return e == cudaSuccess ? 0 : -1;
 }
 
@@ -787,8 +794,14 @@ int tc_backward_stack(TcState* s, const uint32_t* hmask, const uint32_t* zmask, 
         a.df_idx[l] = (signed char)df_idx[l];
     }
     cudaMemsetAsync(s->flags + nt, 0, nt * sizeof(unsigned), st);
-    const cudaError_t e = launch_coop(tc_bwd_stack_kernel, dim3(s->R / 128), dim3(FWD_THREADS), BS_SMEM, st, a);
-    ast_launch_counter += 1;
+    const int tpp = s->T / 128, ppl = s->n_sm / tpp;
+    cudaError_t e = cudaSuccess;
+    for (int p0 = 0; p0 < s->B && e == cudaSuccess; p0 += ppl) {
+        const int np = s->B - p0 < ppl ? s->B - p0 : ppl;
+        a.tile0 = p0 * tpp;
+        e = launch_coop(tc_bwd_stack_kernel, dim3(np * tpp), dim3(FWD_THREADS), BS_SMEM, st, a);
+        ast_launch_counter += 1;
+    }
     return e == cudaSuccess ? 0 : -1;
 }
 

@@ -23,6 +23,7 @@ struct alignas(64) BwdStackArgs {
     const uint32_t* hmask; const uint32_t* zmask;        // [NL+1][R][4], [NL][R][4]
     unsigned* flags; unsigned* err;
     int T, R, NL, tiles_per_pair, sg_L;
+    int tile0;                       // global index of this launch's first tile (launches cover whole pairs)
     signed char df_idx[33];          // per boundary l: dF buffer added there, or -1
     signed char sg_slot[33];         // per boundary l: style slot whose F . Ssym is added there, or -1
 };
@@ -63,7 +64,8 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_bwd_stack_kernel(const __gr
     uint8_t* gen = tc_smem_raw + (base - smem_u32(tc_smem_raw));
     const uint32_t s_dz = base + BS_DZ, s_rt = base + BS_RT, s_io = base + BS_IO, s_ring = base + BS_RING, bar = base + BS_BAR;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int row0 = blockIdx.x * 128;
+    const int tile = p.tile0 + (int)blockIdx.x;
+    const int row0 = tile * 128;
     const int b = row0 / p.T, t0 = row0 - b * p.T;
     const int NL = p.NL;
 
@@ -244,7 +246,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_bwd_stack_kernel(const __gr
         const uint32_t lane_off = (uint32_t)(q * 32) << 16;
         uint8_t* dzt = gen + BS_DZ + half * TILE16;
         uint8_t* rtt = gen + BS_RT + half * TILE16;
-        unsigned* my_flag = p.flags + blockIdx.x;
+        unsigned* my_flag = p.flags + tile;
         uint32_t acc1_n = 0, acc2_n = 0, io_n = 0, anti_n = 0;
         for (int l = NL; l >= 0; --l) {
             const int s = NL - l;

@@ -33,6 +33,7 @@ struct alignas(64) FwdStackArgs {
     unsigned* flags;                 // [ntiles], zeroed before the launch; += 1 per epilogue warp per published tile
     unsigned* err;
     int T, R, NL, tiles_per_pair;
+    int tile0;                       // global index of this launch's first tile (launches cover whole pairs)
     signed char f_slot[32];          // style slot that receives bf16(H[l+1]), or -1
     unsigned char export_h[33];      // export_h[i] != 0: H[i] is written to global memory (i = 0: start-conv output)
 };
@@ -130,7 +131,8 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_stack_kernel(const __gr
     uint8_t* gen = tc_smem_raw + (base - smem_u32(tc_smem_raw));
     const uint32_t s_act = base + FS_ACT, s_stg = base + FS_STG, s_ring = base + FS_RING, bar = base + FS_BAR;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int row0 = blockIdx.x * 128;
+    const int tile = p.tile0 + (int)blockIdx.x;
+    const int row0 = tile * 128;
     const int b = row0 / p.T, t0 = row0 - b * p.T;
     if (threadIdx.x == 0) TL(0);
 
@@ -290,7 +292,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_stack_kernel(const __gr
         const uint32_t lane_off = (uint32_t)(q * 32) << 16;
         uint8_t* act = gen + FS_ACT + half * 2 * TILE16;             // K-half `half`: hi, lo
         const bool storer = (q == 0) && ((cc & 1) == 0) && (lane == 0);
-        unsigned* my_flag = p.flags + blockIdx.x;
+        unsigned* my_flag = p.flags + tile;
         uint32_t anti_n = 0;
 
         // The epilogue works in 16-column sub-blocks: with 576 threads the register cap is 96, and two live 32-wide
