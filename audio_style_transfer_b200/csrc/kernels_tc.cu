@@ -22,6 +22,7 @@
 #include <cudaTypedefs.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #define TILE16 16384                            // [128 rows][128 B]: one bf16 K-half or one fp32 32-column group
@@ -316,6 +317,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_kernel(const __grid_con
 }
 
 #include "stack_fwd.cuh"
+#include "stack_fwd2.cuh"
 #include "stack_bwd.cuh"
 void tc_set_tl_layer(int l) { cudaMemcpyToSymbol(g_tl_layer, &l, sizeof(l)); }
 
@@ -692,6 +694,7 @@ TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_he
     }
     if (!ok) { *why = "cuTensorMapEncodeTiled failed"; tc_destroy(s); return nullptr; }
     if (cudaFuncSetAttribute(tc_fwd_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FS_SMEM) != cudaSuccess ||
+        cudaFuncSetAttribute(tc_fwd_stack2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FS_SMEM) != cudaSuccess ||
         cudaFuncSetAttribute(tc_bwd_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BS_SMEM) != cudaSuccess ||
         cudaFuncSetAttribute(tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM) != cudaSuccess ||
         cudaFuncSetAttribute(tc_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM) != cudaSuccess) {
@@ -769,7 +772,21 @@ int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b
     cudaMemsetAsync(s->flags, 0, (size_t)(s->R / 128) * sizeof(unsigned), st);
     const int tpp = s->T / 128, ppl = s->n_sm / tpp;         // tiles per pair; pairs per launch (all CTAs co-resident)
     cudaError_t e = cudaSuccess;
-    for (int p0 = 0; p0 < s->B && e == cudaSuccess; p0 += ppl) {
+    int p0 = 0;
+    // two pairs per CTA ("duo", stack_fwd2.cuh) while at least two pairs are left; a last odd pair runs one tile per CTA
+    // (opt-in experiment, see the header of stack_fwd2.cuh: correct but not faster than one launch per pair group)
+    const char* duo = getenv("AST_B200_DUO");
+    if (duo && duo[0] == '1') {
+        for (; p0 + 2 <= s->B && e == cudaSuccess;) {
+            int np = (s->B - p0) & ~1;
+            if (np > 2 * ppl) np = 2 * ppl;
+            a.tile0 = p0 * tpp;
+            e = launch_coop(tc_fwd_stack2_kernel, dim3((np / 2) * tpp), dim3(FWD_THREADS), FS_SMEM, st, a);
+            ast_launch_counter += 1;
+            p0 += np;
+        }
+    }
+    for (; p0 < s->B && e == cudaSuccess; p0 += ppl) {
         const int np = s->B - p0 < ppl ? s->B - p0 : ppl;
         a.tile0 = p0 * tpp;
         e = launch_coop(tc_fwd_stack_kernel, dim3(np * tpp), dim3(FWD_THREADS), FS_SMEM, st, a);
