@@ -769,6 +769,13 @@ int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b
     a.T = s->T; a.R = s->R; a.NL = s->NL; a.tiles_per_pair = s->T / 128;
     for (int l = 0; l < 32; ++l) a.f_slot[l] = (signed char)((s->n_fslots > 0 && l < s->NL) ? f_slot[l] : -1);
     for (int i = 0; i <= s->NL; ++i) a.export_h[i] = export_h[i];
+    a.nslot = 4;
+    {
+        bool any_f = false;
+        for (int l = 0; l < 32; ++l) any_f = any_f || a.f_slot[l] >= 0;
+        const char* r5 = getenv("AST_B200_RING4");              // A/B switch: keep 4 slots even when the staging tile is unused
+        if (!any_f && !(r5 && r5[0] == '1')) a.nslot = 5;
+    }
     cudaMemsetAsync(s->flags, 0, (size_t)(s->R / 128) * sizeof(unsigned), st);
     const int tpp = s->T / 128, ppl = s->n_sm / tpp;         // tiles per pair; pairs per launch (all CTAs co-resident)
     cudaError_t e = cudaSuccess;

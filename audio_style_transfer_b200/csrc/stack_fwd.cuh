@@ -34,6 +34,7 @@ struct alignas(64) FwdStackArgs {
     unsigned* err;
     int T, R, NL, tiles_per_pair;
     int tile0;                       // global index of this launch's first tile (launches cover whole pairs)
+    int nslot;                       // ring slots: 4, or 5 when no extract copy is staged (the 32 KB staging tile joins the ring)
     signed char f_slot[32];          // style slot that receives bf16(H[l+1]), or -1
     unsigned char export_h[33];      // export_h[i] != 0: H[i] is written to global memory (i = 0: start-conv output)
 };
@@ -44,14 +45,14 @@ struct alignas(64) FwdStackArgs {
 #define FS_SLOT 32768
 #define FS_BAR (FS_RING + 4 * FS_SLOT)
 #define FS_SMEM (FS_BAR + 1024 + 1024)
-#define FSB_FULL(i) (8u * (i))
-#define FSB_EMPTY(i) (32u + 8u * (i))
-#define FSB_ACT 64u
-#define FSB_ACC1 72u
-#define FSB_RT(j) (80u + 8u * (j))
-#define FSB_ACC2 96u
-#define FSB_TMEM 104u
-#define FSB_ANTI 112u
+#define FSB_FULL(i) (8u * (i))                    // up to 8 ring slots
+#define FSB_EMPTY(i) (64u + 8u * (i))
+#define FSB_ACT 128u
+#define FSB_ACC1 136u
+#define FSB_RT(j) (144u + 8u * (j))
+#define FSB_ACC2 160u
+#define FSB_TMEM 168u
+#define FSB_ANTI 176u
 #define FS_PUB 16u                                // flag increments per published operand tile (one per epilogue warp)
 #define FS_SPIN_LIMIT (1u << 22)
 // detailed stamps of ONE layer (g_tl_layer), second half of the timeline buffer: [gridDim.x*64 + cta*64 + i]
@@ -129,7 +130,8 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_stack_kernel(const __gr
     extern __shared__ uint8_t tc_smem_raw[];
     const uint32_t base = (smem_u32(tc_smem_raw) + 1023u) & ~1023u;
     uint8_t* gen = tc_smem_raw + (base - smem_u32(tc_smem_raw));
-    const uint32_t s_act = base + FS_ACT, s_stg = base + FS_STG, s_ring = base + FS_RING, bar = base + FS_BAR;
+    const uint32_t nslot = (uint32_t)p.nslot;
+    const uint32_t s_act = base + FS_ACT, s_stg = base + FS_STG, s_ring = base + (nslot == 5 ? FS_STG : FS_RING), bar = base + FS_BAR;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tile = p.tile0 + (int)blockIdx.x;
     const int row0 = tile * 128;
@@ -139,7 +141,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_stack_kernel(const __gr
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&p.tmA_hi); tma_prefetch_desc(&p.tmA_lo); tma_prefetch_desc(&p.tmW1); tma_prefetch_desc(&p.tmW2);
         tma_prefetch_desc(&p.tmF);
-        for (int i = 0; i < 4; ++i) { mbar_init(bar + FSB_FULL(i), 1); mbar_init(bar + FSB_EMPTY(i), 1); }
+        for (int i = 0; i < 5; ++i) { mbar_init(bar + FSB_FULL(i), 1); mbar_init(bar + FSB_EMPTY(i), 1); }
         mbar_init(bar + FSB_ACT, 16); mbar_init(bar + FSB_ACC1, 1);
         mbar_init(bar + FSB_RT(0), 8); mbar_init(bar + FSB_RT(1), 8); mbar_init(bar + FSB_ACC2, 1);
         mbar_init(bar + FSB_ANTI, 1);
@@ -157,8 +159,8 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_stack_kernel(const __gr
         if (lane == 0) {
             uint32_t nfill = 0;
             auto acquire = [&]() -> uint32_t {               // next ring slot, armed for 32 KB
-                const uint32_t slot = nfill & 3u;
-                if (nfill >= 4) mbar_wait(bar + FSB_EMPTY(slot), ((nfill >> 2) - 1u) & 1u);
+                const uint32_t slot = nfill % nslot;
+                if (nfill >= nslot) mbar_wait(bar + FSB_EMPTY(slot), ((nfill / nslot) - 1u) & 1u);
                 ++nfill;
                 mbar_expect_tx(bar + FSB_FULL(slot), 2 * TILE16);
                 return slot;
@@ -184,6 +186,20 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_stack_kernel(const __gr
                 for (int k = 0; k < 3; k += 2) {
                     if (!(k == 0 ? live0 : live2)) continue;
                     const int t = t0 + (k - 1) * d;
+                    auto load_a = [&](int j) {
+                        const uint32_t slot = acquire();
+                        const uint32_t st = s_ring + slot * FS_SLOT, fb = bar + FSB_FULL(slot);
+                        tma_load_4d(st, &p.tmA_hi, fb, j * 64, t, b, l & 1);
+                        tma_load_4d(st + TILE16, &p.tmA_lo, fb, j * 64, t, b, l & 1);
+                    };
+                    if (polled && nslot == 5) {
+                        // second tap with the 5-slot ring: weight and operand slot of a K-half back to back, so both are
+                        // requested as soon as the first tap's K-half 0 has freed its two slots (round-robin slot order)
+                        load_w1(k, 0); load_a(0);
+                        load_w1(k, 1); load_a(1);
+                        TLD(3 + k);
+                        continue;
+                    }
                     load_w1(k, 0);
                     load_w1(k, 1);
                     if (!polled) {                            // relu(h_l) of the tap rows is in global memory
@@ -193,12 +209,8 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_stack_kernel(const __gr
                         polled = true;
                         TLD(2);
                     }
-                    for (int j = 0; j < 2; ++j) {
-                        const uint32_t slot = acquire();
-                        const uint32_t st = s_ring + slot * FS_SLOT, fb = bar + FSB_FULL(slot);
-                        tma_load_4d(st, &p.tmA_hi, fb, j * 64, t, b, l & 1);
-                        tma_load_4d(st + TILE16, &p.tmA_lo, fb, j * 64, t, b, l & 1);
-                    }
+                    load_a(0);
+                    load_a(1);
                     TLD(3 + k);
                 }
                 for (int j = 0; j < 2; ++j) {                 // 1x1 weights, K-half j: hi rows then lo rows
@@ -224,8 +236,8 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_stack_kernel(const __gr
         if (lane == 0) {
             uint32_t nuse = 0;
             auto take = [&]() -> uint32_t {
-                const uint32_t slot = nuse & 3u;
-                mbar_wait(bar + FSB_FULL(slot), (nuse >> 2) & 1u);
+                const uint32_t slot = nuse % nslot;
+                mbar_wait(bar + FSB_FULL(slot), (nuse / nslot) & 1u);
                 ++nuse;
                 return slot;
             };
@@ -255,12 +267,14 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_stack_kernel(const __gr
                     mma_slice(acc1, s_act + j * 2 * TILE16, s_ring + sw * FS_SLOT, j > 0 ? 1u : 0u);
                     umma_commit(bar + FSB_EMPTY(sw));
                 }
+                bool first = true;
                 for (int k = 0; k < 3; k += 2) {
                     if (!tap_live(t0, k, d, p.T)) continue;
+                    const bool inter = !first && nslot == 5;              // producer fill order: W W A A, or W A W A (see there)
                     uint32_t sw[2];
-                    sw[0] = take();                           // weights of both K-halves arrive first (producer fill order)
-                    sw[1] = take();
+                    if (!inter) { sw[0] = take(); sw[1] = take(); }
                     for (int j = 0; j < 2; ++j) {
+                        if (inter) sw[j] = take();
                         const uint32_t sa = take();
                         tc_fence_after();
                         TLD(11 + k + j);
@@ -268,6 +282,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_stack_kernel(const __gr
                         umma_commit(bar + FSB_EMPTY(sa));
                         umma_commit(bar + FSB_EMPTY(sw[j]));
                     }
+                    first = false;
                 }
                 umma_commit(bar + FSB_ACC1);
                 TLD(15);
