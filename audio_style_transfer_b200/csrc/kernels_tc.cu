@@ -764,17 +764,16 @@ int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b
     a.tmA_hi = s->tm_a_hi; a.tmA_lo = s->tm_a_lo; a.tmW1 = s->tm_w1f; a.tmW2 = s->tm_w2f;
     a.tmF = s->n_fslots > 0 ? s->tm_F : s->tm_a_hi;          // never dereferenced without an f_slot
     a.x = x; a.W0 = W0; a.b0 = b0; a.bd = bd; a.br = br; a.H = H; a.zmask = zmask; a.hmask = hmask;
-    a.a_hi = s->a_hi; a.a_lo = s->a_lo;
+    a.a_hi = s->a_hi; a.a_lo = s->a_lo; a.F = s->F;
     a.flags = s->flags; a.err = tc_stack_err(s);
     a.T = s->T; a.R = s->R; a.NL = s->NL; a.tiles_per_pair = s->T / 128;
     for (int l = 0; l < 32; ++l) a.f_slot[l] = (signed char)((s->n_fslots > 0 && l < s->NL) ? f_slot[l] : -1);
     for (int i = 0; i <= s->NL; ++i) a.export_h[i] = export_h[i];
-    a.nslot = 4;
+    // 5 ring slots: the extract copy is written straight from registers, so its 32 KB staging tile joins the operand ring
+    // (AST_B200_RING4=1: A/B switch back to 4 slots + staged TMA store of the extract copy)
     {
-        bool any_f = false;
-        for (int l = 0; l < 32; ++l) any_f = any_f || a.f_slot[l] >= 0;
-        const char* r5 = getenv("AST_B200_RING4");              // A/B switch: keep 4 slots even when the staging tile is unused
-        if (!any_f && !(r5 && r5[0] == '1')) a.nslot = 5;
+        const char* r4 = getenv("AST_B200_RING4");
+        a.nslot = (r4 && r4[0] == '1') ? 4 : 5;
     }
     cudaMemsetAsync(s->flags, 0, (size_t)(s->R / 128) * sizeof(unsigned), st);
     const int tpp = s->T / 128, ppl = s->n_sm / tpp;         // tiles per pair; pairs per launch (all CTAs co-resident)

@@ -195,6 +195,13 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N, bool a_mn =
            ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
+// 32-byte store (one full sector) -- sm_100 has 256-bit global accesses
+__device__ __forceinline__ void st_global_v8(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, uint32_t e, uint32_t f,
+                                             uint32_t g, uint32_t h) {
+    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                 ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d), "r"(e), "r"(f), "r"(g), "r"(h) : "memory");
+}
+
 // ---- lean epilogue arithmetic ------------------------------------------------------------------------
 // word |= bit  iff  x > 0   (fp32 compare on the integer image: positive and non-zero; 2 SASS instructions)
 __device__ __forceinline__ void or_bit_if_pos(uint32_t& word, float x, uint32_t bit) {

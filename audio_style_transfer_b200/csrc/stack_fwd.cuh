@@ -30,6 +30,7 @@ struct alignas(64) FwdStackArgs {
     float* H;                        // fp32 residual stream [NL+1][R][128]: only exported layers are written
     uint32_t* zmask; uint32_t* hmask;            // [NL][R][4], [NL+1][R][4]
     __nv_bfloat16* a_hi; __nv_bfloat16* a_lo;    // the buffers behind tmA_hi / tmA_lo (published with plain stores)
+    __nv_bfloat16* F;                // the buffer behind tmF: bf16 extract copies [n_style][R][128]
     unsigned* flags;                 // [ntiles], zeroed before the launch; += 1 per epilogue warp per published tile
     unsigned* err;
     int T, R, NL, tiles_per_pair;
@@ -367,7 +368,12 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_stack_kernel(const __gr
 #pragma unroll
                         for (int e = 0; e < 4; ++e) out[e] = make_float4(h[4 * e], h[4 * e + 1], h[4 * e + 2], h[4 * e + 3]);
                     }
-                    if (f >= 0) {
+                    if (f >= 0 && p.nslot == 5) {
+                        // bf16 extract copy straight from registers: 16 columns = 32 bytes = one full sector per thread
+                        st_global_v8(p.F + ((size_t)f * p.R + row) * AST_C + cc * 32 + sb * 16,
+                                     pack_bf16(h[0], h[1]), pack_bf16(h[2], h[3]), pack_bf16(h[4], h[5]), pack_bf16(h[6], h[7]),
+                                     pack_bf16(h[8], h[9]), pack_bf16(h[10], h[11]), pack_bf16(h[12], h[13]), pack_bf16(h[14], h[15]));
+                    } else if (f >= 0) {
 #pragma unroll
                         for (int c = 0; c < 2; ++c)
                             *reinterpret_cast<uint4*>(gen + FS_STG + half * TILE16 + sw128_off(r, (cc & 1) * 4 + sb * 2 + c)) =
@@ -375,7 +381,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_stack_kernel(const __gr
                                            pack_bf16(h[8 * c + 4], h[8 * c + 5]), pack_bf16(h[8 * c + 6], h[8 * c + 7]));
                     }
                 }
-                if (f >= 0) {                          // bf16 extract copy: staged tile -> TMA store, one thread per half
+                if (f >= 0 && p.nslot != 5) {          // 4-slot ring: staged tile -> TMA store, one thread per half
                     fence_proxy_async_smem();
                     named_bar_sync(1 + half, 256);
                     if (storer) {
@@ -385,7 +391,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_stack_kernel(const __gr
                     }
                 }
             }
-            if (f >= 0) named_bar_sync(1 + half, 256);             // STG of this half may be overwritten again (ACT: every
+            if (f >= 0 && p.nslot != 5) named_bar_sync(1 + half, 256);             // STG of this half may be overwritten again (ACT: every
                                                                    // warp only ever touches the region it staged itself)
             if (threadIdx.x == 128) TLD(41);
         };
