@@ -10,7 +10,8 @@
 //     consumed after an acquire poll of at most two per-tile flags;
 //   * head gradients (fp32 dF tile, or the bf16 F / Ssym operands of the fused style gradient) do not depend
 //     on the sweep: they are prefetched into their own 64 KB region one boundary ahead;
-//   * weights and neighbour tiles stream through a 6 x 16 KB ring.
+//   * weights and neighbour tiles stream through an 8 x 16 KB ring: all six weight tiles of a boundary are requested
+//     before the neighbour flags are polled, and all four neighbour tiles right after.
 #pragma once
 
 struct alignas(64) BwdStackArgs {
@@ -28,23 +29,26 @@ struct alignas(64) BwdStackArgs {
     signed char sg_slot[33];         // per boundary l: style slot whose F . Ssym is added there, or -1
 };
 
-#define BS_DZ 0                                   // [K-half] x [128][64] bf16: own dz tile (centre-tap operand)
-#define BS_RT 32768                               // [K-half] x [128][64] bf16: bf16(g'), A operand of the 1x1 GEMM
-#define BS_IO 65536                               // 64 KB: fp32 dF tile (4 column groups) or F (2) + Ssym (2) bf16 tiles
-#define BS_RING 131072                            // 6 slots x 16 KB
-#define BS_NSLOT 6
+// The own dz tile (centre-tap operand, read at the START of a boundary's transposed conv) and bf16(g') (operand of the 1x1
+// GEMM, written after that conv has completed and dead once the 1x1 GEMM is done, i.e. before the next dz tile is staged)
+// are never live together: they share one 32 KB buffer, which leaves room for an 8-slot ring.
+#define BS_DZ 0                                   // [K-half] x [128][64] bf16: own dz tile / bf16(g')
+#define BS_RT BS_DZ
+#define BS_IO 32768                               // 64 KB: fp32 dF tile (4 column groups) or F (2) + Ssym (2) bf16 tiles
+#define BS_RING 98304                             // 8 slots x 16 KB
+#define BS_NSLOT 8
 #define BS_BAR (BS_RING + BS_NSLOT * TILE16)
 #define BS_SMEM (BS_BAR + 1024 + 1024)
 #define BSB_FULL(i) (8u * (i))
-#define BSB_EMPTY(i) (48u + 8u * (i))
-#define BSB_DZ 96u
-#define BSB_ACC1 104u
-#define BSB_RT(j) (112u + 8u * (j))
-#define BSB_ACC2 128u
-#define BSB_IOFULL 136u
-#define BSB_IOFREE 144u
-#define BSB_ANTI 152u
-#define BSB_TMEM 160u
+#define BSB_EMPTY(i) (64u + 8u * (i))
+#define BSB_DZ 128u
+#define BSB_ACC1 136u
+#define BSB_RT(j) (144u + 8u * (j))
+#define BSB_ACC2 160u
+#define BSB_IOFULL 168u
+#define BSB_IOFREE 176u
+#define BSB_ANTI 184u
+#define BSB_TMEM 192u
 
 // timeline (scripts/timeline_stack.py): detailed stamps of boundary g_tl_layer in block 2 of the buffer, one stamp per
 // boundary (publish done) in block 3
@@ -122,7 +126,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_bwd_stack_kernel(const __gr
                         tma_load_2d(s_ring + slot * TILE16, &p.tmW1, bar + BSB_FULL(slot), j * 64, w1row + k * 128);
                     };
                     // Fill order (= the MMA issuer's take order): all weight tiles of this boundary's transposed conv (centre
-                    // tap, then every live side tap: at most 6 slots = the whole ring, none of them waits for a neighbour), then
+                    // tap, then every live side tap: at most 6 of the 8 slots, none of them waits for a neighbour), then
                     // ONE poll of all the neighbour flags, then the operand tiles of the side taps.
                     TLB(1);
                     load_w1(1, 0);                            // centre tap: the dz tile is resident
