@@ -62,6 +62,11 @@ struct ast_ctx {
     float** d_dFptr;
     const float** d_Hcptr;
     float lambd;
+    // gamma term (stft_reg.cu): frames [reg_f_lo, reg_f_lo + reg_nf) of the clip are evaluated here, the ones
+    // in [reg_own_f_lo, reg_own_f_hi) count towards this context's partial sum
+    float gamma;
+    int reg_f_lo, reg_nf, reg_own_f_lo, reg_own_f_hi, reg_f_total;
+    float2* reg_tw; signed char* reg_sgn; float* reg_fpart; float* reg_dadx;
     bool have_w, have_t;
     TcState* tc;       // tensor-core path state (AST_PREC_BF16), else NULL
     // host-buffer step (ast_step_host)
@@ -162,6 +167,7 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
     for (auto& g : c->gphase) g = nullptr;
     for (auto& e : c->ev) e = nullptr;
     c->have_w = c->have_t = false; c->launches_per_step = c->launches_fwd = c->launches_bwd = 0; c->lambd = 0.f;
+    c->gamma = 0.f; c->reg_nf = 0; c->reg_tw = nullptr; c->reg_sgn = nullptr; c->reg_fpart = nullptr; c->reg_dadx = nullptr;
 
     // time-sharding window (all zero = unsharded)
     c->total_T = cfg->total_T > 0 ? cfg->total_T : cfg->T;
@@ -232,8 +238,9 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
     DA(c->scratch3R, (size_t)3 * c->R);
     const size_t gsz = (size_t)c->B * c->nmat * c->msize;
     DA(c->gram_part, gsz * c->gram_nchunk);
-    c->n_partials = (int64_t)gsz + c->B;
+    c->n_partials = (int64_t)gsz + 2 * c->B;           // raw Gram | content sse | raw STFT-L1 sum (0 when gamma = 0)
     DA(c->partials, (size_t)c->n_partials);
+    CK(cudaMemset(c->partials, 0, (size_t)c->n_partials * sizeof(float)));
     DA(c->Gn, gsz); DA(c->Ssym, gsz); DA(c->ls_part, (size_t)c->B * c->nmat);
     DA(c->sse_part, (size_t)2 * c->B * c->sse_nblk);   // doubles
     DA(c->Pc, (size_t)c->R * c->n_cont * cfg->cnt_channels);
@@ -302,17 +309,59 @@ extern "C" int ast_set_weights(ast_ctx* c, const float* W0, const float* b0, con
     return AST_OK;
 }
 
+static int setup_regulariser(ast_ctx* c);
 extern "C" int ast_set_targets(ast_ctx* c, const float* Pc, const float* Ps, double lambd, double gamma, void* stream) {
     if (!c || !Pc || !Ps) return fail(AST_EINVAL, "null argument");
-    if (gamma != 0.0) return fail(AST_EUNSUPPORTED, "gamma != 0: the STFT regulariser (methods.py:121-123) is not built yet");
     cudaStream_t s = (cudaStream_t)stream;
     CK(cudaSetDevice(c->cfg.device));
+    if (gamma != 0.0) {
+        int r = setup_regulariser(c);
+        if (r != AST_OK) return r;
+    }
+    c->gamma = (float)gamma;
     CK(cudaMemcpyAsync(c->Pc, Pc, (size_t)c->R * c->n_cont * c->cfg.cnt_channels * sizeof(float), cudaMemcpyDefault, s));
     CK(cudaMemcpyAsync(c->Ps, Ps, (size_t)c->B * c->nmat_used * c->msize * sizeof(float), cudaMemcpyDefault, s));
     CK(cudaStreamSynchronize(s));
     c->lambd = (float)lambd;
     c->have_t = true;
     drop_graphs(c);                                                         // loss weights are baked in the graphs
+    return AST_OK;
+}
+
+// ---- gamma term: which STFT frames this context evaluates (methods.py:122: frame 1024, hop 512, no end padding)
+static int setup_regulariser(ast_ctx* c) {
+    const int64_t Ttot = c->total_T, wb = c->cfg.total_T > 0 ? c->cfg.win_begin : 0;
+    if (Ttot < 1024) return fail(AST_EINVAL, "gamma != 0 needs at least one 1024-sample STFT frame (T = %lld)", (long long)Ttot);
+    const int64_t F = 1 + (Ttot - 1024) / 512;
+    const int64_t ob = wb + c->own_lo, oe = wb + c->own_hi;
+    // frames that touch an owned sample: 512 f <= n < 512 f + 1024 for some n in [ob, oe)
+    int64_t f_lo = ob >= 1023 ? (ob - 1023 + 511) / 512 : 0, f_hi = std::min<int64_t>(F - 1, (oe - 1) / 512);
+    if (f_hi < f_lo) { f_lo = 0; f_hi = -1; }
+    if (f_hi >= f_lo && (512 * f_lo < wb || 512 * f_hi + 1024 > wb + c->T))
+        return fail(AST_EINVAL, "gamma != 0: the window [%lld, %lld) does not hold every STFT frame that touches the owned samples",
+                    (long long)wb, (long long)(wb + c->T));
+    c->reg_f_lo = (int)f_lo; c->reg_nf = (int)(f_hi - f_lo + 1); c->reg_f_total = (int)F;
+    c->reg_own_f_lo = (int)((ob + 511) / 512); c->reg_own_f_hi = (int)std::min<int64_t>(F, (oe + 511) / 512);
+    if (c->reg_tw) return AST_OK;
+    std::vector<float2> tw(1024);
+    for (int j = 0; j < 1024; ++j) {
+        // exact at the quadrant points, so that Im of bins 0 and 512 is exactly 0 as in an FFT
+        const int q = j & 255, quad = j >> 8;
+        const double ang = 2.0 * 3.14159265358979323846 * q / 1024.0;
+        const double cq = cos(ang), sq = q ? sin(ang) : 0.0;
+        double cj, sj;
+        switch (quad) { case 0: cj = cq; sj = sq; break; case 1: cj = -sq; sj = cq; break;
+                        case 2: cj = -cq; sj = -sq; break; default: cj = sq; sj = -cq; }
+        tw[j] = make_float2((float)cj, (float)sj);
+    }
+    int r_;
+    if ((r_ = dalloc(c, &c->reg_tw, 1024)) != AST_OK) return r_;
+    CK(cudaMemcpy(c->reg_tw, tw.data(), sizeof(float2) * 1024, cudaMemcpyHostToDevice));
+    // sized for any window position: at most T/512 + 2 frames touch T samples
+    const size_t nfmax = (size_t)c->T / 512 + 2;
+    if ((r_ = dalloc(c, &c->reg_sgn, (size_t)c->B * nfmax * 513 * 2)) != AST_OK) return r_;
+    if ((r_ = dalloc(c, &c->reg_fpart, (size_t)c->B * nfmax * 4)) != AST_OK) return r_;
+    if ((r_ = dalloc(c, &c->reg_dadx, (size_t)c->R)) != AST_OK) return r_;
     return AST_OK;
 }
 
@@ -358,16 +407,25 @@ static void run_gram(ast_ctx* c, cudaStream_t s) {
     launch_gram_reduce(c->gram_part, c->partials, c->cfg.gatys, c->L, c->B, c->gram_nchunk, s);
 }
 
+// everything between the encoder and the (optional) all-reduce: raw Gram, content squared error, raw STFT-L1 sum
+static void run_partials(ast_ctx* c, const float* d_x, cudaStream_t s) {
+    // (Forking the content SSE onto a second stream next to the Gram kernels was measured: no gain within run-to-run noise.)
+    run_gram(c, s);
+    float* tail = c->partials + (size_t)c->B * c->nmat * c->msize;
+    launch_content_sse(c->d_Hcptr, c->n_cont, c->cfg.cnt_channels, c->Pc, c->T, c->B, c->own_lo, c->own_hi,
+                       c->sse_part, c->sse_nblk, tail, s);
+    if (c->gamma != 0.f && c->reg_nf > 0)
+        launch_stft_l1_fwd(d_x, c->reg_tw, c->T, c->B, (int)(c->cfg.total_T > 0 ? c->cfg.win_begin : 0), c->reg_f_lo, c->reg_nf,
+                           c->reg_own_f_lo, c->reg_own_f_hi, c->reg_sgn, c->reg_fpart, c->reg_dadx, tail + c->B, s);
+}
+
 extern "C" int ast_step_forward(ast_ctx* c, const float* d_x, void* stream) {
     if (!c || !d_x) return fail(AST_EINVAL, "null argument");
     if (!c->have_w || !c->have_t) return fail(AST_ESTATE, "ast_set_weights and ast_set_targets must precede a step");
     cudaStream_t s = (cudaStream_t)stream;
     const int before = ast_launch_counter;
     run_encoder(c, d_x, s, false);
-    // (Forking the content SSE onto a second stream next to the Gram kernels was measured: no gain within run-to-run noise.)
-    run_gram(c, s);
-    launch_content_sse(c->d_Hcptr, c->n_cont, c->cfg.cnt_channels, c->Pc, c->T, c->B, c->own_lo, c->own_hi,
-                       c->sse_part, c->sse_nblk, c->partials + (size_t)c->B * c->nmat * c->msize, s);
+    run_partials(c, d_x, s);
     c->launches_fwd = ast_launch_counter - before;
     c->launches_per_step = c->launches_fwd + c->launches_bwd;
     CK(cudaGetLastError());
@@ -390,6 +448,8 @@ static HeadArgs head_args(ast_ctx* c, bool with_targets, float* losses) {
     h.Ssym_bf16 = (with_targets && c->cfg.gatys && c->tc) ? tc_ssym_bf16(c->tc) : nullptr;
     h.ls_part = c->ls_part; h.sse = c->partials + (size_t)c->B * c->nmat * c->msize; h.losses = losses;
     h.nmat = c->nmat; h.nmat_used = with_targets ? c->nmat_used : 0; h.n = c->n_side; h.B = c->B;
+    h.reg_raw = h.sse + c->B; h.gamma = c->gamma;
+    h.reg_scale = c->gamma != 0.f ? (float)(1.0 / ((double)c->reg_f_total * 513.0)) : 0.f;
     h.coef_dGn = (float)((double)c->lambd * 1e3 * 2.0 / Ns);
     h.ls_scale = (float)(1e3 / Ns); h.lc_scale = (float)(10.0 / Nc); h.lambd = c->lambd;
     return h;
@@ -460,6 +520,9 @@ extern "C" int ast_step_backward(ast_ctx* c, float* d_losses, float* d_grad, voi
         cur ^= 1;
     }
     launch_startconv_bwd(c->g, c->W0, c->scratch3R, d_grad, c->T, c->R, s);
+    if (c->gamma != 0.f && c->reg_nf > 0)                 // + gamma * d reg / d x (methods.py:125)
+        launch_stft_l1_grad(c->reg_dadx, c->reg_tw, c->reg_sgn, c->T, c->B, (int)(c->cfg.total_T > 0 ? c->cfg.win_begin : 0),
+                            c->reg_f_lo, c->reg_nf, (float)((double)c->gamma / ((double)c->reg_f_total * 513.0)), d_grad, s);
     c->launches_bwd = ast_launch_counter - bwd_before;
     c->launches_per_step = c->launches_fwd + c->launches_bwd;
     CK(cudaGetLastError());
@@ -569,9 +632,7 @@ extern "C" int ast_step_timed(ast_ctx* c, const float* d_x, float* d_losses, flo
         int r = capture_graph(c, &c->gphase[0], [&](cudaStream_t cs) { run_encoder(c, c->d_x, cs, false); return AST_OK; });
         if (r != AST_OK) return r;
         r = capture_graph(c, &c->gphase[1], [&](cudaStream_t cs) {
-            run_gram(c, cs);
-            launch_content_sse(c->d_Hcptr, c->n_cont, c->cfg.cnt_channels, c->Pc, c->T, c->B, c->own_lo, c->own_hi,
-                               c->sse_part, c->sse_nblk, c->partials + (size_t)c->B * c->nmat * c->msize, cs);
+            run_partials(c, c->d_x, cs);
             return AST_OK;
         });
         if (r != AST_OK) return r;

@@ -72,6 +72,9 @@ struct HeadArgs {
     float ls_scale;       // 1e3 / N_s
     float lc_scale;       // 10 / N_c
     float lambd;
+    const float* reg_raw; // [B] raw STFT-L1 sum (stft_reg.cu; all-reduced when sharded); read only when gamma != 0
+    float reg_scale;      // 1 / (frames * 513)
+    float gamma;
 };
 void launch_heads(const HeadArgs& a, cudaStream_t s);
 
@@ -97,3 +100,11 @@ static inline cudaError_t launch_pdl(Kern kernel, dim3 grid, dim3 block, size_t 
     cfg.attrs = at; cfg.numAttrs = 1;
     return cudaLaunchKernelEx(&cfg, kernel, args);
 }
+
+// ---- gamma term (stft_reg.cu): reg = mean(abs(Re) + abs(Im)) of STFT(inv_mu_law(x)), methods.py:121-123 -------
+// forward: frames [f_lo, f_lo + nf) -> sign(Re), sign(Im) per bin (int8), d a / d x per sample, and
+// raw[b] = sum over the frames in [own_f_lo, own_f_hi).  grad: grad += coef * d(raw sum)/dx over the evaluated frames.
+void launch_stft_l1_fwd(const float* x, const float2* tw, int T, int B, int win_begin, int f_lo, int nf,
+                        int own_f_lo, int own_f_hi, signed char* sgn, float* fpart, float* dadx, float* raw, cudaStream_t s);
+void launch_stft_l1_grad(const float* dadx, const float2* tw, const signed char* sgn, int T, int B, int win_begin,
+                         int f_lo, int nf, float coef, float* grad, cudaStream_t s);

@@ -639,10 +639,12 @@ __global__ void losses_final_kernel(const HeadArgs a) {
     if (threadIdx.x != 0) return;
     const double Ls = (double)a.ls_scale * s;
     const double Lc = (double)a.lc_scale * (double)a.sse[b];
-    a.losses[b * 4 + 0] = (float)(Lc + (double)a.lambd * Ls);
+    // methods.py:125.  The reference also evaluates the regulariser when gamma = 0 (logging only); here it is 0 then.
+    const double reg = a.gamma != 0.f ? (double)a.reg_scale * (double)a.reg_raw[b] : 0.0;
+    a.losses[b * 4 + 0] = (float)(Lc + (double)a.lambd * Ls + (double)a.gamma * reg);
     a.losses[b * 4 + 1] = (float)Lc;
     a.losses[b * 4 + 2] = (float)Ls;
-    a.losses[b * 4 + 3] = 0.f;
+    a.losses[b * 4 + 3] = (float)reg;
 }
 void launch_heads(const HeadArgs& a, cudaStream_t s) {
     dim3 grid(a.nmat, a.B);

@@ -25,15 +25,19 @@ def receptive_field(n_layers: int) -> int:
     return 1 + sum(1 << (l % 10) for l in range(n_layers))
 
 
-def plan_windows(T: int, P: int, n_layers: int) -> List[Tuple[int, int, int, int]]:
+STFT_HALO = 1024    # gamma != 0: every 1024-sample STFT frame (methods.py:122) touching an owned sample must lie in the window
+
+
+def plan_windows(T: int, P: int, n_layers: int, min_halo: int = 0) -> List[Tuple[int, int, int, int]]:
     """[(win_begin, win_end, own_begin, own_end)] per rank; all multiples of 128, windows clipped to
-    [0, T).  Owned ranges tile [0, T) exactly."""
+    [0, T).  Owned ranges tile [0, T) exactly.  min_halo widens the overlap beyond the encoder's 2R
+    (STFT_HALO when the regulariser is on)."""
     if T % ALIGN:
         raise ValueError(f"T={T} must be a multiple of {ALIGN}")
     blocks = T // ALIGN
     if P > blocks:
         raise ValueError(f"cannot split {blocks} blocks of {ALIGN} samples over {P} ranks")
-    halo = -(-2 * receptive_field(n_layers) // ALIGN) * ALIGN
+    halo = -(-max(2 * receptive_field(n_layers), min_halo) // ALIGN) * ALIGN
     plan = []
     for r in range(P):
         ob = (blocks * r // P) * ALIGN
@@ -53,9 +57,10 @@ class TimeShardedStep:
     StyleStep on the GPU; tests inject a CPU evaluator to check this logic under gloo) exposing
     forward_partial(x) / partials() / backward() -> (losses, grad_window)."""
 
-    def __init__(self, T: int, n_layers: int, rank: int, world: int, make_ctx: Callable, all_reduce: Callable):
+    def __init__(self, T: int, n_layers: int, rank: int, world: int, make_ctx: Callable, all_reduce: Callable,
+                 gamma: float = 0.0):
         self.T, self.rank, self.world = T, rank, world
-        self.plan = plan_windows(T, world, n_layers)
+        self.plan = plan_windows(T, world, n_layers, STFT_HALO if gamma != 0.0 else 0)
         self.wb, self.we, self.ob, self.oe = self.plan[rank]
         self.ctx = make_ctx(self.we - self.wb, (T, self.wb, self.ob, self.oe))
         self.all_reduce = all_reduce

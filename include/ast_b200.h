@@ -38,7 +38,7 @@ extern "C" {
 #define AST_OK            0
 #define AST_EINVAL       -1   /* bad argument / unsupported shape                       */
 #define AST_ECUDA        -2   /* CUDA runtime/driver error, or no sm_100 device          */
-#define AST_EUNSUPPORTED -3   /* valid in the reference but outside this path (gamma!=0) */
+#define AST_EUNSUPPORTED -3   /* valid in the reference but outside this path (reserved)   */
 #define AST_ESTATE       -4   /* call order violated (weights/targets not set)          */
 
 #define AST_PREC_FP32     0   /* CUDA-core fp32 everywhere: the <=1e-4 tier                           */
@@ -90,7 +90,9 @@ int  ast_set_weights(ast_ctx* ctx, const float* p_W0, const float* p_b0,
                      const float* p_Wr, const float* p_br, void* stream);
 
 /* define_loss (methods.py:113-125): targets and loss weights baked for the following steps.
- * gamma != 0 -> AST_EUNSUPPORTED (STFT regulariser). */
+ * gamma != 0 turns on the STFT regulariser (methods.py:121-123; needs total_T >= 1024, and when time-sharded a
+ * window that holds every 1024-sample frame touching an owned sample -> else AST_EINVAL).  With gamma == 0 it is
+ * not evaluated and losses[3] is 0. */
 int  ast_set_targets(ast_ctx* ctx, const float* p_Pc, const float* p_Ps,
                      double lambd, double gamma, void* stream);
 
@@ -98,7 +100,7 @@ int  ast_set_targets(ast_ctx* ctx, const float* p_Pc, const float* p_Ps,
 int  ast_embeds(ast_ctx* ctx, const float* d_x, float* d_Ec, float* d_Gn, void* stream);
 
 /* One function evaluation of the L-BFGS-B loop (methods.py:133-137,167):
- * d_losses [B,4] = {total, content, style, regulariser(=0)}, d_grad [B,T] = d total / d x.
+ * d_losses [B,4] = {total, content, style, regulariser}, d_grad [B,T] = d total / d x.
  * Asynchronous on `stream`, no host sync, CUDA-graph capturable. */
 int  ast_step(ast_ctx* ctx, const float* d_x, float* d_losses, float* d_grad, void* stream);
 
@@ -113,7 +115,7 @@ int  ast_step_graph(ast_ctx* ctx, const float* d_x, float* d_losses, float* d_gr
 int  ast_step_host(ast_ctx* ctx, const double* h_x, double* h_losses, double* h_grad);
 
 /* Two-phase step for time-sharded clips.  Phase 1 runs the forward and leaves the raw (un-normalised)
- * Gram partials and content squared-error partials of the owned rows in one contiguous fp32 device
+ * Gram partials, content squared-error partials and (gamma != 0) the raw STFT-L1 sum of the owned frames in one contiguous fp32 device
  * buffer (ast_partials) that the caller all-reduces (sum) across ranks; phase 2 normalises, forms
  * the losses and runs the backward.  ast_step == forward + backward with no reduction between. */
 int  ast_step_forward(ast_ctx* ctx, const float* d_x, void* stream);

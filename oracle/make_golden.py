@@ -18,8 +18,21 @@ from oracle import cases  # noqa: E402
 OUT = Path(__file__).resolve().parent.parent / "tests" / "golden"
 
 
+def regulariser_golden():
+    """gamma term alone (oracle/stft_reg.py) on the BASELINE-size step input."""
+    from oracle import stft_reg
+    x = cases.build_inputs("t16384_cfg0")["x"]
+    reg, g, raw = stft_reg.stft_l1(x)
+    np.savez_compressed(OUT / "reg_t16384.npz", reg=np.float64(reg), raw=np.float64(raw), g=g[::16].astype(np.float64),
+                        g_norm=np.float64(np.linalg.norm(g)), x_sum=np.float64(x.sum()))
+    print(f"reg_t16384: reg={reg:.12g} |g|={np.linalg.norm(g):.6g}")
+
+
 def main(names):
     OUT.mkdir(parents=True, exist_ok=True)
+    if "reg_t16384" in names:
+        regulariser_golden()
+        names = [n for n in names if n != "reg_t16384"]
     for name in names:
         t0 = time.time()
         case = cases.build_inputs(name)
@@ -31,4 +44,4 @@ def main(names):
 
 
 if __name__ == "__main__":
-    main(sys.argv[1:] or list(cases.CASES))
+    main(sys.argv[1:] or list(cases.CASES) + ["reg_t16384"])

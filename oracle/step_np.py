@@ -124,10 +124,9 @@ def step(x, w, Pc, Ps, cont_ids, style_ids, gatys, lambd, gamma=0.0,
 
     x [T] (mu-law units); Pc [T, n_c*cnt_ch]; Ps [nb, L, L] (ours) or [L, C, C] (gatys).
     Returns (losses, dx) with losses = (total, content, style, regulariser).
-    gamma must be 0 here: the STFT regulariser (methods.py:121-123) is SURVEY.md 8(f) rank 2.
+    gamma != 0 adds the STFT regulariser (methods.py:121-123, oracle/stft_reg.py); with gamma == 0 the
+    regulariser slot reports 0 (the reference evaluates it for logging only, methods.py:167).
     Backward formulas: SURVEY.md 8(a)."""
-    if gamma != 0.0:
-        raise NotImplementedError("gamma != 0 (STFT regulariser) is a 'next' row, SURVEY.md 8(f)")
     dt = x.dtype
     cont_ids, style_ids = list(cont_ids), list(style_ids)
     if n_layers is None:
@@ -186,7 +185,13 @@ def step(x, w, Pc, Ps, cont_ids, style_ids, gatys, lambd, gamma=0.0,
         g = g + da * (H[l] > 0)
     dxs = conv3_T(g, w.W0.astype(dt), 1)[:, 0]
     dx = dxs / dt.type(128.0)
-    losses = (loss, Lc, Ls, 0.0)
+    reg = 0.0
+    if gamma != 0.0:                                                 # methods.py:121-125
+        from . import stft_reg
+        reg, dreg, _ = stft_reg.stft_l1(x)
+        loss = loss + gamma * reg
+        dx = dx + dt.type(gamma) * dreg.astype(dt)
+    losses = (loss, Lc, Ls, reg)
     if return_aux:
         return losses, dx, dict(H=H, Z=Z, G=G, Gn=Gn, Ec=Ec)
     return losses, dx

@@ -214,8 +214,11 @@ def test_errors_are_loud():
     with pytest.raises(AstError):                                         # AST_ESTATE: no weights/targets
         st.step(np.zeros((1, 1024), np.float32))
     st.set_weights(synth.make_weights(10))
-    with pytest.raises(AstError):                                         # gamma != 0 -> AST_EUNSUPPORTED
-        st.set_targets(np.zeros((1, 1024, 128), np.float32), np.zeros((1, 128, 10, 10), np.float32), 100.0, 0.1)
+    short = StyleStep(896, [9], list(range(10)), precision="fp32")
+    short.set_weights(synth.make_weights(10))
+    with pytest.raises(AstError):                                         # gamma != 0 needs one 1024-sample STFT frame
+        short.set_targets(np.zeros((1, 896, 128), np.float32), np.zeros((1, 128, 10, 10), np.float32), 100.0, 0.1)
+    short.close()
     with pytest.raises(AstError):
         StyleStep(1024, [9], [3, 3], precision="fp32")                    # duplicate style layer
     st.close()
@@ -294,3 +297,77 @@ def test_step_keeps_only_head_extracts_in_stack_mode():
     with pytest.raises(AstError, match="not retained"):
         st.extract(dropped[0])
     st.close()
+
+
+# ---- gamma term: STFT regulariser (methods.py:121-123) ------------------------------------------------
+@pytest.mark.parametrize("prec", PRECS)
+@pytest.mark.parametrize("kind", ["float", "int"])
+def test_regulariser_matches_oracle(kind, prec):
+    """loss[3] = reg, loss[0] += gamma * reg, grad += gamma * d reg / dx.  The regulariser runs on fp32 CUDA cores in
+    both tiers, so its own value and gradient (isolated as step(gamma) - step(0) of the same context) are held to
+    the fp32 tolerance in both; integer x exercises the reference's x == 0 pass-through (utils.py:103)."""
+    from oracle import stft_reg
+    case = cases.build_inputs("t4096_cfg0")
+    Pc, Ps = cases.oracle_targets(case)
+    x = case["x"].copy()
+    if kind == "int":
+        x = np.floor(x)
+        x[::97] = 0.0
+    gamma = 50.0
+    reg, dreg, _ = stft_reg.stft_l1(x)
+    st = make_step(case, prec)
+    st.set_targets(Pc[None], Ps[None], case["lambd"], 0.0)
+    lo0, g0 = (t.cpu().numpy()[0].astype(np.float64) for t in st.step(x[None]))
+    st.set_targets(Pc[None], Ps[None], case["lambd"], gamma)
+    lo1, g1 = (t.cpu().numpy()[0].astype(np.float64) for t in st.step(x[None]))
+    assert lo0[3] == 0.0
+    assert abs(lo1[3] - reg) <= 1e-5 * reg
+    assert abs((lo1[0] - lo0[0]) - gamma * reg) <= 1e-4 * gamma * reg
+    assert np.array_equal(lo1[1:3], lo0[1:3])
+    assert rel(g1 - g0, gamma * dreg) <= 1e-4
+    # and the whole step against the oracle at the tier's tolerance
+    losses, dx = step_np.step(x, case["w"], Pc, Ps, case["cont"], case["style"], case["gatys"], case["lambd"], gamma,
+                              case["nb"], case["cnt"])
+    assert abs(lo1[0] - losses[0]) <= TOL[prec]["loss"] * abs(losses[0])
+    assert rel(g1, dx) <= grad_tol(prec, fp32_floor(dict(case, x=x), Pc, Ps, dx - gamma * dreg))
+    # graph replay carries the regulariser kernels too
+    lo = torch.empty(1, 4, device="cuda"); g = torch.empty(1, case["T"], device="cuda")
+    st.step_graph(torch.tensor(x[None], dtype=torch.float32, device="cuda"), lo, g)
+    torch.cuda.synchronize()
+    assert np.allclose(g.cpu().numpy()[0], g1, rtol=0, atol=1e-6 * np.abs(g1).max())
+    st.close()
+
+
+def test_regulariser_time_sharded_equals_unsharded():
+    """Each window context evaluates the STFT frames that touch its owned samples and counts the ones that START
+    there; summed partials give the same reg, owned gradient slices the same gradient."""
+    from audio_style_transfer_b200.sharding import plan_windows
+    case = cases.build_inputs("t4096_cfg0")
+    case = dict(case, cont=[5], style=[0, 1, 2, 3, 4, 5], NL=6, T=8192)
+    case["w"] = synth.make_weights(6, 0, 0.1)
+    rng = np.random.default_rng(2)
+    x = rng.normal(0, 40, 8192)
+    Pc = rng.standard_normal((8192, 128)); Ps = rng.standard_normal((128, 6, 6)) * 0.1
+    gamma = 50.0
+    full = make_step(case, "fp32")
+    full.set_targets(Pc[None], Ps[None], case["lambd"], gamma)
+    lo_f, g_f = full.step(x[None])
+    plan = plan_windows(8192, 3, case["NL"], min_halo=1024)
+    steps, parts = [], []
+    for (wb, we, ob, oe) in plan:
+        st = make_step(case, "fp32", window=(8192, wb, ob, oe), T=we - wb)
+        st.set_targets(Pc[None, wb:we], Ps[None], case["lambd"], gamma)
+        st.forward_partial(x[None, wb:we])
+        steps.append(st); parts.append(st.partials())
+    total = torch.stack([p.clone() for p in parts]).sum(0)
+    g = torch.empty(8192, device="cuda")
+    for st, p, (wb, we, ob, oe) in zip(steps, parts, plan):
+        p.copy_(total)
+        lo, gw = st.backward()
+        g[ob:oe] = gw[0, ob - wb:oe - wb]
+        assert torch.allclose(lo, lo_f, rtol=2e-5)
+    assert float(lo_f[0, 3]) > 0
+    assert rel(g.cpu().numpy(), g_f[0].cpu().numpy()) <= 2e-5
+    for st in steps:
+        st.close()
+    full.close()

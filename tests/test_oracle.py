@@ -118,3 +118,78 @@ def test_resolve_style_ids_and_layers_needed():
     assert synth.layers_needed([30], [0]) == 30
     with pytest.raises(ValueError):
         synth.layers_needed([31], [0])
+
+
+# ---- gamma term: STFT regulariser (methods.py:121-123, oracle/stft_reg.py) --------------------------------
+def _reg_inputs(kind, T=4096, seed=3):
+    rng = np.random.default_rng(seed)
+    x = rng.normal(0, 40, T)
+    if kind == "int":              # the first evaluation of a run sees integer mu-law codes, zeros included
+        x = np.floor(x)
+    x[5] = 0.0
+    x[7] = -0.5                    # (x + 0.5) = 0: the reference's sign() is 0 there
+    return x
+
+
+@pytest.mark.parametrize("kind", ["float", "int"])
+def test_regulariser_gradient_matches_torch_autograd_of_literal_graph(kind):
+    from oracle import stft_reg
+    x = _reg_inputs(kind)
+    reg, g, raw = stft_reg.stft_l1(x)
+    reg2, g2 = stft_reg.torch_literal(x)
+    assert abs(reg - reg2) <= 1e-13 * abs(reg2)
+    assert np.linalg.norm(g - g2) <= 1e-12 * np.linalg.norm(g2)
+    assert stft_reg.n_frames(4096) == 7 and stft_reg.n_frames(16384) == 31 and stft_reg.n_frames(1023) == 0
+
+
+def test_regulariser_finite_differences_and_frame_subsets():
+    from oracle import stft_reg
+    x = _reg_inputs("float")
+    reg, g, _ = stft_reg.stft_l1(x)
+    rng = np.random.default_rng(4)
+    for _ in range(3):
+        v = rng.standard_normal(x.shape[0])
+        eps = 1e-6
+        fd = (stft_reg.stft_l1(x + eps * v)[0] - stft_reg.stft_l1(x - eps * v)[0]) / (2 * eps)
+        assert abs(fd - g @ v) <= 2e-4 * max(abs(fd), 1e-6), (fd, g @ v)     # |Re|, |Im| kinks: piecewise smooth only
+    F = stft_reg.n_frames(x.shape[0])
+    a = stft_reg.stft_l1(x, frames=range(0, 3), total_frames=F)
+    b = stft_reg.stft_l1(x, frames=range(3, F), total_frames=F)
+    assert abs(a[0] + b[0] - reg) <= 1e-14 and np.allclose(a[1] + b[1], g, rtol=0, atol=1e-18)
+
+
+def test_reference_abs_and_inv_mu_law_definitions():
+    from oracle import stft_reg
+    from audio_style_transfer_b200.mu_law import inv_mu_law_numpy
+    v = np.array([-2.0, -1e-13, 0.0, 5e-13, 1e-12, 3.0])
+    assert np.allclose(stft_reg.ref_abs(v), [2.0 + 1e-12, 1e-13 + 1e-12, 1e-12, 1e-12, 1e-12, 3.0], rtol=1e-15)
+    assert list(stft_reg.ref_abs_grad(v)) == [-1.0, -1.0, 0.0, 0.0, 1.0, 1.0]
+    x = np.arange(-128, 128).astype(np.float64)
+    a, d = stft_reg.inv_mu_law(x)
+    assert np.allclose(a, inv_mu_law_numpy(x), rtol=1e-5, atol=1e-12)         # utils.py:85-90, the fp32 numpy twin
+    assert a[128] == 0.0 and d[128] == 1.0                                     # x == 0 passes x through
+    assert np.all(d > 0)
+
+
+def test_step_with_gamma_adds_the_regulariser():
+    from oracle import stft_reg
+    case = cases.build_inputs("t1024_ours_s0")
+    Pc, Ps = cases.oracle_targets(case)
+    l0, dx0 = cases.oracle_step(case, Pc, Ps)
+    lg, dxg = step_np.step(case["x"], case["w"], Pc, Ps, case["cont"], case["style"], case["gatys"], case["lambd"], 2.5,
+                           case["nb"], case["cnt"])
+    reg, g, _ = stft_reg.stft_l1(case["x"])
+    assert l0[3] == 0.0 and abs(lg[3] - reg) == 0.0
+    assert abs(lg[0] - (l0[0] + 2.5 * reg)) <= 1e-12 * abs(lg[0])
+    assert np.allclose(dxg - dx0, 2.5 * g, rtol=0, atol=1e-15)
+
+
+def test_regulariser_golden(golden_dir):
+    from oracle import stft_reg
+    gold = np.load(golden_dir / "reg_t16384.npz")
+    x = cases.build_inputs("t16384_cfg0")["x"]
+    assert float(x.sum()) == float(gold["x_sum"])
+    reg, g, raw = stft_reg.stft_l1(x)
+    assert abs(reg - float(gold["reg"])) <= 1e-12 * abs(reg)
+    assert np.allclose(g[::16], gold["g"], rtol=1e-10, atol=1e-18)
+    assert abs(np.linalg.norm(g) - float(gold["g_norm"])) <= 1e-10 * float(gold["g_norm"])

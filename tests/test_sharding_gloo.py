@@ -34,6 +34,23 @@ def test_plan_windows_tile_the_clip():
         sharding.plan_windows(1000, 2, 10)
 
 
+def test_plan_windows_hold_the_stft_frames_of_the_owned_samples():
+    """gamma != 0 (methods.py:121-123): a rank evaluates every 1024-sample / hop-512 STFT frame that touches one of
+    its owned samples, so all of them must lie inside its window; frames that START in the owned range are each
+    counted by exactly one rank."""
+    for T, P, NL in [(8192, 3, 6), (65536, 8, 30), (16384, 4, 2), (16384 + 384, 4, 2)]:
+        plan = sharding.plan_windows(T, P, NL, min_halo=sharding.STFT_HALO)
+        F = 1 + (T - 1024) // 512
+        counted = []
+        for wb, we, ob, oe in plan:
+            touching = [f for f in range(F) if 512 * f < oe and 512 * f + 1024 > ob]
+            assert all(512 * f >= wb and 512 * f + 1024 <= we for f in touching), (T, P, NL, wb, we)
+            counted += [f for f in range(F) if ob <= 512 * f < oe]
+        assert sorted(counted) == list(range(F))
+    short = sharding.plan_windows(8192, 3, 6)            # without the regulariser the halo is the encoder's 2R only
+    assert short[1][2] - short[1][0] < 1024
+
+
 def test_pairs_for_rank_cover_every_pair_once():
     got = sorted(p for r in range(8) for p in sharding.pairs_for_rank(64, r, 8))
     assert got == list(range(64))
