@@ -39,6 +39,8 @@ struct LayerArgsF32 {
 void launch_startconv_fwd(const float* x, const float* W0, const float* b0, float* H0, uint32_t* hmask0,
                           int T, int R, cudaStream_t s);
 void launch_startconv_bwd(const float* g, const float* W0, float* scratch3R, float* dx, int T, int R, cudaStream_t s);
+// second half only: the dots p[3][R] are already in scratch3R (written by the whole-stack backward kernel)
+void launch_startconv_bwd_combine(const float* scratch3R, float* dx, int T, int R, cudaStream_t s);
 void launch_layer_f32(const LayerArgsF32& a, bool bwd, cudaStream_t s);
 int  setup_f32_kernels();
 
@@ -53,6 +55,7 @@ void launch_gram_gatys(const float* const* d_F, int L, int T, int B, int own_lo,
 void launch_gram_reduce(const float* part, float* G, int gatys, int L, int B, int nchunk, cudaStream_t s);
 
 // content squared error over owned rows -> sse[b] (double accumulate, fp32 out)
+// sse == NULL: partials only (the heads kernel sums them)
 void launch_content_sse(const float* const* d_Hc, int n_cont, int cnt_ch, const float* Pc,
                         int T, int B, int own_lo, int own_hi, float* part, int nblk, float* sse, cudaStream_t s);
 
@@ -72,6 +75,12 @@ struct HeadArgs {
     float ls_scale;       // 1e3 / N_s
     float lc_scale;       // 10 / N_c
     float lambd;
+    // single-GPU step only (all NULL in the two-phase, all-reducible path):
+    const float* gram_part;  // Gatys split-K partials [B][nmat][nchunk][n*n]: summed here instead of by gram_reduce_kernel
+    int nchunk;
+    const double* sse_part;  // [B][sse_nblk] content squared-error partials: summed here instead of by content_sse_final
+    int sse_nblk;
+    unsigned* done;          // [B] arrival counters (zero between launches): the last CTA of a pair writes the losses
     const float* reg_raw; // [B] raw STFT-L1 sum (stft_reg.cu; all-reduced when sharded); read only when gamma != 0
     float reg_scale;      // 1 / (frames * 513)
     float gamma;

@@ -89,6 +89,10 @@ __global__ void startconv_bwd_combine(const float* __restrict__ p, float* __rest
     if (t > 0) v += p[2 * (size_t)R + row - 1];
     dx[row] = v * (1.0f / 128.0f);
 }
+void launch_startconv_bwd_combine(const float* scratch3R, float* dx, int T, int R, cudaStream_t s) {
+    startconv_bwd_combine<<<(R + 255) / 256, 256, 0, s>>>(scratch3R, dx, T, R);
+    ast_launch_counter += 1;
+}
 void launch_startconv_bwd(const float* g, const float* W0, float* scratch3R, float* dx, int T, int R, cudaStream_t s) {
     int blocks = (R + 7) / 8;
     if (blocks > 148 * 8) blocks = 148 * 8;
@@ -272,11 +276,13 @@ __global__ void __launch_bounds__(256) layer_f32_kernel(const LayerArgsF32 a) {
     }
 }
 
+int setup_heads_kernel();
 int setup_f32_kernels() {
     cudaError_t e = cudaFuncSetAttribute(layer_f32_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, LF_SMEM);
     if (e != cudaSuccess) return (int)e;
     e = cudaFuncSetAttribute(layer_f32_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, LF_SMEM);
-    return (int)e;
+    if (e != cudaSuccess) return (int)e;
+    return setup_heads_kernel();
 }
 void launch_layer_f32(const LayerArgsF32& a, bool bwd, cudaStream_t s) {
     const int blocks = a.R / LF_BM;
@@ -544,6 +550,7 @@ void launch_content_sse(const float* const* d_Hc, int n_cont, int cnt_ch, const 
     dim3 grid(nblk, B);
     content_sse_kernel<<<grid, 256, 0, s>>>(d_Hc, n_cont, cnt_ch, Pc, T, own_lo, own_hi, reinterpret_cast<double*>(part));
     ast_launch_counter += 1;
+    if (!sse) return;
     content_sse_final<<<B, 32, 0, s>>>(reinterpret_cast<const double*>(part), nblk, sse);
     ast_launch_counter += 1;
 }
@@ -563,8 +570,22 @@ __device__ __forceinline__ double block_sum_d(double v, double* red) {
     for (int i = 0; i < (int)(blockDim.x >> 5); ++i) t += red[i];
     return t;
 }
+// sl = sum of the per-matrix squared differences, sc = content squared error
+__device__ __forceinline__ void write_losses(const HeadArgs& a, int b, double sl, double sc) {
+    const double Ls = (double)a.ls_scale * sl;
+    const double Lc = (double)a.lc_scale * sc;
+    // methods.py:125.  The reference also evaluates the regulariser when gamma = 0 (logging only); here it is 0 then.
+    const double reg = a.gamma != 0.f ? (double)a.reg_scale * (double)a.reg_raw[b] : 0.0;
+    a.losses[b * 4 + 0] = (float)(Lc + (double)a.lambd * Ls + (double)a.gamma * reg);
+    a.losses[b * 4 + 1] = (float)Lc;
+    a.losses[b * 4 + 2] = (float)Ls;
+    a.losses[b * 4 + 3] = (float)reg;
+}
 __global__ void __launch_bounds__(1024) heads_kernel(const HeadArgs a) {
+    extern __shared__ float dgs[];            // [n][n + 1]: dG, read back transposed for Ssym = dG + dG^T
     __shared__ double red[32];
+    __shared__ double red2[2][32];
+    __shared__ int s_last;
     const int mat = blockIdx.x, b = blockIdx.y;
     const int n = a.n, msize = n * n;
     const float* G = a.G + ((size_t)b * a.nmat + mat) * msize;
@@ -573,12 +594,33 @@ __global__ void __launch_bounds__(1024) heads_kernel(const HeadArgs a) {
     // The kernel is a chain of block reductions, i.e. latency: G and Ps are loaded ONCE into registers (<= 16 elements per
     // thread: msize <= 16 blockDim for both head types), and the two sums of the second pass share one reduction.
     // The style loss keeps the direct sum of (gn - Ps)^2: the algebraic one-pass form cancels when gn is close to Ps.
+    // gram_part != NULL (single-GPU step, Gatys layout [b][l][chunk][n*n]): the split-K partials are summed here, in
+    // gram_reduce_kernel's order, instead of by a kernel of their own.
     float gr[16], pr[16];
     double ss = 0.0;
+    if (a.gram_part) {
+        // chunk-outer so that 16 independent loads are in flight per iteration (a per-element chunk loop serialises 16
+        // round trips); ascending chunk order, fp32 adds of the (few) fp32 chunk sums
+        const float* p = a.gram_part + ((size_t)b * a.nmat + mat) * a.nchunk * msize;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) gr[k] = 0.f;
+        for (int ch = 0; ch < a.nchunk; ++ch, p += msize) {
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                const int e = threadIdx.x + k * blockDim.x;
+                if (e < msize) gr[k] += p[e];
+            }
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            const int e = threadIdx.x + k * blockDim.x;
+            gr[k] = e < msize ? G[e] : 0.f;
+        }
+    }
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
         const int e = threadIdx.x + k * blockDim.x;
-        gr[k] = e < msize ? G[e] : 0.f;
         pr[k] = (used && e < msize) ? Ps[e] : 0.f;
         ss += (double)gr[k] * (double)gr[k];
     }
@@ -594,63 +636,91 @@ __global__ void __launch_bounds__(1024) heads_kernel(const HeadArgs a) {
             dot += (double)a.coef_dGn * d * gn;
         }
     }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (int)(blockDim.x >> 5);
     {
         ls = warp_sum_d(ls); dot = warp_sum_d(dot);
-        __shared__ double red2[2][32];
-        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (int)(blockDim.x >> 5);
         if (lane == 0) { red2[0][warp] = ls; red2[1][warp] = dot; }
         __syncthreads();
         ls = 0.0; dot = 0.0;
         for (int i = 0; i < nw; ++i) { ls += red2[0][i]; dot += red2[1][i]; }      // same order in every thread
     }
-    if (threadIdx.x == 0) a.ls_part[(size_t)b * a.nmat + mat] = (float)ls;
+    // ---- losses by the last CTA of this pair to get here (fixed-order sums: the value does not depend on which) ----
+    if (a.done) {
+        if (threadIdx.x == 0) {
+            a.ls_part[(size_t)b * a.nmat + mat] = (float)ls;
+            __threadfence();
+            const unsigned prev = atomicAdd(a.done + b, 1u);
+            s_last = (prev == (unsigned)a.nmat - 1u);
+        }
+        __syncthreads();
+        if (s_last) {                                           // block-uniform
+            __threadfence();
+            double sl = 0.0, sc = 0.0;
+            for (int m = threadIdx.x; m < a.nmat_used; m += blockDim.x) sl += (double)__ldcg(a.ls_part + (size_t)b * a.nmat + m);
+            if (a.sse_part)
+                for (int i = threadIdx.x; i < a.sse_nblk; i += blockDim.x) sc += __ldcg(a.sse_part + (size_t)b * a.sse_nblk + i);
+            sl = block_sum_d(sl, red);
+            sc = a.sse_part ? block_sum_d(sc, red) : (double)a.sse[b];
+            if (threadIdx.x == 0) {
+                write_losses(a, b, sl, sc);
+                a.done[b] = 0u;                                 // ready for the next launch (stream order)
+            }
+        }
+    } else if (threadIdx.x == 0) {
+        a.ls_part[(size_t)b * a.nmat + mat] = (float)ls;
+    }
     const bool clamped = ss < 1e-12;
     float* Gn = a.Gn ? a.Gn + ((size_t)b * a.nmat + mat) * msize : nullptr;
     float* Ss = a.Ssym ? a.Ssym + ((size_t)b * a.nmat + mat) * msize : nullptr;
     __nv_bfloat16* Sb = a.Ssym_bf16 ? a.Ssym_bf16 + ((size_t)b * a.nmat + mat) * msize : nullptr;
+    const int ld = n + 1;
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
         const int e = threadIdx.x + k * blockDim.x;
         if (e >= msize) break;
         const int i = e / n, j = e - i * n;
-        const int et = j * n + i;
-        const double gn = (double)gr[k] * inv, gnt = (double)G[et] * inv;
+        const double gn = (double)gr[k] * inv;
         if (Gn) Gn[e] = (float)gn;
         if (Ss) {
-            double v = 0.0;
+            double dg = 0.0;
             if (used) {
                 const double dgn = (double)a.coef_dGn * (gn - (double)pr[k]);
-                const double dgnt = (double)a.coef_dGn * (gnt - (double)Ps[et]);
-                const double dg = clamped ? dgn * inv : (dgn - gn * dot) * inv;
-                const double dgt = clamped ? dgnt * inv : (dgnt - gnt * dot) * inv;
-                v = dg + dgt;
+                dg = clamped ? dgn * inv : (dgn - gn * dot) * inv;
             }
-            Ss[e] = (float)v;
-            if (Sb) Sb[e] = __float2bfloat16_rn((float)v);
+            dgs[i * ld + j] = (float)dg;
         }
     }
+    if (!Ss) return;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        const int e = threadIdx.x + k * blockDim.x;
+        if (e >= msize) break;
+        const int i = e / n, j = e - i * n;
+        const float v = dgs[i * ld + j] + dgs[j * ld + i];
+        Ss[e] = v;
+        if (Sb) Sb[e] = __float2bfloat16_rn(v);
+    }
 }
-// losses[b] = {Lc + lambd Ls, Lc, Ls, 0}  (methods.py:116-125, gamma = 0)
+// losses[b] = {Lc + lambd Ls + gamma reg, Lc, Ls, reg}  (methods.py:116-125)
 __global__ void losses_final_kernel(const HeadArgs a) {
     const int b = blockIdx.x;
     double s = 0.0;                             // one warp, fixed order
     for (int m = threadIdx.x; m < a.nmat_used; m += 32) s += (double)a.ls_part[(size_t)b * a.nmat + m];
     s = warp_sum_d(s);
     if (threadIdx.x != 0) return;
-    const double Ls = (double)a.ls_scale * s;
-    const double Lc = (double)a.lc_scale * (double)a.sse[b];
-    // methods.py:125.  The reference also evaluates the regulariser when gamma = 0 (logging only); here it is 0 then.
-    const double reg = a.gamma != 0.f ? (double)a.reg_scale * (double)a.reg_raw[b] : 0.0;
-    a.losses[b * 4 + 0] = (float)(Lc + (double)a.lambd * Ls + (double)a.gamma * reg);
-    a.losses[b * 4 + 1] = (float)Lc;
-    a.losses[b * 4 + 2] = (float)Ls;
-    a.losses[b * 4 + 3] = (float)reg;
+    write_losses(a, b, s, (double)a.sse[b]);
+}
+int setup_heads_kernel() {
+    return (int)cudaFuncSetAttribute(heads_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     AST_C * (AST_C + 1) * (int)sizeof(float));
 }
 void launch_heads(const HeadArgs& a, cudaStream_t s) {
     dim3 grid(a.nmat, a.B);
-    heads_kernel<<<grid, a.n * a.n >= 4096 ? 1024 : 256, 0, s>>>(a);
+    const size_t smem = a.Ssym ? (size_t)a.n * (a.n + 1) * sizeof(float) : 0;
+    heads_kernel<<<grid, a.n * a.n >= 4096 ? 1024 : 256, smem, s>>>(a);
     ast_launch_counter += 1;
-    if (a.losses) { losses_final_kernel<<<a.B, 32, 0, s>>>(a); ast_launch_counter += 1; }
+    if (a.losses && !a.done) { losses_final_kernel<<<a.B, 32, 0, s>>>(a); ast_launch_counter += 1; }
 }
 
 // =============================================================================================

@@ -802,12 +802,12 @@ int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b
 }
 
 int tc_backward_stack(TcState* s, const uint32_t* hmask, const uint32_t* zmask, const int* df_idx, const int* sg_slot,
-                      int sg_L, float* g, cudaStream_t st) {
+                      int sg_L, float* g, const float* W0, float* pdots, cudaStream_t st) {
     BwdStackArgs a;
     memset(&a, 0, sizeof(a));
     a.tmDz = s->tm_dz; a.tmW1 = s->tm_w1b; a.tmW2 = s->tm_w2b; a.tmDF = s->tm_dF;
     a.tmF = s->n_fslots > 0 ? s->tm_F : s->tm_dz; a.tmS = s->n_fslots > 0 ? s->tm_ssym : s->tm_w2b;   // unused without slots
-    a.dz = s->dz; a.g = g; a.hmask = hmask; a.zmask = zmask;
+    a.dz = s->dz; a.g = g; a.hmask = hmask; a.zmask = zmask; a.W0 = W0; a.pdots = pdots;
     const size_t nt = (size_t)(s->R / 128);
     a.flags = s->flags + nt; a.err = tc_stack_err(s) + 1;
     a.T = s->T; a.R = s->R; a.NL = s->NL; a.tiles_per_pair = s->T / 128; a.sg_L = sg_L;

@@ -20,7 +20,8 @@ struct alignas(64) BwdStackArgs {
     CUtensorMap tmDF;                // fp32 head gradients [n_head][B][T][128], box {32,128,1,1}
     CUtensorMap tmF, tmS;            // fused style gradient operands: bf16 F [L][B][T][128], bf16 Ssym rows
     __nv_bfloat16* dz;               // the buffer behind tmDz (published with plain stores)
-    float* g;                        // [R][128]: receives the final running gradient (input of the start-conv adjoint)
+    float* g;                        // [R][128]: receives the final running gradient (input of the start-conv adjoint) ...
+    const float* W0; float* pdots;   // ... unless pdots != NULL: then p_k[t] = sum_c W0[k,0,c] g[t,c] goes to pdots[k][R] instead
     const uint32_t* hmask; const uint32_t* zmask;        // [NL+1][R][4], [NL][R][4]
     unsigned* flags; unsigned* err;
     int T, R, NL, tiles_per_pair, sg_L;
@@ -300,7 +301,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_bwd_stack_kernel(const __gr
                     }
                 }
                 tmem_st16(gacc + col, v);
-                if (l == 0) {
+                if (l == 0 && !p.pdots) {
                     float4* out = reinterpret_cast<float4*>(p.g + row * AST_C + cc * 32 + sb * 16);
 #pragma unroll
                     for (int e = 0; e < 4; ++e) out[e] = make_float4(v[4 * e], v[4 * e + 1], v[4 * e + 2], v[4 * e + 3]);
@@ -319,6 +320,33 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_bwd_stack_kernel(const __gr
             }
             tmem_wait_st();
             if (threadIdx.x == 128) TLB(32);
+            if (l == 0 && p.pdots) {
+                // start-conv adjoint dots p_k[t] = sum_c W0[k,0,c] g[t,c], from the final running gradient in TMEM (kept
+                // out of the per-boundary loop above: executed once).  Each thread covers its 32 columns,
+                // the 4 column groups of a row meet in smem (the dz / g' buffer is dead: boundary 0's transposed conv has
+                // completed and there is no 1x1 GEMM below it); fixed order -> reproducible
+                float pk0 = 0.f, pk1 = 0.f, pk2 = 0.f;
+#pragma unroll 1
+                for (int sb = 0; sb < 2; ++sb) {
+                    float v[16];
+                    tmem_ld16_nowait(gacc + lane_off + cc * 32 + sb * 16, v);
+                    tmem_wait_ld();
+                    const float* w = p.W0 + cc * 32 + sb * 16;
+#pragma unroll
+                    for (int e = 0; e < 16; ++e) {
+                        pk0 = fmaf(v[e], __ldg(w + e), pk0);
+                        pk1 = fmaf(v[e], __ldg(w + AST_C + e), pk1);
+                        pk2 = fmaf(v[e], __ldg(w + 2 * AST_C + e), pk2);
+                    }
+                }
+                float* ps = reinterpret_cast<float*>(gen + BS_RT);
+                ps[(0 * 4 + cc) * 128 + r] = pk0; ps[(1 * 4 + cc) * 128 + r] = pk1; ps[(2 * 4 + cc) * 128 + r] = pk2;
+                named_bar_sync(1, 512);
+                if (cc < 3) {
+                    const float* q4 = ps + cc * 4 * 128 + r;
+                    p.pdots[(size_t)cc * p.R + row] = (q4[0] + q4[128]) + (q4[256] + q4[384]);
+                }
+            }
             if (!g2) break;
             // ---- epilogue 2: dz_{l-1} = acc2 * [z>0] -> bf16: own centre-tap operand (smem) + published tile ----
             mbar_wait(bar + BSB_ACC2, acc2_n & 1u);

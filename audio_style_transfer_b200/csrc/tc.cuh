@@ -33,7 +33,7 @@ int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b
 // Whole backward sweep (boundaries NL..0) in one cooperative launch (same availability as tc_forward_stack).
 // df_idx[l] / sg_slot[l] as for tc_layer_bwd, per boundary l; the final running gradient is written to g [R][128].
 int tc_backward_stack(TcState* s, const uint32_t* hmask, const uint32_t* zmask, const int* df_idx, const int* sg_slot,
-                      int sg_L, float* g, cudaStream_t st);
+                      int sg_L, float* g, const float* W0, float* pdots, cudaStream_t st);
 // backward boundary l in NL..0: g += conv^T(dz_l) * hmask + dF[df_idx] (df_idx < 0: none);
 // dz_{l-1} = (g Wr_{l-1}^T) * zmask.  bf16 dz buffers owned by the TcState.  l == NL: no conv (top);
 // l == 0: no 1x1 (bottom).
