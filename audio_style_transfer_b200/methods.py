@@ -128,14 +128,20 @@ class GatysNet(object):
         return graph, 'content', 'style', gatys
 
     def load_model(self, sess=None):
-        """methods.py:79-84.  The NSynth checkpoint (TF tensor bundle) cannot be read without TensorFlow
-        yet; `.npz` weight files with the ast_set_weights layouts are accepted, else
-        a seeded random-init encoder (masked.py:116-117) is used and that is said out loud."""
-        if self.checkpoint_path and str(self.checkpoint_path).endswith('.npz') and os.path.exists(self.checkpoint_path):
-            d = np.load(self.checkpoint_path)
+        """methods.py:79-84.  `checkpoint_path` is what the reference takes: the prefix of a TF V2 checkpoint
+        (`<prefix>.index` + `<prefix>.data-*`, read by tf_checkpoint.py without TensorFlow; the plain variable names,
+        as tf.train.Saver over tf.global_variables() restores them).  `.npz` weight files with the ast_set_weights
+        layouts are accepted too; if neither exists a seeded random-init encoder (masked.py:116-117) is used and that
+        is said out loud."""
+        from . import tf_checkpoint
+        path = str(self.checkpoint_path) if self.checkpoint_path else ''
+        if path and tf_checkpoint.is_bundle(path):
+            w = tf_checkpoint.load_encoder_weights(path, n_layers=self.graph.n_layers)
+        elif path.endswith('.npz') and os.path.exists(path):
+            d = np.load(path)
             w = synth.EncoderWeights(d['W0'], d['b0'], d['Wd'], d['bd'], d['Wr'], d['br'])
         else:
-            print(f'[ast_b200] checkpoint {self.checkpoint_path!r} not readable here: random-init encoder, seed {self.seed}')
+            print(f'[ast_b200] checkpoint {self.checkpoint_path!r} not found: random-init encoder, seed {self.seed}')
             w = synth.make_weights(self.graph.n_layers, seed=self.seed)
         self.graph.set_weights(w)
 
@@ -269,7 +275,7 @@ def build_parser():
     parser.add_argument('--start', nargs='?', type=float, default=1.0)
     parser.add_argument('--gatys', nargs='?', type=bool, default=False, const=True)
     parser.add_argument('--ckpt_path', nargs='?', default='./nsynth/model/wavenet-ckpt/model.ckpt-200000',
-                        help="path to the pretrained model's checkpoint (.npz with W0,b0,Wd,bd,Wr,br; else random init)")
+                        help="path to the pretrained model's checkpoint (TF checkpoint prefix, or .npz with W0,b0,Wd,bd,Wr,br; else random init)")
     parser.add_argument('--dir', help='path to source files', nargs='?', default='./data/src')
     parser.add_argument('--outdir', help='path to output', nargs='?', default='./data/out')
     parser.add_argument('--logdir', help='path to logs', nargs='?', default='./log')
