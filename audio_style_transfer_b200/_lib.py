@@ -15,7 +15,7 @@ from pathlib import Path
 PKG = Path(__file__).resolve().parent
 ROOT = PKG.parent
 SO = PKG / "libast_b200.so"
-SOURCES = ["csrc/api.cu", "csrc/kernels_f32.cu", "csrc/kernels_tc.cu", "csrc/gram_tc.cu", "csrc/stft_reg.cu"]
+SOURCES = ["csrc/api.cu", "csrc/kernels_f32.cu", "csrc/kernels_tc.cu", "csrc/gram_tc.cu", "csrc/stft_reg.cu", "csrc/lbfgs.cu"]
 HEADERS = ["csrc/common.cuh", "csrc/tc.cuh", "csrc/ptx.cuh", "csrc/stack_fwd.cuh", "csrc/stack_fwd2.cuh", "csrc/stack_bwd.cuh", "../include/ast_b200.h"]
 
 AST_PREC_FP32 = 0
@@ -28,6 +28,8 @@ SYMBOLS = [
     "ast_set_weights", "ast_set_targets", "ast_embeds", "ast_step", "ast_step_graph", "ast_step_host",
     "ast_step_forward", "ast_partials", "ast_step_backward", "ast_get_extract",
     "ast_launches_per_step", "ast_step_timed",
+    "ast_opt_create", "ast_opt_destroy", "ast_opt_workspace_bytes", "ast_opt_reset", "ast_opt_buffers", "ast_opt_advance",
+    "ast_opt_status", "ast_opt_result", "ast_opt_epochs", "ast_opt_log", "ast_minimize",
 ]
 
 
@@ -40,6 +42,14 @@ class AstConfig(C.Structure):
         ("precision", C.c_int32),
         ("total_T", C.c_int64), ("win_begin", C.c_int64), ("own_begin", C.c_int64), ("own_end", C.c_int64),
         ("device", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+class AstOptConfig(C.Structure):
+    _fields_ = [
+        ("T", C.c_int32), ("B", C.c_int32), ("m", C.c_int32), ("maxiter", C.c_int32), ("epochs", C.c_int32),
+        ("min_evals", C.c_int32), ("maxls", C.c_int32), ("max_log", C.c_int32), ("keep_epoch_x", C.c_int32),
+        ("device", C.c_int32), ("factr", C.c_double), ("pgtol", C.c_double),
     ]
 
 
@@ -106,6 +116,18 @@ def load() -> C.CDLL:
     lib.ast_get_extract.argtypes = [vp, i32, vp, vp]
     lib.ast_launches_per_step.argtypes = [vp]
     lib.ast_step_timed.argtypes = [vp, vp, vp, vp, vp, vp]
+    lib.ast_opt_create.argtypes = [C.POINTER(AstOptConfig), C.POINTER(vp)]
+    lib.ast_opt_destroy.argtypes = [vp]
+    lib.ast_opt_workspace_bytes.argtypes = [vp]
+    lib.ast_opt_workspace_bytes.restype = i64
+    lib.ast_opt_reset.argtypes = [vp, vp, vp]
+    lib.ast_opt_buffers.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
+    lib.ast_opt_advance.argtypes = [vp, vp]
+    lib.ast_opt_status.argtypes = [vp, vp, vp, vp]
+    lib.ast_opt_result.argtypes = [vp, vp, vp]
+    lib.ast_opt_epochs.argtypes = [vp, vp, vp, vp, vp]
+    lib.ast_opt_log.argtypes = [vp, vp, vp]
+    lib.ast_minimize.argtypes = [vp, vp, i64, i32, C.POINTER(i64)]
     for name in SYMBOLS:
         f = getattr(lib, name)
         if f.restype is C.c_int:      # default restype; the int-returning entry points

@@ -111,6 +111,7 @@ static inline uint32_t* zm(const ast_ctx* c, int l) { return c->zmask + (size_t)
 static inline float* dFb(const ast_ctx* c, int i) { return c->dF + (size_t)i * c->R * AST_C; }
 
 extern "C" const char* ast_last_error(void) { return g_err; }
+int ast_set_error(int code, const char* msg) { return fail(code, "%s", msg); }   // lbfgs.cu
 extern "C" const char* ast_version(void) { return "ast_b200 0.1 sm_100a"; }
 extern "C" int64_t ast_workspace_bytes(const ast_ctx* c) { return c ? c->bytes : 0; }
 extern "C" int ast_launches_per_step(const ast_ctx* c) { return c ? c->launches_per_step : 0; }

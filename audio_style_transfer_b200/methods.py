@@ -97,7 +97,10 @@ class GatysNet(object):
                  cnt_channels=128,
                  gatys=False,
                  style_lyr_ids=None,
-                 precision='bf16', seed=0, device=None):
+                 precision='bf16', seed=0, device=None, optimizer='scipy'):
+        if optimizer not in ('scipy', 'device'):
+            raise ValueError("optimizer must be 'scipy' (the reference's SciPy L-BFGS-B on host buffers) or 'device'")
+        self.optimizer = optimizer
         self.logdir = logdir
         self.savepath = savepath
         self.checkpoint_path = checkpoint_path
@@ -184,6 +187,8 @@ class GatysNet(object):
         fun, last = self.define_loss('loss', phi_s, phi_c, lambd, gamma)
         print('Saving file ... to fol {{{}}}'.format(self.savepath))
         since = time.time()
+        if self.optimizer == 'device':
+            return self._l_bfgs_device(epochs, since, callback)
         i_ = 0
         self.evaluations = 0
         for ep in range(epochs):
@@ -212,6 +217,40 @@ class GatysNet(object):
                 break
         print()
 
+    def _l_bfgs_device(self, epochs, since, callback):
+        """The same loop with the optimiser resident on the device (csrc/lbfgs.cu): every epoch of every evaluation is
+        enqueued without a host round trip; the per-evaluation losses and the per-epoch iterates the reference prints /
+        writes (methods.py:147-157,169-179) are read back once at the end."""
+        from .step import DeviceLBFGS
+        opt = DeviceLBFGS(self.batch_size, B=1, maxiter=100, epochs=epochs, min_evals=50, max_log=min(epochs * 256, 1 << 18),
+                          keep_epoch_x=True, device=self.graph.device)
+        try:
+            opt.reset(self.x)
+            opt.minimize(self.graph)
+            status, _ = opt.status()
+            nfev, end, xs = opt.epochs_info()
+            log = opt.log()[0]
+            self.x = opt.result().astype(np.float64)
+        finally:
+            opt.close()
+        done_epochs = int(status[0, 1])
+        self.evaluations = int(status[0, 4])
+        row = 0
+        for ep in range(done_epochs):
+            n = int(nfev[0, ep])
+            for i in range(n):
+                lo = log[row] if row < len(log) else np.full(4, np.nan, np.float32)
+                if callback is not None:
+                    callback(ep, i, lo)
+                row += 1
+            lo = log[min(row, len(log)) - 1]
+            print('Ep {0:}/{1:}-it {2:}-tlapse {3:.4f}s-loss{4:.4f}-{5:.4f}-{6:.4f}-{7:.4f} ({8:})'.format(
+                ep + 1, epochs, n, time.time() - since, lo[0], lo[1], lo[2], lo[3], DeviceLBFGS.END_REASONS[int(end[0, ep])]))
+            audio = inv_mu_law_numpy(xs[0, ep].astype(np.float64)[None])[0, self.late:-self.late]
+            if self.savepath:
+                os.makedirs(self.savepath, exist_ok=True)
+                write_wav(os.path.join(self.savepath, 'ep-{}.wav'.format(ep)), audio / max(np.max(audio), 1e-12), self.sr)
+
     def run(self, cont_file, source, target, epochs, lambd=0.1, gamma=0.1, audio_channel=0, start=1.0):
         """methods.py:183-216.  File names may also be numpy arrays of audio in [-1, 1)."""
         self.load_model(None)
@@ -233,7 +272,7 @@ class GatysNet(object):
 
 
 def get_dir(dir, args):
-    return gt_s_path(crt_t_fol(dir), **{k: v for k, v in vars(args).items() if k not in ('seed', 'precision', 'synthetic')})
+    return gt_s_path(crt_t_fol(dir), **{k: v for k, v in vars(args).items() if k not in ('seed', 'precision', 'synthetic', 'optimizer')})
 
 
 def get_fpath(fn, args):
@@ -251,7 +290,8 @@ def piece_work(args):
     else:
         content, style = map(lambda name: get_fpath(name, args), [args.cont_fn, args.style_fn])
     test = GatysNet(savepath, args.ckpt_path, logdir, figdir, args.stack, args.batch_size, args.sr, args.cont_lyrs,
-                    args.channels, args.cnt_channels, args.gatys, args.style_lyrs, precision=args.precision, seed=args.seed)
+                    args.channels, args.cnt_channels, args.gatys, args.style_lyrs, precision=args.precision, seed=args.seed,
+                    optimizer=args.optimizer)
     return test.run(content, content, style, epochs=args.epochs, lambd=args.lambd, gamma=args.gamma, start=args.start)
 
 
@@ -283,6 +323,8 @@ def build_parser():
     # additions (not in the reference)
     parser.add_argument('--seed', type=int, default=0, help='seed of the random-init encoder when no checkpoint is readable')
     parser.add_argument('--precision', default='bf16', choices=['bf16', 'fp32'])
+    parser.add_argument('--optimizer', default='scipy', choices=['scipy', 'device'],
+                        help="scipy: SciPy L-BFGS-B on host buffers, as the reference; device: the same algorithm resident on the GPU")
     parser.add_argument('--synthetic', action='store_true', help='ignore the file names, use seeded synthetic audio')
     return parser
 

@@ -219,3 +219,98 @@ class StyleStep:
     @property
     def workspace_bytes(self) -> int:
         return int(self.lib.ast_workspace_bytes(self._h))
+
+
+class DeviceLBFGS:
+    """Owner of one ast_opt: SciPy's L-BFGS-B loop of the reference (methods.py:133-137,164-181) as a state machine in
+    device memory (csrc/lbfgs.cu).  `x`, `losses`, `grad` are zero-copy views of the machine's buffers: evaluate the
+    step at `x` into (`losses`, `grad`), call `advance()`, repeat -- or let `minimize(step)` pump a StyleStep."""
+
+    PHASE_DONE = 2
+    END_REASONS = {0: "none", 1: "maxiter", 2: "pgtol", 3: "ftol", 4: "abnormal line search"}
+
+    def __init__(self, T, B=1, m=10, maxiter=100, epochs=1, min_evals=50, maxls=20, max_log=0, keep_epoch_x=False,
+                 factr=1e7, pgtol=1e-5, device=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("no CUDA device: the device-resident optimiser has no CPU fallback")
+        self.lib = _lib.load()
+        self.device = torch.cuda.current_device() if device is None else int(device)
+        self.dev = torch.device("cuda", self.device)
+        self.T, self.B, self.epochs, self.max_log, self.keep_epoch_x = int(T), int(B), int(epochs), int(max_log), bool(keep_epoch_x)
+        cfg = _lib.AstOptConfig()
+        cfg.T, cfg.B, cfg.m, cfg.maxiter, cfg.epochs, cfg.min_evals = self.T, self.B, int(m), int(maxiter), self.epochs, int(min_evals)
+        cfg.maxls, cfg.max_log, cfg.keep_epoch_x, cfg.device = int(maxls), self.max_log, int(self.keep_epoch_x), self.device
+        cfg.factr, cfg.pgtol = float(factr), float(pgtol)
+        self._h = C.c_void_p()
+        _lib.check(self.lib.ast_opt_create(C.byref(cfg), C.byref(self._h)))
+        px, pl, pg = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        _lib.check(self.lib.ast_opt_buffers(self._h, C.byref(px), C.byref(pl), C.byref(pg)))
+        view = lambda p, n, shape: torch.as_tensor(_DevMem(p.value, n), device=self.dev).view(shape)
+        self.x = view(px, self.B * self.T, (self.B, self.T))
+        self.losses = view(pl, self.B * 4, (self.B, 4))
+        self.grad = view(pg, self.B * self.T, (self.B, self.T))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self.lib.ast_opt_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reset(self, x0):
+        x0 = np.ascontiguousarray(x0, dtype=np.float64)
+        assert x0.size == self.B * self.T
+        with torch.cuda.device(self.dev):
+            _lib.check(self.lib.ast_opt_reset(self._h, _ptr(x0), _stream()))
+            torch.cuda.current_stream().synchronize()       # x0 is pageable host memory
+
+    def advance(self):
+        with torch.cuda.device(self.dev):
+            _lib.check(self.lib.ast_opt_advance(self._h, _stream()))
+
+    def status(self):
+        """(int32 [B,8], float64 [B]): see ast_opt_status in include/ast_b200.h."""
+        st = np.zeros((self.B, 8), np.int32)
+        f = np.zeros(self.B, np.float64)
+        with torch.cuda.device(self.dev):
+            _lib.check(self.lib.ast_opt_status(self._h, _ptr(st), _ptr(f), _stream()))
+        return st, f
+
+    @property
+    def done(self):
+        return bool((self.status()[0][:, 0] == self.PHASE_DONE).all())
+
+    def result(self):
+        out = np.empty((self.B, self.T), np.float64)
+        with torch.cuda.device(self.dev):
+            _lib.check(self.lib.ast_opt_result(self._h, _ptr(out), _stream()))
+        return out
+
+    def epochs_info(self):
+        """(evaluations [B,epochs], end reason [B,epochs], iterate per epoch [B,epochs,T] or None)."""
+        nfev = np.zeros((self.B, self.epochs), np.int32)
+        end = np.zeros((self.B, self.epochs), np.int32)
+        xs = np.zeros((self.B, self.epochs, self.T), np.float32) if self.keep_epoch_x else None
+        with torch.cuda.device(self.dev):
+            _lib.check(self.lib.ast_opt_epochs(self._h, _ptr(nfev), _ptr(end), _ptr(xs), _stream()))
+        return nfev, end, xs
+
+    def log(self):
+        out = np.zeros((self.B, max(self.max_log, 1), 4), np.float32)
+        if self.max_log:
+            with torch.cuda.device(self.dev):
+                _lib.check(self.lib.ast_opt_log(self._h, _ptr(out), _stream()))
+        return out[:, :self.max_log]
+
+    def minimize(self, step: "StyleStep", max_evals=0, chunk=4) -> int:
+        """ast_minimize: [step, advance] graph replays until every pair has stopped.  Returns evaluations enqueued."""
+        assert step.T == self.T and step.B == self.B and step.device == self.device
+        n = C.c_int64()
+        with torch.cuda.device(self.dev):
+            torch.cuda.current_stream().synchronize()
+            _lib.check(self.lib.ast_minimize(step._h, self._h, int(max_evals), int(chunk), C.byref(n)))
+        return int(n.value)

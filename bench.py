@@ -284,6 +284,40 @@ def run_ours(args):
             torch.cuda.synchronize()
             e2e_ms = (time.perf_counter() - t0) * 1e3
             barrier()
+        # ---- the whole L-BFGS-B epoch (methods.py:164-167, maxiter 100): optimiser on the device vs SciPy on the host --
+        optim = None
+        if not sharded and rank == 0:
+            from audio_style_transfer_b200.step import DeviceLBFGS
+            x0 = wl["x"].astype(np.float64)
+            opt = DeviceLBFGS(T, B=B, maxiter=100, epochs=1, min_evals=0, max_log=512, device=local)
+            opt.reset(x0)
+            opt.minimize(st, max_evals=8)                         # graph capture + warm-up
+            opt.reset(x0)
+            t0 = time.perf_counter()
+            enq = opt.minimize(st)
+            dt_dev = time.perf_counter() - t0
+            sd, fk = opt.status()
+            nfev_dev = int(sd[:, 4].max())
+            f_first = float(opt.log()[0, 0, 0])
+            optim = {"device": {"evals_per_s": nfev_dev * B / dt_dev, "evals": nfev_dev, "enqueued": enq, "iterations": int(sd[0, 2]),
+                                "ms_per_eval": dt_dev / nfev_dev * 1e3, "loss_first": f_first, "loss_last": float(fk[0]),
+                                "api": "ast_minimize: [ast_step, ast_opt_advance] graph replays, no host read-back per evaluation"}}
+            opt.close()
+            if B == 1:
+                from scipy.optimize import minimize as sp_minimize
+                cnt, fl = [0], [0.0]
+
+                def fun(xx):
+                    lo, gg = st.step_host(xx)
+                    cnt[0] += 1
+                    fl[0] = float(lo[0, 0])
+                    return fl[0], gg[0]
+                t0 = time.perf_counter()
+                res = sp_minimize(fun, x0[0], jac=True, method="L-BFGS-B", options={"maxiter": 100})
+                dt_sp = time.perf_counter() - t0
+                optim["scipy"] = {"evals_per_s": cnt[0] / dt_sp, "evals": cnt[0], "iterations": int(res.nit),
+                                  "ms_per_eval": dt_sp / cnt[0] * 1e3, "loss_last": float(res.fun),
+                                  "api": "scipy.optimize.minimize(L-BFGS-B) on ast_step_host, as the reference drives its step"}
     tmax = torch.tensor([dev_ms, e2e_ms if not sharded else 0.0], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -352,6 +386,8 @@ def run_ours(args):
                        "h2d_bytes_per_step": B * T * 4, "d2h_bytes_per_step": (B * T + 4 * B) * 4,
                        "ms_per_step": e2e_ms / args.steps,
                        "api": "StyleStep.step_host -> ast_step_host (float64 host in/out, graph replay inside)"}
+    if optim:
+        line["optimizer_epoch"] = optim
     if roof:
         line["roofline"] = roof
     if world == 1 and not args.no_cpu:

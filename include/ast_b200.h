@@ -137,6 +137,57 @@ int  ast_launches_per_step(const ast_ctx* ctx);
 int  ast_step_timed(ast_ctx* ctx, const float* d_x, float* d_losses, float* d_grad, void* stream,
                     float* ms_out);
 
+/* ---- the optimiser around the step, resident on the device ---------------------------------
+ * Reference: `tf.contrib.opt.ScipyOptimizerInterface(loss, method='L-BFGS-B', options={'maxiter': 100})`
+ * (methods.py:133-137), run once per epoch from the variable's current value, stopping after an epoch with fewer than
+ * 50 evaluations (methods.py:164-181).  SciPy's L-BFGS-B (no bounds: limited-memory BFGS direction + the MINPACK-2
+ * dcsrch line search; defaults m 10, factr 1e7, pgtol 1e-5, maxls 20) is restated as a state machine that lives in
+ * device memory: one `ast_opt_advance` consumes the (losses, gradient) evaluated at the point `ast_opt_buffers`
+ * names and leaves the next evaluation point there.  No host read-back is needed between evaluations; B pairs advance
+ * independently (one thread-block cluster each).  The SciPy-driven `ast_step_host` path stays the parity reference. */
+typedef struct ast_opt ast_opt;
+
+typedef struct ast_opt_config {
+    int32_t T;             /* variables per pair (= samples)                                                */
+    int32_t B;             /* independent problems                                                          */
+    int32_t m;             /* history pairs (SciPy maxcor), 0 = 10, <= 16                                   */
+    int32_t maxiter;       /* iterations per epoch (methods.py:137), 0 = 100                                */
+    int32_t epochs;        /* fresh runs from the current iterate (methods.py:164), 0 = 1                   */
+    int32_t min_evals;     /* stop after an epoch with fewer evaluations (methods.py:180-181: 50)           */
+    int32_t maxls;         /* line-search evaluations before the memory is dropped (SciPy maxls), 0 = 20    */
+    int32_t max_log;       /* rows of the per-evaluation losses log [B][max_log][4]                         */
+    int32_t keep_epoch_x;  /* keep the iterate at the end of every epoch (the reference writes ep-N.wav)    */
+    int32_t device;
+    double  factr;         /* 0 = 1e7 (ftol = factr * eps)                                                  */
+    double  pgtol;         /* < 0 = 1e-5                                                                    */
+} ast_opt_config;
+
+int  ast_opt_create(const ast_opt_config* cfg, ast_opt** out);
+int  ast_opt_destroy(ast_opt* opt);
+int64_t ast_opt_workspace_bytes(const ast_opt* opt);
+/* Start from x0 [B,T] float64 (host or device pointer).  Asynchronous on `stream`. */
+int  ast_opt_reset(ast_opt* opt, const double* p_x0, void* stream);
+/* Device buffers of the machine: evaluate the step at *d_x [B,T] and put its results in *d_losses [B,4],
+ * *d_grad [B,T] (any pointer may be NULL). */
+int  ast_opt_buffers(ast_opt* opt, float** d_x, float** d_losses, float** d_grad);
+/* One transition (one kernel launch, asynchronous, CUDA-graph capturable). */
+int  ast_opt_advance(ast_opt* opt, void* stream);
+/* Synchronising read-back: h_status [B][8] = {phase (0 epoch start, 1 line search, 2 done), epochs finished,
+ * iteration, evaluations this epoch, evaluations in total, why the last epoch ended (1 maxiter, 2 pgtol, 3 ftol,
+ * 4 abnormal line search), history pairs held, line-search evaluations}; h_f [B] = loss at the iterate (may be NULL). */
+int  ast_opt_status(ast_opt* opt, int32_t* h_status, double* h_f, void* stream);
+/* The iterate x_k [B,T] as float64 (synchronises). */
+int  ast_opt_result(ast_opt* opt, double* h_x, void* stream);
+/* Per-epoch records [B][epochs]: evaluations used, end reason, and (keep_epoch_x) the iterate [B][epochs][T] fp32. */
+int  ast_opt_epochs(ast_opt* opt, int32_t* h_nfev, int32_t* h_end, float* h_x, void* stream);
+/* The losses {total, content, style, reg} of every evaluation, [B][max_log][4] (methods.py:147-157 prints them). */
+int  ast_opt_log(ast_opt* opt, float* h_log, void* stream);
+/* Whole optimisation: replays [ast_step at the machine's point, ast_opt_advance] as one CUDA graph until every pair
+ * has stopped or max_evals (0 = no cap) evaluations were enqueued; status is read back every `chunk` (0 = 4)
+ * evaluations, one chunk behind, so the device never waits for the host.  ctx must have B and T of opt, weights and
+ * targets set.  Synchronises before returning. */
+int  ast_minimize(ast_ctx* ctx, ast_opt* opt, int64_t max_evals, int32_t chunk, int64_t* evals_enqueued);
+
 #ifdef __cplusplus
 }
 #endif
