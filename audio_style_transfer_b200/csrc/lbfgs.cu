@@ -15,8 +15,12 @@
 // elements in every pass, so vector passes need no barrier of their own.  Dot products: warp shuffle -> CTA ->
 // every CTA writes its partial into every peer's shared memory (DSMEM) -> cluster barrier -> fixed-order sum, so all
 // CTAs hold bit-identical scalars and run the scalar part (dcsrch, tests, two-loop coefficients) redundantly in
-// fp64 without any broadcast.  Vectors are fp32 (x_trial, g, d, S, Y) except the iterate x_k and the two-loop work
-// vector q, which are fp64.
+// fp64 without any broadcast.  Vectors are fp32 (x_trial, g, d, S, Y) except the iterate x_k (fp64).
+//
+// The two-loop recursion runs in COEFFICIENT space: the Gram matrices S.S, S.Y, Y.Y of the history are kept (fp64)
+// and updated, when a pair is stored, by ONE pass that also takes g.S_i and g.Y_i; H g is then O(m^2) scalar work and
+// ONE pass forms d.  An accepted iteration costs 3 cluster reductions instead of 2 m + 3 dependent ones (measured:
+// 117 us -> see DESIGN.md for the per-launch time with 10 pairs held).
 #include "../../include/ast_b200.h"
 #include "common.cuh"
 
@@ -27,7 +31,7 @@
 
 namespace cg = cooperative_groups;
 
-#define OPT_MAXM 16
+#define OPT_MAXM 10
 #define OPT_MAXCL 16
 #define OPT_THREADS 512
 
@@ -40,7 +44,8 @@ struct OptState {
     int brackt, stage, pad;
     double theta, fk, dnorm, stp, gd, gdold;
     double finit, ginit, gtest, width, width1, stx, fx, gx, sty, fy, gy, stmin, stmax;
-    double sy[OPT_MAXM];
+    double sy[OPT_MAXM];       // s_i . y_i as the line search measured it (dr)
+    double rho[OPT_MAXM];      // 1 / sy
 };
 
 struct OptParams {
@@ -53,7 +58,7 @@ struct OptParams {
     double* xk;            // [B][T]  current iterate
     float* gk;             // [B][T]  gradient at x_k
     float* d;              // [B][T]  search direction
-    double* q;             // [B][T]  two-loop work vector
+    double* gram;          // [B][3][m][m] SS, SY, YY inner products of the history
     float* S;              // [B][m][T]
     float* Y;              // [B][m][T]
     float* epoch_x;        // [B][epochs][T] or NULL
@@ -62,42 +67,107 @@ struct OptParams {
     float* log;            // [B][max_log][4]
 };
 
-struct RedBuf {
-    double warp[OPT_THREADS / 32][4];
-    double slot[2][OPT_MAXCL][4];
+// Shared memory of one CTA.  Reductions: every warp leaves its partial sums in warp[w][j]; `cluster_combine` adds the
+// warps, writes the CTA's sums into EVERY peer's slot[par][rank][j] (DSMEM), one cluster barrier, then everybody adds
+// the ranks in the same fixed order -> tot[j] is bit-identical in all CTAs of the cluster.
+struct df { float hi, lo; };      // an unevaluated sum hi + lo of two floats (see 'double-float arithmetic' below)
+#define RED_N 64                 // values per combine: 6 dots x 10 history slots + y.y + max|g|
+struct Shared {
+    double warp[OPT_THREADS / 32][RED_N];
+    double slot[2][OPT_MAXCL][RED_N];
+    double tot[RED_N];
+    // Gram matrices of the history (persist in global memory between launches): SS[i][j] = S_i.S_j,
+    // SY[i][j] = S_i.Y_j, YY[i][j] = Y_i.Y_j, and this gradient's gS[i] = g.S_i, gY[i] = g.Y_i
+    double SS[OPT_MAXM][OPT_MAXM], SY[OPT_MAXM][OPT_MAXM], YY[OPT_MAXM][OPT_MAXM];
+    double gS[OPT_MAXM], gY[OPT_MAXM];
+    df cS[OPT_MAXM], cY[OPT_MAXM], cg;            // H g = cg g + sum_i cS[i] S_i + cY[i] Y_i, coefficients as float pairs
 };
 
-// Cluster-wide reduction of N values (bit j of maxmask: max instead of sum).  Same result in every thread of the
-// cluster.  `par` alternates the slot buffer so that a fast CTA cannot overwrite values a slow one still reads.
-template <int N>
-__device__ __forceinline__ void cluster_reduce(double (&v)[N], unsigned maxmask, RedBuf* rb, int& par) {
-    cg::cluster_group cl = cg::this_cluster();
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+__device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
-    for (int j = 0; j < N; ++j) {
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_max(double v) {
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const double u = __shfl_xor_sync(0xffffffffu, v[j], o);
-            v[j] = ((maxmask >> j) & 1) ? fmax(v[j], u) : v[j] + u;
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+// ---- double-float arithmetic on the fp32 pipe ------------------------------------------------------------------
+// Measured on B200 (scripts/opt_profile.py stamps + ncu): the passes over the vectors were bound by F2F.F64.F32 --
+// converting each loaded float to double runs at a few conversions per clock per SM (pass B: 6500 cycles per history
+// slot for 20 conversions per thread).  So the vector passes keep every sum as an unevaluated (hi, lo) pair of floats
+// (error-free product via fma, TwoSum for the add: ~2^-46 relative) and convert ONCE per reduced value.
+__device__ __forceinline__ void df_acc_prod(df& a, float x, float y) {       // a += x * y
+    const float p = __fmul_rn(x, y);
+    const float e = __fmaf_rn(x, y, -p);
+    const float t = __fadd_rn(a.hi, p);
+    const float bb = __fsub_rn(t, a.hi);
+    const float err = __fadd_rn(__fsub_rn(a.hi, __fsub_rn(t, bb)), __fsub_rn(p, bb));
+    a.hi = t;
+    a.lo = __fadd_rn(a.lo, __fadd_rn(err, e));
+}
+__device__ __forceinline__ df df_add(df a, df b) {
+    const float t = __fadd_rn(a.hi, b.hi);
+    const float bb = __fsub_rn(t, a.hi);
+    const float err = __fadd_rn(__fsub_rn(a.hi, __fsub_rn(t, bb)), __fsub_rn(b.hi, bb));
+    df r;
+    r.hi = t;
+    r.lo = __fadd_rn(__fadd_rn(a.lo, b.lo), err);
+    return r;
+}
+__device__ __forceinline__ double df_to_double(df a) { return (double)a.hi + (double)a.lo; }
+__device__ __forceinline__ df df_shfl_xor(df v, int o) {
+    df u;
+    u.hi = __shfl_xor_sync(0xffffffffu, v.hi, o);
+    u.lo = __shfl_xor_sync(0xffffffffu, v.lo, o);
+    return u;
+}
+__device__ __forceinline__ df warp_sum_df(df v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = df_add(v, df_shfl_xor(v, o));
+    return v;
+}
+// 8 values per lane -> their 8 warp sums with 4 + 2 + 1 + 1 + 1 shuffles instead of 40: each butterfly step halves the
+// values a lane still carries.  Returns the sum of value (lane >> 2); lanes with (lane & 3) == 0 publish it.
+__device__ __forceinline__ df warp_sum8(df (&v)[8], int lane) {
+#pragma unroll
+    for (int step = 0; step < 3; ++step) {
+        const int off = 16 >> step, cnt = 4 >> step;
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int k = 0; k < cnt; ++k) {
+            const df send = up ? v[k] : v[k + cnt];
+            const df keep = up ? v[k + cnt] : v[k];
+            v[k] = df_add(keep, df_shfl_xor(send, off));
         }
-        if (lane == 0) rb->warp[warp][j] = v[j];
     }
+    df r = v[0];
+    r = df_add(r, df_shfl_xor(r, 2));
+    r = df_add(r, df_shfl_xor(r, 1));
+    return r;
+}
+
+// n <= RED_N values, bit j of maxmask: max instead of sum.  Result in sh.tot[0..n), valid for every thread on return.
+__device__ __forceinline__ void cluster_combine(Shared& sh, int n, unsigned long long maxmask, int& par) {
+    cg::cluster_group cl = cg::this_cluster();
     __syncthreads();
-    if (threadIdx.x < N) {
-        const int j = threadIdx.x;
-        double a = rb->warp[0][j];
-        for (int w = 1; w < OPT_THREADS / 32; ++w) a = ((maxmask >> j) & 1) ? fmax(a, rb->warp[w][j]) : a + rb->warp[w][j];
-        const unsigned me = cl.block_rank(), n = cl.num_blocks();
-        for (unsigned r = 0; r < n; ++r) *cl.map_shared_rank(&rb->slot[par][me][j], r) = a;
+    const int j = threadIdx.x;
+    const bool mx = (maxmask >> j) & 1ull;
+    if (j < n) {
+        double a = sh.warp[0][j];
+        for (int w = 1; w < OPT_THREADS / 32; ++w) a = mx ? fmax(a, sh.warp[w][j]) : a + sh.warp[w][j];
+        const unsigned me = cl.block_rank(), nb = cl.num_blocks();
+        for (unsigned r = 0; r < nb; ++r) *cl.map_shared_rank(&sh.slot[par][me][j], r) = a;
     }
     cl.sync();
-    const unsigned n = cl.num_blocks();
-#pragma unroll
-    for (int j = 0; j < N; ++j) {
-        double a = rb->slot[par][0][j];
-        for (unsigned r = 1; r < n; ++r) a = ((maxmask >> j) & 1) ? fmax(a, rb->slot[par][r][j]) : a + rb->slot[par][r][j];
-        v[j] = a;
+    if (j < n) {
+        const unsigned nb = cl.num_blocks();
+        double a = sh.slot[par][0][j];
+        for (unsigned r = 1; r < nb; ++r) a = mx ? fmax(a, sh.slot[par][r][j]) : a + sh.slot[par][r][j];
+        sh.tot[j] = a;
     }
+    __syncthreads();
     par ^= 1;
 }
 
@@ -109,7 +179,7 @@ __device__ __forceinline__ void cluster_reduce(double (&v)[N], unsigned maxmask,
 #define LS_STPMIN 0.0
 #define LS_STPMAX 1e10
 
-__device__ void dcstep(double& stx, double& fx, double& dx, double& sty, double& fy, double& dy, double& stp,
+__device__ __noinline__ void dcstep(double& stx, double& fx, double& dx, double& sty, double& fy, double& dy, double& stp,
                        double fp, double dp, int& brackt, double stpmin, double stpmax) {
     const double sgnd = dp * (dx / fabs(dx));
     double stpf;
@@ -182,7 +252,7 @@ __device__ void dcsrch_start(OptState& s, double f, double g, double stp) {
     s.stp = stp;
 }
 
-__device__ int dcsrch_step(OptState& s, double f, double g) {
+__device__ __noinline__ int dcsrch_step(OptState& s, double f, double g) {
     double stp = s.stp;
     const double ftest = s.finit + stp * s.gtest;
     if (s.stage == 1 && f <= ftest && g >= 0.0) s.stage = 2;
@@ -215,96 +285,158 @@ __device__ int dcsrch_step(OptState& s, double f, double g) {
     return T_FG;
 }
 
+// per-phase clock64() stamps of the lead thread (scripts/opt_profile.py --stamps); NULL in normal use
+__device__ long long* g_opt_stamps = nullptr;
+#define STAMP(n) do { if (lead && g_opt_stamps) g_opt_stamps[n] = clock64(); } while (0)
+#define STAMP_T0(n) do { if (blockIdx.x == 0 && threadIdx.x == 0 && g_opt_stamps) g_opt_stamps[n] = clock64(); } while (0)
+
 // ---- the machine ------------------------------------------------------------------------------------------------
 struct Slice { int lo, hi; };     // this CTA's samples; a thread walks lo + tid, lo + tid + blockDim, ...
 
 #define FOR_OWN(i) for (int i = sl.lo + (int)threadIdx.x; i < sl.hi; i += OPT_THREADS)
+// the same elements four at a time, so that a pass can issue all the loads of a batch before it uses any of them
+// (these passes are latency-bound: 4 elements per thread at T = 16384)
+#define OPT_BATCH 4
+#define FOR_OWN_BATCH(i0) for (int i0 = sl.lo + (int)threadIdx.x; i0 < sl.hi; i0 += OPT_BATCH * OPT_THREADS)
+__device__ __forceinline__ float ldz(const float* p, int i, int hi) { return i < hi ? p[i] : 0.f; }
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
-// d = -H g_k (two-loop recursion, H0 = I / theta), then the line-search start of lnsrlb.  On a non-descent direction
-// L-BFGS-B drops the memory and retries from steepest descent; with no memory left it gives up.  Returns false = gave up.
-__device__ bool new_direction(const OptParams& P, OptState& s, const Slice sl, int pair, RedBuf* rb, int& par) {
+// The two-loop recursion in coefficient space: with q = cg g + sum cS_i S_i + cY_i Y_i every inner product the
+// recursion needs is an entry of the Gram matrices, so H g costs O(m^2) scalar work and NO pass over the vectors
+// (Chen et al., "Large-scale L-BFGS using MapReduce", 2014).  One WARP, lane p = history position p (0 = oldest),
+// slot i_p = (head + p) % m.  Both loops are triangular substitutions: the lane whose turn it is finishes its
+// coefficient, broadcasts it by shuffle, and the lanes still waiting fold it into their running inner product
+// (fp64 latency on this part is long -- a dependent DADD/DFMA chain of ~10 per turn instead of a 21-term warp sum):
+//   loop 1 (newest -> oldest): P_p = S_p.g - sum_{p' > p} alpha_p' S_p.Y_p' ;  alpha_p = rho_p P_p
+//   q0 = (g - sum alpha_p Y_p) / theta ;  R_p = Y_p.q0
+//   loop 2 (oldest -> newest): c_p = alpha_p - rho_p (R_p + sum_{p' < p} c_p' Y_p.S_p')
+//   H g = g / theta - sum (alpha_p / theta) Y_p + sum c_p S_p
+__device__ __noinline__ void two_loop_coefficients(Shared& sh, const OptState& s, int m) {
+    const int lane = threadIdx.x & 31;
+    const int col = s.col;
+    const bool act = lane < col;
+    const int ip = act ? (s.head + lane) % m : 0;            // this lane's slot
+    const double rho = act ? s.rho[ip] : 0.0;
+    const double it = 1.0 / s.theta;
+    double Pp = act ? sh.gS[ip] : 0.0, alpha = 0.0;
+    for (int p = col - 1; p >= 0; --p) {
+        if (lane == p) alpha = rho * Pp;
+        const double a = __shfl_sync(0xffffffffu, alpha, p);
+        const int iq = (s.head + p) % m;
+        if (lane < p) Pp -= a * sh.SY[ip][iq];                // S_lane . Y_p
+    }
+    double R = act ? sh.gY[ip] : 0.0;                         // Y_lane . q0, built from all alphas
+    for (int p = 0; p < col; ++p) {
+        const double a = __shfl_sync(0xffffffffu, alpha, p);
+        const int iq = (s.head + p) % m;
+        if (act) R -= a * sh.YY[iq][ip];
+    }
+    R *= it;
+    double c = 0.0;
+    for (int p = 0; p < col; ++p) {
+        if (lane == p) c = alpha - rho * R;
+        const double cp = __shfl_sync(0xffffffffu, c, p);
+        const int iq = (s.head + p) % m;
+        if (act && lane > p) R += cp * sh.SY[iq][ip];         // Y_lane . S_p
+    }
+    auto split = [](double v) { df r; r.hi = (float)v; r.lo = (float)(v - (double)r.hi); return r; };
+    const df zero = {0.f, 0.f};
+    if (lane < OPT_MAXM) { sh.cS[lane] = zero; sh.cY[lane] = zero; }
+    __syncwarp();
+    if (act) { sh.cS[ip] = split(c); sh.cY[ip] = split(-alpha * it); }
+    if (lane == 0) sh.cg = split(it);
+}
+
+// d = -H g_k, then the line-search start of lnsrlb.  On a non-descent direction L-BFGS-B drops the memory and retries
+// from steepest descent; with no memory left it gives up.  Returns false = gave up.  Needs sh.gS / gY of g_k if col > 0.
+__device__ __noinline__ void set_trial(const OptParams& P, const OptState& s, const Slice sl, int pair);
+__device__ __noinline__ bool new_direction(const OptParams& P, OptState& s, const Slice sl, int pair, Shared& sh, int& par) {
     const size_t base = (size_t)pair * P.T;
     const float* gk = P.gk + base;
-    double* q = P.q + base;
     float* d = P.d + base;
     const float* S = P.S + (size_t)pair * P.m * P.T;
     const float* Y = P.Y + (size_t)pair * P.m * P.T;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (;;) {
-        double alpha[OPT_MAXM];
-        // first loop, newest -> oldest; pass j applies the previous update and takes the next dot
-        {
-            double acc[1] = {0.0};
-            if (s.col > 0) {
-                const float* Sn = S + (size_t)((s.head + s.col - 1) % P.m) * P.T;
-                FOR_OWN(i) { const double v = (double)gk[i]; q[i] = v; acc[0] += (double)Sn[i] * v; }
-            } else {
-                FOR_OWN(i) q[i] = (double)gk[i];
+        STAMP_T0(7);
+        if (threadIdx.x < 32) two_loop_coefficients(sh, s, P.m);
+        __syncthreads();
+        STAMP_T0(8);
+        df dd = {0.f, 0.f}, gd = {0.f, 0.f};
+        const df cgv = sh.cg;
+        const bool unit_step = s.iter != 0;                   // lnsrlb: stp = 1 except on the very first iteration
+        FOR_OWN_BATCH(i0) {
+            // d only has to be a descent direction that the history then describes consistently (s = stp d is what gets
+            // stored, g.d and |d| are taken from the stored d below), so this sum runs in plain fp32 FMAs
+            float q[OPT_BATCH], gv[OPT_BATCH];
+#pragma unroll
+            for (int j = 0; j < OPT_BATCH; ++j) {
+                gv[j] = ldz(gk, i0 + j * OPT_THREADS, sl.hi);
+                q[j] = __fmaf_rn(cgv.hi, gv[j], __fmul_rn(cgv.lo, gv[j]));
             }
-            for (int j = s.col - 1; j >= 0; --j) {
-                const int slot = (s.head + j) % P.m;
-                cluster_reduce<1>(acc, 0u, rb, par);
-                const double a = acc[0] / s.sy[slot];
-                alpha[j] = a;
-                const float* Yj = Y + (size_t)slot * P.T;
-                acc[0] = 0.0;
-                if (j > 0) {
-                    const float* Sp = S + (size_t)((s.head + j - 1) % P.m) * P.T;
-                    FOR_OWN(i) { const double v = q[i] - a * (double)Yj[i]; q[i] = v; acc[0] += (double)Sp[i] * v; }
-                } else {                                     // last update of loop 1, scale by H0, first dot of loop 2
-                    const float* Y0 = Y + (size_t)(s.head % P.m) * P.T;
-                    const double it = 1.0 / s.theta;
-                    FOR_OWN(i) { const double v = (q[i] - a * (double)Yj[i]) * it; q[i] = v; acc[0] += (double)Y0[i] * v; }
+#pragma unroll
+            for (int h = 0; h < OPT_MAXM; h += 5) {            // 40 loads in flight, then their FMAs; slots not held: coefficient 0
+                float sv[OPT_BATCH][5], yv[OPT_BATCH][5];
+#pragma unroll
+                for (int kk = 0; kk < 5; ++kk)
+#pragma unroll
+                    for (int j = 0; j < OPT_BATCH; ++j) {
+                        const bool ok = h + kk < P.m;
+                        sv[j][kk] = ok ? ldz(S + (size_t)(h + kk) * P.T, i0 + j * OPT_THREADS, sl.hi) : 0.f;
+                        yv[j][kk] = ok ? ldz(Y + (size_t)(h + kk) * P.T, i0 + j * OPT_THREADS, sl.hi) : 0.f;
+                    }
+#pragma unroll
+                for (int kk = 0; kk < 5; ++kk) {
+                    const df a = sh.cS[h + kk], b = sh.cY[h + kk];
+#pragma unroll
+                    for (int j = 0; j < OPT_BATCH; ++j) {
+                        q[j] = __fmaf_rn(a.hi, sv[j][kk], q[j]);
+                        q[j] = __fmaf_rn(b.hi, yv[j][kk], q[j]);
+                        q[j] = __fmaf_rn(a.lo, sv[j][kk], __fmaf_rn(b.lo, yv[j][kk], q[j]));
+                    }
                 }
             }
-            if (s.col == 0) {
-                const double it = 1.0 / s.theta;
-                FOR_OWN(i) q[i] *= it;
-            }
-            // second loop, oldest -> newest
-            for (int j = 0; j < s.col; ++j) {
-                const int slot = (s.head + j) % P.m;
-                cluster_reduce<1>(acc, 0u, rb, par);
-                const double c = alpha[j] - acc[0] / s.sy[slot];
-                const float* Sj = S + (size_t)slot * P.T;
-                acc[0] = 0.0;
-                if (j + 1 < s.col) {
-                    const float* Yn = Y + (size_t)((s.head + j + 1) % P.m) * P.T;
-                    FOR_OWN(i) { const double v = q[i] + c * (double)Sj[i]; q[i] = v; acc[0] += (double)Yn[i] * v; }
-                } else {
-                    FOR_OWN(i) q[i] += c * (double)Sj[i];
+#pragma unroll
+            for (int j = 0; j < OPT_BATCH; ++j) {
+                const int i = i0 + j * OPT_THREADS;
+                if (i < sl.hi) {
+                    const float dv = -q[j];
+                    d[i] = dv;
+                    df_acc_prod(dd, dv, dv);
+                    df_acc_prod(gd, gv[j], dv);
+                    if (unit_step) P.x_trial[base + i] = (float)(P.xk[base + i] + (double)dv);
                 }
             }
         }
-        // d = -q (fp32), |d|^2 and g_k . d of the stored direction
-        double r2[2] = {0.0, 0.0};
-        FOR_OWN(i) {
-            const float dv = (float)(-q[i]);
-            d[i] = dv;
-            r2[0] += (double)dv * (double)dv;
-            r2[1] += (double)gk[i] * (double)dv;
-        }
-        cluster_reduce<2>(r2, 0u, rb, par);
-        s.dnorm = sqrt(r2[0]);
+        STAMP_T0(9);
+        dd = warp_sum_df(dd);
+        gd = warp_sum_df(gd);
+        if (lane == 0) { sh.warp[warp][0] = df_to_double(dd); sh.warp[warp][1] = df_to_double(gd); }
+        cluster_combine(sh, 2, 0ull, par);
+        STAMP_T0(10);
+        s.dnorm = sqrt(sh.tot[0]);
         s.stp = s.iter == 0 ? fmin(1.0 / s.dnorm, LS_STPMAX) : 1.0;
-        s.gd = s.gdold = r2[1];
+        s.gd = s.gdold = sh.tot[1];
         s.ifun = 0;
-        if (r2[1] < 0.0) {
-            dcsrch_start(s, s.fk, r2[1], s.stp);
+        if (sh.tot[1] < 0.0) {
+            dcsrch_start(s, s.fk, sh.tot[1], s.stp);
             s.ifun = 1;
+            if (!unit_step) set_trial(P, s, sl, pair);         // (unit step: pass C has already written x_k + d)
             return true;
         }
         if (s.col == 0) return false;
         s.col = 0; s.head = 0; s.theta = 1.0;
+        __syncthreads();                                   // everyone has read the old coefficients
     }
 }
 
-__device__ void set_trial(const OptParams& P, const OptState& s, const Slice sl, int pair) {
+__device__ __noinline__ void set_trial(const OptParams& P, const OptState& s, const Slice sl, int pair) {
     const size_t base = (size_t)pair * P.T;
     const double stp = s.stp;
     FOR_OWN(i) P.x_trial[base + i] = (float)(P.xk[base + i] + stp * (double)P.d[base + i]);
 }
 
-__device__ void end_epoch(const OptParams& P, OptState& s, const Slice sl, int pair, int why, bool lead) {
+__device__ __noinline__ void end_epoch(const OptParams& P, OptState& s, const Slice sl, int pair, int why, bool lead) {
     const size_t base = (size_t)pair * P.T;
     if (P.epoch_x && P.keep_epoch_x) {
         float* ex = P.epoch_x + ((size_t)pair * P.epochs + s.epoch) * P.T;
@@ -326,11 +458,17 @@ __device__ void end_epoch(const OptParams& P, OptState& s, const Slice sl, int p
 }
 
 __global__ void __launch_bounds__(OPT_THREADS) lbfgs_advance_kernel(const OptParams P) {
-    __shared__ RedBuf rb;
+    __shared__ Shared sh;
     cg::cluster_group cl = cg::this_cluster();
     const int ncl = (int)cl.num_blocks(), rank = (int)cl.block_rank();
     const int pair = blockIdx.x / ncl;
     const bool lead = rank == 0 && threadIdx.x == 0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    STAMP(0);
+    double* gram = P.gram + (size_t)pair * 3 * OPT_MAXM * OPT_MAXM;
+    // three independent reads issued together (everything of the optimiser has been pushed out of L2 by the step)
+    const float4 lo4 = *reinterpret_cast<const float4*>(P.losses + pair * 4);
+    if (threadIdx.x < 3 * OPT_MAXM * OPT_MAXM) (&sh.SS[0][0])[threadIdx.x] = gram[threadIdx.x];
     OptState s = P.st[pair];
     cl.sync();                                   // everyone has read the state before the leader may rewrite it
     if (s.phase == PH_DONE) return;
@@ -341,41 +479,64 @@ __global__ void __launch_bounds__(OPT_THREADS) lbfgs_advance_kernel(const OptPar
     sl.hi = min(P.T, sl.lo + chunk);
     const size_t base = (size_t)pair * P.T;
     const float* g = P.g + base;
-    const double f = (double)P.losses[pair * 4];
-    if (lead && s.nfev_total < P.max_log) {
-        float4 lo = *reinterpret_cast<const float4*>(P.losses + pair * 4);
-        *reinterpret_cast<float4*>(P.log + ((size_t)pair * P.max_log + s.nfev_total) * 4) = lo;
-    }
+    const double f = (double)lo4.x;
+    if (lead && s.nfev_total < P.max_log)
+        *reinterpret_cast<float4*>(P.log + ((size_t)pair * P.max_log + s.nfev_total) * 4) = lo4;
     s.nfev += 1;
     s.nfev_total += 1;
+    bool gram_dirty = false;
+    STAMP(1);
+    if (s.phase == PH_LS) {                      // the step's traffic has pushed the history out of L2: ask for it now
+        FOR_OWN(i) {
+            if ((i & 31) == 0) {                 // one request per 128-byte line
+                for (int k = 0; k < P.m; ++k) {
+                    prefetch_l2(P.S + ((size_t)pair * P.m + k) * P.T + i);
+                    prefetch_l2(P.Y + ((size_t)pair * P.m + k) * P.T + i);
+                }
+                prefetch_l2(P.gk + base + i);
+                prefetch_l2(P.xk + base + i);
+                prefetch_l2(P.xk + base + i + 16);
+            }
+        }
+    }
 
     if (s.phase == PH_START) {
         s.col = 0; s.head = 0; s.theta = 1.0; s.iter = 0;
         s.fk = f;
-        double gm[1] = {0.0};
-        FOR_OWN(i) { const float v = g[i]; P.gk[base + i] = v; gm[0] = fmax(gm[0], (double)fabsf(v)); }
-        cluster_reduce<1>(gm, 1u, &rb, par);
-        if (gm[0] <= P.pgtol) end_epoch(P, s, sl, pair, END_PGTOL, lead);
+        float gmf = 0.f;
+        FOR_OWN(i) { const float v = g[i]; P.gk[base + i] = v; gmf = fmaxf(gmf, fabsf(v)); }
+        const double gm = warp_max((double)gmf);
+        if (lane == 0) sh.warp[warp][0] = gm;
+        cluster_combine(sh, 1, 1ull, par);
+        if (sh.tot[0] <= P.pgtol) end_epoch(P, s, sl, pair, END_PGTOL, lead);
         else {
             s.phase = PH_LS;
-            if (new_direction(P, s, sl, pair, &rb, par)) set_trial(P, s, sl, pair);
-            else end_epoch(P, s, sl, pair, END_ABNORMAL, lead);
+            if (!new_direction(P, s, sl, pair, sh, par)) end_epoch(P, s, sl, pair, END_ABNORMAL, lead);
         }
     } else {
-        double gd[1] = {0.0};
-        FOR_OWN(i) gd[0] += (double)g[i] * (double)P.d[base + i];
-        cluster_reduce<1>(gd, 0u, &rb, par);
-        s.gd = gd[0];
-        const int task = dcsrch_step(s, f, gd[0]);
+        df gdv = {0.f, 0.f};
+        FOR_OWN_BATCH(i0) {
+            float a[2][OPT_BATCH];
+#pragma unroll
+            for (int j = 0; j < OPT_BATCH; ++j) { a[0][j] = ldz(g, i0 + j * OPT_THREADS, sl.hi); a[1][j] = ldz(P.d + base, i0 + j * OPT_THREADS, sl.hi); }
+#pragma unroll
+            for (int j = 0; j < OPT_BATCH; ++j) df_acc_prod(gdv, a[0][j], a[1][j]);
+        }
+        gdv = warp_sum_df(gdv);
+        if (lane == 0) sh.warp[warp][0] = df_to_double(gdv);
+        cluster_combine(sh, 1, 0ull, par);
+        s.gd = sh.tot[0];
+        STAMP(2);
+        const int task = dcsrch_step(s, f, s.gd);
+        STAMP(3);
         if (task == T_FG) {
             if (s.ifun >= P.maxls) {                          // lnsrlb: iback >= maxls -> restore, refresh memory, restart
                 bool ok = s.col > 0;
                 if (ok) {
                     s.col = 0; s.head = 0; s.theta = 1.0;
-                    ok = new_direction(P, s, sl, pair, &rb, par);
+                    ok = new_direction(P, s, sl, pair, sh, par);
                 }
-                if (ok) set_trial(P, s, sl, pair);
-                else end_epoch(P, s, sl, pair, END_ABNORMAL, lead);
+                if (!ok) end_epoch(P, s, sl, pair, END_ABNORMAL, lead);
             } else {
                 s.ifun += 1;
                 set_trial(P, s, sl, pair);
@@ -387,41 +548,98 @@ __global__ void __launch_bounds__(OPT_THREADS) lbfgs_advance_kernel(const OptPar
             if (stp == 1.0) { dr = s.gd - s.gdold; ddum = -s.gdold; }
             else { dr = (s.gd - s.gdold) * stp; ddum = -s.gdold * stp * stp; }
             const bool store = dr > 2.220446049250313e-16 * ddum;
-            int slot = 0;
-            if (store) slot = s.col < P.m ? (s.head + s.col) % P.m : s.head;
-            float* Ss = P.S + ((size_t)pair * P.m + slot) * P.T;
-            float* Ys = P.Y + ((size_t)pair * P.m + slot) * P.T;
-            double r2[2] = {0.0, 0.0};                         // y.y, max |g|
+            int slot = s.head, ncol = s.col, nhead = s.head;
+            if (store) {
+                if (s.col < P.m) { slot = (s.head + s.col) % P.m; ncol = s.col + 1; }
+                else { slot = s.head; nhead = (s.head + 1) % P.m; }
+            }
+            float* Sb = P.S + (size_t)pair * P.m * P.T;
+            float* Yb = P.Y + (size_t)pair * P.m * P.T;
+            float* Ss = Sb + (size_t)slot * P.T;
+            float* Ys = Yb + (size_t)slot * P.T;
+            df rrp = {0.f, 0.f};                               // y.y
+            float gmf = 0.f;                                   // max |g|
             FOR_OWN(i) {
                 const double sd = stp * (double)P.d[base + i];
                 P.xk[base + i] += sd;
                 const float gn = g[i];
-                const double y = (double)gn - (double)P.gk[base + i];
+                const float y = __fsub_rn(gn, P.gk[base + i]);  // == (float)((double)gn - (double)gk): the fp64 difference is exact
                 P.gk[base + i] = gn;
-                if (store) { Ss[i] = (float)sd; Ys[i] = (float)y; }
-                r2[0] += y * y;
-                r2[1] = fmax(r2[1], (double)fabsf(gn));
+                if (store) { Ss[i] = (float)sd; Ys[i] = y; }
+                df_acc_prod(rrp, y, y);
+                gmf = fmaxf(gmf, fabsf(gn));
             }
-            cluster_reduce<2>(r2, 2u, &rb, par);
+            STAMP(4);
+            rrp = warp_sum_df(rrp);
+            double rr = df_to_double(rrp), gm = warp_max((double)gmf);
+            if (lane == 0) { sh.warp[warp][60] = rr; sh.warp[warp][61] = gm; }
+            // inner products of every history vector with the new pair and the new gradient: ONE pass, one reduction
+            for (int k = 0; k < P.m; ++k) {
+                const float* Sk = Sb + (size_t)k * P.T;
+                const float* Yk = Yb + (size_t)k * P.T;
+                df v[8];
+#pragma unroll
+                for (int c = 0; c < 8; ++c) { v[c].hi = 0.f; v[c].lo = 0.f; }
+                const bool held = ((k - nhead + P.m) % P.m) < ncol;     // after this iteration's update
+                if (held) FOR_OWN_BATCH(i0) {
+                    float a[5][OPT_BATCH];
+#pragma unroll
+                    for (int j = 0; j < OPT_BATCH; ++j) {
+                        const int i = i0 + j * OPT_THREADS;
+                        a[0][j] = ldz(Sk, i, sl.hi); a[1][j] = ldz(Yk, i, sl.hi);
+                        a[2][j] = ldz(Ss, i, sl.hi); a[3][j] = ldz(Ys, i, sl.hi); a[4][j] = ldz(g, i, sl.hi);
+                    }
+#pragma unroll
+                    for (int j = 0; j < OPT_BATCH; ++j) {
+                        df_acc_prod(v[0], a[0][j], a[2][j]); df_acc_prod(v[1], a[1][j], a[2][j]);     // S_k.s, Y_k.s
+                        df_acc_prod(v[2], a[0][j], a[3][j]); df_acc_prod(v[3], a[1][j], a[3][j]);     // S_k.y, Y_k.y
+                        df_acc_prod(v[4], a[0][j], a[4][j]); df_acc_prod(v[5], a[1][j], a[4][j]);     // S_k.g, Y_k.g
+                    }
+                }
+                const df r = warp_sum8(v, lane);
+                if ((lane & 3) == 0 && (lane >> 2) < 6) sh.warp[warp][k * 6 + (lane >> 2)] = df_to_double(r);
+            }
+            STAMP(5);
+            cluster_combine(sh, 62, 1ull << 61, par);
+            STAMP(6);
+            rr = sh.tot[60];
+            gm = sh.tot[61];
+            if (threadIdx.x < P.m) {                          // this CTA's copy of the Gram matrices (identical in all CTAs)
+                const int k = threadIdx.x;
+                const double* t = sh.tot + k * 6;
+                if (store) {
+                    sh.SS[k][slot] = t[0]; sh.SS[slot][k] = t[0];
+                    sh.SY[slot][k] = t[1];                    // s_new . Y_k
+                    sh.SY[k][slot] = t[2];                    // S_k . y_new
+                    sh.YY[k][slot] = t[3]; sh.YY[slot][k] = t[3];
+                }
+                sh.gS[k] = t[4];
+                sh.gY[k] = t[5];
+            }
+            __syncthreads();
+            gram_dirty = store;
             s.iter += 1;
             const double fold = s.fk;
             s.fk = f;
-            if (r2[1] <= P.pgtol) end_epoch(P, s, sl, pair, END_PGTOL, lead);
+            if (gm <= P.pgtol) end_epoch(P, s, sl, pair, END_PGTOL, lead);
             else if ((fold - f) <= P.ftol * fmax(fmax(fabs(fold), fabs(f)), 1.0)) end_epoch(P, s, sl, pair, END_FTOL, lead);
             else {
                 if (store) {
-                    if (s.col < P.m) s.col += 1;
-                    else s.head = (s.head + 1) % P.m;
+                    s.col = ncol; s.head = nhead;
                     s.sy[slot] = dr;
-                    s.theta = r2[0] / dr;
+                    s.rho[slot] = 1.0 / dr;
+                    s.theta = rr / dr;
                 }
                 if (s.iter >= P.maxiter) end_epoch(P, s, sl, pair, END_MAXITER, lead);
-                else if (new_direction(P, s, sl, pair, &rb, par)) set_trial(P, s, sl, pair);
-                else end_epoch(P, s, sl, pair, END_ABNORMAL, lead);
+                else if (!new_direction(P, s, sl, pair, sh, par)) end_epoch(P, s, sl, pair, END_ABNORMAL, lead);
             }
         }
     }
+    STAMP(11);
+    if (rank == 0 && gram_dirty)
+        for (int i = threadIdx.x; i < 3 * OPT_MAXM * OPT_MAXM; i += OPT_THREADS) gram[i] = (&sh.SS[0][0])[i];
     if (lead) P.st[pair] = s;
+    STAMP(12);
 }
 
 __global__ void lbfgs_reset_kernel(const OptParams P, const double* x0) {
@@ -499,7 +717,7 @@ extern "C" int ast_opt_create(const ast_opt_config* cfg, ast_opt** out) {
     if (cfg->T <= 0 || cfg->B <= 0 || cfg->B > 1024) return ast_set_error(AST_EINVAL, "ast_opt_create: bad T or B");
     ast_opt_config c = *cfg;
     if (c.m <= 0) c.m = 10;
-    if (c.m > OPT_MAXM) return ast_set_error(AST_EINVAL, "ast_opt_create: m > 16");
+    if (c.m > OPT_MAXM) return ast_set_error(AST_EINVAL, "ast_opt_create: m > 10");
     if (c.maxiter <= 0) c.maxiter = 100;
     if (c.epochs <= 0) c.epochs = 1;
     if (c.min_evals < 0) c.min_evals = 0;
@@ -525,7 +743,7 @@ extern "C" int ast_opt_create(const ast_opt_config* cfg, ast_opt** out) {
     float* losses = nullptr; float* grad = nullptr;
     if ((r = oalloc(o, &P.st, (size_t)c.B)) || (r = oalloc(o, &P.x_trial, n)) || (r = oalloc(o, &losses, (size_t)c.B * 4)) ||
         (r = oalloc(o, &grad, n)) || (r = oalloc(o, &P.xk, n)) || (r = oalloc(o, &P.gk, n)) || (r = oalloc(o, &P.d, n)) ||
-        (r = oalloc(o, &P.q, n)) || (r = oalloc(o, &P.S, n * c.m)) || (r = oalloc(o, &P.Y, n * c.m)) ||
+        (r = oalloc(o, &P.gram, (size_t)c.B * 3 * OPT_MAXM * OPT_MAXM)) || (r = oalloc(o, &P.S, n * c.m)) || (r = oalloc(o, &P.Y, n * c.m)) ||
         (r = oalloc(o, &P.epoch_nfev, (size_t)c.B * c.epochs)) || (r = oalloc(o, &P.epoch_end, (size_t)c.B * c.epochs)) ||
         (r = oalloc(o, &P.log, (size_t)c.B * (c.max_log ? c.max_log : 1) * 4)) || (r = oalloc(o, &o->d_x0, n)) ||
         (c.keep_epoch_x && (r = oalloc(o, &P.epoch_x, n * c.epochs)))) {
@@ -535,7 +753,20 @@ extern "C" int ast_opt_create(const ast_opt_config* cfg, ast_opt** out) {
     P.losses = losses; P.g = grad;
     o->d_losses = losses; o->d_grad = grad;
     // one cluster per pair: as many CTAs as give every thread work, at most the portable 8
+    // (16 needs the non-portable opt-in; if this device / driver refuses it, stay at the portable 8)
     int cl = 8;
+    if ((c.T + 15) / 16 >= 2 * OPT_THREADS &&
+        cudaFuncSetAttribute(lbfgs_advance_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) {
+        cudaLaunchConfig_t q = {};
+        q.gridDim = dim3(16); q.blockDim = dim3(OPT_THREADS);
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = 16; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        q.attrs = at; q.numAttrs = 1;
+        int ncl = 0;
+        if (cudaOccupancyMaxActiveClusters(&ncl, lbfgs_advance_kernel, &q) == cudaSuccess && ncl >= 1) cl = 16;
+    }
+    (void)cudaGetLastError();
     while (cl > 1 && (c.T + cl - 1) / cl < OPT_THREADS) cl >>= 1;
     o->cluster = cl;
     if (cudaMallocHost((void**)&o->h_st, 2 * sizeof(OptState) * c.B) != cudaSuccess ||
@@ -547,6 +778,12 @@ extern "C" int ast_opt_create(const ast_opt_config* cfg, ast_opt** out) {
     }
     *out = o;
     return AST_OK;
+}
+
+// debugging aid: d_buf = 16 int64 on the device (or NULL to switch the stamps off)
+extern "C" int ast_opt_debug_stamps(void* d_buf) {
+    long long* p = (long long*)d_buf;
+    return cudaMemcpyToSymbol(g_opt_stamps, &p, sizeof(p)) == cudaSuccess ? AST_OK : AST_ECUDA;
 }
 
 extern "C" int64_t ast_opt_workspace_bytes(const ast_opt* o) { return o ? o->bytes : 0; }

@@ -2,14 +2,14 @@
 """bench.py -- the reference's headline metric on B200: fwd + bwd + Gram-loss steps/s @ 16384 samples.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
-                    [--workload cfg1|cfg0|cfg2] [--precision bf16|fp32] [--pairs B]
+                    [--workload cfg1|cfg0|cfg2|cfg3|cfg4] [--precision bf16|fp32] [--pairs B]
 
 A "step" is one (loss, d loss / d waveform) evaluation of methods.py's L-BFGS-B loop
 (methods.py:133-137,167) on synthetic audio with a random-init NSynth encoder (no network: no
 checkpoint, no wavs).  N=1 workload = BASELINE.json configs[1] (16384-sample pair, --gatys over all
 30 layers, CUDA-graph-captured step).  N>1: one process per GPU, independent pairs per rank, no
-data-path collective (weak scaling); --workload cfg2 instead time-shards one 65536-sample clip with
-one NCCL all-reduce of the Gram partials per step (strong scaling).
+data-path collective (weak scaling; --workload cfg3 = 8 pairs per GPU); --workload cfg2 / cfg4 instead time-shard one
+65536- / 479232-sample clip with one NCCL all-reduce of the Gram partials per step (strong scaling).
 
 Prints ONE JSON line (rank 0).  `value` = device-resident steps/s (CUDA-graph replay, CUDA events);
 `e2e` = the same evaluation through ast_step_host with HOST float64 buffers, as SciPy calls it.
@@ -34,7 +34,10 @@ WORKLOADS = {
     "cfg1": (16384, [29], None, True, "BASELINE configs[1]: 16384-sample pair, --gatys, all 30 layers, lambd 100, gamma 0"),
     "cfg0": (16384, [25], 0, False, "BASELINE configs[0]: 16384-sample pair, channel-wise Gram, --cont_lyrs 25 --stack 0"),
     "cfg2": (65536, [25], 0, False, "BASELINE configs[2]: 65536-sample clip time-sharded over the ranks (cfg0 layer set)"),
+    "cfg3": (16384, [25], 0, False, "BASELINE configs[3]: 64 independent 16384-sample pairs (cfg0 settings), 8 per GPU, data-parallel"),
+    "cfg4": (479232, [29], None, False, "BASELINE configs[4]: 30 s clip (479232 samples), all 30 layers as style layers, channel-wise Gram, time-sharded"),
 }
+TIME_SHARDED = ("cfg2", "cfg4")
 SR = 16000
 
 
@@ -204,8 +207,8 @@ def run_ours(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     name = args.workload or "cfg1"
-    sharded = name == "cfg2" and world > 1
-    B = args.pairs
+    sharded = name in TIME_SHARDED and world > 1
+    B = args.pairs if args.pairs else (8 if name == "cfg3" else 1)
     wl = build_workload(name, B, seed_shift=0 if sharded else rank * B)
     T, NL, L = wl["T"], wl["NL"], wl["L"]
 
@@ -286,10 +289,12 @@ def run_ours(args):
             barrier()
         # ---- the whole L-BFGS-B epoch (methods.py:164-167, maxiter 100): optimiser on the device vs SciPy on the host --
         optim = None
-        if not sharded and rank == 0:
+        if not sharded and rank == 0 and T <= 65536:
             from audio_style_transfer_b200.step import DeviceLBFGS
             x0 = wl["x"].astype(np.float64)
-            opt = DeviceLBFGS(T, B=B, maxiter=100, epochs=1, min_evals=0, max_log=512, device=local)
+            EP = 10                                                # epochs of maxiter 100, no early stop: enough evaluations to time
+            FACTR = 10.0                                           # ftol = 2.2e-15 on both sides: stop only when f stops moving in fp32
+            opt = DeviceLBFGS(T, B=B, maxiter=100, epochs=EP, min_evals=0, max_log=2048, factr=FACTR, device=local)
             opt.reset(x0)
             opt.minimize(st, max_evals=8)                         # graph capture + warm-up
             opt.reset(x0)
@@ -299,8 +304,9 @@ def run_ours(args):
             sd, fk = opt.status()
             nfev_dev = int(sd[:, 4].max())
             f_first = float(opt.log()[0, 0, 0])
-            optim = {"device": {"evals_per_s": nfev_dev * B / dt_dev, "evals": nfev_dev, "enqueued": enq, "iterations": int(sd[0, 2]),
-                                "ms_per_eval": dt_dev / nfev_dev * 1e3, "loss_first": f_first, "loss_last": float(fk[0]),
+            optim = {"epochs": EP, "maxiter": 100, "factr": FACTR,
+                     "device": {"evals_per_s": nfev_dev * B / dt_dev, "evals": nfev_dev, "enqueued": enq,
+                                "ms_per_eval": dt_dev / nfev_dev * 1e3, "ms_per_enqueued_eval": dt_dev / enq * 1e3, "loss_first": f_first, "loss_last": float(fk[0]),
                                 "api": "ast_minimize: [ast_step, ast_opt_advance] graph replays, no host read-back per evaluation"}}
             opt.close()
             if B == 1:
@@ -313,9 +319,12 @@ def run_ours(args):
                     fl[0] = float(lo[0, 0])
                     return fl[0], gg[0]
                 t0 = time.perf_counter()
-                res = sp_minimize(fun, x0[0], jac=True, method="L-BFGS-B", options={"maxiter": 100})
+                xs = x0[0]
+                for _ in range(EP):
+                    res = sp_minimize(fun, xs, jac=True, method="L-BFGS-B", options={"maxiter": 100, "ftol": FACTR * np.finfo(float).eps})
+                    xs = res.x
                 dt_sp = time.perf_counter() - t0
-                optim["scipy"] = {"evals_per_s": cnt[0] / dt_sp, "evals": cnt[0], "iterations": int(res.nit),
+                optim["scipy"] = {"evals_per_s": cnt[0] / dt_sp, "evals": cnt[0],
                                   "ms_per_eval": dt_sp / cnt[0] * 1e3, "loss_last": float(res.fun),
                                   "api": "scipy.optimize.minimize(L-BFGS-B) on ast_step_host, as the reference drives its step"}
     tmax = torch.tensor([dev_ms, e2e_ms if not sharded else 0.0], device=dev, dtype=torch.float64)
@@ -409,7 +418,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
-    ap.add_argument("--pairs", type=int, default=1, help="independent pairs per GPU (B)")
+    ap.add_argument("--pairs", type=int, default=0, help="independent pairs per GPU (B); default 1, cfg3: 8")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -150,7 +150,7 @@ typedef struct ast_opt ast_opt;
 typedef struct ast_opt_config {
     int32_t T;             /* variables per pair (= samples)                                                */
     int32_t B;             /* independent problems                                                          */
-    int32_t m;             /* history pairs (SciPy maxcor), 0 = 10, <= 16                                   */
+    int32_t m;             /* history pairs (SciPy maxcor), 0 = 10, <= 10                                   */
     int32_t maxiter;       /* iterations per epoch (methods.py:137), 0 = 100                                */
     int32_t epochs;        /* fresh runs from the current iterate (methods.py:164), 0 = 1                   */
     int32_t min_evals;     /* stop after an epoch with fewer evaluations (methods.py:180-181: 50)           */

@@ -310,7 +310,8 @@ class LbfgsMachine:
             return self._end_epoch(END_PGTOL)
         if (fold - f) <= self.ftol * max(abs(fold), abs(f), 1.0):
             return self._end_epoch(END_FTOL)
-        rr = float(np.dot(y, y))
+        ys = y.astype(self.store).astype(np.float64)           # the device takes y.y of the STORED (rounded) pair
+        rr = float(np.dot(ys, ys))
         if stp == 1.0:
             dr, ddum = gd - self.gdold, -self.gdold
         else:
