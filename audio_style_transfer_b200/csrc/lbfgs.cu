@@ -80,7 +80,7 @@ struct Shared {
     // SY[i][j] = S_i.Y_j, YY[i][j] = Y_i.Y_j, and this gradient's gS[i] = g.S_i, gY[i] = g.Y_i
     double SS[OPT_MAXM][OPT_MAXM], SY[OPT_MAXM][OPT_MAXM], YY[OPT_MAXM][OPT_MAXM];
     double gS[OPT_MAXM], gY[OPT_MAXM];
-    df cS[OPT_MAXM], cY[OPT_MAXM], cg;            // H g = cg g + sum_i cS[i] S_i + cY[i] Y_i, coefficients as float pairs
+    double cS[OPT_MAXM], cY[OPT_MAXM], cg;        // H g = cg g + sum_i cS[i] S_i + cY[i] Y_i
 };
 
 __device__ __forceinline__ double warp_sum(double v) {
@@ -339,12 +339,10 @@ __device__ __noinline__ void two_loop_coefficients(Shared& sh, const OptState& s
         const int iq = (s.head + p) % m;
         if (act && lane > p) R += cp * sh.SY[iq][ip];         // Y_lane . S_p
     }
-    auto split = [](double v) { df r; r.hi = (float)v; r.lo = (float)(v - (double)r.hi); return r; };
-    const df zero = {0.f, 0.f};
-    if (lane < OPT_MAXM) { sh.cS[lane] = zero; sh.cY[lane] = zero; }
+    if (lane < OPT_MAXM) { sh.cS[lane] = 0.0; sh.cY[lane] = 0.0; }
     __syncwarp();
-    if (act) { sh.cS[ip] = split(c); sh.cY[ip] = split(-alpha * it); }
-    if (lane == 0) sh.cg = split(it);
+    if (act) { sh.cS[ip] = c; sh.cY[ip] = -alpha * it; }
+    if (lane == 0) sh.cg = it;
 }
 
 // d = -H g_k, then the line-search start of lnsrlb.  On a non-descent direction L-BFGS-B drops the memory and retries
@@ -363,17 +361,15 @@ __device__ __noinline__ bool new_direction(const OptParams& P, OptState& s, cons
         __syncthreads();
         STAMP_T0(8);
         df dd = {0.f, 0.f}, gd = {0.f, 0.f};
-        const df cgv = sh.cg;
+        const double cgv = sh.cg;
         const bool unit_step = s.iter != 0;                   // lnsrlb: stp = 1 except on the very first iteration
         FOR_OWN_BATCH(i0) {
-            // d only has to be a descent direction that the history then describes consistently (s = stp d is what gets
-            // stored, g.d and |d| are taken from the stored d below), so this sum runs in plain fp32 FMAs
-            float q[OPT_BATCH], gv[OPT_BATCH];
+            // fp64 here: measured no slower than an fp32 or a float-pair sum (this pass is bound by its 80 loads per thread
+            // and by instruction fetch, not by the conversions), and it keeps d equal to the oracle's to the last bit or two
+            double q[OPT_BATCH];
+            float gv[OPT_BATCH];
 #pragma unroll
-            for (int j = 0; j < OPT_BATCH; ++j) {
-                gv[j] = ldz(gk, i0 + j * OPT_THREADS, sl.hi);
-                q[j] = __fmaf_rn(cgv.hi, gv[j], __fmul_rn(cgv.lo, gv[j]));
-            }
+            for (int j = 0; j < OPT_BATCH; ++j) { gv[j] = ldz(gk, i0 + j * OPT_THREADS, sl.hi); q[j] = cgv * (double)gv[j]; }
 #pragma unroll
             for (int h = 0; h < OPT_MAXM; h += 5) {            // 40 loads in flight, then their FMAs; slots not held: coefficient 0
                 float sv[OPT_BATCH][5], yv[OPT_BATCH][5];
@@ -387,20 +383,16 @@ __device__ __noinline__ bool new_direction(const OptParams& P, OptState& s, cons
                     }
 #pragma unroll
                 for (int kk = 0; kk < 5; ++kk) {
-                    const df a = sh.cS[h + kk], b = sh.cY[h + kk];
+                    const double a = sh.cS[h + kk], b = sh.cY[h + kk];
 #pragma unroll
-                    for (int j = 0; j < OPT_BATCH; ++j) {
-                        q[j] = __fmaf_rn(a.hi, sv[j][kk], q[j]);
-                        q[j] = __fmaf_rn(b.hi, yv[j][kk], q[j]);
-                        q[j] = __fmaf_rn(a.lo, sv[j][kk], __fmaf_rn(b.lo, yv[j][kk], q[j]));
-                    }
+                    for (int j = 0; j < OPT_BATCH; ++j) q[j] += a * (double)sv[j][kk] + b * (double)yv[j][kk];
                 }
             }
 #pragma unroll
             for (int j = 0; j < OPT_BATCH; ++j) {
                 const int i = i0 + j * OPT_THREADS;
                 if (i < sl.hi) {
-                    const float dv = -q[j];
+                    const float dv = (float)(-q[j]);
                     d[i] = dv;
                     df_acc_prod(dd, dv, dv);
                     df_acc_prod(gd, gv[j], dv);

@@ -45,7 +45,7 @@ def lockstep(fn, x0, B=1, evals=60, **kw):
             xo = machs[b].x_trial
             err = np.max(np.abs(xd[b] - xo)) / max(1e-30, np.max(np.abs(xo)))
             worst = max(worst, err)
-            assert err <= 1e-5, (k, b, err)       # the direction is summed in fp32 on the device (csrc/lbfgs.cu pass C): ~3e-6
+            assert err <= 2e-6, (k, b, err)
             assert st[b, 2] == machs[b].iter and st[b, 4] == machs[b].nfev_total, (k, b, st[b])
         if all(m.done for m in machs):
             break
