@@ -48,6 +48,7 @@ int  setup_f32_kernels();
 // [own_lo, own_hi) (row index within the pair) do not contribute (time sharding).
 void launch_gram_ours(const float* const* d_F, int L, int T, int B, int own_lo, int own_hi,
                       float* part, int nchunk, int chunk_rows, cudaStream_t s);
+int  gram_ours_max_small_L();     // L up to which launch_gram_ours uses the one-stack kernel
 void launch_gram_gatys(const float* const* d_F, int L, int T, int B, int own_lo, int own_hi,
                        float* part, int nchunk, int chunk_rows, cudaStream_t s);
 // deterministic fixed-order reduction of partials -> G (fp32).  nmat matrices of msize elements;

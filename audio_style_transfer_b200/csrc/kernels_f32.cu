@@ -1,6 +1,7 @@
 // kernels_f32.cu -- CUDA-core fp32 kernels: the <=1e-4 accuracy tier and every non-GEMM stage.
 // sm_100a only.  Reference lines are cited per kernel (paths relative to the upstream repo).
 #include "common.cuh"
+#include <algorithm>
 #include "ptx.cuh"
 
 // =============================================================================================
@@ -378,8 +379,110 @@ __global__ void __launch_bounds__(320) gram_ours_kernel(const float* const* __re
             }
         }
 }
+// Few style layers (L <= GS_MAXL: one stack, the reference's --stack 0/1/2): the blocked kernel above computes
+// 3 x 64 products per (t, c) of which 55 are needed at L = 10 and is issue-bound (48 us for 84 MB at cfg0).  Here a
+// thread owns ONE channel and ALL L(L+1)/2 pairs in registers (L loads + L(L+1)/2 FMAs per row) and 8 row groups
+// share the channel; same cp.async staging (every byte of F requested once), 4 stages of 16 rows in flight.  The 8 row
+// groups are summed through shared memory in a fixed order at the end -> run-to-run reproducible.
+#define GS_MAXL 12
+#define GS_R 16
+#define GS_STAGES 4
+#define GS_GROUPS 8
+template <int L>
+__global__ void __launch_bounds__(32 * GS_GROUPS) gram_ours_small_kernel(const float* const* __restrict__ F, int T, int own_lo,
+                                                                         int own_hi, float* __restrict__ part, int nchunk,
+                                                                         int chunk_rows) {
+    extern __shared__ __align__(16) float go_s[];          // [stage][L][GS_R][32]; reused as [group][pair][32] at the end
+    constexpr int NP = L * (L + 1) / 2;
+    constexpr int stage_f = L * GS_R * 32;
+    const int cl = threadIdx.x, grp = threadIdx.y;
+    const int tid = grp * 32 + cl;
+    constexpr int nthr = 32 * GS_GROUPS;
+    const int c0 = blockIdx.y * 32, b = blockIdx.z;
+    const int tb = blockIdx.x * chunk_rows;
+    const int t_lo = max(tb, own_lo), t_hi = min(min(tb + chunk_rows, T), own_hi);
+    const int nround = t_hi > t_lo ? (t_hi - t_lo + GS_R - 1) / GS_R : 0;
+    auto issue = [&](int round) {
+        if (round < nround) {
+            float* dst = go_s + (round % GS_STAGES) * stage_f;
+            const int t0 = t_lo + round * GS_R;
+            for (int i = tid; i < L * GS_R * 8; i += nthr) {
+                const int q = i & 7, r = (i >> 3) % GS_R, l = i / (8 * GS_R);
+                const bool ok = t0 + r < t_hi;
+                const float* src = F[l] + ((size_t)b * T + (ok ? t0 + r : t_lo)) * AST_C + c0 + q * 4;
+                cp_async16(smem_u32(dst + (l * GS_R + r) * 32 + q * 4), src, ok);
+            }
+        }
+        cp_async_commit();
+    };
+    float acc[NP];
+#pragma unroll
+    for (int i = 0; i < NP; ++i) acc[i] = 0.f;
+#pragma unroll
+    for (int st = 0; st < GS_STAGES - 1; ++st) issue(st);
+    for (int round = 0; round < nround; ++round) {
+        cp_async_wait<GS_STAGES - 2>();     // this thread's copies of `round` have landed
+        __syncthreads();                    // everyone's have; and everyone is done reading the stage refilled next
+        issue(round + GS_STAGES - 1);
+        const float* sr = go_s + (round % GS_STAGES) * stage_f + cl;
+#pragma unroll
+        for (int rr = 0; rr < GS_R / GS_GROUPS; ++rr) {
+            const int r = grp + rr * GS_GROUPS;
+            float v[L];
+#pragma unroll
+            for (int l = 0; l < L; ++l) v[l] = sr[(l * GS_R + r) * 32];
+            int p = 0;
+#pragma unroll
+            for (int l = 0; l < L; ++l)
+#pragma unroll
+                for (int m = l; m < L; ++m, ++p) acc[p] = fmaf(v[l], v[m], acc[p]);
+        }
+    }
+    cp_async_wait<0>();
+    __syncthreads();
+    float* red = go_s;                                     // [GS_GROUPS][NP][32] <= the staging area
+#pragma unroll
+    for (int p = 0; p < NP; ++p) red[(grp * NP + p) * 32 + cl] = acc[p];
+    __syncthreads();
+    float* out = part + (((size_t)b * nchunk + blockIdx.x) * AST_C + c0 + cl) * L * L;
+    for (int p = grp; p < NP; p += GS_GROUPS) {
+        float a = red[p * 32 + cl];
+#pragma unroll
+        for (int g = 1; g < GS_GROUPS; ++g) a += red[(g * NP + p) * 32 + cl];
+        int l = 0, rem = p;                                 // pair index -> (l <= m)
+        while (rem >= L - l) { rem -= L - l; ++l; }
+        const int m = l + rem;
+        out[l * L + m] = a;
+        out[m * L + l] = a;
+    }
+}
+template <int L>
+static void launch_gos(const float* const* d_F, int T, int B, int own_lo, int own_hi, float* part, int nchunk,
+                       int chunk_rows, cudaStream_t s) {
+    constexpr size_t smem = (size_t)GS_STAGES * L * GS_R * 32 * sizeof(float);
+    static_assert((size_t)GS_GROUPS * (L * (L + 1) / 2) * 32 * sizeof(float) <= smem || L <= 2, "reduction scratch must fit the staging area");
+    static bool once = false;
+    if (!once) {
+        cudaFuncSetAttribute(gram_ours_small_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max(smem, (size_t)GS_GROUPS * 3 * 32 * 4));
+        once = true;
+    }
+    dim3 grid(nchunk, AST_C / 32, B), block(32, GS_GROUPS);
+    gram_ours_small_kernel<L><<<grid, block, std::max(smem, (size_t)GS_GROUPS * 3 * 32 * 4), s>>>(d_F, T, own_lo, own_hi, part, nchunk, chunk_rows);
+}
+int gram_ours_max_small_L() { return GS_MAXL; }
 void launch_gram_ours(const float* const* d_F, int L, int T, int B, int own_lo, int own_hi, float* part, int nchunk,
                       int chunk_rows, cudaStream_t s) {
+    if (L <= GS_MAXL) {
+#define GOS_CASE(n) case n: launch_gos<n>(d_F, T, B, own_lo, own_hi, part, nchunk, chunk_rows, s); break;
+        switch (L) {
+            GOS_CASE(1) GOS_CASE(2) GOS_CASE(3) GOS_CASE(4) GOS_CASE(5) GOS_CASE(6) GOS_CASE(7) GOS_CASE(8)
+            GOS_CASE(9) GOS_CASE(10) GOS_CASE(11) GOS_CASE(12)
+            default: break;
+        }
+#undef GOS_CASE
+        ast_launch_counter += 1;
+        return;
+    }
     const int ng = (L + 7) / 8;
     dim3 grid(nchunk, AST_C / 32, B), block(32, ng * (ng + 1) / 2);
     if (ng <= 2) {
@@ -781,8 +884,99 @@ static void launch_sgo(const float* const* d_F, float* const* d_dF, const float*
     dim3 grid(T / 64, AST_C / 32, B), block(32, L);
     style_grad_ours_kernel<L, ROWS><<<grid, block, 0, s>>>(d_F, d_dF, Ssym, T);
 }
+// One stack (L <= GS_MAXL): the kernel above issues one LDS per FMA (a thread = one (channel, layer) output) and sits at
+// 47 us for 168 MB at cfg0.  Here a thread owns one channel and ALL L outputs of a row: the symmetric L x L coefficient
+// block lives in L(L+1)/2 registers, a row costs L LDS + L^2 FMAs, outputs go straight from registers to dF (32 channels =
+// one 128-byte line per (layer, row)).  Staging as in gram_ours_small_kernel.
+#define SGS_ROWS 256            // rows per CTA
+template <int L>
+__global__ void __launch_bounds__(32 * GS_GROUPS) style_grad_ours_small_kernel(const float* const* __restrict__ F,
+                                                                               float* const* __restrict__ dF,
+                                                                               const float* __restrict__ Ssym, int T) {
+    extern __shared__ __align__(16) float go_s[];          // [stage][L][GS_R][32]
+    constexpr int NP = L * (L + 1) / 2;
+    constexpr int stage_f = L * GS_R * 32;
+    constexpr int nthr = 32 * GS_GROUPS;
+    const int cl = threadIdx.x, grp = threadIdx.y, tid = grp * 32 + cl;
+    const int c0 = blockIdx.y * 32, b = blockIdx.z;
+    const int t_lo = blockIdx.x * SGS_ROWS, t_hi = min(t_lo + SGS_ROWS, T);
+    const int nround = (t_hi - t_lo + GS_R - 1) / GS_R;
+    auto issue = [&](int round) {
+        if (round < nround) {
+            float* dst = go_s + (round % GS_STAGES) * stage_f;
+            const int t0 = t_lo + round * GS_R;
+            for (int i = tid; i < L * GS_R * 8; i += nthr) {
+                const int q = i & 7, r = (i >> 3) % GS_R, l = i / (8 * GS_R);
+                const bool ok = t0 + r < t_hi;
+                const float* src = F[l] + ((size_t)b * T + (ok ? t0 + r : t_lo)) * AST_C + c0 + q * 4;
+                cp_async16(smem_u32(dst + (l * GS_R + r) * 32 + q * 4), src, ok);
+            }
+        }
+        cp_async_commit();
+    };
+#pragma unroll
+    for (int st = 0; st < GS_STAGES - 1; ++st) issue(st);
+    float S[NP];                                            // upper triangle of the symmetric block of this channel
+    {
+        const float* Sc = Ssym + ((size_t)b * AST_C + c0 + cl) * L * L;
+        int p = 0;
+#pragma unroll
+        for (int l = 0; l < L; ++l)
+#pragma unroll
+            for (int m = l; m < L; ++m, ++p) S[p] = Sc[l * L + m];
+    }
+    for (int round = 0; round < nround; ++round) {
+        cp_async_wait<GS_STAGES - 2>();
+        __syncthreads();
+        issue(round + GS_STAGES - 1);
+        const float* sr = go_s + (round % GS_STAGES) * stage_f + cl;
+#pragma unroll
+        for (int rr = 0; rr < GS_R / GS_GROUPS; ++rr) {
+            const int r = grp + rr * GS_GROUPS;
+            const int t = t_lo + round * GS_R + r;
+            float v[L], o[L];
+#pragma unroll
+            for (int l = 0; l < L; ++l) { v[l] = sr[(l * GS_R + r) * 32]; o[l] = 0.f; }
+            int p = 0;
+#pragma unroll
+            for (int l = 0; l < L; ++l)
+#pragma unroll
+                for (int m = l; m < L; ++m, ++p) {
+                    o[l] = fmaf(S[p], v[m], o[l]);
+                    if (m != l) o[m] = fmaf(S[p], v[l], o[m]);
+                }
+            if (t < t_hi) {
+#pragma unroll
+                for (int l = 0; l < L; ++l) dF[l][((size_t)b * T + t) * AST_C + c0 + cl] = o[l];
+            }
+        }
+    }
+    cp_async_wait<0>();
+}
+template <int L>
+static void launch_sgos(const float* const* d_F, float* const* d_dF, const float* Ssym, int T, int B, cudaStream_t s) {
+    constexpr size_t smem = (size_t)GS_STAGES * L * GS_R * 32 * sizeof(float);
+    static bool once = false;
+    if (!once) {
+        cudaFuncSetAttribute(style_grad_ours_small_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        once = true;
+    }
+    dim3 grid((T + SGS_ROWS - 1) / SGS_ROWS, AST_C / 32, B), block(32, GS_GROUPS);
+    style_grad_ours_small_kernel<L><<<grid, block, smem, s>>>(d_F, d_dF, Ssym, T);
+}
 void launch_style_grad_ours(const float* const* d_F, float* const* d_dF, const float* Ssym, int L, int T, int B,
                             cudaStream_t s) {
+    if (L <= GS_MAXL) {
+#define SGOS_CASE(n) case n: launch_sgos<n>(d_F, d_dF, Ssym, T, B, s); break;
+        switch (L) {
+            SGOS_CASE(1) SGOS_CASE(2) SGOS_CASE(3) SGOS_CASE(4) SGOS_CASE(5) SGOS_CASE(6) SGOS_CASE(7) SGOS_CASE(8)
+            SGOS_CASE(9) SGOS_CASE(10) SGOS_CASE(11) SGOS_CASE(12)
+            default: break;
+        }
+#undef SGOS_CASE
+        ast_launch_counter += 1;
+        return;
+    }
 #define SGO_CASE(n) case n: launch_sgo<n>(d_F, d_dF, Ssym, T, B, s); break;
     switch (L) {
         SGO_CASE(1) SGO_CASE(2) SGO_CASE(3) SGO_CASE(4) SGO_CASE(5) SGO_CASE(6) SGO_CASE(7) SGO_CASE(8)
