@@ -118,3 +118,31 @@ void launch_stft_l1_fwd(const float* x, const float2* tw, int T, int B, int win_
                         int own_f_lo, int own_f_hi, signed char* sgn, float* fpart, float* dadx, float* raw, cudaStream_t s);
 void launch_stft_l1_grad(const float* dadx, const float2* tw, const signed char* sgn, int T, int B, int win_begin,
                          int f_lo, int nf, float coef, float* grad, cudaStream_t s);
+
+#ifdef __CUDACC__
+// ---- double-float arithmetic on the fp32 pipe ------------------------------------------------------------------
+struct df { float hi, lo; };      // an unevaluated sum hi + lo of two floats
+// Measured on B200 (scripts/opt_profile.py stamps + ncu of lbfgs_advance_kernel): F2F.F64.F32 -- converting a loaded
+// float to double -- runs at ~2 conversions per clock per SM, so a pass that converts every element is bound by the
+// conversions.  Reductions that want more than fp32 therefore keep every sum as an unevaluated (hi, lo) pair of floats
+// (error-free product via fma, TwoSum for the add: ~2^-46 relative) and convert ONCE per reduced value.
+__device__ __forceinline__ void df_acc_prod(df& a, float x, float y) {       // a += x * y
+    const float p = __fmul_rn(x, y);
+    const float e = __fmaf_rn(x, y, -p);
+    const float t = __fadd_rn(a.hi, p);
+    const float bb = __fsub_rn(t, a.hi);
+    const float err = __fadd_rn(__fsub_rn(a.hi, __fsub_rn(t, bb)), __fsub_rn(p, bb));
+    a.hi = t;
+    a.lo = __fadd_rn(a.lo, __fadd_rn(err, e));
+}
+__device__ __forceinline__ df df_add(df a, df b) {
+    const float t = __fadd_rn(a.hi, b.hi);
+    const float bb = __fsub_rn(t, a.hi);
+    const float err = __fadd_rn(__fsub_rn(a.hi, __fsub_rn(t, bb)), __fsub_rn(b.hi, bb));
+    df r;
+    r.hi = t;
+    r.lo = __fadd_rn(__fadd_rn(a.lo, b.lo), err);
+    return r;
+}
+__device__ __forceinline__ double df_to_double(df a) { return (double)a.hi + (double)a.lo; }
+#endif

@@ -70,7 +70,6 @@ struct OptParams {
 // Shared memory of one CTA.  Reductions: every warp leaves its partial sums in warp[w][j]; `cluster_combine` adds the
 // warps, writes the CTA's sums into EVERY peer's slot[par][rank][j] (DSMEM), one cluster barrier, then everybody adds
 // the ranks in the same fixed order -> tot[j] is bit-identical in all CTAs of the cluster.
-struct df { float hi, lo; };      // an unevaluated sum hi + lo of two floats (see 'double-float arithmetic' below)
 #define RED_N 64                 // values per combine: 6 dots x 10 history slots + y.y + max|g|
 struct Shared {
     double warp[OPT_THREADS / 32][RED_N];
@@ -93,30 +92,7 @@ __device__ __forceinline__ double warp_max(double v) {
     for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
     return v;
 }
-// ---- double-float arithmetic on the fp32 pipe ------------------------------------------------------------------
-// Measured on B200 (scripts/opt_profile.py stamps + ncu): the passes over the vectors were bound by F2F.F64.F32 --
-// converting each loaded float to double runs at a few conversions per clock per SM (pass B: 6500 cycles per history
-// slot for 20 conversions per thread).  So the vector passes keep every sum as an unevaluated (hi, lo) pair of floats
-// (error-free product via fma, TwoSum for the add: ~2^-46 relative) and convert ONCE per reduced value.
-__device__ __forceinline__ void df_acc_prod(df& a, float x, float y) {       // a += x * y
-    const float p = __fmul_rn(x, y);
-    const float e = __fmaf_rn(x, y, -p);
-    const float t = __fadd_rn(a.hi, p);
-    const float bb = __fsub_rn(t, a.hi);
-    const float err = __fadd_rn(__fsub_rn(a.hi, __fsub_rn(t, bb)), __fsub_rn(p, bb));
-    a.hi = t;
-    a.lo = __fadd_rn(a.lo, __fadd_rn(err, e));
-}
-__device__ __forceinline__ df df_add(df a, df b) {
-    const float t = __fadd_rn(a.hi, b.hi);
-    const float bb = __fsub_rn(t, a.hi);
-    const float err = __fadd_rn(__fsub_rn(a.hi, __fsub_rn(t, bb)), __fsub_rn(b.hi, bb));
-    df r;
-    r.hi = t;
-    r.lo = __fadd_rn(__fadd_rn(a.lo, b.lo), err);
-    return r;
-}
-__device__ __forceinline__ double df_to_double(df a) { return (double)a.hi + (double)a.lo; }
+// (float-pair arithmetic: df, df_acc_prod, df_add, df_to_double -- common.cuh)
 __device__ __forceinline__ df df_shfl_xor(df v, int o) {
     df u;
     u.hi = __shfl_xor_sync(0xffffffffu, v.hi, o);
