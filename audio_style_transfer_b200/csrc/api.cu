@@ -212,7 +212,7 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
 
     {   // Gram split-K geometry: few enough chunks to keep the partial buffer small, enough to fill the SMs
         int target = cfg->gatys ? 16 : 128;      // ours: 128 chunks x 4 channel quads = 512 CTAs of the latency-bound kernel
-        if (!cfg->gatys && c->L <= gram_ours_max_small_L()) target = 64;   // one-stack kernel: 256 CTAs, all resident (2 per SM)
+        if (!cfg->gatys) target = 64;            // 64 chunks x 4 channel quads = 256 CTAs, all resident at 2 per SM; halves the partials
         target = std::max(2, (target + c->B - 1) / c->B);
         int rows = (c->T + target - 1) / target;
         rows = std::max(128, ((rows + 127) / 128) * 128);

@@ -2,6 +2,7 @@
 // sm_100a only.  Reference lines are cited per kernel (paths relative to the upstream repo).
 #include "common.cuh"
 #include <algorithm>
+#include <cstdlib>
 #include "ptx.cuh"
 
 // =============================================================================================
@@ -313,7 +314,7 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 
 #define GO_STAGES 3
 template <int R>
-__global__ void __launch_bounds__(320) gram_ours_kernel(const float* const* __restrict__ F, int L, int T, int own_lo,
+__global__ void __launch_bounds__(320, 2) gram_ours_kernel(const float* const* __restrict__ F, int L, int T, int own_lo,
                                                         int own_hi, float* __restrict__ part, int nchunk,
                                                         int chunk_rows, int ng) {
     extern __shared__ __align__(16) float go_s[];          // [stage][8 ng][R][32]
@@ -489,8 +490,16 @@ void launch_gram_ours(const float* const* d_F, int L, int T, int B, int own_lo, 
         const size_t smem = (size_t)GO_STAGES * ng * 8 * 8 * 32 * sizeof(float);      // <= 48 KB
         gram_ours_kernel<8><<<grid, block, smem, s>>>(d_F, L, T, own_lo, own_hi, part, nchunk, chunk_rows, ng);
     } else {
-        const size_t smem = (size_t)GO_STAGES * ng * 8 * 4 * 32 * sizeof(float);      // <= 48 KB at ng = 4
-        gram_ours_kernel<4><<<grid, block, smem, s>>>(d_F, L, T, own_lo, own_hi, part, nchunk, chunk_rows, ng);
+        // 8 rows per round (96 KB at ng = 4, opt-in) and two CTAs per SM: ncu had this kernel at ONE 10-warp CTA per SM
+        // (100 registers x 320 threads, 64 KB carve-out) and 4 rows per barrier: 235 us for 252 MB at L = 30
+        const size_t smem = (size_t)GO_STAGES * ng * 8 * 8 * 32 * sizeof(float);
+        static bool once = false;
+        if (!once) {
+            cudaFuncSetAttribute(gram_ours_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * 4 * 8 * 8 * 32 * 4);
+            cudaFuncSetAttribute(gram_ours_kernel<8>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+            once = true;
+        }
+        gram_ours_kernel<8><<<grid, block, smem, s>>>(d_F, L, T, own_lo, own_hi, part, nchunk, chunk_rows, ng);
     }
     ast_launch_counter += 1;
 }
@@ -964,8 +973,108 @@ static void launch_sgos(const float* const* d_F, float* const* d_dF, const float
     dim3 grid((T + SGS_ROWS - 1) / SGS_ROWS, AST_C / 32, B), block(32, GS_GROUPS);
     style_grad_ours_small_kernel<L><<<grid, block, smem, s>>>(d_F, d_dF, Ssym, T);
 }
+// Several stacks (L > GS_MAXL, e.g. the CLI default: all 30 layers): the per-(channel, layer) kernel below issues one
+// LDS per FMA (900 of each per (t, c) at L = 30).  Here a thread owns one channel, SGT_LO = 6 outputs and SGT_RT = 4
+// rows: per input layer m it loads 6 coefficients + 4 values for 24 FMAs (2.4 FMA per LDS).  The coefficient block of
+// the CTA's 32 channels sits in shared memory as [l][m][32] (conflict-free, 115 KB at L = 30), rows are staged by
+// cp.async, 8 per round.  Same summation order over m as the other two kernels.
+#define SGT_LO 6
+#define SGT_RT 4
+#define SGT_R 8
+#define SGT_ROWS 256
+template <int LT>          // LT > 0: L known at compile time (immediate shared-memory offsets, unrolled m loop); 0: runtime L
+__global__ void __launch_bounds__(32 * 6 * (SGT_R / SGT_RT)) style_grad_ours_tiled_kernel(const float* const* __restrict__ F,
+                                                                                         float* const* __restrict__ dF,
+                                                                                         const float* __restrict__ Ssym,
+                                                                                         int Lrt, int T, int nstage) {
+    const int L = LT ? LT : Lrt;
+    extern __shared__ __align__(16) float go_s[];          // coef [L][L][32] | stages [nstage][L][SGT_R][32]
+    const int cl = threadIdx.x, og = threadIdx.y, rg = threadIdx.z;
+    const int nthr = blockDim.x * blockDim.y * blockDim.z;
+    const int tid = (rg * blockDim.y + og) * 32 + cl;
+    const int c0 = blockIdx.y * 32, b = blockIdx.z;
+    float* coef = go_s;
+    float* stg = go_s + L * L * 32;
+    const int stage_f = L * SGT_R * 32;
+    const int t_lo = blockIdx.x * SGT_ROWS, t_hi = min(t_lo + SGT_ROWS, T);
+    const int nround = (t_hi - t_lo + SGT_R - 1) / SGT_R;
+    auto issue = [&](int round) {
+        if (round < nround) {
+            float* dst = stg + (round % nstage) * stage_f;
+            const int t0 = t_lo + round * SGT_R;
+            for (int i = tid; i < L * SGT_R * 8; i += nthr) {
+                const int q = i & 7, r = (i >> 3) % SGT_R, l = i / (8 * SGT_R);
+                const bool ok = t0 + r < t_hi;
+                const float* src = F[l] + ((size_t)b * T + (ok ? t0 + r : t_lo)) * AST_C + c0 + q * 4;
+                cp_async16(smem_u32(dst + (l * SGT_R + r) * 32 + q * 4), src, ok);
+            }
+        }
+        cp_async_commit();
+    };
+    for (int st = 0; st < nstage - 1; ++st) issue(st);
+    for (int i = tid; i < L * L * 32; i += nthr) {          // coef[l][m][ch] = Ssym[b][c0 + ch][l][m]
+        const int ch = i & 31, lm = i >> 5;
+        coef[i] = Ssym[((size_t)b * AST_C + c0 + ch) * L * L + lm];
+    }
+    const int l0 = og * SGT_LO;
+    for (int round = 0; round < nround; ++round) {
+        if (nstage == 3) cp_async_wait<1>(); else cp_async_wait<0>();
+        __syncthreads();                                    // (also publishes coef before its first use)
+        issue(round + nstage - 1);
+        const float* sr = stg + (round % nstage) * stage_f + (rg * SGT_RT) * 32 + cl;
+        float acc[SGT_LO][SGT_RT];
+#pragma unroll
+        for (int i = 0; i < SGT_LO; ++i)
+#pragma unroll
+            for (int r = 0; r < SGT_RT; ++r) acc[i][r] = 0.f;
+#pragma unroll (LT ? 6 : 2)
+        for (int m = 0; m < L; ++m) {
+            float v[SGT_RT], cf[SGT_LO];
+#pragma unroll
+            for (int r = 0; r < SGT_RT; ++r) v[r] = sr[(m * SGT_R + r) * 32];
+#pragma unroll
+            for (int i = 0; i < SGT_LO; ++i) cf[i] = l0 + i < L ? coef[((l0 + i) * L + m) * 32 + cl] : 0.f;
+#pragma unroll
+            for (int i = 0; i < SGT_LO; ++i)
+#pragma unroll
+                for (int r = 0; r < SGT_RT; ++r) acc[i][r] = fmaf(cf[i], v[r], acc[i][r]);
+        }
+#pragma unroll
+        for (int r = 0; r < SGT_RT; ++r) {
+            const int t = t_lo + round * SGT_R + rg * SGT_RT + r;
+            if (t < t_hi) {
+#pragma unroll
+                for (int i = 0; i < SGT_LO; ++i)
+                    if (l0 + i < L) dF[l0 + i][((size_t)b * T + t) * AST_C + c0 + cl] = acc[i][r];
+            }
+        }
+        if (nstage == 2) __syncthreads();                   // two stages: the one just read is refilled by the next issue
+    }
+    cp_async_wait<0>();
+}
+static bool launch_sgot(const float* const* d_F, float* const* d_dF, const float* Ssym, int L, int T, int B, cudaStream_t s) {
+    const int nog = (L + SGT_LO - 1) / SGT_LO;
+    if (nog > 6) return false;
+    int nstage = 3;
+    auto bytes = [&](int ns) { return ((size_t)L * L * 32 + (size_t)ns * L * SGT_R * 32) * sizeof(float); };
+    if (bytes(nstage) > 227 * 1024) nstage = 2;
+    if (bytes(nstage) > 227 * 1024) return false;
+    static size_t set_for = 0;
+    if (bytes(nstage) > set_for) {
+        if (cudaFuncSetAttribute(style_grad_ours_tiled_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes(nstage)) != cudaSuccess ||
+            cudaFuncSetAttribute(style_grad_ours_tiled_kernel<30>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes(nstage)) != cudaSuccess)
+            return false;
+        set_for = bytes(nstage);
+    }
+    dim3 grid((T + SGT_ROWS - 1) / SGT_ROWS, AST_C / 32, B), block(32, nog, SGT_R / SGT_RT);
+    if (L == 30) style_grad_ours_tiled_kernel<30><<<grid, block, bytes(nstage), s>>>(d_F, d_dF, Ssym, L, T, nstage);   // all three stacks
+    else         style_grad_ours_tiled_kernel<0><<<grid, block, bytes(nstage), s>>>(d_F, d_dF, Ssym, L, T, nstage);
+    return true;
+}
 void launch_style_grad_ours(const float* const* d_F, float* const* d_dF, const float* Ssym, int L, int T, int B,
                             cudaStream_t s) {
+    static const bool old_path = getenv("AST_B200_SGO_OLD") != nullptr;      // A/B switch for profiling: per-(channel, layer) kernel
+    if (L > GS_MAXL && !old_path && launch_sgot(d_F, d_dF, Ssym, L, T, B, s)) { ast_launch_counter += 1; return; }
     if (L <= GS_MAXL) {
 #define SGOS_CASE(n) case n: launch_sgos<n>(d_F, d_dF, Ssym, T, B, s); break;
         switch (L) {

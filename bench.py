@@ -2,7 +2,7 @@
 """bench.py -- the reference's headline metric on B200: fwd + bwd + Gram-loss steps/s @ 16384 samples.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
-                    [--workload cfg1|cfg0|cfg2|cfg3|cfg4] [--precision bf16|fp32] [--pairs B]
+                    [--workload cfg1|cfg0|cfg2|cfg3|cfg4|cli] [--precision bf16|fp32] [--pairs B]
 
 A "step" is one (loss, d loss / d waveform) evaluation of methods.py's L-BFGS-B loop
 (methods.py:133-137,167) on synthetic audio with a random-init NSynth encoder (no network: no
@@ -37,6 +37,7 @@ WORKLOADS = {
     "cfg3": (16384, [25], 0, False, "BASELINE configs[3]: 64 independent 16384-sample pairs (cfg0 settings), 8 per GPU, data-parallel"),
     "cfg4": (479232, [29], None, False, "BASELINE configs[4]: 30 s clip (479232 samples), all 30 layers as style layers, channel-wise Gram, time-sharded"),
 }
+WORKLOADS["cli"] = (16384, [29], None, False, "methods.py CLI defaults: 16384 samples, --cont_lyrs 29, --stack unset = all 30 layers, channel-wise Gram")
 TIME_SHARDED = ("cfg2", "cfg4")
 SR = 16000
 

@@ -42,7 +42,7 @@ def make_step(case, prec, B=1, window=None, T=None):
 
 
 SMALL = ["t1024_ours_s0", "t1024_ours_sub", "t1024_ours_ids", "t2048_gatys_s1", "t4096_cfg0", "t4096_cfg1",
-         "t4096_alias30"]
+         "t4096_alias30", "t2048_ours_all30"]
 
 
 @pytest.mark.parametrize("prec", PRECS)
