@@ -2,6 +2,7 @@
 // sm_100a only.  Reference lines are cited per kernel (paths relative to the upstream repo).
 #include "common.cuh"
 #include <algorithm>
+#include <cooperative_groups.h>
 #include <cstdlib>
 #include "ptx.cuh"
 
@@ -814,6 +815,148 @@ __global__ void __launch_bounds__(1024) heads_kernel(const HeadArgs a) {
         if (Sb) Sb[e] = __float2bfloat16_rn(v);
     }
 }
+// The same head for the Gatys matrices (n = 128) with a CLUSTER of 4 CTAs per matrix: 30 one-CTA launches of the kernel
+// above leave 118 SMs idle and chain ~8 dependent memory round trips per CTA (27 us under ncu).  Here a CTA owns 32 rows
+// (8 elements per thread, every load of a phase in flight at once), the three sums go through DSMEM + one cluster
+// barrier each, and the transposed term of Ssym = dG + dG^T is read from the peer CTA's shared memory.
+#define HG_CL 4
+#define HG_THREADS 512
+#define HG_E 8                                  // elements per thread: 32 rows x 128 / 512
+__device__ __forceinline__ void hg_cluster_sum(double* v, int n, double (*wred)[2], double (*slot)[HG_CL][2], int& par) {
+    namespace cgx = cooperative_groups;
+    cgx::cluster_group cl = cgx::this_cluster();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int j = 0; j < n; ++j) v[j] = warp_sum_d(v[j]);
+    if (lane == 0) for (int j = 0; j < n; ++j) wred[warp][j] = v[j];
+    __syncthreads();
+    if ((int)threadIdx.x < n) {
+        double t = 0.0;
+        for (int w = 0; w < HG_THREADS / 32; ++w) t += wred[w][threadIdx.x];
+        const unsigned me = cl.block_rank();
+        for (unsigned r = 0; r < HG_CL; ++r) *cl.map_shared_rank(&slot[par][me][threadIdx.x], r) = t;
+    }
+    cl.sync();
+    for (int j = 0; j < n; ++j) {
+        double t = 0.0;
+        for (int r = 0; r < HG_CL; ++r) t += slot[par][r][j];
+        v[j] = t;
+    }
+    par ^= 1;
+}
+__global__ void __cluster_dims__(HG_CL, 1, 1) __launch_bounds__(HG_THREADS) heads_gatys_cluster_kernel(const HeadArgs a) {
+    namespace cgx = cooperative_groups;
+    cgx::cluster_group cl = cgx::this_cluster();
+    __shared__ float dgs[32][AST_C + 1];       // this CTA's 32 rows of dG
+    __shared__ double wred[HG_THREADS / 32][2];
+    __shared__ double slot[2][HG_CL][2];
+    __shared__ double red[32];
+    __shared__ int s_last;
+    const int rank = (int)cl.block_rank();
+    const int mat = blockIdx.x / HG_CL, b = blockIdx.y;
+    constexpr int n = AST_C, msize = AST_C * AST_C;
+    const bool used = mat < a.nmat_used;
+    const float* Ps = used ? a.Ps + ((size_t)b * a.nmat_used + mat) * msize : nullptr;
+    const int e0 = rank * (msize / HG_CL) + threadIdx.x;                 // element e0 + k * HG_THREADS
+    int par = 0;
+    float gr[HG_E], pr[HG_E];
+#pragma unroll
+    for (int k = 0; k < HG_E; ++k) pr[k] = used ? Ps[e0 + k * HG_THREADS] : 0.f;
+    if (a.gram_part) {                                                   // split-K partials, ascending chunk order, fp32 adds
+        const float* p = a.gram_part + ((size_t)b * a.nmat + mat) * a.nchunk * msize;
+#pragma unroll
+        for (int k = 0; k < HG_E; ++k) gr[k] = 0.f;
+        for (int c0 = 0; c0 < a.nchunk; c0 += 4) {
+            float t[4][HG_E];
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+#pragma unroll
+                for (int k = 0; k < HG_E; ++k) t[c][k] = c0 + c < a.nchunk ? p[(size_t)(c0 + c) * msize + e0 + k * HG_THREADS] : 0.f;
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+#pragma unroll
+                for (int k = 0; k < HG_E; ++k) gr[k] += t[c][k];
+        }
+    } else {
+        const float* G = a.G + ((size_t)b * a.nmat + mat) * msize;
+#pragma unroll
+        for (int k = 0; k < HG_E; ++k) gr[k] = G[e0 + k * HG_THREADS];
+    }
+    double v[2] = {0.0, 0.0};
+#pragma unroll
+    for (int k = 0; k < HG_E; ++k) v[0] += (double)gr[k] * (double)gr[k];
+    hg_cluster_sum(v, 1, wred, slot, par);
+    const double ss = v[0];
+    const double inv = 1.0 / sqrt(fmax(ss, 1e-12));
+    v[0] = 0.0; v[1] = 0.0;                                              // style squared error, <dGn, Gn>
+    if (used) {
+#pragma unroll
+        for (int k = 0; k < HG_E; ++k) {
+            const double gn = (double)gr[k] * inv;
+            const double d = gn - (double)pr[k];
+            v[0] += d * d;
+            v[1] += (double)a.coef_dGn * d * gn;
+        }
+    }
+    hg_cluster_sum(v, 2, wred, slot, par);
+    const double ls = v[0], dot = v[1];
+    // ---- losses: one CTA per matrix reports; the last matrix of the pair to report writes them (fixed-order sums) ----
+    if (rank == 0) {
+        if (a.done) {
+            if (threadIdx.x == 0) {
+                a.ls_part[(size_t)b * a.nmat + mat] = (float)ls;
+                __threadfence();
+                const unsigned prev = atomicAdd(a.done + b, 1u);
+                s_last = (prev == (unsigned)a.nmat - 1u);
+            }
+            __syncthreads();
+            if (s_last) {
+                __threadfence();
+                double sl = 0.0, sc = 0.0;
+                for (int m = threadIdx.x; m < a.nmat_used; m += HG_THREADS) sl += (double)__ldcg(a.ls_part + (size_t)b * a.nmat + m);
+                if (a.sse_part)
+                    for (int i = threadIdx.x; i < a.sse_nblk; i += HG_THREADS) sc += __ldcg(a.sse_part + (size_t)b * a.sse_nblk + i);
+                sl = block_sum_d(sl, red);
+                sc = a.sse_part ? block_sum_d(sc, red) : (double)a.sse[b];
+                if (threadIdx.x == 0) {
+                    write_losses(a, b, sl, sc);
+                    a.done[b] = 0u;
+                }
+            }
+        } else if (threadIdx.x == 0) {
+            a.ls_part[(size_t)b * a.nmat + mat] = (float)ls;
+        }
+    }
+    const bool clamped = ss < 1e-12;
+    float* Gn = a.Gn ? a.Gn + ((size_t)b * a.nmat + mat) * msize : nullptr;
+    float* Ss = a.Ssym ? a.Ssym + ((size_t)b * a.nmat + mat) * msize : nullptr;
+    __nv_bfloat16* Sb = a.Ssym_bf16 ? a.Ssym_bf16 + ((size_t)b * a.nmat + mat) * msize : nullptr;
+#pragma unroll
+    for (int k = 0; k < HG_E; ++k) {
+        const int e = e0 + k * HG_THREADS;
+        const int i = e / n, j = e - i * n;
+        const double gn = (double)gr[k] * inv;
+        if (Gn) Gn[e] = (float)gn;
+        double dg = 0.0;
+        if (used) {
+            const double dgn = (double)a.coef_dGn * (gn - (double)pr[k]);
+            dg = clamped ? dgn * inv : (dgn - gn * dot) * inv;
+        }
+        dgs[i - rank * 32][j] = (float)dg;
+    }
+    cl.sync();                                   // every CTA's rows of dG are in its shared memory
+    if (Ss) {
+#pragma unroll
+        for (int k = 0; k < HG_E; ++k) {
+            const int e = e0 + k * HG_THREADS;
+            const int i = e / n, j = e - i * n;
+            const float* peer = cl.map_shared_rank(&dgs[j & 31][i], (unsigned)(j >> 5));      // dG[j][i]
+            const float val = dgs[i - rank * 32][j] + *peer;
+            Ss[e] = val;
+            if (Sb) Sb[e] = __float2bfloat16_rn(val);
+        }
+    }
+    cl.sync();                                   // nobody exits while a peer may still read its shared memory
+}
 // losses[b] = {Lc + lambd Ls + gamma reg, Lc, Ls, reg}  (methods.py:116-125)
 __global__ void losses_final_kernel(const HeadArgs a) {
     const int b = blockIdx.x;
@@ -830,7 +973,9 @@ int setup_heads_kernel() {
 void launch_heads(const HeadArgs& a, cudaStream_t s) {
     dim3 grid(a.nmat, a.B);
     const size_t smem = a.Ssym ? (size_t)a.n * (a.n + 1) * sizeof(float) : 0;
-    heads_kernel<<<grid, a.n * a.n >= 4096 ? 1024 : 256, smem, s>>>(a);
+    static const bool one_cta = getenv("AST_B200_HEADS_1CTA") != nullptr;    // A/B switch for profiling
+    if (a.n == AST_C && !one_cta) heads_gatys_cluster_kernel<<<dim3(HG_CL * a.nmat, a.B), HG_THREADS, 0, s>>>(a);
+    else heads_kernel<<<grid, a.n * a.n >= 4096 ? 1024 : 256, smem, s>>>(a);
     ast_launch_counter += 1;
     if (a.losses && !a.done) { losses_final_kernel<<<a.B, 32, 0, s>>>(a); ast_launch_counter += 1; }
 }
@@ -981,23 +1126,22 @@ static void launch_sgos(const float* const* d_F, float* const* d_dF, const float
 #define SGT_LO 6
 #define SGT_RT 4
 #define SGT_R 8
-#define SGT_ROWS 256
 template <int LT>          // LT > 0: L known at compile time (immediate shared-memory offsets, unrolled m loop); 0: runtime L
 __global__ void __launch_bounds__(32 * 6 * (SGT_R / SGT_RT)) style_grad_ours_tiled_kernel(const float* const* __restrict__ F,
                                                                                          float* const* __restrict__ dF,
                                                                                          const float* __restrict__ Ssym,
-                                                                                         int Lrt, int T, int nstage) {
+                                                                                         int Lrt, int T, int nstage, int rows_per_cta) {
     const int L = LT ? LT : Lrt;
-    extern __shared__ __align__(16) float go_s[];          // coef [L][L][32] | stages [nstage][L][SGT_R][32]
+    extern __shared__ __align__(16) float go_s[];          // coef [L][L][33] | stages [nstage][L][SGT_R][32]
     const int cl = threadIdx.x, og = threadIdx.y, rg = threadIdx.z;
     const int nthr = blockDim.x * blockDim.y * blockDim.z;
     const int tid = (rg * blockDim.y + og) * 32 + cl;
     const int c0 = blockIdx.y * 32, b = blockIdx.z;
-    float* coef = go_s;
-    float* stg = go_s + L * L * 32;
+    float* coef = go_s;                                     // row pitch 33: the transposing fill and the reads are both conflict-free
+    float* stg = go_s + ((L * L * 33 + 3) & ~3);
     const int stage_f = L * SGT_R * 32;
-    const int t_lo = blockIdx.x * SGT_ROWS, t_hi = min(t_lo + SGT_ROWS, T);
-    const int nround = (t_hi - t_lo + SGT_R - 1) / SGT_R;
+    const int t_lo = blockIdx.x * rows_per_cta, t_hi = min(t_lo + rows_per_cta, T);
+    const int nround = t_hi > t_lo ? (t_hi - t_lo + SGT_R - 1) / SGT_R : 0;
     auto issue = [&](int round) {
         if (round < nround) {
             float* dst = stg + (round % nstage) * stage_f;
@@ -1012,9 +1156,14 @@ __global__ void __launch_bounds__(32 * 6 * (SGT_R / SGT_RT)) style_grad_ours_til
         cp_async_commit();
     };
     for (int st = 0; st < nstage - 1; ++st) issue(st);
-    for (int i = tid; i < L * L * 32; i += nthr) {          // coef[l][m][ch] = Ssym[b][c0 + ch][l][m]
-        const int ch = i & 31, lm = i >> 5;
-        coef[i] = Ssym[((size_t)b * AST_C + c0 + ch) * L * L + lm];
+    {   // coef[l][m][ch] = Ssym[b][c0 + ch][l][m]: the 32 channels' blocks are one contiguous run of 32 L^2 floats; read it
+        // coalesced (the first version gathered 32 lines per warp load and spent a quarter of the kernel here)
+        const float* src = Ssym + ((size_t)b * AST_C + c0) * L * L;
+        const int LL = L * L;
+        for (int i = tid; i < LL * 32; i += nthr) {
+            const int ch = i / LL, lm = i - ch * LL;
+            coef[lm * 33 + ch] = src[i];
+        }
     }
     const int l0 = og * SGT_LO;
     for (int round = 0; round < nround; ++round) {
@@ -1033,7 +1182,7 @@ __global__ void __launch_bounds__(32 * 6 * (SGT_R / SGT_RT)) style_grad_ours_til
 #pragma unroll
             for (int r = 0; r < SGT_RT; ++r) v[r] = sr[(m * SGT_R + r) * 32];
 #pragma unroll
-            for (int i = 0; i < SGT_LO; ++i) cf[i] = l0 + i < L ? coef[((l0 + i) * L + m) * 32 + cl] : 0.f;
+            for (int i = 0; i < SGT_LO; ++i) cf[i] = l0 + i < L ? coef[((l0 + i) * L + m) * 33 + cl] : 0.f;
 #pragma unroll
             for (int i = 0; i < SGT_LO; ++i)
 #pragma unroll
@@ -1056,7 +1205,7 @@ static bool launch_sgot(const float* const* d_F, float* const* d_dF, const float
     const int nog = (L + SGT_LO - 1) / SGT_LO;
     if (nog > 6) return false;
     int nstage = 3;
-    auto bytes = [&](int ns) { return ((size_t)L * L * 32 + (size_t)ns * L * SGT_R * 32) * sizeof(float); };
+    auto bytes = [&](int ns) { return ((size_t)((L * L * 33 + 3) & ~3) + (size_t)ns * L * SGT_R * 32) * sizeof(float); };
     if (bytes(nstage) > 227 * 1024) nstage = 2;
     if (bytes(nstage) > 227 * 1024) return false;
     static size_t set_for = 0;
@@ -1066,9 +1215,12 @@ static bool launch_sgot(const float* const* d_F, float* const* d_dF, const float
             return false;
         set_for = bytes(nstage);
     }
-    dim3 grid((T + SGT_ROWS - 1) / SGT_ROWS, AST_C / 32, B), block(32, nog, SGT_R / SGT_RT);
-    if (L == 30) style_grad_ours_tiled_kernel<30><<<grid, block, bytes(nstage), s>>>(d_F, d_dF, Ssym, L, T, nstage);   // all three stacks
-    else         style_grad_ours_tiled_kernel<0><<<grid, block, bytes(nstage), s>>>(d_F, d_dF, Ssym, L, T, nstage);
+    // one CTA per SM (207 KB of shared memory) and equal work per CTA: exactly one wave
+    const int nx = std::max(1, 148 / (4 * B));
+    const int rows = std::max(SGT_R, ((T + nx - 1) / nx + SGT_R - 1) / SGT_R * SGT_R);
+    dim3 grid((T + rows - 1) / rows, AST_C / 32, B), block(32, nog, SGT_R / SGT_RT);
+    if (L == 30) style_grad_ours_tiled_kernel<30><<<grid, block, bytes(nstage), s>>>(d_F, d_dF, Ssym, L, T, nstage, rows);   // all three stacks
+    else         style_grad_ours_tiled_kernel<0><<<grid, block, bytes(nstage), s>>>(d_F, d_dF, Ssym, L, T, nstage, rows);
     return true;
 }
 void launch_style_grad_ours(const float* const* d_F, float* const* d_dF, const float* Ssym, int L, int T, int B,
