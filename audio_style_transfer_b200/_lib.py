@@ -15,7 +15,7 @@ from pathlib import Path
 PKG = Path(__file__).resolve().parent
 ROOT = PKG.parent
 SO = PKG / "libast_b200.so"
-SOURCES = ["csrc/api.cu", "csrc/kernels_f32.cu", "csrc/kernels_tc.cu", "csrc/gram_tc.cu", "csrc/stft_reg.cu", "csrc/lbfgs.cu"]
+SOURCES = ["csrc/api.cu", "csrc/kernels_f32.cu", "csrc/kernels_tc.cu", "csrc/gram_tc.cu", "csrc/stft_reg.cu", "csrc/lbfgs.cu", "csrc/gram_ours_tc.cu"]
 HEADERS = ["csrc/common.cuh", "csrc/tc.cuh", "csrc/ptx.cuh", "csrc/stack_fwd.cuh", "csrc/stack_fwd2.cuh", "csrc/stack_bwd.cuh", "../include/ast_b200.h"]
 
 AST_PREC_FP32 = 0

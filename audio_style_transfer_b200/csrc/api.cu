@@ -40,6 +40,7 @@ struct ast_ctx {
     int n_head;
     int nmat, nmat_used, msize, n_side;
     int gram_chunk_rows, gram_nchunk, sse_nblk;
+    bool gram_ours_tc;            // channel-wise Gram on tensor cores (gram_ours_tc.cu)
     int64_t bytes;
     std::vector<void*> allocs;
     // weights (fp32 masters + transposes for the backward)
@@ -213,6 +214,9 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
     {   // Gram split-K geometry: few enough chunks to keep the partial buffer small, enough to fill the SMs
         int target = cfg->gatys ? 16 : 128;      // ours: 128 chunks x 4 channel quads = 512 CTAs of the latency-bound kernel
         if (!cfg->gatys) target = 64;            // 64 chunks x 4 channel quads = 256 CTAs, all resident at 2 per SM; halves the partials
+        c->gram_ours_tc = !cfg->gatys && cfg->precision == AST_PREC_BF16 && gram_ours_tc_supported(c->L) &&
+                          getenv("AST_B200_GRAM_OURS_CUDA") == nullptr;      // (A/B switch for profiling)
+        if (c->gram_ours_tc) target = 37;        // one CTA per SM (164 KB of smem): 37 chunks x 4 quads = 148 CTAs, one wave
         target = std::max(2, (target + c->B - 1) / c->B);
         int rows = (c->T + target - 1) / target;
         rows = std::max(128, ((rows + 127) / 128) * 128);
@@ -414,7 +418,8 @@ static void run_gram(ast_ctx* c, cudaStream_t s, bool fused = false) {
     else if (c->cfg.gatys)
         launch_gram_gatys(c->d_Fptr, c->L, c->T, c->B, c->own_lo, c->own_hi, c->gram_part, c->gram_nchunk, c->gram_chunk_rows, s);
     else
-        launch_gram_ours(c->d_Fptr, c->L, c->T, c->B, c->own_lo, c->own_hi, c->gram_part, c->gram_nchunk, c->gram_chunk_rows, s);
+        if (c->gram_ours_tc) launch_gram_ours_tc(c->d_Fptr, c->L, c->T, c->B, c->own_lo, c->own_hi, c->gram_part, c->gram_nchunk, c->gram_chunk_rows, s);
+        else launch_gram_ours(c->d_Fptr, c->L, c->T, c->B, c->own_lo, c->own_hi, c->gram_part, c->gram_nchunk, c->gram_chunk_rows, s);
     if (!fold_gram_reduce(c, fused))
         launch_gram_reduce(c->gram_part, c->partials, c->cfg.gatys, c->L, c->B, c->gram_nchunk, s);
 }

@@ -1,0 +1,168 @@
+// gram_ours_tc.cu -- channel-wise ("ours") Gram for many style layers (13 <= L <= 32: the CLI default of all 30 layers,
+// BASELINE configs[4]) on tensor cores.  Reference: methods.py:69,73  G[c,l,m] = sum_t S[l,t,c] S[m,t,c].
+//
+// Per channel c this is a 32 x 32 x T product V_c V_c^T with V_c = [layer][t].  The CUDA-core kernel it replaces in the
+// tensor-core tier (gram_ours_kernel, kernels_f32.cu) is issue-bound: 640 FMAs per (t, c), 155 us for 252 MB at L = 30,
+// T = 16384 (FMA bound 37 us, HBM bound 39 us).  The shape -- 128 independent 32 x 32 accumulators, K streamed from HBM once
+// -- does not fit tcgen05's 128-row tiles and shared-memory descriptors, so this is warp-level `mma.sync.m16n8k8` with
+// TF32 operands split in two terms (hi hi + hi lo + lo hi: fp32-grade products, fp32 accumulate).
+//
+// A warp owns 2 channels.  With K = t, the A fragment (rows = layer, cols = t) and the B fragment (k = t, n = layer) of
+// V V^T are the same loads: per k-step of 8 rows a lane reads V[g + 8a][tig + 4b] (g = lane / 4, tig = lane % 4,
+// a < 4, b < 2) = 8 values, which feed the 6 upper-triangular 16 x 8 tiles.  For those loads to be conflict-free the
+// staging buffer is [channel][layer][t] with a row pitch of 12 floats (banks 12 g + tig are all distinct) and a plane
+// pitch of 32 * 12 + 1; HBM rows are [t][channel], so the transposition goes through registers: coalesced 16-byte loads
+// of 4 channels, prefetched TWO rounds ahead in two register sets (one round ahead measured 113 us: a round then costs
+// latency + transfer), 4 scattered (conflict-free) 4-byte shared stores each.
+#include "common.cuh"
+#include "ptx.cuh"
+
+#include <algorithm>
+#include <cstdlib>
+
+#define GT_THREADS 512                      // 16 warps x 2 channels = 32 channels per CTA
+#define GT_R 8                              // rows (t) per round = 1 k-step
+#define GT_PT 12                            // row pitch (floats): 12 g + tig distinct mod 32 for g < 8, tig < 4
+#define GT_PL (32 * GT_PT + 1)              // channel-plane pitch: 4 q * GT_PL = 4 q (mod 32) for the transposing stores
+#define GT_STAGE (32 * GT_PL)               // floats per stage
+#define GT_NLD ((32 * GT_R * 8) / GT_THREADS)                          // 16-byte loads per thread per round at L = 32
+
+__device__ __forceinline__ uint32_t tf32_of(float x) {
+    uint32_t u;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+    return u;
+}
+__device__ __forceinline__ void mma_tf32(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// grid = (nchunk, 4 channel quads, B); part[b][chunk][c][l][m] like the CUDA-core kernels.
+__global__ void __launch_bounds__(GT_THREADS, 1) gram_ours_tc_kernel(const float* const* __restrict__ F, int L, int T, int own_lo,
+                                                                    int own_hi, float* __restrict__ part, int nchunk, int chunk_rows) {
+    extern __shared__ __align__(16) float gt_s[];          // [2 stages][32 channels][32 layers][GT_PT] (+1 per plane)
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, tig = lane & 3;
+    const int c0 = blockIdx.y * 32, b = blockIdx.z;
+    const int tb = blockIdx.x * chunk_rows;
+    const int t_lo = max(tb, own_lo), t_hi = min(min(tb + chunk_rows, T), own_hi);
+    const int nround = t_hi > t_lo ? (t_hi - t_lo + GT_R - 1) / GT_R : 0;
+    const int nld = (L * GT_R * 8 + GT_THREADS - 1) / GT_THREADS;          // <= GT_NLD
+    for (int i = tid; i < 2 * GT_STAGE; i += GT_THREADS) gt_s[i] = 0.f;    // layers L..31 stay zero
+    __syncthreads();
+
+    auto fetch = [&](float4 (&pf)[GT_NLD], int round) {                    // global -> registers (coalesced: 8 lanes = one 128-byte row segment)
+        const int t0 = t_lo + round * GT_R;
+#pragma unroll
+        for (int it = 0; it < GT_NLD; ++it) {
+            const int i = tid + it * GT_THREADS;
+            const int q = i & 7, t = (i >> 3) & (GT_R - 1), l = i / (8 * GT_R);
+            const bool ok = it < nld && l < L && t0 + t < t_hi;
+            pf[it] = ok ? *reinterpret_cast<const float4*>(F[l] + ((size_t)b * T + t0 + t) * AST_C + c0 + q * 4)
+                        : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    };
+    auto stash = [&](const float4 (&pf)[GT_NLD], int stage) {              // registers -> [channel][layer][t]
+        float* dst = gt_s + stage * GT_STAGE;
+#pragma unroll
+        for (int it = 0; it < GT_NLD; ++it) {
+            const int i = tid + it * GT_THREADS;
+            const int q = i & 7, t = (i >> 3) & (GT_R - 1), l = i / (8 * GT_R);
+            if (it < nld && l < L) {
+                float* d = dst + (q * 4) * GT_PL + l * GT_PT + t;
+                d[0] = pf[it].x; d[GT_PL] = pf[it].y; d[2 * GT_PL] = pf[it].z; d[3 * GT_PL] = pf[it].w;
+            }
+        }
+    };
+
+    float acc[2][6][4];
+#pragma unroll
+    for (int ch = 0; ch < 2; ++ch)
+#pragma unroll
+        for (int tl = 0; tl < 6; ++tl)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) acc[ch][tl][k] = 0.f;
+
+    auto compute = [&](int stage) {
+        const float* st = gt_s + stage * GT_STAGE;
+#pragma unroll
+        for (int ch = 0; ch < 2; ++ch) {
+            const float* pl = st + (warp * 2 + ch) * GT_PL + g * GT_PT + tig;
+#pragma unroll
+            for (int ks = 0; ks < GT_R / 8; ++ks) {
+                uint32_t hi[4][2], lo[4][2];                               // V[g + 8a][8 ks + tig + 4 bb]
+#pragma unroll
+                for (int a = 0; a < 4; ++a)
+#pragma unroll
+                    for (int bb = 0; bb < 2; ++bb) {
+                        const float v = pl[(8 * a) * GT_PT + 8 * ks + 4 * bb];
+                        hi[a][bb] = tf32_of(v);
+                        lo[a][bb] = tf32_of(v - __uint_as_float(hi[a][bb]));
+                    }
+                // tiles (row block of 16 layers, column block of 8 layers), upper triangle: (0,0..3), (1,2..3)
+#pragma unroll
+                for (int tl = 0; tl < 6; ++tl) {
+                    const int mt = tl < 4 ? 0 : 1, j = tl < 4 ? tl : tl - 2;
+                    const int a0 = 2 * mt, a1 = 2 * mt + 1;
+                    mma_tf32(acc[ch][tl], hi[a0][0], hi[a1][0], hi[a0][1], hi[a1][1], hi[j][0], hi[j][1]);
+                    mma_tf32(acc[ch][tl], hi[a0][0], hi[a1][0], hi[a0][1], hi[a1][1], lo[j][0], lo[j][1]);
+                    mma_tf32(acc[ch][tl], lo[a0][0], lo[a1][0], lo[a0][1], lo[a1][1], hi[j][0], hi[j][1]);
+                }
+            }
+        }
+    };
+    // On entry to round r: stage r & 1 holds round r, register set (r + 1) & 1 holds round r + 1 (requested a round ago), the
+    // other set holds round r + 2 (just requested).  A round stashes r + 1, re-requests r + 3 into the freed set, computes r.
+    float4 s0[GT_NLD], s1[GT_NLD];
+    auto round_body = [&](int r, float4 (&x)[GT_NLD]) {
+        if (r + 1 < nround) stash(x, (r + 1) & 1);
+        if (r + 3 < nround) fetch(x, r + 3);
+        compute(r & 1);
+        __syncthreads();
+    };
+    if (nround > 0) {
+        fetch(s0, 0);
+        stash(s0, 0);
+        if (nround > 1) fetch(s1, 1);
+        if (nround > 2) fetch(s0, 2);
+    }
+    __syncthreads();
+    for (int r = 0; r < nround; r += 2) {
+        round_body(r, s1);
+        if (r + 1 < nround) round_body(r + 1, s0);
+    }
+    // C fragment: c0 (row g, col 2 tig), c1 (g, 2 tig + 1), c2 (g + 8, 2 tig), c3 (g + 8, 2 tig + 1).  Entries with l <= m are written
+    // together with their mirror, so the partial is exactly symmetric.
+#pragma unroll
+    for (int ch = 0; ch < 2; ++ch) {
+        float* out = part + (((size_t)b * nchunk + blockIdx.x) * AST_C + c0 + warp * 2 + ch) * L * L;
+#pragma unroll
+        for (int tl = 0; tl < 6; ++tl) {
+            const int mt = tl < 4 ? 0 : 1, j = tl < 4 ? tl : tl - 2;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int l = 16 * mt + g + (k >> 1) * 8, m = 8 * j + 2 * tig + (k & 1);
+                if (l <= m && m < L) {
+                    out[l * L + m] = acc[ch][tl][k];
+                    out[m * L + l] = acc[ch][tl][k];
+                }
+            }
+        }
+    }
+}
+
+int gram_ours_tc_supported(int L) { return L > gram_ours_max_small_L() && L <= 32; }
+
+void launch_gram_ours_tc(const float* const* d_F, int L, int T, int B, int own_lo, int own_hi, float* part, int nchunk,
+                         int chunk_rows, cudaStream_t s) {
+    const size_t smem = (size_t)2 * GT_STAGE * sizeof(float);
+    static bool once = false;
+    if (!once) {
+        cudaFuncSetAttribute(gram_ours_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        once = true;
+    }
+    dim3 grid(nchunk, AST_C / 32, B);
+    gram_ours_tc_kernel<<<grid, GT_THREADS, smem, s>>>(d_F, L, T, own_lo, own_hi, part, nchunk, chunk_rows);
+    ast_launch_counter += 1;
+}
