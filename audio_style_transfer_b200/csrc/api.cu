@@ -498,6 +498,7 @@ static int step_backward_impl(ast_ctx* c, float* d_losses, float* d_grad, void* 
         tc_style_grad(c->tc, c->L, hos, s);
     }
     else if (c->cfg.gatys) launch_style_grad_gatys(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
+    else if (c->gram_ours_tc && getenv("AST_B200_SGO_CUDA") == nullptr) launch_style_grad_ours_tc(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
     else              launch_style_grad_ours(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
     {
         bool init[30];

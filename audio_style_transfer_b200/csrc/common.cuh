@@ -51,6 +51,8 @@ void launch_gram_ours(const float* const* d_F, int L, int T, int B, int own_lo, 
 int  gram_ours_max_small_L();     // L up to which launch_gram_ours uses the one-stack kernel
 // tensor-core tier, 13 <= L <= 32 (gram_ours_tc.cu): per-channel 32 x 32 Gram by mma.sync with 3xTF32 operands
 int  gram_ours_tc_supported(int L);
+int  style_grad_ours_tc_supported(int L);
+void launch_style_grad_ours_tc(const float* const* d_F, float* const* d_dF, const float* Ssym, int L, int T, int B, cudaStream_t s);
 void launch_gram_ours_tc(const float* const* d_F, int L, int T, int B, int own_lo, int own_hi,
                          float* part, int nchunk, int chunk_rows, cudaStream_t s);
 void launch_gram_gatys(const float* const* d_F, int L, int T, int B, int own_lo, int own_hi,

@@ -166,3 +166,143 @@ void launch_gram_ours_tc(const float* const* d_F, int L, int T, int B, int own_l
     gram_ours_tc_kernel<<<grid, GT_THREADS, smem, s>>>(d_F, L, T, own_lo, own_hi, part, nchunk, chunk_rows);
     ast_launch_counter += 1;
 }
+
+// =====================================================================================================================
+// Channel-wise style gradient on tensor cores (13 <= L <= 32), reference SURVEY.md 8(a):
+//   dF_l[t, c] = sum_m Ssym[c, l, m] F_m[t, c]        (Ssym = dG + dG^T, symmetric)
+// Per channel: OUT[t][l] = V^T[t][m] S[m][l]: M = t (16 rows per round), K = m (4 k-steps), N = l (4 tiles of 8).
+// The coefficient block of a warp's 2 channels lives in registers for the whole CTA as TF32 B fragments (rounded once:
+// 2^-11 relative, the same class as the bf16 Ssym of the Gatys path); the A operand is split in two TF32 terms.
+// Staging [channel][layer][t] with row pitch 24 (banks 24 tig + g all distinct) is filled by 4-byte cp.async (HBM rows are
+// [t][channel]; no register staging, so the next round is in flight while this one is computed and written out).
+// Outputs go back through the consumed stage as [l][t][c] (pitches 548 / 33: conflict-free both ways) and leave as
+// 128-byte rows.  The CUDA-core kernel it replaces (style_grad_ours_tiled_kernel) is 258 us for 504 MB at L = 30.
+// =====================================================================================================================
+#define ST_THREADS 512
+#define ST_R 16
+#define ST_PT 24
+#define ST_PL (32 * ST_PT + 1)
+#define ST_STAGE (32 * ST_PL)                 // floats per input stage (98.4 KB)
+#define ST_OPL 548                            // output staging: index = l * 548 + t * 33 + c
+#define ST_OPT 33
+
+__device__ __forceinline__ void cp_async_commit_st() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src, bool valid) {
+    const int sz = valid ? 4 : 0;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(sz) : "memory");
+}
+
+__global__ void __launch_bounds__(ST_THREADS, 1) style_grad_ours_tc_kernel(const float* const* __restrict__ F,
+                                                                          float* const* __restrict__ dF,
+                                                                          const float* __restrict__ Ssym, int L, int T,
+                                                                          int rows_per_cta) {
+    extern __shared__ __align__(16) float st_s[];          // [2][ST_STAGE]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, tig = lane & 3;
+    const int c0 = blockIdx.y * 32, b = blockIdx.z;
+    const int t_lo = blockIdx.x * rows_per_cta, t_hi = min(t_lo + rows_per_cta, T);
+    const int nround = t_hi > t_lo ? (t_hi - t_lo + ST_R - 1) / ST_R : 0;
+    for (int i = tid; i < 2 * ST_STAGE; i += ST_THREADS) st_s[i] = 0.f;      // layers L..31 stay zero
+    // B fragments: b0 = S[m = 8 ks + tig][l = 8 j + g], b1 = S[m + 4][l]
+    uint32_t bf[2][4][4][2];
+#pragma unroll
+    for (int ch = 0; ch < 2; ++ch) {
+        const float* Sc = Ssym + ((size_t)b * AST_C + c0 + warp * 2 + ch) * L * L;
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks)
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int m = 8 * ks + tig + 4 * h, l = 8 * j + g;
+                    bf[ch][ks][j][h] = tf32_of(m < L && l < L ? Sc[l * L + m] : 0.f);
+                }
+    }
+    __syncthreads();
+    auto issue = [&](int round) {                                          // 4-byte cp.async, transposing [t][c] -> [c][l][t]
+        if (round < nround) {
+            const uint32_t dst = smem_u32(st_s + (round & 1) * ST_STAGE);
+            const int t0 = t_lo + round * ST_R;
+            for (int i = tid; i < L * ST_R * 32; i += ST_THREADS) {
+                const int c = i & 31, t = (i >> 5) & (ST_R - 1), l = i / (32 * ST_R);
+                const bool ok = t0 + t < t_hi;
+                const float* src = F[l] + ((size_t)b * T + (ok ? t0 + t : t_lo)) * AST_C + c0 + c;
+                cp_async4(dst + (uint32_t)(c * ST_PL + l * ST_PT + t) * 4u, src, ok);
+            }
+        }
+        cp_async_commit_st();
+    };
+    issue(0);
+    issue(1);
+    for (int round = 0; round < nround; ++round) {
+        asm volatile("cp.async.wait_group 1;" ::: "memory");              // this thread's copies of `round` have landed
+        __syncthreads();                                                  // everyone's have
+        float* st = st_s + (round & 1) * ST_STAGE;
+        float acc[2][4][4];
+#pragma unroll
+        for (int ch = 0; ch < 2; ++ch) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+#pragma unroll
+                for (int k = 0; k < 4; ++k) acc[ch][j][k] = 0.f;
+            const float* pl = st + (warp * 2 + ch) * ST_PL + tig * ST_PT + g;
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+                // A(row t, col m) = V[m][t]: a0 (t = g, m = 8 ks + tig), a1 (t = g + 8, m), a2 (t = g, m + 4), a3 (t = g + 8, m + 4)
+                uint32_t ah[4], al[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float v = pl[(8 * ks + 4 * (k >> 1)) * ST_PT + 8 * (k & 1)];
+                    ah[k] = tf32_of(v);
+                    al[k] = tf32_of(v - __uint_as_float(ah[k]));
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    mma_tf32(acc[ch][j], ah[0], ah[1], ah[2], ah[3], bf[ch][ks][j][0], bf[ch][ks][j][1]);
+                    mma_tf32(acc[ch][j], al[0], al[1], al[2], al[3], bf[ch][ks][j][0], bf[ch][ks][j][1]);
+                }
+            }
+        }
+        __syncthreads();                                                  // everyone is done reading this stage: reuse it for the outputs
+        // C fragment: c0 (t = g, l = 8 j + 2 tig), c1 (t = g, l + 1), c2 (t = g + 8, l), c3 (t = g + 8, l + 1)
+#pragma unroll
+        for (int ch = 0; ch < 2; ++ch)
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int l = 8 * j + 2 * tig + (k & 1), t = g + 8 * (k >> 1);
+                    st[l * ST_OPL + t * ST_OPT + warp * 2 + ch] = acc[ch][j][k];
+                }
+        __syncthreads();
+        const int t0 = t_lo + round * ST_R;
+        for (int i = tid; i < L * ST_R * 32; i += ST_THREADS) {           // 32 lanes = one 128-byte row of dF_l
+            const int c = i & 31, t = (i >> 5) & (ST_R - 1), l = i / (32 * ST_R);
+            if (t0 + t < t_hi) dF[l][((size_t)b * T + t0 + t) * AST_C + c0 + c] = st[l * ST_OPL + t * ST_OPT + c];
+        }
+        __syncthreads();                                                  // outputs are out: the stage may be refilled
+        // the refill must leave layers L..31 of the INPUT layout zero: the output staging has just overwritten parts of them
+        for (int i = tid; i < (32 - L) * 32 * ST_R; i += ST_THREADS) {
+            const int t = i & (ST_R - 1), c = (i / ST_R) & 31, l = L + i / (32 * ST_R);
+            st[c * ST_PL + l * ST_PT + t] = 0.f;
+        }
+        issue(round + 2);
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+
+int style_grad_ours_tc_supported(int L) { return gram_ours_tc_supported(L); }
+
+void launch_style_grad_ours_tc(const float* const* d_F, float* const* d_dF, const float* Ssym, int L, int T, int B, cudaStream_t s) {
+    const size_t smem = (size_t)2 * ST_STAGE * sizeof(float);
+    static bool once = false;
+    if (!once) {
+        cudaFuncSetAttribute(style_grad_ours_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        once = true;
+    }
+    const int nx = std::max(1, 148 / (4 * B));                            // one CTA per SM, one wave
+    const int rows = std::max(ST_R, ((T + nx - 1) / nx + ST_R - 1) / ST_R * ST_R);
+    dim3 grid((T + rows - 1) / rows, AST_C / 32, B);
+    style_grad_ours_tc_kernel<<<grid, ST_THREADS, smem, s>>>(d_F, d_dF, Ssym, L, T, rows);
+    ast_launch_counter += 1;
+}
