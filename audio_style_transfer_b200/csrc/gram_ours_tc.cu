@@ -177,7 +177,8 @@ void launch_gram_ours_tc(const float* const* d_F, int L, int T, int B, int own_l
 // [t][channel]; no register staging, so the next round is in flight while this one is computed and written out).
 // Outputs go back through the consumed stage as [l][t][c] (pitches 548 / 33: conflict-free both ways) and leave as
 // 128-byte rows (8-byte stores straight from the accumulator registers -- 32 rows per warp instruction, partial sectors --
-// were measured: 302 us against 207 us).  The CUDA-core kernel it replaces (style_grad_ours_tiled_kernel) is 258 us for 504 MB at L = 30.
+// were measured: 302 us against 207 us; so was the transposed product OUT^T = S V with 8-row rounds, four 33 KB stages,
+// a separate output double buffer and ONE barrier per round: 252 us -- the kernel is not waiting for its loads).  The CUDA-core kernel it replaces (style_grad_ours_tiled_kernel) is 258 us for 504 MB at L = 30.
 // =====================================================================================================================
 #define ST_THREADS 512
 #define ST_R 16
