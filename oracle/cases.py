@@ -22,6 +22,7 @@ CASES = {
     "t4096_cfg0":       (4096, [25], 0, None, False, 128, 128, 5),     # BASELINE configs[0] layer set
     "t4096_cfg1":       (4096, [29], None, None, True, 128, 128, 2),   # BASELINE configs[1] layer set
     "t4096_alias30":    (4096, [30], 2, None, False, 128, 128, 1),     # extracts[30] aliases [29]
+    "t1024_ours_l17":   (1024, [19], None, list(range(3, 20)), False, 96, 128, 1),   # 17 style layers (not a multiple of 8), 96 channels
     "t2048_ours_all30": (2048, [29], None, None, False, 128, 128, 1),  # the CLI default head: --stack unset = all 30 layers, channel-wise (cfg4's head)
     # BASELINE.json sizes
     "t16384_cfg0":      (16384, [25], 0, None, False, 128, 128, 1),

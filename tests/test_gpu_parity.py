@@ -42,7 +42,7 @@ def make_step(case, prec, B=1, window=None, T=None):
 
 
 SMALL = ["t1024_ours_s0", "t1024_ours_sub", "t1024_ours_ids", "t2048_gatys_s1", "t4096_cfg0", "t4096_cfg1",
-         "t4096_alias30", "t2048_ours_all30"]
+         "t4096_alias30", "t2048_ours_all30", "t1024_ours_l17"]
 
 
 @pytest.mark.parametrize("prec", PRECS)
@@ -169,20 +169,21 @@ def test_batch_of_pairs_equals_loop(prec):
     stB.close(); st1.close()
 
 
+@pytest.mark.parametrize("nl", [6, 14])       # 14 style layers: the 13..32-layer channel-wise head (tensor cores in the bf16 tier)
 @pytest.mark.parametrize("prec", PRECS)
-def test_time_sharded_windows_equal_unsharded(prec):
+def test_time_sharded_windows_equal_unsharded(prec, nl):
     """Time sharding emulated on one GPU: P window contexts, partial sums added (= the all-reduce),
     owned gradient slices concatenated.  Must agree with the single-context step; on integer data the
     forward at the seams is bit-exact."""
     from audio_style_transfer_b200.sharding import plan_windows
     case = cases.build_inputs("t4096_cfg0")
-    case = dict(case, cont=[5], style=[0, 1, 2, 3, 4, 5], NL=6)
-    case["w"] = synth.make_weights(6, 0, 0.1)
+    case = dict(case, cont=[nl - 1], style=list(range(nl)), NL=nl)
+    case["w"] = synth.make_weights(nl, 0, 0.1)
     Pc, Ps = cases.oracle_targets(case)
     full = make_step(case, prec)
     full.set_targets(Pc[None], Ps[None], case["lambd"])
     lo_f, g_f = full.step(case["x"][None])
-    P = 3
+    P = 3 if nl == 6 else 2
     plan = plan_windows(case["T"], P, case["NL"])
     steps, parts = [], []
     for (wb, we, ob, oe) in plan:
