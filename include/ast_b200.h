@@ -43,7 +43,8 @@ extern "C" {
 
 #define AST_PREC_FP32     0   /* CUDA-core fp32 everywhere: the <=1e-4 tier                           */
 #define AST_PREC_BF16     1   /* tcgen05 bf16 tensor cores, fp32 accumulate in TMEM: the <=1e-2 tier.  */
-                              /* forward operands are 2-term bf16 splits (hi+lo), backward plain bf16 */
+                              /* forward operands are 2-term bf16 splits (hi+lo), backward plain bf16; */
+                              /* channel-wise head with 13..32 style layers: mma.sync TF32 (Gram 3xTF32) */
 
 #define AST_MAX_IDS      32
 #define AST_CHANNELS    128   /* ae_width, model.py:73 */
