@@ -16,7 +16,8 @@ PKG = Path(__file__).resolve().parent
 ROOT = PKG.parent
 SO = PKG / "libast_b200.so"
 SOURCES = ["csrc/api.cu", "csrc/kernels_f32.cu", "csrc/kernels_tc.cu", "csrc/gram_tc.cu", "csrc/stft_reg.cu", "csrc/lbfgs.cu", "csrc/gram_ours_tc.cu"]
-HEADERS = ["csrc/common.cuh", "csrc/tc.cuh", "csrc/ptx.cuh", "csrc/stack_fwd.cuh", "csrc/stack_fwd2.cuh", "csrc/stack_bwd.cuh", "../include/ast_b200.h"]
+HEADERS = ["csrc/common.cuh", "csrc/tc.cuh", "csrc/ptx.cuh", "csrc/stack_fwd.cuh", "csrc/stack_bwd.cuh", "../include/ast_b200.h"]
+SO_EXP = PKG / "libast_b200_exp.so"      # the same sources with -DAST_EXPERIMENTS: timeline stamps, fault injection, A/B switches
 
 AST_PREC_FP32 = 0
 AST_PREC_BF16 = 1
@@ -27,7 +28,7 @@ SYMBOLS = [
     "ast_create", "ast_destroy", "ast_last_error", "ast_version", "ast_workspace_bytes",
     "ast_set_weights", "ast_set_targets", "ast_embeds", "ast_step", "ast_step_graph", "ast_step_host",
     "ast_step_forward", "ast_partials", "ast_step_backward", "ast_get_extract",
-    "ast_launches_per_step", "ast_step_timed",
+    "ast_launches_per_step", "ast_step_timed", "ast_check", "ast_uses_stack_kernels",
     "ast_opt_create", "ast_opt_destroy", "ast_opt_workspace_bytes", "ast_opt_reset", "ast_opt_buffers", "ast_opt_advance",
     "ast_opt_status", "ast_opt_result", "ast_opt_epochs", "ast_opt_log", "ast_minimize",
 ]
@@ -41,7 +42,7 @@ class AstConfig(C.Structure):
         ("gatys", C.c_int32), ("nb_channels", C.c_int32), ("cnt_channels", C.c_int32),
         ("precision", C.c_int32),
         ("total_T", C.c_int64), ("win_begin", C.c_int64), ("own_begin", C.c_int64), ("own_end", C.c_int64),
-        ("device", C.c_int32), ("reserved", C.c_int32),
+        ("device", C.c_int32), ("kernel_path", C.c_int32),
     ]
 
 
@@ -59,44 +60,48 @@ class AstError(RuntimeError):
         self.code = code
 
 
-def nvcc_command(out: Path = SO):
+def nvcc_command(out: Path = SO, experiments: bool = False):
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    return [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-            "-shared", "-Xcompiler", "-fPIC", "-o", str(out)] + [str(PKG / s) for s in SOURCES]
+    return [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "--threads", "0",
+            "-shared", "-Xcompiler", "-fPIC"] + (["-DAST_EXPERIMENTS"] if experiments else []) + \
+           ["-o", str(out)] + [str(PKG / s) for s in SOURCES]
 
 
-def needs_build() -> bool:
-    if not SO.exists():
+def needs_build(so: Path = SO) -> bool:
+    if not so.exists():
         return True
-    t = SO.stat().st_mtime
+    t = so.stat().st_mtime
     return any((PKG / p).resolve().stat().st_mtime > t for p in SOURCES + HEADERS)
 
 
 def build(force: bool = False, verbose: bool = False) -> Path:
-    """Compile every CUDA source for sm_100a into the in-tree libast_b200.so (nvcc cross-compiles
-    without a GPU)."""
-    if force or needs_build():
-        cmd = nvcc_command()
-        if verbose:
-            print(" ".join(cmd), file=sys.stderr)
-        r = subprocess.run(cmd, capture_output=True, text=True)
-        if r.returncode != 0:
-            raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
+    """Compile every CUDA source for sm_100a into the in-tree libast_b200.so (nvcc cross-compiles without a GPU),
+    and the same sources with -DAST_EXPERIMENTS into libast_b200_exp.so (timeline stamps, fault injection and the
+    A/B switches: test / profiling infrastructure, never loaded by the product path)."""
+    for so, exp in ((SO, False), (SO_EXP, True)):
+        if force or needs_build(so):
+            cmd = nvcc_command(so, exp)
+            if verbose:
+                print(" ".join(cmd), file=sys.stderr)
+            r = subprocess.run(cmd, capture_output=True, text=True)
+            if r.returncode != 0:
+                raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
     return SO
 
 
-_lib = None
+_libs = {}
 
 
-def load() -> C.CDLL:
-    """dlopen the in-tree library and declare every prototype of include/ast_b200.h."""
-    global _lib
-    if _lib is not None:
-        return _lib
-    if not SO.exists():
-        raise ImportError(f"{SO} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+def load(experiments: bool = False) -> C.CDLL:
+    """dlopen the in-tree library and declare every prototype of include/ast_b200.h.  experiments=True loads the
+    -DAST_EXPERIMENTS build instead (tests/test_gpu_loud.py, scripts/timeline_stack.py)."""
+    if experiments in _libs:
+        return _libs[experiments]
+    so = SO_EXP if experiments else SO
+    if not so.exists():
+        raise ImportError(f"{so} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
                           "(there is no CPU fallback for the step)")
-    lib = C.CDLL(str(SO))
+    lib = C.CDLL(str(so))
     vp, i32, i64, dbl = C.c_void_p, C.c_int32, C.c_int64, C.c_double
     lib.ast_create.argtypes = [C.POINTER(AstConfig), C.POINTER(vp)]
     lib.ast_destroy.argtypes = [vp]
@@ -116,6 +121,12 @@ def load() -> C.CDLL:
     lib.ast_get_extract.argtypes = [vp, i32, vp, vp]
     lib.ast_launches_per_step.argtypes = [vp]
     lib.ast_step_timed.argtypes = [vp, vp, vp, vp, vp, vp]
+    lib.ast_check.argtypes = [vp, vp]
+    lib.ast_uses_stack_kernels.argtypes = [vp]
+    if experiments:
+        lib.ast_debug_timeline.argtypes = [vp]
+        lib.ast_debug_tl_layer.argtypes = [i32]
+        lib.ast_debug_skip_publish.argtypes = [i32]
     lib.ast_opt_create.argtypes = [C.POINTER(AstOptConfig), C.POINTER(vp)]
     lib.ast_opt_destroy.argtypes = [vp]
     lib.ast_opt_workspace_bytes.argtypes = [vp]
@@ -132,7 +143,7 @@ def load() -> C.CDLL:
         f = getattr(lib, name)
         if f.restype is C.c_int:      # default restype; the int-returning entry points
             f.restype = C.c_int
-    _lib = lib
+    _libs[experiments] = lib
     return lib
 
 

@@ -13,6 +13,17 @@
 thread_local int ast_launch_counter = 0;
 static thread_local char g_err[512] = "";
 
+// A/B switches for profiling exist only in -DAST_EXPERIMENTS builds; the shipped library reads no environment variable.
+static inline bool exp_switch(const char* name) {
+#ifdef AST_EXPERIMENTS
+    const char* v = getenv(name);
+    return v && v[0] == '1';
+#else
+    (void)name;
+    return false;
+#endif
+}
+
 static int fail(int code, const char* fmt, ...) {
     va_list ap;
     va_start(ap, fmt);
@@ -27,8 +38,10 @@ static int fail(int code, const char* fmt, ...) {
             return fail(AST_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
     } while (0)
 
+static unsigned long long g_ctx_generation = 0;      // bumped by ast_create and ast_set_targets (lbfgs.cu graph cache)
 struct ast_ctx {
     ast_config cfg;
+    unsigned long long generation;
     int T, B, R, NL, L, n_cont, prec;
     int own_lo, own_hi;           // window-local owned rows
     int64_t total_T;
@@ -78,7 +91,7 @@ struct ast_ctx {
     const float* gdev_x; float* gdev_losses; float* gdev_grad;
     cudaGraphExec_t gphase[3];                  // ast_step_timed: encoder fwd | gram + heads | backward
     float *d_x, *d_losses, *d_grad;
-    float *p_x, *p_out;            // pinned
+    float *p_x, *p_out;            // pinned; p_out = [B*4 losses | R gradient | 2 hand-off error words]
     int launches_per_step;         // kernels of the last forward + the last backward
     int launches_fwd, launches_bwd;
     bool use_stack;                // whole-stack forward kernel (one launch) instead of one kernel per layer
@@ -112,6 +125,7 @@ static inline uint32_t* zm(const ast_ctx* c, int l) { return c->zmask + (size_t)
 static inline float* dFb(const ast_ctx* c, int i) { return c->dF + (size_t)i * c->R * AST_C; }
 
 extern "C" const char* ast_last_error(void) { return g_err; }
+unsigned long long ast_ctx_generation(const ast_ctx* c) { return c ? c->generation : 0; }
 int ast_set_error(int code, const char* msg) { return fail(code, "%s", msg); }   // lbfgs.cu
 extern "C" const char* ast_version(void) { return "ast_b200 0.1 sm_100a"; }
 extern "C" int64_t ast_workspace_bytes(const ast_ctx* c) { return c ? c->bytes : 0; }
@@ -151,6 +165,7 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
     if (cfg->nb_channels < 1 || cfg->nb_channels > 128) return fail(AST_EINVAL, "nb_channels outside 1..128");
     if (cfg->cnt_channels < 1 || cfg->cnt_channels > 128) return fail(AST_EINVAL, "cnt_channels outside 1..128");
     if (cfg->precision != AST_PREC_FP32 && cfg->precision != AST_PREC_BF16) return fail(AST_EINVAL, "unknown precision %d", cfg->precision);
+    if (cfg->kernel_path < AST_PATH_AUTO || cfg->kernel_path > AST_PATH_PER_LAYER_BWD) return fail(AST_EINVAL, "unknown kernel_path %d", cfg->kernel_path);
 
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
@@ -166,6 +181,7 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
     c->cfg = *cfg;
     c->T = cfg->T; c->B = cfg->B; c->R = cfg->B * cfg->T; c->NL = cfg->n_layers; c->L = cfg->n_style;
     c->n_cont = cfg->n_cont; c->prec = cfg->precision; c->bytes = 0;
+    c->generation = ++g_ctx_generation;
     c->tc = nullptr; c->hstream = nullptr; c->gexec = nullptr; c->p_x = c->p_out = nullptr;
     c->gdev = nullptr; c->gdev_x = nullptr; c->gdev_losses = c->gdev_grad = nullptr;
     for (auto& g : c->gphase) g = nullptr;
@@ -214,8 +230,7 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
     {   // Gram split-K geometry: few enough chunks to keep the partial buffer small, enough to fill the SMs
         int target = cfg->gatys ? 16 : 128;      // ours: 128 chunks x 4 channel quads = 512 CTAs of the latency-bound kernel
         if (!cfg->gatys) target = 64;            // 64 chunks x 4 channel quads = 256 CTAs, all resident at 2 per SM; halves the partials
-        c->gram_ours_tc = !cfg->gatys && cfg->precision == AST_PREC_BF16 && gram_ours_tc_supported(c->L) &&
-                          getenv("AST_B200_GRAM_OURS_CUDA") == nullptr;      // (A/B switch for profiling)
+        c->gram_ours_tc = !cfg->gatys && cfg->precision == AST_PREC_BF16 && gram_ours_tc_supported(c->L) && !exp_switch("AST_B200_GRAM_OURS_CUDA");
         if (c->gram_ours_tc) target = 37;        // one CTA per SM (164 KB of smem): 37 chunks x 4 quads = 148 CTAs, one wave
         target = std::max(2, (target + c->B - 1) / c->B);
         int rows = (c->T + target - 1) / target;
@@ -266,22 +281,21 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
         cudaMemcpy(c->d_Hcptr, hc, sizeof(hc), cudaMemcpyHostToDevice);
     }
     if (cudaMallocHost(&c->p_x, (size_t)c->R * sizeof(float)) != cudaSuccess ||
-        cudaMallocHost(&c->p_out, ((size_t)c->R + 4 * c->B) * sizeof(float)) != cudaSuccess) {
+        cudaMallocHost(&c->p_out, ((size_t)c->R + 4 * c->B + 2) * sizeof(float)) != cudaSuccess) {
         ast_destroy(c); return fail(AST_ECUDA, "cudaMallocHost failed");
     }
     if (cudaStreamCreateWithFlags(&c->hstream, cudaStreamNonBlocking) != cudaSuccess) { ast_destroy(c); return fail(AST_ECUDA, "stream create failed"); }
     for (auto& e : c->ev) if (cudaEventCreate(&e) != cudaSuccess) { ast_destroy(c); return fail(AST_ECUDA, "event create failed"); }
     if (setup_f32_kernels() != 0) { ast_destroy(c); return fail(AST_ECUDA, "cudaFuncSetAttribute failed (is the GPU sm_100?)"); }
-    { const char* e1 = getenv("AST_B200_NO_DOTS"); const char* e2 = getenv("AST_B200_NO_FOLD");
-      c->fuse_dots = !(e1 && e1[0] == '1'); c->fuse_heads = !(e2 && e2[0] == '1'); }
+    c->fuse_dots = !exp_switch("AST_B200_NO_DOTS"); c->fuse_heads = !exp_switch("AST_B200_NO_FOLD");
     if (c->prec == AST_PREC_BF16) {
         const char* why = nullptr;
         c->tc = tc_create(c->T, c->B, c->NL, c->H, c->g, c->dF, c->n_head, cfg->gatys ? c->L : 0, c->gram_part,
                           (int64_t)c->B * c->nmat * c->gram_nchunk, &c->bytes, &why);
         if (!c->tc) { ast_destroy(c); return fail(AST_ECUDA, "tensor-core path setup failed: %s", why ? why : "?"); }
-        const char* no = getenv("AST_B200_NO_STACK");           // A/B switch for profiling: one kernel per layer instead
-        c->use_stack = tc_stack_ok(c->tc) && !(no && no[0] == '1');                      // "1": per-layer kernels both ways
-        c->use_stack_bwd = c->use_stack && !(no && no[0] == '2');                        // "2": whole-stack forward only
+        // cfg->kernel_path: AST_PATH_PER_LAYER = one kernel per layer both ways, AST_PATH_PER_LAYER_BWD = whole-stack forward only
+        c->use_stack = tc_stack_ok(c->tc) && cfg->kernel_path != AST_PATH_PER_LAYER;
+        c->use_stack_bwd = c->use_stack && cfg->kernel_path != AST_PATH_PER_LAYER_BWD;
     }
     if (cudaDeviceSynchronize() != cudaSuccess || cudaGetLastError() != cudaSuccess) { ast_destroy(c); return fail(AST_ECUDA, "context setup failed"); }
     *out = c;
@@ -336,6 +350,7 @@ extern "C" int ast_set_targets(ast_ctx* c, const float* Pc, const float* Ps, dou
     CK(cudaStreamSynchronize(s));
     c->lambd = (float)lambd;
     c->have_t = true;
+    c->generation = ++g_ctx_generation;
     drop_graphs(c);                                                         // loss weights are baked in the graphs
     return AST_OK;
 }
@@ -380,7 +395,7 @@ static int setup_regulariser(ast_ctx* c) {
 // ---- forward --------------------------------------------------------------------------------
 // keep_all: every H[i] is written to global memory (ast_embeds / ast_get_extract); the optimisation step keeps only
 // what its heads read -- the whole-stack kernel holds the residual stream in TMEM.
-static void run_encoder(ast_ctx* c, const float* d_x, cudaStream_t s, bool keep_all) {
+static int run_encoder(ast_ctx* c, const float* d_x, cudaStream_t s, bool keep_all) {
     if (c->tc && c->use_stack) {
         unsigned char keep[33];
         for (int i = 0; i <= c->NL; ++i) keep[i] = keep_all ? 1 : 0;
@@ -388,8 +403,9 @@ static void run_encoder(ast_ctx* c, const float* d_x, cudaStream_t s, bool keep_
         if (!c->cfg.gatys)                      // channel-wise Gram and its gradient read the fp32 extracts
             for (int i = 0; i < c->L; ++i) keep[c->style_layer[i] + 1] = 1;
         memcpy(c->h_kept, keep, sizeof(keep));
-        tc_forward_stack(c->tc, d_x, c->W0, c->b0, c->bd, c->br, c->H, c->zmask, c->hmask, c->f_slot, keep, s);
-        return;
+        if (tc_forward_stack(c->tc, d_x, c->W0, c->b0, c->bd, c->br, c->H, c->zmask, c->hmask, c->f_slot, keep, s) != 0)
+            return fail(AST_ECUDA, "whole-stack forward launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+        return AST_OK;
     }
     memset(c->h_kept, 1, sizeof(c->h_kept));
     launch_startconv_fwd(d_x, c->W0, c->b0, Hl(c, 0), hm(c, 0), c->T, c->R, s);
@@ -408,6 +424,7 @@ static void run_encoder(ast_ctx* c, const float* d_x, cudaStream_t s, bool keep_
         a.T = c->T; a.R = c->R; a.shift = dil(l);
         launch_layer_f32(a, false, s);
     }
+    return AST_OK;
 }
 // fused (single-GPU ast_step*): nothing all-reduces the partials between the two phases, so the heads kernel sums the
 // Gatys split-K chunks and the content partials itself and its last CTA writes the losses (3 launches fewer).
@@ -441,7 +458,8 @@ static int step_forward_impl(ast_ctx* c, const float* d_x, void* stream, bool fu
     if (!c->have_w || !c->have_t) return fail(AST_ESTATE, "ast_set_weights and ast_set_targets must precede a step");
     cudaStream_t s = (cudaStream_t)stream;
     const int before = ast_launch_counter;
-    run_encoder(c, d_x, s, false);
+    const int re = run_encoder(c, d_x, s, false);
+    if (re != AST_OK) return re;
     run_partials(c, d_x, s, fused);
     c->launches_fwd = ast_launch_counter - before;
     c->launches_per_step = c->launches_fwd + c->launches_bwd;
@@ -498,7 +516,7 @@ static int step_backward_impl(ast_ctx* c, float* d_losses, float* d_grad, void* 
         tc_style_grad(c->tc, c->L, hos, s);
     }
     else if (c->cfg.gatys) launch_style_grad_gatys(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
-    else if (c->gram_ours_tc && getenv("AST_B200_SGO_CUDA") == nullptr) launch_style_grad_ours_tc(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
+    else if (c->gram_ours_tc && !exp_switch("AST_B200_SGO_CUDA")) launch_style_grad_ours_tc(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
     else              launch_style_grad_ours(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
     {
         bool init[30];
@@ -520,7 +538,8 @@ static int step_backward_impl(ast_ctx* c, float* d_losses, float* d_grad, void* 
             if (fuse_sg && l >= 1 && c->f_slot[l - 1] >= 0 && !is_cont[l - 1]) { sg_slot[l] = c->f_slot[l - 1]; df_idx[l] = -1; }
         }
         // the start-conv adjoint's channel dots are taken from the final running gradient while it is still in registers
-        tc_backward_stack(c->tc, c->hmask, c->zmask, df_idx, sg_slot, c->L, c->g, c->W0, c->fuse_dots ? c->scratch3R : nullptr, s);
+        if (tc_backward_stack(c->tc, c->hmask, c->zmask, df_idx, sg_slot, c->L, c->g, c->W0, c->fuse_dots ? c->scratch3R : nullptr, s) != 0)
+            return fail(AST_ECUDA, "whole-stack backward launch failed: %s", cudaGetErrorString(cudaGetLastError()));
     }
     int cur = 0;
     for (int l = c->NL; l >= 0 && !(c->tc && c->use_stack_bwd); --l) {
@@ -571,7 +590,8 @@ extern "C" int ast_embeds(ast_ctx* c, const float* d_x, float* d_Ec, float* d_Gn
     if (!c || !d_x) return fail(AST_EINVAL, "null argument");
     if (!c->have_w) return fail(AST_ESTATE, "ast_set_weights must precede ast_embeds");
     cudaStream_t s = (cudaStream_t)stream;
-    run_encoder(c, d_x, s, true);
+    const int re = run_encoder(c, d_x, s, true);
+    if (re != AST_OK) return re;
     if (d_Ec) launch_content_gather(c->d_Hcptr, c->n_cont, c->cfg.cnt_channels, d_Ec, c->R, s);
     if (d_Gn) {
         run_gram(c, s);
@@ -611,6 +631,35 @@ static int capture_graph(ast_ctx* c, cudaGraphExec_t* out, F body) {
     return AST_OK;
 }
 
+// A bounded wait of the whole-stack kernels expired (stack_fwd.cuh: 1 = a neighbour's hand-off flag, 2 = an mbarrier):
+// the results of that evaluation are invalid.  The words stay set (sticky) until ast_check clears them.
+static int stack_fault(ast_ctx* c, unsigned efwd, unsigned ebwd) {
+    (void)c;
+    return fail(AST_ECUDA, "whole-stack kernel hand-off timed out (forward %u, backward %u; 1 = neighbour flag, 2 = mbarrier): "
+                "the results of this evaluation are invalid", efwd, ebwd);
+}
+int ast_stack_fault_words(ast_ctx* c, unsigned* e2) {                 // lbfgs.cu (status read-back of ast_minimize)
+    e2[0] = e2[1] = 0;
+    if (!c || !c->tc) return AST_OK;
+    CK(cudaMemcpy(e2, tc_stack_err(c->tc), 2 * sizeof(unsigned), cudaMemcpyDeviceToHost));
+    return AST_OK;
+}
+extern "C" int ast_check(ast_ctx* c, void* stream) {
+    if (!c) return fail(AST_EINVAL, "null argument");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaStreamSynchronize((cudaStream_t)stream));
+    CK(cudaGetLastError());
+    unsigned e[2];
+    const int r = ast_stack_fault_words(c, e);
+    if (r != AST_OK) return r;
+    if (e[0] | e[1]) {
+        cudaMemset(tc_stack_err(c->tc), 0, 2 * sizeof(unsigned));
+        return stack_fault(c, e[0], e[1]);
+    }
+    return AST_OK;
+}
+extern "C" int ast_uses_stack_kernels(const ast_ctx* c) { return c && c->use_stack ? 1 : 0; }
+
 // the evaluation as SciPy sees it: host float64 in, host float64 out
 extern "C" int ast_step_host(ast_ctx* c, const double* h_x, double* h_losses, double* h_grad) {
     if (!c || !h_x || !h_losses || !h_grad) return fail(AST_EINVAL, "null argument");
@@ -624,13 +673,19 @@ extern "C" int ast_step_host(ast_ctx* c, const double* h_x, double* h_losses, do
             const int rr = ast_step(c, c->d_x, c->d_losses, c->d_grad, s);
             cudaMemcpyAsync(c->p_out, c->d_losses, (size_t)c->B * 4 * sizeof(float), cudaMemcpyDeviceToHost, s);
             cudaMemcpyAsync(c->p_out + 4 * c->B, c->d_grad, (size_t)c->R * sizeof(float), cudaMemcpyDeviceToHost, s);
+            if (c->tc) cudaMemcpyAsync(c->p_out + 4 * c->B + c->R, tc_stack_err(c->tc), 2 * sizeof(unsigned), cudaMemcpyDeviceToHost, s);
             return rr;
         });
         if (r != AST_OK) return r;
     }
     for (int i = 0; i < c->R; ++i) c->p_x[i] = (float)h_x[i];
+    if (c->tc) { c->p_out[4 * c->B + c->R] = 0.f; c->p_out[4 * c->B + c->R + 1] = 0.f; }
     CK(cudaGraphLaunch(c->gexec, c->hstream));
     CK(cudaStreamSynchronize(c->hstream));
+    if (c->tc) {
+        const unsigned* ew = reinterpret_cast<const unsigned*>(c->p_out + 4 * c->B + c->R);
+        if (ew[0] | ew[1]) return stack_fault(c, ew[0], ew[1]);
+    }
     for (int i = 0; i < 4 * c->B; ++i) h_losses[i] = (double)c->p_out[i];
     const float* g = c->p_out + 4 * c->B;
     for (int i = 0; i < c->R; ++i) h_grad[i] = (double)g[i];
@@ -662,7 +717,7 @@ extern "C" int ast_step_timed(ast_ctx* c, const float* d_x, float* d_losses, flo
     cudaStream_t s = (cudaStream_t)stream;
     if (!c->gphase[0]) {
         CK(cudaStreamSynchronize(s));
-        int r = capture_graph(c, &c->gphase[0], [&](cudaStream_t cs) { run_encoder(c, c->d_x, cs, false); return AST_OK; });
+        int r = capture_graph(c, &c->gphase[0], [&](cudaStream_t cs) { return run_encoder(c, c->d_x, cs, false); });
         if (r != AST_OK) return r;
         r = capture_graph(c, &c->gphase[1], [&](cudaStream_t cs) {
             run_partials(c, c->d_x, cs, c->fuse_heads);
@@ -692,19 +747,12 @@ extern "C" int ast_step_timed(ast_ctx* c, const float* d_x, float* d_losses, flo
     return AST_OK;
 }
 
-// profiling aid (scripts/timeline.py): per-CTA clock64() stamps of the forward layer kernel's phases
+#ifdef AST_EXPERIMENTS
+// profiling / fault-injection aids (scripts/timeline_stack.py, tests/test_gpu_loud.py): -DAST_EXPERIMENTS builds only
 void tc_set_timeline(unsigned long long* d_buf);
-extern "C" int ast_debug_timeline(void* d_buf) { tc_set_timeline((unsigned long long*)d_buf); return AST_OK; }
-void tc_set_dbg_skipw(int v);
-// 1 if a bounded spin of the whole-stack kernels expired since the context was created (results are then invalid)
-extern "C" int ast_debug_stack_err(ast_ctx* c) {
-    if (!c || !c->tc) return 0;
-    unsigned e[2] = {0, 0};
-    cudaDeviceSynchronize();
-    cudaMemcpy(e, tc_stack_err(c->tc), sizeof(e), cudaMemcpyDeviceToHost);
-    return (int)(e[0] | e[1]);
-}
-extern "C" int ast_debug_uses_stack(ast_ctx* c) { return c && c->use_stack ? 1 : 0; }
 void tc_set_tl_layer(int l);
+void tc_set_dbg_skip_publish(int v);
+extern "C" int ast_debug_timeline(void* d_buf) { tc_set_timeline((unsigned long long*)d_buf); return AST_OK; }
 extern "C" int ast_debug_tl_layer(int l) { tc_set_tl_layer(l); return AST_OK; }
-extern "C" int ast_debug_skipw(int v) { tc_set_dbg_skipw(v); return AST_OK; }
+extern "C" int ast_debug_skip_publish(int tile_plus_1) { tc_set_dbg_skip_publish(tile_plus_1); return AST_OK; }
+#endif

@@ -973,7 +973,11 @@ int setup_heads_kernel() {
 void launch_heads(const HeadArgs& a, cudaStream_t s) {
     dim3 grid(a.nmat, a.B);
     const size_t smem = a.Ssym ? (size_t)a.n * (a.n + 1) * sizeof(float) : 0;
+#ifdef AST_EXPERIMENTS
     static const bool one_cta = getenv("AST_B200_HEADS_1CTA") != nullptr;    // A/B switch for profiling
+#else
+    const bool one_cta = false;
+#endif
     if (a.n == AST_C && !one_cta) heads_gatys_cluster_kernel<<<dim3(HG_CL * a.nmat, a.B), HG_THREADS, 0, s>>>(a);
     else heads_kernel<<<grid, a.n * a.n >= 4096 ? 1024 : 256, smem, s>>>(a);
     ast_launch_counter += 1;
@@ -1225,7 +1229,11 @@ static bool launch_sgot(const float* const* d_F, float* const* d_dF, const float
 }
 void launch_style_grad_ours(const float* const* d_F, float* const* d_dF, const float* Ssym, int L, int T, int B,
                             cudaStream_t s) {
+#ifdef AST_EXPERIMENTS
     static const bool old_path = getenv("AST_B200_SGO_OLD") != nullptr;      // A/B switch for profiling: per-(channel, layer) kernel
+#else
+    const bool old_path = false;
+#endif
     if (L > GS_MAXL && !old_path && launch_sgot(d_F, d_dF, Ssym, L, T, B, s)) { ast_launch_counter += 1; return; }
     if (L <= GS_MAXL) {
 #define SGOS_CASE(n) case n: launch_sgos<n>(d_F, d_dF, Ssym, T, B, s); break;

@@ -28,15 +28,18 @@
 #define TILE16 16384                            // [128 rows][128 B]: one bf16 K-half or one fp32 32-column group
 static constexpr uint32_t IDESC = umma_idesc_bf16(128, 128);
 
-// optional per-CTA timeline (debug / profiling aid, scripts/timeline.py): slot i of CTA c <- clock64()
+#ifdef AST_EXPERIMENTS
+// optional per-CTA timeline (profiling aid, scripts/timeline_stack.py; -DAST_EXPERIMENTS builds only): slot i of CTA c <- clock64()
 __device__ unsigned long long* g_timeline = nullptr;
 #define TL(i) do { if (g_timeline) g_timeline[(size_t)blockIdx.x * 64 + (i)] = clock64(); } while (0)
 void tc_set_timeline(unsigned long long* d_buf) { cudaMemcpyToSymbol(g_timeline, &d_buf, sizeof(d_buf)); }
-// TIMING EXPERIMENT ONLY (scripts/timeline.py --skipw): the forward producer does not load the conv weight tiles,
-// so results are garbage; tells whether the K=3 GEMM phase is bound by operand bytes or by TMA latency.
-__device__ int g_dbg_skipw = 0;
-void tc_set_dbg_skipw(int v) { cudaMemcpyToSymbol(g_dbg_skipw, &v, sizeof(v)); }
 void tc_set_tl_layer(int l);
+// fault injection for tests/test_gpu_loud.py: tile `g_dbg_skip_publish - 1` never releases its hand-off flags
+__device__ int g_dbg_skip_publish = 0;
+void tc_set_dbg_skip_publish(int v) { cudaMemcpyToSymbol(g_dbg_skip_publish, &v, sizeof(v)); }
+#else
+#define TL(i) do { } while (0)
+#endif
 
 __device__ __forceinline__ bool tap_live(int t0, int k, int shift, int T) {
     const int t = t0 + (k - 1) * shift;
@@ -133,7 +136,6 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_kernel(const __grid_con
         // ================================ TMA producer ========================================
         if (lane == 0) {
             int fills[3] = {0, 0, 0};
-            const bool skipw = g_dbg_skipw != 0;
             int tap_of[6];
             {
                 int n = 0;
@@ -143,11 +145,9 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_kernel(const __grid_con
             auto load_w = [&](int it) {                      // arms the stage and requests its two weight tiles
                 const int slot = it % 3, k = tap_of[it], j = it & 1;
                 const uint32_t st = base + slot * FWD_STAGE, fb = bar + FB_FULL(slot);
-                mbar_expect_tx(fb, (skipw ? 2 : 4) * TILE16);
-                if (!skipw) {
-                    tma_load_2d(st + 2 * TILE16, &p.tmW1, fb, j * 64, p.w1_row + (k * 2 + 0) * 128);
-                    tma_load_2d(st + 3 * TILE16, &p.tmW1, fb, j * 64, p.w1_row + (k * 2 + 1) * 128);
-                }
+                mbar_expect_tx(fb, 4 * TILE16);
+                tma_load_2d(st + 2 * TILE16, &p.tmW1, fb, j * 64, p.w1_row + (k * 2 + 0) * 128);
+                tma_load_2d(st + 3 * TILE16, &p.tmW1, fb, j * 64, p.w1_row + (k * 2 + 1) * 128);
             };
             const int npre = n1 < 3 ? n1 : 3;
             for (int it = 0; it < npre; ++it) load_w(it);
@@ -317,9 +317,10 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_kernel(const __grid_con
 }
 
 #include "stack_fwd.cuh"
-#include "stack_fwd2.cuh"
 #include "stack_bwd.cuh"
+#ifdef AST_EXPERIMENTS
 void tc_set_tl_layer(int l) { cudaMemcpyToSymbol(g_tl_layer, &l, sizeof(l)); }
+#endif
 
 // =============================================================================================
 // backward boundary l (between layer l-1 and layer l), plain bf16 operands
@@ -605,8 +606,9 @@ struct TcState {
     CUtensorMap tm_F, tm_ssym, tm_gpart, tm_dF_st;
     CUtensorMap tm_a_hi, tm_a_lo, tm_dz, tm_H, tm_g, tm_dF;      // box = 128 rows x 128 bytes, loads and stores
     CUtensorMap tm_w1f, tm_w2f, tm_w1b, tm_w2b;
+    CUtensorMap tm_ha_hi[4], tm_ha_lo[4], tm_hz[4];              // halo boxes of 8, 16, 32, 64 rows (whole-stack kernels)
     int cur;                       // dz buffer holding the most recent backward output
-    unsigned* flags;               // [2][R/128] publish counters of the forward / backward stack kernels, then err[2]
+    unsigned* flags;               // [2][R/128][2] publish counters (per tile and K-half) of the forward / backward stack kernels, then err[2]
     int n_sm, coop;                // SM count; cooperative launch supported
 };
 
@@ -665,9 +667,9 @@ TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_he
               cudaMalloc(&s->dz, act) == cudaSuccess && cudaMalloc(&s->w1f, mat * NL * 3 * 2) == cudaSuccess &&
               cudaMalloc(&s->w2f, mat * NL * 2) == cudaSuccess && cudaMalloc(&s->w1b, mat * NL * 3) == cudaSuccess &&
               cudaMalloc(&s->w2b, mat * NL) == cudaSuccess;
-    ok = ok && cudaMalloc(&s->flags, ((size_t)2 * (s->R / 128) + 2) * sizeof(unsigned)) == cudaSuccess;
+    ok = ok && cudaMalloc(&s->flags, ((size_t)4 * (s->R / 128) + 2) * sizeof(unsigned)) == cudaSuccess;
     if (!ok) { *why = "cudaMalloc failed"; tc_destroy(s); return nullptr; }
-    cudaMemset(s->flags, 0, ((size_t)2 * (s->R / 128) + 2) * sizeof(unsigned));
+    cudaMemset(s->flags, 0, ((size_t)4 * (s->R / 128) + 2) * sizeof(unsigned));
     {
         int dev = 0;
         cudaGetDevice(&dev);
@@ -680,6 +682,9 @@ TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_he
          make_act_map(&s->tm_g, g, true, T, B, 1, 128) && make_act_map(&s->tm_dF, dF, true, T, B, n_head > 0 ? n_head : 1, 128) &&
          make_w_map(&s->tm_w1f, s->w1f, (size_t)NL * 3 * 2 * AST_C) && make_w_map(&s->tm_w2f, s->w2f, (size_t)NL * 2 * AST_C) &&
          make_w_map(&s->tm_w1b, s->w1b, (size_t)NL * 3 * AST_C) && make_w_map(&s->tm_w2b, s->w2b, (size_t)NL * AST_C);
+    for (int i = 0; i < 4 && ok; ++i)
+        ok = make_act_map(&s->tm_ha_hi[i], s->a_hi, false, T, B, 2, 8 << i) && make_act_map(&s->tm_ha_lo[i], s->a_lo, false, T, B, 2, 8 << i) &&
+             make_act_map(&s->tm_hz[i], s->dz, false, T, B, 2, 8 << i);
     s->n_fslots = n_fslots;
     if (ok && n_fslots > 0) {
         const size_t fb = (size_t)n_fslots * s->R * AST_C * sizeof(__nv_bfloat16), sb = (size_t)B * n_fslots * mat;
@@ -693,9 +698,8 @@ TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_he
              make_act_map(&s->tm_dF_st, dF, true, T, B, n_head > 0 ? n_head : 1, 32) && setup_gram_tc_kernels() == 0;
     }
     if (!ok) { *why = "cuTensorMapEncodeTiled failed"; tc_destroy(s); return nullptr; }
-    if (cudaFuncSetAttribute(tc_fwd_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FS_SMEM) != cudaSuccess ||
-        cudaFuncSetAttribute(tc_fwd_stack2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FS_SMEM) != cudaSuccess ||
-        cudaFuncSetAttribute(tc_bwd_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BS_SMEM) != cudaSuccess ||
+    if (cudaFuncSetAttribute(tc_fwd_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, F2_SMEM) != cudaSuccess ||
+        cudaFuncSetAttribute(tc_bwd_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, B2_SMEM) != cudaSuccess ||
         cudaFuncSetAttribute(tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM) != cudaSuccess ||
         cudaFuncSetAttribute(tc_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM) != cudaSuccess) {
         *why = "cudaFuncSetAttribute(max dynamic smem) failed";
@@ -755,47 +759,35 @@ static cudaError_t launch_coop(Kern kernel, dim3 grid, dim3 block, size_t smem, 
 }
 // one pair must fit one tile per SM; bigger batches are launched pair group by pair group
 bool tc_stack_ok(const TcState* s) { return s && s->coop && s->T / 128 <= s->n_sm && s->NL <= 32; }
-unsigned* tc_stack_err(TcState* s) { return s->flags + (size_t)2 * (s->R / 128); }
+unsigned* tc_stack_err(TcState* s) { return s->flags + (size_t)4 * (s->R / 128); }
 int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b0, const float* bd, const float* br,
                      float* H, uint32_t* zmask, uint32_t* hmask, const int* f_slot, const unsigned char* export_h,
                      cudaStream_t st) {
     FwdStackArgs a;
     memset(&a, 0, sizeof(a));
     a.tmA_hi = s->tm_a_hi; a.tmA_lo = s->tm_a_lo; a.tmW1 = s->tm_w1f; a.tmW2 = s->tm_w2f;
-    a.tmF = s->n_fslots > 0 ? s->tm_F : s->tm_a_hi;          // never dereferenced without an f_slot
+    for (int i = 0; i < 4; ++i) { a.tmHa_hi[i] = s->tm_ha_hi[i]; a.tmHa_lo[i] = s->tm_ha_lo[i]; }
     a.x = x; a.W0 = W0; a.b0 = b0; a.bd = bd; a.br = br; a.H = H; a.zmask = zmask; a.hmask = hmask;
     a.a_hi = s->a_hi; a.a_lo = s->a_lo; a.F = s->F;
     a.flags = s->flags; a.err = tc_stack_err(s);
     a.T = s->T; a.R = s->R; a.NL = s->NL; a.tiles_per_pair = s->T / 128;
     for (int l = 0; l < 32; ++l) a.f_slot[l] = (signed char)((s->n_fslots > 0 && l < s->NL) ? f_slot[l] : -1);
     for (int i = 0; i <= s->NL; ++i) a.export_h[i] = export_h[i];
-    // 5 ring slots: the extract copy is written straight from registers, so its 32 KB staging tile joins the operand ring
-    // (AST_B200_RING4=1: A/B switch back to 4 slots + staged TMA store of the extract copy)
-    {
-        const char* r4 = getenv("AST_B200_RING4");
-        a.nslot = (r4 && r4[0] == '1') ? 4 : 5;
-    }
-    cudaMemsetAsync(s->flags, 0, (size_t)(s->R / 128) * sizeof(unsigned), st);
-    const int tpp = s->T / 128, ppl = s->n_sm / tpp;         // tiles per pair; pairs per launch (all CTAs co-resident)
-    cudaError_t e = cudaSuccess;
-    int p0 = 0;
-    // two pairs per CTA ("duo", stack_fwd2.cuh) while at least two pairs are left; a last odd pair runs one tile per CTA
-    // (opt-in experiment, see the header of stack_fwd2.cuh: correct but not faster than one launch per pair group)
-    const char* duo = getenv("AST_B200_DUO");
-    if (duo && duo[0] == '1') {
-        for (; p0 + 2 <= s->B && e == cudaSuccess;) {
-            int np = (s->B - p0) & ~1;
-            if (np > 2 * ppl) np = 2 * ppl;
-            a.tile0 = p0 * tpp;
-            e = launch_coop(tc_fwd_stack2_kernel, dim3((np / 2) * tpp), dim3(FWD_THREADS), FS_SMEM, st, a);
-            ast_launch_counter += 1;
-            p0 += np;
+    {   // publish i (relu(h_i)) is consumed by layer i: its dilation decides how many warps release per K-half
+        unsigned acc = 0;
+        for (int i = 0; i < 34; ++i) {
+            if (i < s->NL) acc += (unsigned)stack_npub(stack_dil(i));
+            a.need[i] = (unsigned short)acc;
         }
     }
-    for (; p0 < s->B && e == cudaSuccess; p0 += ppl) {
+    const size_t nt = (size_t)(s->R / 128);
+    cudaMemsetAsync(s->flags, 0, 2 * nt * sizeof(unsigned), st);
+    const int tpp = s->T / 128, ppl = s->n_sm / tpp;         // tiles per pair; pairs per launch (all CTAs co-resident)
+    cudaError_t e = cudaSuccess;
+    for (int p0 = 0; p0 < s->B && e == cudaSuccess; p0 += ppl) {
         const int np = s->B - p0 < ppl ? s->B - p0 : ppl;
         a.tile0 = p0 * tpp;
-        e = launch_coop(tc_fwd_stack_kernel, dim3(np * tpp), dim3(FWD_THREADS), FS_SMEM, st, a);
+        e = launch_coop(tc_fwd_stack_kernel, dim3(np * tpp), dim3(F2_THREADS), F2_SMEM, st, a);
         ast_launch_counter += 1;
     }
     return e == cudaSuccess ? 0 : -1;
@@ -806,23 +798,31 @@ int tc_backward_stack(TcState* s, const uint32_t* hmask, const uint32_t* zmask, 
     BwdStackArgs a;
     memset(&a, 0, sizeof(a));
     a.tmDz = s->tm_dz; a.tmW1 = s->tm_w1b; a.tmW2 = s->tm_w2b; a.tmDF = s->tm_dF;
+    for (int i = 0; i < 4; ++i) a.tmHz[i] = s->tm_hz[i];
     a.tmF = s->n_fslots > 0 ? s->tm_F : s->tm_dz; a.tmS = s->n_fslots > 0 ? s->tm_ssym : s->tm_w2b;   // unused without slots
     a.dz = s->dz; a.g = g; a.hmask = hmask; a.zmask = zmask; a.W0 = W0; a.pdots = pdots;
     const size_t nt = (size_t)(s->R / 128);
-    a.flags = s->flags + nt; a.err = tc_stack_err(s) + 1;
+    a.flags = s->flags + 2 * nt; a.err = tc_stack_err(s) + 1;
     a.T = s->T; a.R = s->R; a.NL = s->NL; a.tiles_per_pair = s->T / 128; a.sg_L = sg_L;
     for (int l = 0; l < 33; ++l) { a.df_idx[l] = -1; a.sg_slot[l] = -1; }
     for (int l = 0; l <= s->NL; ++l) {
         a.sg_slot[l] = (signed char)((s->n_fslots > 0 && df_idx[l] < 0) ? sg_slot[l] : -1);
         a.df_idx[l] = (signed char)df_idx[l];
     }
-    cudaMemsetAsync(s->flags + nt, 0, nt * sizeof(unsigned), st);
+    {   // dz_m is consumed by boundary m; publishes run from m = NL-1 down to 0
+        unsigned acc = 0;
+        for (int m = 32; m >= 0; --m) {
+            if (m < s->NL) acc += (unsigned)stack_npub(stack_dil(m));
+            a.need[m] = (unsigned short)acc;
+        }
+    }
+    cudaMemsetAsync(s->flags + 2 * nt, 0, 2 * nt * sizeof(unsigned), st);
     const int tpp = s->T / 128, ppl = s->n_sm / tpp;
     cudaError_t e = cudaSuccess;
     for (int p0 = 0; p0 < s->B && e == cudaSuccess; p0 += ppl) {
         const int np = s->B - p0 < ppl ? s->B - p0 : ppl;
         a.tile0 = p0 * tpp;
-        e = launch_coop(tc_bwd_stack_kernel, dim3(np * tpp), dim3(FWD_THREADS), BS_SMEM, st, a);
+        e = launch_coop(tc_bwd_stack_kernel, dim3(np * tpp), dim3(F2_THREADS), B2_SMEM, st, a);
         ast_launch_counter += 1;
     }
     return e == cudaSuccess ? 0 : -1;

@@ -262,9 +262,14 @@ __device__ __noinline__ int dcsrch_step(OptState& s, double f, double g) {
 }
 
 // per-phase clock64() stamps of the lead thread (scripts/opt_profile.py --stamps); NULL in normal use
+#ifdef AST_EXPERIMENTS
 __device__ long long* g_opt_stamps = nullptr;
 #define STAMP(n) do { if (lead && g_opt_stamps) g_opt_stamps[n] = clock64(); } while (0)
 #define STAMP_T0(n) do { if (blockIdx.x == 0 && threadIdx.x == 0 && g_opt_stamps) g_opt_stamps[n] = clock64(); } while (0)
+#else
+#define STAMP(n) do { } while (0)
+#define STAMP_T0(n) do { } while (0)
+#endif
 
 // ---- the machine ------------------------------------------------------------------------------------------------
 struct Slice { int lo, hi; };     // this CTA's samples; a thread walks lo + tid, lo + tid + blockDim, ...
@@ -630,6 +635,8 @@ __global__ void lbfgs_reset_kernel(const OptParams P, const double* x0) {
 static thread_local char o_err[256] = "";
 extern "C" const char* ast_last_error(void);
 int ast_set_error(int code, const char* msg);      // api.cu: routes into ast_last_error()
+unsigned long long ast_ctx_generation(const ast_ctx* c);   // api.cu: changes whenever a ctx is (re)created or its targets are re-baked
+extern "C" int ast_check(ast_ctx* c, void* stream);
 
 #define OCK(call)                                                                              \
     do {                                                                                       \
@@ -652,6 +659,7 @@ struct ast_opt {
     cudaEvent_t ev[2];
     cudaGraphExec_t gexec;     // [step, advance] captured for (ctx, this)
     ast_ctx* gctx;
+    unsigned long long gctx_gen;
     cudaStream_t stream;
 };
 
@@ -748,11 +756,13 @@ extern "C" int ast_opt_create(const ast_opt_config* cfg, ast_opt** out) {
     return AST_OK;
 }
 
-// debugging aid: d_buf = 16 int64 on the device (or NULL to switch the stamps off)
+#ifdef AST_EXPERIMENTS
+// profiling aid (scripts/opt_profile.py): d_buf = 16 int64 on the device (or NULL to switch the stamps off)
 extern "C" int ast_opt_debug_stamps(void* d_buf) {
     long long* p = (long long*)d_buf;
     return cudaMemcpyToSymbol(g_opt_stamps, &p, sizeof(p)) == cudaSuccess ? AST_OK : AST_ECUDA;
 }
+#endif
 
 extern "C" int64_t ast_opt_workspace_bytes(const ast_opt* o) { return o ? o->bytes : 0; }
 
@@ -850,7 +860,9 @@ extern "C" int ast_minimize(ast_ctx* ctx, ast_opt* o, int64_t max_evals, int32_t
     if (max_evals <= 0) max_evals = (int64_t)o->cfg.epochs * 15000;
     OCK(cudaSetDevice(o->cfg.device));
     cudaStream_t s = o->stream;
-    if (o->gexec && o->gctx != ctx) { cudaGraphExecDestroy(o->gexec); o->gexec = nullptr; }
+    // the captured [step, advance] graph bakes the context's loss weights and launch parameters: re-capture when the
+    // context is another one OR has been re-created / re-targeted since (same address, different generation)
+    if (o->gexec && (o->gctx != ctx || o->gctx_gen != ast_ctx_generation(ctx))) { cudaGraphExecDestroy(o->gexec); o->gexec = nullptr; }
     if (!o->gexec) {
         cudaGraph_t graph = nullptr;
         OCK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
@@ -863,6 +875,7 @@ extern "C" int ast_minimize(ast_ctx* ctx, ast_opt* o, int64_t max_evals, int32_t
         cudaGraphDestroy(graph);
         if (e2 != cudaSuccess) { o->gexec = nullptr; return ast_set_error(AST_ECUDA, "ast_minimize: graph instantiate failed"); }
         o->gctx = ctx;
+        o->gctx_gen = ast_ctx_generation(ctx);
     }
     int64_t n = 0;
     int slot = 0;
@@ -881,5 +894,5 @@ extern "C" int ast_minimize(ast_ctx* ctx, ast_opt* o, int64_t max_evals, int32_t
     }
     OCK(cudaStreamSynchronize(s));
     if (evals_enqueued) *evals_enqueued = n;
-    return AST_OK;
+    return ast_check(ctx, s);          // a hand-off timeout inside any of the evaluations invalidates the run: AST_ECUDA
 }

@@ -44,11 +44,13 @@ class StyleStep:
     (methods.py:44-77).  `window=(total_T, win_begin, own_begin, own_end)` makes this context one
     time shard of a longer clip (multi-GPU)."""
 
+    KERNEL_PATHS = {"auto": 0, "per_layer": 1, "per_layer_bwd": 2}
+
     def __init__(self, T, cont_ids, style_ids, gatys=False, nb_channels=128, cnt_channels=128, B=1,
-                 precision="bf16", device=None, window=None):
+                 precision="bf16", device=None, window=None, kernel_path="auto", experiments=False):
         if not torch.cuda.is_available():
             raise RuntimeError("no CUDA device: the B200 step has no CPU fallback")
-        self.lib = _lib.load()
+        self.lib = _lib.load(experiments)
         self.device = torch.cuda.current_device() if device is None else int(device)
         self.dev = torch.device("cuda", self.device)
         self.T, self.B = int(T), int(B)
@@ -72,6 +74,7 @@ class StyleStep:
         if window is not None:
             cfg.total_T, cfg.win_begin, cfg.own_begin, cfg.own_end = [int(v) for v in window]
         cfg.device = self.device
+        cfg.kernel_path = self.KERNEL_PATHS[kernel_path]
         self._h = C.c_void_p()
         _lib.check(self.lib.ast_create(C.byref(cfg), C.byref(self._h)))
         self.ec_cols = len(self.cont_ids) * self.cnt_channels
@@ -201,16 +204,13 @@ class StyleStep:
     @property
     def uses_stack_kernels(self) -> bool:
         """True when the encoder forward / backward run as ONE cooperative kernel each (clip fits one tile per SM)."""
-        f = self.lib.ast_debug_uses_stack
-        f.argtypes = [C.c_void_p]
-        return bool(f(self._h))
+        return bool(self.lib.ast_uses_stack_kernels(self._h))
 
-    @property
-    def stack_error(self) -> bool:
-        """True if a bounded spin of the whole-stack kernels ever expired in this context (results invalid)."""
-        f = self.lib.ast_debug_stack_err
-        f.argtypes = [C.c_void_p]
-        return bool(f(self._h))
+    def check(self):
+        """ast_check: synchronise the current stream; raises AstError if a hand-off wait of the whole-stack kernels
+        expired in any evaluation since the last check (those results are invalid) or CUDA reported an error."""
+        with torch.cuda.device(self.dev):
+            _lib.check(self.lib.ast_check(self._h, _stream()))
 
     @property
     def launches_per_step(self) -> int:

@@ -41,10 +41,19 @@ extern "C" {
 #define AST_EUNSUPPORTED -3   /* valid in the reference but outside this path (reserved)   */
 #define AST_ESTATE       -4   /* call order violated (weights/targets not set)          */
 
-#define AST_PREC_FP32     0   /* CUDA-core fp32 everywhere: the <=1e-4 tier                           */
+#define AST_PREC_FP32     0   /* CUDA-core fp32 everywhere.  Gradient vs fp64: <= 1e-4 up to ~20 layers; at 26..30   */
+                              /* layers it sits at the fp32 floor of this network (an fp32 CPU run of the same step  */
+                              /* is 6e-5 .. 5e-4 from fp64: ReLU sign flips), DESIGN.md "accuracy tiers"             */
 #define AST_PREC_BF16     1   /* tcgen05 bf16 tensor cores, fp32 accumulate in TMEM: the <=1e-2 tier.  */
                               /* forward operands are 2-term bf16 splits (hi+lo), backward plain bf16; */
                               /* channel-wise head with 13..32 style layers: mma.sync TF32 (Gram 3xTF32) */
+
+/* ast_config.kernel_path (tensor-core tier): AUTO = one cooperative whole-stack kernel per direction when a pair has at
+ * most one 128-row tile per SM, else one kernel per layer.  The other two force the per-layer kernels (parity tests
+ * compare the paths; they compute the same step). */
+#define AST_PATH_AUTO          0
+#define AST_PATH_PER_LAYER     1   /* one kernel per layer, forward and backward                  */
+#define AST_PATH_PER_LAYER_BWD 2   /* whole-stack forward, one kernel per layer in the backward   */
 
 #define AST_MAX_IDS      32
 #define AST_CHANNELS    128   /* ae_width, model.py:73 */
@@ -73,7 +82,7 @@ typedef struct ast_config {
     int64_t own_begin;
     int64_t own_end;
     int32_t device;                  /* CUDA device ordinal                                              */
-    int32_t reserved;
+    int32_t kernel_path;             /* AST_PATH_* (0 = auto)                                            */
 } ast_config;
 
 /* GatysNet.__init__/build (methods.py:20-77): allocate workspaces for a fixed (T, B, layer set). */
@@ -128,6 +137,15 @@ int  ast_step_backward(ast_ctx* ctx, float* d_losses, float* d_grad, void* strea
  * are: the whole-stack kernels keep the residual stream on chip (TMEM) and write the content extracts (and, for the
  * channel-wise Gram, the style extracts) only; any other layer returns AST_ESTATE ("not retained"). */
 int  ast_get_extract(ast_ctx* ctx, int32_t layer, float* d_out, void* stream);
+
+/* Asynchronous error check.  ast_step / ast_step_graph / ast_step_forward / ast_step_backward only enqueue work; the
+ * whole-stack kernels hand rows between SMs through flags with BOUNDED waits, and a wait that expires (profiler, debugger,
+ * heavy preemption) invalidates that evaluation.  ast_check synchronises `stream` and returns AST_ECUDA (sticky until this
+ * call, which clears it) if any evaluation since the last check timed out, or if CUDA reported an error.
+ * ast_step_host and ast_minimize run the same check themselves before they return. */
+int  ast_check(ast_ctx* ctx, void* stream);
+/* 1 if the context runs the cooperative whole-stack kernels (one launch per direction), 0 if one kernel per layer. */
+int  ast_uses_stack_kernels(const ast_ctx* ctx);
 
 /* Number of kernels one ast_step launches (for bench.py's gpu_launches). */
 int  ast_launches_per_step(const ast_ctx* ctx);

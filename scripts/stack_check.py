@@ -1,10 +1,8 @@
-"""GPU bring-up of the whole-stack forward kernel: same context config with and without AST_B200_NO_STACK.
+"""GPU bring-up of the whole-stack kernels: same context config through the per-layer kernels (kernel_path) and the stack kernels.
 
     python scripts/stack_check.py [T] [NL] [gatys 0/1] [B]
 Run under `timeout`: a protocol bug in a persistent kernel shows up as a hang.
 """
-import ctypes as C
-import os
 import sys
 import time
 
@@ -23,7 +21,7 @@ T = int(sys.argv[1]) if len(sys.argv) > 1 else 2048
 NL = int(sys.argv[2]) if len(sys.argv) > 2 else 12
 gatys = bool(int(sys.argv[3])) if len(sys.argv) > 3 else True
 B = int(sys.argv[4]) if len(sys.argv) > 4 else 1
-REF_MODE = sys.argv[5] if len(sys.argv) > 5 else "1"      # "1": per-layer kernels; "2": stack forward + per-layer backward
+REF_MODE = sys.argv[5] if len(sys.argv) > 5 else "per_layer"      # or "per_layer_bwd": stack forward + per-layer backward
 w = synth.make_weights(NL, 0, 0.1)
 torch.manual_seed(0)
 x = torch.randn(B, T, device='cuda') * 40
@@ -31,20 +29,24 @@ cont, style = [NL - 1], list(range(NL)) if gatys else list(range(min(NL, 10)))
 
 
 def make(no_stack):
-    os.environ["AST_B200_NO_STACK"] = REF_MODE if no_stack else "0"
-    st = StyleStep(T, cont, style, gatys, precision='bf16', B=B)
+    st = StyleStep(T, cont, style, gatys, precision='bf16', B=B, kernel_path=REF_MODE if no_stack else "auto")
     st.set_weights(w)
     return st
 
 
+def chk(st, what):
+    try:
+        st.check()
+        print(f'check after {what}: ok', flush=True)
+    except Exception as e:  # noqa: BLE001
+        print(f'check after {what}: {e}', flush=True)
+
+
 ref, tc = make(True), make(False)
-ref.lib.ast_debug_uses_stack.argtypes = [C.c_void_p]
-ref.lib.ast_debug_stack_err.argtypes = [C.c_void_p]
-print('uses_stack ref/new:', ref.lib.ast_debug_uses_stack(ref._h), tc.lib.ast_debug_uses_stack(tc._h), flush=True)
+print('uses_stack ref/new:', ref.uses_stack_kernels, tc.uses_stack_kernels, flush=True)
 Ec_r, Gn_r = ref.embeds(x)
 Ec_t, Gn_t = tc.embeds(x)
-torch.cuda.synchronize()
-print('stack_err after embeds:', tc.lib.ast_debug_stack_err(tc._h), flush=True)
+chk(tc, 'embeds')
 for l in range(-1, NL):
     a, b = tc.extract(l), ref.extract(l)
     print(f"layer {l:2d}: rel {rel(a, b):.3e}  max|ref| {float(b.abs().max()):.3g} nan={bool(torch.isnan(a).any())}")
@@ -53,10 +55,9 @@ for st in (ref, tc):
     st.set_targets(Ec_r * 0.9, Gn_r.roll(1, 1), 100.0)
 lo_r, g_r = ref.step(x)
 lo_t, g_t = tc.step(x)
-torch.cuda.synchronize()
+chk(tc, 'step')
 print('losses ref', lo_r.tolist(), 'new', lo_t.tolist())
 print('grad rel', rel(g_t, g_r), 'launches ref/new', ref.launches_per_step, tc.launches_per_step)
-print('stack_err after step:', tc.lib.ast_debug_stack_err(tc._h), flush=True)
 lo = torch.empty(B, 4, device='cuda')
 g = torch.empty(B, T, device='cuda')
 for name, st in (('per-layer', ref), ('stack', tc)):
@@ -69,4 +70,5 @@ for name, st in (('per-layer', ref), ('stack', tc)):
     torch.cuda.synchronize()
     print(f'{name:10s} ms/step {(time.time() - t0) / 50 * 1e3:.4f}  phases {st.step_timed(x, lo, g)}', flush=True)
 lo2, g2 = tc.step(x)
-print('graph replay equals eager:', bool(torch.equal(g2, g)), 'stack_err', tc.lib.ast_debug_stack_err(tc._h))
+print('graph replay equals eager:', bool(torch.equal(g2, g)))
+chk(tc, 'graph replays')

@@ -18,13 +18,13 @@ layer = int(sys.argv[1]) if len(sys.argv) > 1 else 12
 gatys = bool(int(sys.argv[2])) if len(sys.argv) > 2 else True
 T, NL = 16384, 30
 NT = T // 128
-st = StyleStep(T, [NL - 1], list(range(NL)) if gatys else list(range(9, 29, 2)), gatys, precision='bf16')
+st = StyleStep(T, [NL - 1], list(range(NL)) if gatys else list(range(9, 29, 2)), gatys, precision='bf16', experiments=True)
 st.set_weights(synth.make_weights(NL, 0, 0.0))
 x = torch.randn(1, T, device='cuda') * 40
 Ec, Gn = st.embeds(x)
 st.set_targets(Ec * 0.9, Gn.roll(1, 1), 100.0)
 buf = torch.zeros(4 * NT * 64, dtype=torch.int64, device='cuda')
-lib = _lib.load()
+lib = _lib.load(experiments=True)
 for _ in range(3):
     st.step(x)
 torch.cuda.synchronize()
@@ -46,12 +46,11 @@ for cta in (0, 64):
     for l in range(NL):
         print(f'   l{l:2d} d={1 << (l % 10):3d}  acc1 {acc1[l]:8d}  fin {fin[l]:8d}  period {fin[l] - prev:6d}  (gemm1 wait {acc1[l] - prev:6d})')
         prev = fin[l]
-names = {0: 'P: layer start', 1: 'P: centre W issued', 2: 'P: all flags ok', 3: 'P: tap0 issued', 4: 'P: (unused)',
-         5: 'P: tap2 issued', 6: 'P: W2 issued', 8: 'M: ACT ready', 9: 'M: centre j0 go', 10: 'M: centre j1 go',
-         11: 'M: tap0 j0 go', 12: 'M: tap0 j1 go', 13: 'M: tap2 j0 go', 14: 'M: tap2 j1 go', 15: 'M: acc1 commit issued',
-         16: 'M: gemm2 j0 go', 17: 'M: gemm2 j1 go', 18: 'M: acc2 commit issued', 30: 'E: acc1 complete',
-         32: 'E: epi1 done', 33: 'E: acc2 complete', 35: "E: h' staged (smem+TMEM)", 36: 'E: staged+fenced',
-         37: 'E: published, flag, ACT arrive', 41: 'E: layer done'}
+names = {0: 'P: layer start', 2: 'P: far flags ok', 6: 'P: W2 issued', 8: 'M: ACT(0) ready', 9: 'M: ACT(1) ready',
+         10: 'M: HALO(0) landed', 11: 'M: HALO(1) landed / far tap0 j0', 12: 'M: far tap0 j1', 13: 'M: far tap2 j0', 14: 'M: far tap2 j1',
+         15: 'M: acc1 commit issued', 16: 'M: gemm2 j0 go', 17: 'M: gemm2 j1 go', 18: 'M: acc2 commit issued',
+         20: 'H: flags(0) ok', 21: 'H: flags(1) ok', 30: 'E: acc1 complete', 32: 'E: epi1 done', 33: 'E: acc2 complete',
+         36: 'E: published j0, ACT(0) arrive', 37: 'E: published j1, ACT(1) arrive', 41: 'E: layer done'}
 for cta in (5, 64, 100):
     ev = de[cta]
     t0 = min(ev[k] for k in names if ev[k])
@@ -65,12 +64,11 @@ for cta in (64,):
     done = bco[cta, 1:NL + 1]                 # stamp at boundary l = publish of dz_{l-1} done
     print(f'--- CTA {cta}: boundary period (cycles), boundaries {NL}..1')
     print('   ', [int(done[l - 1] - done[l]) for l in range(NL - 1, 0, -1)])
-bnames = {0: 'P: boundary start', 1: 'P: IO issued', 2: 'P: centre W issued', 3: 'P: all flags ok', 4: 'P: dz tiles issued',
-          5: 'P: flags ok tap2', 6: 'P: tap2 issued', 8: 'P: W2 issued (+anti)', 10: 'M: DZ ready', 11: 'M: centre j0 go',
-          12: 'M: centre j1 go', 13: 'M: tap0 j0 go', 14: 'M: tap0 j1 go', 15: 'M: tap2 j0 go', 16: 'M: tap2 j1 go',
-          17: 'M: acc1 commit issued', 18: 'M: gemm2 j0 go', 19: 'M: gemm2 j1 go', 20: 'M: acc2 commit issued',
-          30: 'E: acc1 complete', 31: 'E: IO landed', 32: 'E: epi1 done', 33: 'E: acc2 complete', 34: 'E: dz staged',
-          35: 'E: published, flag, DZ arrive'}
+bnames = {0: 'P: boundary start', 3: 'P: far flags ok', 8: 'P: W2 issued', 10: 'M: DZ(0) ready', 11: 'M: DZ(1) ready',
+          12: 'M: HALO(0) landed', 13: 'M: HALO(1) landed', 14: 'M: far tap0 j0', 15: 'M: far tap0 j1', 16: 'M: far tap2 j0',
+          17: 'M: far tap2 j1', 18: 'M: acc1 commit issued', 19: 'M: gemm2 j0 go', 20: 'M: gemm2 j1 go', 21: 'M: acc2 commit issued',
+          24: 'H: flags(0) ok', 25: 'H: flags(1) ok', 30: 'E: acc1 complete', 31: 'E: IO landed', 32: 'E: epi1 done',
+          33: 'E: acc2 complete', 34: 'E: published j0, DZ(0) arrive', 35: 'E: published j1, DZ(1) arrive'}
 for cta in (64, 100):
     ev = bde[cta]
     t0 = min(ev[k] for k in bnames if ev[k])
