@@ -147,6 +147,7 @@ def load(experiments: bool = False) -> C.CDLL:
     return lib
 
 
-def check(code: int):
+def check(code: int, lib=None):
+    """Raise AstError with the message of the library that returned `code` (the message is thread-local per .so)."""
     if code != 0:
-        raise AstError(code, load().ast_last_error().decode())
+        raise AstError(code, (lib or load()).ast_last_error().decode())

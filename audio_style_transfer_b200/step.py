@@ -76,7 +76,7 @@ class StyleStep:
         cfg.device = self.device
         cfg.kernel_path = self.KERNEL_PATHS[kernel_path]
         self._h = C.c_void_p()
-        _lib.check(self.lib.ast_create(C.byref(cfg), C.byref(self._h)))
+        _lib.check(self.lib.ast_create(C.byref(cfg), C.byref(self._h)), self.lib)
         self.ec_cols = len(self.cont_ids) * self.cnt_channels
         if self.gatys:
             self.gn_shape = (self.B, self.L, 128, 128)
@@ -103,14 +103,14 @@ class StyleStep:
         arrs = [f(w.W0), f(w.b0), f(w.Wd[:self.n_layers]), f(w.bd[:self.n_layers]),
                 f(w.Wr[:self.n_layers]), f(w.br[:self.n_layers])]
         with torch.cuda.device(self.dev):
-            _lib.check(self.lib.ast_set_weights(self._h, *[_ptr(a) for a in arrs], _stream()))
+            _lib.check(self.lib.ast_set_weights(self._h, *[_ptr(a) for a in arrs], _stream()), self.lib)
 
     def set_targets(self, Pc, Ps, lambd, gamma=0.0):
         """define_loss (methods.py:113-125): bake targets and loss weights."""
         Pc = self._as_f32(Pc, (self.B, self.T, self.ec_cols))
         Ps = self._as_f32(Ps, self.gn_shape)
         with torch.cuda.device(self.dev):
-            _lib.check(self.lib.ast_set_targets(self._h, _ptr(Pc), _ptr(Ps), float(lambd), float(gamma), _stream()))
+            _lib.check(self.lib.ast_set_targets(self._h, _ptr(Pc), _ptr(Ps), float(lambd), float(gamma), _stream()), self.lib)
 
     def _as_f32(self, a, shape):
         if isinstance(a, torch.Tensor):
@@ -134,7 +134,7 @@ class StyleStep:
         with torch.cuda.device(self.dev):
             Ec = torch.empty((self.B, self.T, self.ec_cols), dtype=torch.float32, device=self.dev) if content else None
             Gn = torch.empty(self.gn_shape, dtype=torch.float32, device=self.dev) if style else None
-            _lib.check(self.lib.ast_embeds(self._h, _ptr(x), _ptr(Ec), _ptr(Gn), _stream()))
+            _lib.check(self.lib.ast_embeds(self._h, _ptr(x), _ptr(Ec), _ptr(Gn), _stream()), self.lib)
         return Ec, Gn
 
     # -- the step -------------------------------------------------------------------------------
@@ -146,21 +146,21 @@ class StyleStep:
                 losses = torch.empty((self.B, 4), dtype=torch.float32, device=self.dev)
             if grad is None:
                 grad = torch.empty((self.B, self.T), dtype=torch.float32, device=self.dev)
-            _lib.check(self.lib.ast_step(self._h, _ptr(x), _ptr(losses), _ptr(grad), _stream()))
+            _lib.check(self.lib.ast_step(self._h, _ptr(x), _ptr(losses), _ptr(grad), _stream()), self.lib)
         return losses, grad
 
     def step_graph(self, x, losses, grad):
         """The same evaluation replayed from the library's captured CUDA graph (fixed device buffers)."""
         assert x.is_cuda and x.dtype == torch.float32 and x.is_contiguous()
         with torch.cuda.device(self.dev):
-            _lib.check(self.lib.ast_step_graph(self._h, _ptr(x), _ptr(losses), _ptr(grad), _stream()))
+            _lib.check(self.lib.ast_step_graph(self._h, _ptr(x), _ptr(losses), _ptr(grad), _stream()), self.lib)
         return losses, grad
 
     def step_timed(self, x, losses, grad):
         """One step with CUDA events between phases; returns ms (encoder fwd, bwd, gram+heads, total)."""
         ms = (C.c_float * 4)()
         with torch.cuda.device(self.dev):
-            _lib.check(self.lib.ast_step_timed(self._h, _ptr(x), _ptr(losses), _ptr(grad), _stream(), ms))
+            _lib.check(self.lib.ast_step_timed(self._h, _ptr(x), _ptr(losses), _ptr(grad), _stream(), ms), self.lib)
         return list(ms)
 
     def step_host(self, x64: np.ndarray):
@@ -170,19 +170,19 @@ class StyleStep:
         assert x64.size == self.B * self.T
         losses = np.empty((self.B, 4), np.float64)
         grad = np.empty((self.B, self.T), np.float64)
-        _lib.check(self.lib.ast_step_host(self._h, _ptr(x64), _ptr(losses), _ptr(grad)))
+        _lib.check(self.lib.ast_step_host(self._h, _ptr(x64), _ptr(losses), _ptr(grad)), self.lib)
         return losses, grad
 
     # -- two-phase step for time sharding -------------------------------------------------------
     def forward_partial(self, x):
         x = self._x(x)
         with torch.cuda.device(self.dev):
-            _lib.check(self.lib.ast_step_forward(self._h, _ptr(x), _stream()))
+            _lib.check(self.lib.ast_step_forward(self._h, _ptr(x), _stream()), self.lib)
 
     def partials(self) -> torch.Tensor:
         """Zero-copy torch view of the raw Gram + content-SSE partial sums (all-reduce this)."""
         p, n = C.c_void_p(), C.c_int64()
-        _lib.check(self.lib.ast_partials(self._h, C.byref(p), C.byref(n)))
+        _lib.check(self.lib.ast_partials(self._h, C.byref(p), C.byref(n)), self.lib)
         return torch.as_tensor(_DevMem(p.value, n.value), device=self.dev)
 
     def backward(self, losses=None, grad=None):
@@ -191,14 +191,14 @@ class StyleStep:
                 losses = torch.empty((self.B, 4), dtype=torch.float32, device=self.dev)
             if grad is None:
                 grad = torch.empty((self.B, self.T), dtype=torch.float32, device=self.dev)
-            _lib.check(self.lib.ast_step_backward(self._h, _ptr(losses), _ptr(grad), _stream()))
+            _lib.check(self.lib.ast_step_backward(self._h, _ptr(losses), _ptr(grad), _stream()), self.lib)
         return losses, grad
 
     def extract(self, layer: int) -> torch.Tensor:
         """cfg.extracts[layer] of the last forward (model.py:116); layer -1 = start-conv output."""
         out = torch.empty((self.B, self.T, 128), dtype=torch.float32, device=self.dev)
         with torch.cuda.device(self.dev):
-            _lib.check(self.lib.ast_get_extract(self._h, int(layer), _ptr(out), _stream()))
+            _lib.check(self.lib.ast_get_extract(self._h, int(layer), _ptr(out), _stream()), self.lib)
         return out
 
     @property
@@ -210,7 +210,7 @@ class StyleStep:
         """ast_check: synchronise the current stream; raises AstError if a hand-off wait of the whole-stack kernels
         expired in any evaluation since the last check (those results are invalid) or CUDA reported an error."""
         with torch.cuda.device(self.dev):
-            _lib.check(self.lib.ast_check(self._h, _stream()))
+            _lib.check(self.lib.ast_check(self._h, _stream()), self.lib)
 
     @property
     def launches_per_step(self) -> int:
@@ -242,9 +242,9 @@ class DeviceLBFGS:
         cfg.maxls, cfg.max_log, cfg.keep_epoch_x, cfg.device = int(maxls), self.max_log, int(self.keep_epoch_x), self.device
         cfg.factr, cfg.pgtol = float(factr), float(pgtol)
         self._h = C.c_void_p()
-        _lib.check(self.lib.ast_opt_create(C.byref(cfg), C.byref(self._h)))
+        _lib.check(self.lib.ast_opt_create(C.byref(cfg), C.byref(self._h)), self.lib)
         px, pl, pg = C.c_void_p(), C.c_void_p(), C.c_void_p()
-        _lib.check(self.lib.ast_opt_buffers(self._h, C.byref(px), C.byref(pl), C.byref(pg)))
+        _lib.check(self.lib.ast_opt_buffers(self._h, C.byref(px), C.byref(pl), C.byref(pg)), self.lib)
         view = lambda p, n, shape: torch.as_tensor(_DevMem(p.value, n), device=self.dev).view(shape)
         self.x = view(px, self.B * self.T, (self.B, self.T))
         self.losses = view(pl, self.B * 4, (self.B, 4))
@@ -265,19 +265,19 @@ class DeviceLBFGS:
         x0 = np.ascontiguousarray(x0, dtype=np.float64)
         assert x0.size == self.B * self.T
         with torch.cuda.device(self.dev):
-            _lib.check(self.lib.ast_opt_reset(self._h, _ptr(x0), _stream()))
+            _lib.check(self.lib.ast_opt_reset(self._h, _ptr(x0), _stream()), self.lib)
             torch.cuda.current_stream().synchronize()       # x0 is pageable host memory
 
     def advance(self):
         with torch.cuda.device(self.dev):
-            _lib.check(self.lib.ast_opt_advance(self._h, _stream()))
+            _lib.check(self.lib.ast_opt_advance(self._h, _stream()), self.lib)
 
     def status(self):
         """(int32 [B,8], float64 [B]): see ast_opt_status in include/ast_b200.h."""
         st = np.zeros((self.B, 8), np.int32)
         f = np.zeros(self.B, np.float64)
         with torch.cuda.device(self.dev):
-            _lib.check(self.lib.ast_opt_status(self._h, _ptr(st), _ptr(f), _stream()))
+            _lib.check(self.lib.ast_opt_status(self._h, _ptr(st), _ptr(f), _stream()), self.lib)
         return st, f
 
     @property
@@ -287,7 +287,7 @@ class DeviceLBFGS:
     def result(self):
         out = np.empty((self.B, self.T), np.float64)
         with torch.cuda.device(self.dev):
-            _lib.check(self.lib.ast_opt_result(self._h, _ptr(out), _stream()))
+            _lib.check(self.lib.ast_opt_result(self._h, _ptr(out), _stream()), self.lib)
         return out
 
     def epochs_info(self):
@@ -296,14 +296,14 @@ class DeviceLBFGS:
         end = np.zeros((self.B, self.epochs), np.int32)
         xs = np.zeros((self.B, self.epochs, self.T), np.float32) if self.keep_epoch_x else None
         with torch.cuda.device(self.dev):
-            _lib.check(self.lib.ast_opt_epochs(self._h, _ptr(nfev), _ptr(end), _ptr(xs), _stream()))
+            _lib.check(self.lib.ast_opt_epochs(self._h, _ptr(nfev), _ptr(end), _ptr(xs), _stream()), self.lib)
         return nfev, end, xs
 
     def log(self):
         out = np.zeros((self.B, max(self.max_log, 1), 4), np.float32)
         if self.max_log:
             with torch.cuda.device(self.dev):
-                _lib.check(self.lib.ast_opt_log(self._h, _ptr(out), _stream()))
+                _lib.check(self.lib.ast_opt_log(self._h, _ptr(out), _stream()), self.lib)
         return out[:, :self.max_log]
 
     def minimize(self, step: "StyleStep", max_evals=0, chunk=4) -> int:
@@ -312,5 +312,5 @@ class DeviceLBFGS:
         n = C.c_int64()
         with torch.cuda.device(self.dev):
             torch.cuda.current_stream().synchronize()
-            _lib.check(self.lib.ast_minimize(step._h, self._h, int(max_evals), int(chunk), C.byref(n)))
+            _lib.check(self.lib.ast_minimize(step._h, self._h, int(max_evals), int(chunk), C.byref(n)), self.lib)
         return int(n.value)

@@ -33,10 +33,10 @@ def grad_tol(prec, floor):
     return max(TOL[prec]["grad"], (10.0 if prec == "fp32" else 100.0) * floor)
 
 
-def make_step(case, prec, B=1, window=None, T=None):
+def make_step(case, prec, B=1, window=None, T=None, kernel_path="auto"):
     from audio_style_transfer_b200.step import StyleStep
     st = StyleStep(T or case["T"], case["cont"], case["style"], case["gatys"], case["nb"], case["cnt"], B=B,
-                   precision=prec, window=window)
+                   precision=prec, window=window, kernel_path=kernel_path)
     st.set_weights(case["w"])
     return st
 
@@ -226,17 +226,17 @@ def test_errors_are_loud():
 
 
 # ---- whole-stack kernels (one cooperative launch per direction) ---------------------------------------
-def _step_with_env(case, Pc, Ps, mode, monkeypatch):
-    """mode "0": whole-stack kernels (default); "1": one kernel per layer; "2": stack forward + per-layer backward."""
-    monkeypatch.setenv("AST_B200_NO_STACK", mode)
-    st = make_step(case, "bf16")
+def _step_with_path(case, Pc, Ps, mode):
+    """mode "auto": whole-stack kernels; "per_layer": one kernel per layer; "per_layer_bwd": stack forward + per-layer
+    backward (ast_config.kernel_path)."""
+    st = make_step(case, "bf16", kernel_path=mode)
     st.set_targets(Pc[None], Ps[None], case["lambd"])
     lo, g = st.step(case["x"][None])
     return st, lo.cpu().numpy()[0], g.cpu().numpy()[0]
 
 
 @pytest.mark.parametrize("name", ["t4096_cfg0", "t4096_cfg1", "t16384_cfg1"])
-def test_stack_kernels_agree_with_per_layer_path(name, monkeypatch):
+def test_stack_kernels_agree_with_per_layer_path(name):
     """The persistent whole-stack kernels and the per-layer kernels compute the same step.  The forward differs only in
     the order the three taps are accumulated (fp32): features agree to ~1e-5.  Gradients of the bf16 tier move by a few
     1e-3 under ANY reordering of the fp32 accumulation (bf16 rounding flips cascade through the masked backward; CPU
@@ -244,10 +244,10 @@ def test_stack_kernels_agree_with_per_layer_path(name, monkeypatch):
     case = cases.build_inputs(name)
     Pc, Ps = cases.oracle_targets(case)
     losses, dx = cases.oracle_step(case, Pc, Ps)
-    st_s, lo_s, g_s = _step_with_env(case, Pc, Ps, "0", monkeypatch)
-    st_l, lo_l, g_l = _step_with_env(case, Pc, Ps, "1", monkeypatch)
+    st_s, lo_s, g_s = _step_with_path(case, Pc, Ps, "auto")
+    st_l, lo_l, g_l = _step_with_path(case, Pc, Ps, "per_layer")
     assert st_s.uses_stack_kernels and not st_l.uses_stack_kernels
-    assert not st_s.stack_error
+    st_s.check()
     assert st_s.launches_per_step < st_l.launches_per_step
     last = case["NL"] - 1
     if last in [min(i, 29) for i in case["cont"]]:                 # retained by both paths
@@ -256,8 +256,8 @@ def test_stack_kernels_agree_with_per_layer_path(name, monkeypatch):
     tol = TOL["bf16"]["grad"]
     assert rel(g_s, dx) <= tol and rel(g_l, dx) <= tol
     assert rel(g_s, g_l) <= tol
-    # identical forward (mode "2"): the two backward implementations alone
-    st_m, lo_m, g_m = _step_with_env(case, Pc, Ps, "2", monkeypatch)
+    # identical forward (mode "per_layer_bwd"): the two backward implementations alone
+    st_m, lo_m, g_m = _step_with_path(case, Pc, Ps, "per_layer_bwd")
     assert np.array_equal(lo_m, lo_s)
     assert rel(g_s, g_m) <= tol
     for st in (st_s, st_l, st_m):
@@ -278,7 +278,7 @@ def test_stack_step_is_reproducible_and_graph_equals_eager():
         st.step_graph(x, lo, g)
         torch.cuda.synchronize()
         assert torch.equal(g, g0) and torch.equal(lo, lo0)       # flag hand-off leaves no run-to-run variation
-    assert not st.stack_error
+    st.check()
     st.close()
 
 
