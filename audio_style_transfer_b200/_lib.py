@@ -28,7 +28,7 @@ SYMBOLS = [
     "ast_create", "ast_destroy", "ast_last_error", "ast_version", "ast_workspace_bytes",
     "ast_set_weights", "ast_set_targets", "ast_embeds", "ast_step", "ast_step_graph", "ast_step_host",
     "ast_step_forward", "ast_partials", "ast_step_backward", "ast_get_extract",
-    "ast_launches_per_step", "ast_step_timed", "ast_check", "ast_uses_stack_kernels",
+    "ast_launches_per_step", "ast_step_timed", "ast_check", "ast_uses_stack_kernels", "ast_stft_reg_noalloc",
     "ast_opt_create", "ast_opt_destroy", "ast_opt_workspace_bytes", "ast_opt_reset", "ast_opt_buffers", "ast_opt_advance",
     "ast_opt_status", "ast_opt_result", "ast_opt_epochs", "ast_opt_log", "ast_minimize",
 ]
@@ -122,6 +122,7 @@ def load(experiments: bool = False) -> C.CDLL:
     lib.ast_launches_per_step.argtypes = [vp]
     lib.ast_step_timed.argtypes = [vp, vp, vp, vp, vp, vp]
     lib.ast_check.argtypes = [vp, vp]
+    lib.ast_stft_reg_noalloc.argtypes = [vp, i32, vp, vp, vp]
     lib.ast_uses_stack_kernels.argtypes = [vp]
     if experiments:
         lib.ast_debug_timeline.argtypes = [vp]

@@ -165,3 +165,101 @@ void launch_stft_l1_grad(const float* dadx, const float2* tw, const signed char*
     stft_l1_grad_kernel<<<dim3(T / 128, B), 128, 0, s>>>(dadx, tw, sgn, T, win_begin, f_lo, nf, coef, grad);
     ast_launch_counter += 1;
 }
+
+// =====================================================================================================================
+// ast_stft_reg_noalloc -- the gamma term (value and gradient) of ONE clip with NO allocation of any kind.
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  The scratch that launch_stft_l1_fwd /
+// launch_stft_l1_grad take from the context's workspace (twiddles, sign(Re)/sign(Im) per bin, d a / d x per sample,
+// per-CTA partials) lives here in ONE file-scope device array of fixed size: every GPU that loads the library holds
+// these 404 KB until exit.  All calls on a device share the array, it keeps the last call's contents (nothing in it
+// has to start at zero: every word a call reads is written by that call first; the caller's d_grad IS cleared here
+// because the adjoint kernel accumulates), and two calls that overlap on the GPU race -- serialise them on one stream.
+// =====================================================================================================================
+#include "../../include/ast_b200.h"
+#include <cstdio>
+#include <mutex>
+#include <vector>
+
+int ast_set_error(int code, const char* msg);          // api.cu: routes into ast_last_error()
+
+#define NA_MAX_T AST_NOALLOC_MAX_T                                      // 65536 samples
+#define NA_MAX_NF (NA_MAX_T / REG_HOP)                                   // 128 >= 1 + (T - 1024) / 512 frames
+#define NA_OFF_TW 0                                                      // float2[1024]
+#define NA_OFF_DADX (NA_OFF_TW + REG_FRAME * 8)                          // float[NA_MAX_T]
+#define NA_OFF_FPART (NA_OFF_DADX + NA_MAX_T * 4)                        // float[NA_MAX_NF * REG_BCHUNK]
+#define NA_OFF_RAW (NA_OFF_FPART + NA_MAX_NF * REG_BCHUNK * 4)           // float[1] (padded to 256 B)
+#define NA_OFF_SGN (NA_OFF_RAW + 256)                                    // int8[NA_MAX_NF * 513 * 2]
+#define NA_BYTES (((NA_OFF_SGN + NA_MAX_NF * REG_BINS * 2) + 255) / 256 * 256)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NA_BYTES];
+
+// In host code `g_noalloc_scratch` is a host-side stand-in, not a device address: the device address is asked for once
+// per device (with that device current) and remembered here.
+#define NA_MAX_DEVICES 64
+static unsigned char* g_na_ptr[NA_MAX_DEVICES] = {nullptr};
+static std::mutex g_na_mutex;
+
+__global__ void stft_l1_finish_kernel(const float* __restrict__ raw, double scale, float* __restrict__ reg) {
+    reg[0] = (float)(scale * (double)raw[0]);                            // as losses_final_kernel forms losses[3]
+}
+
+static int noalloc_setup(int dev, cudaStream_t s, unsigned char** out) {
+    std::lock_guard<std::mutex> lock(g_na_mutex);
+    if (g_na_ptr[dev]) { *out = g_na_ptr[dev]; return AST_OK; }
+    // one-time, synchronous: not allowed while the caller's stream is being captured
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &cs) != cudaSuccess) return ast_set_error(AST_ECUDA, "ast_stft_reg_noalloc: cudaStreamIsCapturing failed");
+    if (cs != cudaStreamCaptureStatusNone)
+        return ast_set_error(AST_ESTATE, "ast_stft_reg_noalloc: the first call on a device sets up its scratch (one synchronous 8 KB "
+                                         "copy) and must be made outside stream capture");
+    unsigned char* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess || !ptr) return ast_set_error(AST_ECUDA, "ast_stft_reg_noalloc: cudaGetSymbolAddress(scratch) failed");
+    // the twiddle table of setup_regulariser (api.cu): exact at the quadrant points
+    float2 tw[REG_FRAME];
+    for (int j = 0; j < REG_FRAME; ++j) {
+        const int q = j & 255, quad = j >> 8;
+        const double ang = 2.0 * 3.14159265358979323846 * q / 1024.0;
+        const double cq = cos(ang), sq = q ? sin(ang) : 0.0;
+        double cj, sj;
+        switch (quad) { case 0: cj = cq; sj = sq; break; case 1: cj = -sq; sj = cq; break;
+                        case 2: cj = -cq; sj = -sq; break; default: cj = sq; sj = -cq; }
+        tw[j] = make_float2((float)cj, (float)sj);
+    }
+    if (cudaMemcpy(ptr + NA_OFF_TW, tw, sizeof(tw), cudaMemcpyHostToDevice) != cudaSuccess)
+        return ast_set_error(AST_ECUDA, "ast_stft_reg_noalloc: copying the twiddle table failed");
+    g_na_ptr[dev] = ptr;
+    *out = ptr;
+    return AST_OK;
+}
+
+extern "C" int ast_stft_reg_noalloc(const float* d_x, int32_t T, float* d_reg, float* d_grad, void* stream) {
+    if (!d_x || !d_reg || !d_grad) return ast_set_error(AST_EINVAL, "ast_stft_reg_noalloc: null argument");
+    if (T < REG_FRAME || T % 128 != 0) return ast_set_error(AST_EINVAL, "ast_stft_reg_noalloc: T must be a multiple of 128 and at least 1024 (one STFT frame)");
+    if (T > NA_MAX_T) {
+        char msg[160];
+        snprintf(msg, sizeof(msg), "ast_stft_reg_noalloc: T = %d exceeds AST_NOALLOC_MAX_T = %d (the fixed scratch array); use "
+                 "ast_set_targets(gamma) + ast_step for longer clips", (int)T, (int)NA_MAX_T);
+        return ast_set_error(AST_EINVAL, msg);
+    }
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= NA_MAX_DEVICES) return ast_set_error(AST_ECUDA, "ast_stft_reg_noalloc: no current CUDA device");
+    cudaStream_t s = (cudaStream_t)stream;
+    unsigned char* p = nullptr;
+    const int r = noalloc_setup(dev, s, &p);
+    if (r != AST_OK) return r;
+    const float2* tw = reinterpret_cast<const float2*>(p + NA_OFF_TW);
+    float* dadx = reinterpret_cast<float*>(p + NA_OFF_DADX);
+    float* fpart = reinterpret_cast<float*>(p + NA_OFF_FPART);
+    float* raw = reinterpret_cast<float*>(p + NA_OFF_RAW);
+    signed char* sgn = reinterpret_cast<signed char*>(p + NA_OFF_SGN);
+    const int nf = 1 + (T - REG_FRAME) / REG_HOP;                        // methods.py:122: no end padding
+    const double scale = 1.0 / ((double)nf * (double)REG_BINS);
+    if (cudaMemsetAsync(d_grad, 0, (size_t)T * sizeof(float), s) != cudaSuccess) return ast_set_error(AST_ECUDA, "ast_stft_reg_noalloc: cudaMemsetAsync failed");
+    launch_stft_l1_fwd(d_x, tw, T, 1, 0, 0, nf, 0, nf, sgn, fpart, dadx, raw, s);
+    stft_l1_finish_kernel<<<1, 1, 0, s>>>(raw, scale, d_reg);
+    ast_launch_counter += 1;
+    launch_stft_l1_grad(dadx, tw, sgn, T, 1, 0, 0, nf, (float)scale, d_grad, s);
+    if (cudaGetLastError() != cudaSuccess) return ast_set_error(AST_ECUDA, "ast_stft_reg_noalloc: kernel launch failed");
+    return AST_OK;
+}

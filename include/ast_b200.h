@@ -156,6 +156,20 @@ int  ast_launches_per_step(const ast_ctx* ctx);
 int  ast_step_timed(ast_ctx* ctx, const float* d_x, float* d_losses, float* d_grad, void* stream,
                     float* ms_out);
 
+/* The gamma term alone -- reg = mean(abs(Re) + abs(Im)) of STFT(inv_mu_law(x), 1024, 512) and d reg / d x -- for ONE clip,
+ * with NO allocation of any kind.  This entry point has no counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid it).  It calls no cudaMalloc / cudaFree / allocating library routine: the scratch the context-based
+ * path keeps in its workspace lives in one file-scope device array of 404 KB that every GPU loading the library holds
+ * until exit, which is why T is limited to AST_NOALLOC_MAX_T samples (larger -> AST_EINVAL; T % 128 == 0, T >= 1024).
+ * d_x [T], d_grad [T] (overwritten), d_reg [1] are device pointers on the CURRENT device; asynchronous on `stream`.
+ * The same numbers come out of ast_set_targets(gamma != 0) + ast_step as losses[3] and (grad(gamma) - grad(0)) / gamma.
+ * All calls on a device share the scratch: calls that overlap on the GPU (different streams) race -- serialise them.
+ * The first call on a device does a one-time synchronous set-up (8 KB table) and must be outside stream capture
+ * (AST_ESTATE otherwise); every later call only enqueues one memset and four kernels and is capturable. */
+#define AST_NOALLOC_MAX_T 65536
+int  ast_stft_reg_noalloc(const float* d_x, int32_t T, float* d_reg, float* d_grad, void* stream);
+
 /* ---- the optimiser around the step, resident on the device ---------------------------------
  * Reference: `tf.contrib.opt.ScipyOptimizerInterface(loss, method='L-BFGS-B', options={'maxiter': 100})`
  * (methods.py:133-137), run once per epoch from the variable's current value, stopping after an epoch with fewer than
