@@ -606,9 +606,10 @@ struct TcState {
     CUtensorMap tm_F, tm_ssym, tm_gpart, tm_dF_st;
     CUtensorMap tm_a_hi, tm_a_lo, tm_dz, tm_H, tm_g, tm_dF;      // box = 128 rows x 128 bytes, loads and stores
     CUtensorMap tm_w1f, tm_w2f, tm_w1b, tm_w2b;
-    CUtensorMap tm_ha_hi[4], tm_ha_lo[4], tm_hz[4];              // halo boxes of 8, 16, 32, 64 rows (whole-stack kernels)
+    uint4 *ll_f, *ll_b;            // near hand-off lines of the whole-stack kernels (stack_fwd.cuh / stack_bwd.cuh)
     int cur;                       // dz buffer holding the most recent backward output
-    unsigned* flags;               // [2][R/128][2] publish counters (per tile and K-half) of the forward / backward stack kernels, then err[2]
+    unsigned* flags;               // [2][R/128][2] publish counters (per tile and K-half) of the forward / backward stack
+                                   // kernels, then err[2], then {epoch, CTAs done} of the forward and of the backward kernel
     int n_sm, coop;                // SM count; cooperative launch supported
 };
 
@@ -667,9 +668,16 @@ TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_he
               cudaMalloc(&s->dz, act) == cudaSuccess && cudaMalloc(&s->w1f, mat * NL * 3 * 2) == cudaSuccess &&
               cudaMalloc(&s->w2f, mat * NL * 2) == cudaSuccess && cudaMalloc(&s->w1b, mat * NL * 3) == cudaSuccess &&
               cudaMalloc(&s->w2b, mat * NL) == cudaSuccess;
-    ok = ok && cudaMalloc(&s->flags, ((size_t)4 * (s->R / 128) + 2) * sizeof(unsigned)) == cudaSuccess;
+    ok = ok && cudaMalloc(&s->flags, ((size_t)4 * (s->R / 128) + 6) * sizeof(unsigned)) == cudaSuccess;
     if (!ok) { *why = "cudaMalloc failed"; tc_destroy(s); return nullptr; }
-    cudaMemset(s->flags, 0, ((size_t)4 * (s->R / 128) + 2) * sizeof(unsigned));
+    cudaMemset(s->flags, 0, ((size_t)4 * (s->R / 128) + 6) * sizeof(unsigned));
+    {   // LL lines: [2 ping-pong][tiles][2 sides][2 K-halves][4 cc]([2 parts])[4][32 rows] x 16 B; tag 0 never validates
+        const size_t nt_ = (size_t)(s->R / 128);
+        const size_t lf = nt_ * 2 * 2 * 2 * LL_ROWS * 8 * 4 * sizeof(uint4), lb = lf / 2;
+        if (cudaMalloc(&s->ll_f, lf) != cudaSuccess || cudaMalloc(&s->ll_b, lb) != cudaSuccess) { *why = "cudaMalloc failed"; tc_destroy(s); return nullptr; }
+        cudaMemset(s->ll_f, 0, lf); cudaMemset(s->ll_b, 0, lb);
+        *bytes += (int64_t)(lf + lb);
+    }
     {
         int dev = 0;
         cudaGetDevice(&dev);
@@ -682,9 +690,6 @@ TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_he
          make_act_map(&s->tm_g, g, true, T, B, 1, 128) && make_act_map(&s->tm_dF, dF, true, T, B, n_head > 0 ? n_head : 1, 128) &&
          make_w_map(&s->tm_w1f, s->w1f, (size_t)NL * 3 * 2 * AST_C) && make_w_map(&s->tm_w2f, s->w2f, (size_t)NL * 2 * AST_C) &&
          make_w_map(&s->tm_w1b, s->w1b, (size_t)NL * 3 * AST_C) && make_w_map(&s->tm_w2b, s->w2b, (size_t)NL * AST_C);
-    for (int i = 0; i < 4 && ok; ++i)
-        ok = make_act_map(&s->tm_ha_hi[i], s->a_hi, false, T, B, 2, 8 << i) && make_act_map(&s->tm_ha_lo[i], s->a_lo, false, T, B, 2, 8 << i) &&
-             make_act_map(&s->tm_hz[i], s->dz, false, T, B, 2, 8 << i);
     s->n_fslots = n_fslots;
     if (ok && n_fslots > 0) {
         const size_t fb = (size_t)n_fslots * s->R * AST_C * sizeof(__nv_bfloat16), sb = (size_t)B * n_fslots * mat;
@@ -713,7 +718,7 @@ void tc_destroy(TcState* s) {
     if (!s) return;
     cudaFree(s->a_hi); cudaFree(s->a_lo); cudaFree(s->dz);
     cudaFree(s->w1f); cudaFree(s->w2f); cudaFree(s->w1b); cudaFree(s->w2b);
-    cudaFree(s->F); cudaFree(s->ssym); cudaFree(s->flags);
+    cudaFree(s->F); cudaFree(s->ssym); cudaFree(s->flags); cudaFree(s->ll_f); cudaFree(s->ll_b);
     delete s;
 }
 
@@ -766,11 +771,10 @@ int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b
     FwdStackArgs a;
     memset(&a, 0, sizeof(a));
     a.tmA_hi = s->tm_a_hi; a.tmA_lo = s->tm_a_lo; a.tmW1 = s->tm_w1f; a.tmW2 = s->tm_w2f;
-    for (int i = 0; i < 4; ++i) { a.tmHa_hi[i] = s->tm_ha_hi[i]; a.tmHa_lo[i] = s->tm_ha_lo[i]; }
     a.x = x; a.W0 = W0; a.b0 = b0; a.bd = bd; a.br = br; a.H = H; a.zmask = zmask; a.hmask = hmask;
     a.a_hi = s->a_hi; a.a_lo = s->a_lo; a.F = s->F;
-    a.flags = s->flags; a.err = tc_stack_err(s);
-    a.T = s->T; a.R = s->R; a.NL = s->NL; a.tiles_per_pair = s->T / 128;
+    a.flags = s->flags; a.err = tc_stack_err(s); a.epoch = tc_stack_err(s) + 2; a.ll = s->ll_f;
+    a.T = s->T; a.R = s->R; a.NL = s->NL; a.tiles_per_pair = s->T / 128; a.ntiles = s->R / 128;
     for (int l = 0; l < 32; ++l) a.f_slot[l] = (signed char)((s->n_fslots > 0 && l < s->NL) ? f_slot[l] : -1);
     for (int i = 0; i <= s->NL; ++i) a.export_h[i] = export_h[i];
     {   // publish i (relu(h_i)) is consumed by layer i: its dilation decides how many warps release per K-half
@@ -798,12 +802,11 @@ int tc_backward_stack(TcState* s, const uint32_t* hmask, const uint32_t* zmask, 
     BwdStackArgs a;
     memset(&a, 0, sizeof(a));
     a.tmDz = s->tm_dz; a.tmW1 = s->tm_w1b; a.tmW2 = s->tm_w2b; a.tmDF = s->tm_dF;
-    for (int i = 0; i < 4; ++i) a.tmHz[i] = s->tm_hz[i];
     a.tmF = s->n_fslots > 0 ? s->tm_F : s->tm_dz; a.tmS = s->n_fslots > 0 ? s->tm_ssym : s->tm_w2b;   // unused without slots
     a.dz = s->dz; a.g = g; a.hmask = hmask; a.zmask = zmask; a.W0 = W0; a.pdots = pdots;
     const size_t nt = (size_t)(s->R / 128);
-    a.flags = s->flags + 2 * nt; a.err = tc_stack_err(s) + 1;
-    a.T = s->T; a.R = s->R; a.NL = s->NL; a.tiles_per_pair = s->T / 128; a.sg_L = sg_L;
+    a.flags = s->flags + 2 * nt; a.err = tc_stack_err(s) + 1; a.epoch = tc_stack_err(s) + 4; a.ll = s->ll_b;
+    a.T = s->T; a.R = s->R; a.NL = s->NL; a.tiles_per_pair = s->T / 128; a.ntiles = s->R / 128; a.sg_L = sg_L;
     for (int l = 0; l < 33; ++l) { a.df_idx[l] = -1; a.sg_slot[l] = -1; }
     for (int l = 0; l <= s->NL; ++l) {
         a.sg_slot[l] = (signed char)((s->n_fslots > 0 && df_idx[l] < 0) ? sg_slot[l] : -1);

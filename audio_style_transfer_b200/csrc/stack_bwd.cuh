@@ -5,19 +5,19 @@
 // CTA i owns time tile i for all boundaries:
 //   * the fp32 running gradient g lives in TMEM (128 columns) and is updated in place by the epilogue; it leaves the
 //     SM once, after boundary 0, as the start-conv adjoint's channel dots (or as g itself);
-//   * dz (bf16) is kept as a 256-row operand window per K-half: rows [64, 192) the own tile, the halo rows the d
-//     boundary rows of the neighbours.  Near boundaries (d <= 64): the three taps of the transposed conv are UMMA
-//     descriptors into the window at row offsets 64+d, 64, 64-d; tiles publish only their first / last d rows.
-//     Far boundaries: whole tiles are published and streamed through the ring;
+//   * dz (bf16) is kept as a 192-row operand window per K-half: rows [32, 160) the own tile, the halo rows the d
+//     boundary rows of the neighbours.  Near boundaries (d <= 32): the three taps of the transposed conv are UMMA
+//     descriptors into the window at row offsets 32+d, 32, 32-d; tiles hand over only their first / last d rows as
+//     tagged LL lines that the epilogue warps of the neighbour poll and import (no fence, no flag: stack_fwd.cuh).
+//     Far boundaries: whole tiles are published (full-line copies + ONE release per K-half) and streamed through the ring;
 //   * bf16(g') (A operand of the 1x1^T GEMM) overlays the window centre: dead before the next dz tile is staged;
 //   * head gradients (fp32 dF tile, or the bf16 F / Ssym operands of the fused style gradient) do not depend on the
 //     sweep: prefetched into their own 64 KB region one boundary ahead;
-//   * weights (and far-tap tiles) stream through a 6 x 16 KB ring.
+//   * weights (and far-tap tiles) stream through a 7 x 16 KB ring.
 #pragma once
 
 struct alignas(64) BwdStackArgs {
     CUtensorMap tmDz;                // bf16 dz ping-pong [2][B][T][128], box {64,128,1,1}: far taps
-    CUtensorMap tmHz[4];             // same buffer, box {64, 8<<i, 1, 1}: halo rows of the near boundaries
     CUtensorMap tmW1, tmW2;          // backward weight operand rows (tc_weights_bwd_kernel), box {64,128}
     CUtensorMap tmDF;                // fp32 head gradients [n_head][B][T][128], box {32,128,1,1}
     CUtensorMap tmF, tmS;            // fused style gradient operands: bf16 F [L][B][T][128], bf16 Ssym rows
@@ -25,18 +25,20 @@ struct alignas(64) BwdStackArgs {
     float* g;                        // [R][128]: receives the final running gradient (input of the start-conv adjoint) ...
     const float* W0; float* pdots;   // ... unless pdots != NULL: then p_k[t] = sum_c W0[k,0,c] g[t,c] goes to pdots[k][R] instead
     const uint32_t* hmask; const uint32_t* zmask;        // [NL+1][R][4], [NL][R][4]
+    uint4* ll;                       // near hand-off lines [2][ntiles][2 sides][2 K-halves][4 cc][4][32 rows] x 16 B
     unsigned* flags; unsigned* err;  // [ntiles][2]
-    int T, R, NL, tiles_per_pair, sg_L;
+    unsigned* epoch;                 // [0] launch epoch (tags), [1] CTAs done (see stack_fwd.cuh)
+    int T, R, NL, tiles_per_pair, ntiles, sg_L;
     int tile0;                       // global index of this launch's first tile (launches cover whole pairs)
     unsigned short need[33];         // need[m]: flag value once dz_m (consumed by boundary m) has been published
     signed char df_idx[33];          // per boundary l: dF buffer added there, or -1
     signed char sg_slot[33];         // per boundary l: style slot whose F . Ssym is added there, or -1
 };
 
-#define B2_WBUF 32768                             // one K-half window buffer: [256 rows][128 B] bf16 dz
+#define B2_WBUF F2_WBUF                           // one K-half window buffer: [192 rows][128 B] bf16 dz
 #define B2_IO (2 * B2_WBUF)                       // 64 KB: fp32 dF tile (4 column groups) or F (2) + Ssym (2) bf16 tiles
 #define B2_RING (B2_IO + 65536)
-#define B2_NSLOT 6
+#define B2_NSLOT 7
 #define B2_BAR (B2_RING + B2_NSLOT * TILE16)
 #define B2_SMEM (B2_BAR + 1024 + 1024)
 #define B2B_FULL(i) (8u * (i))
@@ -61,8 +63,6 @@ struct alignas(64) BwdStackArgs {
 #define TLB(i) do { } while (0)
 #define TLC() do { } while (0)
 #endif
-// far-tap test of the anti-dependency (see the halo producer): taps of layer m reach beyond the adjacent tiles or wrap
-__device__ __forceinline__ bool bs_anti_needed(int m) { const int e = m % 10; return e == 8 || e == 9 || e == 0; }
 
 __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __grid_constant__ BwdStackArgs p) {
     extern __shared__ uint8_t tc_smem_raw[];
@@ -75,19 +75,29 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
     const int row0 = tile * 128;
     const int b = row0 / p.T, t0 = row0 - b * p.T;
     const int NL = p.NL;
+    const uint32_t epoch = *reinterpret_cast<const volatile unsigned*>(p.epoch);
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&p.tmDz); tma_prefetch_desc(&p.tmW1); tma_prefetch_desc(&p.tmW2); tma_prefetch_desc(&p.tmDF);
         tma_prefetch_desc(&p.tmF); tma_prefetch_desc(&p.tmS);
-        for (int i = 0; i < 4; ++i) tma_prefetch_desc(&p.tmHz[i]);
         for (int i = 0; i < B2_NSLOT; ++i) { mbar_init(bar + B2B_FULL(i), 1); mbar_init(bar + B2B_EMPTY(i), 1); }
-        for (int j = 0; j < 2; ++j) { mbar_init(bar + B2B_DZ(j), 16); mbar_init(bar + B2B_HALO(j), 1); mbar_init(bar + B2B_RT(j), 16); }
+        for (int j = 0; j < 2; ++j) { mbar_init(bar + B2B_DZ(j), 16); mbar_init(bar + B2B_HALO(j), 16); mbar_init(bar + B2B_RT(j), 16); }
         mbar_init(bar + B2B_ACC1, 1); mbar_init(bar + B2B_ACC2, 1);
         mbar_init(bar + B2B_IOFULL, 1); mbar_init(bar + B2B_IOFREE, 16); mbar_init(bar + B2B_ANTI, 1);
         *ab = 0u;
         mbar_init_fence();
     }
     if (warp == 1) tmem_alloc<512>(bar + B2B_TMEM);
+    if (warp >= 2) {
+        // halo rows of the dz window start as zeros and stay zero where the pair ends (the transposed conv's padding)
+        const int e = (warp - 2) * 32 + lane;
+        for (int i = e; i < 2 * 2 * F2_HALO * 8; i += 512) {
+            const int buf = i / (2 * F2_HALO * 8), rem = i % (2 * F2_HALO * 8), hr = rem >> 3, ch = rem & 7;
+            const int wr = hr < F2_HALO ? hr : 128 + hr;
+            *reinterpret_cast<uint4*>(gen + buf * B2_WBUF + wr * 128 + ch * 16) = make_uint4(0u, 0u, 0u, 0u);
+        }
+        fence_proxy_async_smem();
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -130,27 +140,27 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
                         const uint32_t slot = acquire();
                         tma_load_2d(s_ring + slot * TILE16, &p.tmW1, bar + B2B_FULL(slot), j * 64, w1row + k * 128);
                     };
+                    load_w1(1, 0);                            // centre tap, both K-halves: the dz tile is resident
+                    load_w1(1, 1);
                     if (stack_near(d)) {
-                        for (int j = 0; j < 2; ++j) { load_w1(1, j); load_w1(0, j); load_w1(2, j); }
+                        for (int j = 0; j < 2; ++j) { load_w1(0, j); load_w1(2, j); }
                     } else {
-                        load_w1(1, 0);                        // centre tap: the dz tile is resident
-                        load_w1(1, 1);
+                        // all weight tiles of this boundary's transposed conv (at most 6 of the 7 slots, none of them waits for a
+                        // neighbour), ONE poll of the neighbour flags, then the tap tiles
                         const bool live0 = tap_live(t0, 0, -d, p.T), live2 = tap_live(t0, 2, -d, p.T);
-                        bool polled = false;
-                        for (int k = 0; k < 3; k += 2) {
-                            if (!(k == 0 ? live0 : live2)) continue;
-                            const int t = t0 - (k - 1) * d;
-                            for (int j = 0; j < 2; ++j) {
-                                load_w1(k, j);
-                                if (!polled) {
-                                    stack_wait_rows2(p.flags, p.tiles_per_pair, p.T, b, live0 ? t0 + d : t0 - d, live2 ? t0 - d : t0 + d,
-                                                     p.need[l], ab, p.err);
-                                    fence_proxy_async_all();
-                                    polled = true;
-                                    TLB(3);
+                        if (live0) { load_w1(0, 0); load_w1(0, 1); }
+                        if (live2) { load_w1(2, 0); load_w1(2, 1); }
+                        if (live0 || live2) {
+                            stack_wait_rows2(p.flags, p.tiles_per_pair, p.T, b, live0 ? t0 + d : t0 - d, live2 ? t0 - d : t0 + d,
+                                             p.need[l], ab, p.err);
+                            fence_proxy_async_all();
+                            TLB(3);
+                            for (int k = 0; k < 3; k += 2) {
+                                if (!(k == 0 ? live0 : live2)) continue;
+                                for (int j = 0; j < 2; ++j) {
+                                    const uint32_t slot = acquire();
+                                    tma_load_4d(s_ring + slot * TILE16, &p.tmDz, bar + B2B_FULL(slot), j * 64, t0 - (k - 1) * d, b, (NL - l) & 1);
                                 }
-                                const uint32_t slot = acquire();
-                                tma_load_4d(s_ring + slot * TILE16, &p.tmDz, bar + B2B_FULL(slot), j * 64, t, b, (NL - l) & 1);
                             }
                         }
                     }
@@ -161,6 +171,13 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
                         tma_load_2d(s_ring + slot * TILE16, &p.tmW2, bar + B2B_FULL(slot), j * 64, (l - 1) * AST_C);
                     }
                     TLB(8);
+                    // Anti-dependency of a FAR publish of dz_{l-1} (whole tile -> the ping-pong buffer that holds dz_{l+1} if that
+                    // was far too): the tiles whose +-d_{l+1} taps read this tile are done once they have published dz_l.
+                    if (l + 1 < NL && !stack_near(stack_dil(l - 1)) && !stack_near(stack_dil(l + 1))) {
+                        const int dp = stack_dil(l + 1);
+                        stack_wait_rows2(p.flags, p.tiles_per_pair, p.T, b, t0 - dp, t0 + dp, p.need[l], ab, p.err);
+                        mbar_arrive(bar + B2B_ANTI);
+                    }
                 }
             }
         }
@@ -184,21 +201,23 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
                 const int d = stack_dil(l);
                 const int df = p.df_idx[l], sg = p.sg_slot[l];
                 if (g1) {
+                    for (int j = 0; j < 2; ++j) {             // centre tap, both K-halves
+                        stack_mbar_wait(bar + B2B_DZ(j), dz_n & 1u, ab, p.err);          // own dz_l, K-half j, staged
+                        tc_fence_after();
+                        TLB(10 + j);
+                        const uint32_t sw = take();
+                        tc_fence_after();
+                        mma4(acc1, win(j) + F2_CENTRE, s_ring + sw * TILE16, j > 0 ? 1u : 0u);
+                        umma_commit(bar + B2B_EMPTY(sw));
+                    }
                     if (stack_near(d)) {
                         for (int j = 0; j < 2; ++j) {
-                            stack_mbar_wait(bar + B2B_DZ(j), dz_n & 1u, ab, p.err);      // own dz_l, K-half j, staged
-                            tc_fence_after();
-                            TLB(10 + j);
-                            uint32_t sw = take();
-                            tc_fence_after();
-                            mma4(acc1, win(j) + F2_CENTRE, s_ring + sw * TILE16, j > 0 ? 1u : 0u);
-                            umma_commit(bar + B2B_EMPTY(sw));
                             stack_mbar_wait(bar + B2B_HALO(j), n_near & 1u, ab, p.err);
                             tc_fence_after();
                             TLB(12 + j);
 #pragma unroll
                             for (int k = 0; k < 3; k += 2) {
-                                sw = take();
+                                const uint32_t sw = take();
                                 tc_fence_after();
                                 mma4(acc1, win(j) + (uint32_t)(F2_HALO - (k - 1) * d) * 128u, s_ring + sw * TILE16, 1u);
                                 umma_commit(bar + B2B_EMPTY(sw));
@@ -206,25 +225,19 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
                         }
                         ++n_near;
                     } else {
-                        for (int j = 0; j < 2; ++j) {
-                            stack_mbar_wait(bar + B2B_DZ(j), dz_n & 1u, ab, p.err);
-                            tc_fence_after();
-                            TLB(10 + j);
-                            const uint32_t sw = take();
-                            tc_fence_after();
-                            mma4(acc1, win(j) + F2_CENTRE, s_ring + sw * TILE16, j > 0 ? 1u : 0u);
-                            umma_commit(bar + B2B_EMPTY(sw));
-                        }
+                        uint32_t sw[2][2];
+                        const bool live0 = tap_live(t0, 0, -d, p.T), live2 = tap_live(t0, 2, -d, p.T);
+                        if (live0) { sw[0][0] = take(); sw[0][1] = take(); }        // weights first (producer fill order)
+                        if (live2) { sw[1][0] = take(); sw[1][1] = take(); }
                         for (int k = 0; k < 3; k += 2) {
-                            if (!tap_live(t0, k, -d, p.T)) continue;
+                            if (!(k == 0 ? live0 : live2)) continue;
                             for (int j = 0; j < 2; ++j) {
-                                const uint32_t sw = take();
                                 const uint32_t sa = take();
                                 tc_fence_after();
                                 TLB(14 + k + j);
-                                mma4(acc1, s_ring + sa * TILE16, s_ring + sw * TILE16, 1u);
-                                umma_commit(bar + B2B_EMPTY(sw));
+                                mma4(acc1, s_ring + sa * TILE16, s_ring + sw[k >> 1][j] * TILE16, 1u);
                                 umma_commit(bar + B2B_EMPTY(sa));
+                                umma_commit(bar + B2B_EMPTY(sw[k >> 1][j]));
                             }
                         }
                     }
@@ -257,46 +270,6 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
             }
         }
         __syncwarp();
-    } else if (warp == 18) {
-        // ================================ halo producer ==========================================
-        if (lane == 0) {
-            uint32_t acc1_n = 0;                              // ACC1 commits of the boundaries above l
-            const unsigned* fl = p.flags + (size_t)b * p.tiles_per_pair * 2;
-            const int ti = t0 >> 7;
-            const bool has_up = t0 > 0, has_dn = t0 + 128 < p.T;
-            for (int l = NL; l >= 0; --l) {
-                const bool g1 = l < NL, g2 = l >= 1;
-                const int d = stack_dil(l);
-                if (g1 && stack_near(d)) {
-                    // the halo rows are dead once the previous boundary's transposed conv has completed
-                    if (l + 1 < NL) stack_mbar_wait(bar + B2B_ACC1, (acc1_n - 1u) & 1u, ab, p.err);
-                    const int bi = d <= 8 ? 0 : (d == 16 ? 1 : (d == 32 ? 2 : 3));
-                    const int dbox = 8 << bi;
-                    for (int j = 0; j < 2; ++j) {
-                        const unsigned* f_up = fl + 2 * (has_up ? ti - 1 : (has_dn ? ti + 1 : ti)) + j;
-                        const unsigned* f_dn = fl + 2 * (has_dn ? ti + 1 : (has_up ? ti - 1 : ti)) + j;
-                        if (has_up || has_dn) {
-                            stack_wait_flags(f_up, f_dn, p.need[l], ab, p.err);
-                            fence_proxy_async_all();
-                        }
-                        TLB(24 + j);
-                        const uint32_t hb = bar + B2B_HALO(j);
-                        mbar_expect_tx(hb, 2u * (uint32_t)dbox * 128u);
-                        tma_load_4d(win(j) + (uint32_t)(F2_HALO - dbox) * 128u, &p.tmHz[bi], hb, j * 64, t0 - dbox, b, (NL - l) & 1);
-                        tma_load_4d(win(j) + (uint32_t)(F2_HALO + 128) * 128u, &p.tmHz[bi], hb, j * 64, t0 + 128, b, (NL - l) & 1);
-                    }
-                }
-                if (g1 || p.sg_slot[l] >= 0) ++acc1_n;
-                // Anti-dependency of this boundary's publish: dz_{l-1} overwrites ping-pong buffer of dz_{l+1}, whose readers
-                // (tiles whose +-d_{l+1} taps cover this tile) are done once they have published dz_l.  The adjacent tiles
-                // were waited for by this boundary's own taps unless d_l >= 256; the far taps need the extra look.
-                if (g2 && l + 1 < NL && bs_anti_needed(l + 1)) {
-                    const int dp = stack_dil(l + 1);
-                    stack_wait_rows2(p.flags, p.tiles_per_pair, p.T, b, t0 - dp, t0 + dp, p.need[l], ab, p.err);
-                    mbar_arrive(bar + B2B_ANTI);
-                }
-            }
-        }
     } else {
         // ================================ epilogue warps ======================================
         const int q = warp & 3, cc = (warp - 2) >> 2;                // TMEM lane quadrant, 16-column group of a K-half
@@ -307,7 +280,12 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
         unsigned* my_flag = p.flags + (size_t)tile * 2;
         const uint16_t* hmask16 = reinterpret_cast<const uint16_t*>(p.hmask);
         const uint16_t* zmask16 = reinterpret_cast<const uint16_t*>(p.zmask);
+        const bool has_up = t0 > 0, has_dn = t0 + 128 < p.T;
         uint32_t acc1_n = 0, acc2_n = 0, io_n = 0, anti_n = 0;
+        // LL item of (ping-pong pp, tile tl, side sd, K-half j, cc, row slot): lines [4][LL_ROWS], slot fastest (stack_fwd.cuh)
+        auto ll_item = [&](int pp, int tl, int sd, int j, int slot, int c) -> uint4* {
+            return p.ll + ((((((size_t)pp * p.ntiles + tl) * 2 + sd) * 2 + j) * 4 + c) * 4) * LL_ROWS + slot;
+        };
         for (int l = NL; l >= 0; --l) {
             const bool g1 = l < NL, g2 = l >= 1;
             const int df = p.df_idx[l], sg = p.sg_slot[l];
@@ -326,6 +304,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
             float pk0 = 0.f, pk1 = 0.f, pk2 = 0.f;
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
+                if (j == 1) named_bar_sync(1 + q, 128);       // K-half 0 of the whole quadrant before anyone starts K-half 1
                 const int colc = j * 64 + cc * 16;
                 const uint32_t col = lane_off + colc;
                 float v[16];
@@ -397,7 +376,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
                 // completed); fixed order -> reproducible
                 float* ps = reinterpret_cast<float*>(gen + B2_RING);
                 ps[(0 * 4 + cc) * 128 + r] = pk0; ps[(1 * 4 + cc) * 128 + r] = pk1; ps[(2 * 4 + cc) * 128 + r] = pk2;
-                named_bar_sync(1, 512);
+                named_bar_sync(5, 512);
                 if (cc < 3) {
                     const float* q4 = ps + cc * 4 * 128 + r;
                     p.pdots[(size_t)cc * p.R + row] = (q4[0] + q4[128]) + (q4[256] + q4[384]);
@@ -412,8 +391,10 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
             const int m = l - 1;                              // the boundary that consumes dz_{l-1}
             const int dn = stack_dil(m);
             const bool near = stack_near(dn);
+            const uint32_t tag = (epoch << 6) | (uint32_t)(m + 1);
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
+                if (j == 1) named_bar_sync(1 + q, 128);
                 const int colc = j * 64 + cc * 16;
                 float v[16];
                 tmem_ld16_nowait(acc2 + lane_off + colc, v);
@@ -428,21 +409,64 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
                 *reinterpret_cast<uint4*>(w + sw1) = make_uint4(P[4], P[5], P[6], P[7]);
                 fence_proxy_async_smem();
                 tc_fence_before();
-                if (j == 0 && l + 1 < NL && bs_anti_needed(l + 1)) { stack_mbar_wait(bar + B2B_ANTI, anti_n & 1u, ab, p.err); ++anti_n; }
-                if (!near || r < dn || r >= 128 - dn)
-                    st_global_v8(p.dz + ((size_t)((NL - m) & 1) * p.R + row) * AST_C + colc, P[0], P[1], P[2], P[3], P[4], P[5], P[6], P[7]);
-                __syncwarp();
-                // release before the DZ arrival: cumulative flag counts then imply every releasing warp finished this publish
-                if (lane == 0) {
-                    if (dn > 32 || q == 0 || q == 3) red_release_gpu_add(my_flag + j, 1u);
-                    mbar_arrive(bar + B2B_DZ(j));
+                if (near) {
+                    if (r < dn || r >= 128 - dn) {
+                        const int sd = r < dn ? 0 : 1, slot = r < dn ? r : r - (128 - dn);
+                        uint4* d0 = ll_item((NL - m) & 1, tile, sd, j, slot, cc);
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) ll_store(d0 + e * LL_ROWS, P[2 * e], P[2 * e + 1], tag);
+                    }
+                    __syncwarp();
+                    if (lane == 0) {
+                        if (q == 0 || q == 3) red_relaxed_gpu_add(my_flag + j, 1u);      // bookkeeping for the anti-dependency polls only
+                        mbar_arrive(bar + B2B_DZ(j));
+                    }
+                } else {
+                    if (j == 0 && l + 1 < NL && !stack_near(stack_dil(l + 1))) { stack_mbar_wait(bar + B2B_ANTI, anti_n & 1u, ab, p.err); ++anti_n; }
+                    named_bar_sync(1 + q, 128);
+                    // far publish: the four warps of a row quadrant copy full 128-byte lines of the staged K-half, then ONE release
+                    const uint8_t* wc = gen + j * B2_WBUF + F2_CENTRE;
+                    const size_t g0 = ((size_t)((NL - m) & 1) * p.R + row0) * AST_C + j * 64 + (lane & 7) * 8;
+#pragma unroll
+                    for (int it = 0; it < 2; ++it) {
+                        const int rr = q * 32 + cc * 8 + it * 4 + (lane >> 3);
+                        *reinterpret_cast<uint4*>(p.dz + g0 + (size_t)rr * AST_C) = *reinterpret_cast<const uint4*>(wc + sw128_off(rr, lane & 7));
+                    }
+                    named_bar_sync(5, 512);
+                    if (warp == 2 && lane == 0) red_release_gpu_add(my_flag + j, 1u);
+                    if (lane == 0) mbar_arrive(bar + B2B_DZ(j));
                 }
                 if (threadIdx.x == 64) { TLB(34 + j); }
+            }
+            if (near) {
+                // near hand-off, consumer side: the dn boundary rows of both neighbours -> window halo (see stack_fwd.cuh)
+                const int e = (warp - 2) * 32 + lane;
+                const int slot = e % dn, rest = e / dn, c = rest & 3, hs = rest >> 2;      // slot fastest: coalesced
+                const bool active = hs < 2 && (hs == 0 ? has_up : has_dn);
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    if (active) {
+                        uint32_t w[8];
+                        ll_wait_item(ll_item((NL - m) & 1, hs == 0 ? tile - 1 : tile + 1, hs == 0 ? 1 : 0, j, slot, c), tag, w, ab, p.err);
+                        const int wr = hs == 0 ? F2_HALO - dn + slot : F2_HALO + 128 + slot;
+                        uint8_t* wb = gen + j * B2_WBUF + wr * 128;
+                        *reinterpret_cast<uint4*>(wb + (((2 * c) ^ (wr & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+                        *reinterpret_cast<uint4*>(wb + (((2 * c + 1) ^ (wr & 7)) << 4)) = make_uint4(w[4], w[5], w[6], w[7]);
+                        fence_proxy_async_smem();
+                    }
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar + B2B_HALO(j));
+                    if (threadIdx.x == 64) TLB(24 + j);
+                }
             }
             if (threadIdx.x == 64) TLC();
         }
     }
     tc_fence_before();
     __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(p.epoch + 1, 1u) == gridDim.x - 1) { p.epoch[1] = 0u; __threadfence(); atomicAdd(p.epoch, 1u); }
+    }
     if (warp == 1) tmem_dealloc<512>(tmem);
 }

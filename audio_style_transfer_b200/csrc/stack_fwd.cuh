@@ -5,33 +5,39 @@
 // What stays on the SM
 //   * the fp32 residual stream h: TMEM (128 columns), updated in place by the epilogue; only content / style
 //     extracts are exported to global memory;
-//   * relu(h) as a bf16 hi/lo operand WINDOW of 256 rows per K-half: rows [64, 192) are the CTA's own tile, rows
-//     [64-d, 64) and [192, 192+d) the d boundary rows of the two neighbour tiles.  For d <= 64 ("near" layers, 21
-//     of 30) all three taps of the dilated conv are UMMA descriptors into this window at row offsets 64-d, 64, 64+d
+//   * relu(h) as a bf16 hi/lo operand WINDOW of 192 rows per K-half: rows [32, 160) are the CTA's own tile, rows
+//     [32-d, 32) and [160, 160+d) the d boundary rows of the two neighbour tiles.  For d <= 32 ("near" layers, 18
+//     of 30) all three taps of the dilated conv are UMMA descriptors into this window at row offsets 32-d, 32, 32+d
 //     (K-major SWIZZLE_128B descriptors may start at any row: scripts/experiments/umma_row_offset.cu) -- no operand
 //     tile is streamed, the ring carries weights only;
 //   * relu(z) (A operand of the 1x1 conv) overlays the centre of the window: it is dead once the 1x1 GEMM is done.
 // What crosses SMs
-//   * near layers: a tile publishes ONLY its first and last d rows (32-byte stores straight from the epilogue
-//     registers into the canonical [2][B][T][128] bf16 buffers + one release per boundary warp); the neighbour polls
-//     the flag and pulls the rows into its window halo with two small TMA boxes per part.  Rows outside the pair are
-//     zero-filled by TMA: that IS the reference's per-layer 'SAME' padding (masked.py:139);
-//   * far layers (d >= 128): whole tiles are published and the +-d taps are streamed through the ring as before.
+//   * near layers: a tile hands over ONLY its first and last d rows, in "LL" form: every 8-byte unit is {4 bytes of
+//     payload, 4-byte tag} (tag = launch epoch | publish index), written with 16-byte volatile stores straight from the
+//     epilogue registers.  No fence, no flag: the consumer polls the data itself and a unit is valid when its tag
+//     matches (an aligned 8-byte store is single-copy atomic), so the hand-off costs one store -> L2 -> load trip
+//     instead of store, membar, red, poll, acquire fence and a TMA load (measured ~5k cycles that way).  The 16
+//     epilogue warps import the rows themselves: one 64-byte LL item -> two swizzled 16-byte chunks of the window
+//     halo.  Halo rows outside the pair stay zero from the start of the kernel: that IS the reference's per-layer
+//     'SAME' padding (masked.py:139);
+//   * far layers (d >= 64): whole tiles are published to the canonical [2][B][T][128] bf16 buffers (full 128-byte lines
+//     copied from the staged smem tile, ONE gpu-scope release per K-half after a CTA barrier); consumers poll the
+//     per-tile flags and stream the shifted tiles through the ring by TMA (rows outside the pair zero-filled by TMA).
 // Pipelining inside a tile (what hides the epilogues behind the MMAs): everything is split by K-half j (channels
-// 64j .. 64j+63).  All 16 epilogue warps first finish K-half 0 of a phase, signal it, then do K-half 1:
+// 64j .. 64j+63).  All 16 epilogue warps first finish K-half 0 of a phase, signal it, then do K-half 1 (a named barrier
+// per row quadrant keeps the hardware's highest-warp-first arbitration from running one warp through both halves):
 //   epilogue 1 (relu(z) hi/lo)  : RT(0) lets the 1x1 GEMM start on K-half 0 while K-half 1 is still being split;
-//   epilogue 2 (h', relu(h'))   : ACT(0) + publish(0) let the next layer's centre-tap MMAs on K-half 0 start and the
+//   epilogue 2 (h', relu(h'))   : ACT(0) + hand-off(0) let the next layer's centre-tap MMAs on K-half 0 start and the
 //                                 neighbours fetch K-half 0 of the halo while K-half 1 is still in the epilogue.
-// Roles: warp 0 = weight / far-operand ring producer, warp 1 = MMA issuer, warps 2..17 = epilogue (TMEM lane quadrant
-// q = warp % 4, 16-column group cc of each K-half), warp 18 = halo producer (flag polls + halo TMA, anti-dependency
-// polls).  All CTAs are co-resident (cooperative launch, grid <= #SMs, 1 CTA/SM); every wait targets work of an
-// earlier publish, so the dependency graph is acyclic.  Every spin is bounded: on expiry the CTA raises *err, sets its
-// abort word and all further waits fall through, so the kernel always terminates and the host reports AST_ECUDA.
+// Roles: warp 0 = weight / far-operand ring producer (+ anti-dependency polls), warp 1 = MMA issuer, warps 2..17 =
+// epilogue (TMEM lane quadrant q = warp % 4, 16-column group cc of each K-half) and halo import.  All CTAs are
+// co-resident (cooperative launch, grid <= #SMs, 1 CTA/SM); every wait targets work of an earlier publish, so the
+// dependency graph is acyclic.  Every spin is bounded: on expiry the CTA raises *err, sets its abort word and all
+// further waits fall through, so the kernel always terminates and the host reports AST_ECUDA (ast_check).
 #pragma once
 
 struct alignas(64) FwdStackArgs {
     CUtensorMap tmA_hi, tmA_lo;      // bf16 relu(h) hi / lo [2][B][T][128] ping-pong, box {64,128,1,1}: far taps
-    CUtensorMap tmHa_hi[4], tmHa_lo[4];   // same buffers, box {64, 8<<i, 1, 1}: halo rows of the near layers
     CUtensorMap tmW1, tmW2;          // forward weight operand rows (see tc_weights_fwd_kernel), box {64,128}
     const float* x;                  // [B][T] waveform
     const float* W0; const float* b0;            // start conv [3][128], [128]
@@ -40,24 +46,28 @@ struct alignas(64) FwdStackArgs {
     uint32_t* zmask; uint32_t* hmask;            // [NL][R][4], [NL+1][R][4]
     __nv_bfloat16* a_hi; __nv_bfloat16* a_lo;    // the buffers behind tmA_* (published with plain stores)
     __nv_bfloat16* F;                // bf16 extract copies [n_style][R][128]
+    uint4* ll;                       // near hand-off lines [2][ntiles][2 sides][2 K-halves][4 cc][2 parts][4][32 rows] x 16 B
     unsigned* flags;                 // [ntiles][2] (K-half), zeroed before the launch
+    unsigned* epoch;                 // [0] launch epoch (tags), [1] CTAs done: the last CTA of a launch bumps the epoch
     unsigned* err;
-    int T, R, NL, tiles_per_pair;
+    int T, R, NL, tiles_per_pair, ntiles;
     int tile0;                       // global index of this launch's first tile (launches cover whole pairs)
     unsigned short need[34];         // need[i]: flag value once publish i (relu(h_i), i = 0: start conv) is complete
     signed char f_slot[32];          // style slot that receives bf16(H[l+1]), or -1
     unsigned char export_h[33];      // export_h[i] != 0: H[i] is written to global memory (i = 0: start-conv output)
 };
 
-#define F2_HALO 64
-#define F2_WBUF 32768                             // one (K-half, part) window buffer: [256 rows][128 B]
+#define F2_HALO 32
+#define F2_WROWS (128 + 2 * F2_HALO)
+#define F2_WBUF (F2_WROWS * 128)                  // one (K-half, part) window buffer: [192 rows][128 B]
 #define F2_CENTRE (F2_HALO * 128)                 // byte offset of the own tile inside a window buffer
 #define F2_RING (4 * F2_WBUF)
-#define F2_NSLOT 3
+#define F2_NSLOT 4
 #define F2_SLOT 32768                             // hi [128][64] | lo [128][64]
 #define F2_BAR (F2_RING + F2_NSLOT * F2_SLOT)
 #define F2_SMEM (F2_BAR + 1024 + 1024)
-#define F2_THREADS 608
+#define F2_THREADS 576
+#define LL_ROWS 32                                // row slots per (tile, side, K-half, cc, part, line) of the near hand-off
 #define F2B_FULL(i) (8u * (i))
 #define F2B_EMPTY(i) (32u + 8u * (i))
 #define F2B_ACT(j) (64u + 8u * (j))
@@ -82,7 +92,7 @@ __device__ int g_tl_layer = 12;
 // dilation of layer l (model.py:98) and the publish geometry that follows from the CONSUMER layer's dilation
 __device__ __host__ __forceinline__ int stack_dil(int l) { return 1 << (l % 10); }
 __device__ __host__ __forceinline__ bool stack_near(int d) { return d <= F2_HALO; }
-__device__ __host__ __forceinline__ int stack_npub(int d) { return d <= 32 ? 8 : 16; }   // warps that release per publish and K-half
+__device__ __host__ __forceinline__ int stack_npub(int d) { return stack_near(d) ? 8 : 1; }   // flag increments per publish and K-half
 
 // ---- bounded waits ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ bool stack_aborted(const volatile unsigned* ab) { return *ab != 0u; }
@@ -146,6 +156,34 @@ __device__ __forceinline__ void stack_wait_rows2(const unsigned* flags, int tile
 
 __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 
+// ---- LL lines (near hand-off) ------------------------------------------------------------------------------------
+__device__ __forceinline__ void ll_store(uint4* p, uint32_t d0, uint32_t d1, uint32_t tag) {
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(d0), "r"(tag), "r"(d1), "r"(tag) : "memory");
+}
+__device__ __forceinline__ uint4 ll_load(const uint4* p) {
+    uint4 v;
+    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void red_relaxed_gpu_add(unsigned* p, unsigned v) {
+    asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// Polls one 64-byte LL item (4 lines, LL_ROWS lines apart: the row slot is the fastest index so that the lanes of a
+// warp -- consecutive rows -- store and load contiguous bytes) until all 8 tags match; false after an abort.
+__device__ __forceinline__ bool ll_wait_item(const uint4* src, uint32_t tag, uint32_t (&w)[8], volatile unsigned* ab, unsigned* err) {
+    unsigned spins = 0;
+    for (;;) {
+        uint4 v[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) v[i] = ll_load(src + i * LL_ROWS);
+        bool ok = true;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { ok = ok && v[i].y == tag && v[i].w == tag; w[2 * i] = v[i].x; w[2 * i + 1] = v[i].z; }
+        if (ok) return true;
+        if (++spins > FS_SPIN_LIMIT || stack_aborted(ab)) { stack_abort(ab, err, 3u); return false; }
+    }
+}
+
 __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __grid_constant__ FwdStackArgs p) {
     extern __shared__ uint8_t tc_smem_raw[];
     const uint32_t base = (smem_u32(tc_smem_raw) + 1023u) & ~1023u;
@@ -157,18 +195,28 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
     const int row0 = tile * 128;
     const int b = row0 / p.T, t0 = row0 - b * p.T;
     const int NL = p.NL;
+    const uint32_t epoch = *reinterpret_cast<const volatile unsigned*>(p.epoch);      // stable: bumped by the previous launch's last CTA
     if (threadIdx.x == 0) TL(0);
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&p.tmA_hi); tma_prefetch_desc(&p.tmA_lo); tma_prefetch_desc(&p.tmW1); tma_prefetch_desc(&p.tmW2);
-        for (int i = 0; i < 4; ++i) { tma_prefetch_desc(&p.tmHa_hi[i]); tma_prefetch_desc(&p.tmHa_lo[i]); }
         for (int i = 0; i < F2_NSLOT; ++i) { mbar_init(bar + F2B_FULL(i), 1); mbar_init(bar + F2B_EMPTY(i), 1); }
-        for (int j = 0; j < 2; ++j) { mbar_init(bar + F2B_ACT(j), 16); mbar_init(bar + F2B_HALO(j), 1); mbar_init(bar + F2B_RT(j), 16); }
+        for (int j = 0; j < 2; ++j) { mbar_init(bar + F2B_ACT(j), 16); mbar_init(bar + F2B_HALO(j), 16); mbar_init(bar + F2B_RT(j), 16); }
         mbar_init(bar + F2B_ACC1, 1); mbar_init(bar + F2B_ACC2, 1); mbar_init(bar + F2B_ANTI, 1);
         *ab = 0u;
         mbar_init_fence();
     }
     if (warp == 1) tmem_alloc<512>(bar + F2B_TMEM);
+    if (warp >= 2) {
+        // halo rows of the operand window start as zeros and stay zero where the pair ends (the 'SAME' padding)
+        const int e = (warp - 2) * 32 + lane;                        // 0..511
+        for (int i = e; i < 4 * 2 * F2_HALO * 8; i += 512) {         // (buffer, halo row, 16-byte chunk)
+            const int buf = i / (2 * F2_HALO * 8), rem = i % (2 * F2_HALO * 8), hr = rem >> 3, ch = rem & 7;
+            const int wr = hr < F2_HALO ? hr : 128 + hr;
+            *reinterpret_cast<uint4*>(gen + buf * F2_WBUF + wr * 128 + ch * 16) = make_uint4(0u, 0u, 0u, 0u);
+        }
+        fence_proxy_async_smem();
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -196,32 +244,35 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
                     tma_load_2d(st, &p.tmW1, fb, j * 64, w1row + (k * 2 + 0) * 128);
                     tma_load_2d(st + TILE16, &p.tmW1, fb, j * 64, w1row + (k * 2 + 1) * 128);
                 };
+                auto load_a = [&](int k, int j) {
+                    const uint32_t slot = acquire();
+                    const uint32_t st = s_ring + slot * F2_SLOT, fb = bar + F2B_FULL(slot);
+                    tma_load_4d(st, &p.tmA_hi, fb, j * 64, t0 + (k - 1) * d, b, l & 1);
+                    tma_load_4d(st + TILE16, &p.tmA_lo, fb, j * 64, t0 + (k - 1) * d, b, l & 1);
+                };
                 TLD(0);
                 if (stack_near(d)) {
-                    // fill order = the MMA issuer's take order: per K-half the centre, -d and +d tap weights
-                    for (int j = 0; j < 2; ++j) { load_w1(1, j); load_w1(0, j); load_w1(2, j); }
+                    // fill order = the MMA issuer's take order: both centre-tap K-halves first (they need no neighbour),
+                    // then per K-half the -d and +d tap weights
+                    load_w1(1, 0); load_w1(1, 1);
+                    for (int j = 0; j < 2; ++j) { load_w1(0, j); load_w1(2, j); }
                 } else {
+                    // centre weights, then the first live side tap's weights (none of them waits for a neighbour), ONE poll
+                    // of all the flags this layer needs, then operand tiles (and the second tap's weights) as slots free up
                     load_w1(1, 0);
                     load_w1(1, 1);
                     const bool live0 = tap_live(t0, 0, d, p.T), live2 = tap_live(t0, 2, d, p.T);
-                    bool polled = false;
-                    for (int k = 0; k < 3; k += 2) {
-                        if (!(k == 0 ? live0 : live2)) continue;
-                        const int t = t0 + (k - 1) * d;
-                        for (int j = 0; j < 2; ++j) {
-                            load_w1(k, j);
-                            if (!polled) {                    // relu(h_l) of the tap rows is in global memory (both K-halves)
-                                stack_wait_rows2(p.flags, p.tiles_per_pair, p.T, b, live0 ? t0 - d : t0 + d, live2 ? t0 + d : t0 - d,
-                                                 p.need[l], ab, p.err);
-                                fence_proxy_async_all();
-                                polled = true;
-                                TLD(2);
-                            }
-                            const uint32_t slot = acquire();
-                            const uint32_t st = s_ring + slot * F2_SLOT, fb = bar + F2B_FULL(slot);
-                            tma_load_4d(st, &p.tmA_hi, fb, j * 64, t, b, l & 1);
-                            tma_load_4d(st + TILE16, &p.tmA_lo, fb, j * 64, t, b, l & 1);
-                        }
+                    const int k1 = live0 ? 0 : 2;                      // first live side tap (if any)
+                    if (live0 || live2) {
+                        load_w1(k1, 0);
+                        load_w1(k1, 1);
+                        stack_wait_rows2(p.flags, p.tiles_per_pair, p.T, b, live0 ? t0 - d : t0 + d, live2 ? t0 + d : t0 - d,
+                                         p.need[l], ab, p.err);
+                        fence_proxy_async_all();
+                        TLD(2);
+                        load_a(k1, 0);
+                        load_a(k1, 1);
+                        if (live0 && live2) { load_w1(2, 0); load_a(2, 0); load_w1(2, 1); load_a(2, 1); }
                     }
                 }
                 for (int j = 0; j < 2; ++j) {                 // 1x1 weights, K-half j: hi rows then lo rows
@@ -231,6 +282,15 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
                     tma_load_2d(st + TILE16, &p.tmW2, fb, j * 64, w2row + 128);
                 }
                 TLD(6);
+                // Anti-dependency of a FAR publish l+1 (whole tile -> ping-pong buffer (l+1)&1, which holds relu(h_{l-1}) if
+                // publish l-1 was far too): the tiles whose +-d_{l-1} taps read this tile must be past layer l-1's conv, i.e.
+                // have made publish l.  Every publish bumps the flags (near ones without release semantics, for this purpose
+                // only).  Polled here, off the critical path.
+                if (l >= 1 && l + 1 < NL && !stack_near(stack_dil(l + 1)) && !stack_near(stack_dil(l - 1))) {
+                    const int dp = stack_dil(l - 1);
+                    stack_wait_rows2(p.flags, p.tiles_per_pair, p.T, b, t0 - dp, t0 + dp, p.need[l], ab, p.err);
+                    mbar_arrive(bar + F2B_ANTI);
+                }
             }
         }
     } else if (warp == 1) {
@@ -259,21 +319,24 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
             for (int l = 0; l < NL; ++l) {
                 const uint32_t par = (uint32_t)l & 1u;
                 const int d = stack_dil(l);
+                // centre tap, both K-halves: the own tile is resident, nothing to wait for but its staging
+                for (int j = 0; j < 2; ++j) {
+                    stack_mbar_wait(bar + F2B_ACT(j), par, ab, p.err);           // own relu(h_l), K-half j, staged
+                    tc_fence_after();
+                    TLD(8 + j);
+                    const uint32_t sw = take();
+                    tc_fence_after();
+                    mma_slice(acc1, win(j, 0) + F2_CENTRE, win(j, 1) + F2_CENTRE, s_ring + sw * F2_SLOT, j > 0 ? 1u : 0u);
+                    umma_commit(bar + F2B_EMPTY(sw));
+                }
                 if (stack_near(d)) {
                     for (int j = 0; j < 2; ++j) {
-                        stack_mbar_wait(bar + F2B_ACT(j), par, ab, p.err);       // own relu(h_l), K-half j, staged
-                        tc_fence_after();
-                        TLD(8 + j);
-                        uint32_t sw = take();
-                        tc_fence_after();
-                        mma_slice(acc1, win(j, 0) + F2_CENTRE, win(j, 1) + F2_CENTRE, s_ring + sw * F2_SLOT, j > 0 ? 1u : 0u);
-                        umma_commit(bar + F2B_EMPTY(sw));
-                        stack_mbar_wait(bar + F2B_HALO(j), n_near & 1u, ab, p.err);   // the neighbours' boundary rows landed
+                        stack_mbar_wait(bar + F2B_HALO(j), n_near & 1u, ab, p.err);   // the neighbours' boundary rows are in the window
                         tc_fence_after();
                         TLD(10 + j);
 #pragma unroll
                         for (int k = 0; k < 3; k += 2) {
-                            sw = take();
+                            const uint32_t sw = take();
                             tc_fence_after();
                             const uint32_t ro = (uint32_t)(F2_HALO + (k - 1) * d) * 128u;
                             mma_slice(acc1, win(j, 0) + ro, win(j, 1) + ro, s_ring + sw * F2_SLOT, 1u);
@@ -282,26 +345,28 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
                     }
                     ++n_near;
                 } else {
-                    for (int j = 0; j < 2; ++j) {
-                        stack_mbar_wait(bar + F2B_ACT(j), par, ab, p.err);
-                        tc_fence_after();
-                        TLD(8 + j);
-                        const uint32_t sw = take();
-                        tc_fence_after();
-                        mma_slice(acc1, win(j, 0) + F2_CENTRE, win(j, 1) + F2_CENTRE, s_ring + sw * F2_SLOT, j > 0 ? 1u : 0u);
-                        umma_commit(bar + F2B_EMPTY(sw));
-                    }
-                    for (int k = 0; k < 3; k += 2) {
-                        if (!tap_live(t0, k, d, p.T)) continue;
+                    const bool live0 = tap_live(t0, 0, d, p.T), live2 = tap_live(t0, 2, d, p.T);
+                    if (live0 || live2) {                                   // producer fill order: W W A A, then W A W A
+                        uint32_t sw[2];
+                        sw[0] = take(); sw[1] = take();
                         for (int j = 0; j < 2; ++j) {
-                            const uint32_t sw = take();
                             const uint32_t sa = take();
                             tc_fence_after();
-                            TLD(11 + k + j);
-                            mma_slice(acc1, s_ring + sa * F2_SLOT, s_ring + sa * F2_SLOT + TILE16, s_ring + sw * F2_SLOT, 1u);
-                            umma_commit(bar + F2B_EMPTY(sw));
+                            TLD(11 + j);
+                            mma_slice(acc1, s_ring + sa * F2_SLOT, s_ring + sa * F2_SLOT + TILE16, s_ring + sw[j] * F2_SLOT, 1u);
                             umma_commit(bar + F2B_EMPTY(sa));
+                            umma_commit(bar + F2B_EMPTY(sw[j]));
                         }
+                        if (live0 && live2)
+                            for (int j = 0; j < 2; ++j) {
+                                const uint32_t swj = take();
+                                const uint32_t sa = take();
+                                tc_fence_after();
+                                TLD(13 + j);
+                                mma_slice(acc1, s_ring + sa * F2_SLOT, s_ring + sa * F2_SLOT + TILE16, s_ring + swj * F2_SLOT, 1u);
+                                umma_commit(bar + F2B_EMPTY(swj));
+                                umma_commit(bar + F2B_EMPTY(sa));
+                            }
                     }
                 }
                 umma_commit(bar + F2B_ACC1);
@@ -319,50 +384,6 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
             }
         }
         __syncwarp();
-    } else if (warp == 18) {
-        // ================================ halo producer ==========================================
-        if (lane == 0) {
-            uint32_t n_near = 0;
-            const unsigned* fl = p.flags + (size_t)b * p.tiles_per_pair * 2;
-            const int ti = t0 >> 7;
-            const bool has_up = t0 > 0, has_dn = t0 + 128 < p.T;
-            for (int l = 0; l < NL; ++l) {
-                const int d = stack_dil(l);
-                if (stack_near(d)) {
-                    // the halo rows of the previous near layer are dead once that layer's conv MMAs have completed
-                    if (l > 0) stack_mbar_wait(bar + F2B_ACC1, (uint32_t)(l - 1) & 1u, ab, p.err);
-                    const int bi = d <= 8 ? 0 : (d == 16 ? 1 : (d == 32 ? 2 : 3));
-                    const int dbox = 8 << bi;
-                    for (int j = 0; j < 2; ++j) {
-                        const unsigned* f_up = fl + 2 * (has_up ? ti - 1 : (has_dn ? ti + 1 : ti)) + j;
-                        const unsigned* f_dn = fl + 2 * (has_dn ? ti + 1 : (has_up ? ti - 1 : ti)) + j;
-                        if (has_up || has_dn) {
-                            stack_wait_flags(f_up, f_dn, p.need[l], ab, p.err);
-                            fence_proxy_async_all();
-                        }
-                        TLD(20 + j);
-                        const uint32_t hb = bar + F2B_HALO(j);
-                        mbar_expect_tx(hb, 4u * (uint32_t)dbox * 128u);
-                        const uint32_t top = (uint32_t)(F2_HALO - dbox) * 128u, bot = (uint32_t)(F2_HALO + 128) * 128u;
-                        tma_load_4d(win(j, 0) + top, &p.tmHa_hi[bi], hb, j * 64, t0 - dbox, b, l & 1);
-                        tma_load_4d(win(j, 1) + top, &p.tmHa_lo[bi], hb, j * 64, t0 - dbox, b, l & 1);
-                        tma_load_4d(win(j, 0) + bot, &p.tmHa_hi[bi], hb, j * 64, t0 + 128, b, l & 1);
-                        tma_load_4d(win(j, 1) + bot, &p.tmHa_lo[bi], hb, j * 64, t0 + 128, b, l & 1);
-                    }
-                    ++n_near;
-                }
-                // Anti-dependency of publish l+1 (relu(h_{l+1}) overwrites ping-pong buffer (l+1)&1 = relu(h_{l-1})): the
-                // tiles whose +-d_{l-1} taps read this tile must be past layer l-1, i.e. have published relu(h_l).  For
-                // d_{l-1} <= 128 those are the adjacent tiles, already waited for by this layer's taps; the far taps
-                // (d_{l-1} >= 128, incl. the 512 -> 1 wrap) need this extra look, done here off the critical path.
-                if (l >= 1 && l + 1 < NL && ((l - 1) % 10) >= 7) {
-                    const int dp = stack_dil(l - 1);
-                    stack_wait_rows2(p.flags, p.tiles_per_pair, p.T, b, t0 - dp, t0 + dp, p.need[l], ab, p.err);
-                    mbar_arrive(bar + F2B_ANTI);
-                }
-            }
-            (void)n_near;
-        }
     } else {
         // ================================ epilogue warps ======================================
         const int q = warp & 3, cc = (warp - 2) >> 2;                // TMEM lane quadrant, 16-column group of a K-half
@@ -373,7 +394,12 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
         unsigned* my_flag = p.flags + (size_t)tile * 2;
         uint16_t* hmask16 = reinterpret_cast<uint16_t*>(p.hmask);
         uint16_t* zmask16 = reinterpret_cast<uint16_t*>(p.zmask);
+        const bool has_up = t0 > 0, has_dn = t0 + 128 < p.T;
         uint32_t anti_n = 0;
+        // LL item of (ping-pong pp, tile tl, side sd, K-half j, cc, part, row slot): lines [4][LL_ROWS] with the slot fastest
+        auto ll_item = [&](int pp, int tl, int sd, int j, int slot, int c, int part) -> uint4* {
+            return p.ll + ((((((size_t)pp * p.ntiles + tl) * 2 + sd) * 2 + j) * 8 + c * 2 + part) * 4) * LL_ROWS + slot;
+        };
 
         // relu(v[0..15]) -> bf16 hi / lo of columns 64 j + 16 cc ...: two 16-byte chunks each into window (j, hi/lo)
         auto stage16 = [&](int j, const float (&v)[16], uint32_t (&Hh)[8], uint32_t (&Ll)[8]) {
@@ -387,54 +413,110 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
             *reinterpret_cast<uint4*>(wlo + sw1) = make_uint4(Ll[4], Ll[5], Ll[6], Ll[7]);
         };
         // h_i, K-half j (columns 64 j + 16 cc .. + 15 of this thread's row) is in v: TMEM, own operand window, hand-off
-        // to the neighbours, sign mask, exports.  Critical outputs first.
+        // to the neighbours.  Nothing else: masks and exports follow in finish().
         auto emit = [&](int i, int j, const float (&v)[16]) {
             const int l = i - 1;                       // for TLD
-            const bool more = i < NL;
             const int col = j * 64 + cc * 16;
             tmem_st16(hacc + lane_off + col, v);
-            if (more) {
-                uint32_t Hh[8], Ll[8];
-                stage16(j, v, Hh, Ll);
-                fence_proxy_async_smem();
-                tc_fence_before();
-                const int dn = stack_dil(i);           // dilation of the layer that consumes relu(h_i)
-                const bool near = stack_near(dn);
-                if (i >= 2 && j == 0 && ((i - 2) % 10) >= 7) { stack_mbar_wait(bar + F2B_ANTI, anti_n & 1u, ab, p.err); ++anti_n; }
-                if (!near || r < dn || r >= 128 - dn) {
-                    const size_t g = ((size_t)(i & 1) * p.R + row) * AST_C + col;
-                    st_global_v8(p.a_hi + g, Hh[0], Hh[1], Hh[2], Hh[3], Hh[4], Hh[5], Hh[6], Hh[7]);
-                    st_global_v8(p.a_lo + g, Ll[0], Ll[1], Ll[2], Ll[3], Ll[4], Ll[5], Ll[6], Ll[7]);
+            if (i >= NL) return;
+            uint32_t Hh[8], Ll[8];
+            stage16(j, v, Hh, Ll);
+            fence_proxy_async_smem();
+            tc_fence_before();
+            const int dn = stack_dil(i);               // dilation of the layer that consumes relu(h_i)
+#ifdef AST_EXPERIMENTS
+            const bool mute = g_dbg_skip_publish == tile + 1 && i >= 3;     // fault injection (tests/test_gpu_loud.py)
+#else
+            const bool mute = false;
+#endif
+            if (stack_near(dn)) {
+                const uint32_t tag = (epoch << 6) | (uint32_t)(i + 1);
+                if ((r < dn || r >= 128 - dn) && !mute) {
+                    const int sd = r < dn ? 0 : 1, slot = r < dn ? r : r - (128 - dn);
+                    uint4* d0 = ll_item(i & 1, tile, sd, j, slot, cc, 0);
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) ll_store(d0 + e * LL_ROWS, Hh[2 * e], Hh[2 * e + 1], tag);
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) ll_store(d0 + (4 + e) * LL_ROWS, Ll[2 * e], Ll[2 * e + 1], tag);
                 }
                 __syncwarp();
-                // Flag counts are cumulative over publishes, so "count >= need[i]" must imply that every releasing warp
-                // finished publish i: the ACT arrival (which gates the next layer's conv and with it every warp's publish
-                // i+1) comes AFTER this warp's release.
                 if (lane == 0) {
-#ifdef AST_EXPERIMENTS
-                    const bool mute = g_dbg_skip_publish == tile + 1 && i >= 3;     // fault injection (tests/test_gpu_loud.py)
-#else
-                    const bool mute = false;
-#endif
-                    if ((dn > 32 || q == 0 || q == 3) && !mute) red_release_gpu_add(my_flag + j, 1u);
+                    if (q == 0 || q == 3) red_relaxed_gpu_add(my_flag + j, 1u);      // bookkeeping for the anti-dependency polls only
                     mbar_arrive(bar + F2B_ACT(j));
                 }
-                if (threadIdx.x == 64) TLD(36 + j);
-            }
-            uint32_t word = 0;
+            } else {
+                // far publish: the four warps of a row quadrant copy full 128-byte lines of the staged K-half; after a CTA
+                // barrier ONE thread releases the flag (one gpu-scope membar per K-half instead of sixteen)
+                if (j == 0 && i >= 2 && !stack_near(stack_dil(i - 2))) { stack_mbar_wait(bar + F2B_ANTI, anti_n & 1u, ab, p.err); ++anti_n; }
+                named_bar_sync(1 + q, 128);
+                const uint8_t* whi = gen + (j * 2 + 0) * F2_WBUF + F2_CENTRE;
+                const uint8_t* wlo = gen + (j * 2 + 1) * F2_WBUF + F2_CENTRE;
+                const size_t g0 = ((size_t)(i & 1) * p.R + row0) * AST_C + j * 64 + (lane & 7) * 8;
 #pragma unroll
-            for (int e = 0; e < 16; ++e) or_bit_if_pos(word, v[e], 1u << e);
-            hmask16[((size_t)i * p.R + row) * 8 + j * 4 + cc] = (uint16_t)word;
+                for (int it = 0; it < 2; ++it) {
+                    const int rr = q * 32 + cc * 8 + it * 4 + (lane >> 3);
+                    const uint32_t so = sw128_off(rr, lane & 7);
+                    const uint4 H = *reinterpret_cast<const uint4*>(whi + so);
+                    const uint4 L = *reinterpret_cast<const uint4*>(wlo + so);
+                    *reinterpret_cast<uint4*>(p.a_hi + g0 + (size_t)rr * AST_C) = H;
+                    *reinterpret_cast<uint4*>(p.a_lo + g0 + (size_t)rr * AST_C) = L;
+                }
+                named_bar_sync(5, 512);
+                if (warp == 2 && lane == 0 && !mute) red_release_gpu_add(my_flag + j, 1u);
+                if (lane == 0) mbar_arrive(bar + F2B_ACT(j));
+            }
+            if (threadIdx.x == 64) TLD(36 + j);
+        };
+        // Everything of h_i that nobody waits for -- sign mask, fp32 export, bf16 extract copy -- re-read from TMEM once the
+        // hand-off is out: these stores must not sit in front of a release (membar) or delay the second K-half.
+        auto finish = [&](int i) {
             const int f = i >= 1 ? (int)p.f_slot[i - 1] : -1;
-            if (p.export_h[i]) {
-                float4* out = reinterpret_cast<float4*>(p.H + ((size_t)i * p.R + row) * AST_C + col);
+            const bool exp = p.export_h[i] != 0;
 #pragma unroll
-                for (int e = 0; e < 4; ++e) out[e] = make_float4(v[4 * e], v[4 * e + 1], v[4 * e + 2], v[4 * e + 3]);
+            for (int j = 0; j < 2; ++j) {
+                const int col = j * 64 + cc * 16;
+                float v[16];
+                tmem_ld16_nowait(hacc + lane_off + col, v);
+                tmem_wait_ld();
+                uint32_t word = 0;
+#pragma unroll
+                for (int e = 0; e < 16; ++e) or_bit_if_pos(word, v[e], 1u << e);
+                hmask16[((size_t)i * p.R + row) * 8 + j * 4 + cc] = (uint16_t)word;
+                if (exp) {
+                    float4* out = reinterpret_cast<float4*>(p.H + ((size_t)i * p.R + row) * AST_C + col);
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) out[e] = make_float4(v[4 * e], v[4 * e + 1], v[4 * e + 2], v[4 * e + 3]);
+                }
+                if (f >= 0)                            // bf16 extract copy: 16 columns = 32 bytes = one full sector per thread
+                    st_global_v8(p.F + ((size_t)f * p.R + row) * AST_C + col,
+                                 pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]),
+                                 pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]), pack_bf16(v[14], v[15]));
             }
-            if (f >= 0)                                // bf16 extract copy: 16 columns = 32 bytes = one full sector per thread
-                st_global_v8(p.F + ((size_t)f * p.R + row) * AST_C + col,
-                             pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]),
-                             pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]), pack_bf16(v[14], v[15]));
+        };
+        // Near hand-off, consumer side: the d boundary rows of both neighbours (publish i) -> window halo, K-half by K-half.
+        // Item e of a K-half = (halo side hs, cc, part, row slot): 64 bytes of LL lines -> two 16-byte chunks.
+        auto import_halo = [&](int i) {
+            const int l = i - 1;                       // for TLD
+            const int d = stack_dil(i);
+            const uint32_t tag = (epoch << 6) | (uint32_t)(i + 1);
+            const int e = (warp - 2) * 32 + lane;
+            const int slot = e % d, rest = e / d, part = rest & 1, c = (rest >> 1) & 3, hs = rest >> 3;      // slot fastest: coalesced
+            const bool active = hs < 2 && (hs == 0 ? has_up : has_dn);
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                if (active) {
+                    uint32_t w[8];
+                    ll_wait_item(ll_item(i & 1, hs == 0 ? tile - 1 : tile + 1, hs == 0 ? 1 : 0, j, slot, c, part), tag, w, ab, p.err);
+                    const int wr = hs == 0 ? F2_HALO - d + slot : F2_HALO + 128 + slot;
+                    uint8_t* wb = gen + (j * 2 + part) * F2_WBUF + wr * 128;
+                    *reinterpret_cast<uint4*>(wb + (((2 * c) ^ (wr & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+                    *reinterpret_cast<uint4*>(wb + (((2 * c + 1) ^ (wr & 7)) << 4)) = make_uint4(w[4], w[5], w[6], w[7]);
+                    fence_proxy_async_smem();
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar + F2B_HALO(j));
+                if (threadIdx.x == 64) TLD(20 + j);
+            }
         };
 
         // ---- pseudo layer: start conv (model.py:80-93), same arithmetic as startconv_fwd_kernel ----
@@ -462,6 +544,8 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
                 emit(0, j, v);
             }
             tmem_wait_st();
+            if (NL > 0) import_halo(0);
+            finish(0);
         }
         for (int l = 0; l < NL; ++l) {
             const uint32_t par = (uint32_t)l & 1u;
@@ -470,8 +554,10 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
             tc_fence_after();
             if (threadIdx.x == 64 && l < 30) TL(2 + l);
             if (threadIdx.x == 64) TLD(30);
+            uint32_t zword = 0;
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
+                if (j == 1) named_bar_sync(1 + q, 128);       // K-half 0 of the whole quadrant before anyone starts K-half 1
                 const int col = j * 64 + cc * 16;
                 float v[16];
                 tmem_ld16_nowait(acc1 + lane_off + col, v);
@@ -487,11 +573,11 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar + F2B_RT(j));
-                uint32_t word = 0;
 #pragma unroll
-                for (int e = 0; e < 16; ++e) or_bit_if_pos(word, v[e], 1u << e);
-                zmask16[((size_t)l * p.R + row) * 8 + j * 4 + cc] = (uint16_t)word;
+                for (int e = 0; e < 16; ++e) or_bit_if_pos(zword, v[e], 1u << (16 * j + e));
             }
+            zmask16[((size_t)l * p.R + row) * 8 + cc] = (uint16_t)zword;
+            zmask16[((size_t)l * p.R + row) * 8 + 4 + cc] = (uint16_t)(zword >> 16);
             if (threadIdx.x == 64) TLD(32);
             // ---- epilogue 2: h' = h + (acc2 + br)  (same association as the reference, model.py:109-114) ----
             stack_mbar_wait(bar + F2B_ACC2, par, ab, p.err);
@@ -499,6 +585,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
             if (threadIdx.x == 64) TLD(33);
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
+                if (j == 1) named_bar_sync(1 + q, 128);
                 const int col = j * 64 + cc * 16;
                 float v[16], h[16];
                 tmem_ld16_nowait(acc2 + lane_off + col, v);
@@ -515,12 +602,19 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
                 emit(l + 1, j, v);
             }
             tmem_wait_st();
+            if (l + 1 < NL && stack_near(stack_dil(l + 1))) import_halo(l + 1);
+            finish(l + 1);
             if (threadIdx.x == 64) TLD(41);
             if (threadIdx.x == 64 && l < 30) TL(32 + l);
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (threadIdx.x == 0) TL(1);
+    if (threadIdx.x == 0) {
+        TL(1);
+        // the last CTA of this launch opens the next epoch (tags of this launch can then never validate again)
+        __threadfence();
+        if (atomicAdd(p.epoch + 1, 1u) == gridDim.x - 1) { p.epoch[1] = 0u; __threadfence(); atomicAdd(p.epoch, 1u); }
+    }
     if (warp == 1) tmem_dealloc<512>(tmem);
 }
