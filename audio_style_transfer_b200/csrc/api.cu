@@ -232,13 +232,14 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
         if (!cfg->gatys) target = 64;            // 64 chunks x 4 channel quads = 256 CTAs, all resident at 2 per SM; halves the partials
         c->gram_ours_tc = !cfg->gatys && cfg->precision == AST_PREC_BF16 && gram_ours_tc_supported(c->L) && !exp_switch("AST_B200_GRAM_OURS_CUDA");
         if (c->gram_ours_tc) target = 37;        // one CTA per SM (164 KB of smem): 37 chunks x 4 quads = 148 CTAs, one wave
-        target = std::max(2, (target + c->B - 1) / c->B);
+        // (the split does NOT depend on B: pair b of a batch then sums in the same order as the same pair alone, so a batch
+        // equals its pairs evaluated one by one bit for bit -- tests/test_gpu_configs.py)
         int rows = (c->T + target - 1) / target;
         rows = std::max(128, ((rows + 127) / 128) * 128);
         if (cfg->gatys && cfg->precision == AST_PREC_BF16) {
             // tensor-core Gram: one wave of CTAs, each accumulating its tiles in TMEM
             const int ntiles = c->T / 128;
-            int nch = std::max(1, std::min(ntiles, 148 / std::max(1, c->L * c->B)));
+            int nch = std::max(1, std::min(ntiles, 148 / std::max(1, c->L)));
             const int ct = (ntiles + nch - 1) / nch;
             rows = ct * 128;
         }

@@ -443,11 +443,20 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
                 const int e = (warp - 2) * 32 + lane;
                 const int slot = e % dn, rest = e / dn, c = rest & 3, hs = rest >> 2;      // slot fastest: coalesced
                 const bool active = hs < 2 && (hs == 0 ? has_up : has_dn);
+                const uint4* src[2];
+                uint4 vv[2][4];
+                if (active) {                          // both K-halves' lines are requested at once
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) {
+                        src[j] = ll_item((NL - m) & 1, hs == 0 ? tile - 1 : tile + 1, hs == 0 ? 1 : 0, j, slot, c);
+                        ll_fetch(src[j], vv[j]);
+                    }
+                }
 #pragma unroll
                 for (int j = 0; j < 2; ++j) {
                     if (active) {
                         uint32_t w[8];
-                        ll_wait_item(ll_item((NL - m) & 1, hs == 0 ? tile - 1 : tile + 1, hs == 0 ? 1 : 0, j, slot, c), tag, w, ab, p.err);
+                        ll_wait_item(src[j], vv[j], tag, w, ab, p.err);
                         const int wr = hs == 0 ? F2_HALO - dn + slot : F2_HALO + 128 + slot;
                         uint8_t* wb = gen + j * B2_WBUF + wr * 128;
                         *reinterpret_cast<uint4*>(wb + (((2 * c) ^ (wr & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);

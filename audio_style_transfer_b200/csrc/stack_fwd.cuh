@@ -168,20 +168,27 @@ __device__ __forceinline__ uint4 ll_load(const uint4* p) {
 __device__ __forceinline__ void red_relaxed_gpu_add(unsigned* p, unsigned v) {
     asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
-// Polls one 64-byte LL item (4 lines, LL_ROWS lines apart: the row slot is the fastest index so that the lanes of a
-// warp -- consecutive rows -- store and load contiguous bytes) until all 8 tags match; false after an abort.
-__device__ __forceinline__ bool ll_wait_item(const uint4* src, uint32_t tag, uint32_t (&w)[8], volatile unsigned* ab, unsigned* err) {
+// One 64-byte LL item = 4 lines, LL_ROWS lines apart (the row slot is the fastest index so that the lanes of a warp --
+// consecutive rows -- store and load contiguous bytes).  ll_fetch issues the four loads; ll_ready tells whether all 8 tags
+// match and extracts the 8 payload words; ll_wait_item re-polls until they do (false after an abort).
+__device__ __forceinline__ void ll_fetch(const uint4* src, uint4 (&v)[4]) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = ll_load(src + i * LL_ROWS);
+}
+__device__ __forceinline__ bool ll_ready(const uint4 (&v)[4], uint32_t tag, uint32_t (&w)[8]) {
+    bool ok = true;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { ok = ok && v[i].y == tag && v[i].w == tag; w[2 * i] = v[i].x; w[2 * i + 1] = v[i].z; }
+    return ok;
+}
+__device__ __forceinline__ bool ll_wait_item(const uint4* src, uint4 (&v)[4], uint32_t tag, uint32_t (&w)[8], volatile unsigned* ab,
+                                             unsigned* err) {
     unsigned spins = 0;
-    for (;;) {
-        uint4 v[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) v[i] = ll_load(src + i * LL_ROWS);
-        bool ok = true;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) { ok = ok && v[i].y == tag && v[i].w == tag; w[2 * i] = v[i].x; w[2 * i + 1] = v[i].z; }
-        if (ok) return true;
+    while (!ll_ready(v, tag, w)) {
         if (++spins > FS_SPIN_LIMIT || stack_aborted(ab)) { stack_abort(ab, err, 3u); return false; }
+        ll_fetch(src, v);
     }
+    return true;
 }
 
 __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __grid_constant__ FwdStackArgs p) {
@@ -502,11 +509,20 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
             const int e = (warp - 2) * 32 + lane;
             const int slot = e % d, rest = e / d, part = rest & 1, c = (rest >> 1) & 3, hs = rest >> 3;      // slot fastest: coalesced
             const bool active = hs < 2 && (hs == 0 ? has_up : has_dn);
+            const uint4* src[2];
+            uint4 v[2][4];
+            if (active) {                              // both K-halves' lines are requested at once: one L2 round trip, not two
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    src[j] = ll_item(i & 1, hs == 0 ? tile - 1 : tile + 1, hs == 0 ? 1 : 0, j, slot, c, part);
+                    ll_fetch(src[j], v[j]);
+                }
+            }
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
                 if (active) {
                     uint32_t w[8];
-                    ll_wait_item(ll_item(i & 1, hs == 0 ? tile - 1 : tile + 1, hs == 0 ? 1 : 0, j, slot, c, part), tag, w, ab, p.err);
+                    ll_wait_item(src[j], v[j], tag, w, ab, p.err);
                     const int wr = hs == 0 ? F2_HALO - d + slot : F2_HALO + 128 + slot;
                     uint8_t* wb = gen + (j * 2 + part) * F2_WBUF + wr * 128;
                     *reinterpret_cast<uint4*>(wb + (((2 * c) ^ (wr & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);

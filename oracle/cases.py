@@ -27,11 +27,25 @@ CASES = {
     # BASELINE.json sizes
     "t16384_cfg0":      (16384, [25], 0, None, False, 128, 128, 1),
     "t16384_cfg1":      (16384, [29], None, None, True, 128, 128, 1),
+    # BASELINE configs[2]: 4 s clip (time-sharded on the GPU), cfg0's layer set
+    "t65536_cfg2":      (65536, [25], 0, None, False, 128, 128, 1),
 }
+# "<case>_pN": the same case with the step input of pair N of a batch (BASELINE configs[3]): x = mu_law(content) +
+# N(0,1) drawn with seed 3 + N; targets unchanged.  Pair 0 is the plain case.
+PAIR_SEED0 = 3
 LAMBD = 100.0   # methods.py:256 default
 
 
+def pair_x(case, n):
+    """Step input of pair n of a batch built from `case` (n = 0: the case's own x)."""
+    return synth.step_input(case["c_mu"], seed=PAIR_SEED0 + n).astype(np.float64)
+
+
 def build_inputs(name, bias_scale=0.1):
+    if "_p" in name and name.rsplit("_p", 1)[1].isdigit():
+        base, n = name.rsplit("_p", 1)
+        case = build_inputs(base, bias_scale)
+        return dict(case, name=name, x=pair_x(case, int(n)))
     T, cont, stack, ids, gatys, nb, cnt, chunks = CASES[name]
     style = synth.resolve_style_ids(stack, ids)
     NL = synth.layers_needed(cont, style)

@@ -30,7 +30,11 @@ def fp32_floor(case, Pc, Ps, dx64):
 
 
 def grad_tol(prec, floor):
-    return max(TOL[prec]["grad"], (10.0 if prec == "fp32" else 100.0) * floor)
+    """BASELINE.json's tolerances: bf16 tier a flat 1e-2; fp32 tier 1e-4, or three times the measured distance of an fp32
+    CPU run of the same step from fp64 where that is larger (20..30 layers: ReLU sign flips).  The
+    floor is ONE sample of fp32 rounding noise with a different summation order; the largest ratio measured on B200 is
+    2.2 (t2048_ours_all30: 3.5e-4 against a floor of 1.6e-4), every other case is below 1.7."""
+    return TOL["bf16"]["grad"] if prec == "bf16" else max(TOL["fp32"]["grad"], 3.0 * floor)
 
 
 def make_step(case, prec, B=1, window=None, T=None, kernel_path="auto"):
@@ -69,6 +73,7 @@ def test_step_matches_oracle(name, prec):
     assert abs(lo[1] - losses[1]) <= tol["loss"] * max(abs(losses[1]), abs(losses[0]))
     assert lo[3] == 0.0
     floor = fp32_floor(case, Pc, Ps, dx)
+    print(f"{name}[{prec}]: grad rel-L2 {rel(g, dx):.2e} (fp32 CPU floor {floor:.2e}, tolerance {grad_tol(prec, floor):.2e})")
     assert rel(g, dx) <= grad_tol(prec, floor), (rel(g, dx), floor)
     st.close()
 
@@ -116,13 +121,13 @@ def test_index_probe_bit_exact(prec):
     st = StyleStep(T, [NL - 1], list(range(NL)), precision=prec)
     st.set_weights(w)
     st.embeds(x[None], style=False)
-    nl_exact = NL if prec == "fp32" else 0
+    # Every value (and every conv output before the 1x1) stays far below 2^16, so the bf16 hi/lo split is exact too:
+    # BOTH tiers must reproduce every layer bit for bit -- d = 1 .. 512 (layers 0..9, the far taps reach 4 tiles away)
+    # and the 512 -> 1 wrap (layers 10, 11).
+    assert max(np.abs(h).max() for h in H) < 2 ** 13
     for l in range(-1, NL):
         got = st.extract(l)[0].cpu().numpy().astype(np.float64)
-        if np.abs(H[l + 1]).max() < 2 ** (24 if prec == "fp32" else 16):
-            assert np.array_equal(got, H[l + 1]), f"layer {l}"
-            nl_exact = max(nl_exact, l + 1)
-    assert nl_exact >= 4
+        assert np.array_equal(got, H[l + 1]), f"layer {l} (d={1 << (max(l, 0) % 10)})"
     st.close()
 
 
@@ -163,9 +168,8 @@ def test_batch_of_pairs_equals_loop(prec):
     for i in range(B):
         lo, g = st1.step(xs[i:i + 1])
         assert torch.equal(st1.extract(case["NL"] - 1)[0], exB[i]), i      # encoder: bit for bit
-        # Gram split-K geometry depends on B, so sums differ in the last bits only
-        assert rel(g[0].cpu().numpy(), gB[i].cpu().numpy()) <= 1e-5, i
-        assert torch.allclose(lo[0], loB[i], rtol=1e-5), i
+        # the Gram split does not depend on B (csrc/api.cu): a pair inside a batch IS the pair alone
+        assert torch.equal(g[0], gB[i]) and torch.equal(lo[0], loB[i]), (i, rel(g[0].cpu().numpy(), gB[i].cpu().numpy()))
     stB.close(); st1.close()
 
 
