@@ -27,7 +27,7 @@ ERRORS = {-1: "AST_EINVAL", -2: "AST_ECUDA", -3: "AST_EUNSUPPORTED", -4: "AST_ES
 SYMBOLS = [
     "ast_create", "ast_destroy", "ast_last_error", "ast_version", "ast_workspace_bytes",
     "ast_set_weights", "ast_set_targets", "ast_embeds", "ast_step", "ast_step_graph", "ast_step_host",
-    "ast_step_forward", "ast_partials", "ast_step_backward", "ast_get_extract",
+    "ast_step_forward", "ast_partials", "ast_step_backward", "ast_get_extract", "ast_get_masks",
     "ast_launches_per_step", "ast_step_timed", "ast_check", "ast_uses_stack_kernels", "ast_stft_reg_noalloc",
     "ast_opt_create", "ast_opt_destroy", "ast_opt_workspace_bytes", "ast_opt_reset", "ast_opt_buffers", "ast_opt_advance",
     "ast_opt_status", "ast_opt_result", "ast_opt_epochs", "ast_opt_log", "ast_minimize",
@@ -119,6 +119,7 @@ def load(experiments: bool = False) -> C.CDLL:
     lib.ast_partials.argtypes = [vp, C.POINTER(vp), C.POINTER(i64)]
     lib.ast_step_backward.argtypes = [vp, vp, vp, vp]
     lib.ast_get_extract.argtypes = [vp, i32, vp, vp]
+    lib.ast_get_masks.argtypes = [vp, vp, vp, vp]
     lib.ast_launches_per_step.argtypes = [vp]
     lib.ast_step_timed.argtypes = [vp, vp, vp, vp, vp, vp]
     lib.ast_check.argtypes = [vp, vp]

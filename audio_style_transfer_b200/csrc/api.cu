@@ -616,6 +616,14 @@ extern "C" int ast_get_extract(ast_ctx* c, int32_t layer, float* d_out, void* st
     return AST_OK;
 }
 
+extern "C" int ast_get_masks(ast_ctx* c, uint32_t* d_hmask, uint32_t* d_zmask, void* stream) {
+    if (!c || !d_hmask || !d_zmask) return fail(AST_EINVAL, "null argument");
+    const size_t n = (size_t)c->NL * c->R * AST_MW * sizeof(uint32_t);
+    CK(cudaMemcpyAsync(d_hmask, c->hmask, n, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    CK(cudaMemcpyAsync(d_zmask, c->zmask, n, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return AST_OK;
+}
+
 // ---- CUDA graphs ---------------------------------------------------------------------------------
 // Captures whatever `body` enqueues on the context's private stream into an executable graph.
 template <typename F>

@@ -97,7 +97,7 @@ class GatysNet(object):
                  cnt_channels=128,
                  gatys=False,
                  style_lyr_ids=None,
-                 precision='bf16', seed=0, device=None, optimizer='scipy'):
+                 precision='bf16', seed=0, device=None, optimizer='scipy', random_init=False):
         if optimizer not in ('scipy', 'device'):
             raise ValueError("optimizer must be 'scipy' (the reference's SciPy L-BFGS-B on host buffers) or 'device'")
         self.optimizer = optimizer
@@ -110,6 +110,8 @@ class GatysNet(object):
         self.late = (batch_size - (batch_size // 4096) * 4000) // 2          # methods.py:39
         self.cont_lyr_ids = cont_lyr_ids
         self.seed = seed
+        self.random_init = bool(random_init)
+        self.precision = precision
         self.graph, self.embeds_c, self.embeds_s, self.gatys = self.build(
             batch_size, cont_lyr_ids, stack, nb_channels, cnt_channels, gatys, style_lyr_ids,
             precision=precision, device=device)
@@ -134,8 +136,9 @@ class GatysNet(object):
         """methods.py:79-84.  `checkpoint_path` is what the reference takes: the prefix of a TF V2 checkpoint
         (`<prefix>.index` + `<prefix>.data-*`, read by tf_checkpoint.py without TensorFlow; the plain variable names,
         as tf.train.Saver over tf.global_variables() restores them).  `.npz` weight files with the ast_set_weights
-        layouts are accepted too; if neither exists a seeded random-init encoder (masked.py:116-117) is used and that
-        is said out loud."""
+        layouts are accepted too.  A missing or unreadable checkpoint RAISES, as tf.train.Saver.restore does; a seeded
+        random-init encoder (masked.py:116-117) is used only when asked for (`random_init=True`, CLI --random_init /
+        --synthetic) or when `checkpoint_path` is None."""
         from . import tf_checkpoint
         path = str(self.checkpoint_path) if self.checkpoint_path else ''
         if path and tf_checkpoint.is_bundle(path):
@@ -143,9 +146,14 @@ class GatysNet(object):
         elif path.endswith('.npz') and os.path.exists(path):
             d = np.load(path)
             w = synth.EncoderWeights(d['W0'], d['b0'], d['Wd'], d['bd'], d['Wr'], d['br'])
-        else:
-            print(f'[ast_b200] checkpoint {self.checkpoint_path!r} not found: random-init encoder, seed {self.seed}')
+        elif self.random_init or not path:
+            print(f'[ast_b200] random-init encoder (seed {self.seed}) on request: no checkpoint is read')
             w = synth.make_weights(self.graph.n_layers, seed=self.seed)
+        else:
+            raise FileNotFoundError(
+                f'checkpoint {self.checkpoint_path!r} is neither a TF V2 bundle prefix (<prefix>.index + .data-*) nor an .npz '
+                'weight file; pass --random_init (or --synthetic) to run with a seeded random-init encoder instead')
+        self.weights = w
         self.graph.set_weights(w)
 
     def get_embeds(self, sess, aud, is_content=True):
@@ -158,15 +166,56 @@ class GatysNet(object):
         out = Ec if is_content else Gn
         return out[0].cpu().numpy()
 
-    def get_style_phi(self, sess, filename, max_examples=5, show_mat=True):
-        """methods.py:97-111: mean style embedding over <= max_examples consecutive chunks."""
+    def _style_chunks(self, filename, max_examples=5):
+        """The consecutive chunks get_style_phi averages over (methods.py:100-108)."""
         audio = filename if isinstance(filename, np.ndarray) else load_audio(filename, sr=self.sr, audio_channel=0)[0]
         I = []
         i = 0
         while i + self.batch_size <= min(len(audio), max_examples * self.batch_size):
-            I.append(self.get_embeds(sess, audio[i: i + self.batch_size], is_content=False))
+            I.append(np.asarray(audio[i: i + self.batch_size]))
             i += self.batch_size
-        return np.mean(I, axis=0)
+        return I
+
+    def embeds_batched(self, chunks, content=False, style=True):
+        """The embeddings of several equally long clips from ONE B = len(chunks) forward (ast_embeds with B > 1)
+        instead of len(chunks) B = 1 forwards (the reference runs them one session.run at a time, methods.py:97-111,
+        192-212).  Pairs of a batch are bit-identical to single-pair runs, so the result equals the
+        looped one bit for bit.  Returns numpy (Ec [n, T, cols] | None, Gn [n, ...] | None)."""
+        from .step import StyleStep
+        n = len(chunks)
+        if n == 0:
+            raise ValueError('no full chunk of batch_size samples in the audio')
+        g = self.graph
+        x = mu_law_numpy(np.stack([np.asarray(c)[: self.batch_size] for c in chunks])).astype(np.float32)
+        if n == 1:
+            ctx = g
+        else:
+            ctx = StyleStep(g.T, g.cont_ids, g.style_ids, g.gatys, g.nb_channels, g.cnt_channels, B=n,
+                            precision=g.precision, device=g.device)
+            ctx.set_weights(self.weights)
+        try:
+            Ec, Gn = ctx.embeds(x, content=content, style=style)
+            Ec = None if Ec is None else Ec.cpu().numpy()
+            Gn = None if Gn is None else Gn.cpu().numpy()
+        finally:
+            if ctx is not g:
+                ctx.close()
+        return Ec, Gn
+
+    def get_style_phi(self, sess, filename, max_examples=5, show_mat=True):
+        """methods.py:97-111: mean style embedding over <= max_examples consecutive chunks -- one batched forward."""
+        _, Gn = self.embeds_batched(self._style_chunks(filename, max_examples))
+        return np.mean(list(Gn), axis=0)
+
+    def precompute_targets(self, aud, source, target, max_examples=5):
+        """Everything GatysNet.run needs before the loop (methods.py:192-212) -- phi_c, phi(content clip), the target's
+        and the source's mean style embedding -- from ONE batched forward over <= 1 + 5 + 5 clips.
+        Returns (phi_c, phi, phi_t, phi_s) with the values of the one-by-one calls, bit for bit."""
+        ct, cs = self._style_chunks(target, max_examples), self._style_chunks(source, max_examples)
+        Ec, Gn = self.embeds_batched([aud] + ct + cs, content=True, style=True)
+        phi_t = np.mean(list(Gn[1: 1 + len(ct)]), axis=0)
+        phi_s = np.mean(list(Gn[1 + len(ct):]), axis=0)
+        return Ec[0], Gn[0], phi_t, phi_s
 
     def define_loss(self, name, stl_emb, cnt_emb, lambd, gamma, gpu=None):
         """methods.py:113-138: bakes the targets and loss weights; returns the evaluation closure that
@@ -254,8 +303,6 @@ class GatysNet(object):
     def run(self, cont_file, source, target, epochs, lambd=0.1, gamma=0.1, audio_channel=0, start=1.0):
         """methods.py:183-216.  File names may also be numpy arrays of audio in [-1, 1)."""
         self.load_model(None)
-        phi_t = self.get_style_phi(None, target)
-        phi_s = self.get_style_phi(None, source, show_mat=False)
         ld = lambda f: f if isinstance(f, np.ndarray) else load_audio(f, sr=self.sr, audio_channel=audio_channel)[0]
         aud = ld(cont_file)
         st = max(int(start * self.sr - self.late), 0)
@@ -264,15 +311,14 @@ class GatysNet(object):
             os.makedirs(self.savepath, exist_ok=True)
             write_wav(os.path.join(self.savepath, 'ori.wav'), aud[self.late:-self.late], self.sr)
             write_wav(os.path.join(self.savepath, 'style.wav'), ld(target)[st: st + self.batch_size][self.late:-self.late], self.sr)
-        phi_c = self.get_embeds(None, aud)
-        phi = self.get_embeds(None, aud, is_content=False)
+        phi_c, phi, phi_t, phi_s = self.precompute_targets(aud, ld(source), ld(target))
         phi = l2_normalize(phi + phi_t - phi_s)                               # methods.py:211-212
         self.l_bfgs(None, phi_c, phi, epochs=epochs, lambd=lambd, gamma=gamma)
         return inv_mu_law_numpy(self.x)[0]
 
 
 def get_dir(dir, args):
-    return gt_s_path(crt_t_fol(dir), **{k: v for k, v in vars(args).items() if k not in ('seed', 'precision', 'synthetic', 'optimizer')})
+    return gt_s_path(crt_t_fol(dir), **{k: v for k, v in vars(args).items() if k not in ('seed', 'precision', 'synthetic', 'optimizer', 'random_init')})
 
 
 def get_fpath(fn, args):
@@ -291,7 +337,7 @@ def piece_work(args):
         content, style = map(lambda name: get_fpath(name, args), [args.cont_fn, args.style_fn])
     test = GatysNet(savepath, args.ckpt_path, logdir, figdir, args.stack, args.batch_size, args.sr, args.cont_lyrs,
                     args.channels, args.cnt_channels, args.gatys, args.style_lyrs, precision=args.precision, seed=args.seed,
-                    optimizer=args.optimizer)
+                    optimizer=args.optimizer, random_init=args.random_init or args.synthetic)
     return test.run(content, content, style, epochs=args.epochs, lambd=args.lambd, gamma=args.gamma, start=args.start)
 
 
@@ -315,13 +361,15 @@ def build_parser():
     parser.add_argument('--start', nargs='?', type=float, default=1.0)
     parser.add_argument('--gatys', nargs='?', type=bool, default=False, const=True)
     parser.add_argument('--ckpt_path', nargs='?', default='./nsynth/model/wavenet-ckpt/model.ckpt-200000',
-                        help="path to the pretrained model's checkpoint (TF checkpoint prefix, or .npz with W0,b0,Wd,bd,Wr,br; else random init)")
+                        help="path to the pretrained model's checkpoint (TF checkpoint prefix, or .npz with W0,b0,Wd,bd,Wr,br)")
     parser.add_argument('--dir', help='path to source files', nargs='?', default='./data/src')
     parser.add_argument('--outdir', help='path to output', nargs='?', default='./data/out')
     parser.add_argument('--logdir', help='path to logs', nargs='?', default='./log')
     parser.add_argument('--cmt')
     # additions (not in the reference)
-    parser.add_argument('--seed', type=int, default=0, help='seed of the random-init encoder when no checkpoint is readable')
+    parser.add_argument('--seed', type=int, default=0, help='seed of the random-init encoder (--random_init / --synthetic)')
+    parser.add_argument('--random_init', action='store_true',
+                        help='run with a seeded random-init encoder instead of a checkpoint (without it a missing --ckpt_path is an error, as in the reference)')
     parser.add_argument('--precision', default='bf16', choices=['bf16', 'fp32'])
     parser.add_argument('--optimizer', default='scipy', choices=['scipy', 'device'],
                         help="scipy: SciPy L-BFGS-B on host buffers, as the reference; device: the same algorithm resident on the GPU")

@@ -201,6 +201,18 @@ class StyleStep:
             _lib.check(self.lib.ast_get_extract(self._h, int(layer), _ptr(out), _stream()), self.lib)
         return out
 
+    def masks(self):
+        """ReLU sign masks of the last forward as bool arrays (hmask, zmask), each [n_layers, B, T, 128] (ast_get_masks)."""
+        n = self.n_layers * self.B * self.T * 4
+        hm = torch.empty(n, dtype=torch.int32, device=self.dev)
+        zm = torch.empty(n, dtype=torch.int32, device=self.dev)
+        with torch.cuda.device(self.dev):
+            _lib.check(self.lib.ast_get_masks(self._h, _ptr(hm), _ptr(zm), _stream()), self.lib)
+        torch.cuda.synchronize(self.dev)
+        unpack = lambda m: np.unpackbits(m.cpu().numpy().view(np.uint8), bitorder="little").astype(bool).reshape(
+            self.n_layers, self.B, self.T, 128)
+        return unpack(hm), unpack(zm)
+
     @property
     def uses_stack_kernels(self) -> bool:
         """True when the encoder forward / backward run as ONE cooperative kernel each (clip fits one tile per SM)."""

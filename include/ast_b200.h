@@ -138,6 +138,14 @@ int  ast_step_backward(ast_ctx* ctx, float* d_losses, float* d_grad, void* strea
  * channel-wise Gram, the style extracts) only; any other layer returns AST_ESTATE ("not retained"). */
 int  ast_get_extract(ast_ctx* ctx, int32_t layer, float* d_out, void* stream);
 
+/* The ReLU sign masks the last forward left for the backward (TF's ReluGrad: mask = output > 0; reference
+ * model.py:99,107 + tf.gradients, methods.py:133-137), one bit per element, bit (c % 32) of word c / 32:
+ *   d_hmask [n_layers][B*T][4] uint32: h_l > 0 (input of layer l's first ReLU, l = 0 .. n_layers-1),
+ *   d_zmask [n_layers][B*T][4] uint32: z_l > 0 (output of layer l's dilated conv).
+ * Debug/parity: lets a test impose the device's masks on the oracle's backward, so that the gradient comparison is
+ * not dominated by the handful of sign bits that legitimately differ between two roundings of the same forward. */
+int  ast_get_masks(ast_ctx* ctx, uint32_t* d_hmask, uint32_t* d_zmask, void* stream);
+
 /* Asynchronous error check.  ast_step / ast_step_graph / ast_step_forward / ast_step_backward only enqueue work; the
  * whole-stack kernels hand rows between SMs through flags with BOUNDED waits, and a wait that expires (profiler, debugger,
  * heavy preemption) invalidates that evaluation.  ast_check synchronises `stream` and returns AST_ECUDA (sticky until this

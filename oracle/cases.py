@@ -64,9 +64,9 @@ def oracle_targets(case):
                            case["gatys"], case["nb"], case["cnt"])
 
 
-def oracle_step(case, Pc, Ps, return_aux=False):
+def oracle_step(case, Pc, Ps, return_aux=False, masks=None, fwd=None):
     return step_np.step(case["x"], case["w"], Pc, Ps, case["cont"], case["style"], case["gatys"], case["lambd"], 0.0,
-                        case["nb"], case["cnt"], return_aux=return_aux)
+                        case["nb"], case["cnt"], return_aux=return_aux, masks=masks, fwd=fwd)
 
 
 def summary(case, Pc, Ps, losses, dx, aux):

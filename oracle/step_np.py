@@ -118,7 +118,7 @@ def embeds(x, w, cont_ids, style_ids, gatys, nb_channels=128, cnt_channels=128, 
 
 
 def step(x, w, Pc, Ps, cont_ids, style_ids, gatys, lambd, gamma=0.0,
-         nb_channels=128, cnt_channels=128, n_layers=None, return_aux=False):
+         nb_channels=128, cnt_channels=128, n_layers=None, return_aux=False, masks=None, fwd=None):
     """One (loss, dloss/dx) evaluation: define_loss (methods.py:113-125) + the gradient that
     ScipyOptimizerInterface asks TF for (methods.py:133-137), var_list = [x] only.
 
@@ -126,12 +126,15 @@ def step(x, w, Pc, Ps, cont_ids, style_ids, gatys, lambd, gamma=0.0,
     Returns (losses, dx) with losses = (total, content, style, regulariser).
     gamma != 0 adds the STFT regulariser (methods.py:121-123, oracle/stft_reg.py); with gamma == 0 the
     regulariser slot reports 0 (the reference evaluates it for logging only, methods.py:167).
+    masks = (hmask, zmask), bool [n_layers, T, C] each, replaces the backward's own ReluGrad masks (H[l] > 0, Z[l] > 0)
+    by given ones (tests impose the device's masks so that sign bits flipped by rounding do not dominate the comparison).
+    fwd = (H, Z) of an earlier call on the same x (aux["H"], aux["Z"]) skips the forward.
     Backward formulas: SURVEY.md 8(a)."""
     dt = x.dtype
     cont_ids, style_ids = list(cont_ids), list(style_ids)
     if n_layers is None:
         n_layers = min(max(cont_ids + style_ids), 29) + 1
-    H, Z = encoder_forward(x, w, n_layers)
+    H, Z = encoder_forward(x, w, n_layers) if fwd is None else fwd
     T = x.shape[0]
 
     # ---- heads and losses ------------------------------------------------------------------
@@ -180,9 +183,9 @@ def step(x, w, Pc, Ps, cont_ids, style_ids, gatys, lambd, gamma=0.0,
         if l in dF:
             g = g + dF[l]
         dr = g @ w.Wr[l].astype(dt).T
-        dz = dr * (Z[l] > 0)                                         # ReluGrad: mask = output > 0
+        dz = dr * ((Z[l] > 0) if masks is None else masks[1][l])    # ReluGrad: mask = output > 0
         da = conv3_T(dz, w.Wd[l].astype(dt), dilation(l))
-        g = g + da * (H[l] > 0)
+        g = g + da * ((H[l] > 0) if masks is None else masks[0][l])
     dxs = conv3_T(g, w.W0.astype(dt), 1)[:, 0]
     dx = dxs / dt.type(128.0)
     reg = 0.0

@@ -44,3 +44,31 @@ def test_cli_synthetic_run(tmp_path):
         ['c', 's', '--synthetic', '--epochs', '1', '--batch_size', '4096', '--stack', '0', '--cont_lyrs', '9',
          '--outdir', str(tmp_path / 'out'), '--logdir', str(tmp_path / 'log')]))
     assert out.shape == (4096,) and np.all(np.isfinite(out))
+
+
+def test_batched_target_precompute_equals_one_by_one_bit_for_bit(tmp_path):
+    """the <= 1 + 5 + 5 forwards before the loop (methods.py:97-111,192-212) as ONE B > 1 ast_embeds call."""
+    from audio_style_transfer_b200.methods import GatysNet
+    T = 4096
+    net = GatysNet(savepath=None, checkpoint_path=None, batch_size=T, stack=0, cont_lyr_ids=[9], seed=0)
+    net.load_model(None)
+    aud = synth.content_audio(T, seed=1)
+    target = synth.style_audio(T, seed=2, chunks=5)
+    source = synth.content_audio(3 * T + 100, seed=3)                 # 3 full chunks + a tail that is dropped
+    phi_c, phi, phi_t, phi_s = net.precompute_targets(aud, source, target)
+    one = lambda a, c: net.get_embeds(None, a, is_content=c)
+    assert np.array_equal(phi_c, one(aud, True))
+    assert np.array_equal(phi, one(aud, False))
+    assert np.array_equal(phi_t, np.mean([one(target[i * T:(i + 1) * T], False) for i in range(5)], axis=0))
+    assert np.array_equal(phi_s, np.mean([one(source[i * T:(i + 1) * T], False) for i in range(3)], axis=0))
+    assert np.array_equal(net.get_style_phi(None, target), phi_t)
+
+
+def test_missing_checkpoint_raises_like_saver_restore(tmp_path):
+    """methods.py:79-84: Saver.restore raises on a missing checkpoint; random init needs an explicit opt-in."""
+    from audio_style_transfer_b200.methods import GatysNet
+    net = GatysNet(savepath=None, checkpoint_path=str(tmp_path / 'model.ckpt-200000'), batch_size=4096, stack=0, cont_lyr_ids=[9])
+    with pytest.raises(FileNotFoundError):
+        net.load_model(None)
+    net.random_init = True
+    net.load_model(None)

@@ -30,11 +30,37 @@ def fp32_floor(case, Pc, Ps, dx64):
 
 
 def grad_tol(prec, floor):
-    """BASELINE.json's tolerances: bf16 tier a flat 1e-2; fp32 tier 1e-4, or three times the measured distance of an fp32
-    CPU run of the same step from fp64 where that is larger (20..30 layers: ReLU sign flips).  The
-    floor is ONE sample of fp32 rounding noise with a different summation order; the largest ratio measured on B200 is
-    2.2 (t2048_ours_all30: 3.5e-4 against a floor of 1.6e-4), every other case is below 1.7."""
-    return TOL["bf16"]["grad"] if prec == "bf16" else max(TOL["fp32"]["grad"], 3.0 * floor)
+    """Bound on the RAW gradient distance (each side with its own ReLU masks).  bf16 tier: BASELINE.json's flat 1e-2.
+    fp32 tier: 1e-4, or ten times the distance of an fp32 CPU run of the same step from fp64 where that is larger.  The
+    raw figure of a 20..30-layer case is decided by a handful of ReLU sign bits that two roundings of the same forward
+    legitimately disagree on (measured on B200, t16384_cfg0: ONE flipped bit near t = 11328 is 3.0e-4 of the gradient,
+    everything else 1.5e-7), so it is a loose secondary bound; the strict statement is check_with_device_masks."""
+    return TOL["bf16"]["grad"] if prec == "bf16" else max(TOL["fp32"]["grad"], 10.0 * floor)
+
+
+# a sign bit may differ from the oracle's only where the fp64 value is within rounding of zero: |v| <= FLIP_EPS * rms(v)
+FLIP_EPS = {"fp32": 2e-5, "bf16": 2e-2}
+
+
+def check_with_device_masks(st, case, Pc, Ps, aux, g, prec, b=0):
+    """The strict gradient statement: BASELINE.json's tolerance (1e-4 fp32 tier, 1e-2 bf16 tier), no cushion, against the
+    oracle's backward evaluated with the DEVICE's ReLU sign masks (ast_get_masks), plus: every sign bit that differs from
+    the oracle's own sits on a value within rounding of zero.  Returns (masked distance, differing bits)."""
+    hm, zm = st.masks()
+    hm, zm = hm[:, b], zm[:, b]
+    nflip = 0
+    for dev, ref in ((hm, aux["H"]), (zm, aux["Z"])):
+        for l in range(case["NL"]):
+            diff = dev[l] != (ref[l] > 0)
+            n = int(diff.sum())
+            if n:
+                nflip += n
+                worst = float(np.abs(ref[l][diff]).max()) / float(np.sqrt(np.mean(ref[l] ** 2)))
+                assert worst <= FLIP_EPS[prec], (l, n, worst)
+    _, dxm = cases.oracle_step(case, Pc, Ps, masks=(hm, zm), fwd=(aux["H"], aux["Z"]))
+    e = rel(g, dxm)
+    assert e <= TOL[prec]["grad"], (e, nflip)
+    return e, nflip
 
 
 def make_step(case, prec, B=1, window=None, T=None, kernel_path="auto"):
@@ -73,7 +99,9 @@ def test_step_matches_oracle(name, prec):
     assert abs(lo[1] - losses[1]) <= tol["loss"] * max(abs(losses[1]), abs(losses[0]))
     assert lo[3] == 0.0
     floor = fp32_floor(case, Pc, Ps, dx)
-    print(f"{name}[{prec}]: grad rel-L2 {rel(g, dx):.2e} (fp32 CPU floor {floor:.2e}, tolerance {grad_tol(prec, floor):.2e})")
+    em, nflip = check_with_device_masks(st, case, Pc, Ps, aux, g, prec)
+    print(f"{name}[{prec}]: grad rel-L2 {em:.2e} with the device's masks ({nflip} sign bits differ), raw {rel(g, dx):.2e} "
+          f"(fp32 CPU floor {floor:.2e})")
     assert rel(g, dx) <= grad_tol(prec, floor), (rel(g, dx), floor)
     st.close()
 
@@ -85,7 +113,7 @@ def test_baseline_size_matches_oracle_and_golden(name, prec, golden_dir):
     with the committed golden vectors, then the CUDA step against both."""
     case = cases.build_inputs(name)
     Pc, Ps = cases.oracle_targets(case)
-    losses, dx = cases.oracle_step(case, Pc, Ps)
+    losses, dx, aux = cases.oracle_step(case, Pc, Ps, return_aux=True)
     gold = np.load(golden_dir / f"{name}.npz")
     assert np.allclose(losses[:3], gold["losses"], rtol=1e-9)
     assert rel(dx[::int(gold["dx_stride"])], gold["dx"]) <= 1e-8
@@ -96,8 +124,9 @@ def test_baseline_size_matches_oracle_and_golden(name, prec, golden_dir):
     tol = TOL[prec]
     assert abs(lo[0] - losses[0]) <= tol["loss"] * abs(losses[0])
     floor = fp32_floor(case, Pc, Ps, dx)
-    print(f"{name}[{prec}]: loss rel {abs(lo[0] - losses[0]) / abs(losses[0]):.2e} grad rel-L2 {rel(g, dx):.2e} "
-          f"(fp32 CPU floor {floor:.2e})")
+    em, nflip = check_with_device_masks(st, case, Pc, Ps, aux, g, prec)
+    print(f"{name}[{prec}]: loss rel {abs(lo[0] - losses[0]) / abs(losses[0]):.2e} grad rel-L2 {em:.2e} with the device's "
+          f"masks ({nflip} sign bits differ), raw {rel(g, dx):.2e} (fp32 CPU floor {floor:.2e})")
     assert rel(g, dx) <= grad_tol(prec, floor), (rel(g, dx), floor)
     # the SciPy-facing host entry point returns the same numbers (float64 each way, CUDA graph inside)
     lh, gh = st.step_host(case["x"])
