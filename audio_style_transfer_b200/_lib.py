@@ -22,12 +22,14 @@ SO_EXP = PKG / "libast_b200_exp.so"      # the same sources with -DAST_EXPERIMEN
 AST_PREC_FP32 = 0
 AST_PREC_BF16 = 1
 AST_MAX_IDS = 32
+AST_HALO_ROWS = 1024
 ERRORS = {-1: "AST_EINVAL", -2: "AST_ECUDA", -3: "AST_EUNSUPPORTED", -4: "AST_ESTATE"}
 
 SYMBOLS = [
     "ast_create", "ast_destroy", "ast_last_error", "ast_version", "ast_workspace_bytes",
     "ast_set_weights", "ast_set_targets", "ast_embeds", "ast_step", "ast_step_graph", "ast_step_host",
     "ast_step_forward", "ast_partials", "ast_step_backward", "ast_get_extract", "ast_get_masks",
+    "ast_segments", "ast_step_forward_seg", "ast_step_backward_seg", "ast_segment_buffer",
     "ast_launches_per_step", "ast_step_timed", "ast_check", "ast_uses_stack_kernels", "ast_stft_reg_noalloc",
     "ast_opt_create", "ast_opt_destroy", "ast_opt_workspace_bytes", "ast_opt_reset", "ast_opt_buffers", "ast_opt_advance",
     "ast_opt_status", "ast_opt_result", "ast_opt_epochs", "ast_opt_log", "ast_minimize",
@@ -42,7 +44,7 @@ class AstConfig(C.Structure):
         ("gatys", C.c_int32), ("nb_channels", C.c_int32), ("cnt_channels", C.c_int32),
         ("precision", C.c_int32),
         ("total_T", C.c_int64), ("win_begin", C.c_int64), ("own_begin", C.c_int64), ("own_end", C.c_int64),
-        ("device", C.c_int32), ("kernel_path", C.c_int32),
+        ("device", C.c_int32), ("kernel_path", C.c_int32), ("halo_exchange", C.c_int32),
     ]
 
 
@@ -120,6 +122,10 @@ def load(experiments: bool = False) -> C.CDLL:
     lib.ast_step_backward.argtypes = [vp, vp, vp, vp]
     lib.ast_get_extract.argtypes = [vp, i32, vp, vp]
     lib.ast_get_masks.argtypes = [vp, vp, vp, vp]
+    lib.ast_segments.argtypes = [vp]
+    lib.ast_step_forward_seg.argtypes = [vp, vp, i32, vp]
+    lib.ast_step_backward_seg.argtypes = [vp, i32, vp, vp, vp]
+    lib.ast_segment_buffer.argtypes = [vp, i32, i32, C.POINTER(vp)]
     lib.ast_launches_per_step.argtypes = [vp]
     lib.ast_step_timed.argtypes = [vp, vp, vp, vp, vp, vp]
     lib.ast_check.argtypes = [vp, vp]
@@ -129,6 +135,7 @@ def load(experiments: bool = False) -> C.CDLL:
         lib.ast_debug_timeline.argtypes = [vp]
         lib.ast_debug_tl_layer.argtypes = [i32]
         lib.ast_debug_skip_publish.argtypes = [i32]
+        lib.ast_debug_group_tiles.argtypes = [i32]
     lib.ast_opt_create.argtypes = [C.POINTER(AstOptConfig), C.POINTER(vp)]
     lib.ast_opt_destroy.argtypes = [vp]
     lib.ast_opt_workspace_bytes.argtypes = [vp]

@@ -63,6 +63,7 @@ struct ast_ctx {
     uint32_t* hmask;   // [NL+1][R][4]
     uint32_t* zmask;   // [NL][R][4]
     float* g;          // [R][128]
+    float* g_alt;      // [R][128]: second running-gradient buffer (backward segments ping-pong, stack_bwd.cuh)
     float* dz[2];      // fp32 mode: [R][128] fp32 each
     float* dF;         // [n_head][R][128]
     float* scratch3R;
@@ -257,6 +258,7 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
     DA(c->hmask, (size_t)(c->NL + 1) * c->R * AST_MW);
     DA(c->zmask, (size_t)c->NL * c->R * AST_MW);
     DA(c->g, RC);
+    if (c->prec == AST_PREC_BF16) { DA(c->g_alt, RC); } else c->g_alt = nullptr;   // backward segments ping-pong between g and g_alt
     if (c->prec == AST_PREC_FP32) { DA(c->dz[0], RC); DA(c->dz[1], RC); } else { c->dz[0] = c->dz[1] = nullptr; }
     DA(c->dF, (size_t)c->n_head * RC);
     DA(c->scratch3R, (size_t)3 * c->R);
@@ -297,6 +299,12 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
         // cfg->kernel_path: AST_PATH_PER_LAYER = one kernel per layer both ways, AST_PATH_PER_LAYER_BWD = whole-stack forward only
         c->use_stack = tc_stack_ok(c->tc) && cfg->kernel_path != AST_PATH_PER_LAYER;
         c->use_stack_bwd = c->use_stack && cfg->kernel_path != AST_PATH_PER_LAYER_BWD;
+        if (cfg->halo_exchange) {
+            if (!c->use_stack_bwd) { ast_destroy(c); return fail(AST_EUNSUPPORTED, "halo_exchange needs the whole-stack kernels (kernel_path auto)"); }
+            tc_plan_segments(c->tc, true);
+        }
+    } else if (cfg->halo_exchange) {
+        ast_destroy(c); return fail(AST_EUNSUPPORTED, "halo_exchange is a tensor-core tier (AST_PREC_BF16) feature");
     }
     if (cudaDeviceSynchronize() != cudaSuccess || cudaGetLastError() != cudaSuccess) { ast_destroy(c); return fail(AST_ECUDA, "context setup failed"); }
     *out = c;
@@ -396,7 +404,8 @@ static int setup_regulariser(ast_ctx* c) {
 // ---- forward --------------------------------------------------------------------------------
 // keep_all: every H[i] is written to global memory (ast_embeds / ast_get_extract); the optimisation step keeps only
 // what its heads read -- the whole-stack kernel holds the residual stream in TMEM.
-static int run_encoder(ast_ctx* c, const float* d_x, cudaStream_t s, bool keep_all) {
+static int n_segments(const ast_ctx* c) { return (c->tc && c->use_stack_bwd) ? tc_segments(c->tc) : 1; }
+static int run_encoder(ast_ctx* c, const float* d_x, cudaStream_t s, bool keep_all, int seg = -1) {
     if (c->tc && c->use_stack) {
         unsigned char keep[33];
         for (int i = 0; i <= c->NL; ++i) keep[i] = keep_all ? 1 : 0;
@@ -404,7 +413,7 @@ static int run_encoder(ast_ctx* c, const float* d_x, cudaStream_t s, bool keep_a
         if (!c->cfg.gatys)                      // channel-wise Gram and its gradient read the fp32 extracts
             for (int i = 0; i < c->L; ++i) keep[c->style_layer[i] + 1] = 1;
         memcpy(c->h_kept, keep, sizeof(keep));
-        if (tc_forward_stack(c->tc, d_x, c->W0, c->b0, c->bd, c->br, c->H, c->zmask, c->hmask, c->f_slot, keep, s) != 0)
+        if (tc_forward_stack(c->tc, d_x, c->W0, c->b0, c->bd, c->br, c->H, c->zmask, c->hmask, c->f_slot, keep, seg, s) != 0)
             return fail(AST_ECUDA, "whole-stack forward launch failed: %s", cudaGetErrorString(cudaGetLastError()));
         return AST_OK;
     }
@@ -454,14 +463,19 @@ static void run_partials(ast_ctx* c, const float* d_x, cudaStream_t s, bool fuse
                            c->reg_own_f_lo, c->reg_own_f_hi, c->reg_sgn, c->reg_fpart, c->reg_dadx, tail + c->B, s);
 }
 
-static int step_forward_impl(ast_ctx* c, const float* d_x, void* stream, bool fused) {
+// seg < 0: the whole forward.  seg >= 0 (time shards that exchange halos): encoder segment `seg` only; the last segment
+// is followed by the partial sums.
+static int step_forward_impl(ast_ctx* c, const float* d_x, void* stream, bool fused, int seg = -1) {
     if (!c || !d_x) return fail(AST_EINVAL, "null argument");
     if (!c->have_w || !c->have_t) return fail(AST_ESTATE, "ast_set_weights and ast_set_targets must precede a step");
+    const int nseg = n_segments(c);
+    if (seg >= nseg) return fail(AST_EINVAL, "segment %d outside 0..%d", seg, nseg - 1);
     cudaStream_t s = (cudaStream_t)stream;
     const int before = ast_launch_counter;
-    const int re = run_encoder(c, d_x, s, false);
+    const int re = run_encoder(c, d_x, s, false, nseg > 1 ? seg : -1);
     if (re != AST_OK) return re;
-    run_partials(c, d_x, s, fused);
+    if (seg < 0 || seg == nseg - 1) run_partials(c, d_x, s, fused);
+    if (seg > 0) { c->launches_fwd += ast_launch_counter - before; c->launches_per_step = c->launches_fwd + c->launches_bwd; CK(cudaGetLastError()); return AST_OK; }
     c->launches_fwd = ast_launch_counter - before;
     c->launches_per_step = c->launches_fwd + c->launches_bwd;
     CK(cudaGetLastError());
@@ -499,19 +513,26 @@ static HeadArgs head_args(ast_ctx* c, bool with_targets, float* losses, bool fus
 }
 
 // ---- backward -------------------------------------------------------------------------------
-static int step_backward_impl(ast_ctx* c, float* d_losses, float* d_grad, void* stream, bool fused) {
+// seg < 0: the whole backward.  seg >= 0: the heads + head gradients go with the TOP segment (seg == nseg-1, called
+// first), the start-conv adjoint and the gamma term with segment 0 (called last).
+static int step_backward_impl(ast_ctx* c, float* d_losses, float* d_grad, void* stream, bool fused, int seg = -1) {
     if (!c || !d_losses || !d_grad) return fail(AST_EINVAL, "null argument");
     if (!c->have_w || !c->have_t) return fail(AST_ESTATE, "ast_set_weights and ast_set_targets must precede a step");
+    const int nseg = n_segments(c);
+    if (seg >= nseg) return fail(AST_EINVAL, "segment %d outside 0..%d", seg, nseg - 1);
+    if (nseg == 1) seg = -1;
+    const bool do_top = seg < 0 || seg == nseg - 1, do_bottom = seg <= 0;
     cudaStream_t s = (cudaStream_t)stream;
     const int bwd_before = ast_launch_counter;
-    launch_heads(head_args(c, true, d_losses, fused), s);
+    if (do_top) launch_heads(head_args(c, true, d_losses, fused), s);
     // Gatys + tensor cores: the style gradient of an extract is fused into the backward layer kernel unless the
     // same extract also carries a content term (then the standalone kernel fills its dF buffer first)
     bool is_cont[30];
     for (int l = 0; l < 30; ++l) is_cont[l] = false;
     for (int i = 0; i < c->n_cont; ++i) is_cont[c->cont_layer[i]] = true;
     const bool fuse_sg = c->cfg.gatys && c->tc;
-    if (fuse_sg) {
+    if (!do_top) { /* head gradients were formed with the top segment */ }
+    else if (fuse_sg) {
         int hos[AST_MAX_IDS];
         for (int i = 0; i < c->L; ++i) hos[i] = is_cont[c->style_layer[i]] ? c->head_of_slot[i] : -1;
         tc_style_grad(c->tc, c->L, hos, s);
@@ -519,7 +540,7 @@ static int step_backward_impl(ast_ctx* c, float* d_losses, float* d_grad, void* 
     else if (c->cfg.gatys) launch_style_grad_gatys(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
     else if (c->gram_ours_tc && !exp_switch("AST_B200_SGO_CUDA")) launch_style_grad_ours_tc(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
     else              launch_style_grad_ours(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
-    {
+    if (do_top) {
         bool init[30];
         for (int l = 0; l < 30; ++l) init[l] = false;
         for (int i = 0; i < c->L; ++i) init[c->style_layer[i]] = true;
@@ -539,7 +560,7 @@ static int step_backward_impl(ast_ctx* c, float* d_losses, float* d_grad, void* 
             if (fuse_sg && l >= 1 && c->f_slot[l - 1] >= 0 && !is_cont[l - 1]) { sg_slot[l] = c->f_slot[l - 1]; df_idx[l] = -1; }
         }
         // the start-conv adjoint's channel dots are taken from the final running gradient while it is still in registers
-        if (tc_backward_stack(c->tc, c->hmask, c->zmask, df_idx, sg_slot, c->L, c->g, c->W0, c->fuse_dots ? c->scratch3R : nullptr, s) != 0)
+        if (tc_backward_stack(c->tc, c->hmask, c->zmask, df_idx, sg_slot, c->L, c->g, c->g_alt, c->W0, c->fuse_dots ? c->scratch3R : nullptr, seg, s) != 0)
             return fail(AST_ECUDA, "whole-stack backward launch failed: %s", cudaGetErrorString(cudaGetLastError()));
     }
     int cur = 0;
@@ -565,14 +586,40 @@ static int step_backward_impl(ast_ctx* c, float* d_losses, float* d_grad, void* 
         launch_layer_f32(a, true, s);
         cur ^= 1;
     }
+    if (!do_bottom) {
+        c->launches_bwd = (do_top ? 0 : c->launches_bwd) + ast_launch_counter - bwd_before;
+        c->launches_per_step = c->launches_fwd + c->launches_bwd;
+        CK(cudaGetLastError());
+        return AST_OK;
+    }
     if (c->tc && c->use_stack_bwd && c->fuse_dots) launch_startconv_bwd_combine(c->scratch3R, d_grad, c->T, c->R, s);
     else launch_startconv_bwd(c->g, c->W0, c->scratch3R, d_grad, c->T, c->R, s);
     if (c->gamma != 0.f && c->reg_nf > 0)                 // + gamma * d reg / d x (methods.py:125)
         launch_stft_l1_grad(c->reg_dadx, c->reg_tw, c->reg_sgn, c->T, c->B, (int)(c->cfg.total_T > 0 ? c->cfg.win_begin : 0),
                             c->reg_f_lo, c->reg_nf, (float)((double)c->gamma / ((double)c->reg_f_total * 513.0)), d_grad, s);
-    c->launches_bwd = ast_launch_counter - bwd_before;
+    c->launches_bwd = (do_top ? 0 : c->launches_bwd) + ast_launch_counter - bwd_before;
     c->launches_per_step = c->launches_fwd + c->launches_bwd;
     CK(cudaGetLastError());
+    return AST_OK;
+}
+
+// ---- per-stack segments for time shards that exchange halo rows (include/ast_b200.h) ----------------------------
+extern "C" int ast_segments(const ast_ctx* c) { return c ? n_segments(c) : 0; }
+extern "C" int ast_step_forward_seg(ast_ctx* c, const float* d_x, int32_t seg, void* stream) {
+    if (seg < 0) return fail(AST_EINVAL, "segment %d outside 0..", seg);
+    return step_forward_impl(c, d_x, stream, false, seg);
+}
+extern "C" int ast_step_backward_seg(ast_ctx* c, int32_t seg, float* d_losses, float* d_grad, void* stream) {
+    if (seg < 0) return fail(AST_EINVAL, "segment %d outside 0..", seg);
+    return step_backward_impl(c, d_losses, d_grad, stream, false, seg);
+}
+extern "C" int ast_segment_buffer(ast_ctx* c, int32_t backward, int32_t seg, float** d_buf) {
+    if (!c || !d_buf) return fail(AST_EINVAL, "null argument");
+    const int nseg = n_segments(c);
+    if (seg < 0 || seg >= nseg) return fail(AST_EINVAL, "segment %d outside 0..%d", seg, nseg - 1);
+    if (backward) { *d_buf = (seg & 1) ? c->g_alt : c->g; return AST_OK; }
+    if (seg == nseg - 1) return fail(AST_EINVAL, "the last forward segment leaves nothing to exchange");
+    *d_buf = Hl(c, tc_segment_end(c->tc, seg));
     return AST_OK;
 }
 
@@ -764,4 +811,6 @@ void tc_set_dbg_skip_publish(int v);
 extern "C" int ast_debug_timeline(void* d_buf) { tc_set_timeline((unsigned long long*)d_buf); return AST_OK; }
 extern "C" int ast_debug_tl_layer(int l) { tc_set_tl_layer(l); return AST_OK; }
 extern "C" int ast_debug_skip_publish(int tile_plus_1) { tc_set_dbg_skip_publish(tile_plus_1); return AST_OK; }
+void tc_set_dbg_group_tiles(int v);
+extern "C" int ast_debug_group_tiles(int n) { tc_set_dbg_group_tiles(n); return AST_OK; }
 #endif

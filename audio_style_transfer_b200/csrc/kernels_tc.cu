@@ -37,7 +37,13 @@ void tc_set_tl_layer(int l);
 // fault injection for tests/test_gpu_loud.py: tile `g_dbg_skip_publish - 1` never releases its hand-off flags
 __device__ int g_dbg_skip_publish = 0;
 void tc_set_dbg_skip_publish(int v) { cudaMemcpyToSymbol(g_dbg_skip_publish, &v, sizeof(v)); }
+// tests: pretend the GPU has only this many SMs when planning segments / groups (0 = the real count), so that a clip
+// that also fits ONE launch runs as several groups and must reproduce the one-launch result bit for bit
+static int g_dbg_group_tiles = 0;
+void tc_set_dbg_group_tiles(int v) { g_dbg_group_tiles = v; }
+#define TC_GROUP_CAP(s) (g_dbg_group_tiles > 0 ? g_dbg_group_tiles : (s)->n_sm)
 #else
+#define TC_GROUP_CAP(s) ((s)->n_sm)
 #define TL(i) do { } while (0)
 #endif
 
@@ -611,6 +617,7 @@ struct TcState {
     unsigned* flags;               // [2][R/128][2] publish counters (per tile and K-half) of the forward / backward stack
                                    // kernels, then err[2], then {epoch, CTAs done} of the forward and of the backward kernel
     int n_sm, coop;                // SM count; cooperative launch supported
+    int nseg, seg_lo[4], seg_hi[4], seg_halo[4];   // layer segments of the whole-stack kernels and their halo (tiles per side)
 };
 
 static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
@@ -685,6 +692,9 @@ TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_he
         cudaDeviceGetAttribute(&s->coop, cudaDevAttrCooperativeLaunch, dev);
     }
     *bytes += (int64_t)(3 * act + mat * NL * 12);
+    // far taps of a group-edge tile read rows of these buffers that no launch of the group has written: keep them finite
+    cudaMemset(s->a_hi, 0, act); cudaMemset(s->a_lo, 0, act); cudaMemset(s->dz, 0, act);
+    tc_plan_segments(s, false);
     ok = make_act_map(&s->tm_a_hi, s->a_hi, false, T, B, 2, 128) && make_act_map(&s->tm_a_lo, s->a_lo, false, T, B, 2, 128) &&
          make_act_map(&s->tm_dz, s->dz, false, T, B, 2, 128) && make_act_map(&s->tm_H, H, true, T, B, NL + 1, 128) &&
          make_act_map(&s->tm_g, g, true, T, B, 1, 128) && make_act_map(&s->tm_dF, dF, true, T, B, n_head > 0 ? n_head : 1, 128) &&
@@ -762,12 +772,55 @@ static cudaError_t launch_coop(Kern kernel, dim3 grid, dim3 block, size_t smem, 
     cfg.attrs = at; cfg.numAttrs = 1;
     return cudaLaunchKernelEx(&cfg, kernel, args);
 }
-// one pair must fit one tile per SM; bigger batches are launched pair group by pair group
-bool tc_stack_ok(const TcState* s) { return s && s->coop && s->T / 128 <= s->n_sm && s->NL <= 32; }
+// ---- segments and groups (stack_fwd.cuh) -----------------------------------------------------------------------
+// One segment = all layers when every pair fits one tile per SM and nobody exchanges halos; else one segment per
+// 10-layer stack (dilations 1..512, sum 1023: the halo a group needs on each inner side is 8 tiles; 1 tile for a last
+// segment of <= 6 layers).
+void tc_plan_segments(TcState* s, bool per_stack) {
+    const bool split = per_stack || s->T / 128 > TC_GROUP_CAP(s);
+    s->nseg = 0;
+    for (int lo = 0; lo < s->NL; lo = s->seg_hi[s->nseg - 1]) {
+        const int hi = split ? (lo + 10 < s->NL ? lo + 10 : s->NL) : s->NL;
+        int sum = 0;
+        for (int l = lo; l < hi; ++l) sum += stack_dil(l);
+        s->seg_lo[s->nseg] = lo; s->seg_hi[s->nseg] = hi; s->seg_halo[s->nseg] = (sum + 127) / 128;
+        ++s->nseg;
+    }
+}
+int tc_segments(const TcState* s) { return s->nseg; }
+int tc_segment_end(const TcState* s, int k) { return s->seg_hi[k]; }
+bool tc_stack_ok(const TcState* s) { return s && s->coop && s->NL <= 32 && s->n_sm >= 64; }
 unsigned* tc_stack_err(TcState* s) { return s->flags + (size_t)4 * (s->R / 128); }
+
+struct TcLaunch { int tile0, ntiles, grp_t0, grp_t1, wr_t0, wr_t1; };
+// The launches of one segment: whole pairs while a pair fits the SMs, else groups of <= n_sm consecutive tiles of one pair
+// with `halo` tiles per inner side that are computed but not written.
+static int tc_plan_launches(const TcState* s, int halo, TcLaunch* out, int max_out) {
+    const int tpp = s->T / 128, cap = TC_GROUP_CAP(s);
+    int n = 0;
+    if (tpp <= cap) {
+        const int ppl = cap / tpp;
+        for (int p0 = 0; p0 < s->B && n < max_out; p0 += ppl) {
+            const int np = s->B - p0 < ppl ? s->B - p0 : ppl;
+            out[n++] = TcLaunch{p0 * tpp, np * tpp, 0, s->T, 0, s->T};
+        }
+        return n;
+    }
+    for (int p = 0; p < s->B; ++p)
+        for (int a = 0; a < tpp && n < max_out;) {
+            const int lo = a - halo > 0 ? a - halo : 0;
+            const int hi = lo + cap < tpp ? lo + cap : tpp;
+            const int e = hi == tpp ? tpp : hi - halo;
+            out[n++] = TcLaunch{p * tpp + lo, hi - lo, lo * 128, hi * 128, a * 128, e * 128};
+            a = e;
+        }
+    return n;
+}
+#define TC_MAX_LAUNCHES 256
+
 int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b0, const float* bd, const float* br,
                      float* H, uint32_t* zmask, uint32_t* hmask, const int* f_slot, const unsigned char* export_h,
-                     cudaStream_t st) {
+                     int seg, cudaStream_t st) {
     FwdStackArgs a;
     memset(&a, 0, sizeof(a));
     a.tmA_hi = s->tm_a_hi; a.tmA_lo = s->tm_a_lo; a.tmW1 = s->tm_w1f; a.tmW2 = s->tm_w2f;
@@ -777,33 +830,38 @@ int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b
     a.T = s->T; a.R = s->R; a.NL = s->NL; a.tiles_per_pair = s->T / 128; a.ntiles = s->R / 128;
     for (int l = 0; l < 32; ++l) a.f_slot[l] = (signed char)((s->n_fslots > 0 && l < s->NL) ? f_slot[l] : -1);
     for (int i = 0; i <= s->NL; ++i) a.export_h[i] = export_h[i];
-    {   // publish i (relu(h_i)) is consumed by layer i: its dilation decides how many warps release per K-half
-        unsigned acc = 0;
-        for (int i = 0; i < 34; ++i) {
-            if (i < s->NL) acc += (unsigned)stack_npub(stack_dil(i));
-            a.need[i] = (unsigned short)acc;
-        }
-    }
-    const size_t nt = (size_t)(s->R / 128);
-    cudaMemsetAsync(s->flags, 0, 2 * nt * sizeof(unsigned), st);
-    const int tpp = s->T / 128, ppl = s->n_sm / tpp;         // tiles per pair; pairs per launch (all CTAs co-resident)
+    for (int k = 0; k + 1 < s->nseg; ++k) a.export_h[s->seg_hi[k]] = 1;      // the next segment resumes from H[seg_hi]
+    TcLaunch ln[TC_MAX_LAUNCHES];
     cudaError_t e = cudaSuccess;
-    for (int p0 = 0; p0 < s->B && e == cudaSuccess; p0 += ppl) {
-        const int np = s->B - p0 < ppl ? s->B - p0 : ppl;
-        a.tile0 = p0 * tpp;
-        e = launch_coop(tc_fwd_stack_kernel, dim3(np * tpp), dim3(F2_THREADS), F2_SMEM, st, a);
-        ast_launch_counter += 1;
+    for (int k = (seg < 0 ? 0 : seg); k < (seg < 0 ? s->nseg : seg + 1) && e == cudaSuccess; ++k) {
+        a.l_begin = s->seg_lo[k]; a.l_end = s->seg_hi[k];
+        {   // publish i (relu(h_i)) is consumed by layer i: its dilation decides how many warps release per K-half
+            unsigned acc = 0;
+            for (int i = 0; i < 34; ++i) {
+                if (i >= a.l_begin && i < a.l_end) acc += (unsigned)stack_npub(stack_dil(i));
+                a.need[i] = (unsigned short)acc;
+            }
+        }
+        const int nl = tc_plan_launches(s, s->seg_halo[k], ln, TC_MAX_LAUNCHES);
+        const bool disjoint = s->T / 128 <= TC_GROUP_CAP(s);       // whole-pair launches: one memset covers them all
+        if (disjoint) cudaMemsetAsync(s->flags, 0, 2 * (size_t)(s->R / 128) * sizeof(unsigned), st);
+        for (int i = 0; i < nl && e == cudaSuccess; ++i) {
+            a.tile0 = ln[i].tile0; a.grp_t0 = ln[i].grp_t0; a.grp_t1 = ln[i].grp_t1; a.wr_t0 = ln[i].wr_t0; a.wr_t1 = ln[i].wr_t1;
+            if (!disjoint) cudaMemsetAsync(s->flags + (size_t)2 * ln[i].tile0, 0, (size_t)2 * ln[i].ntiles * sizeof(unsigned), st);
+            e = launch_coop(tc_fwd_stack_kernel, dim3(ln[i].ntiles), dim3(F2_THREADS), F2_SMEM, st, a);
+            ast_launch_counter += 1;
+        }
     }
     return e == cudaSuccess ? 0 : -1;
 }
 
 int tc_backward_stack(TcState* s, const uint32_t* hmask, const uint32_t* zmask, const int* df_idx, const int* sg_slot,
-                      int sg_L, float* g, const float* W0, float* pdots, cudaStream_t st) {
+                      int sg_L, float* g, float* g_alt, const float* W0, float* pdots, int seg, cudaStream_t st) {
     BwdStackArgs a;
     memset(&a, 0, sizeof(a));
     a.tmDz = s->tm_dz; a.tmW1 = s->tm_w1b; a.tmW2 = s->tm_w2b; a.tmDF = s->tm_dF;
     a.tmF = s->n_fslots > 0 ? s->tm_F : s->tm_dz; a.tmS = s->n_fslots > 0 ? s->tm_ssym : s->tm_w2b;   // unused without slots
-    a.dz = s->dz; a.g = g; a.hmask = hmask; a.zmask = zmask; a.W0 = W0; a.pdots = pdots;
+    a.dz = s->dz; a.hmask = hmask; a.zmask = zmask; a.W0 = W0; a.pdots = pdots;
     const size_t nt = (size_t)(s->R / 128);
     a.flags = s->flags + 2 * nt; a.err = tc_stack_err(s) + 1; a.epoch = tc_stack_err(s) + 4; a.ll = s->ll_b;
     a.T = s->T; a.R = s->R; a.NL = s->NL; a.tiles_per_pair = s->T / 128; a.ntiles = s->R / 128; a.sg_L = sg_L;
@@ -812,21 +870,27 @@ int tc_backward_stack(TcState* s, const uint32_t* hmask, const uint32_t* zmask, 
         a.sg_slot[l] = (signed char)((s->n_fslots > 0 && df_idx[l] < 0) ? sg_slot[l] : -1);
         a.df_idx[l] = (signed char)df_idx[l];
     }
-    {   // dz_m is consumed by boundary m; publishes run from m = NL-1 down to 0
-        unsigned acc = 0;
-        for (int m = 32; m >= 0; --m) {
-            if (m < s->NL) acc += (unsigned)stack_npub(stack_dil(m));
-            a.need[m] = (unsigned short)acc;
-        }
-    }
-    cudaMemsetAsync(s->flags + 2 * nt, 0, 2 * nt * sizeof(unsigned), st);
-    const int tpp = s->T / 128, ppl = s->n_sm / tpp;
+    TcLaunch ln[TC_MAX_LAUNCHES];
     cudaError_t e = cudaSuccess;
-    for (int p0 = 0; p0 < s->B && e == cudaSuccess; p0 += ppl) {
-        const int np = s->B - p0 < ppl ? s->B - p0 : ppl;
-        a.tile0 = p0 * tpp;
-        e = launch_coop(tc_bwd_stack_kernel, dim3(np * tpp), dim3(F2_THREADS), B2_SMEM, st, a);
-        ast_launch_counter += 1;
+    for (int k = (seg < 0 ? s->nseg - 1 : seg); k >= (seg < 0 ? 0 : seg) && e == cudaSuccess; --k) {
+        a.l_top = k == s->nseg - 1 ? s->NL : s->seg_hi[k]; a.l_bot = s->seg_lo[k];
+        a.g = (k & 1) ? g_alt : g; a.g_in = (k & 1) ? g : g_alt;      // segment k leaves its result in buffer k & 1 (segment 0: g)
+        {   // dz_m is consumed by boundary m; this launch publishes m = l_top-1 down to l_bot (l_bot-1 = -1 never exists)
+            unsigned acc = 0;
+            for (int m = 32; m >= 0; --m) {
+                if (m < a.l_top && m >= a.l_bot && m < s->NL) acc += (unsigned)stack_npub(stack_dil(m));
+                a.need[m] = (unsigned short)acc;
+            }
+        }
+        const int nl = tc_plan_launches(s, s->seg_halo[k], ln, TC_MAX_LAUNCHES);
+        const bool disjoint = s->T / 128 <= TC_GROUP_CAP(s);
+        if (disjoint) cudaMemsetAsync(s->flags + 2 * nt, 0, 2 * nt * sizeof(unsigned), st);
+        for (int i = 0; i < nl && e == cudaSuccess; ++i) {
+            a.tile0 = ln[i].tile0; a.grp_t0 = ln[i].grp_t0; a.grp_t1 = ln[i].grp_t1; a.wr_t0 = ln[i].wr_t0; a.wr_t1 = ln[i].wr_t1;
+            if (!disjoint) cudaMemsetAsync(s->flags + 2 * nt + (size_t)2 * ln[i].tile0, 0, (size_t)2 * ln[i].ntiles * sizeof(unsigned), st);
+            e = launch_coop(tc_bwd_stack_kernel, dim3(ln[i].ntiles), dim3(F2_THREADS), B2_SMEM, st, a);
+            ast_launch_counter += 1;
+        }
     }
     return e == cudaSuccess ? 0 : -1;
 }

@@ -14,6 +14,10 @@
 //   * head gradients (fp32 dF tile, or the bf16 F / Ssym operands of the fused style gradient) do not depend on the
 //     sweep: prefetched into their own 64 KB region one boundary ahead;
 //   * weights (and far-tap tiles) stream through a 7 x 16 KB ring.
+// Segments and groups (see stack_fwd.cuh): one launch runs the boundaries l_top .. l_bot on a group of tiles.
+//   l_top < NL ("resume"): boundary l_top starts from the running gradient in global memory (p.g, which already holds
+//                          that boundary's conv^T and head terms) and only forms dz_{l_top-1};
+//   l_bot > 0  ("stop")  : boundary l_bot adds its conv^T and head terms, writes g to global memory and ends there.
 #pragma once
 
 struct alignas(64) BwdStackArgs {
@@ -22,6 +26,8 @@ struct alignas(64) BwdStackArgs {
     CUtensorMap tmDF;                // fp32 head gradients [n_head][B][T][128], box {32,128,1,1}
     CUtensorMap tmF, tmS;            // fused style gradient operands: bf16 F [L][B][T][128], bf16 Ssym rows
     __nv_bfloat16* dz;               // the buffer behind tmDz (published with plain stores)
+    const float* g_in;               // [R][128]: running gradient a resumed launch (l_top < NL) starts from; never the same
+                                     // buffer as g: groups of one segment overlap, a later group still reads rows an earlier one owns
     float* g;                        // [R][128]: receives the final running gradient (input of the start-conv adjoint) ...
     const float* W0; float* pdots;   // ... unless pdots != NULL: then p_k[t] = sum_c W0[k,0,c] g[t,c] goes to pdots[k][R] instead
     const uint32_t* hmask; const uint32_t* zmask;        // [NL+1][R][4], [NL][R][4]
@@ -29,7 +35,10 @@ struct alignas(64) BwdStackArgs {
     unsigned* flags; unsigned* err;  // [ntiles][2]
     unsigned* epoch;                 // [0] launch epoch (tags), [1] CTAs done (see stack_fwd.cuh)
     int T, R, NL, tiles_per_pair, ntiles, sg_L;
-    int tile0;                       // global index of this launch's first tile (launches cover whole pairs)
+    int tile0;                       // global index of this launch's first tile
+    int l_top, l_bot;                // boundaries of this launch, l_top >= l_bot
+    int grp_t0, grp_t1;              // in-pair time range covered by this launch's tiles (hand-off edges)
+    int wr_t0, wr_t1;                // tiles with t0 in this range write the running gradient / the start-conv dots
     unsigned short need[33];         // need[m]: flag value once dz_m (consumed by boundary m) has been published
     signed char df_idx[33];          // per boundary l: dF buffer added there, or -1
     signed char sg_slot[33];         // per boundary l: style slot whose F . Ssym is added there, or -1
@@ -74,8 +83,15 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
     const int tile = p.tile0 + (int)blockIdx.x;
     const int row0 = tile * 128;
     const int b = row0 / p.T, t0 = row0 - b * p.T;
-    const int NL = p.NL;
+    const int NL = p.NL, LT = p.l_top, LBT = p.l_bot;
+    const bool resume = LT < NL, stop = LBT > 0;
+    const int gt0 = p.grp_t0, gt1 = p.grp_t1;
     const uint32_t epoch = *reinterpret_cast<const volatile unsigned*>(p.epoch);
+    // what boundary l does in THIS launch: conv^T + head terms (g1), the 1x1^T that forms dz_{l-1} (g2)
+    auto has_g1 = [&](int l) { return l < NL && !(resume && l == LT); };
+    auto has_g2 = [&](int l) { return l >= 1 && !(stop && l == LBT); };
+    auto df_of = [&](int l) { return (resume && l == LT) ? -1 : (int)p.df_idx[l]; };
+    auto sg_of = [&](int l) { return (resume && l == LT) ? -1 : (int)p.sg_slot[l]; };
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&p.tmDz); tma_prefetch_desc(&p.tmW1); tma_prefetch_desc(&p.tmW2); tma_prefetch_desc(&p.tmDF);
@@ -116,10 +132,10 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
                 mbar_expect_tx(bar + B2B_FULL(slot), TILE16);
                 return slot;
             };
-            for (int l = NL; l >= 0; --l) {
-                const bool g1 = l < NL, g2 = l >= 1;
+            for (int l = LT; l >= LBT; --l) {
+                const bool g1 = has_g1(l), g2 = has_g2(l);
                 const int d = stack_dil(l);
-                const int df = p.df_idx[l], sg = p.sg_slot[l];
+                const int df = df_of(l), sg = sg_of(l);
                 TLB(0);
                 if (df >= 0 || sg >= 0) {                     // head gradient operands: independent of the sweep
                     if (io_n > 0) stack_mbar_wait(bar + B2B_IOFREE, (io_n - 1u) & 1u, ab, p.err);
@@ -147,11 +163,11 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
                     } else {
                         // all weight tiles of this boundary's transposed conv (at most 6 of the 7 slots, none of them waits for a
                         // neighbour), ONE poll of the neighbour flags, then the tap tiles
-                        const bool live0 = tap_live(t0, 0, -d, p.T), live2 = tap_live(t0, 2, -d, p.T);
+                        const bool live0 = stack_tap_live(t0, 0, -d, gt0, gt1), live2 = stack_tap_live(t0, 2, -d, gt0, gt1);
                         if (live0) { load_w1(0, 0); load_w1(0, 1); }
                         if (live2) { load_w1(2, 0); load_w1(2, 1); }
                         if (live0 || live2) {
-                            stack_wait_rows2(p.flags, p.tiles_per_pair, p.T, b, live0 ? t0 + d : t0 - d, live2 ? t0 - d : t0 + d,
+                            stack_wait_rows2(p.flags, p.tiles_per_pair, gt0, gt1, b, live0 ? t0 + d : t0 - d, live2 ? t0 - d : t0 + d,
                                              p.need[l], ab, p.err);
                             fence_proxy_async_all();
                             TLB(3);
@@ -173,9 +189,9 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
                     TLB(8);
                     // Anti-dependency of a FAR publish of dz_{l-1} (whole tile -> the ping-pong buffer that holds dz_{l+1} if that
                     // was far too): the tiles whose +-d_{l+1} taps read this tile are done once they have published dz_l.
-                    if (l + 1 < NL && !stack_near(stack_dil(l - 1)) && !stack_near(stack_dil(l + 1))) {
+                    if (l + 1 < LT && !stack_near(stack_dil(l - 1)) && !stack_near(stack_dil(l + 1))) {
                         const int dp = stack_dil(l + 1);
-                        stack_wait_rows2(p.flags, p.tiles_per_pair, p.T, b, t0 - dp, t0 + dp, p.need[l], ab, p.err);
+                        stack_wait_rows2(p.flags, p.tiles_per_pair, gt0, gt1, b, t0 - dp, t0 + dp, p.need[l], ab, p.err);
                         mbar_arrive(bar + B2B_ANTI);
                     }
                 }
@@ -196,10 +212,10 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
                 for (int kk = 0; kk < 4; ++kk)
                     umma_f16(acc, umma_desc_kmajor_sw128(a + kk * 32), umma_desc_kmajor_sw128(w + kk * 32), IDESC, (kk > 0) ? 1u : accum0);
             };
-            for (int l = NL; l >= 0; --l) {
-                const bool g1 = l < NL, g2 = l >= 1;
+            for (int l = LT; l >= LBT; --l) {
+                const bool g1 = has_g1(l), g2 = has_g2(l);
                 const int d = stack_dil(l);
-                const int df = p.df_idx[l], sg = p.sg_slot[l];
+                const int df = df_of(l), sg = sg_of(l);
                 if (g1) {
                     for (int j = 0; j < 2; ++j) {             // centre tap, both K-halves
                         stack_mbar_wait(bar + B2B_DZ(j), dz_n & 1u, ab, p.err);          // own dz_l, K-half j, staged
@@ -226,7 +242,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
                         ++n_near;
                     } else {
                         uint32_t sw[2][2];
-                        const bool live0 = tap_live(t0, 0, -d, p.T), live2 = tap_live(t0, 2, -d, p.T);
+                        const bool live0 = stack_tap_live(t0, 0, -d, gt0, gt1), live2 = stack_tap_live(t0, 2, -d, gt0, gt1);
                         if (live0) { sw[0][0] = take(); sw[0][1] = take(); }        // weights first (producer fill order)
                         if (live2) { sw[1][0] = take(); sw[1][1] = take(); }
                         for (int k = 0; k < 3; k += 2) {
@@ -280,15 +296,16 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
         unsigned* my_flag = p.flags + (size_t)tile * 2;
         const uint16_t* hmask16 = reinterpret_cast<const uint16_t*>(p.hmask);
         const uint16_t* zmask16 = reinterpret_cast<const uint16_t*>(p.zmask);
-        const bool has_up = t0 > 0, has_dn = t0 + 128 < p.T;
+        const bool has_up = t0 > gt0, has_dn = t0 + 128 < gt1;
+        const bool wr = t0 >= p.wr_t0 && t0 < p.wr_t1;
         uint32_t acc1_n = 0, acc2_n = 0, io_n = 0, anti_n = 0;
         // LL item of (ping-pong pp, tile tl, side sd, K-half j, cc, row slot): lines [4][LL_ROWS], slot fastest (stack_fwd.cuh)
         auto ll_item = [&](int pp, int tl, int sd, int j, int slot, int c) -> uint4* {
             return p.ll + ((((((size_t)pp * p.ntiles + tl) * 2 + sd) * 2 + j) * 4 + c) * 4) * LL_ROWS + slot;
         };
-        for (int l = NL; l >= 0; --l) {
-            const bool g1 = l < NL, g2 = l >= 1;
-            const int df = p.df_idx[l], sg = p.sg_slot[l];
+        for (int l = LT; l >= LBT; --l) {
+            const bool g1 = has_g1(l), g2 = has_g2(l);
+            const int df = df_of(l), sg = sg_of(l);
             const bool has_io = df >= 0 || sg >= 0;
             uint32_t hm[2] = {0u, 0u}, zm[2] = {0u, 0u};
 #pragma unroll
@@ -330,6 +347,10 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
                     tmem_wait_ld();
 #pragma unroll
                     for (int e = 0; e < 16; ++e) v[e] += w[e];
+                } else if (resume && l == LT) {               // ... a resumed launch takes it from global memory
+                    const float4* gin = reinterpret_cast<const float4*>(p.g_in + row * AST_C + colc);
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) { const float4 t = gin[e]; v[4 * e] = t.x; v[4 * e + 1] = t.y; v[4 * e + 2] = t.z; v[4 * e + 3] = t.w; }
                 }
                 if (df >= 0) {
                     const uint8_t* dcg = gen + B2_IO + (j * 2 + (cc >> 1)) * TILE16;
@@ -351,11 +372,13 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
                     __syncwarp();
                     if (lane == 0) mbar_arrive(bar + B2B_RT(j));
                 }
-                if (l == 0) {
-                    if (!p.pdots) {
-                        float4* out = reinterpret_cast<float4*>(p.g + row * AST_C + colc);
+                if (l == LBT) {
+                    if (stop || !p.pdots) {
+                        if (wr) {
+                            float4* out = reinterpret_cast<float4*>(p.g + row * AST_C + colc);
 #pragma unroll
-                        for (int e = 0; e < 4; ++e) out[e] = make_float4(v[4 * e], v[4 * e + 1], v[4 * e + 2], v[4 * e + 3]);
+                            for (int e = 0; e < 4; ++e) out[e] = make_float4(v[4 * e], v[4 * e + 1], v[4 * e + 2], v[4 * e + 3]);
+                        }
                     } else {
                         // start-conv adjoint dots p_k[t] = sum_c W0[k,0,c] g[t,c] over this thread's columns
                         const float* w = p.W0 + colc;
@@ -371,13 +394,13 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
             if (has_io) { __syncwarp(); if (lane == 0) mbar_arrive(bar + B2B_IOFREE); }
             tmem_wait_st();
             if (threadIdx.x == 64) TLB(32);
-            if (l == 0 && p.pdots) {
+            if (l == 0 && !stop && p.pdots) {
                 // the 4 column groups of a row meet in smem (the ring is dead: boundary 0 has no 1x1 GEMM and its conv has
                 // completed); fixed order -> reproducible
                 float* ps = reinterpret_cast<float*>(gen + B2_RING);
                 ps[(0 * 4 + cc) * 128 + r] = pk0; ps[(1 * 4 + cc) * 128 + r] = pk1; ps[(2 * 4 + cc) * 128 + r] = pk2;
                 named_bar_sync(5, 512);
-                if (cc < 3) {
+                if (cc < 3 && wr) {
                     const float* q4 = ps + cc * 4 * 128 + r;
                     p.pdots[(size_t)cc * p.R + row] = (q4[0] + q4[128]) + (q4[256] + q4[384]);
                 }
@@ -422,7 +445,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
                         mbar_arrive(bar + B2B_DZ(j));
                     }
                 } else {
-                    if (j == 0 && l + 1 < NL && !stack_near(stack_dil(l + 1))) { stack_mbar_wait(bar + B2B_ANTI, anti_n & 1u, ab, p.err); ++anti_n; }
+                    if (j == 0 && l + 1 < LT && !stack_near(stack_dil(l + 1))) { stack_mbar_wait(bar + B2B_ANTI, anti_n & 1u, ab, p.err); ++anti_n; }
                     named_bar_sync(1 + q, 128);
                     // far publish: the four warps of a row quadrant copy full 128-byte lines of the staged K-half, then ONE release
                     const uint8_t* wc = gen + j * B2_WBUF + F2_CENTRE;

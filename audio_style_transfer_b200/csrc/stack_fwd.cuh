@@ -34,6 +34,14 @@
 // co-resident (cooperative launch, grid <= #SMs, 1 CTA/SM); every wait targets work of an earlier publish, so the
 // dependency graph is acyclic.  Every spin is bounded: on expiry the CTA raises *err, sets its abort word and all
 // further waits fall through, so the kernel always terminates and the host reports AST_ECUDA (ast_check).
+//
+// Segments and groups (clips with more tiles than SMs, time shards with a per-stack halo exchange).  One launch runs the
+// layers [l_begin, l_end) on a GROUP of at most #SMs consecutive tiles of one pair (or on whole pairs).  l_begin > 0
+// resumes from the fp32 stream H[l_begin] in global memory (written by the previous segment's launches, or received from
+// the neighbour rank); l_end < NL leaves H[l_end] there.  A group edge that is not a clip end behaves like one (zero
+// halo, stale far-tap rows): the error this makes travels sum(d) <= 1023 rows per 10-layer segment into the group, so
+// the host gives every group ceil(sum(d) / 128) halo tiles per inner side and only tiles in [wr_t0, wr_t1) write masks,
+// exports and extract copies (tc_plan_groups in kernels_tc.cu).
 #pragma once
 
 struct alignas(64) FwdStackArgs {
@@ -51,7 +59,10 @@ struct alignas(64) FwdStackArgs {
     unsigned* epoch;                 // [0] launch epoch (tags), [1] CTAs done: the last CTA of a launch bumps the epoch
     unsigned* err;
     int T, R, NL, tiles_per_pair, ntiles;
-    int tile0;                       // global index of this launch's first tile (launches cover whole pairs)
+    int tile0;                       // global index of this launch's first tile
+    int l_begin, l_end;              // layers of this launch; l_begin == 0 starts from the waveform (start conv)
+    int grp_t0, grp_t1;              // in-pair time range covered by this launch's tiles (hand-off edges)
+    int wr_t0, wr_t1;                // tiles with t0 in this range write masks / exports / extract copies
     unsigned short need[34];         // need[i]: flag value once publish i (relu(h_i), i = 0: start conv) is complete
     signed char f_slot[32];          // style slot that receives bf16(H[l+1]), or -1
     unsigned char export_h[33];      // export_h[i] != 0: H[i] is written to global memory (i = 0: start-conv output)
@@ -130,15 +141,16 @@ __device__ __forceinline__ void stack_wait_flags(const unsigned* f0, const unsig
     fence_acq_rel_gpu();
 }
 // Both K-half flags of every tile that holds rows [ta, ta+127] / [tb, tb+127] of pair b (far taps, anti-dependency).
-__device__ __forceinline__ void stack_wait_rows2(const unsigned* flags, int tiles_per_pair, int T, int b, int ta, int tb,
+// Only tiles of this launch's group [g0, g1) are waited for (rows outside it are not produced by this launch).
+__device__ __forceinline__ void stack_wait_rows2(const unsigned* flags, int tiles_per_pair, int g0, int g1, int b, int ta, int tb,
                                                  unsigned need, volatile unsigned* ab, unsigned* err) {
-    const bool la = !(ta + 127 < 0 || ta >= T), lb = !(tb + 127 < 0 || tb >= T);
+    const bool la = !(ta + 127 < g0 || ta >= g1), lb = !(tb + 127 < g0 || tb >= g1);
     if (!la && !lb) return;
     if (!la) ta = tb;
     if (!lb) tb = ta;
     const unsigned* base = flags + (size_t)b * tiles_per_pair * 2;
-    const unsigned* f[4] = {base + 2 * ((ta < 0 ? 0 : ta) >> 7), base + 2 * ((ta + 127 >= T ? T - 1 : ta + 127) >> 7),
-                            base + 2 * ((tb < 0 ? 0 : tb) >> 7), base + 2 * ((tb + 127 >= T ? T - 1 : tb + 127) >> 7)};
+    const unsigned* f[4] = {base + 2 * ((ta < g0 ? g0 : ta) >> 7), base + 2 * ((ta + 127 >= g1 ? g1 - 1 : ta + 127) >> 7),
+                            base + 2 * ((tb < g0 ? g0 : tb) >> 7), base + 2 * ((tb + 127 >= g1 ? g1 - 1 : tb + 127) >> 7)};
     unsigned spins = 0;
     for (;;) {
         bool ok = true;
@@ -152,6 +164,13 @@ __device__ __forceinline__ void stack_wait_rows2(const unsigned* flags, int tile
         if (++spins > FS_SPIN_LIMIT || stack_aborted(ab)) { stack_abort(ab, err, 1u); break; }
     }
     fence_acq_rel_gpu();
+}
+
+// a far tap is live when its 128 source rows touch the group (rows outside the clip are zero-filled by TMA, rows of the
+// clip outside the group are stale: both only reach rows the host discards, or are the reference's padding)
+__device__ __forceinline__ bool stack_tap_live(int t0, int k, int shift, int g0, int g1) {
+    const int t = t0 + (k - 1) * shift;
+    return t + 128 > g0 && t < g1;
 }
 
 __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
@@ -201,7 +220,8 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
     const int tile = p.tile0 + (int)blockIdx.x;
     const int row0 = tile * 128;
     const int b = row0 / p.T, t0 = row0 - b * p.T;
-    const int NL = p.NL;
+    const int NL = p.NL, LB = p.l_begin, LE = p.l_end;
+    const int g0 = p.grp_t0, g1 = p.grp_t1;
     const uint32_t epoch = *reinterpret_cast<const volatile unsigned*>(p.epoch);      // stable: bumped by the previous launch's last CTA
     if (threadIdx.x == 0) TL(0);
 
@@ -242,7 +262,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
                 mbar_expect_tx(bar + F2B_FULL(slot), 2 * TILE16);
                 return slot;
             };
-            for (int l = 0; l < NL; ++l) {
+            for (int l = LB; l < LE; ++l) {
                 const int d = stack_dil(l);
                 const int w1row = l * 3 * 2 * AST_C, w2row = l * 2 * AST_C;
                 auto load_w1 = [&](int k, int j) {
@@ -268,12 +288,12 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
                     // of all the flags this layer needs, then operand tiles (and the second tap's weights) as slots free up
                     load_w1(1, 0);
                     load_w1(1, 1);
-                    const bool live0 = tap_live(t0, 0, d, p.T), live2 = tap_live(t0, 2, d, p.T);
+                    const bool live0 = stack_tap_live(t0, 0, d, g0, g1), live2 = stack_tap_live(t0, 2, d, g0, g1);
                     const int k1 = live0 ? 0 : 2;                      // first live side tap (if any)
                     if (live0 || live2) {
                         load_w1(k1, 0);
                         load_w1(k1, 1);
-                        stack_wait_rows2(p.flags, p.tiles_per_pair, p.T, b, live0 ? t0 - d : t0 + d, live2 ? t0 + d : t0 - d,
+                        stack_wait_rows2(p.flags, p.tiles_per_pair, g0, g1, b, live0 ? t0 - d : t0 + d, live2 ? t0 + d : t0 - d,
                                          p.need[l], ab, p.err);
                         fence_proxy_async_all();
                         TLD(2);
@@ -293,9 +313,9 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
                 // publish l-1 was far too): the tiles whose +-d_{l-1} taps read this tile must be past layer l-1's conv, i.e.
                 // have made publish l.  Every publish bumps the flags (near ones without release semantics, for this purpose
                 // only).  Polled here, off the critical path.
-                if (l >= 1 && l + 1 < NL && !stack_near(stack_dil(l + 1)) && !stack_near(stack_dil(l - 1))) {
+                if (l - 1 >= LB && l + 1 < LE && !stack_near(stack_dil(l + 1)) && !stack_near(stack_dil(l - 1))) {
                     const int dp = stack_dil(l - 1);
-                    stack_wait_rows2(p.flags, p.tiles_per_pair, p.T, b, t0 - dp, t0 + dp, p.need[l], ab, p.err);
+                    stack_wait_rows2(p.flags, p.tiles_per_pair, g0, g1, b, t0 - dp, t0 + dp, p.need[l], ab, p.err);
                     mbar_arrive(bar + F2B_ANTI);
                 }
             }
@@ -323,8 +343,8 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
                     umma_f16(acc, a_hi, w_lo, IDESC, 1u);
                 }
             };
-            for (int l = 0; l < NL; ++l) {
-                const uint32_t par = (uint32_t)l & 1u;
+            for (int l = LB; l < LE; ++l) {
+                const uint32_t par = (uint32_t)(l - LB) & 1u;
                 const int d = stack_dil(l);
                 // centre tap, both K-halves: the own tile is resident, nothing to wait for but its staging
                 for (int j = 0; j < 2; ++j) {
@@ -352,7 +372,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
                     }
                     ++n_near;
                 } else {
-                    const bool live0 = tap_live(t0, 0, d, p.T), live2 = tap_live(t0, 2, d, p.T);
+                    const bool live0 = stack_tap_live(t0, 0, d, g0, g1), live2 = stack_tap_live(t0, 2, d, g0, g1);
                     if (live0 || live2) {                                   // producer fill order: W W A A, then W A W A
                         uint32_t sw[2];
                         sw[0] = take(); sw[1] = take();
@@ -401,7 +421,8 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
         unsigned* my_flag = p.flags + (size_t)tile * 2;
         uint16_t* hmask16 = reinterpret_cast<uint16_t*>(p.hmask);
         uint16_t* zmask16 = reinterpret_cast<uint16_t*>(p.zmask);
-        const bool has_up = t0 > 0, has_dn = t0 + 128 < p.T;
+        const bool has_up = t0 > g0, has_dn = t0 + 128 < g1;
+        const bool wr = t0 >= p.wr_t0 && t0 < p.wr_t1;               // this tile's rows are exact: it writes the global outputs
         uint32_t anti_n = 0;
         // LL item of (ping-pong pp, tile tl, side sd, K-half j, cc, part, row slot): lines [4][LL_ROWS] with the slot fastest
         auto ll_item = [&](int pp, int tl, int sd, int j, int slot, int c, int part) -> uint4* {
@@ -425,7 +446,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
             const int l = i - 1;                       // for TLD
             const int col = j * 64 + cc * 16;
             tmem_st16(hacc + lane_off + col, v);
-            if (i >= NL) return;
+            if (i >= LE) return;                       // h_{l_end} is not consumed by this launch (LE == NL: by no layer at all)
             uint32_t Hh[8], Ll[8];
             stage16(j, v, Hh, Ll);
             fence_proxy_async_smem();
@@ -454,7 +475,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
             } else {
                 // far publish: the four warps of a row quadrant copy full 128-byte lines of the staged K-half; after a CTA
                 // barrier ONE thread releases the flag (one gpu-scope membar per K-half instead of sixteen)
-                if (j == 0 && i >= 2 && !stack_near(stack_dil(i - 2))) { stack_mbar_wait(bar + F2B_ANTI, anti_n & 1u, ab, p.err); ++anti_n; }
+                if (j == 0 && i - 2 >= LB && !stack_near(stack_dil(i - 2))) { stack_mbar_wait(bar + F2B_ANTI, anti_n & 1u, ab, p.err); ++anti_n; }
                 named_bar_sync(1 + q, 128);
                 const uint8_t* whi = gen + (j * 2 + 0) * F2_WBUF + F2_CENTRE;
                 const uint8_t* wlo = gen + (j * 2 + 1) * F2_WBUF + F2_CENTRE;
@@ -477,6 +498,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
         // Everything of h_i that nobody waits for -- sign mask, fp32 export, bf16 extract copy -- re-read from TMEM once the
         // hand-off is out: these stores must not sit in front of a release (membar) or delay the second K-half.
         auto finish = [&](int i) {
+            if (!wr) return;
             const int f = i >= 1 ? (int)p.f_slot[i - 1] : -1;
             const bool exp = p.export_h[i] != 0;
 #pragma unroll
@@ -535,8 +557,23 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
             }
         };
 
-        // ---- pseudo layer: start conv (model.py:80-93), same arithmetic as startconv_fwd_kernel ----
-        {
+        if (LB > 0) {
+            // ---- resume: h_{l_begin} of this row from the fp32 stream in global memory ----
+            const float* hrow = p.H + ((size_t)LB * p.R + row) * AST_C;
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                float v[16];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float4 t4 = *reinterpret_cast<const float4*>(hrow + j * 64 + cc * 16 + 4 * e);
+                    v[4 * e] = t4.x; v[4 * e + 1] = t4.y; v[4 * e + 2] = t4.z; v[4 * e + 3] = t4.w;
+                }
+                emit(LB, j, v);
+            }
+            tmem_wait_st();
+            if (stack_near(stack_dil(LB))) import_halo(LB);
+        } else {
+            // ---- pseudo layer: start conv (model.py:80-93), same arithmetic as startconv_fwd_kernel ----
             const int t = t0 + r;
             const float* xb = p.x + (size_t)b * p.T;
             const float xm = (t > 0) ? xb[t - 1] * (1.0f / 128.0f) : 0.f;
@@ -560,11 +597,11 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
                 emit(0, j, v);
             }
             tmem_wait_st();
-            if (NL > 0) import_halo(0);
+            if (LE > 0) import_halo(0);
             finish(0);
         }
-        for (int l = 0; l < NL; ++l) {
-            const uint32_t par = (uint32_t)l & 1u;
+        for (int l = LB; l < LE; ++l) {
+            const uint32_t par = (uint32_t)(l - LB) & 1u;
             // ---- epilogue 1: z = acc1 + bd -> sign mask, relu(z) hi/lo -> A operand of the 1x1 GEMM (window centre) ----
             stack_mbar_wait(bar + F2B_ACC1, par, ab, p.err);
             tc_fence_after();
@@ -592,8 +629,10 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
 #pragma unroll
                 for (int e = 0; e < 16; ++e) or_bit_if_pos(zword, v[e], 1u << (16 * j + e));
             }
-            zmask16[((size_t)l * p.R + row) * 8 + cc] = (uint16_t)zword;
-            zmask16[((size_t)l * p.R + row) * 8 + 4 + cc] = (uint16_t)(zword >> 16);
+            if (wr) {
+                zmask16[((size_t)l * p.R + row) * 8 + cc] = (uint16_t)zword;
+                zmask16[((size_t)l * p.R + row) * 8 + 4 + cc] = (uint16_t)(zword >> 16);
+            }
             if (threadIdx.x == 64) TLD(32);
             // ---- epilogue 2: h' = h + (acc2 + br)  (same association as the reference, model.py:109-114) ----
             stack_mbar_wait(bar + F2B_ACC2, par, ab, p.err);
@@ -618,7 +657,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
                 emit(l + 1, j, v);
             }
             tmem_wait_st();
-            if (l + 1 < NL && stack_near(stack_dil(l + 1))) import_halo(l + 1);
+            if (l + 1 < LE && stack_near(stack_dil(l + 1))) import_halo(l + 1);
             finish(l + 1);
             if (threadIdx.x == 64) TLD(41);
             if (threadIdx.x == 64 && l < 30) TL(32 + l);

@@ -25,15 +25,20 @@ void tc_layer_fwd(TcState* s, int l, const float* bd, const float* br, uint32_t*
 // Whole encoder forward (start conv + all layers) in one cooperative launch; available when the clip has at most
 // one 128-row tile per SM.  Writes zmask[l], hmask[l], the bf16 extract copies, and H[i] only where export_h[i] != 0
 // (i = 0: start-conv output, i = l+1: output of layer l).  *tc_stack_err() != 0 afterwards = a bounded spin expired.
+// Clips with more tiles than SMs run as layer SEGMENTS (one per 10-layer stack) x tile GROUPS (stack_fwd.cuh); seg < 0 runs
+// every segment, seg >= 0 only that one (time shards exchange halo rows of H[tc_segment_end(seg)] / g between segments).
 bool tc_stack_ok(const TcState* s);
 unsigned* tc_stack_err(TcState* s);
+void tc_plan_segments(TcState* s, bool per_stack);
+int tc_segments(const TcState* s);
+int tc_segment_end(const TcState* s, int k);
 int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b0, const float* bd, const float* br,
                      float* H, uint32_t* zmask, uint32_t* hmask, const int* f_slot, const unsigned char* export_h,
-                     cudaStream_t st);
+                     int seg, cudaStream_t st);
 // Whole backward sweep (boundaries NL..0) in one cooperative launch (same availability as tc_forward_stack).
 // df_idx[l] / sg_slot[l] as for tc_layer_bwd, per boundary l; the final running gradient is written to g [R][128].
 int tc_backward_stack(TcState* s, const uint32_t* hmask, const uint32_t* zmask, const int* df_idx, const int* sg_slot,
-                      int sg_L, float* g, const float* W0, float* pdots, cudaStream_t st);
+                      int sg_L, float* g, float* g_alt, const float* W0, float* pdots, int seg, cudaStream_t st);
 // backward boundary l in NL..0: g += conv^T(dz_l) * hmask + dF[df_idx] (df_idx < 0: none);
 // dz_{l-1} = (g Wr_{l-1}^T) * zmask.  bf16 dz buffers owned by the TcState.  l == NL: no conv (top);
 // l == 0: no 1x1 (bottom).

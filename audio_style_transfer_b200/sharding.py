@@ -46,6 +46,27 @@ def plan_windows(T: int, P: int, n_layers: int, min_halo: int = 0) -> List[Tuple
     return plan
 
 
+HALO = 1024         # AST_HALO_ROWS: >= 1023 = sum of the dilations of one 10-layer stack (model.py:98)
+
+
+def plan_windows_exchange(T: int, P: int) -> List[Tuple[int, int, int, int]]:
+    """Windows for shards that EXCHANGE halo rows stack by stack (HaloShardedStep): owned ranges as in plan_windows,
+    window = owned range +- 2 * HALO rows (clipped): HALO rows whose features must be exact for the backward of the
+    owned rows, and HALO more that the forward of those needs and that are refreshed from the neighbour after every
+    stack.  Every owned range must hold the 2 * HALO rows its neighbours fetch."""
+    if T % ALIGN:
+        raise ValueError(f"T={T} must be a multiple of {ALIGN}")
+    blocks = T // ALIGN
+    plan = []
+    for r in range(P):
+        ob = (blocks * r // P) * ALIGN
+        oe = (blocks * (r + 1) // P) * ALIGN
+        if P > 1 and oe - ob < 2 * HALO:
+            raise ValueError(f"shard of {oe - ob} samples is shorter than the {2 * HALO} rows its neighbours fetch")
+        plan.append((max(0, ob - 2 * HALO), min(T, oe + 2 * HALO), ob, oe))
+    return plan
+
+
 def pairs_for_rank(n_pairs: int, rank: int, world: int) -> range:
     """Data parallelism over independent content/style pairs: pair p -> rank p % world
     (SURVEY.md 8(e)); no collective in the step."""
@@ -75,3 +96,54 @@ class TimeShardedStep:
         self.all_reduce(self.ctx.partials())          # in place, sum over ranks
         losses, grad = self.ctx.backward()
         return losses, grad[:, self.ob - self.wb:self.oe - self.wb]
+
+
+class HaloShardedStep:
+    """Time sharding with a receptive-field halo exchange (BASELINE.json north_star; SURVEY.md 8(e) option ii).
+
+    The encoder is three stacks of ten layers with dilations 1..512 (model.py:96-106), so ONE stack moves information by
+    at most 1023 rows.  Rank r evaluates its window stack by stack (StyleStep.forward_seg / backward_seg); after each
+    forward stack it overwrites the outer HALO rows of its window (which its own zero-padded evaluation got wrong) with
+    the neighbour's exact rows of the fp32 residual stream, after each backward stack the HALO rows next to its owned
+    range with the neighbour's running gradient.  Per step and interior side: 2 + 2 messages of HALO x 128 fp32
+    (512 KB), plus the one all-reduce of the raw Gram partials.  `exchange(pairs)` moves rows between ranks:
+    pairs = [(send_tensor, recv_tensor, peer_rank), ...]; on NCCL it is one batch_isend_irecv, tests inject copies."""
+
+    def __init__(self, T: int, rank: int, world: int, make_ctx: Callable, all_reduce: Callable, exchange: Callable):
+        self.T, self.rank, self.world = T, rank, world
+        self.plan = plan_windows_exchange(T, world)
+        self.wb, self.we, self.ob, self.oe = self.plan[rank]
+        self.ctx = make_ctx(self.we - self.wb, (T, self.wb, self.ob, self.oe))
+        self.all_reduce, self.exchange = all_reduce, exchange
+        self.nseg = self.ctx.segments
+        self.up = rank - 1 if rank > 0 else None             # neighbour that owns the samples before mine
+        self.dn = rank + 1 if rank + 1 < world else None
+
+    def window(self, full):
+        return full[:, self.wb:self.we]
+
+    def _swap(self, buf, send_up, recv_up, send_dn, recv_dn):
+        """buf [B, T_win, 128]; the four (begin, end) ranges are global sample indices."""
+        rows = lambda a: buf[:, a[0] - self.wb:a[1] - self.wb]
+        pairs = []
+        if self.up is not None:
+            pairs.append((rows(send_up), rows(recv_up), self.up))
+        if self.dn is not None:
+            pairs.append((rows(send_dn), rows(recv_dn), self.dn))
+        if pairs:
+            self.exchange(pairs)
+
+    def step(self, x_window, losses, grad):
+        """Returns (losses [B,4] -- identical on every rank, grad of the OWNED samples [B, own_e-own_b])."""
+        c, H, ob, oe = self.ctx, HALO, self.ob, self.oe
+        for k in range(self.nseg):
+            c.forward_seg(x_window, k)
+            if k + 1 < self.nseg:
+                # my exact region is [ob-H, oe+H); the neighbour above needs [ob+H, ob+2H) of it, the one below [oe-2H, oe-H)
+                self._swap(c.segment_buffer(False, k), (ob + H, ob + 2 * H), (ob - 2 * H, ob - H), (oe - 2 * H, oe - H), (oe + H, oe + 2 * H))
+        self.all_reduce(c.partials())
+        for k in range(self.nseg - 1, -1, -1):
+            c.backward_seg(k, losses, grad)
+            if k > 0:
+                self._swap(c.segment_buffer(True, k), (ob, ob + H), (ob - H, ob), (oe - H, oe), (oe, oe + H))
+        return losses, grad[:, ob - self.wb:oe - self.wb]

@@ -47,7 +47,7 @@ class StyleStep:
     KERNEL_PATHS = {"auto": 0, "per_layer": 1, "per_layer_bwd": 2}
 
     def __init__(self, T, cont_ids, style_ids, gatys=False, nb_channels=128, cnt_channels=128, B=1,
-                 precision="bf16", device=None, window=None, kernel_path="auto", experiments=False):
+                 precision="bf16", device=None, window=None, kernel_path="auto", experiments=False, halo_exchange=False):
         if not torch.cuda.is_available():
             raise RuntimeError("no CUDA device: the B200 step has no CPU fallback")
         self.lib = _lib.load(experiments)
@@ -75,6 +75,7 @@ class StyleStep:
             cfg.total_T, cfg.win_begin, cfg.own_begin, cfg.own_end = [int(v) for v in window]
         cfg.device = self.device
         cfg.kernel_path = self.KERNEL_PATHS[kernel_path]
+        cfg.halo_exchange = int(bool(halo_exchange))
         self._h = C.c_void_p()
         _lib.check(self.lib.ast_create(C.byref(cfg), C.byref(self._h)), self.lib)
         self.ec_cols = len(self.cont_ids) * self.cnt_channels
@@ -193,6 +194,27 @@ class StyleStep:
                 grad = torch.empty((self.B, self.T), dtype=torch.float32, device=self.dev)
             _lib.check(self.lib.ast_step_backward(self._h, _ptr(losses), _ptr(grad), _stream()), self.lib)
         return losses, grad
+
+    # -- the same two phases stack by stack (time shards that exchange halo rows; include/ast_b200.h) ------------
+    @property
+    def segments(self) -> int:
+        return int(self.lib.ast_segments(self._h))
+
+    def forward_seg(self, x, seg: int):
+        x = self._x(x)
+        with torch.cuda.device(self.dev):
+            _lib.check(self.lib.ast_step_forward_seg(self._h, _ptr(x), int(seg), _stream()), self.lib)
+
+    def backward_seg(self, seg: int, losses, grad):
+        with torch.cuda.device(self.dev):
+            _lib.check(self.lib.ast_step_backward_seg(self._h, int(seg), _ptr(losses), _ptr(grad), _stream()), self.lib)
+
+    def segment_buffer(self, backward: bool, seg: int) -> torch.Tensor:
+        """Zero-copy [B, T, 128] fp32 view of what neighbours exchange after segment `seg`: the residual stream at the
+        segment's end (forward) or the running gradient (backward)."""
+        p = C.c_void_p()
+        _lib.check(self.lib.ast_segment_buffer(self._h, int(bool(backward)), int(seg), C.byref(p)), self.lib)
+        return torch.as_tensor(_DevMem(p.value, self.B * self.T * 128), device=self.dev).view(self.B, self.T, 128)
 
     def extract(self, layer: int) -> torch.Tensor:
         """cfg.extracts[layer] of the last forward (model.py:116); layer -1 = start-conv output."""

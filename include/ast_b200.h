@@ -48,9 +48,10 @@ extern "C" {
                               /* forward operands are 2-term bf16 splits (hi+lo), backward plain bf16; */
                               /* channel-wise head with 13..32 style layers: mma.sync TF32 (Gram 3xTF32) */
 
-/* ast_config.kernel_path (tensor-core tier): AUTO = one cooperative whole-stack kernel per direction when a pair has at
- * most one 128-row tile per SM, else one kernel per layer.  The other two force the per-layer kernels (parity tests
- * compare the paths; they compute the same step). */
+/* ast_config.kernel_path (tensor-core tier): AUTO = the cooperative whole-stack kernels: one launch per direction when a
+ * pair has at most one 128-row tile per SM, else one launch per 10-layer stack and group of <= #SMs tiles (a group
+ * carries 8 halo tiles per inner side that are computed and discarded).  The other two force the one-kernel-per-layer
+ * path (parity tests compare the paths; they compute the same step). */
 #define AST_PATH_AUTO          0
 #define AST_PATH_PER_LAYER     1   /* one kernel per layer, forward and backward                  */
 #define AST_PATH_PER_LAYER_BWD 2   /* whole-stack forward, one kernel per layer in the backward   */
@@ -83,7 +84,16 @@ typedef struct ast_config {
     int64_t own_end;
     int32_t device;                  /* CUDA device ordinal                                              */
     int32_t kernel_path;             /* AST_PATH_* (0 = auto)                                            */
+    /* Time shards that EXCHANGE halo rows with their neighbour ranks (BASELINE.json north_star; the reference is
+     * single-device, methods.py:48-54,143).  1: the step runs stack by stack (ast_segments / ast_step_forward_seg /
+     * ast_step_backward_seg) and between two segments the caller moves AST_HALO_ROWS rows per side of the fp32 stream
+     * (forward) / running gradient (backward) between neighbours (ast_segment_buffer); the window then needs only
+     * 2 * AST_HALO_ROWS rows beyond the owned range per interior side instead of 2 x the whole receptive field.
+     * Tensor-core tier only. */
+    int32_t halo_exchange;
 } ast_config;
+
+#define AST_HALO_ROWS 1024   /* >= 1023 = sum of the dilations of one 10-layer stack (model.py:98) */
 
 /* GatysNet.__init__/build (methods.py:20-77): allocate workspaces for a fixed (T, B, layer set). */
 int  ast_create(const ast_config* cfg, ast_ctx** out);
@@ -131,6 +141,20 @@ int  ast_step_host(ast_ctx* ctx, const double* h_x, double* h_losses, double* h_
 int  ast_step_forward(ast_ctx* ctx, const float* d_x, void* stream);
 int  ast_partials(ast_ctx* ctx, float** d_buf, int64_t* count);
 int  ast_step_backward(ast_ctx* ctx, float* d_losses, float* d_grad, void* stream);
+
+/* The same two phases stack by stack, for contexts created with halo_exchange = 1 (n = ast_segments(ctx), 3 for
+ * 21..30 layers).  Forward: seg = 0 .. n-1; after segment seg < n-1 the fp32 stream at the segment's end is exact on
+ * [own_begin - AST_HALO_ROWS, own_end + AST_HALO_ROWS) and the caller overwrites the AST_HALO_ROWS rows outside that range on
+ * each interior side of the window with the neighbour rank's rows (ast_segment_buffer(ctx, 0, seg): [B][T][128] fp32);
+ * the last segment also forms the partial sums (then: all-reduce ast_partials).  Backward: seg = n-1 .. 0; segment n-1
+ * starts with the heads; after segment seg > 0 the running gradient (ast_segment_buffer(ctx, 1, seg)) is exact on the
+ * owned rows and the caller overwrites the AST_HALO_ROWS rows on each interior side of the owned range with the neighbour's;
+ * segment 0 ends with the gradient in d_grad.  Unsharded contexts report their own segment count (1 unless the clip
+ * has more tiles than SMs) and may be driven the same way without any exchange. */
+int  ast_segments(const ast_ctx* ctx);
+int  ast_step_forward_seg(ast_ctx* ctx, const float* d_x, int32_t seg, void* stream);
+int  ast_step_backward_seg(ast_ctx* ctx, int32_t seg, float* d_losses, float* d_grad, void* stream);
+int  ast_segment_buffer(ast_ctx* ctx, int32_t backward, int32_t seg, float** d_buf);
 
 /* cfg.extracts[layer] of the last forward (model.py:116), [B,T,128] fp32 -> d_out.  Debug/parity.
  * After ast_embeds every layer is available.  After ast_step* in the tensor-core tier only the layers a head reads

@@ -38,8 +38,9 @@ def test_version_string(lib):
 
 
 def test_config_struct_layout_matches_header():
-    # 3 + 1 + 32 + 1 + 32 + 4 int32 = 73 int32 -> padded to 296 bytes, then 4 int64, then 2 int32
-    assert C.sizeof(_lib.AstConfig) == 296 + 32 + 8
+    # 3 + 1 + 32 + 1 + 32 + 4 int32 = 73 int32 -> padded to 296 bytes, then 4 int64, then 3 int32 (+ 4 bytes of tail padding)
+    assert C.sizeof(_lib.AstConfig) == 296 + 32 + 16
+    assert _lib.AstConfig.halo_exchange.offset == 296 + 32 + 8
     assert _lib.AstConfig.total_T.offset == 296
 
 

@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 
 def test_default_build_exports_no_debug_hooks():
     lib = _lib.load()
-    for name in ("ast_debug_timeline", "ast_debug_skip_publish", "ast_debug_tl_layer", "ast_opt_debug_stamps", "ast_debug_skipw"):
+    for name in ("ast_debug_timeline", "ast_debug_skip_publish", "ast_debug_tl_layer", "ast_opt_debug_stamps", "ast_debug_skipw", "ast_debug_group_tiles"):
         assert not hasattr(lib, name), name
 
 
