@@ -136,6 +136,14 @@ def gpu_targets(st, content, style):
     return Pc, l2n(Gc + Gs - Gc)
 
 
+def workload_config(name, wl, B, world, sharded):
+    """The `config` object: the workload only, the SAME keys and values in both arms (the driver compares them)."""
+    return {"workload": name, "desc": wl["desc"], "T": wl["T"], "n_layers": wl["NL"], "style_layers": wl["L"],
+            "gatys": wl["gatys"], "pairs_per_gpu": B,
+            "parallelism": ("time-sharded x%d" % world) if sharded else ("pairs dp%d" % world),
+            "weights": "random-init (seed 0)"}
+
+
 def cpu_step_factory(wl, threads):
     """The CPU arm: oracle/torch_step.py (torch-CPU fp32 restatement, kind='port').  The reference's own
     TF1 CPU path cannot run on this image (no TensorFlow for Python 3.12, no network)."""
@@ -180,8 +188,9 @@ def run_reference(args):
         "impl": "reference", "metric": "fwd+bwd+Gram-loss steps/sec @16384 samples", "value": sps, "unit": "steps/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": name, "desc": wl["desc"], "T": wl["T"], "n_layers": wl["NL"], "style_layers": wl["L"],
-                   "gatys": wl["gatys"], "pairs": 1, "weights": "random-init (seed 0)"},
+        "config": workload_config(name, wl, 8 if name == "cfg3" and not args.pairs else (args.pairs or 1), args.gpus,
+                                  name in TIME_SHARDED and args.gpus > 1),
+        "timing": {"note": "one pair evaluated per step on rank 0's host cores (the CPU arm does not batch or shard)"},
         "audio_sec_per_sec": sps * wl["T"] / SR,
         "cpu_baseline": {"value": sps, "unit": "steps/s", "cores": cores, "kind": "port",
                          "sample": f"{n} full evaluations of the workload timed (of --steps {args.steps}); torch-CPU fp32 "
@@ -190,6 +199,136 @@ def run_reference(args):
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def nccl_exchange(pairs):
+    """HaloShardedStep's exchange over NCCL: one batched group of sends / receives of 512 KB row blocks (NVLink)."""
+    import torch.distributed as dist
+    ops = []
+    for send, recv, peer in pairs:
+        ops.append(dist.P2POp(dist.isend, send, peer))
+        ops.append(dist.P2POp(dist.irecv, recv, peer))
+    for r in dist.batch_isend_irecv(ops):
+        r.wait()
+
+
+def run_timesharded(name, precision, rank, world, local, steps, warmup, mode="halo"):
+    """One long clip time-sharded over the ranks (BASELINE configs[2] / [4]): per-rank windows, halo rows exchanged stack by
+    stack between neighbours (mode "halo": HaloShardedStep) or 2R-overlapped windows without any exchange (mode
+    "overlap": TimeShardedStep), ONE all-reduce of the raw Gram / content partials per step.  Before timing, the owned
+    gradient slices are gathered and compared with the unsharded step evaluated on rank 0 (same kernels, one GPU), which
+    is also timed there: efficiency = t(1 GPU) / (N * t(N GPUs)).  Returns the record (meaningful on rank 0)."""
+    import torch
+    import torch.distributed as dist
+    from audio_style_transfer_b200.step import StyleStep
+    from audio_style_transfer_b200.sharding import HALO, HaloShardedStep, TimeShardedStep
+    dev = torch.device("cuda", local)
+    wl = build_workload(name, 1)
+    T, NL = wl["T"], wl["NL"]
+    x_full = torch.as_tensor(wl["x"], device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def barrier():
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, n):
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n)]
+        for a, b in ev:
+            flush.zero_()
+            a.record(); fn(); b.record()
+        torch.cuda.synchronize()
+        return sum(a.elapsed_time(b) for a, b in ev) / n
+
+    # ---- unsharded context: targets on every rank; on rank 0 also the reference result and the 1-GPU time ----------
+    full = StyleStep(T, wl["cont"], wl["style"], wl["gatys"], precision=precision, device=local)
+    full.set_weights(wl["w"])
+    Pc, Ps = gpu_targets(full, torch.as_tensor(wl["content"], device=dev), torch.as_tensor(wl["style_a"], device=dev))
+    n1_ms, lo_full, g_full, n1_launches = None, None, None, None
+    if rank == 0:
+        full.set_targets(Pc, Ps, wl["lambd"])
+        lo_full, g_full = torch.empty((1, 4), device=dev), torch.empty((1, T), device=dev)
+        for _ in range(3):
+            full.step_graph(x_full, lo_full, g_full)
+        n1_ms = timed(lambda: full.step_graph(x_full, lo_full, g_full), max(5, min(steps, 20)))
+        full.check()
+        n1_launches = full.launches_per_step
+    full.close()
+    del full
+    torch.cuda.empty_cache()
+    barrier()
+
+    def make_ctx(Tw, window):
+        c = StyleStep(Tw, wl["cont"], wl["style"], wl["gatys"], precision=precision, device=local, window=window,
+                      halo_exchange=(mode == "halo"))
+        c.set_weights(wl["w"])
+        return c
+    if mode == "halo":
+        sh = HaloShardedStep(T, rank, world, make_ctx, lambda p: dist.all_reduce(p), nccl_exchange)
+    else:
+        sh = TimeShardedStep(T, NL, rank, world, make_ctx, lambda p: dist.all_reduce(p))
+    st = sh.ctx
+    st.set_targets(sh.window(Pc).contiguous(), Ps, wl["lambd"])
+    x = sh.window(x_full).contiguous()
+    losses = torch.empty((1, 4), device=dev)
+    grad = torch.empty((1, st.T), device=dev)
+    if mode == "halo":
+        one_step = lambda: sh.step(x, losses, grad)
+    else:
+        def one_step():
+            st.forward_partial(x)
+            dist.all_reduce(st.partials())
+            st.backward(losses, grad)
+    # ---- correctness of the real NCCL + CUDA path: owned gradient slices vs the unsharded step -------------------
+    one_step()
+    st.check()
+    own = grad[0, sh.ob - sh.wb:sh.oe - sh.wb].contiguous()
+    sizes = [oe - ob for (_, _, ob, oe) in sh.plan]
+    pad = max(sizes)
+    mine = torch.zeros(pad, device=dev)
+    mine[:own.numel()] = own
+    parts = [torch.empty(pad, device=dev) for _ in range(world)]
+    dist.all_gather(parts, mine)
+    check = None
+    if rank == 0:
+        g = torch.cat([p[:n] for p, n in zip(parts, sizes)])
+        check = {"grad_rel_l2_vs_unsharded": float((g - g_full[0]).double().norm() / g_full[0].double().norm()),
+                 "loss_rel": float(abs(losses[0, 0] - lo_full[0, 0]) / abs(lo_full[0, 0])),
+                 "tolerance": 1e-2, "gathered_with": "all_gather of the owned slices over NCCL"}
+    for _ in range(max(3, warmup)):
+        one_step()
+    barrier()
+    ms = timed(one_step, steps)
+    barrier()
+    parts_buf = st.partials()
+    ar_ms = timed(lambda: dist.all_reduce(parts_buf), 20)
+    ex_ms = None
+    if mode == "halo" and world > 1:
+        buf = st.segment_buffer(False, 0)
+        ob, oe, H = sh.ob, sh.oe, HALO
+        ex_ms = timed(lambda: sh._swap(buf, (ob + H, ob + 2 * H), (ob - 2 * H, ob - H), (oe - 2 * H, oe - H), (oe + H, oe + 2 * H)), 20)
+    t = torch.tensor([ms, ar_ms, ex_ms or 0.0, float(st.T)], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ar_ms, ex_ms, win_max = [float(v) for v in t]
+    launches, nseg = st.launches_per_step, st.segments
+    st.check()
+    st.close()
+    if rank != 0:
+        return None
+    flops = algorithmic_flops(T, NL, wl["L"], wl["gatys"])
+    return {"workload": name, "desc": wl["desc"], "mode": "halo exchange per 10-layer stack (HaloShardedStep)" if mode == "halo"
+            else "2R-overlapped windows, no exchange (TimeShardedStep)",
+            "T": T, "n_gpus": world, "ms_per_step": ms, "steps_per_s": 1e3 / ms, "audio_sec_per_sec": T / SR * 1e3 / ms,
+            "n1_ms_per_step": n1_ms, "speedup_vs_own_n1": n1_ms / ms, "efficiency_vs_own_n1": n1_ms / ms / world,
+            "allreduce_us": ar_ms * 1e3, "allreduce_bytes": int(parts_buf.numel()) * 4,
+            "halo_exchange_us": ex_ms * 1e3 if mode == "halo" else None,
+            "halo_bytes_per_message": HALO * 128 * 4 if mode == "halo" else 0,
+            "collectives_per_step": (1 + 2 * (nseg - 1)) if mode == "halo" else 1,
+            "window_rows_max": int(win_max), "owned_rows": T // world,
+            "redundant_rows_frac": (win_max - T / world) / (T / world),
+            "launches_per_step": launches, "n1_launches_per_step": n1_launches,
+            "model_tflops": flops / (ms * 1e-3) / 1e12, "check": check,
+            "timing": "CUDA events, L2 flushed between steps, max over ranks; eager launches + NCCL (no graph)"}
 
 
 def run_ours(args):
@@ -218,43 +357,47 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def finish():
+        if world > 1:
+            dist.destroy_process_group()
+
+    # ---- a time-sharded clip as the headline workload (--workload cfg2 / cfg4 on N > 1 GPUs) ------------------------
+    if sharded:
+        with ClockSampler(local) as clk:
+            rec = run_timesharded(name, args.precision, rank, world, local, args.steps, args.warmup, args.shard_mode)
+        if rank == 0:
+            line = {
+                "metric": "fwd+bwd+Gram-loss steps/sec @16384 samples", "value": rec["steps_per_s"], "unit": "steps/s",
+                "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": rec["ms_per_step"],
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "bf16 (fwd operands 2-term bf16 split, fp32 accumulate in TMEM)" if args.precision == "bf16" else "f32",
+                "data": "synthetic", "config": workload_config(name, wl, B, world, True),
+                "timing": {"l2": "flushed between timed steps (256 MiB memset outside the events)",
+                           "graph": "eager launches + NCCL", "clock": "CUDA events on the launching stream, max over ranks"},
+                "audio_sec_per_sec": rec["audio_sec_per_sec"], "algorithmic_gflop_per_step": algorithmic_flops(T, NL, L, wl["gatys"]) / 1e9,
+                "model_tflops": rec["model_tflops"], "gpu_launches": rec["launches_per_step"] * args.steps,
+                "launches_per_step": rec["launches_per_step"], "clocks": clk.summary(), "timesharded": rec,
+            }
+            print(json.dumps(line), flush=True)
+        ok = rank != 0 or (rec["check"]["grad_rel_l2_vs_unsharded"] <= 1e-2 and rec["check"]["loss_rel"] <= 1e-2)
+        finish()
+        if not ok:
+            raise SystemExit("bench.py: the time-sharded gradient does not match the unsharded step")
+        return
+
     # ---- contexts + targets (product path) -----------------------------------------------------
     x_full = torch.as_tensor(wl["x"], device=dev)
-    if sharded:
-        full = StyleStep(T, wl["cont"], wl["style"], wl["gatys"], B=B, precision=args.precision, device=local)
-        full.set_weights(wl["w"])
-        Pc, Ps = gpu_targets(full, torch.as_tensor(wl["content"], device=dev), torch.as_tensor(wl["style_a"], device=dev))
-        full.close()
+    st = StyleStep(T, wl["cont"], wl["style"], wl["gatys"], B=B, precision=args.precision, device=local)
+    st.set_weights(wl["w"])
+    Pc, Ps = gpu_targets(st, torch.as_tensor(wl["content"], device=dev), torch.as_tensor(wl["style_a"], device=dev))
+    st.set_targets(Pc, Ps, wl["lambd"])
+    x = x_full
+    losses = torch.empty((B, 4), device=dev)
+    grad = torch.empty((B, T), device=dev)
 
-        def make_ctx(Tw, window):
-            s = StyleStep(Tw, wl["cont"], wl["style"], wl["gatys"], B=B, precision=args.precision, device=local, window=window)
-            s.set_weights(wl["w"])
-            return s
-        ts = TimeShardedStep(T, NL, rank, world, make_ctx, lambda p: dist.all_reduce(p))
-        st = ts.ctx
-        st.set_targets(ts.window(Pc).contiguous(), Ps, wl["lambd"])
-        x = ts.window(x_full).contiguous()
-        own = ts.oe - ts.ob
-        losses = torch.empty((B, 4), device=dev)
-        grad = torch.empty((B, st.T), device=dev)
-
-        def one_step():
-            st.forward_partial(x)
-            dist.all_reduce(st.partials())
-            st.backward(losses, grad)
-        units_per_step = B            # whole-job: one evaluation of B clips per step, all ranks together
-    else:
-        st = StyleStep(T, wl["cont"], wl["style"], wl["gatys"], B=B, precision=args.precision, device=local)
-        st.set_weights(wl["w"])
-        Pc, Ps = gpu_targets(st, torch.as_tensor(wl["content"], device=dev), torch.as_tensor(wl["style_a"], device=dev))
-        st.set_targets(Pc, Ps, wl["lambd"])
-        x = x_full
-        losses = torch.empty((B, 4), device=dev)
-        grad = torch.empty((B, T), device=dev)
-
-        def one_step():
-            st.step_graph(x, losses, grad)
-        units_per_step = B * world    # independent pairs on every rank (weak scaling)
+    def one_step():
+        st.step_graph(x, losses, grad)
+    units_per_step = B * world    # independent pairs on every rank (weak scaling)
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
 
@@ -373,9 +516,25 @@ def run_ours(args):
                 "bwd": {"kernel": kbwd, "achieved": fl_bwd / dur_bwd / 1e12, "avg_launch_us": dur_bwd * 1e6,
                         "note": "duration = heads + head gradients + backward sweep + start-conv adjoint phase"},
                 "phases_ms": {"encoder_fwd": enc_ms, "gram_partials": gram_ms, "heads_bwd": bwd_ms, "total": tot_ms}}
+    # ---- N > 1: the time-sharded configs in the SAME run (the headline above stays independent pairs) ----------------
+    # configs[2] (65536-sample clip) at every N, configs[4] (479232 samples, 30 channel-wise style layers) at N = 8: halo
+    # exchange per stack + one all-reduce per step, each checked against the unsharded step before it is timed
+    shard_recs = []
+    if world > 1 and not args.no_timesharded:
+        launches_per_step = st.launches_per_step
+        st.close()
+        del flush
+        torch.cuda.empty_cache()
+        for wname in (["cfg2"] + (["cfg4"] if world == 8 else [])):
+            try:
+                rec = run_timesharded(wname, args.precision, rank, world, local, min(args.steps, 30), args.warmup, args.shard_mode)
+            except Exception as e:      # noqa: BLE001 -- reported, the headline line still prints
+                rec = {"workload": wname, "error": repr(e)}
+            shard_recs.append(rec)
+    else:
+        launches_per_step = st.launches_per_step
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
+        finish()
         return
     flops = algorithmic_flops(T, NL, L, wl["gatys"], B)
     line = {
@@ -384,17 +543,19 @@ def run_ours(args):
         "higher_is_better": True, "scaling": "strong" if sharded else "weak", "vs_baseline": None,
         "dtype": "bf16 (fwd operands 2-term bf16 split, fp32 accumulate in TMEM)" if args.precision == "bf16" else "f32",
         "data": "synthetic",
-        "config": {"workload": name, "desc": wl["desc"], "T": T, "n_layers": NL, "style_layers": L, "gatys": wl["gatys"],
-                   "pairs_per_gpu": B, "parallelism": ("time-sharded x%d" % world) if sharded else ("pairs dp%d" % world),
-                   "weights": "random-init (seed 0)", "l2": "flushed between timed steps (256 MiB memset outside the events)",
-                   "graph": "one cudaGraphLaunch per step"},
+        "config": workload_config(name, wl, B, world, sharded),
+        "timing": {"l2": "flushed between timed steps (256 MiB memset outside the events)",
+                   "graph": "eager launches + NCCL" if sharded else "one cudaGraphLaunch per step",
+                   "clock": "CUDA events on the launching stream, max over ranks"},
         "audio_sec_per_sec": value * T / SR,
         "algorithmic_gflop_per_step": flops / 1e9,
         "model_tflops": flops * (1.0 if sharded else world) / (ms_per_step * 1e-3) / 1e12,
-        "gpu_launches": st.launches_per_step * args.steps,
-        "launches_per_step": st.launches_per_step,
+        "gpu_launches": launches_per_step * args.steps,
+        "launches_per_step": launches_per_step,
         "clocks": clk.summary(),
     }
+    if shard_recs:
+        line["timesharded"] = shard_recs[0] if len(shard_recs) == 1 else shard_recs
     if not sharded:
         line["e2e"] = {"value": units_per_step / (e2e_ms / args.steps * 1e-3), "unit": "steps/s",
                        "h2d_bytes_per_step": B * T * 4, "d2h_bytes_per_step": (B * T + 4 * B) * 4,
@@ -411,8 +572,10 @@ def run_ours(args):
                                 "sample": f"{n} full evaluations of the same workload (torch-CPU fp32 restatement, "
                                           "oracle/torch_step.py; reference TF1 path unavailable on this image)"}
     print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    finish()
+    bad = [r for r in shard_recs if r and ("error" in r or r["check"]["grad_rel_l2_vs_unsharded"] > 1e-2 or r["check"]["loss_rel"] > 1e-2)]
+    if bad:
+        raise SystemExit(f"bench.py: time-sharded self-check failed: {bad}")
 
 
 def main():
@@ -425,6 +588,10 @@ def main():
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--pairs", type=int, default=0, help="independent pairs per GPU (B); default 1, cfg3: 8")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--shard-mode", dest="shard_mode", default="halo", choices=["halo", "overlap"],
+                    help="time-sharded clips: halo rows exchanged stack by stack (default) or 2R-overlapped windows without exchange")
+    ap.add_argument("--no-timesharded", dest="no_timesharded", action="store_true",
+                    help="N > 1: skip the time-sharded configs[2] / configs[4] records measured next to the headline")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
