@@ -505,12 +505,12 @@ def run_ours(args):
             fl_bwd, dur_bwd, kbwd = fl_layer, bwd_ms * 1e-3 / (NL + 1), "tc_bwd_kernel"
         ach = fl_launch / dur_fwd / 1e12
         traffic = None
-        tj = ROOT / "profiles" / "r1_traffic.json"
+        tj = ROOT / "profiles" / "r2_traffic.json"
         if tj.exists() and name == "cfg1" and B == 1 and args.precision == "bf16":     # captured on exactly this workload
             traffic = json.loads(tj.read_text()).get(kname, {}).get("traffic")
         roof = {"bound": "tensor", "kernel": kname,
                 "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": ach / pk["tflops"], "traffic": traffic,
-                "traffic_source": "profiles/r1_traffic.json (ncu --set full, dram read+write per launch)" if traffic else None,
+                "traffic_source": "profiles/r2_traffic.json (ncu --set full, dram read+write per launch)" if traffic else None,
                 "peak_source": pk["src"] + " (bf16 sustained)", "flops_per_launch": fl_launch,
                 "avg_launch_us": dur_fwd * 1e6, "note": note,
                 "bwd": {"kernel": kbwd, "achieved": fl_bwd / dur_bwd / 1e12, "avg_launch_us": dur_bwd * 1e6,
