@@ -76,6 +76,7 @@ struct ast_ctx {
     float *Pc, *Ps;
     const float** d_Fptr;
     float** d_dFptr;
+    OursPtrs ours_ptrs;            // the same tables by value for the tensor-core channel-wise head
     const float** d_Hcptr;
     float lambd;
     // gamma term (stft_reg.cu): frames [reg_f_lo, reg_f_lo + reg_nf) of the clip are evaluated here, the ones
@@ -279,6 +280,8 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
         const float* fp[AST_MAX_IDS] = {nullptr}; float* dfp[AST_MAX_IDS] = {nullptr}; const float* hc[AST_MAX_IDS] = {nullptr};
         for (int i = 0; i < c->L; ++i) { fp[i] = Hl(c, c->style_layer[i] + 1); dfp[i] = dFb(c, c->head_buf[c->style_layer[i]]); }
         for (int i = 0; i < c->n_cont; ++i) hc[i] = Hl(c, c->cont_layer[i] + 1);
+        memset(&c->ours_ptrs, 0, sizeof(c->ours_ptrs));
+        for (int i = 0; i < c->L && i < 32; ++i) { c->ours_ptrs.F[i] = fp[i]; c->ours_ptrs.dF[i] = dfp[i]; }
         cudaMemcpy(c->d_Fptr, fp, sizeof(fp), cudaMemcpyHostToDevice);
         cudaMemcpy(c->d_dFptr, dfp, sizeof(dfp), cudaMemcpyHostToDevice);
         cudaMemcpy(c->d_Hcptr, hc, sizeof(hc), cudaMemcpyHostToDevice);
@@ -445,7 +448,7 @@ static void run_gram(ast_ctx* c, cudaStream_t s, bool fused = false) {
     else if (c->cfg.gatys)
         launch_gram_gatys(c->d_Fptr, c->L, c->T, c->B, c->own_lo, c->own_hi, c->gram_part, c->gram_nchunk, c->gram_chunk_rows, s);
     else
-        if (c->gram_ours_tc) launch_gram_ours_tc(c->d_Fptr, c->L, c->T, c->B, c->own_lo, c->own_hi, c->gram_part, c->gram_nchunk, c->gram_chunk_rows, s);
+        if (c->gram_ours_tc) launch_gram_ours_tc(c->ours_ptrs, c->L, c->T, c->B, c->own_lo, c->own_hi, c->gram_part, c->gram_nchunk, c->gram_chunk_rows, s);
         else launch_gram_ours(c->d_Fptr, c->L, c->T, c->B, c->own_lo, c->own_hi, c->gram_part, c->gram_nchunk, c->gram_chunk_rows, s);
     if (!fold_gram_reduce(c, fused))
         launch_gram_reduce(c->gram_part, c->partials, c->cfg.gatys, c->L, c->B, c->gram_nchunk, s);
@@ -538,7 +541,7 @@ static int step_backward_impl(ast_ctx* c, float* d_losses, float* d_grad, void* 
         tc_style_grad(c->tc, c->L, hos, s);
     }
     else if (c->cfg.gatys) launch_style_grad_gatys(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
-    else if (c->gram_ours_tc && !exp_switch("AST_B200_SGO_CUDA")) launch_style_grad_ours_tc(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
+    else if (c->gram_ours_tc && !exp_switch("AST_B200_SGO_CUDA")) launch_style_grad_ours_tc(c->ours_ptrs, c->Ssym, c->L, c->T, c->B, s);
     else              launch_style_grad_ours(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
     if (do_top) {
         bool init[30];

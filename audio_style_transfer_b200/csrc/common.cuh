@@ -52,8 +52,12 @@ int  gram_ours_max_small_L();     // L up to which launch_gram_ours uses the one
 // tensor-core tier, 13 <= L <= 32 (gram_ours_tc.cu): per-channel 32 x 32 Gram by mma.sync with 3xTF32 operands
 int  gram_ours_tc_supported(int L);
 int  style_grad_ours_tc_supported(int L);
-void launch_style_grad_ours_tc(const float* const* d_F, float* const* d_dF, const float* Ssym, int L, int T, int B, cudaStream_t s);
-void launch_gram_ours_tc(const float* const* d_F, int L, int T, int B, int own_lo, int own_hi,
+// Per-layer base pointers of the style extracts / their gradient buffers, passed BY VALUE (kernel parameter space ->
+// uniform constant loads): indexing a pointer array in global memory inside the streaming loops put a dependent global
+// load in front of every address (ncu, round 2: 26 % of the style-gradient kernel's stall samples).
+struct OursPtrs { const float* F[32]; float* dF[32]; };
+void launch_style_grad_ours_tc(const OursPtrs& ptrs, const float* Ssym, int L, int T, int B, cudaStream_t s);
+void launch_gram_ours_tc(const OursPtrs& ptrs, int L, int T, int B, int own_lo, int own_hi,
                          float* part, int nchunk, int chunk_rows, cudaStream_t s);
 void launch_gram_gatys(const float* const* d_F, int L, int T, int B, int own_lo, int own_hi,
                        float* part, int nchunk, int chunk_rows, cudaStream_t s);

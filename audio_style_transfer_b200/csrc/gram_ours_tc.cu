@@ -5,7 +5,11 @@
 // tensor-core tier (gram_ours_kernel, kernels_f32.cu) is issue-bound: 640 FMAs per (t, c), 155 us for 252 MB at L = 30,
 // T = 16384 (FMA bound 37 us, HBM bound 39 us).  The shape -- 128 independent 32 x 32 accumulators, K streamed from HBM once
 // -- does not fit tcgen05's 128-row tiles and shared-memory descriptors, so this is warp-level `mma.sync.m16n8k8` with
-// TF32 operands split in two terms (hi hi + hi lo + lo hi: fp32-grade products, fp32 accumulate).
+// single-pass TF32 operands (round to nearest, 2^-11 per operand -- four times finer than the bf16 extract copies the
+// Gatys Gram of the same tier multiplies; the unbiased product errors average over the 16384 terms of a sum: measured
+// Gn rel-L2 vs fp64 in tests/test_gpu_parity.py), fp32 accumulate.  Round 1 split the operands in two terms (3 MMAs per
+// product): ncu showed the kernel throttling on exactly that tensor work (math pipe throttle the top stall, 48 % pipe
+// activity, profiles/r2_ncu_stack_and_head_kernels.md).
 //
 // A warp owns 2 channels.  With K = t, the A fragment (rows = layer, cols = t) and the B fragment (k = t, n = layer) of
 // V V^T are the same loads: per k-step of 8 rows a lane reads V[g + 8a][tig + 4b] (g = lane / 4, tig = lane % 4,
@@ -39,7 +43,7 @@ __device__ __forceinline__ void mma_tf32(float (&c)[4], uint32_t a0, uint32_t a1
 }
 
 // grid = (nchunk, 4 channel quads, B); part[b][chunk][c][l][m] like the CUDA-core kernels.
-__global__ void __launch_bounds__(GT_THREADS, 1) gram_ours_tc_kernel(const float* const* __restrict__ F, int L, int T, int own_lo,
+__global__ void __launch_bounds__(GT_THREADS, 1) gram_ours_tc_kernel(const __grid_constant__ OursPtrs P, int L, int T, int own_lo,
                                                                     int own_hi, float* __restrict__ part, int nchunk, int chunk_rows) {
     extern __shared__ __align__(16) float gt_s[];          // [2 stages][32 channels][32 layers][GT_PT] (+1 per plane)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -59,7 +63,7 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gram_ours_tc_kernel(const float
             const int i = tid + it * GT_THREADS;
             const int q = i & 7, t = (i >> 3) & (GT_R - 1), l = i / (8 * GT_R);
             const bool ok = it < nld && l < L && t0 + t < t_hi;
-            pf[it] = ok ? *reinterpret_cast<const float4*>(F[l] + ((size_t)b * T + t0 + t) * AST_C + c0 + q * 4)
+            pf[it] = ok ? *reinterpret_cast<const float4*>(P.F[l < 32 ? l : 0] + ((size_t)b * T + t0 + t) * AST_C + c0 + q * 4)
                         : make_float4(0.f, 0.f, 0.f, 0.f);
         }
     };
@@ -91,23 +95,17 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gram_ours_tc_kernel(const float
             const float* pl = st + (warp * 2 + ch) * GT_PL + g * GT_PT + tig;
 #pragma unroll
             for (int ks = 0; ks < GT_R / 8; ++ks) {
-                uint32_t hi[4][2], lo[4][2];                               // V[g + 8a][8 ks + tig + 4 bb]
+                uint32_t hi[4][2];                                         // V[g + 8a][8 ks + tig + 4 bb]
 #pragma unroll
                 for (int a = 0; a < 4; ++a)
 #pragma unroll
-                    for (int bb = 0; bb < 2; ++bb) {
-                        const float v = pl[(8 * a) * GT_PT + 8 * ks + 4 * bb];
-                        hi[a][bb] = tf32_of(v);
-                        lo[a][bb] = tf32_of(v - __uint_as_float(hi[a][bb]));
-                    }
+                    for (int bb = 0; bb < 2; ++bb) hi[a][bb] = tf32_of(pl[(8 * a) * GT_PT + 8 * ks + 4 * bb]);
                 // tiles (row block of 16 layers, column block of 8 layers), upper triangle: (0,0..3), (1,2..3)
 #pragma unroll
                 for (int tl = 0; tl < 6; ++tl) {
                     const int mt = tl < 4 ? 0 : 1, j = tl < 4 ? tl : tl - 2;
                     const int a0 = 2 * mt, a1 = 2 * mt + 1;
                     mma_tf32(acc[ch][tl], hi[a0][0], hi[a1][0], hi[a0][1], hi[a1][1], hi[j][0], hi[j][1]);
-                    mma_tf32(acc[ch][tl], hi[a0][0], hi[a1][0], hi[a0][1], hi[a1][1], lo[j][0], lo[j][1]);
-                    mma_tf32(acc[ch][tl], lo[a0][0], lo[a1][0], lo[a0][1], lo[a1][1], hi[j][0], hi[j][1]);
                 }
             }
         }
@@ -154,7 +152,7 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gram_ours_tc_kernel(const float
 
 int gram_ours_tc_supported(int L) { return L > gram_ours_max_small_L() && L <= 32; }
 
-void launch_gram_ours_tc(const float* const* d_F, int L, int T, int B, int own_lo, int own_hi, float* part, int nchunk,
+void launch_gram_ours_tc(const OursPtrs& ptrs, int L, int T, int B, int own_lo, int own_hi, float* part, int nchunk,
                          int chunk_rows, cudaStream_t s) {
     const size_t smem = (size_t)2 * GT_STAGE * sizeof(float);
     static bool once = false;
@@ -163,7 +161,7 @@ void launch_gram_ours_tc(const float* const* d_F, int L, int T, int B, int own_l
         once = true;
     }
     dim3 grid(nchunk, AST_C / 32, B);
-    gram_ours_tc_kernel<<<grid, GT_THREADS, smem, s>>>(d_F, L, T, own_lo, own_hi, part, nchunk, chunk_rows);
+    gram_ours_tc_kernel<<<grid, GT_THREADS, smem, s>>>(ptrs, L, T, own_lo, own_hi, part, nchunk, chunk_rows);
     ast_launch_counter += 1;
 }
 
@@ -172,7 +170,7 @@ void launch_gram_ours_tc(const float* const* d_F, int L, int T, int B, int own_l
 //   dF_l[t, c] = sum_m Ssym[c, l, m] F_m[t, c]        (Ssym = dG + dG^T, symmetric)
 // Per channel: OUT[t][l] = V^T[t][m] S[m][l]: M = t (16 rows per round), K = m (4 k-steps), N = l (4 tiles of 8).
 // The coefficient block of a warp's 2 channels lives in registers for the whole CTA as TF32 B fragments (rounded once:
-// 2^-11 relative, the same class as the bf16 Ssym of the Gatys path); the A operand is split in two TF32 terms.
+// 2^-11 relative, the same class as the bf16 Ssym of the Gatys path); so is the A operand (round 1 split it in two terms).
 // Staging [channel][layer][t] with row pitch 24 (banks 24 tig + g all distinct) is filled by 4-byte cp.async (HBM rows are
 // [t][channel]; no register staging, so the next round is in flight while this one is computed and written out).
 // Outputs go back through the consumed stage as [l][t][c] (pitches 548 / 33: conflict-free both ways) and leave as
@@ -194,8 +192,7 @@ __device__ __forceinline__ void cp_async4(uint32_t dst, const void* src, bool va
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(sz) : "memory");
 }
 
-__global__ void __launch_bounds__(ST_THREADS, 1) style_grad_ours_tc_kernel(const float* const* __restrict__ F,
-                                                                          float* const* __restrict__ dF,
+__global__ void __launch_bounds__(ST_THREADS, 1) style_grad_ours_tc_kernel(const __grid_constant__ OursPtrs P,
                                                                           const float* __restrict__ Ssym, int L, int T,
                                                                           int rows_per_cta) {
     extern __shared__ __align__(16) float st_s[];          // [2][ST_STAGE]
@@ -225,12 +222,12 @@ __global__ void __launch_bounds__(ST_THREADS, 1) style_grad_ours_tc_kernel(const
         if (round < nround) {
             const uint32_t dst = smem_u32(st_s + (round & 1) * ST_STAGE);
             const int t0 = t_lo + round * ST_R;
-            for (int i = tid; i < L * ST_R * 32; i += ST_THREADS) {
-                const int c = i & 31, t = (i >> 5) & (ST_R - 1), l = i / (32 * ST_R);
-                const bool ok = t0 + t < t_hi;
-                const float* src = F[l] + ((size_t)b * T + (ok ? t0 + t : t_lo)) * AST_C + c0 + c;
-                cp_async4(dst + (uint32_t)(c * ST_PL + l * ST_PT + t) * 4u, src, ok);
-            }
+            // ST_THREADS == 32 * ST_R: a thread keeps its (t, c) and walks the layers; the layer's base pointer is uniform
+            const int c = tid & 31, t = tid >> 5;
+            const bool ok = t0 + t < t_hi;
+            const size_t off = ((size_t)b * T + (ok ? t0 + t : t_lo)) * AST_C + c0 + c;
+            const uint32_t d0 = dst + (uint32_t)(c * ST_PL + t) * 4u;
+            for (int l = 0; l < L; ++l) cp_async4(d0 + (uint32_t)(l * ST_PT) * 4u, P.F[l] + off, ok);
         }
         cp_async_commit_st();
     };
@@ -251,18 +248,11 @@ __global__ void __launch_bounds__(ST_THREADS, 1) style_grad_ours_tc_kernel(const
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks) {
                 // A(row t, col m) = V[m][t]: a0 (t = g, m = 8 ks + tig), a1 (t = g + 8, m), a2 (t = g, m + 4), a3 (t = g + 8, m + 4)
-                uint32_t ah[4], al[4];
+                uint32_t ah[4];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const float v = pl[(8 * ks + 4 * (k >> 1)) * ST_PT + 8 * (k & 1)];
-                    ah[k] = tf32_of(v);
-                    al[k] = tf32_of(v - __uint_as_float(ah[k]));
-                }
+                for (int k = 0; k < 4; ++k) ah[k] = tf32_of(pl[(8 * ks + 4 * (k >> 1)) * ST_PT + 8 * (k & 1)]);
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    mma_tf32(acc[ch][j], ah[0], ah[1], ah[2], ah[3], bf[ch][ks][j][0], bf[ch][ks][j][1]);
-                    mma_tf32(acc[ch][j], al[0], al[1], al[2], al[3], bf[ch][ks][j][0], bf[ch][ks][j][1]);
-                }
+                for (int j = 0; j < 4; ++j) mma_tf32(acc[ch][j], ah[0], ah[1], ah[2], ah[3], bf[ch][ks][j][0], bf[ch][ks][j][1]);
             }
         }
         __syncthreads();                                                  // everyone is done reading this stage: reuse it for the outputs
@@ -278,9 +268,14 @@ __global__ void __launch_bounds__(ST_THREADS, 1) style_grad_ours_tc_kernel(const
                 }
         __syncthreads();
         const int t0 = t_lo + round * ST_R;
-        for (int i = tid; i < L * ST_R * 32; i += ST_THREADS) {           // 32 lanes = one 128-byte row of dF_l
-            const int c = i & 31, t = (i >> 5) & (ST_R - 1), l = i / (32 * ST_R);
-            if (t0 + t < t_hi) dF[l][((size_t)b * T + t0 + t) * AST_C + c0 + c] = st[l * ST_OPL + t * ST_OPT + c];
+        {                                                                 // 32 lanes = one 128-byte row of dF_l
+            const int c = tid & 31, t = tid >> 5;
+            if (t0 + t < t_hi) {
+                const size_t off = ((size_t)b * T + t0 + t) * AST_C + c0 + c;
+                const float* so = st + t * ST_OPT + c;
+#pragma unroll 6
+                for (int l = 0; l < L; ++l) P.dF[l][off] = so[l * ST_OPL];
+            }
         }
         __syncthreads();                                                  // outputs are out: the stage may be refilled
         // the refill must leave layers L..31 of the INPUT layout zero: the output staging has just overwritten parts of them
@@ -295,7 +290,8 @@ __global__ void __launch_bounds__(ST_THREADS, 1) style_grad_ours_tc_kernel(const
 
 int style_grad_ours_tc_supported(int L) { return gram_ours_tc_supported(L); }
 
-void launch_style_grad_ours_tc(const float* const* d_F, float* const* d_dF, const float* Ssym, int L, int T, int B, cudaStream_t s) {
+static_assert(ST_THREADS == 32 * ST_R, "a thread of the style-gradient kernel owns one (t, c) of a round");
+void launch_style_grad_ours_tc(const OursPtrs& ptrs, const float* Ssym, int L, int T, int B, cudaStream_t s) {
     const size_t smem = (size_t)2 * ST_STAGE * sizeof(float);
     static bool once = false;
     if (!once) {
@@ -305,6 +301,6 @@ void launch_style_grad_ours_tc(const float* const* d_F, float* const* d_dF, cons
     const int nx = std::max(1, 148 / (4 * B));                            // one CTA per SM, one wave
     const int rows = std::max(ST_R, ((T + nx - 1) / nx + ST_R - 1) / ST_R * ST_R);
     dim3 grid((T + rows - 1) / rows, AST_C / 32, B);
-    style_grad_ours_tc_kernel<<<grid, ST_THREADS, smem, s>>>(d_F, d_dF, Ssym, L, T, rows);
+    style_grad_ours_tc_kernel<<<grid, ST_THREADS, smem, s>>>(ptrs, Ssym, L, T, rows);
     ast_launch_counter += 1;
 }
