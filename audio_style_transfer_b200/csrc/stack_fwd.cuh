@@ -142,8 +142,9 @@ __device__ __forceinline__ void stack_wait_flags(const unsigned* f0, const unsig
 }
 // Both K-half flags of every tile that holds rows [ta, ta+127] / [tb, tb+127] of pair b (far taps, anti-dependency).
 // Only tiles of this launch's group [g0, g1) are waited for (rows outside it are not produced by this launch).
+// jsel: 0 / 1 = only that K-half's flag, 2 = both.
 __device__ __forceinline__ void stack_wait_rows2(const unsigned* flags, int tiles_per_pair, int g0, int g1, int b, int ta, int tb,
-                                                 unsigned need, volatile unsigned* ab, unsigned* err) {
+                                                 unsigned need, volatile unsigned* ab, unsigned* err, int jsel = 2) {
     const bool la = !(ta + 127 < g0 || ta >= g1), lb = !(tb + 127 < g0 || tb >= g1);
     if (!la && !lb) return;
     if (!la) ta = tb;
@@ -158,7 +159,7 @@ __device__ __forceinline__ void stack_wait_rows2(const unsigned* flags, int tile
         for (int i = 0; i < 4; ++i) {
             unsigned vx, vy;
             asm volatile("ld.relaxed.gpu.global.v2.u32 {%0, %1}, [%2];" : "=r"(vx), "=r"(vy) : "l"(f[i]) : "memory");
-            ok = ok && vx >= need && vy >= need;
+            ok = ok && (jsel == 1 || vx >= need) && (jsel == 0 || vy >= need);
         }
         if (ok) break;
         if (++spins > FS_SPIN_LIMIT || stack_aborted(ab)) { stack_abort(ab, err, 1u); break; }
@@ -284,22 +285,23 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
                     load_w1(1, 0); load_w1(1, 1);
                     for (int j = 0; j < 2; ++j) { load_w1(0, j); load_w1(2, j); }
                 } else {
-                    // centre weights, then the first live side tap's weights (none of them waits for a neighbour), ONE poll
-                    // of all the flags this layer needs, then operand tiles (and the second tap's weights) as slots free up
+                    // centre weights, then K-half by K-half: the live side taps' weights (they wait for no neighbour), a poll of
+                    // THAT K-half's flags of the tiles the taps read, the shifted operand tiles.  The neighbours publish K-half 0
+                    // ~4.5k cycles before K-half 1: its taps' MMAs run while K-half 1 is still on its way.
                     load_w1(1, 0);
                     load_w1(1, 1);
                     const bool live0 = stack_tap_live(t0, 0, d, g0, g1), live2 = stack_tap_live(t0, 2, d, g0, g1);
-                    const int k1 = live0 ? 0 : 2;                      // first live side tap (if any)
                     if (live0 || live2) {
-                        load_w1(k1, 0);
-                        load_w1(k1, 1);
-                        stack_wait_rows2(p.flags, p.tiles_per_pair, g0, g1, b, live0 ? t0 - d : t0 + d, live2 ? t0 + d : t0 - d,
-                                         p.need[l], ab, p.err);
-                        fence_proxy_async_all();
-                        TLD(2);
-                        load_a(k1, 0);
-                        load_a(k1, 1);
-                        if (live0 && live2) { load_w1(2, 0); load_a(2, 0); load_w1(2, 1); load_a(2, 1); }
+                        for (int j = 0; j < 2; ++j) {
+                            if (live0) load_w1(0, j);
+                            if (live2) load_w1(2, j);
+                            stack_wait_rows2(p.flags, p.tiles_per_pair, g0, g1, b, live0 ? t0 - d : t0 + d, live2 ? t0 + d : t0 - d,
+                                             p.need[l], ab, p.err, j);
+                            fence_proxy_async_all();
+                            TLD(2 + j);
+                            if (live0) load_a(0, j);
+                            if (live2) load_a(2, j);
+                        }
                     }
                 }
                 for (int j = 0; j < 2; ++j) {                 // 1x1 weights, K-half j: hi rows then lo rows
@@ -373,27 +375,20 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
                     ++n_near;
                 } else {
                     const bool live0 = stack_tap_live(t0, 0, d, g0, g1), live2 = stack_tap_live(t0, 2, d, g0, g1);
-                    if (live0 || live2) {                                   // producer fill order: W W A A, then W A W A
-                        uint32_t sw[2];
-                        sw[0] = take(); sw[1] = take();
+                    if (live0 || live2) {                                   // producer fill order per K-half: W (W) A (A)
+                        const int ntap = (int)live0 + (int)live2;
                         for (int j = 0; j < 2; ++j) {
-                            const uint32_t sa = take();
-                            tc_fence_after();
-                            TLD(11 + j);
-                            mma_slice(acc1, s_ring + sa * F2_SLOT, s_ring + sa * F2_SLOT + TILE16, s_ring + sw[j] * F2_SLOT, 1u);
-                            umma_commit(bar + F2B_EMPTY(sa));
-                            umma_commit(bar + F2B_EMPTY(sw[j]));
-                        }
-                        if (live0 && live2)
-                            for (int j = 0; j < 2; ++j) {
-                                const uint32_t swj = take();
+                            uint32_t sw[2];
+                            for (int k = 0; k < ntap; ++k) sw[k] = take();
+                            for (int k = 0; k < ntap; ++k) {
                                 const uint32_t sa = take();
                                 tc_fence_after();
-                                TLD(13 + j);
-                                mma_slice(acc1, s_ring + sa * F2_SLOT, s_ring + sa * F2_SLOT + TILE16, s_ring + swj * F2_SLOT, 1u);
-                                umma_commit(bar + F2B_EMPTY(swj));
+                                TLD(11 + 2 * k + j);
+                                mma_slice(acc1, s_ring + sa * F2_SLOT, s_ring + sa * F2_SLOT + TILE16, s_ring + sw[k] * F2_SLOT, 1u);
                                 umma_commit(bar + F2B_EMPTY(sa));
+                                umma_commit(bar + F2B_EMPTY(sw[k]));
                             }
+                        }
                     }
                 }
                 umma_commit(bar + F2B_ACC1);
