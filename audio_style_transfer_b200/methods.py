@@ -97,7 +97,7 @@ class GatysNet(object):
                  cnt_channels=128,
                  gatys=False,
                  style_lyr_ids=None,
-                 precision='bf16', seed=0, device=None, optimizer='scipy', random_init=False):
+                 precision='bf16', seed=0, device=None, optimizer='scipy', random_init=False, time_shards=False):
         if optimizer not in ('scipy', 'device'):
             raise ValueError("optimizer must be 'scipy' (the reference's SciPy L-BFGS-B on host buffers) or 'device'")
         self.optimizer = optimizer
@@ -111,6 +111,13 @@ class GatysNet(object):
         self.cont_lyr_ids = cont_lyr_ids
         self.seed = seed
         self.random_init = bool(random_init)
+        # time_shards: ONE clip evaluated by all ranks of the torch.distributed job (one process per GPU, launched with
+        # torchrun): every rank owns a slice of the clip and exchanges halo rows with its neighbours (sharding.py).
+        # The reference is single-device (methods.py:48,143); this is how --batch_size beyond one GPU's reach is run.
+        self.time_shards = bool(time_shards)
+        self.sharded = None
+        if self.time_shards and optimizer != 'scipy':
+            raise ValueError("time_shards runs SciPy's L-BFGS-B on every rank (the device optimiser's vectors are not sharded)")
         self.precision = precision
         self.graph, self.embeds_c, self.embeds_s, self.gatys = self.build(
             batch_size, cont_lyr_ids, stack, nb_channels, cnt_channels, gatys, style_lyr_ids,
@@ -220,14 +227,69 @@ class GatysNet(object):
     def define_loss(self, name, stl_emb, cnt_emb, lambd, gamma, gpu=None):
         """methods.py:113-138: bakes the targets and loss weights; returns the evaluation closure that
         ScipyOptimizerInterface would have built: fun(x64) -> (loss, grad64) and the last loss parts."""
-        self.graph.set_targets(np.asarray(cnt_emb)[None], np.asarray(stl_emb)[None], lambd, gamma)
         last = {}
+        if self.time_shards:
+            return self._define_loss_sharded(stl_emb, cnt_emb, lambd, gamma, last), last
+        self.graph.set_targets(np.asarray(cnt_emb)[None], np.asarray(stl_emb)[None], lambd, gamma)
 
         def fun(x64):
             losses, grad = self.graph.step_host(x64)
             last['losses'] = losses[0]
             return float(losses[0, 0]), grad[0]
         return fun, last
+
+    def _define_loss_sharded(self, stl_emb, cnt_emb, lambd, gamma, last):
+        """define_loss for a clip sharded over the ranks: fun(x64) evaluates this rank's window with halo exchange
+        (HaloShardedStep), all-gathers the owned gradient slices and returns the SAME (loss, gradient) on every rank, so
+        that every rank's SciPy takes the same iterations from the same numbers and no broadcast of x is needed."""
+        import torch
+        import torch.distributed as dist
+        from .sharding import HaloShardedStep
+        from .step import StyleStep
+        if gamma != 0.0:
+            raise ValueError('time_shards: the gamma term is supported by the overlapped-window path only (sharding.TimeShardedStep)')
+        if not (dist.is_available() and dist.is_initialized()):
+            raise RuntimeError('time_shards needs an initialised torch.distributed process group (launch with torchrun)')
+        rank, world = dist.get_rank(), dist.get_world_size()
+        g = self.graph
+
+        def make_ctx(Tw, window):
+            c = StyleStep(Tw, g.cont_ids, g.style_ids, g.gatys, g.nb_channels, g.cnt_channels, precision=g.precision,
+                          device=g.device, window=window, halo_exchange=True)
+            c.set_weights(self.weights)
+            return c
+
+        def exchange(pairs):
+            ops = []
+            for send, recv, peer in pairs:
+                ops.append(dist.P2POp(dist.isend, send, peer))
+                ops.append(dist.P2POp(dist.irecv, recv, peer))
+            for r in dist.batch_isend_irecv(ops):
+                r.wait()
+        if self.sharded is not None:
+            self.sharded.ctx.close()
+        hs = HaloShardedStep(self.batch_size, rank, world, make_ctx, lambda p: dist.all_reduce(p), exchange)
+        self.sharded = hs
+        hs.ctx.set_targets(np.ascontiguousarray(np.asarray(cnt_emb)[None, hs.wb:hs.we]), np.asarray(stl_emb)[None], lambd, 0.0)
+        dev = hs.ctx.dev
+        losses = torch.empty((1, 4), device=dev)
+        grad = torch.empty((1, hs.we - hs.wb), device=dev)
+        sizes = [oe - ob for (_, _, ob, oe) in hs.plan]
+        pad = max(sizes)
+        mine = torch.zeros(pad, device=dev)
+        parts = [torch.empty(pad, device=dev) for _ in range(world)]
+
+        def fun(x64):
+            xw = torch.as_tensor(np.ascontiguousarray(x64[hs.wb:hs.we], dtype=np.float32)[None], device=dev)
+            _, own = hs.step(xw, losses, grad)
+            mine[:own.shape[1]] = own[0]
+            dist.all_gather(parts, mine)
+            hs.ctx.check()
+            full = torch.cat([p[:n] for p, n in zip(parts, sizes)]).double().cpu().numpy()
+            lo = losses[0].double().cpu().numpy()
+            last['losses'] = lo
+            return float(lo[0]), full
+        return fun
 
     def l_bfgs(self, sess, phi_c, phi_s, epochs, lambd, gamma, callback=None):
         """methods.py:140-181: `epochs` fresh L-BFGS-B runs of maxiter=100 from the variable's current value;
@@ -259,7 +321,7 @@ class GatysNet(object):
             self.evaluations += i
             i_ = i
             audio = inv_mu_law_numpy(self.x)[0, self.late:-self.late]
-            if self.savepath:
+            if self.savepath and (self.sharded is None or self.sharded.rank == 0):
                 os.makedirs(self.savepath, exist_ok=True)
                 write_wav(os.path.join(self.savepath, 'ep-{}.wav'.format(ep)), audio / max(np.max(audio), 1e-12), self.sr)
             if i_ < 50:
@@ -307,7 +369,7 @@ class GatysNet(object):
         aud = ld(cont_file)
         st = max(int(start * self.sr - self.late), 0)
         aud = aud[st: st + self.batch_size]
-        if self.savepath:
+        if self.savepath and int(os.environ.get('RANK', '0')) == 0:
             os.makedirs(self.savepath, exist_ok=True)
             write_wav(os.path.join(self.savepath, 'ori.wav'), aud[self.late:-self.late], self.sr)
             write_wav(os.path.join(self.savepath, 'style.wav'), ld(target)[st: st + self.batch_size][self.late:-self.late], self.sr)
@@ -318,7 +380,7 @@ class GatysNet(object):
 
 
 def get_dir(dir, args):
-    return gt_s_path(crt_t_fol(dir), **{k: v for k, v in vars(args).items() if k not in ('seed', 'precision', 'synthetic', 'optimizer', 'random_init')})
+    return gt_s_path(crt_t_fol(dir), **{k: v for k, v in vars(args).items() if k not in ('seed', 'precision', 'synthetic', 'optimizer', 'random_init', 'time_shards')})
 
 
 def get_fpath(fn, args):
@@ -335,9 +397,19 @@ def piece_work(args):
         style = synth.style_audio(args.batch_size, seed=2, chunks=5)
     else:
         content, style = map(lambda name: get_fpath(name, args), [args.cont_fn, args.style_fn])
+    device = None
+    if args.time_shards:                       # one process per GPU (torchrun): rank r drives GPU LOCAL_RANK
+        import torch
+        import torch.distributed as dist
+        device = int(os.environ.get('LOCAL_RANK', '0'))
+        torch.cuda.set_device(device)
+        if not dist.is_initialized():
+            os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+            dist.init_process_group('nccl', device_id=torch.device('cuda', device))
     test = GatysNet(savepath, args.ckpt_path, logdir, figdir, args.stack, args.batch_size, args.sr, args.cont_lyrs,
                     args.channels, args.cnt_channels, args.gatys, args.style_lyrs, precision=args.precision, seed=args.seed,
-                    optimizer=args.optimizer, random_init=args.random_init or args.synthetic)
+                    optimizer=args.optimizer, random_init=args.random_init or args.synthetic, time_shards=args.time_shards,
+                    device=device)
     return test.run(content, content, style, epochs=args.epochs, lambd=args.lambd, gamma=args.gamma, start=args.start)
 
 
@@ -374,6 +446,9 @@ def build_parser():
     parser.add_argument('--optimizer', default='scipy', choices=['scipy', 'device'],
                         help="scipy: SciPy L-BFGS-B on host buffers, as the reference; device: the same algorithm resident on the GPU")
     parser.add_argument('--synthetic', action='store_true', help='ignore the file names, use seeded synthetic audio')
+    parser.add_argument('--time_shards', action='store_true',
+                        help='one clip over all ranks of the job (launch with torchrun, one process per GPU): each rank owns a '
+                             'slice of the clip, halo rows are exchanged between neighbours, Gram partials all-reduced')
     return parser
 
 

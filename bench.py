@@ -331,6 +331,48 @@ def run_timesharded(name, precision, rank, world, local, steps, warmup, mode="ha
             "timing": "CUDA events, L2 flushed between steps, max over ranks; eager launches + NCCL (no graph)"}
 
 
+def run_other_config(name, precision, local, steps, B=None):
+    """A compact record of another BASELINE config on ONE GPU, measured the same way as the headline (CUDA-graph replay,
+    CUDA events, L2 flushed between steps): the default N = 1 run carries configs[0], configs[3]'s per-GPU shape and the
+    methods.py CLI defaults next to configs[1], so that they are driver-run numbers too."""
+    import torch
+    from audio_style_transfer_b200.step import StyleStep
+    dev = torch.device("cuda", local)
+    B = B or (8 if name == "cfg3" else 1)
+    wl = build_workload(name, B)
+    T = wl["T"]
+    st = StyleStep(T, wl["cont"], wl["style"], wl["gatys"], B=B, precision=precision, device=local)
+    st.set_weights(wl["w"])
+    Pc, Ps = gpu_targets(st, torch.as_tensor(wl["content"], device=dev), torch.as_tensor(wl["style_a"], device=dev))
+    st.set_targets(Pc, Ps, wl["lambd"])
+    x = torch.as_tensor(wl["x"], device=dev)
+    losses, grad = torch.empty((B, 4), device=dev), torch.empty((B, T), device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    for _ in range(3):
+        st.step_graph(x, losses, grad)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for a, b in ev:
+        flush.zero_()
+        a.record(); st.step_graph(x, losses, grad); b.record()
+    torch.cuda.synchronize()
+    st.check()
+    ms = sum(a.elapsed_time(b) for a, b in ev) / steps
+    xh = wl["x"].astype(np.float64)
+    for _ in range(2):
+        st.step_host(xh)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        st.step_host(xh)
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / steps
+    rec = {"config": workload_config(name, wl, B, 1, False), "ms_per_step": ms, "steps_per_s": B / (ms * 1e-3),
+           "audio_sec_per_sec": B * T / SR / (ms * 1e-3), "e2e_steps_per_s": B / (e2e_ms * 1e-3),
+           "launches_per_step": st.launches_per_step, "steps": steps,
+           "model_tflops": algorithmic_flops(T, wl["NL"], wl["L"], wl["gatys"], B) / (ms * 1e-3) / 1e12,
+           "finite": bool(torch.isfinite(grad).all() and torch.isfinite(losses).all())}
+    st.close()
+    return rec
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -561,6 +603,14 @@ def run_ours(args):
                        "h2d_bytes_per_step": B * T * 4, "d2h_bytes_per_step": (B * T + 4 * B) * 4,
                        "ms_per_step": e2e_ms / args.steps,
                        "api": "StyleStep.step_host -> ast_step_host (float64 host in/out, graph replay inside)"}
+    if world == 1 and name == "cfg1" and B == 1 and not args.no_other_configs:
+        others = []
+        for wname in ("cfg0", "cfg3", "cli", "cfg2"):
+            try:
+                others.append(run_other_config(wname, args.precision, local, min(args.steps, 30)))
+            except Exception as e:      # noqa: BLE001
+                others.append({"config": {"workload": wname}, "error": repr(e)})
+        line["other_configs"] = others
     if optim:
         line["optimizer_epoch"] = optim
     if roof:
@@ -590,6 +640,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--shard-mode", dest="shard_mode", default="halo", choices=["halo", "overlap"],
                     help="time-sharded clips: halo rows exchanged stack by stack (default) or 2R-overlapped windows without exchange")
+    ap.add_argument("--no-other-configs", dest="no_other_configs", action="store_true",
+                    help="N = 1: skip the compact records of configs[0], configs[3] (8 pairs), the CLI defaults and configs[2] on one GPU")
     ap.add_argument("--no-timesharded", dest="no_timesharded", action="store_true",
                     help="N > 1: skip the time-sharded configs[2] / configs[4] records measured next to the headline")
     args = ap.parse_args()
