@@ -77,6 +77,8 @@ struct ast_ctx {
     const float** d_Fptr;
     float** d_dFptr;
     OursPtrs ours_ptrs;            // the same tables by value for the tensor-core channel-wise head
+    unsigned* p2p_sig;             // [2 sides][2 directions] completion words the neighbour ranks signal (halo_exchange)
+    std::vector<void*> ipc_open;   // neighbours' buffers mapped by ast_p2p_attach (closed in ast_destroy)
     const float** d_Hcptr;
     float lambd;
     // gamma term (stft_reg.cu): frames [reg_f_lo, reg_f_lo + reg_nf) of the clip are evaluated here, the ones
@@ -143,6 +145,7 @@ extern "C" int ast_destroy(ast_ctx* c) {
     if (!c) return AST_OK;
     cudaSetDevice(c->cfg.device);
     if (c->tc) tc_destroy(c->tc);
+    for (void* q : c->ipc_open) cudaIpcCloseMemHandle(q);
     if (c->gexec) cudaGraphExecDestroy(c->gexec);
     if (c->gdev) cudaGraphExecDestroy(c->gdev);
     for (auto& g : c->gphase) if (g) cudaGraphExecDestroy(g);
@@ -184,6 +187,7 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
     c->T = cfg->T; c->B = cfg->B; c->R = cfg->B * cfg->T; c->NL = cfg->n_layers; c->L = cfg->n_style;
     c->n_cont = cfg->n_cont; c->prec = cfg->precision; c->bytes = 0;
     c->generation = ++g_ctx_generation;
+    c->p2p_sig = nullptr;
     c->tc = nullptr; c->hstream = nullptr; c->gexec = nullptr; c->p_x = c->p_out = nullptr;
     c->gdev = nullptr; c->gdev_x = nullptr; c->gdev_losses = c->gdev_grad = nullptr;
     for (auto& g : c->gphase) g = nullptr;
@@ -305,6 +309,9 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
         if (cfg->halo_exchange) {
             if (!c->use_stack_bwd) { ast_destroy(c); return fail(AST_EUNSUPPORTED, "halo_exchange needs the whole-stack kernels (kernel_path auto)"); }
             tc_plan_segments(c->tc, true);
+            DA(c->p2p_sig, 4);
+            CK(cudaMemset(c->p2p_sig, 0, 4 * sizeof(unsigned)));
+            tc_set_peer_geometry(c->tc, c->own_lo, c->own_hi, c->p2p_sig);
         }
     } else if (cfg->halo_exchange) {
         ast_destroy(c); return fail(AST_EUNSUPPORTED, "halo_exchange is a tensor-core tier (AST_PREC_BF16) feature");
@@ -624,6 +631,58 @@ extern "C" int ast_segment_buffer(ast_ctx* c, int32_t backward, int32_t seg, flo
     if (seg == nseg - 1) return fail(AST_EINVAL, "the last forward segment leaves nothing to exchange");
     *d_buf = Hl(c, tc_segment_end(c->tc, seg));
     return AST_OK;
+}
+
+// ---- peer-mapped halos: the neighbour ranks' buffers inside this process (include/ast_b200.h) ----------------------
+static int p2p_ready(ast_ctx* c, int side) {
+    if (!c) return fail(AST_EINVAL, "null argument");
+    if (!c->p2p_sig) return fail(AST_ESTATE, "ast_p2p_*: the context was not created with halo_exchange = 1");
+    if (side < 0 || side > 1) return fail(AST_EINVAL, "side %d: 0 = the rank before this window, 1 = after", side);
+    if (c->B != 1) return fail(AST_EUNSUPPORTED, "peer-mapped halos are built for B = 1");
+    return AST_OK;
+}
+static int p2p_set(ast_ctx* c, int side, const float* H, const float* g, const float* g_alt, unsigned* sig, int64_t peer_wb, int peer_T) {
+    const int64_t off = c->cfg.win_begin - peer_wb;              // neighbour row = in-window t + off
+    if (off < -(int64_t)1 << 30 || off > (int64_t)1 << 30) return fail(AST_EINVAL, "window offsets too far apart");
+    // the rows this rank reads must lie inside the neighbour's window
+    const int lo = c->own_lo, hi = c->own_hi;
+    const int64_t a = side == 0 ? lo - 2 * AST_HALO_ROWS + off : hi + off, b = side == 0 ? lo + off : hi + 2 * AST_HALO_ROWS + off;
+    if (a < 0 || b > peer_T) return fail(AST_EINVAL, "the neighbour's window [%lld, +%d) does not hold the halo rows of side %d", (long long)peer_wb, peer_T, side);
+    tc_set_peer(c->tc, side, H, g, g_alt, sig, peer_T, (int)off);
+    return AST_OK;
+}
+extern "C" int ast_p2p_export(ast_ctx* c, void* h_handles) {
+    int r = p2p_ready(c, 0);
+    if (r != AST_OK) return r;
+    if (!h_handles) return fail(AST_EINVAL, "null argument");
+    cudaIpcMemHandle_t* h = static_cast<cudaIpcMemHandle_t*>(h_handles);
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaIpcGetMemHandle(&h[0], c->H));
+    CK(cudaIpcGetMemHandle(&h[1], c->g));
+    CK(cudaIpcGetMemHandle(&h[2], c->g_alt));
+    CK(cudaIpcGetMemHandle(&h[3], c->p2p_sig));
+    return AST_OK;
+}
+extern "C" int ast_p2p_attach(ast_ctx* c, int32_t side, const void* h_handles, int64_t peer_win_begin, int32_t peer_T) {
+    int r = p2p_ready(c, side);
+    if (r != AST_OK) return r;
+    if (!h_handles) return fail(AST_EINVAL, "null argument");
+    const cudaIpcMemHandle_t* h = static_cast<const cudaIpcMemHandle_t*>(h_handles);
+    CK(cudaSetDevice(c->cfg.device));
+    void* q[4] = {nullptr, nullptr, nullptr, nullptr};
+    for (int i = 0; i < 4; ++i) {
+        cudaError_t e = cudaIpcOpenMemHandle(&q[i], h[i], cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) return fail(AST_ECUDA, "cudaIpcOpenMemHandle failed: %s (is peer access between the two GPUs possible?)", cudaGetErrorString(e));
+        c->ipc_open.push_back(q[i]);
+    }
+    return p2p_set(c, side, (const float*)q[0], (const float*)q[1], (const float*)q[2], (unsigned*)q[3], peer_win_begin, peer_T);
+}
+// Same process (several contexts of one process: tests, one-process multi-GPU with peer access enabled by the caller).
+extern "C" int ast_p2p_attach_local(ast_ctx* c, int32_t side, ast_ctx* peer) {
+    int r = p2p_ready(c, side);
+    if (r != AST_OK) return r;
+    if ((r = p2p_ready(peer, side)) != AST_OK) return r;
+    return p2p_set(c, side, peer->H, peer->g, peer->g_alt, peer->p2p_sig, peer->cfg.win_begin, peer->T);
 }
 
 extern "C" int ast_step_backward(ast_ctx* c, float* d_losses, float* d_grad, void* stream) {

@@ -618,6 +618,15 @@ struct TcState {
                                    // kernels, then err[2], then {epoch, CTAs done} of the forward and of the backward kernel
     int n_sm, coop;                // SM count; cooperative launch supported
     int nseg, seg_lo[4], seg_hi[4], seg_halo[4];   // layer segments of the whole-stack kernels and their halo (tiles per side)
+    // peer-mapped halos of a time shard (tc_set_peer): side 0 = the rank before this window, 1 = after
+    struct {
+        bool on;
+        const float* H[2]; const float* g[2]; const float* g_alt[2]; unsigned* sig[2];
+        int R[2]; int row_off[2];
+        int own_lo, own_hi;            // owned range in window coordinates
+        unsigned* sig_local;           // this rank's signal words [2 sides][2 directions]
+        unsigned step_f, step_b;       // forward / backward evaluations started (all ranks count alike)
+    } peer;
 };
 
 static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
@@ -792,6 +801,45 @@ int tc_segment_end(const TcState* s, int k) { return s->seg_hi[k]; }
 bool tc_stack_ok(const TcState* s) { return s && s->coop && s->NL <= 32 && s->n_sm >= 64; }
 unsigned* tc_stack_err(TcState* s) { return s->flags + (size_t)4 * (s->R / 128); }
 
+void tc_set_peer_geometry(TcState* s, int own_lo, int own_hi, unsigned* sig_local) {
+    s->peer.own_lo = own_lo; s->peer.own_hi = own_hi; s->peer.sig_local = sig_local;
+}
+void tc_set_peer(TcState* s, int side, const float* H, const float* g, const float* g_alt, unsigned* sig, int peer_R, int row_off) {
+    s->peer.on = true;
+    s->peer.H[side] = H; s->peer.g[side] = g; s->peer.g_alt[side] = g_alt; s->peer.sig[side] = sig;
+    s->peer.R[side] = peer_R; s->peer.row_off[side] = row_off;
+}
+// The StackPeer block of segment k.  order = position of the segment in its sweep (forward: k, backward: nseg-1-k); a
+// segment waits for the signal the neighbours' previous segment of the SAME evaluation sent, and (unless it is the last of
+// the sweep) signals them in turn.  src_of(side) = the neighbour's buffer this segment resumes from.
+template <typename SrcOf>
+static StackPeer tc_peer_block(TcState* s, int order, int dir, int halo_in, int halo_out, SrcOf src_of) {
+    StackPeer pr;
+    memset(&pr, 0, sizeof(pr));
+    if (!s->peer.on) return pr;
+    unsigned& step = dir == 0 ? s->peer.step_f : s->peer.step_b;
+    if (order == 0) ++step;
+    const unsigned base = step * 8u;
+    const int lo = s->peer.own_lo, hi = s->peer.own_hi;
+    if (order > 0) {
+        pr.wait_seq = base + (unsigned)order;
+        for (int sd = 0; sd < 2; ++sd) {
+            if (!s->peer.sig[sd]) continue;
+            pr.src[sd] = src_of(sd);
+            pr.row_off[sd] = s->peer.row_off[sd];
+            pr.sig_wait[sd] = s->peer.sig_local + sd * 2 + dir;
+        }
+        pr.t0[0] = lo - halo_out; pr.t1[0] = lo - halo_in;          // rows before the owned range ...
+        pr.t0[1] = hi + halo_in;  pr.t1[1] = hi + halo_out;         // ... and after it
+    }
+    if (order + 1 < s->nseg) {
+        pr.signal_seq = base + (unsigned)order + 1u;
+        for (int sd = 0; sd < 2; ++sd) pr.sig_out[sd] = s->peer.sig[sd] ? s->peer.sig[sd] + (1 - sd) * 2 + dir : nullptr;
+    }
+    return pr;
+}
+#define TC_HALO_ROWS 1024
+
 struct TcLaunch { int tile0, ntiles, grp_t0, grp_t1, wr_t0, wr_t1; };
 // The launches of one segment: whole pairs while a pair fits the SMs, else groups of <= n_sm consecutive tiles of one pair
 // with `halo` tiles per inner side that are computed but not written.
@@ -845,7 +893,12 @@ int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b
         const int nl = tc_plan_launches(s, s->seg_halo[k], ln, TC_MAX_LAUNCHES);
         const bool disjoint = s->T / 128 <= TC_GROUP_CAP(s);       // whole-pair launches: one memset covers them all
         if (disjoint) cudaMemsetAsync(s->flags, 0, 2 * (size_t)(s->R / 128) * sizeof(unsigned), st);
+        // forward: the stream is exact on own +- 1024 after a segment; the 1024 rows beyond come from the neighbours' H[l_begin]
+        const StackPeer pr = tc_peer_block(s, k, 0, TC_HALO_ROWS, 2 * TC_HALO_ROWS, [&](int sd) {
+            return s->peer.H[sd] + (size_t)a.l_begin * s->peer.R[sd] * AST_C; });
         for (int i = 0; i < nl && e == cudaSuccess; ++i) {
+            a.peer = pr;
+            if (i + 1 < nl) a.peer.signal_seq = 0;                 // only the segment's last launch signals
             a.tile0 = ln[i].tile0; a.grp_t0 = ln[i].grp_t0; a.grp_t1 = ln[i].grp_t1; a.wr_t0 = ln[i].wr_t0; a.wr_t1 = ln[i].wr_t1;
             if (!disjoint) cudaMemsetAsync(s->flags + (size_t)2 * ln[i].tile0, 0, (size_t)2 * ln[i].ntiles * sizeof(unsigned), st);
             e = launch_coop(tc_fwd_stack_kernel, dim3(ln[i].ntiles), dim3(F2_THREADS), F2_SMEM, st, a);
@@ -885,7 +938,13 @@ int tc_backward_stack(TcState* s, const uint32_t* hmask, const uint32_t* zmask, 
         const int nl = tc_plan_launches(s, s->seg_halo[k], ln, TC_MAX_LAUNCHES);
         const bool disjoint = s->T / 128 <= TC_GROUP_CAP(s);
         if (disjoint) cudaMemsetAsync(s->flags + 2 * nt, 0, 2 * nt * sizeof(unsigned), st);
+        // backward: the running gradient is exact on the owned rows after a segment; the 1024 rows on either side come from the
+        // neighbours' result of the previous segment (their buffer of the same parity as this rank's g_in)
+        const StackPeer pr = tc_peer_block(s, s->nseg - 1 - k, 1, 0, TC_HALO_ROWS, [&](int sd) {
+            return (k & 1) ? s->peer.g[sd] : s->peer.g_alt[sd]; });
         for (int i = 0; i < nl && e == cudaSuccess; ++i) {
+            a.peer = pr;
+            if (i + 1 < nl) a.peer.signal_seq = 0;
             a.tile0 = ln[i].tile0; a.grp_t0 = ln[i].grp_t0; a.grp_t1 = ln[i].grp_t1; a.wr_t0 = ln[i].wr_t0; a.wr_t1 = ln[i].wr_t1;
             if (!disjoint) cudaMemsetAsync(s->flags + 2 * nt + (size_t)2 * ln[i].tile0, 0, (size_t)2 * ln[i].ntiles * sizeof(unsigned), st);
             e = launch_coop(tc_bwd_stack_kernel, dim3(ln[i].ntiles), dim3(F2_THREADS), B2_SMEM, st, a);

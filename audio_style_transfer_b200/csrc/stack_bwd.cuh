@@ -39,6 +39,7 @@ struct alignas(64) BwdStackArgs {
     int l_top, l_bot;                // boundaries of this launch, l_top >= l_bot
     int grp_t0, grp_t1;              // in-pair time range covered by this launch's tiles (hand-off edges)
     int wr_t0, wr_t1;                // tiles with t0 in this range write the running gradient / the start-conv dots
+    StackPeer peer;                  // peer-mapped halo rows of the running gradient (stack_fwd.cuh)
     unsigned short need[33];         // need[m]: flag value once dz_m (consumed by boundary m) has been published
     signed char df_idx[33];          // per boundary l: dF buffer added there, or -1
     signed char sg_slot[33];         // per boundary l: style slot whose F . Ssym is added there, or -1
@@ -299,6 +300,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
         const bool has_up = t0 > gt0, has_dn = t0 + 128 < gt1;
         const bool wr = t0 >= p.wr_t0 && t0 < p.wr_t1;
         uint32_t acc1_n = 0, acc2_n = 0, io_n = 0, anti_n = 0;
+        const int peer_side = resume ? stack_peer_side(p.peer, t0, ab, p.err) : -1;
         // LL item of (ping-pong pp, tile tl, side sd, K-half j, cc, row slot): lines [4][LL_ROWS], slot fastest (stack_fwd.cuh)
         auto ll_item = [&](int pp, int tl, int sd, int j, int slot, int c) -> uint4* {
             return p.ll + ((((((size_t)pp * p.ntiles + tl) * 2 + sd) * 2 + j) * 4 + c) * 4) * LL_ROWS + slot;
@@ -347,10 +349,14 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
                     tmem_wait_ld();
 #pragma unroll
                     for (int e = 0; e < 16; ++e) v[e] += w[e];
-                } else if (resume && l == LT) {               // ... a resumed launch takes it from global memory
-                    const float4* gin = reinterpret_cast<const float4*>(p.g_in + row * AST_C + colc);
+                } else if (resume && l == LT) {               // ... a resumed launch takes it from global memory (own or neighbour's)
+                    const float* gin = peer_side < 0 ? p.g_in + row * AST_C + colc
+                                                     : p.peer.src[peer_side] + (size_t)(t0 + r + p.peer.row_off[peer_side]) * AST_C + colc;
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) { const float4 t = gin[e]; v[4 * e] = t.x; v[4 * e + 1] = t.y; v[4 * e + 2] = t.z; v[4 * e + 3] = t.w; }
+                    for (int e = 0; e < 4; ++e) {
+                        const float4 t = peer_side < 0 ? *reinterpret_cast<const float4*>(gin + 4 * e) : ld_relaxed_sys_f4(gin + 4 * e);
+                        v[4 * e] = t.x; v[4 * e + 1] = t.y; v[4 * e + 2] = t.z; v[4 * e + 3] = t.w;
+                    }
                 }
                 if (df >= 0) {
                     const uint8_t* dcg = gen + B2_IO + (j * 2 + (cc >> 1)) * TILE16;
@@ -498,7 +504,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_bwd_stack_kernel(const __gri
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence();
-        if (atomicAdd(p.epoch + 1, 1u) == gridDim.x - 1) { p.epoch[1] = 0u; __threadfence(); atomicAdd(p.epoch, 1u); }
+        if (atomicAdd(p.epoch + 1, 1u) == gridDim.x - 1) { p.epoch[1] = 0u; __threadfence(); atomicAdd(p.epoch, 1u); stack_peer_signal(p.peer); }
     }
     if (warp == 1) tmem_dealloc<512>(tmem);
 }

@@ -44,6 +44,37 @@
 // exports and extract copies (tc_plan_groups in kernels_tc.cu).
 #pragma once
 
+struct StackPeer {
+    const float* src[2];             // the neighbour's buffer this segment resumes from (fp32 [rows][128]), or NULL
+    int t0[2], t1[2];                // tiles with t0 in [t0[s], t1[s]) take their rows from side s
+    int row_off[2];                  // neighbour row = in-window t + row_off[s]
+    const unsigned* sig_wait[2];     // this rank's word the neighbour signals; wait until *sig_wait[s] >= wait_seq
+    unsigned* sig_out[2];            // the neighbours' words to signal when this launch (signal_seq != 0) has completed
+    unsigned wait_seq, signal_seq;
+};
+// sys-scope flag and data accesses of the peer-mapped halo path
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ float4 ld_relaxed_sys_f4(const float* p) {
+    float4 v;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+#define FS_PEER_WAIT_NS 30000000000ull            // a neighbour rank may lag by seconds (first step, host jitter): 30 s
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// Which neighbour (if any) serves the rows of the tile at in-window time t0; waits for its signal.
+__device__ __forceinline__ int stack_peer_side(const StackPeer& pr, int t0, volatile unsigned* ab, unsigned* err);
+
 struct alignas(64) FwdStackArgs {
     CUtensorMap tmA_hi, tmA_lo;      // bf16 relu(h) hi / lo [2][B][T][128] ping-pong, box {64,128,1,1}: far taps
     CUtensorMap tmW1, tmW2;          // forward weight operand rows (see tc_weights_fwd_kernel), box {64,128}
@@ -63,6 +94,11 @@ struct alignas(64) FwdStackArgs {
     int l_begin, l_end;              // layers of this launch; l_begin == 0 starts from the waveform (start conv)
     int grp_t0, grp_t1;              // in-pair time range covered by this launch's tiles (hand-off edges)
     int wr_t0, wr_t1;                // tiles with t0 in this range write masks / exports / extract copies
+    // Time shards with peer-mapped halos (ast_p2p_attach): a resumed launch reads the rows of its window that only the
+    // neighbour rank computes exactly straight from the neighbour's buffer over NVLink, after the neighbour's previous
+    // segment has signalled completion into this rank's memory; the last CTA of a segment's last launch signals both
+    // neighbours.  side 0 = the rank that owns the samples before this window's, 1 = after.
+    StackPeer peer;
     unsigned short need[34];         // need[i]: flag value once publish i (relu(h_i), i = 0: start conv) is complete
     signed char f_slot[32];          // style slot that receives bf16(H[l+1]), or -1
     unsigned char export_h[33];      // export_h[i] != 0: H[i] is written to global memory (i = 0: start-conv output)
@@ -209,6 +245,29 @@ __device__ __forceinline__ bool ll_wait_item(const uint4* src, uint4 (&v)[4], ui
         ll_fetch(src, v);
     }
     return true;
+}
+
+__device__ __forceinline__ int stack_peer_side(const StackPeer& pr, int t0, volatile unsigned* ab, unsigned* err) {
+    int side = -1;
+    if (pr.src[0] && t0 >= pr.t0[0] && t0 < pr.t1[0]) side = 0;
+    else if (pr.src[1] && t0 >= pr.t0[1] && t0 < pr.t1[1]) side = 1;
+    if (side < 0) return -1;
+    if (ld_acquire_sys(pr.sig_wait[side]) >= pr.wait_seq) return side;
+    const unsigned long long t_start = global_timer_ns();
+    while (ld_acquire_sys(pr.sig_wait[side]) < pr.wait_seq) {
+        if (stack_aborted(ab)) return side;
+        if (global_timer_ns() - t_start > FS_PEER_WAIT_NS) { stack_abort(ab, err, 4u); return side; }
+        __nanosleep(200);
+    }
+    return side;
+}
+// the last CTA of a launch that closes a segment tells both neighbours that this rank's rows are in place
+__device__ __forceinline__ void stack_peer_signal(const StackPeer& pr) {
+    if (!pr.signal_seq) return;
+    __threadfence_system();
+#pragma unroll
+    for (int sd = 0; sd < 2; ++sd)
+        if (pr.sig_out[sd]) st_release_sys(pr.sig_out[sd], pr.signal_seq);
 }
 
 __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __grid_constant__ FwdStackArgs p) {
@@ -553,16 +612,24 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
         };
 
         if (LB > 0) {
-            // ---- resume: h_{l_begin} of this row from the fp32 stream in global memory ----
-            const float* hrow = p.H + ((size_t)LB * p.R + row) * AST_C;
+            // ---- resume: h_{l_begin} of this row from the fp32 stream in global memory -- this rank's own, or, for the rows
+            // of a time shard's window that only the neighbour computes exactly, the neighbour's over NVLink ----
+            const int side = stack_peer_side(p.peer, t0, ab, p.err);
+            const float* hrow = side < 0 ? p.H + ((size_t)LB * p.R + row) * AST_C
+                                         : p.peer.src[side] + (size_t)(t0 + r + p.peer.row_off[side]) * AST_C;
+            float4 hv[2][4];                            // all eight loads in flight at once: over NVLink a round trip is microseconds
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float* q4 = hrow + j * 64 + cc * 16 + 4 * e;
+                    hv[j][e] = side < 0 ? *reinterpret_cast<const float4*>(q4) : ld_relaxed_sys_f4(q4);
+                }
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
                 float v[16];
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const float4 t4 = *reinterpret_cast<const float4*>(hrow + j * 64 + cc * 16 + 4 * e);
-                    v[4 * e] = t4.x; v[4 * e + 1] = t4.y; v[4 * e + 2] = t4.z; v[4 * e + 3] = t4.w;
-                }
+                for (int e = 0; e < 4; ++e) { v[4 * e] = hv[j][e].x; v[4 * e + 1] = hv[j][e].y; v[4 * e + 2] = hv[j][e].z; v[4 * e + 3] = hv[j][e].w; }
                 emit(LB, j, v);
             }
             tmem_wait_st();
@@ -664,7 +731,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
         TL(1);
         // the last CTA of this launch opens the next epoch (tags of this launch can then never validate again)
         __threadfence();
-        if (atomicAdd(p.epoch + 1, 1u) == gridDim.x - 1) { p.epoch[1] = 0u; __threadfence(); atomicAdd(p.epoch, 1u); }
+        if (atomicAdd(p.epoch + 1, 1u) == gridDim.x - 1) { p.epoch[1] = 0u; __threadfence(); atomicAdd(p.epoch, 1u); stack_peer_signal(p.peer); }
     }
     if (warp == 1) tmem_dealloc<512>(tmem);
 }

@@ -30,6 +30,9 @@ void tc_layer_fwd(TcState* s, int l, const float* bd, const float* br, uint32_t*
 bool tc_stack_ok(const TcState* s);
 unsigned* tc_stack_err(TcState* s);
 void tc_plan_segments(TcState* s, bool per_stack);
+// peer-mapped halos (time shards whose neighbours' buffers are mapped into this process: ast_p2p_attach)
+void tc_set_peer_geometry(TcState* s, int own_lo, int own_hi, unsigned* sig_local);
+void tc_set_peer(TcState* s, int side, const float* H, const float* g, const float* g_alt, unsigned* sig, int peer_R, int row_off);
 int tc_segments(const TcState* s);
 int tc_segment_end(const TcState* s, int k);
 int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b0, const float* bd, const float* br,

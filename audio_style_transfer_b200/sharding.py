@@ -107,9 +107,13 @@ class HaloShardedStep:
     the neighbour's exact rows of the fp32 residual stream, after each backward stack the HALO rows next to its owned
     range with the neighbour's running gradient.  Per step and interior side: 2 + 2 messages of HALO x 128 fp32
     (512 KB), plus the one all-reduce of the raw Gram partials.  `exchange(pairs)` moves rows between ranks:
-    pairs = [(send_tensor, recv_tensor, peer_rank), ...]; on NCCL it is one batch_isend_irecv, tests inject copies."""
+    pairs = [(send_tensor, recv_tensor, peer_rank), ...]; on NCCL it is one batch_isend_irecv, tests inject copies.
 
-    def __init__(self, T: int, rank: int, world: int, make_ctx: Callable, all_reduce: Callable, exchange: Callable):
+    attach_p2p() replaces those messages by peer-mapped memory: every rank maps its neighbours' buffers once (CUDA IPC) and
+    the stack kernels read the halo rows over NVLink themselves, gated by completion words the neighbours' kernels write
+    (include/ast_b200.h: ast_p2p_*).  A step is then forward, all-reduce, backward: no host-side exchange at all."""
+
+    def __init__(self, T: int, rank: int, world: int, make_ctx: Callable, all_reduce: Callable, exchange: Callable = None):
         self.T, self.rank, self.world = T, rank, world
         self.plan = plan_windows_exchange(T, world)
         self.wb, self.we, self.ob, self.oe = self.plan[rank]
@@ -118,6 +122,17 @@ class HaloShardedStep:
         self.nseg = self.ctx.segments
         self.up = rank - 1 if rank > 0 else None             # neighbour that owns the samples before mine
         self.dn = rank + 1 if rank + 1 < world else None
+        self.p2p = False
+
+    def attach_p2p(self, all_gather_object: Callable):
+        """all_gather_object(obj) -> [obj of rank 0, obj of rank 1, ...] (torch.distributed.all_gather_object).  Every rank
+        must call this before any rank starts a step, and no rank may close its context while a neighbour still steps."""
+        infos = all_gather_object((self.ctx.p2p_export(), self.wb, self.we - self.wb))
+        for side, peer in ((0, self.up), (1, self.dn)):
+            if peer is not None:
+                handles, wb, Tw = infos[peer]
+                self.ctx.p2p_attach(side, handles, wb, Tw)
+        self.p2p = True
 
     def window(self, full):
         return full[:, self.wb:self.we]
@@ -136,6 +151,11 @@ class HaloShardedStep:
     def step(self, x_window, losses, grad):
         """Returns (losses [B,4] -- identical on every rank, grad of the OWNED samples [B, own_e-own_b])."""
         c, H, ob, oe = self.ctx, HALO, self.ob, self.oe
+        if self.p2p:                                  # the kernels fetch the halo rows themselves
+            c.forward_partial(x_window)
+            self.all_reduce(c.partials())
+            c.backward(losses, grad)
+            return losses, grad[:, ob - self.wb:oe - self.wb]
         for k in range(self.nseg):
             c.forward_seg(x_window, k)
             if k + 1 < self.nseg:

@@ -216,6 +216,19 @@ class StyleStep:
         _lib.check(self.lib.ast_segment_buffer(self._h, int(bool(backward)), int(seg), C.byref(p)), self.lib)
         return torch.as_tensor(_DevMem(p.value, self.B * self.T * 128), device=self.dev).view(self.B, self.T, 128)
 
+    # -- peer-mapped halos (include/ast_b200.h: ast_p2p_*) ---------------------------------------------------------
+    def p2p_export(self) -> bytes:
+        buf = C.create_string_buffer(256)
+        _lib.check(self.lib.ast_p2p_export(self._h, buf), self.lib)
+        return buf.raw
+
+    def p2p_attach(self, side: int, handles: bytes, peer_win_begin: int, peer_T: int):
+        with torch.cuda.device(self.dev):
+            _lib.check(self.lib.ast_p2p_attach(self._h, int(side), C.create_string_buffer(handles, 256), int(peer_win_begin), int(peer_T)), self.lib)
+
+    def p2p_attach_local(self, side: int, peer: "StyleStep"):
+        _lib.check(self.lib.ast_p2p_attach_local(self._h, int(side), peer._h), self.lib)
+
     def extract(self, layer: int) -> torch.Tensor:
         """cfg.extracts[layer] of the last forward (model.py:116); layer -1 = start-conv output."""
         out = torch.empty((self.B, self.T, 128), dtype=torch.float32, device=self.dev)

@@ -260,11 +260,19 @@ def run_timesharded(name, precision, rank, world, local, steps, warmup, mode="ha
 
     def make_ctx(Tw, window):
         c = StyleStep(Tw, wl["cont"], wl["style"], wl["gatys"], precision=precision, device=local, window=window,
-                      halo_exchange=(mode == "halo"))
+                      halo_exchange=(mode in ("halo", "p2p")))
         c.set_weights(wl["w"])
         return c
-    if mode == "halo":
+    if mode in ("halo", "p2p"):
         sh = HaloShardedStep(T, rank, world, make_ctx, lambda p: dist.all_reduce(p), nccl_exchange)
+        if mode == "p2p":                      # halo rows read by the resuming kernels from the neighbours' mapped buffers
+
+            def gather(obj):
+                out = [None] * world
+                dist.all_gather_object(out, obj)
+                return out
+            sh.attach_p2p(gather)
+            barrier()
     else:
         sh = TimeShardedStep(T, NL, rank, world, make_ctx, lambda p: dist.all_reduce(p))
     st = sh.ctx
@@ -272,7 +280,7 @@ def run_timesharded(name, precision, rank, world, local, steps, warmup, mode="ha
     x = sh.window(x_full).contiguous()
     losses = torch.empty((1, 4), device=dev)
     grad = torch.empty((1, st.T), device=dev)
-    if mode == "halo":
+    if mode in ("halo", "p2p"):
         one_step = lambda: sh.step(x, losses, grad)
     else:
         def one_step():
@@ -312,17 +320,21 @@ def run_timesharded(name, precision, rank, world, local, steps, warmup, mode="ha
     ms, ar_ms, ex_ms, win_max = [float(v) for v in t]
     launches, nseg = st.launches_per_step, st.segments
     st.check()
+    barrier()                                  # no rank unmaps its buffers while a neighbour may still read them
     st.close()
     if rank != 0:
         return None
     flops = algorithmic_flops(T, NL, wl["L"], wl["gatys"])
-    return {"workload": name, "desc": wl["desc"], "mode": "halo exchange per 10-layer stack (HaloShardedStep)" if mode == "halo"
-            else "2R-overlapped windows, no exchange (TimeShardedStep)",
+    modes = {"halo": "halo exchange per 10-layer stack: NCCL send/recv between the stack kernels (HaloShardedStep)",
+             "p2p": "halo exchange per 10-layer stack INSIDE the stack kernels: peer-mapped neighbour buffers read over NVLink, "
+                    "completion words written by the neighbour's kernel (HaloShardedStep.attach_p2p)",
+             "overlap": "2R-overlapped windows, no exchange (TimeShardedStep)"}
+    return {"workload": name, "desc": wl["desc"], "mode": modes[mode],
             "T": T, "n_gpus": world, "ms_per_step": ms, "steps_per_s": 1e3 / ms, "audio_sec_per_sec": T / SR * 1e3 / ms,
             "n1_ms_per_step": n1_ms, "speedup_vs_own_n1": n1_ms / ms, "efficiency_vs_own_n1": n1_ms / ms / world,
             "allreduce_us": ar_ms * 1e3, "allreduce_bytes": int(parts_buf.numel()) * 4,
             "halo_exchange_us": ex_ms * 1e3 if mode == "halo" else None,
-            "halo_bytes_per_message": HALO * 128 * 4 if mode == "halo" else 0,
+            "halo_bytes_per_message": HALO * 128 * 4 if mode in ("halo", "p2p") else 0,
             "collectives_per_step": (1 + 2 * (nseg - 1)) if mode == "halo" else 1,
             "window_rows_max": int(win_max), "owned_rows": T // world,
             "redundant_rows_frac": (win_max - T / world) / (T / world),
@@ -638,8 +650,9 @@ def main():
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--pairs", type=int, default=0, help="independent pairs per GPU (B); default 1, cfg3: 8")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--shard-mode", dest="shard_mode", default="halo", choices=["halo", "overlap"],
-                    help="time-sharded clips: halo rows exchanged stack by stack (default) or 2R-overlapped windows without exchange")
+    ap.add_argument("--shard-mode", dest="shard_mode", default="p2p", choices=["p2p", "halo", "overlap"],
+                    help="time-sharded clips: halo rows read from peer-mapped neighbour buffers inside the stack kernels (default), "
+                         "exchanged by NCCL send/recv between the stack kernels, or 2R-overlapped windows without exchange")
     ap.add_argument("--no-other-configs", dest="no_other_configs", action="store_true",
                     help="N = 1: skip the compact records of configs[0], configs[3] (8 pairs), the CLI defaults and configs[2] on one GPU")
     ap.add_argument("--no-timesharded", dest="no_timesharded", action="store_true",

@@ -156,6 +156,22 @@ int  ast_step_forward_seg(ast_ctx* ctx, const float* d_x, int32_t seg, void* str
 int  ast_step_backward_seg(ast_ctx* ctx, int32_t seg, float* d_losses, float* d_grad, void* stream);
 int  ast_segment_buffer(ast_ctx* ctx, int32_t backward, int32_t seg, float** d_buf);
 
+/* Peer-mapped halos: instead of moving the halo rows between two segments (ast_segment_buffer + send / receive), a rank
+ * maps its neighbours' buffers into its own address space once, and the stack kernels do the exchange themselves: the
+ * kernel that resumes a segment reads the neighbour's rows over NVLink (ld.relaxed.sys on the mapped pointer) after the
+ * neighbour's previous segment has signalled completion into this rank's memory (st.release.sys from the last CTA of
+ * that kernel / ld.acquire.sys polls, bounded: 30 s).  With every interior side attached, ast_step_forward /
+ * ast_step_backward (or the _seg calls without any copy between them) evaluate the shard; the all-reduce of
+ * ast_partials stays the caller's.  All ranks must start the same evaluations in the same order.
+ *   ast_p2p_export : AST_P2P_HANDLE_BYTES bytes (four cudaIpcMemHandle_t) to hand to the neighbour processes;
+ *   ast_p2p_attach : side 0 = the rank that owns the samples before this window, 1 = after; peer_win_begin / peer_T as
+ *                    in the neighbour's ast_config;  ast_p2p_attach_local: the neighbour is a context of this process.
+ * No reference counterpart (single device, methods.py:48-54,143).  B = 1 only. */
+#define AST_P2P_HANDLE_BYTES 256
+int  ast_p2p_export(ast_ctx* ctx, void* h_handles);
+int  ast_p2p_attach(ast_ctx* ctx, int32_t side, const void* h_handles, int64_t peer_win_begin, int32_t peer_T);
+int  ast_p2p_attach_local(ast_ctx* ctx, int32_t side, ast_ctx* peer);
+
 /* cfg.extracts[layer] of the last forward (model.py:116), [B,T,128] fp32 -> d_out.  Debug/parity.
  * After ast_embeds every layer is available.  After ast_step* in the tensor-core tier only the layers a head reads
  * are: the whole-stack kernels keep the residual stream on chip (TMEM) and write the content extracts (and, for the

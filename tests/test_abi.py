@@ -21,7 +21,7 @@ def lib():
 def header_symbols():
     text = (ROOT / "include" / "ast_b200.h").read_text()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(ast_[a-z_]+)\s*\(", text)))
+    return sorted(set(re.findall(r"\b(ast_[a-z0-9_]+)\s*\(", text)))
 
 
 def test_header_and_binding_agree():

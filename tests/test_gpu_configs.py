@@ -89,7 +89,7 @@ def run_windows(case, Pc, Ps, plan, x):
     return steps, np.array(los), g.cpu().numpy()
 
 
-def run_halo_windows(case, Pc, Ps, P, x, B=1):
+def run_halo_windows(case, Pc, Ps, P, x, B=1, p2p=False):
     """HaloShardedStep for P "ranks" that are contexts on ONE GPU, driven in lockstep; the exchange is a device copy
     between the contexts' segment buffers and the all-reduce a sum of their partial buffers.  Returns (losses, gradient
     of the whole clip, last extract of the whole clip)."""
@@ -106,6 +106,12 @@ def run_halo_windows(case, Pc, Ps, P, x, B=1):
         hs.ctx.set_targets(Pc[None, hs.wb:hs.we], Ps[None], case["lambd"])
         return hs
     shards = [make(r) for r in range(P)]
+    if p2p:                                            # peer-mapped halos: the neighbours are contexts of this process
+        for r, h in enumerate(shards):
+            if r > 0:
+                h.ctx.p2p_attach_local(0, shards[r - 1].ctx)
+            if r + 1 < P:
+                h.ctx.p2p_attach_local(1, shards[r + 1].ctx)
     nseg = shards[0].nseg
     assert nseg == 3 and all(h.ctx.uses_stack_kernels for h in shards)
     xw = [torch.as_tensor(x[None, h.wb:h.we], dtype=torch.float32, device="cuda").contiguous() for h in shards]
@@ -121,7 +127,9 @@ def run_halo_windows(case, Pc, Ps, P, x, B=1):
     for k in range(nseg):
         for h, xx in zip(shards, xw):
             h.ctx.forward_seg(xx, k)
-        if k + 1 < nseg:
+        # (every context's segment k is enqueued before any segment k + 1: a kernel that resumes from a neighbour's rows
+        # finds the neighbour's completion word already written -- ranks that WAIT on one another must not share a GPU)
+        if k + 1 < nseg and not p2p:
             for h in shards:
                 ob, oe = h.ob, h.oe
                 h._swap(h.ctx.segment_buffer(False, k), (ob + H, ob + 2 * H), (ob - 2 * H, ob - H), (oe - 2 * H, oe - H), (oe + H, oe + 2 * H))
@@ -133,7 +141,7 @@ def run_halo_windows(case, Pc, Ps, P, x, B=1):
     for k in range(nseg - 1, -1, -1):
         for h, lo, g in zip(shards, los, grads):
             h.ctx.backward_seg(k, lo, g)
-        if k > 0:
+        if k > 0 and not p2p:
             for h in shards:
                 ob, oe = h.ob, h.oe
                 h._swap(h.ctx.segment_buffer(True, k), (ob, ob + H), (ob - H, ob), (oe - H, oe), (oe, oe + H))
@@ -241,6 +249,12 @@ def test_cfg2_clip_unsharded_and_eight_windows_match_oracle(golden_dir):
     assert torch.equal(ex_h, ex_f)                     # the seam: every shard's owned rows of the last extract, bit for bit
     print(f"8 halo-exchange shards vs unsharded: gradient rel-L2 {rel(g_h, g_f):.2e}")
     assert rel(g_h, g_f) <= 5e-3
+    # ... and with the halo rows read by the resuming kernels from the neighbours' buffers (ast_p2p_attach_local), twice:
+    # the completion words carry the evaluation number
+    for rep_ in range(2):
+        lo_p, g_p, ex_p = run_halo_windows(case, Pc, Ps, 8, case["x"], p2p=True)
+        assert torch.equal(ex_p, ex_f)
+        assert np.array_equal(g_p, g_h) and np.array_equal(lo_p, lo_h)      # the same rows by another route: same bits
 
 
 def test_cfg4_geometry_two_windows_equal_unsharded():
