@@ -21,6 +21,7 @@ SO_EXP = PKG / "libast_b200_exp.so"      # the same sources with -DAST_EXPERIMEN
 
 AST_PREC_FP32 = 0
 AST_PREC_BF16 = 1
+AST_PREC_TC3 = 2
 AST_MAX_IDS = 32
 AST_HALO_ROWS = 1024
 ERRORS = {-1: "AST_EINVAL", -2: "AST_ECUDA", -3: "AST_EUNSUPPORTED", -4: "AST_ESTATE"}

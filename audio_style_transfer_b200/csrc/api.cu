@@ -77,6 +77,7 @@ struct ast_ctx {
     const float** d_Fptr;
     float** d_dFptr;
     OursPtrs ours_ptrs;            // the same tables by value for the tensor-core channel-wise head
+    bool split;                    // AST_PREC_TC3: convs on tcgen05 with hi / lo operands both ways, heads in fp32 on CUDA cores
     unsigned* p2p_sig;             // [2 sides][2 directions] completion words the neighbour ranks signal (halo_exchange)
     std::vector<void*> ipc_open;   // neighbours' buffers mapped by ast_p2p_attach (closed in ast_destroy)
     const float** d_Hcptr;
@@ -169,7 +170,8 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
     if (cfg->n_style < 1 || cfg->n_style > AST_MAX_IDS) return fail(AST_EINVAL, "n_style=%d outside 1..%d", cfg->n_style, AST_MAX_IDS);
     if (cfg->nb_channels < 1 || cfg->nb_channels > 128) return fail(AST_EINVAL, "nb_channels outside 1..128");
     if (cfg->cnt_channels < 1 || cfg->cnt_channels > 128) return fail(AST_EINVAL, "cnt_channels outside 1..128");
-    if (cfg->precision != AST_PREC_FP32 && cfg->precision != AST_PREC_BF16) return fail(AST_EINVAL, "unknown precision %d", cfg->precision);
+    if (cfg->precision != AST_PREC_FP32 && cfg->precision != AST_PREC_BF16 && cfg->precision != AST_PREC_TC3)
+        return fail(AST_EINVAL, "unknown precision %d", cfg->precision);
     if (cfg->kernel_path < AST_PATH_AUTO || cfg->kernel_path > AST_PATH_PER_LAYER_BWD) return fail(AST_EINVAL, "unknown kernel_path %d", cfg->kernel_path);
 
     int ndev = 0;
@@ -263,7 +265,7 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
     DA(c->hmask, (size_t)(c->NL + 1) * c->R * AST_MW);
     DA(c->zmask, (size_t)c->NL * c->R * AST_MW);
     DA(c->g, RC);
-    if (c->prec == AST_PREC_BF16) { DA(c->g_alt, RC); } else c->g_alt = nullptr;   // backward segments ping-pong between g and g_alt
+    if (c->prec != AST_PREC_FP32) { DA(c->g_alt, RC); } else c->g_alt = nullptr;   // backward segments ping-pong between g and g_alt
     if (c->prec == AST_PREC_FP32) { DA(c->dz[0], RC); DA(c->dz[1], RC); } else { c->dz[0] = c->dz[1] = nullptr; }
     DA(c->dF, (size_t)c->n_head * RC);
     DA(c->scratch3R, (size_t)3 * c->R);
@@ -298,14 +300,17 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
     for (auto& e : c->ev) if (cudaEventCreate(&e) != cudaSuccess) { ast_destroy(c); return fail(AST_ECUDA, "event create failed"); }
     if (setup_f32_kernels() != 0) { ast_destroy(c); return fail(AST_ECUDA, "cudaFuncSetAttribute failed (is the GPU sm_100?)"); }
     c->fuse_dots = !exp_switch("AST_B200_NO_DOTS"); c->fuse_heads = !exp_switch("AST_B200_NO_FOLD");
-    if (c->prec == AST_PREC_BF16) {
+    c->split = c->prec == AST_PREC_TC3;
+    if (c->prec != AST_PREC_FP32) {
         const char* why = nullptr;
-        c->tc = tc_create(c->T, c->B, c->NL, c->H, c->g, c->dF, c->n_head, cfg->gatys ? c->L : 0, c->gram_part,
-                          (int64_t)c->B * c->nmat * c->gram_nchunk, &c->bytes, &why);
+        // accurate tier: no bf16 extract copies (its heads read the fp32 extracts), hi / lo backward operands
+        c->tc = tc_create(c->T, c->B, c->NL, c->H, c->g, c->dF, c->n_head, (cfg->gatys && !c->split) ? c->L : 0, c->gram_part,
+                          (int64_t)c->B * c->nmat * c->gram_nchunk, c->split, &c->bytes, &why);
         if (!c->tc) { ast_destroy(c); return fail(AST_ECUDA, "tensor-core path setup failed: %s", why ? why : "?"); }
         // cfg->kernel_path: AST_PATH_PER_LAYER = one kernel per layer both ways, AST_PATH_PER_LAYER_BWD = whole-stack forward only
         c->use_stack = tc_stack_ok(c->tc) && cfg->kernel_path != AST_PATH_PER_LAYER;
         c->use_stack_bwd = c->use_stack && cfg->kernel_path != AST_PATH_PER_LAYER_BWD;
+        if (c->split && !c->use_stack_bwd) { ast_destroy(c); return fail(AST_EUNSUPPORTED, "AST_PREC_TC3 runs on the whole-stack kernels only (kernel_path auto)"); }
         if (cfg->halo_exchange) {
             if (!c->use_stack_bwd) { ast_destroy(c); return fail(AST_EUNSUPPORTED, "halo_exchange needs the whole-stack kernels (kernel_path auto)"); }
             tc_plan_segments(c->tc, true);
@@ -420,7 +425,7 @@ static int run_encoder(ast_ctx* c, const float* d_x, cudaStream_t s, bool keep_a
         unsigned char keep[33];
         for (int i = 0; i <= c->NL; ++i) keep[i] = keep_all ? 1 : 0;
         for (int i = 0; i < c->n_cont; ++i) keep[c->cont_layer[i] + 1] = 1;
-        if (!c->cfg.gatys)                      // channel-wise Gram and its gradient read the fp32 extracts
+        if (!c->cfg.gatys || c->split)          // channel-wise Gram and its gradient (and every head of the accurate tier) read the fp32 extracts
             for (int i = 0; i < c->L; ++i) keep[c->style_layer[i] + 1] = 1;
         memcpy(c->h_kept, keep, sizeof(keep));
         if (tc_forward_stack(c->tc, d_x, c->W0, c->b0, c->bd, c->br, c->H, c->zmask, c->hmask, c->f_slot, keep, seg, s) != 0)
@@ -450,7 +455,7 @@ static int run_encoder(ast_ctx* c, const float* d_x, cudaStream_t s, bool keep_a
 // Gatys split-K chunks and the content partials itself and its last CTA writes the losses (3 launches fewer).
 static inline bool fold_gram_reduce(const ast_ctx* c, bool fused) { return fused && c->cfg.gatys && c->gram_nchunk < 32; }
 static void run_gram(ast_ctx* c, cudaStream_t s, bool fused = false) {
-    if (c->cfg.gatys && c->tc)
+    if (c->cfg.gatys && c->tc && !c->split)
         tc_gram(c->tc, c->L, c->gram_nchunk, c->gram_chunk_rows / 128, c->own_lo / 128, c->own_hi / 128, s);
     else if (c->cfg.gatys)
         launch_gram_gatys(c->d_Fptr, c->L, c->T, c->B, c->own_lo, c->own_hi, c->gram_part, c->gram_nchunk, c->gram_chunk_rows, s);
@@ -507,7 +512,7 @@ static HeadArgs head_args(ast_ctx* c, bool with_targets, float* losses, bool fus
     const double Ns = (double)c->nmat_used * c->msize;
     const double Nc = (double)c->total_T * c->n_cont * c->cfg.cnt_channels;
     h.G = c->partials; h.Ps = c->Ps; h.Gn = c->Gn; h.Ssym = with_targets ? c->Ssym : nullptr;
-    h.Ssym_bf16 = (with_targets && c->cfg.gatys && c->tc) ? tc_ssym_bf16(c->tc) : nullptr;
+    h.Ssym_bf16 = (with_targets && c->cfg.gatys && c->tc && !c->split) ? tc_ssym_bf16(c->tc) : nullptr;
     h.ls_part = c->ls_part; h.sse = c->partials + (size_t)c->B * c->nmat * c->msize; h.losses = losses;
     h.nmat = c->nmat; h.nmat_used = with_targets ? c->nmat_used : 0; h.n = c->n_side; h.B = c->B;
     if (fused) {
@@ -540,7 +545,7 @@ static int step_backward_impl(ast_ctx* c, float* d_losses, float* d_grad, void* 
     bool is_cont[30];
     for (int l = 0; l < 30; ++l) is_cont[l] = false;
     for (int i = 0; i < c->n_cont; ++i) is_cont[c->cont_layer[i]] = true;
-    const bool fuse_sg = c->cfg.gatys && c->tc;
+    const bool fuse_sg = c->cfg.gatys && c->tc && !c->split;
     if (!do_top) { /* head gradients were formed with the top segment */ }
     else if (fuse_sg) {
         int hos[AST_MAX_IDS];

@@ -324,6 +324,7 @@ __global__ void __launch_bounds__(FWD_THREADS, 1) tc_fwd_kernel(const __grid_con
 
 #include "stack_fwd.cuh"
 #include "stack_bwd.cuh"
+#include "stack_bwd_split.cuh"
 #ifdef AST_EXPERIMENTS
 void tc_set_tl_layer(int l) { cudaMemcpyToSymbol(g_tl_layer, &l, sizeof(l)); }
 #endif
@@ -599,6 +600,11 @@ __global__ void tc_weights_bwd_kernel(const float* __restrict__ W, __nv_bfloat16
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = __float2bfloat16_rn(W[i]);
 }
+// lo part of the 2-term split of the backward operands (accurate tier): bf16(W - float(bf16(W)))
+__global__ void tc_weights_bwd_lo_kernel(const float* __restrict__ W, __nv_bfloat16* __restrict__ out, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = __float2bfloat16_rn(W[i] - __bfloat162float(__float2bfloat16_rn(W[i])));
+}
 
 // =============================================================================================
 // host side
@@ -607,6 +613,11 @@ struct TcState {
     int T, B, R, NL;
     __nv_bfloat16 *a_hi, *a_lo, *dz;           // [2][R][128] each (ping-pong)
     __nv_bfloat16 *w1f, *w2f, *w1b, *w2b;
+    // accurate tier (AST_PREC_TC3): lo parts of the backward operands, the head gradients' base pointer
+    bool split;
+    __nv_bfloat16 *dz_lo, *w1b_lo, *w2b_lo;
+    CUtensorMap tm_dz_lo, tm_w1b_lo, tm_w2b_lo;
+    const float* dF;
     __nv_bfloat16 *F, *ssym;                   // Gatys head: bf16 extracts [n_fslots][R][128], bf16 Ssym [B*n_fslots][128][128]
     int n_fslots;
     CUtensorMap tm_F, tm_ssym, tm_gpart, tm_dF_st;
@@ -664,7 +675,7 @@ static bool make_rows_map(CUtensorMap* m, void* ptr, bool fp32, size_t rows, int
 }
 
 TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_head, int n_fslots,
-                   float* gram_part, int64_t gram_part_mats, int64_t* bytes, const char** why) {
+                   float* gram_part, int64_t gram_part_mats, bool split, int64_t* bytes, const char** why) {
     if (!g_encode) {
         void* fn = nullptr;
         cudaDriverEntryPointQueryResult qres;
@@ -677,7 +688,7 @@ TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_he
     }
     TcState* s = new TcState();
     memset(s, 0, sizeof(*s));
-    s->T = T; s->B = B; s->R = B * T; s->NL = NL;
+    s->T = T; s->B = B; s->R = B * T; s->NL = NL; s->split = split; s->dF = dF;
     const size_t act = (size_t)2 * s->R * AST_C * sizeof(__nv_bfloat16);
     const size_t mat = (size_t)AST_C * AST_C * sizeof(__nv_bfloat16);
     bool ok = cudaMalloc(&s->a_hi, act) == cudaSuccess && cudaMalloc(&s->a_lo, act) == cudaSuccess &&
@@ -689,7 +700,7 @@ TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_he
     cudaMemset(s->flags, 0, ((size_t)4 * (s->R / 128) + 6) * sizeof(unsigned));
     {   // LL lines: [2 ping-pong][tiles][2 sides][2 K-halves][4 cc]([2 parts])[4][32 rows] x 16 B; tag 0 never validates
         const size_t nt_ = (size_t)(s->R / 128);
-        const size_t lf = nt_ * 2 * 2 * 2 * LL_ROWS * 8 * 4 * sizeof(uint4), lb = lf / 2;
+        const size_t lf = nt_ * 2 * 2 * 2 * LL_ROWS * 8 * 4 * sizeof(uint4), lb = split ? lf : lf / 2;   // split: hi and lo lines
         if (cudaMalloc(&s->ll_f, lf) != cudaSuccess || cudaMalloc(&s->ll_b, lb) != cudaSuccess) { *why = "cudaMalloc failed"; tc_destroy(s); return nullptr; }
         cudaMemset(s->ll_f, 0, lf); cudaMemset(s->ll_b, 0, lb);
         *bytes += (int64_t)(lf + lb);
@@ -709,6 +720,14 @@ TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_he
          make_act_map(&s->tm_g, g, true, T, B, 1, 128) && make_act_map(&s->tm_dF, dF, true, T, B, n_head > 0 ? n_head : 1, 128) &&
          make_w_map(&s->tm_w1f, s->w1f, (size_t)NL * 3 * 2 * AST_C) && make_w_map(&s->tm_w2f, s->w2f, (size_t)NL * 2 * AST_C) &&
          make_w_map(&s->tm_w1b, s->w1b, (size_t)NL * 3 * AST_C) && make_w_map(&s->tm_w2b, s->w2b, (size_t)NL * AST_C);
+    if (ok && split) {
+        if (cudaMalloc(&s->dz_lo, act) != cudaSuccess || cudaMalloc(&s->w1b_lo, mat * NL * 3) != cudaSuccess ||
+            cudaMalloc(&s->w2b_lo, mat * NL) != cudaSuccess) { *why = "cudaMalloc failed"; tc_destroy(s); return nullptr; }
+        cudaMemset(s->dz_lo, 0, act);
+        *bytes += (int64_t)(act + mat * NL * 4);
+        ok = make_act_map(&s->tm_dz_lo, s->dz_lo, false, T, B, 2, 128) && make_w_map(&s->tm_w1b_lo, s->w1b_lo, (size_t)NL * 3 * AST_C) &&
+             make_w_map(&s->tm_w2b_lo, s->w2b_lo, (size_t)NL * AST_C);
+    }
     s->n_fslots = n_fslots;
     if (ok && n_fslots > 0) {
         const size_t fb = (size_t)n_fslots * s->R * AST_C * sizeof(__nv_bfloat16), sb = (size_t)B * n_fslots * mat;
@@ -724,6 +743,7 @@ TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_he
     if (!ok) { *why = "cuTensorMapEncodeTiled failed"; tc_destroy(s); return nullptr; }
     if (cudaFuncSetAttribute(tc_fwd_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, F2_SMEM) != cudaSuccess ||
         cudaFuncSetAttribute(tc_bwd_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, B2_SMEM) != cudaSuccess ||
+        cudaFuncSetAttribute(tc_bwd_stack_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, S2_SMEM) != cudaSuccess ||
         cudaFuncSetAttribute(tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM) != cudaSuccess ||
         cudaFuncSetAttribute(tc_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM) != cudaSuccess) {
         *why = "cudaFuncSetAttribute(max dynamic smem) failed";
@@ -738,6 +758,7 @@ void tc_destroy(TcState* s) {
     cudaFree(s->a_hi); cudaFree(s->a_lo); cudaFree(s->dz);
     cudaFree(s->w1f); cudaFree(s->w2f); cudaFree(s->w1b); cudaFree(s->w2b);
     cudaFree(s->F); cudaFree(s->ssym); cudaFree(s->flags); cudaFree(s->ll_f); cudaFree(s->ll_b);
+    cudaFree(s->dz_lo); cudaFree(s->w1b_lo); cudaFree(s->w2b_lo);
     delete s;
 }
 
@@ -747,6 +768,10 @@ int tc_set_weights(TcState* s, const float* Wd, const float* Wr, cudaStream_t st
     tc_weights_fwd_kernel<<<(unsigned)((nr + 255) / 256), 256, 0, st>>>(Wr, s->w2f, s->NL);
     tc_weights_bwd_kernel<<<(unsigned)((nd + 255) / 256), 256, 0, st>>>(Wd, s->w1b, nd);
     tc_weights_bwd_kernel<<<(unsigned)((nr + 255) / 256), 256, 0, st>>>(Wr, s->w2b, nr);
+    if (s->split) {
+        tc_weights_bwd_lo_kernel<<<(unsigned)((nd + 255) / 256), 256, 0, st>>>(Wd, s->w1b_lo, nd);
+        tc_weights_bwd_lo_kernel<<<(unsigned)((nr + 255) / 256), 256, 0, st>>>(Wr, s->w2b_lo, nr);
+    }
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
@@ -947,6 +972,12 @@ int tc_backward_stack(TcState* s, const uint32_t* hmask, const uint32_t* zmask, 
             if (i + 1 < nl) a.peer.signal_seq = 0;
             a.tile0 = ln[i].tile0; a.grp_t0 = ln[i].grp_t0; a.grp_t1 = ln[i].grp_t1; a.wr_t0 = ln[i].wr_t0; a.wr_t1 = ln[i].wr_t1;
             if (!disjoint) cudaMemsetAsync(s->flags + 2 * nt + (size_t)2 * ln[i].tile0, 0, (size_t)2 * ln[i].ntiles * sizeof(unsigned), st);
+            if (s->split) {
+                BwdSplitArgs q;
+                memset(&q, 0, sizeof(q));
+                q.b = a; q.tmDzLo = s->tm_dz_lo; q.tmW1Lo = s->tm_w1b_lo; q.tmW2Lo = s->tm_w2b_lo; q.dz_lo = s->dz_lo; q.dF = s->dF;
+                e = launch_coop(tc_bwd_stack_split_kernel, dim3(ln[i].ntiles), dim3(F2_THREADS), S2_SMEM, st, q);
+            } else
             e = launch_coop(tc_bwd_stack_kernel, dim3(ln[i].ntiles), dim3(F2_THREADS), B2_SMEM, st, a);
             ast_launch_counter += 1;
         }

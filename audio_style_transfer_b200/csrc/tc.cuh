@@ -11,8 +11,9 @@ struct TcState;
 // n_fslots > 0 (Gatys head): also a bf16 copy F [n_fslots][R][128] of the style extracts, a bf16 image
 // of Ssym [B*n_fslots][128][128], and a map over the caller's Gram partial buffer
 // gram_part [gram_part_mats][128][128] fp32.
+// split: the accurate tier (AST_PREC_TC3): the backward sweep keeps hi / lo bf16 pairs of every operand (stack_bwd_split.cuh)
 TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_head, int n_fslots,
-                   float* gram_part, int64_t gram_part_mats, int64_t* bytes, const char** why);
+                   float* gram_part, int64_t gram_part_mats, bool split, int64_t* bytes, const char** why);
 void tc_destroy(TcState* s);
 // bf16 operand copies of the fp32 master weights (device pointers, layouts of ast_set_weights).
 int tc_set_weights(TcState* s, const float* Wd, const float* Wr, cudaStream_t st);

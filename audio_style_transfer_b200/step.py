@@ -13,7 +13,7 @@ import torch
 from . import _lib
 from .synth import EncoderWeights, layers_needed
 
-PRECISIONS = {"fp32": _lib.AST_PREC_FP32, "bf16": _lib.AST_PREC_BF16}
+PRECISIONS = {"fp32": _lib.AST_PREC_FP32, "bf16": _lib.AST_PREC_BF16, "tc3": _lib.AST_PREC_TC3}
 
 
 class _DevMem:

@@ -424,7 +424,9 @@ def run_ours(args):
                 "metric": "fwd+bwd+Gram-loss steps/sec @16384 samples", "value": rec["steps_per_s"], "unit": "steps/s",
                 "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": rec["ms_per_step"],
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-                "dtype": "bf16 (fwd operands 2-term bf16 split, fp32 accumulate in TMEM)" if args.precision == "bf16" else "f32",
+                "dtype": {"bf16": "bf16 (fwd operands 2-term bf16 split, fp32 accumulate in TMEM)",
+                          "tc3": "bf16 hi/lo operand pairs forward AND backward (3 MMAs per product), fp32 accumulate in TMEM, fp32 heads",
+                          "fp32": "f32"}[args.precision],
                 "data": "synthetic", "config": workload_config(name, wl, B, world, True),
                 "timing": {"l2": "flushed between timed steps (256 MiB memset outside the events)",
                            "graph": "eager launches + NCCL", "clock": "CUDA events on the launching stream, max over ranks"},
@@ -545,7 +547,7 @@ def run_ours(args):
         phases = [float(np.median([r[i] for r in reps])) for i in range(4)]
         enc_ms, bwd_ms, gram_ms, tot_ms = phases
         fl_layer = 2.0 * B * T * 128 * 128 * 4                       # one layer: K=3 conv + 1x1, 2 FLOP/MAC
-        stack = args.precision == "bf16" and st.uses_stack_kernels
+        stack = args.precision in ("bf16", "tc3") and st.uses_stack_kernels
         n_sg = L if (wl["gatys"] and args.precision == "bf16") else 0  # style-gradient GEMMs fused into the backward
         if stack:
             # ONE launch runs the start conv and all NL layers; the graph phase = that kernel + a 512-byte memset node
@@ -595,7 +597,9 @@ def run_ours(args):
         "metric": "fwd+bwd+Gram-loss steps/sec @16384 samples", "value": value, "unit": "steps/s",
         "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_per_step,
         "higher_is_better": True, "scaling": "strong" if sharded else "weak", "vs_baseline": None,
-        "dtype": "bf16 (fwd operands 2-term bf16 split, fp32 accumulate in TMEM)" if args.precision == "bf16" else "f32",
+        "dtype": {"bf16": "bf16 (fwd operands 2-term bf16 split, fp32 accumulate in TMEM)",
+                          "tc3": "bf16 hi/lo operand pairs forward AND backward (3 MMAs per product), fp32 accumulate in TMEM, fp32 heads",
+                          "fp32": "f32"}[args.precision],
         "data": "synthetic",
         "config": workload_config(name, wl, B, world, sharded),
         "timing": {"l2": "flushed between timed steps (256 MiB memset outside the events)",
@@ -647,7 +651,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
-    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "tc3", "fp32"])
     ap.add_argument("--pairs", type=int, default=0, help="independent pairs per GPU (B); default 1, cfg3: 8")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--shard-mode", dest="shard_mode", default="p2p", choices=["p2p", "halo", "overlap"],

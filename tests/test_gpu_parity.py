@@ -10,8 +10,13 @@ from oracle import cases, step_np
 
 pytestmark = pytest.mark.gpu
 
-TOL = {"fp32": dict(loss=1e-4, grad=1e-4, feat=2e-5), "bf16": dict(loss=1e-2, grad=1e-2, feat=2e-3)}
-PRECS = ["fp32", "bf16"]
+# tc3 = the accurate tensor-core tier (AST_PREC_TC3: tcgen05 convs with hi/lo bf16 operands both ways, fp32 heads).  Its
+# forward is the bf16 tier's (features ~1e-5..2e-5 from fp64: the fp32 accumulation inside the tensor core, not the operand
+# precision, is the floor -- fp16 hi/lo operands measured the same), its backward is 5-10x closer: <= 6e-4 with the device's
+# masks at every case (bf16 tier: 1.6e-3..5.6e-3).  It does not reach the 1e-4 of the CUDA-core fp32 tier.
+TOL = {"fp32": dict(loss=1e-4, grad=1e-4, feat=2e-5), "bf16": dict(loss=1e-2, grad=1e-2, feat=2e-3),
+       "tc3": dict(loss=1e-4, grad=1e-3, feat=2e-4)}
+PRECS = ["fp32", "bf16", "tc3"]
 
 
 def rel(a, b):
@@ -35,11 +40,11 @@ def grad_tol(prec, floor):
     raw figure of a 20..30-layer case is decided by a handful of ReLU sign bits that two roundings of the same forward
     legitimately disagree on (measured on B200, t16384_cfg0: ONE flipped bit near t = 11328 is 3.0e-4 of the gradient,
     everything else 1.5e-7), so it is a loose secondary bound; the strict statement is check_with_device_masks."""
-    return TOL["bf16"]["grad"] if prec == "bf16" else max(TOL["fp32"]["grad"], 10.0 * floor)
+    return TOL["bf16"]["grad"] if prec in ("bf16", "tc3") else max(TOL["fp32"]["grad"], 10.0 * floor)
 
 
 # a sign bit may differ from the oracle's only where the fp64 value is within rounding of zero: |v| <= FLIP_EPS * rms(v)
-FLIP_EPS = {"fp32": 2e-5, "bf16": 2e-2}
+FLIP_EPS = {"fp32": 2e-5, "bf16": 2e-2, "tc3": 2e-2}
 
 
 def check_with_device_masks(st, case, Pc, Ps, aux, g, prec, b=0):
