@@ -868,10 +868,13 @@ static StackPeer tc_peer_block(TcState* s, int order, int dir, int halo_in, int 
 struct TcLaunch { int tile0, ntiles, grp_t0, grp_t1, wr_t0, wr_t1; };
 // The launches of one segment: whole pairs while a pair fits the SMs, else groups of <= n_sm consecutive tiles of one pair
 // with `halo` tiles per inner side that are computed but not written.
-static int tc_plan_launches(const TcState* s, int halo, TcLaunch* out, int max_out) {
+// [r0, r1): the tiles of a pair that have to be evaluated at all (the backward of a time shard that exchanges halos needs
+// only own +- 1024 rows of its window); outside the whole-pair case the range's ends behave like clip ends.
+static int tc_plan_launches(const TcState* s, int halo, TcLaunch* out, int max_out, int r0 = 0, int r1 = -1) {
     const int tpp = s->T / 128, cap = TC_GROUP_CAP(s);
+    if (r1 < 0) r1 = tpp;
     int n = 0;
-    if (tpp <= cap) {
+    if (tpp <= cap && r0 == 0 && r1 == tpp) {
         const int ppl = cap / tpp;
         for (int p0 = 0; p0 < s->B && n < max_out; p0 += ppl) {
             const int np = s->B - p0 < ppl ? s->B - p0 : ppl;
@@ -880,10 +883,10 @@ static int tc_plan_launches(const TcState* s, int halo, TcLaunch* out, int max_o
         return n;
     }
     for (int p = 0; p < s->B; ++p)
-        for (int a = 0; a < tpp && n < max_out;) {
-            const int lo = a - halo > 0 ? a - halo : 0;
-            const int hi = lo + cap < tpp ? lo + cap : tpp;
-            const int e = hi == tpp ? tpp : hi - halo;
+        for (int a = r0; a < r1 && n < max_out;) {
+            const int lo = a - halo > r0 ? a - halo : r0;
+            const int hi = lo + cap < r1 ? lo + cap : r1;
+            const int e = hi == r1 ? r1 : hi - halo;
             out[n++] = TcLaunch{p * tpp + lo, hi - lo, lo * 128, hi * 128, a * 128, e * 128};
             a = e;
         }
@@ -960,9 +963,17 @@ int tc_backward_stack(TcState* s, const uint32_t* hmask, const uint32_t* zmask, 
                 a.need[m] = (unsigned short)acc;
             }
         }
-        const int nl = tc_plan_launches(s, s->seg_halo[k], ln, TC_MAX_LAUNCHES);
-        const bool disjoint = s->T / 128 <= TC_GROUP_CAP(s);
-        if (disjoint) cudaMemsetAsync(s->flags + 2 * nt, 0, 2 * nt * sizeof(unsigned), st);
+        // a time shard with halo exchange: only own +- 1024 rows carry exact masks and head gradients, and only the owned rows
+        // are kept -- the outer 1024 rows of the window are the forward's business
+        int r0 = 0, r1 = -1;
+        if (s->peer.sig_local) {
+            r0 = (s->peer.own_lo - TC_HALO_ROWS) / 128; r1 = (s->peer.own_hi + TC_HALO_ROWS) / 128;
+            if (r0 < 0) r0 = 0;
+            if (r1 > s->T / 128) r1 = s->T / 128;
+        }
+        const int nl = tc_plan_launches(s, s->seg_halo[k], ln, TC_MAX_LAUNCHES, r0, r1);
+        const bool disjoint = s->T / 128 <= TC_GROUP_CAP(s) && r0 == 0 && (r1 < 0 || r1 == s->T / 128);   // whole-pair launches
+        cudaMemsetAsync(s->flags + 2 * nt, 0, 2 * nt * sizeof(unsigned), st);
         // backward: the running gradient is exact on the owned rows after a segment; the 1024 rows on either side come from the
         // neighbours' result of the previous segment (their buffer of the same parity as this rank's g_in)
         const StackPeer pr = tc_peer_block(s, s->nseg - 1 - k, 1, 0, TC_HALO_ROWS, [&](int sd) {
@@ -971,7 +982,7 @@ int tc_backward_stack(TcState* s, const uint32_t* hmask, const uint32_t* zmask, 
             a.peer = pr;
             if (i + 1 < nl) a.peer.signal_seq = 0;
             a.tile0 = ln[i].tile0; a.grp_t0 = ln[i].grp_t0; a.grp_t1 = ln[i].grp_t1; a.wr_t0 = ln[i].wr_t0; a.wr_t1 = ln[i].wr_t1;
-            if (!disjoint) cudaMemsetAsync(s->flags + 2 * nt + (size_t)2 * ln[i].tile0, 0, (size_t)2 * ln[i].ntiles * sizeof(unsigned), st);
+            if (i > 0 && !disjoint) cudaMemsetAsync(s->flags + 2 * nt + (size_t)2 * ln[i].tile0, 0, (size_t)2 * ln[i].ntiles * sizeof(unsigned), st);
             if (s->split) {
                 BwdSplitArgs q;
                 memset(&q, 0, sizeof(q));

@@ -244,7 +244,7 @@ def run_timesharded(name, precision, rank, world, local, steps, warmup, mode="ha
     full = StyleStep(T, wl["cont"], wl["style"], wl["gatys"], precision=precision, device=local)
     full.set_weights(wl["w"])
     Pc, Ps = gpu_targets(full, torch.as_tensor(wl["content"], device=dev), torch.as_tensor(wl["style_a"], device=dev))
-    n1_ms, lo_full, g_full, n1_launches = None, None, None, None
+    n1_ms, lo_full, g_full, n1_launches, ex_full = None, None, None, None, None
     if rank == 0:
         full.set_targets(Pc, Ps, wl["lambd"])
         lo_full, g_full = torch.empty((1, 4), device=dev), torch.empty((1, T), device=dev)
@@ -253,6 +253,7 @@ def run_timesharded(name, precision, rank, world, local, steps, warmup, mode="ha
         n1_ms = timed(lambda: full.step_graph(x_full, lo_full, g_full), max(5, min(steps, 20)))
         full.check()
         n1_launches = full.launches_per_step
+        ex_full = full.extract(NL - 1)[0].clone()          # the seam check: every shard's owned rows must equal these bit for bit
     full.close()
     del full
     torch.cuda.empty_cache()
@@ -297,11 +298,20 @@ def run_timesharded(name, precision, rank, world, local, steps, warmup, mode="ha
     mine[:own.numel()] = own
     parts = [torch.empty(pad, device=dev) for _ in range(world)]
     dist.all_gather(parts, mine)
+    # the seam, bit for bit: the encoder's last extract on the owned rows of every rank against the unsharded clip's
+    ex_own = torch.zeros((pad, 128), device=dev)
+    ex_own[:own.numel()] = st.extract(NL - 1)[0, sh.ob - sh.wb:sh.oe - sh.wb]
+    ex_parts = [torch.empty((pad, 128), device=dev) for _ in range(world)]
+    dist.all_gather(ex_parts, ex_own)
     check = None
     if rank == 0:
+        ex = torch.cat([p[:n] for p, n in zip(ex_parts, sizes)])
+        seam = bool(torch.equal(ex, ex_full))
+        del ex, ex_full
         g = torch.cat([p[:n] for p, n in zip(parts, sizes)])
         check = {"grad_rel_l2_vs_unsharded": float((g - g_full[0]).double().norm() / g_full[0].double().norm()),
                  "loss_rel": float(abs(losses[0, 0] - lo_full[0, 0]) / abs(lo_full[0, 0])),
+                 "seam_last_extract_bit_exact": seam,
                  "tolerance": 1e-2, "gathered_with": "all_gather of the owned slices over NCCL"}
     for _ in range(max(3, warmup)):
         one_step()
@@ -435,7 +445,8 @@ def run_ours(args):
                 "launches_per_step": rec["launches_per_step"], "clocks": clk.summary(), "timesharded": rec,
             }
             print(json.dumps(line), flush=True)
-        ok = rank != 0 or (rec["check"]["grad_rel_l2_vs_unsharded"] <= 1e-2 and rec["check"]["loss_rel"] <= 1e-2)
+        ok = rank != 0 or (rec["check"]["grad_rel_l2_vs_unsharded"] <= 1e-2 and rec["check"]["loss_rel"] <= 1e-2
+                           and rec["check"]["seam_last_extract_bit_exact"])
         finish()
         if not ok:
             raise SystemExit("bench.py: the time-sharded gradient does not match the unsharded step")
@@ -639,7 +650,8 @@ def run_ours(args):
                                           "oracle/torch_step.py; reference TF1 path unavailable on this image)"}
     print(json.dumps(line), flush=True)
     finish()
-    bad = [r for r in shard_recs if r and ("error" in r or r["check"]["grad_rel_l2_vs_unsharded"] > 1e-2 or r["check"]["loss_rel"] > 1e-2)]
+    bad = [r for r in shard_recs if r and ("error" in r or r["check"]["grad_rel_l2_vs_unsharded"] > 1e-2 or r["check"]["loss_rel"] > 1e-2
+                                           or not r["check"]["seam_last_extract_bit_exact"])]
     if bad:
         raise SystemExit(f"bench.py: time-sharded self-check failed: {bad}")
 
