@@ -31,7 +31,7 @@ SYMBOLS = [
     "ast_set_weights", "ast_set_targets", "ast_embeds", "ast_step", "ast_step_graph", "ast_step_host",
     "ast_step_forward", "ast_partials", "ast_step_backward", "ast_get_extract", "ast_get_masks",
     "ast_segments", "ast_step_forward_seg", "ast_step_backward_seg", "ast_segment_buffer",
-    "ast_p2p_export", "ast_p2p_attach", "ast_p2p_attach_local",
+    "ast_p2p_export", "ast_p2p_attach", "ast_p2p_attach_local", "ast_p2p_detach",
     "ast_launches_per_step", "ast_step_timed", "ast_check", "ast_uses_stack_kernels", "ast_stft_reg_noalloc",
     "ast_opt_create", "ast_opt_destroy", "ast_opt_workspace_bytes", "ast_opt_reset", "ast_opt_buffers", "ast_opt_advance",
     "ast_opt_status", "ast_opt_result", "ast_opt_epochs", "ast_opt_log", "ast_minimize",
@@ -131,6 +131,7 @@ def load(experiments: bool = False) -> C.CDLL:
     lib.ast_p2p_export.argtypes = [vp, vp]
     lib.ast_p2p_attach.argtypes = [vp, i32, vp, i64, i32]
     lib.ast_p2p_attach_local.argtypes = [vp, i32, vp]
+    lib.ast_p2p_detach.argtypes = [vp]
     lib.ast_launches_per_step.argtypes = [vp]
     lib.ast_step_timed.argtypes = [vp, vp, vp, vp, vp, vp]
     lib.ast_check.argtypes = [vp, vp]

@@ -682,6 +682,14 @@ extern "C" int ast_p2p_attach(ast_ctx* c, int32_t side, const void* h_handles, i
     }
     return p2p_set(c, side, (const float*)q[0], (const float*)q[1], (const float*)q[2], (unsigned*)q[3], peer_win_begin, peer_T);
 }
+// Back to exchanging the halo rows by copies (ast_segment_buffer): forget the neighbours (their mappings stay open until
+// ast_destroy).  Every rank of the job must do the same.
+extern "C" int ast_p2p_detach(ast_ctx* c) {
+    int r = p2p_ready(c, 0);
+    if (r != AST_OK) return r;
+    tc_clear_peers(c->tc);
+    return AST_OK;
+}
 // Same process (several contexts of one process: tests, one-process multi-GPU with peer access enabled by the caller).
 extern "C" int ast_p2p_attach_local(ast_ctx* c, int32_t side, ast_ctx* peer) {
     int r = p2p_ready(c, side);

@@ -829,6 +829,10 @@ unsigned* tc_stack_err(TcState* s) { return s->flags + (size_t)4 * (s->R / 128);
 void tc_set_peer_geometry(TcState* s, int own_lo, int own_hi, unsigned* sig_local) {
     s->peer.own_lo = own_lo; s->peer.own_hi = own_hi; s->peer.sig_local = sig_local;
 }
+void tc_clear_peers(TcState* s) {
+    s->peer.on = false;
+    for (int sd = 0; sd < 2; ++sd) { s->peer.H[sd] = s->peer.g[sd] = s->peer.g_alt[sd] = nullptr; s->peer.sig[sd] = nullptr; }
+}
 void tc_set_peer(TcState* s, int side, const float* H, const float* g, const float* g_alt, unsigned* sig, int peer_R, int row_off) {
     s->peer.on = true;
     s->peer.H[side] = H; s->peer.g[side] = g; s->peer.g_alt[side] = g_alt; s->peer.sig[side] = sig;

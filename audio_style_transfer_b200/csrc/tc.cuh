@@ -33,6 +33,7 @@ unsigned* tc_stack_err(TcState* s);
 void tc_plan_segments(TcState* s, bool per_stack);
 // peer-mapped halos (time shards whose neighbours' buffers are mapped into this process: ast_p2p_attach)
 void tc_set_peer_geometry(TcState* s, int own_lo, int own_hi, unsigned* sig_local);
+void tc_clear_peers(TcState* s);
 void tc_set_peer(TcState* s, int side, const float* H, const float* g, const float* g_alt, unsigned* sig, int peer_R, int row_off);
 int tc_segments(const TcState* s);
 int tc_segment_end(const TcState* s, int k);

@@ -226,6 +226,9 @@ class StyleStep:
         with torch.cuda.device(self.dev):
             _lib.check(self.lib.ast_p2p_attach(self._h, int(side), C.create_string_buffer(handles, 256), int(peer_win_begin), int(peer_T)), self.lib)
 
+    def p2p_detach(self):
+        _lib.check(self.lib.ast_p2p_detach(self._h), self.lib)
+
     def p2p_attach_local(self, side: int, peer: "StyleStep"):
         _lib.check(self.lib.ast_p2p_attach_local(self._h, int(side), peer._h), self.lib)
 

@@ -170,12 +170,14 @@ int  ast_segment_buffer(ast_ctx* ctx, int32_t backward, int32_t seg, float** d_b
  * ast_partials stays the caller's.  All ranks must start the same evaluations in the same order.
  *   ast_p2p_export : AST_P2P_HANDLE_BYTES bytes (four cudaIpcMemHandle_t) to hand to the neighbour processes;
  *   ast_p2p_attach : side 0 = the rank that owns the samples before this window, 1 = after; peer_win_begin / peer_T as
- *                    in the neighbour's ast_config;  ast_p2p_attach_local: the neighbour is a context of this process.
+ *                    in the neighbour's ast_config;  ast_p2p_attach_local: the neighbour is a context of this process;
+ *   ast_p2p_detach : back to copies (every rank of the job, or none).
  * No reference counterpart (single device, methods.py:48-54,143).  B = 1 only. */
 #define AST_P2P_HANDLE_BYTES 256
 int  ast_p2p_export(ast_ctx* ctx, void* h_handles);
 int  ast_p2p_attach(ast_ctx* ctx, int32_t side, const void* h_handles, int64_t peer_win_begin, int32_t peer_T);
 int  ast_p2p_attach_local(ast_ctx* ctx, int32_t side, ast_ctx* peer);
+int  ast_p2p_detach(ast_ctx* ctx);   /* forget the neighbours again: halo rows are exchanged by copies as before */
 
 /* cfg.extracts[layer] of the last forward (model.py:116), [B,T,128] fp32 -> d_out.  Debug/parity.
  * After ast_embeds every layer is available.  After ast_step* in the tensor-core tier only the layers a head reads
