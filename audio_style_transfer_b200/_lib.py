@@ -15,8 +15,8 @@ from pathlib import Path
 PKG = Path(__file__).resolve().parent
 ROOT = PKG.parent
 SO = PKG / "libast_b200.so"
-SOURCES = ["csrc/api.cu", "csrc/kernels_f32.cu", "csrc/kernels_tc.cu", "csrc/gram_tc.cu", "csrc/stft_reg.cu", "csrc/lbfgs.cu", "csrc/gram_ours_tc.cu"]
-HEADERS = ["csrc/common.cuh", "csrc/tc.cuh", "csrc/ptx.cuh", "csrc/stack_fwd.cuh", "csrc/stack_bwd.cuh", "../include/ast_b200.h"]
+SOURCES = ["csrc/api.cu", "csrc/kernels_f32.cu", "csrc/kernels_tc.cu", "csrc/gram_tc.cu", "csrc/stft_reg.cu", "csrc/lbfgs.cu", "csrc/gram_ours_tc.cu", "csrc/gram_ours_tma.cu"]
+HEADERS = ["csrc/common.cuh", "csrc/tc.cuh", "csrc/ptx.cuh", "csrc/stack_fwd.cuh", "csrc/stack_bwd.cuh", "csrc/stack_bwd_split.cuh", "../include/ast_b200.h"]
 SO_EXP = PKG / "libast_b200_exp.so"      # the same sources with -DAST_EXPERIMENTS: timeline stamps, fault injection, A/B switches
 
 AST_PREC_FP32 = 0

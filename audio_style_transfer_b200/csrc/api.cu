@@ -54,6 +54,9 @@ struct ast_ctx {
     int nmat, nmat_used, msize, n_side;
     int gram_chunk_rows, gram_nchunk, sse_nblk;
     bool gram_ours_tc;            // channel-wise Gram on tensor cores (gram_ours_tc.cu)
+    bool ours_tma;                // ... fed by TMA from the transposed extract copies Ht the whole-stack forward writes (gram_ours_tma.cu)
+    float* Ht;                    // [R/16][L][128][16] fp32
+    OursTma ours_tma_map;
     int64_t bytes;
     std::vector<void*> allocs;
     // weights (fp32 masters + transposes for the backward)
@@ -190,6 +193,7 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
     c->n_cont = cfg->n_cont; c->prec = cfg->precision; c->bytes = 0;
     c->generation = ++g_ctx_generation;
     c->p2p_sig = nullptr;
+    c->ours_tma = false; c->Ht = nullptr;
     c->tc = nullptr; c->hstream = nullptr; c->gexec = nullptr; c->p_x = c->p_out = nullptr;
     c->gdev = nullptr; c->gdev_x = nullptr; c->gdev_losses = c->gdev_grad = nullptr;
     for (auto& g : c->gphase) g = nullptr;
@@ -240,10 +244,12 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
         if (!cfg->gatys) target = 64;            // 64 chunks x 4 channel quads = 256 CTAs, all resident at 2 per SM; halves the partials
         c->gram_ours_tc = !cfg->gatys && cfg->precision == AST_PREC_BF16 && gram_ours_tc_supported(c->L) && !exp_switch("AST_B200_GRAM_OURS_CUDA");
         if (c->gram_ours_tc) target = 37;        // one CTA per SM (164 KB of smem): 37 chunks x 4 quads = 148 CTAs, one wave
+        c->ours_tma = c->gram_ours_tc && cfg->kernel_path != AST_PATH_PER_LAYER && !exp_switch("AST_B200_OURS_NO_TMA");
         // (the split does NOT depend on B: pair b of a batch then sums in the same order as the same pair alone, so a batch
         // equals its pairs evaluated one by one bit for bit -- tests/test_gpu_configs.py)
         int rows = (c->T + target - 1) / target;
         rows = std::max(128, ((rows + 127) / 128) * 128);
+        if (c->ours_tma) rows = ours_tma_chunk_rows(c->T, target);     // multiples of 16 rows: 37 chunks at T = 16384, not 32
         if (cfg->gatys && cfg->precision == AST_PREC_BF16) {
             // tensor-core Gram: one wave of CTAs, each accumulating its tiles in TMEM
             const int ntiles = c->T / 128;
@@ -311,6 +317,13 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
         c->use_stack = tc_stack_ok(c->tc) && cfg->kernel_path != AST_PATH_PER_LAYER;
         c->use_stack_bwd = c->use_stack && cfg->kernel_path != AST_PATH_PER_LAYER_BWD;
         if (c->split && !c->use_stack_bwd) { ast_destroy(c); return fail(AST_EUNSUPPORTED, "AST_PREC_TC3 runs on the whole-stack kernels only (kernel_path auto)"); }
+        if (c->ours_tma && !c->use_stack) c->ours_tma = false;         // only the whole-stack forward writes the transposed copies
+        if (c->ours_tma) {
+            DA(c->Ht, (size_t)c->L * RC);
+            CK(cudaMemset(c->Ht, 0, (size_t)c->L * RC * sizeof(float)));     // rows no launch writes (window edges of a time shard) stay finite
+            if (ours_tma_make_map(&c->ours_tma_map, c->Ht, c->L, c->R) != 0) { ast_destroy(c); return fail(AST_ECUDA, "tensor map over the transposed extracts failed"); }
+            tc_set_transposed_extracts(c->tc, c->Ht, c->L);
+        }
         if (cfg->halo_exchange) {
             if (!c->use_stack_bwd) { ast_destroy(c); return fail(AST_EUNSUPPORTED, "halo_exchange needs the whole-stack kernels (kernel_path auto)"); }
             tc_plan_segments(c->tc, true);
@@ -425,8 +438,9 @@ static int run_encoder(ast_ctx* c, const float* d_x, cudaStream_t s, bool keep_a
         unsigned char keep[33];
         for (int i = 0; i <= c->NL; ++i) keep[i] = keep_all ? 1 : 0;
         for (int i = 0; i < c->n_cont; ++i) keep[c->cont_layer[i] + 1] = 1;
-        if (!c->cfg.gatys || c->split)          // channel-wise Gram and its gradient (and every head of the accurate tier) read the fp32 extracts
+        if ((!c->cfg.gatys && !c->ours_tma) || c->split)   // channel-wise Gram and its gradient (and every head of the accurate tier) read the fp32 extracts
             for (int i = 0; i < c->L; ++i) keep[c->style_layer[i] + 1] = 1;
+        if (c->ours_tma) keep[c->NL] = 1;       // the head reads the transposed copies; the last extract stays for ast_get_extract
         memcpy(c->h_kept, keep, sizeof(keep));
         if (tc_forward_stack(c->tc, d_x, c->W0, c->b0, c->bd, c->br, c->H, c->zmask, c->hmask, c->f_slot, keep, seg, s) != 0)
             return fail(AST_ECUDA, "whole-stack forward launch failed: %s", cudaGetErrorString(cudaGetLastError()));
@@ -460,7 +474,8 @@ static void run_gram(ast_ctx* c, cudaStream_t s, bool fused = false) {
     else if (c->cfg.gatys)
         launch_gram_gatys(c->d_Fptr, c->L, c->T, c->B, c->own_lo, c->own_hi, c->gram_part, c->gram_nchunk, c->gram_chunk_rows, s);
     else
-        if (c->gram_ours_tc) launch_gram_ours_tc(c->ours_ptrs, c->L, c->T, c->B, c->own_lo, c->own_hi, c->gram_part, c->gram_nchunk, c->gram_chunk_rows, s);
+        if (c->ours_tma) launch_gram_ours_tma(c->ours_tma_map, c->L, c->T, c->B, c->own_lo, c->own_hi, c->gram_part, c->gram_nchunk, c->gram_chunk_rows, s);
+        else if (c->gram_ours_tc) launch_gram_ours_tc(c->ours_ptrs, c->L, c->T, c->B, c->own_lo, c->own_hi, c->gram_part, c->gram_nchunk, c->gram_chunk_rows, s);
         else launch_gram_ours(c->d_Fptr, c->L, c->T, c->B, c->own_lo, c->own_hi, c->gram_part, c->gram_nchunk, c->gram_chunk_rows, s);
     if (!fold_gram_reduce(c, fused))
         launch_gram_reduce(c->gram_part, c->partials, c->cfg.gatys, c->L, c->B, c->gram_nchunk, s);
@@ -553,6 +568,7 @@ static int step_backward_impl(ast_ctx* c, float* d_losses, float* d_grad, void* 
         tc_style_grad(c->tc, c->L, hos, s);
     }
     else if (c->cfg.gatys) launch_style_grad_gatys(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
+    else if (c->ours_tma) launch_style_grad_ours_tma(c->ours_tma_map, c->ours_ptrs, c->Ssym, c->L, c->T, c->B, s);
     else if (c->gram_ours_tc && !exp_switch("AST_B200_SGO_CUDA")) launch_style_grad_ours_tc(c->ours_ptrs, c->Ssym, c->L, c->T, c->B, s);
     else              launch_style_grad_ours(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);
     if (do_top) {

@@ -620,6 +620,7 @@ struct TcState {
     const float* dF;
     __nv_bfloat16 *F, *ssym;                   // Gatys head: bf16 extracts [n_fslots][R][128], bf16 Ssym [B*n_fslots][128][128]
     int n_fslots;
+    float* Ht; int n_tslots;                   // transposed fp32 extract copies [R/16][n_tslots][128][16] of the channel-wise head, or NULL (owned by the caller)
     CUtensorMap tm_F, tm_ssym, tm_gpart, tm_dF_st;
     CUtensorMap tm_a_hi, tm_a_lo, tm_dz, tm_H, tm_g, tm_dF;      // box = 128 rows x 128 bytes, loads and stores
     CUtensorMap tm_w1f, tm_w2f, tm_w1b, tm_w2b;
@@ -824,6 +825,7 @@ void tc_plan_segments(TcState* s, bool per_stack) {
 int tc_segments(const TcState* s) { return s->nseg; }
 int tc_segment_end(const TcState* s, int k) { return s->seg_hi[k]; }
 bool tc_stack_ok(const TcState* s) { return s && s->coop && s->NL <= 32 && s->n_sm >= 64; }
+void tc_set_transposed_extracts(TcState* s, float* Ht, int n_slots) { s->Ht = Ht; s->n_tslots = n_slots; }
 unsigned* tc_stack_err(TcState* s) { return s->flags + (size_t)4 * (s->R / 128); }
 
 void tc_set_peer_geometry(TcState* s, int own_lo, int own_hi, unsigned* sig_local) {
@@ -909,6 +911,8 @@ int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b
     a.flags = s->flags; a.err = tc_stack_err(s); a.epoch = tc_stack_err(s) + 2; a.ll = s->ll_f;
     a.T = s->T; a.R = s->R; a.NL = s->NL; a.tiles_per_pair = s->T / 128; a.ntiles = s->R / 128;
     for (int l = 0; l < 32; ++l) a.f_slot[l] = (signed char)((s->n_fslots > 0 && l < s->NL) ? f_slot[l] : -1);
+    a.Ht = s->Ht; a.n_tslots = s->n_tslots;
+    for (int l = 0; l < 32; ++l) a.t_slot[l] = (signed char)((s->Ht && l < s->NL) ? f_slot[l] : -1);
     for (int i = 0; i <= s->NL; ++i) a.export_h[i] = export_h[i];
     for (int k = 0; k + 1 < s->nseg; ++k) a.export_h[s->seg_hi[k]] = 1;      // the next segment resumes from H[seg_hi]
     TcLaunch ln[TC_MAX_LAUNCHES];

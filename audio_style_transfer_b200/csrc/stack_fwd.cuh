@@ -85,6 +85,8 @@ struct alignas(64) FwdStackArgs {
     uint32_t* zmask; uint32_t* hmask;            // [NL][R][4], [NL+1][R][4]
     __nv_bfloat16* a_hi; __nv_bfloat16* a_lo;    // the buffers behind tmA_* (published with plain stores)
     __nv_bfloat16* F;                // bf16 extract copies [n_style][R][128]
+    float* Ht;                       // transposed fp32 extract copies [R/16][n_tslots][128][16 rows] (channel-wise head, gram_ours_tma.cu) or NULL
+    int n_tslots;
     uint4* ll;                       // near hand-off lines [2][ntiles][2 sides][2 K-halves][4 cc][2 parts][4][32 rows] x 16 B
     unsigned* flags;                 // [ntiles][2] (K-half), zeroed before the launch
     unsigned* epoch;                 // [0] launch epoch (tags), [1] CTAs done: the last CTA of a launch bumps the epoch
@@ -101,6 +103,7 @@ struct alignas(64) FwdStackArgs {
     StackPeer peer;
     unsigned short need[34];         // need[i]: flag value once publish i (relu(h_i), i = 0: start conv) is complete
     signed char f_slot[32];          // style slot that receives bf16(H[l+1]), or -1
+    signed char t_slot[32];          // style slot whose transposed copy Ht[slot] receives H[l+1], or -1
     unsigned char export_h[33];      // export_h[i] != 0: H[i] is written to global memory (i = 0: start-conv output)
 };
 
@@ -554,6 +557,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
         auto finish = [&](int i) {
             if (!wr) return;
             const int f = i >= 1 ? (int)p.f_slot[i - 1] : -1;
+            const int ts = i >= 1 ? (int)p.t_slot[i - 1] : -1;
             const bool exp = p.export_h[i] != 0;
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
@@ -574,6 +578,11 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
                     st_global_v8(p.F + ((size_t)f * p.R + row) * AST_C + col,
                                  pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]),
                                  pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]), pack_bf16(v[14], v[15]));
+                if (ts >= 0) {                         // transposed copy [row / 16][slot][channel][row % 16]: a warp's 32 rows of one channel = two 64-byte runs
+                    float* ht = p.Ht + (((((size_t)(row >> 4) * p.n_tslots + ts) * AST_C + col) << 4) | (row & 15));
+#pragma unroll
+                    for (int e = 0; e < 16; ++e) ht[e * 16] = v[e];
+                }
             }
         };
         // Near hand-off, consumer side: the d boundary rows of both neighbours (publish i) -> window halo, K-half by K-half.
