@@ -569,10 +569,13 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
 #pragma unroll
                 for (int e = 0; e < 16; ++e) or_bit_if_pos(word, v[e], 1u << e);
                 hmask16[((size_t)i * p.R + row) * 8 + j * 4 + cc] = (uint16_t)word;
-                if (exp) {
-                    float4* out = reinterpret_cast<float4*>(p.H + ((size_t)i * p.R + row) * AST_C + col);
+                if (exp) {                             // 16 columns = 64 bytes = two full sectors per thread
+                    float* out = p.H + ((size_t)i * p.R + row) * AST_C + col;
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) out[e] = make_float4(v[4 * e], v[4 * e + 1], v[4 * e + 2], v[4 * e + 3]);
+                    for (int e = 0; e < 2; ++e)
+                        st_global_v8(out + 8 * e, __float_as_uint(v[8 * e]), __float_as_uint(v[8 * e + 1]), __float_as_uint(v[8 * e + 2]),
+                                     __float_as_uint(v[8 * e + 3]), __float_as_uint(v[8 * e + 4]), __float_as_uint(v[8 * e + 5]),
+                                     __float_as_uint(v[8 * e + 6]), __float_as_uint(v[8 * e + 7]));
                 }
                 if (f >= 0)                            // bf16 extract copy: 16 columns = 32 bytes = one full sector per thread
                     st_global_v8(p.F + ((size_t)f * p.R + row) * AST_C + col,
