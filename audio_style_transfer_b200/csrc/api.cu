@@ -244,7 +244,9 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
         if (!cfg->gatys) target = 64;            // 64 chunks x 4 channel quads = 256 CTAs, all resident at 2 per SM; halves the partials
         c->gram_ours_tc = !cfg->gatys && cfg->precision == AST_PREC_BF16 && gram_ours_tc_supported(c->L) && !exp_switch("AST_B200_GRAM_OURS_CUDA");
         if (c->gram_ours_tc) target = 37;        // one CTA per SM (164 KB of smem): 37 chunks x 4 quads = 148 CTAs, one wave
-        c->ours_tma = c->gram_ours_tc && cfg->kernel_path != AST_PATH_PER_LAYER && !exp_switch("AST_B200_OURS_NO_TMA");
+        c->ours_tma = !cfg->gatys && cfg->precision == AST_PREC_BF16 && ours_tma_supported(c->L) && cfg->kernel_path != AST_PATH_PER_LAYER &&
+                      !exp_switch("AST_B200_OURS_NO_TMA");
+        if (c->ours_tma) target = 37;            // one CTA per SM: 37 chunks x 4 channel quads = 148 CTAs, one wave
         // (the split does NOT depend on B: pair b of a batch then sums in the same order as the same pair alone, so a batch
         // equals its pairs evaluated one by one bit for bit -- tests/test_gpu_configs.py)
         int rows = (c->T + target - 1) / target;

@@ -62,6 +62,7 @@ void launch_gram_ours_tc(const OursPtrs& ptrs, int L, int T, int B, int own_lo, 
 // The same two fed by TMA from transposed extract copies Ht [R/16][L][128][16 rows] that the whole-stack forward kernel
 // writes (gram_ours_tma.cu).  OursTma::map holds the CUtensorMap over Ht; chunk_rows / own_lo / own_hi / T multiples of 16.
 struct OursTma { alignas(64) unsigned char map[128]; };
+int  ours_tma_supported(int L);
 int  ours_tma_make_map(OursTma* o, float* Ht, int L, int R);      // 0 = ok
 int  ours_tma_chunk_rows(int T, int target);
 void launch_gram_ours_tma(const OursTma& o, int L, int T, int B, int own_lo, int own_hi, float* part, int nchunk,
