@@ -72,7 +72,8 @@ typedef struct ast_config {
     int32_t n_layers;                /* NL = 1 + highest extract used (TF prunes the rest)              */
     int32_t n_cont;                  /* --cont_lyrs (methods.py:254)                                     */
     int32_t cont_ids[AST_MAX_IDS];
-    int32_t n_style;                 /* resolved style ids (methods.py:60-66)                            */
+    int32_t n_style;                 /* resolved style ids (methods.py:60-66); an encoder layer may appear only once
+                                      * (29 and 30 are the same layer): AST_EUNSUPPORTED otherwise, see INTEGRATION.md */
     int32_t style_ids[AST_MAX_IDS];
     int32_t gatys;                   /* --gatys (methods.py:261)                                         */
     int32_t nb_channels;             /* --channels (methods.py:258), ours only                           */
