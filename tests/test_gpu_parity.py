@@ -410,3 +410,44 @@ def test_regulariser_time_sharded_equals_unsharded():
     for st in steps:
         st.close()
     full.close()
+
+
+@pytest.mark.parametrize("L", [1, 2, 12, 13, 16, 17, 30])
+def test_tma_fed_channelwise_head_agrees_with_the_second_implementation(L):
+    """The channel-wise head of the bf16 tier streams transposed extract copies by TMA (gram_ours_tma.cu, 16- and 32-layer
+    stages); the per-layer kernel path keeps the kernels that read the [t][c] extracts (kernels_f32.cu / gram_ours_tc.cu).
+    Same Gram (TF32 / fp32 products, fp32 sums: 1e-4) for every stage geometry -- one layer, a full 16-layer stage, one past
+    it, all 30 -- and, for the edge counts, the Gram against the fp64 oracle."""
+    from audio_style_transfer_b200 import synth
+    from audio_style_transfer_b200.mu_law import mu_law_numpy
+    T = 1024
+    style = list(range(30 - L, 30))                                 # the top L layers: every dilation class
+    cont = [29]
+    w = synth.make_weights(30, seed=0, bias_scale=0.1)
+    c_mu = mu_law_numpy(synth.content_audio(T)).astype(np.float64)
+    s_mu = mu_law_numpy(synth.style_audio(T, chunks=1)).astype(np.float64)
+    case = dict(T=T, cont=cont, style=style, gatys=False, nb=128, cnt=128, NL=30, w=w, c_mu=c_mu, s_chunks=[s_mu],
+                x=synth.step_input(c_mu).astype(np.float64), lambd=cases.LAMBD)
+    st_a, st_b = make_step(case, "bf16"), make_step(case, "bf16", kernel_path="per_layer")
+    assert st_a.uses_stack_kernels and not st_b.uses_stack_kernels
+    Ec_a, Gn_a = st_a.embeds(s_mu[None])
+    Ec_b, Gn_b = st_b.embeds(s_mu[None])
+    assert rel(Gn_a.cpu().numpy(), Gn_b.cpu().numpy()) <= 1e-4, L
+    if L in (1, 16, 17):
+        Pc, Ps = cases.oracle_targets(case)
+        assert rel(Gn_a[0].cpu().numpy(), Ps[:Gn_a.shape[1]]) <= TOL["bf16"]["feat"], L
+    rng = np.random.default_rng(L)
+    Pc = rng.standard_normal((1, T, 128)).astype(np.float32)
+    Ps = rng.standard_normal(tuple(Gn_a.shape)).astype(np.float32)
+    Ps /= np.sqrt((Ps ** 2).sum(axis=(-2, -1), keepdims=True))
+    res = []
+    for st in (st_a, st_b):
+        st.set_targets(Pc, Ps, case["lambd"])
+        lo, g = st.step(case["x"][None])
+        torch.cuda.synchronize()
+        st.check()
+        res.append((lo.cpu().numpy()[0], g.cpu().numpy()[0]))
+        st.close()
+    (lo_a, g_a), (lo_b, g_b) = res
+    assert abs(lo_a[0] - lo_b[0]) <= 1e-3 * abs(lo_b[0]), (L, lo_a, lo_b)
+    assert rel(g_a, g_b) <= TOL["bf16"]["grad"], L                 # two accumulation orders of the bf16 tier (see above)
