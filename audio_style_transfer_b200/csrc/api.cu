@@ -55,7 +55,7 @@ struct ast_ctx {
     int gram_chunk_rows, gram_nchunk, sse_nblk;
     bool gram_ours_tc;            // channel-wise Gram on tensor cores (gram_ours_tc.cu)
     bool ours_tma;                // ... fed by TMA from the transposed extract copies Ht the whole-stack forward writes (gram_ours_tma.cu)
-    float* Ht;                    // [R/16][L][128][16] fp32
+    unsigned char* Ht;            // [R/32][L][128][32] fp16
     OursTma ours_tma_map;
     int64_t bytes;
     std::vector<void*> allocs;
@@ -251,7 +251,7 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
         // equals its pairs evaluated one by one bit for bit -- tests/test_gpu_configs.py)
         int rows = (c->T + target - 1) / target;
         rows = std::max(128, ((rows + 127) / 128) * 128);
-        if (c->ours_tma) rows = ours_tma_chunk_rows(c->T, target);     // multiples of 16 rows: 37 chunks at T = 16384, not 32
+        if (c->ours_tma) rows = ours_tma_chunk_rows(c->T, target);     // multiples of 32 rows: 35 chunks at T = 16384, not 32
         if (cfg->gatys && cfg->precision == AST_PREC_BF16) {
             // tensor-core Gram: one wave of CTAs, each accumulating its tiles in TMEM
             const int ntiles = c->T / 128;
@@ -321,8 +321,8 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
         if (c->split && !c->use_stack_bwd) { ast_destroy(c); return fail(AST_EUNSUPPORTED, "AST_PREC_TC3 runs on the whole-stack kernels only (kernel_path auto)"); }
         if (c->ours_tma && !c->use_stack) c->ours_tma = false;         // only the whole-stack forward writes the transposed copies
         if (c->ours_tma) {
-            DA(c->Ht, (size_t)c->L * RC);
-            CK(cudaMemset(c->Ht, 0, (size_t)c->L * RC * sizeof(float)));     // rows no launch writes (window edges of a time shard) stay finite
+            DA(c->Ht, ours_tma_bytes(c->L, c->R));
+            CK(cudaMemset(c->Ht, 0, ours_tma_bytes(c->L, c->R)));            // rows no launch writes (window edges of a time shard) stay finite
             if (ours_tma_make_map(&c->ours_tma_map, c->Ht, c->L, c->R) != 0) { ast_destroy(c); return fail(AST_ECUDA, "tensor map over the transposed extracts failed"); }
             tc_set_transposed_extracts(c->tc, c->Ht, c->L);
         }

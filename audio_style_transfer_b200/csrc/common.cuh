@@ -59,11 +59,12 @@ struct OursPtrs { const float* F[32]; float* dF[32]; };
 void launch_style_grad_ours_tc(const OursPtrs& ptrs, const float* Ssym, int L, int T, int B, cudaStream_t s);
 void launch_gram_ours_tc(const OursPtrs& ptrs, int L, int T, int B, int own_lo, int own_hi,
                          float* part, int nchunk, int chunk_rows, cudaStream_t s);
-// The same two fed by TMA from transposed extract copies Ht [R/16][L][128][16 rows] that the whole-stack forward kernel
-// writes (gram_ours_tma.cu).  OursTma::map holds the CUtensorMap over Ht; chunk_rows / own_lo / own_hi / T multiples of 16.
+// The same two fed by TMA from transposed fp16 extract copies Ht [R/32][L][128][32 rows] that the whole-stack forward kernel
+// writes (gram_ours_tma.cu).  OursTma::map holds the CUtensorMap over Ht; chunk_rows / own_lo / own_hi / T multiples of 32.
 struct OursTma { alignas(64) unsigned char map[128]; };
 int  ours_tma_supported(int L);
-int  ours_tma_make_map(OursTma* o, float* Ht, int L, int R);      // 0 = ok
+size_t ours_tma_bytes(int L, int R);                              // size of Ht
+int  ours_tma_make_map(OursTma* o, void* Ht, int L, int R);       // 0 = ok
 int  ours_tma_chunk_rows(int T, int target);
 void launch_gram_ours_tma(const OursTma& o, int L, int T, int B, int own_lo, int own_hi, float* part, int nchunk,
                           int chunk_rows, cudaStream_t s);

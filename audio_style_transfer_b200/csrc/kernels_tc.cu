@@ -19,6 +19,7 @@
 #include "ptx.cuh"
 
 #include <cuda.h>
+#include <cuda_fp16.h>
 #include <cudaTypedefs.h>
 
 #include <cstdio>
@@ -620,7 +621,7 @@ struct TcState {
     const float* dF;
     __nv_bfloat16 *F, *ssym;                   // Gatys head: bf16 extracts [n_fslots][R][128], bf16 Ssym [B*n_fslots][128][128]
     int n_fslots;
-    float* Ht; int n_tslots;                   // transposed fp32 extract copies [R/16][n_tslots][128][16] of the channel-wise head, or NULL (owned by the caller)
+    __half* Ht; int n_tslots;                  // transposed fp16 extract copies [R/32][n_tslots][128][32] of the channel-wise head, or NULL (owned by the caller)
     CUtensorMap tm_F, tm_ssym, tm_gpart, tm_dF_st;
     CUtensorMap tm_a_hi, tm_a_lo, tm_dz, tm_H, tm_g, tm_dF;      // box = 128 rows x 128 bytes, loads and stores
     CUtensorMap tm_w1f, tm_w2f, tm_w1b, tm_w2b;
@@ -825,7 +826,7 @@ void tc_plan_segments(TcState* s, bool per_stack) {
 int tc_segments(const TcState* s) { return s->nseg; }
 int tc_segment_end(const TcState* s, int k) { return s->seg_hi[k]; }
 bool tc_stack_ok(const TcState* s) { return s && s->coop && s->NL <= 32 && s->n_sm >= 64; }
-void tc_set_transposed_extracts(TcState* s, float* Ht, int n_slots) { s->Ht = Ht; s->n_tslots = n_slots; }
+void tc_set_transposed_extracts(TcState* s, void* Ht, int n_slots) { s->Ht = static_cast<__half*>(Ht); s->n_tslots = n_slots; }
 unsigned* tc_stack_err(TcState* s) { return s->flags + (size_t)4 * (s->R / 128); }
 
 void tc_set_peer_geometry(TcState* s, int own_lo, int own_hi, unsigned* sig_local) {

@@ -43,6 +43,7 @@
 // the host gives every group ceil(sum(d) / 128) halo tiles per inner side and only tiles in [wr_t0, wr_t1) write masks,
 // exports and extract copies (tc_plan_groups in kernels_tc.cu).
 #pragma once
+#include <cuda_fp16.h>
 
 struct StackPeer {
     const float* src[2];             // the neighbour's buffer this segment resumes from (fp32 [rows][128]), or NULL
@@ -85,7 +86,7 @@ struct alignas(64) FwdStackArgs {
     uint32_t* zmask; uint32_t* hmask;            // [NL][R][4], [NL+1][R][4]
     __nv_bfloat16* a_hi; __nv_bfloat16* a_lo;    // the buffers behind tmA_* (published with plain stores)
     __nv_bfloat16* F;                // bf16 extract copies [n_style][R][128]
-    float* Ht;                       // transposed fp32 extract copies [R/16][n_tslots][128][16 rows] (channel-wise head, gram_ours_tma.cu) or NULL
+    __half* Ht;                      // transposed fp16 extract copies [R/32][n_tslots][128][32 rows] (channel-wise head, gram_ours_tma.cu) or NULL
     int n_tslots;
     uint4* ll;                       // near hand-off lines [2][ntiles][2 sides][2 K-halves][4 cc][2 parts][4][32 rows] x 16 B
     unsigned* flags;                 // [ntiles][2] (K-half), zeroed before the launch
@@ -581,10 +582,14 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
                     st_global_v8(p.F + ((size_t)f * p.R + row) * AST_C + col,
                                  pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]),
                                  pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]), pack_bf16(v[14], v[15]));
-                if (ts >= 0) {                         // transposed copy [row / 16][slot][channel][row % 16]: a warp's 32 rows of one channel = two 64-byte runs
-                    float* ht = p.Ht + (((((size_t)(row >> 4) * p.n_tslots + ts) * AST_C + col) << 4) | (row & 15));
+                if (ts >= 0) {                         // transposed fp16 copy [row / 32][slot][channel][row % 32]: a warp's 32 rows of one channel = one 64-byte run
+                    __half* ht = p.Ht + ((((size_t)(row >> 5) * p.n_tslots + ts) * AST_C + col) << 5) + (row & 31);
 #pragma unroll
-                    for (int e = 0; e < 16; ++e) ht[e * 16] = v[e];
+                    for (int e = 0; e < 16; ++e) {
+                        unsigned short hv;
+                        asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(hv) : "f"(v[e]));
+                        reinterpret_cast<unsigned short*>(ht)[e * 32] = hv;
+                    }
                 }
             }
         };

@@ -29,9 +29,9 @@ void tc_layer_fwd(TcState* s, int l, const float* bd, const float* br, uint32_t*
 // Clips with more tiles than SMs run as layer SEGMENTS (one per 10-layer stack) x tile GROUPS (stack_fwd.cuh); seg < 0 runs
 // every segment, seg >= 0 only that one (time shards exchange halo rows of H[tc_segment_end(seg)] / g between segments).
 bool tc_stack_ok(const TcState* s);
-// The whole-stack forward also writes H[l+1] of every style layer transposed into Ht [R/16][n_slots][128][16 rows]
+// The whole-stack forward also writes H[l+1] of every style layer transposed, in fp16, into Ht [R/32][n_slots][128][32 rows]
 // (slot = f_slot[l]): the operand layout of the TMA-fed channel-wise head (gram_ours_tma.cu).  NULL switches it off.
-void tc_set_transposed_extracts(TcState* s, float* Ht, int n_slots);
+void tc_set_transposed_extracts(TcState* s, void* Ht, int n_slots);
 unsigned* tc_stack_err(TcState* s);
 void tc_plan_segments(TcState* s, bool per_stack);
 // peer-mapped halos (time shards whose neighbours' buffers are mapped into this process: ast_p2p_attach)
