@@ -251,7 +251,7 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
         // equals its pairs evaluated one by one bit for bit -- tests/test_gpu_configs.py)
         int rows = (c->T + target - 1) / target;
         rows = std::max(128, ((rows + 127) / 128) * 128);
-        if (c->ours_tma) rows = ours_tma_chunk_rows(c->T, target);     // multiples of 32 rows: 35 chunks at T = 16384, not 32
+        if (c->ours_tma) rows = ours_tma_chunk_rows(c->T, target);     // multiples of 32 rows: 37 chunks at T = 16384, not 32
         if (cfg->gatys && cfg->precision == AST_PREC_BF16) {
             // tensor-core Gram: one wave of CTAs, each accumulating its tiles in TMEM
             const int ntiles = c->T / 128;
