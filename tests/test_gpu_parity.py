@@ -451,3 +451,28 @@ def test_tma_fed_channelwise_head_agrees_with_the_second_implementation(L):
     (lo_a, g_a), (lo_b, g_b) = res
     assert abs(lo_a[0] - lo_b[0]) <= 1e-3 * abs(lo_b[0]), (L, lo_a, lo_b)
     assert rel(g_a, g_b) <= TOL["bf16"]["grad"], L                 # two accumulation orders of the bf16 tier (see above)
+
+
+def test_channelwise_head_saturates_instead_of_overflowing():
+    """The TMA-fed channel-wise head reads fp16 copies of the style extracts (gram_ours_tma.cu): values beyond +-65504 are
+    clipped by a saturating conversion ("Differences ..."), never turned into inf / NaN.  Biases of 2e5 push
+    every extract past the fp16 range: Gram, losses and gradient must stay finite, and the extract itself (fp32) is exact."""
+    from audio_style_transfer_b200 import synth
+    from audio_style_transfer_b200.mu_law import mu_law_numpy
+    T = 1024
+    w = synth.make_weights(10, seed=0, bias_scale=2e5)
+    c_mu = mu_law_numpy(synth.content_audio(T)).astype(np.float64)
+    case = dict(T=T, cont=[9], style=list(range(10)), gatys=False, nb=128, cnt=128, NL=10, w=w)
+    st = make_step(case, "bf16")
+    x = synth.step_input(c_mu)[None]
+    Ec, Gn = st.embeds(x)
+    assert float(st.extract(9).abs().max()) > 65504.0               # the premise: out of fp16 range
+    assert bool(torch.isfinite(Gn).all())
+    rng = np.random.default_rng(0)
+    Pc = rng.standard_normal((1, T, 128)).astype(np.float32)
+    st.set_targets(Pc, Gn.cpu().numpy() * 0.5, cases.LAMBD)
+    lo, g = st.step(x)
+    torch.cuda.synchronize()
+    st.check()
+    assert bool(torch.isfinite(lo).all()) and bool(torch.isfinite(g).all())
+    st.close()
