@@ -329,8 +329,8 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
         if (cfg->halo_exchange) {
             if (!c->use_stack_bwd) { ast_destroy(c); return fail(AST_EUNSUPPORTED, "halo_exchange needs the whole-stack kernels (kernel_path auto)"); }
             tc_plan_segments(c->tc, true);
-            DA(c->p2p_sig, 4);
-            CK(cudaMemset(c->p2p_sig, 0, 4 * sizeof(unsigned)));
+            DA(c->p2p_sig, 8);                             // 4 completion words + 2 evaluation counters (tc_set_peer_geometry)
+            CK(cudaMemset(c->p2p_sig, 0, 8 * sizeof(unsigned)));
             tc_set_peer_geometry(c->tc, c->own_lo, c->own_hi, c->p2p_sig);
         }
     } else if (cfg->halo_exchange) {

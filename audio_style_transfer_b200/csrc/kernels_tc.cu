@@ -638,7 +638,7 @@ struct TcState {
         int R[2]; int row_off[2];
         int own_lo, own_hi;            // owned range in window coordinates
         unsigned* sig_local;           // this rank's signal words [2 sides][2 directions]
-        unsigned step_f, step_b;       // forward / backward evaluations started (all ranks count alike)
+        unsigned* d_step;              // device [2]: forward / backward evaluations started (all ranks count alike); bumped on the stream
     } peer;
 };
 
@@ -831,6 +831,7 @@ unsigned* tc_stack_err(TcState* s) { return s->flags + (size_t)4 * (s->R / 128);
 
 void tc_set_peer_geometry(TcState* s, int own_lo, int own_hi, unsigned* sig_local) {
     s->peer.own_lo = own_lo; s->peer.own_hi = own_hi; s->peer.sig_local = sig_local;
+    s->peer.d_step = sig_local + 4;                  // the caller's buffer: 4 signal words, then the two evaluation counters
 }
 void tc_clear_peers(TcState* s) {
     s->peer.on = false;
@@ -844,17 +845,19 @@ void tc_set_peer(TcState* s, int side, const float* H, const float* g, const flo
 // The StackPeer block of segment k.  order = position of the segment in its sweep (forward: k, backward: nseg-1-k); a
 // segment waits for the signal the neighbours' previous segment of the SAME evaluation sent, and (unless it is the last of
 // the sweep) signals them in turn.  src_of(side) = the neighbour's buffer this segment resumes from.
+__global__ void tc_peer_step_bump_kernel(unsigned* step) { *step += 1u; }
 template <typename SrcOf>
-static StackPeer tc_peer_block(TcState* s, int order, int dir, int halo_in, int halo_out, SrcOf src_of) {
+static StackPeer tc_peer_block(TcState* s, int order, int dir, int halo_in, int halo_out, SrcOf src_of, cudaStream_t st) {
     StackPeer pr;
     memset(&pr, 0, sizeof(pr));
     if (!s->peer.on) return pr;
-    unsigned& step = dir == 0 ? s->peer.step_f : s->peer.step_b;
-    if (order == 0) ++step;
-    const unsigned base = step * 8u;
+    // the evaluation number lives in device memory and is counted on the stream: eager launches and replays of a captured
+    // graph (HaloShardedStep.capture) number their evaluations alike on every rank
+    if (order == 0) { tc_peer_step_bump_kernel<<<1, 1, 0, st>>>(s->peer.d_step + dir); ast_launch_counter += 1; }
+    pr.step = s->peer.d_step + dir;
     const int lo = s->peer.own_lo, hi = s->peer.own_hi;
     if (order > 0) {
-        pr.wait_seq = base + (unsigned)order;
+        pr.wait_seq = (unsigned)order;
         for (int sd = 0; sd < 2; ++sd) {
             if (!s->peer.sig[sd]) continue;
             pr.src[sd] = src_of(sd);
@@ -865,7 +868,7 @@ static StackPeer tc_peer_block(TcState* s, int order, int dir, int halo_in, int 
         pr.t0[1] = hi + halo_in;  pr.t1[1] = hi + halo_out;         // ... and after it
     }
     if (order + 1 < s->nseg) {
-        pr.signal_seq = base + (unsigned)order + 1u;
+        pr.signal_seq = (unsigned)order + 1u;
         for (int sd = 0; sd < 2; ++sd) pr.sig_out[sd] = s->peer.sig[sd] ? s->peer.sig[sd] + (1 - sd) * 2 + dir : nullptr;
     }
     return pr;
@@ -932,7 +935,7 @@ int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b
         if (disjoint) cudaMemsetAsync(s->flags, 0, 2 * (size_t)(s->R / 128) * sizeof(unsigned), st);
         // forward: the stream is exact on own +- 1024 after a segment; the 1024 rows beyond come from the neighbours' H[l_begin]
         const StackPeer pr = tc_peer_block(s, k, 0, TC_HALO_ROWS, 2 * TC_HALO_ROWS, [&](int sd) {
-            return s->peer.H[sd] + (size_t)a.l_begin * s->peer.R[sd] * AST_C; });
+            return s->peer.H[sd] + (size_t)a.l_begin * s->peer.R[sd] * AST_C; }, st);
         for (int i = 0; i < nl && e == cudaSuccess; ++i) {
             a.peer = pr;
             if (i + 1 < nl) a.peer.signal_seq = 0;                 // only the segment's last launch signals
@@ -986,7 +989,7 @@ int tc_backward_stack(TcState* s, const uint32_t* hmask, const uint32_t* zmask, 
         // backward: the running gradient is exact on the owned rows after a segment; the 1024 rows on either side come from the
         // neighbours' result of the previous segment (their buffer of the same parity as this rank's g_in)
         const StackPeer pr = tc_peer_block(s, s->nseg - 1 - k, 1, 0, TC_HALO_ROWS, [&](int sd) {
-            return (k & 1) ? s->peer.g[sd] : s->peer.g_alt[sd]; });
+            return (k & 1) ? s->peer.g[sd] : s->peer.g_alt[sd]; }, st);
         for (int i = 0; i < nl && e == cudaSuccess; ++i) {
             a.peer = pr;
             if (i + 1 < nl) a.peer.signal_seq = 0;

@@ -49,9 +49,11 @@ struct StackPeer {
     const float* src[2];             // the neighbour's buffer this segment resumes from (fp32 [rows][128]), or NULL
     int t0[2], t1[2];                // tiles with t0 in [t0[s], t1[s]) take their rows from side s
     int row_off[2];                  // neighbour row = in-window t + row_off[s]
-    const unsigned* sig_wait[2];     // this rank's word the neighbour signals; wait until *sig_wait[s] >= wait_seq
-    unsigned* sig_out[2];            // the neighbours' words to signal when this launch (signal_seq != 0) has completed
-    unsigned wait_seq, signal_seq;
+    const unsigned* sig_wait[2];     // this rank's word the neighbour signals; wait until *sig_wait[s] >= *step * 8 + wait_seq
+    unsigned* sig_out[2];            // the neighbours' words to signal (*step * 8 + signal_seq) when this launch (signal_seq != 0) has completed
+    const unsigned* step;            // device word: evaluations of this sweep direction started so far (bumped by a one-thread kernel in
+                                     // front of the sweep's first launch, so a captured graph counts on as it is replayed)
+    unsigned wait_seq, signal_seq;   // position of the segment in its sweep (wait) / + 1 (signal)
 };
 // sys-scope flag and data accesses of the peer-mapped halo path
 __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
@@ -256,9 +258,10 @@ __device__ __forceinline__ int stack_peer_side(const StackPeer& pr, int t0, vola
     if (pr.src[0] && t0 >= pr.t0[0] && t0 < pr.t1[0]) side = 0;
     else if (pr.src[1] && t0 >= pr.t0[1] && t0 < pr.t1[1]) side = 1;
     if (side < 0) return -1;
-    if (ld_acquire_sys(pr.sig_wait[side]) >= pr.wait_seq) return side;
+    const unsigned want = *pr.step * 8u + pr.wait_seq;
+    if (ld_acquire_sys(pr.sig_wait[side]) >= want) return side;
     const unsigned long long t_start = global_timer_ns();
-    while (ld_acquire_sys(pr.sig_wait[side]) < pr.wait_seq) {
+    while (ld_acquire_sys(pr.sig_wait[side]) < want) {
         if (stack_aborted(ab)) return side;
         if (global_timer_ns() - t_start > FS_PEER_WAIT_NS) { stack_abort(ab, err, 4u); return side; }
         __nanosleep(200);
@@ -271,7 +274,7 @@ __device__ __forceinline__ void stack_peer_signal(const StackPeer& pr) {
     __threadfence_system();
 #pragma unroll
     for (int sd = 0; sd < 2; ++sd)
-        if (pr.sig_out[sd]) st_release_sys(pr.sig_out[sd], pr.signal_seq);
+        if (pr.sig_out[sd]) st_release_sys(pr.sig_out[sd], *pr.step * 8u + pr.signal_seq);
 }
 
 __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __grid_constant__ FwdStackArgs p) {

@@ -111,7 +111,8 @@ class HaloShardedStep:
 
     attach_p2p() replaces those messages by peer-mapped memory: every rank maps its neighbours' buffers once (CUDA IPC) and
     the stack kernels read the halo rows over NVLink themselves, gated by completion words the neighbours' kernels write
-    (include/ast_b200.h: ast_p2p_*).  A step is then forward, all-reduce, backward: no host-side exchange at all."""
+    (include/ast_b200.h: ast_p2p_*).  A step is then forward, all-reduce, backward: no host-side exchange at all, and
+    capture() turns it into one CUDA graph per rank."""
 
     def __init__(self, T: int, rank: int, world: int, make_ctx: Callable, all_reduce: Callable, exchange: Callable = None):
         self.T, self.rank, self.world = T, rank, world
@@ -136,6 +137,24 @@ class HaloShardedStep:
 
     def window(self, full):
         return full[:, self.wb:self.we]
+
+    def capture(self, x_window, losses, grad, warmup: int = 2):
+        """Peer-mapped halos only: captures forward -> all-reduce -> backward of this rank into ONE CUDA graph (the stack
+        kernels, their flag memsets, the NCCL all-reduce) and returns `replay()`.  The evaluation number the completion words
+        carry is counted in device memory on the stream (kernels_tc.cu: tc_peer_step_bump_kernel), so every replay is a new
+        evaluation on every rank.  x_window / losses / grad are the graph's static buffers: write the next x into
+        x_window in place.  Every rank must capture, and replay equally often."""
+        import torch
+        if not self.p2p:
+            raise RuntimeError("capture() needs attach_p2p(): the NCCL send/recv route exchanges rows between host calls")
+        for _ in range(max(1, warmup)):               # NCCL communicator and every lazy allocation exist before the capture
+            self.step(x_window, losses, grad)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, capture_error_mode="thread_local"):
+            self.step(x_window, losses, grad)
+        self._graph = g
+        return g.replay
 
     def _swap(self, buf, send_up, recv_up, send_dn, recv_dn):
         """buf [B, T_win, 128]; the four (begin, end) ranges are global sample indices."""

@@ -334,6 +334,38 @@ def run_timesharded(name, precision, rank, world, local, steps, warmup, mode="ha
     barrier()
     ms = timed(one_step, steps)
     barrier()
+    # ---- the same step as ONE captured CUDA graph per rank (stack kernels + flag memsets + the NCCL all-reduce); peer-mapped
+    # halos only: the NCCL send/recv route exchanges rows between host calls -----------------------------------------
+    eager_ms, graph_ms, graph_note, graph_same = ms, None, None, None
+    if mode == "p2p" and world > 1:
+        ok, same, replay = 1, 0, None
+        try:
+            g_eager, lo_eager = grad.clone(), losses.clone()
+            replay = sh.capture(x, losses, grad)
+            replay()
+            torch.cuda.synchronize()
+            st.check()
+            same = int(torch.equal(grad, g_eager) and torch.equal(losses, lo_eager))
+        except Exception as e:      # noqa: BLE001 -- a failed capture must not take the record down: the eager number stands
+            ok, graph_note = 0, "graph capture failed: " + repr(e)
+            try:
+                torch.cuda.synchronize()
+            except Exception:       # noqa: BLE001
+                pass
+        flag = torch.tensor([ok, same], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag[0]) == 1:
+            graph_same = bool(int(flag[1]))
+            for _ in range(3):
+                replay()
+            barrier()
+            graph_ms = timed(replay, steps)
+            barrier()
+            st.check()
+            if graph_same:
+                ms = graph_ms
+        elif graph_note is None:
+            graph_note = "graph capture failed on another rank"
     parts_buf = st.partials()
     ar_ms = timed(lambda: dist.all_reduce(parts_buf), 20)
     ex_ms = None
@@ -341,9 +373,10 @@ def run_timesharded(name, precision, rank, world, local, steps, warmup, mode="ha
         buf = st.segment_buffer(False, 0)
         ob, oe, H = sh.ob, sh.oe, HALO
         ex_ms = timed(lambda: sh._swap(buf, (ob + H, ob + 2 * H), (ob - 2 * H, ob - H), (oe - 2 * H, oe - H), (oe + H, oe + 2 * H)), 20)
-    t = torch.tensor([ms, ar_ms, ex_ms or 0.0, float(st.T)], device=dev, dtype=torch.float64)
+    t = torch.tensor([ms, ar_ms, ex_ms or 0.0, float(st.T), eager_ms, graph_ms or 0.0], device=dev, dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, ar_ms, ex_ms, win_max = [float(v) for v in t]
+    ms, ar_ms, ex_ms, win_max, eager_ms, graph_ms_max = [float(v) for v in t]
+    graph_ms = graph_ms_max if graph_ms is not None else None
     launches, nseg = st.launches_per_step, st.segments
     st.check()
     barrier()                                  # no rank unmaps its buffers while a neighbour may still read them
@@ -366,7 +399,11 @@ def run_timesharded(name, precision, rank, world, local, steps, warmup, mode="ha
             "redundant_rows_frac": (win_max - T / world) / (T / world),
             "launches_per_step": launches, "n1_launches_per_step": n1_launches,
             "model_tflops": flops / (ms * 1e-3) / 1e12, "check": check,
-            "timing": "CUDA events, L2 flushed between steps, max over ranks; eager launches + NCCL (no graph)"}
+            "eager_ms_per_step": eager_ms, "graph_ms_per_step": graph_ms, "graph_equals_eager_bit_for_bit": graph_same,
+            "graph_note": graph_note,
+            "timing": "CUDA events, L2 flushed between steps, max over ranks; ms_per_step = " +
+                      ("replays of ONE captured CUDA graph per rank (stack kernels + NCCL all-reduce; HaloShardedStep.capture)"
+                       if graph_ms is not None and graph_same else "eager launches + NCCL (no graph)")}
 
 
 def run_other_config(name, precision, local, steps, B=None):
