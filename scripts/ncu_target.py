@@ -1,5 +1,5 @@
 """Small target for `ncu --set full`: 3 steps of cfg1 (Gatys, whole-stack kernels) and 3 of the CLI-default workload
-(all 30 layers channel-wise: gram_ours_tc / style_grad_ours_tc).  No oracle, no timing: see B200_PROFILING.md."""
+(all 30 layers channel-wise: gram_ours_tma / style_grad_ours_tma).  No oracle, no timing: see B200_PROFILING.md."""
 import sys
 from pathlib import Path
 
