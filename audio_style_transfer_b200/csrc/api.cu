@@ -252,7 +252,7 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
         int rows = (c->T + target - 1) / target;
         rows = std::max(128, ((rows + 127) / 128) * 128);
         if (c->ours_tma) rows = ours_tma_chunk_rows(c->T, target);     // multiples of 32 rows: 37 chunks at T = 16384, not 32
-        if (cfg->gatys && cfg->precision == AST_PREC_BF16) {
+        if (cfg->gatys && cfg->precision != AST_PREC_FP32) {
             // tensor-core Gram: one wave of CTAs, each accumulating its tiles in TMEM
             const int ntiles = c->T / 128;
             int nch = std::max(1, std::min(ntiles, 148 / std::max(1, c->L)));
@@ -311,8 +311,9 @@ extern "C" int ast_create(const ast_config* cfg, ast_ctx** out) {
     c->split = c->prec == AST_PREC_TC3;
     if (c->prec != AST_PREC_FP32) {
         const char* why = nullptr;
-        // accurate tier: no bf16 extract copies (its heads read the fp32 extracts), hi / lo backward operands
-        c->tc = tc_create(c->T, c->B, c->NL, c->H, c->g, c->dF, c->n_head, (cfg->gatys && !c->split) ? c->L : 0, c->gram_part,
+        // accurate tier: hi / lo backward operands; its Gatys heads multiply hi / lo bf16 pairs of the extracts and of Ssym on
+        // tcgen05 (gram_tc.cu: *_split_kernel), its channel-wise heads read the fp32 extracts on CUDA cores
+        c->tc = tc_create(c->T, c->B, c->NL, c->H, c->g, c->dF, c->n_head, cfg->gatys ? c->L : 0, c->gram_part,
                           (int64_t)c->B * c->nmat * c->gram_nchunk, c->split, &c->bytes, &why);
         if (!c->tc) { ast_destroy(c); return fail(AST_ECUDA, "tensor-core path setup failed: %s", why ? why : "?"); }
         // cfg->kernel_path: AST_PATH_PER_LAYER = one kernel per layer both ways, AST_PATH_PER_LAYER_BWD = whole-stack forward only
@@ -440,7 +441,7 @@ static int run_encoder(ast_ctx* c, const float* d_x, cudaStream_t s, bool keep_a
         unsigned char keep[33];
         for (int i = 0; i <= c->NL; ++i) keep[i] = keep_all ? 1 : 0;
         for (int i = 0; i < c->n_cont; ++i) keep[c->cont_layer[i] + 1] = 1;
-        if ((!c->cfg.gatys && !c->ours_tma) || c->split)   // channel-wise Gram and its gradient (and every head of the accurate tier) read the fp32 extracts
+        if (!c->cfg.gatys && !c->ours_tma)      // the channel-wise heads of the fp32-extract kernels (accurate tier, per-layer path)
             for (int i = 0; i < c->L; ++i) keep[c->style_layer[i] + 1] = 1;
         if (c->ours_tma) keep[c->NL] = 1;       // the head reads the transposed copies; the last extract stays for ast_get_extract
         memcpy(c->h_kept, keep, sizeof(keep));
@@ -471,7 +472,7 @@ static int run_encoder(ast_ctx* c, const float* d_x, cudaStream_t s, bool keep_a
 // Gatys split-K chunks and the content partials itself and its last CTA writes the losses (3 launches fewer).
 static inline bool fold_gram_reduce(const ast_ctx* c, bool fused) { return fused && c->cfg.gatys && c->gram_nchunk < 32; }
 static void run_gram(ast_ctx* c, cudaStream_t s, bool fused = false) {
-    if (c->cfg.gatys && c->tc && !c->split)
+    if (c->cfg.gatys && c->tc)
         tc_gram(c->tc, c->L, c->gram_nchunk, c->gram_chunk_rows / 128, c->own_lo / 128, c->own_hi / 128, s);
     else if (c->cfg.gatys)
         launch_gram_gatys(c->d_Fptr, c->L, c->T, c->B, c->own_lo, c->own_hi, c->gram_part, c->gram_nchunk, c->gram_chunk_rows, s);
@@ -529,7 +530,8 @@ static HeadArgs head_args(ast_ctx* c, bool with_targets, float* losses, bool fus
     const double Ns = (double)c->nmat_used * c->msize;
     const double Nc = (double)c->total_T * c->n_cont * c->cfg.cnt_channels;
     h.G = c->partials; h.Ps = c->Ps; h.Gn = c->Gn; h.Ssym = with_targets ? c->Ssym : nullptr;
-    h.Ssym_bf16 = (with_targets && c->cfg.gatys && c->tc && !c->split) ? tc_ssym_bf16(c->tc) : nullptr;
+    h.Ssym_bf16 = (with_targets && c->cfg.gatys && c->tc) ? tc_ssym_bf16(c->tc) : nullptr;
+    h.Ssym_bf16_lo = (with_targets && c->cfg.gatys && c->tc && c->split) ? tc_ssym_bf16_lo(c->tc) : nullptr;
     h.ls_part = c->ls_part; h.sse = c->partials + (size_t)c->B * c->nmat * c->msize; h.losses = losses;
     h.nmat = c->nmat; h.nmat_used = with_targets ? c->nmat_used : 0; h.n = c->n_side; h.B = c->B;
     if (fused) {
@@ -567,6 +569,11 @@ static int step_backward_impl(ast_ctx* c, float* d_losses, float* d_grad, void* 
     else if (fuse_sg) {
         int hos[AST_MAX_IDS];
         for (int i = 0; i < c->L; ++i) hos[i] = is_cont[c->style_layer[i]] ? c->head_of_slot[i] : -1;
+        tc_style_grad(c->tc, c->L, hos, s);
+    }
+    else if (c->cfg.gatys && c->tc && c->split) {       // accurate tier: every slot through the hi / lo tcgen05 kernel; the backward reads dF
+        int hos[AST_MAX_IDS];
+        for (int i = 0; i < c->L; ++i) hos[i] = c->head_of_slot[i];
         tc_style_grad(c->tc, c->L, hos, s);
     }
     else if (c->cfg.gatys) launch_style_grad_gatys(c->d_Fptr, c->d_dFptr, c->Ssym, c->L, c->T, c->B, s);

@@ -87,6 +87,7 @@ struct HeadArgs {
     float* Gn;            // out, may be NULL: normalised Gram [B][nmat][msize]
     float* Ssym;          // out, may be NULL: [B][nmat][msize]
     __nv_bfloat16* Ssym_bf16;   // out, may be NULL: bf16 image of Ssym (B operand of the tensor-core style gradient)
+    __nv_bfloat16* Ssym_bf16_lo; // out, may be NULL: bf16(Ssym - float(Ssym_bf16)) (accurate tier: hi / lo operand pairs)
     float* ls_part;       // [B][nmat] per-matrix sum of squared differences
     const float* sse;     // [B] content squared error (already all-reduced when sharded)
     float* losses;        // out [B][4]

@@ -111,8 +111,106 @@ __global__ void __launch_bounds__(192, 1) gram_tc_kernel(const __grid_constant__
     if (warp == 1) tmem_dealloc<128>(acc);
 }
 
-void launch_gram_tc(const GramTcArgs& a, int nchunk, int L, int B, cudaStream_t s) {
-    launch_pdl(gram_tc_kernel, dim3(nchunk, L, B), dim3(192), GRAM_SMEM, s, a);
+// The accurate tier (AST_PREC_TC3): F = F_hi + F_lo as two bf16 copies; G = F_hi^T F_hi + F_hi^T F_lo + F_lo^T F_hi (the lo x lo
+// term is below fp32 rounding), three MMAs per k-step into the same TMEM accumulator.  Two stages of {hi, lo} tiles (64 KB).
+#define GRAMS_NS 2
+#define GRAMS_STAGE (4 * TILE16)
+#define GRAMS_SMEM (GRAMS_NS * GRAMS_STAGE + 4 * TILE16 + 1024 + 128)
+
+__global__ void __launch_bounds__(192, 1) gram_tc_split_kernel(const __grid_constant__ GramTcArgs p) {
+    extern __shared__ uint8_t tc_smem_raw[];
+    const uint32_t base = (smem_u32(tc_smem_raw) + 1023u) & ~1023u;
+    uint8_t* gen = tc_smem_raw + (base - smem_u32(tc_smem_raw));
+    const uint32_t s_out = base + GRAMS_NS * GRAMS_STAGE, bar = s_out + 4 * TILE16;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int l = blockIdx.y, b = blockIdx.z;
+    const int lo = max(p.tile_lo, (int)blockIdx.x * p.chunk_tiles);
+    const int hi = min(p.tile_hi, ((int)blockIdx.x + 1) * p.chunk_tiles);
+    const int ntile = max(hi - lo, 0);
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&p.tmF); tma_prefetch_desc(&p.tmFlo); tma_prefetch_desc(&p.tmP);
+        for (int i = 0; i < GRAMS_NS; ++i) { mbar_init(bar + GB_FULL(i), 1); mbar_init(bar + GB_EMPTY(i), 1); }
+        mbar_init(bar + GB_ACC, 1);
+        mbar_init_fence();
+    }
+    if (warp == 1) tmem_alloc<128>(bar + GB_TMEM);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t acc = *reinterpret_cast<volatile uint32_t*>(gen + (bar + GB_TMEM - base));
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int it = 0; it < ntile; ++it) {
+                const int slot = it % GRAMS_NS;
+                mbar_wait(bar + GB_EMPTY(slot), ((it / GRAMS_NS) & 1) ^ 1);
+                const uint32_t st = base + slot * GRAMS_STAGE, fb = bar + GB_FULL(slot);
+                mbar_expect_tx(fb, 4 * TILE16);
+                tma_load_4d(st, &p.tmF, fb, 0, (lo + it) * 128, b, l);
+                tma_load_4d(st + TILE16, &p.tmF, fb, 64, (lo + it) * 128, b, l);
+                tma_load_4d(st + 2 * TILE16, &p.tmFlo, fb, 0, (lo + it) * 128, b, l);
+                tma_load_4d(st + 3 * TILE16, &p.tmFlo, fb, 64, (lo + it) * 128, b, l);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(128, 128, true, true);
+            for (int it = 0; it < ntile; ++it) {
+                const int slot = it % GRAMS_NS;
+                mbar_wait(bar + GB_FULL(slot), (it / GRAMS_NS) & 1);
+                tc_fence_after();
+                const uint32_t st = base + slot * GRAMS_STAGE;
+#pragma unroll
+                for (int ks = 0; ks < 8; ++ks) {
+                    const uint64_t dh = umma_desc_mnmajor_sw128(st + ks * 2048, TILE16);
+                    const uint64_t dl = umma_desc_mnmajor_sw128(st + 2 * TILE16 + ks * 2048, TILE16);
+                    umma_f16(acc, dh, dh, idesc, (it > 0 || ks > 0) ? 1u : 0u);
+                    umma_f16(acc, dh, dl, idesc, 1u);
+                    umma_f16(acc, dl, dh, idesc, 1u);
+                }
+                umma_commit(bar + GB_EMPTY(slot));
+            }
+            umma_commit(bar + GB_ACC);
+        }
+        __syncwarp();
+    } else {
+        const int q = warp & 3, r = q * 32 + lane;
+        const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+        float v[32];
+        mbar_wait(bar + GB_ACC, 0);
+        tc_fence_after();
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+            if (ntile > 0) tmem_ld32(acc + lane_off + cc * 32, v);
+            else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = 0.f;
+            }
+            uint8_t* o = gen + (s_out - base) + cc * TILE16;
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                *reinterpret_cast<float4*>(o + sw128_off(r, i)) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+            const int prow = (((b * p.L + l) * (int)gridDim.x) + (int)blockIdx.x) * 128 + q * 32;
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc) tma_store_2d(&p.tmP, s_out + cc * TILE16 + q * 4096, cc * 32, prow);
+            tma_store_commit();
+            tma_store_wait_all();
+        }
+        __syncwarp();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<128>(acc);
+}
+
+void launch_gram_tc(const GramTcArgs& a, int nchunk, int L, int B, bool split, cudaStream_t s) {
+    if (split) gram_tc_split_kernel<<<dim3(nchunk, L, B), 192, GRAMS_SMEM, s>>>(a);
+    else launch_pdl(gram_tc_kernel, dim3(nchunk, L, B), dim3(192), GRAM_SMEM, s, a);
     ast_launch_counter += 1;
 }
 
@@ -196,13 +294,103 @@ __global__ void __launch_bounds__(192, 3) sgrad_tc_kernel(const __grid_constant_
     if (warp == 1) tmem_dealloc<128>(acc);
 }
 
-void launch_sgrad_tc(const SGradTcArgs& a, int ntiles, cudaStream_t s) {
-    launch_pdl(sgrad_tc_kernel, dim3(ntiles, a.n_active), dim3(192), SG_SMEM, s, a);
+// The accurate tier: dF = F_hi S_hi + F_lo S_hi + F_hi S_lo.  Tiles 0,1 = F_hi, 2,3 = F_lo, 4,5 = S_hi, 6,7 = S_lo (K-halves).
+#define SGS_SMEM (8 * TILE16 + 1024 + 128)
+
+__global__ void __launch_bounds__(192, 1) sgrad_tc_split_kernel(const __grid_constant__ SGradTcArgs p) {
+    extern __shared__ uint8_t tc_smem_raw[];
+    const uint32_t base = (smem_u32(tc_smem_raw) + 1023u) & ~1023u;
+    uint8_t* gen = tc_smem_raw + (base - smem_u32(tc_smem_raw));
+    const uint32_t bar = base + 8 * TILE16;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int row0 = blockIdx.x * 128, l = p.slot_of[blockIdx.y];
+    const int b = row0 / p.T, t0 = row0 - b * p.T;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&p.tmF); tma_prefetch_desc(&p.tmS); tma_prefetch_desc(&p.tmFlo); tma_prefetch_desc(&p.tmSlo);
+        tma_prefetch_desc(&p.tmDF);
+        mbar_init(bar + GB_FULL(0), 1); mbar_init(bar + GB_ACC, 1);
+        mbar_init_fence();
+    }
+    if (warp == 1) tmem_alloc<128>(bar + GB_TMEM);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t acc = *reinterpret_cast<volatile uint32_t*>(gen + (bar + GB_TMEM - base));
+
+    if (warp == 0) {
+        if (lane == 0) {
+            const uint32_t fb = bar + GB_FULL(0);
+            mbar_expect_tx(fb, 8 * TILE16);
+            for (int j = 0; j < 2; ++j) {
+                tma_load_4d(base + j * TILE16, &p.tmF, fb, j * 64, t0, b, l);
+                tma_load_4d(base + (2 + j) * TILE16, &p.tmFlo, fb, j * 64, t0, b, l);
+                tma_load_2d(base + (4 + j) * TILE16, &p.tmS, fb, j * 64, (b * p.L + l) * 128);
+                tma_load_2d(base + (6 + j) * TILE16, &p.tmSlo, fb, j * 64, (b * p.L + l) * 128);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(128, 128);
+            mbar_wait(bar + GB_FULL(0), 0);
+            tc_fence_after();
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk) {
+                    const uint64_t fh = umma_desc_kmajor_sw128(base + j * TILE16 + kk * 32);
+                    const uint64_t fl = umma_desc_kmajor_sw128(base + (2 + j) * TILE16 + kk * 32);
+                    const uint64_t sh = umma_desc_kmajor_sw128(base + (4 + j) * TILE16 + kk * 32);
+                    const uint64_t sl = umma_desc_kmajor_sw128(base + (6 + j) * TILE16 + kk * 32);
+                    umma_f16(acc, fh, sh, idesc, (j > 0 || kk > 0) ? 1u : 0u);
+                    umma_f16(acc, fl, sh, idesc, 1u);
+                    umma_f16(acc, fh, sl, idesc, 1u);
+                }
+            umma_commit(bar + GB_ACC);
+        }
+        __syncwarp();
+    } else {
+        const int q = warp & 3, r = q * 32 + lane;
+        const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+        float v[32];
+        mbar_wait(bar + GB_ACC, 0);                 // MMAs complete: the operand tiles are dead, reuse the first four as staging
+        tc_fence_after();
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+            tmem_ld32(acc + lane_off + cc * 32, v);
+            uint8_t* o = gen + cc * TILE16;
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                *reinterpret_cast<float4*>(o + sw128_off(r, i)) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc)
+                tma_store_4d(&p.tmDF, base + cc * TILE16 + q * 4096, cc * 32, t0 + q * 32, b, p.head_of_slot[l]);
+            tma_store_commit();
+            tma_store_wait_all();
+        }
+        __syncwarp();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<128>(acc);
+}
+
+void launch_sgrad_tc(const SGradTcArgs& a, int ntiles, bool split, cudaStream_t s) {
+    if (split) sgrad_tc_split_kernel<<<dim3(ntiles, a.n_active), 192, SGS_SMEM, s>>>(a);
+    else launch_pdl(sgrad_tc_kernel, dim3(ntiles, a.n_active), dim3(192), SG_SMEM, s, a);
     ast_launch_counter += 1;
 }
 
 int setup_gram_tc_kernels() {
     cudaError_t e = cudaFuncSetAttribute(gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GRAM_SMEM);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(gram_tc_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GRAMS_SMEM);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(sgrad_tc_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SGS_SMEM);
     if (e != cudaSuccess) return (int)e;
     return (int)cudaFuncSetAttribute(sgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SG_SMEM);
 }

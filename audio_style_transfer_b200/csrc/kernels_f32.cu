@@ -786,6 +786,7 @@ __global__ void __launch_bounds__(1024) heads_kernel(const HeadArgs a) {
     float* Gn = a.Gn ? a.Gn + ((size_t)b * a.nmat + mat) * msize : nullptr;
     float* Ss = a.Ssym ? a.Ssym + ((size_t)b * a.nmat + mat) * msize : nullptr;
     __nv_bfloat16* Sb = a.Ssym_bf16 ? a.Ssym_bf16 + ((size_t)b * a.nmat + mat) * msize : nullptr;
+    __nv_bfloat16* Sbl = a.Ssym_bf16_lo ? a.Ssym_bf16_lo + ((size_t)b * a.nmat + mat) * msize : nullptr;
     const int ld = n + 1;
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
@@ -813,6 +814,7 @@ __global__ void __launch_bounds__(1024) heads_kernel(const HeadArgs a) {
         const float v = dgs[i * ld + j] + dgs[j * ld + i];
         Ss[e] = v;
         if (Sb) Sb[e] = __float2bfloat16_rn(v);
+        if (Sbl) Sbl[e] = __float2bfloat16_rn(v - __bfloat162float(__float2bfloat16_rn(v)));
     }
 }
 // The same head for the Gatys matrices (n = 128) with a CLUSTER of 4 CTAs per matrix: 30 one-CTA launches of the kernel
@@ -930,6 +932,7 @@ __global__ void __cluster_dims__(HG_CL, 1, 1) __launch_bounds__(HG_THREADS) head
     float* Gn = a.Gn ? a.Gn + ((size_t)b * a.nmat + mat) * msize : nullptr;
     float* Ss = a.Ssym ? a.Ssym + ((size_t)b * a.nmat + mat) * msize : nullptr;
     __nv_bfloat16* Sb = a.Ssym_bf16 ? a.Ssym_bf16 + ((size_t)b * a.nmat + mat) * msize : nullptr;
+    __nv_bfloat16* Sbl = a.Ssym_bf16_lo ? a.Ssym_bf16_lo + ((size_t)b * a.nmat + mat) * msize : nullptr;
 #pragma unroll
     for (int k = 0; k < HG_E; ++k) {
         const int e = e0 + k * HG_THREADS;
@@ -953,6 +956,7 @@ __global__ void __cluster_dims__(HG_CL, 1, 1) __launch_bounds__(HG_THREADS) head
             const float val = dgs[i - rank * 32][j] + *peer;
             Ss[e] = val;
             if (Sb) Sb[e] = __float2bfloat16_rn(val);
+            if (Sbl) Sbl[e] = __float2bfloat16_rn(val - __bfloat162float(__float2bfloat16_rn(val)));
         }
     }
     cl.sync();                                   // nobody exits while a peer may still read its shared memory

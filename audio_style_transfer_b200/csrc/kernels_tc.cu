@@ -620,6 +620,8 @@ struct TcState {
     CUtensorMap tm_dz_lo, tm_w1b_lo, tm_w2b_lo;
     const float* dF;
     __nv_bfloat16 *F, *ssym;                   // Gatys head: bf16 extracts [n_fslots][R][128], bf16 Ssym [B*n_fslots][128][128]
+    __nv_bfloat16 *F_lo, *ssym_lo;             // accurate tier: their lo parts
+    CUtensorMap tm_F_lo, tm_ssym_lo;
     int n_fslots;
     __half* Ht; int n_tslots;                  // transposed fp16 extract copies [R/32][n_tslots][128][32] of the channel-wise head, or NULL (owned by the caller)
     CUtensorMap tm_F, tm_ssym, tm_gpart, tm_dF_st;
@@ -741,6 +743,14 @@ TcState* tc_create(int T, int B, int NL, float* H, float* g, float* dF, int n_he
              make_rows_map(&s->tm_ssym, s->ssym, false, (size_t)B * n_fslots * AST_C, 128) &&
              make_rows_map(&s->tm_gpart, gram_part, true, (size_t)gram_part_mats * AST_C, 32) &&
              make_act_map(&s->tm_dF_st, dF, true, T, B, n_head > 0 ? n_head : 1, 32) && setup_gram_tc_kernels() == 0;
+        if (ok && split) {                       // the accurate tier's heads multiply hi / lo pairs of the extracts and of Ssym
+            if (cudaMalloc(&s->F_lo, fb) != cudaSuccess || cudaMalloc(&s->ssym_lo, sb) != cudaSuccess) {
+                *why = "cudaMalloc failed"; tc_destroy(s); return nullptr;
+            }
+            *bytes += (int64_t)(fb + sb);
+            ok = make_act_map(&s->tm_F_lo, s->F_lo, false, T, B, n_fslots, 128) &&
+                 make_rows_map(&s->tm_ssym_lo, s->ssym_lo, false, (size_t)B * n_fslots * AST_C, 128);
+        }
     }
     if (!ok) { *why = "cuTensorMapEncodeTiled failed"; tc_destroy(s); return nullptr; }
     if (cudaFuncSetAttribute(tc_fwd_stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, F2_SMEM) != cudaSuccess ||
@@ -759,7 +769,7 @@ void tc_destroy(TcState* s) {
     if (!s) return;
     cudaFree(s->a_hi); cudaFree(s->a_lo); cudaFree(s->dz);
     cudaFree(s->w1f); cudaFree(s->w2f); cudaFree(s->w1b); cudaFree(s->w2b);
-    cudaFree(s->F); cudaFree(s->ssym); cudaFree(s->flags); cudaFree(s->ll_f); cudaFree(s->ll_b);
+    cudaFree(s->F); cudaFree(s->ssym); cudaFree(s->F_lo); cudaFree(s->ssym_lo); cudaFree(s->flags); cudaFree(s->ll_f); cudaFree(s->ll_b);
     cudaFree(s->dz_lo); cudaFree(s->w1b_lo); cudaFree(s->w2b_lo);
     delete s;
 }
@@ -911,7 +921,7 @@ int tc_forward_stack(TcState* s, const float* x, const float* W0, const float* b
     memset(&a, 0, sizeof(a));
     a.tmA_hi = s->tm_a_hi; a.tmA_lo = s->tm_a_lo; a.tmW1 = s->tm_w1f; a.tmW2 = s->tm_w2f;
     a.x = x; a.W0 = W0; a.b0 = b0; a.bd = bd; a.br = br; a.H = H; a.zmask = zmask; a.hmask = hmask;
-    a.a_hi = s->a_hi; a.a_lo = s->a_lo; a.F = s->F;
+    a.a_hi = s->a_hi; a.a_lo = s->a_lo; a.F = s->F; a.F_lo = s->F_lo;
     a.flags = s->flags; a.err = tc_stack_err(s); a.epoch = tc_stack_err(s) + 2; a.ll = s->ll_f;
     a.T = s->T; a.R = s->R; a.NL = s->NL; a.tiles_per_pair = s->T / 128; a.ntiles = s->R / 128;
     for (int l = 0; l < 32; ++l) a.f_slot[l] = (signed char)((s->n_fslots > 0 && l < s->NL) ? f_slot[l] : -1);
@@ -1032,18 +1042,21 @@ void tc_gram(TcState* s, int L, int nchunk, int chunk_tiles, int tile_lo, int ti
     GramTcArgs a;
     memset(&a, 0, sizeof(a));
     a.tmF = s->tm_F; a.tmP = s->tm_gpart;
+    if (s->split) a.tmFlo = s->tm_F_lo;
     a.L = L; a.chunk_tiles = chunk_tiles; a.tile_lo = tile_lo; a.tile_hi = tile_hi;
-    launch_gram_tc(a, nchunk, L, s->B, st);
+    launch_gram_tc(a, nchunk, L, s->B, s->split, st);
 }
 __nv_bfloat16* tc_ssym_bf16(TcState* s) { return s ? s->ssym : nullptr; }
+__nv_bfloat16* tc_ssym_bf16_lo(TcState* s) { return s ? s->ssym_lo : nullptr; }
 void tc_style_grad(TcState* s, int L, const int* head_of_slot, cudaStream_t st) {
     SGradTcArgs a;
     memset(&a, 0, sizeof(a));
     a.tmF = s->tm_F; a.tmS = s->tm_ssym; a.tmDF = s->tm_dF_st;
+    if (s->split) { a.tmFlo = s->tm_F_lo; a.tmSlo = s->tm_ssym_lo; }
     a.T = s->T; a.L = L;
     for (int i = 0; i < L && i < 32; ++i) {
         a.head_of_slot[i] = head_of_slot[i];
         if (head_of_slot[i] >= 0) a.slot_of[a.n_active++] = i;
     }
-    if (a.n_active > 0) launch_sgrad_tc(a, s->R / 128, st);
+    if (a.n_active > 0) launch_sgrad_tc(a, s->R / 128, s->split, st);
 }

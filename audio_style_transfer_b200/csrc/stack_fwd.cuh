@@ -88,6 +88,7 @@ struct alignas(64) FwdStackArgs {
     uint32_t* zmask; uint32_t* hmask;            // [NL][R][4], [NL+1][R][4]
     __nv_bfloat16* a_hi; __nv_bfloat16* a_lo;    // the buffers behind tmA_* (published with plain stores)
     __nv_bfloat16* F;                // bf16 extract copies [n_style][R][128]
+    __nv_bfloat16* F_lo;             // accurate tier: bf16(h - float(bf16(h))), same layout, or NULL
     __half* Ht;                      // transposed fp16 extract copies [R/32][n_tslots][128][32 rows] (channel-wise head, gram_ours_tma.cu) or NULL
     int n_tslots;
     uint4* ll;                       // near hand-off lines [2][ntiles][2 sides][2 K-halves][4 cc][2 parts][4][32 rows] x 16 B
@@ -581,10 +582,18 @@ __global__ void __launch_bounds__(F2_THREADS, 1) tc_fwd_stack_kernel(const __gri
                                      __float_as_uint(v[8 * e + 3]), __float_as_uint(v[8 * e + 4]), __float_as_uint(v[8 * e + 5]),
                                      __float_as_uint(v[8 * e + 6]), __float_as_uint(v[8 * e + 7]));
                 }
-                if (f >= 0)                            // bf16 extract copy: 16 columns = 32 bytes = one full sector per thread
+                if (f >= 0 && !p.F_lo)                 // bf16 extract copy: 16 columns = 32 bytes = one full sector per thread
                     st_global_v8(p.F + ((size_t)f * p.R + row) * AST_C + col,
                                  pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]),
                                  pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]), pack_bf16(v[14], v[15]));
+                if (f >= 0 && p.F_lo) {                // accurate tier: hi and lo parts
+                    uint32_t Fh[8], Fl[8];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) split_bf16x2(v[2 * e], v[2 * e + 1], Fh[e], Fl[e]);
+                    const size_t fo = ((size_t)f * p.R + row) * AST_C + col;
+                    st_global_v8(p.F + fo, Fh[0], Fh[1], Fh[2], Fh[3], Fh[4], Fh[5], Fh[6], Fh[7]);
+                    st_global_v8(p.F_lo + fo, Fl[0], Fl[1], Fl[2], Fl[3], Fl[4], Fl[5], Fl[6], Fl[7]);
+                }
                 if (ts >= 0) {                         // transposed fp16 copy [row / 32][slot][channel][row % 32]: a warp's 32 rows of one channel = one 64-byte run
                     __half* ht = p.Ht + ((((size_t)(row >> 5) * p.n_tslots + ts) * AST_C + col) << 5) + (row & 31);
 #pragma unroll

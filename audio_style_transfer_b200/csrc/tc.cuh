@@ -56,14 +56,16 @@ void tc_layer_bwd(TcState* s, int l, const uint32_t* hmask_in, int df_idx, int s
 
 // Gatys Gram partials of the owned tiles [tile_lo, tile_hi) of every pair: part[(b*L+l)][chunk][128][128]
 void tc_gram(TcState* s, int L, int nchunk, int chunk_tiles, int tile_lo, int tile_hi, cudaStream_t st);
-// bf16 image of Ssym that the heads kernel fills ([B*L][128][128]), or NULL
+// bf16 image of Ssym that the heads kernel fills ([B*L][128][128]), or NULL; its lo part (accurate tier), or NULL
 __nv_bfloat16* tc_ssym_bf16(TcState* s);
+__nv_bfloat16* tc_ssym_bf16_lo(TcState* s);
 // dF[head_of_slot[i]] = F[i] . Ssym[i] for every style slot i with head_of_slot[i] >= 0
 void tc_style_grad(TcState* s, int L, const int* head_of_slot, cudaStream_t st);
 
 // ---- gram_tc.cu ------------------------------------------------------------------------------------
 struct alignas(64) GramTcArgs {
     CUtensorMap tmF;                 // bf16 [L][B][T][128], box {64,128,1,1}
+    CUtensorMap tmFlo;               // accurate tier: the lo parts bf16(h - float(bf16(h))), same layout
     CUtensorMap tmP;                 // fp32 partials as rows [mats*128][128], box {32,32}
     int L, chunk_tiles, tile_lo, tile_hi;
 };
@@ -71,11 +73,12 @@ struct alignas(64) SGradTcArgs {
     CUtensorMap tmF;                 // bf16 [L][B][T][128], box {64,128,1,1}
     CUtensorMap tmS;                 // bf16 Ssym rows [B*L*128][128], box {64,128}
     CUtensorMap tmDF;                // fp32 [n_head][B][T][128], store box {32,32,1,1}
+    CUtensorMap tmFlo, tmSlo;        // accurate tier: lo parts of F and Ssym
     int T, L;
     int n_active;                    // grid.y: only slots that need the standalone kernel are launched
     int slot_of[32];                 // blockIdx.y -> style slot
     int head_of_slot[32];            // style slot -> dF buffer
 };
-void launch_gram_tc(const GramTcArgs& a, int nchunk, int L, int B, cudaStream_t s);
-void launch_sgrad_tc(const SGradTcArgs& a, int ntiles, cudaStream_t s);
+void launch_gram_tc(const GramTcArgs& a, int nchunk, int L, int B, bool split, cudaStream_t s);
+void launch_sgrad_tc(const SGradTcArgs& a, int ntiles, bool split, cudaStream_t s);
 int setup_gram_tc_kernels();
