@@ -58,8 +58,9 @@ extern "C" {
 #define AST_PATH_PER_LAYER_BWD 2   /* whole-stack forward, one kernel per layer in the backward   */
 
 #define AST_PREC_TC3      2   /* accurate tensor-core tier: the dilated / 1x1 convs and their transposes on tcgen05 with  */
-                              /* 2-term bf16 operand splits BOTH ways (3 MMAs per product, fp32 accumulate in TMEM); heads  */
-                              /* (Gram, normalise, losses, head gradients) in fp32 on CUDA cores from the fp32 extracts     */
+                              /* 2-term bf16 operand splits BOTH ways (3 MMAs per product, fp32 accumulate in TMEM); Gatys   */
+                              /* Gram and style gradient likewise on tcgen05 from hi / lo bf16 copies of the extracts;      */
+                              /* channel-wise Gram and style gradient, normalisation and losses in fp32 on CUDA cores        */
 
 #define AST_MAX_IDS      32
 #define AST_CHANNELS    128   /* ae_width, model.py:73 */
