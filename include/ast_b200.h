@@ -128,7 +128,11 @@ int  ast_embeds(ast_ctx* ctx, const float* d_x, float* d_Ec, float* d_Gn, void* 
 
 /* One function evaluation of the L-BFGS-B loop (methods.py:133-137,167):
  * d_losses [B,4] = {total, content, style, regulariser}, d_grad [B,T] = d total / d x.
- * Asynchronous on `stream`, no host sync, CUDA-graph capturable. */
+ * Asynchronous on `stream`, no host sync, CUDA-graph capturable.
+ * A context holds ONE evaluation's activations, masks and hand-off flags: evaluations of the same context (ast_step*,
+ * ast_embeds, ast_minimize; ast_step_host runs on the context's private stream) must not overlap on the GPU --
+ * order them on one stream or synchronise between streams; overlapping ones fail loudly (AST_ECUDA from ast_check /
+ * ast_step_host: hand-off timed out).  Different contexts are independent. */
 int  ast_step(ast_ctx* ctx, const float* d_x, float* d_losses, float* d_grad, void* stream);
 
 /* ast_step replayed from a captured CUDA graph (north_star (e)): captured on first use for this
