@@ -27,6 +27,7 @@ CASES = {
     # BASELINE.json sizes
     "t16384_cfg0":      (16384, [25], 0, None, False, 128, 128, 1),
     "t16384_cfg1":      (16384, [29], None, None, True, 128, 128, 1),
+    "t16384_cli":       (16384, [25], None, None, False, 128, 128, 1),  # methods.py CLI defaults at full size: all 30 layers channel-wise (bench --workload cli, cfg4's head)
     # BASELINE configs[2]: 4 s clip (time-sharded on the GPU), cfg0's layer set
     "t65536_cfg2":      (65536, [25], 0, None, False, 128, 128, 1),
 }

@@ -112,10 +112,11 @@ def test_step_matches_oracle(name, prec):
 
 
 @pytest.mark.parametrize("prec", PRECS)
-@pytest.mark.parametrize("name", ["t16384_cfg0", "t16384_cfg1"])
+@pytest.mark.parametrize("name", ["t16384_cfg0", "t16384_cfg1", "t16384_cli"])
 def test_baseline_size_matches_oracle_and_golden(name, prec, golden_dir):
-    """BASELINE.json configs[0]/[1] sizes: oracle computed here (tens of seconds) and cross-checked
-    with the committed golden vectors, then the CUDA step against both."""
+    """BASELINE.json configs[0]/[1] sizes and the methods.py CLI defaults (all 30 layers channel-wise: cfg4's head) at
+    16384 samples: oracle computed here (tens of seconds) and cross-checked with the committed golden vectors, then
+    the CUDA step against both."""
     case = cases.build_inputs(name)
     Pc, Ps = cases.oracle_targets(case)
     losses, dx, aux = cases.oracle_step(case, Pc, Ps, return_aux=True)
