@@ -51,6 +51,29 @@ def test_plan_windows_hold_the_stft_frames_of_the_owned_samples():
     assert short[1][2] - short[1][0] < 1024
 
 
+def test_exchange_windows_and_the_capture_guard():
+    """Halo-exchange windows: owned range +- 2 * 1024 rows, every owned range long enough for what the neighbours fetch;
+    capture() (one CUDA graph per rank) is refused unless the halos are peer-mapped -- the NCCL send/recv route exchanges
+    rows between host calls."""
+    for T, P in [(65536, 2), (65536, 8), (479232, 8), (479232, 4)]:
+        plan = sharding.plan_windows_exchange(T, P)
+        assert plan[0][2] == 0 and plan[-1][3] == T
+        for (wb, we, ob, oe), nxt in zip(plan, plan[1:] + [None]):
+            assert wb == max(0, ob - 2 * sharding.HALO) and we == min(T, oe + 2 * sharding.HALO)
+            assert oe - ob >= 2 * sharding.HALO and ob % 128 == 0 and oe % 128 == 0
+            if nxt:
+                assert oe == nxt[2]
+    with pytest.raises(ValueError):
+        sharding.plan_windows_exchange(16384, 16)          # 1024-sample shards cannot serve 2048 halo rows
+
+    class Ctx:
+        segments = 3
+    hs = sharding.HaloShardedStep(65536, 1, 4, lambda Tw, window: Ctx(), lambda p: None, lambda pairs: None)
+    assert (hs.up, hs.dn) == (0, 2) and hs.we - hs.wb == 16384 + 4 * sharding.HALO
+    with pytest.raises(RuntimeError, match="attach_p2p"):
+        hs.capture(None, None, None)
+
+
 def test_pairs_for_rank_cover_every_pair_once():
     got = sorted(p for r in range(8) for p in sharding.pairs_for_rank(64, r, 8))
     assert got == list(range(64))
